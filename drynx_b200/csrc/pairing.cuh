@@ -1,0 +1,221 @@
+// Optimal ate pairing e: G1 x G2 -> GT on BN256, plus GT exponentiation.
+// Replaces kyber v3.0.8 pairing/bn256 optate.go (miller, finalExponentiation, optimalAte) and the GT
+// "Add"/"Mul" used by lib/range/range_proof.go:396-397 and :540-546.
+//   e(P, Q) = ( f_{6u+2,Q}(P) * l_{[6u+2]Q, pi(Q)}(P) * l_{[6u+2]Q + pi(Q), -pi^2(Q)}(P) ) ^ ((p^12 - 1)/n)
+// The reduced value is canonical, so this file is free to differ from kyber's algorithm: lines are
+// multiplied in as sparse elements (13 Fp2 products), the hard part of the final exponentiation runs on
+// Granger-Scott cyclotomic squarings, and inverses in the cyclotomic subgroup are conjugations.
+#pragma once
+#include "curve.cuh"
+
+namespace drx {
+
+struct TwistJ {  // Jacobian point on the twist with cached t = z^2
+  Fp2 x, y, z, t;
+};
+
+// Tangent at r evaluated at the G1 point q; r <- 2r. Line = c + b*w + a*w^3.
+DRX_NI void line_dbl(Fp2& a, Fp2& b, Fp2& c, TwistJ& r, const G1Aff& q) {
+  const Fp2 A = fp2_sqr(r.x);
+  const Fp2 B = fp2_sqr(r.y);
+  const Fp2 C = fp2_sqr(B);
+  Fp2 D = fp2_sub(fp2_sub(fp2_sqr(fp2_add(r.x, B)), A), C);
+  D = fp2_dbl(D);
+  const Fp2 E = fp2_add(fp2_dbl(A), A);
+  const Fp2 G = fp2_sqr(E);
+  TwistJ o;
+  o.x = fp2_sub(fp2_sub(G, D), D);
+  o.z = fp2_sub(fp2_sub(fp2_sqr(fp2_add(r.y, r.z)), B), r.t);
+  Fp2 t = fp2_dbl(C);
+  t = fp2_dbl(t);
+  t = fp2_dbl(t);
+  o.y = fp2_sub(fp2_mul(fp2_sub(D, o.x), E), t);
+  o.t = fp2_sqr(o.z);
+  t = fp2_dbl(fp2_mul(E, r.t));
+  b = fp2_mul_fp(fp2_neg(t), q.x);
+  a = fp2_sub(fp2_sub(fp2_sqr(fp2_add(r.x, E)), A), G);
+  t = fp2_dbl(B);
+  t = fp2_dbl(t);
+  a = fp2_sub(a, t);
+  c = fp2_mul_fp(fp2_dbl(fp2_mul(o.z, r.t)), q.y);
+  r = o;
+}
+
+// Chord through r and the affine twist point p (with p.y^2 = r2) evaluated at q; r <- r + p.
+DRX_NI void line_add(Fp2& a, Fp2& b, Fp2& c, TwistJ& r, const G2Aff& p, const G1Aff& q, const Fp2& r2) {
+  const Fp2 B = fp2_mul(p.x, r.t);
+  Fp2 D = fp2_sub(fp2_sub(fp2_sqr(fp2_add(p.y, r.z)), r2), r.t);
+  D = fp2_mul(D, r.t);
+  const Fp2 H = fp2_sub(B, r.x);
+  const Fp2 I = fp2_sqr(H);
+  Fp2 E = fp2_dbl(I);
+  E = fp2_dbl(E);
+  const Fp2 J = fp2_mul(H, E);
+  const Fp2 L1 = fp2_sub(fp2_sub(D, r.y), r.y);
+  const Fp2 V = fp2_mul(r.x, E);
+  TwistJ o;
+  o.x = fp2_sub(fp2_sub(fp2_sub(fp2_sqr(L1), J), V), V);
+  o.z = fp2_sub(fp2_sub(fp2_sqr(fp2_add(r.z, H)), r.t), I);
+  Fp2 t = fp2_mul(fp2_sub(V, o.x), L1);
+  Fp2 t2 = fp2_dbl(fp2_mul(r.y, J));
+  o.y = fp2_sub(t, t2);
+  o.t = fp2_sqr(o.z);
+  t = fp2_sub(fp2_sub(fp2_sqr(fp2_add(p.y, o.z)), r2), o.t);
+  t2 = fp2_dbl(fp2_mul(L1, p.x));
+  a = fp2_sub(t2, t);
+  c = fp2_dbl(fp2_mul_fp(o.z, q.y));
+  b = fp2_dbl(fp2_mul_fp(fp2_neg(L1), q.x));
+  r = o;
+}
+
+// Miller function value for affine, finite P in G1 and Q in G2.
+DRX_NI void miller_loop(Fp12& f, const G1Aff& P, const G2Aff& Q) {
+  f = fp12_one();
+  TwistJ r;
+  r.x = Q.x;
+  r.y = Q.y;
+  r.z = fp2_one();
+  r.t = fp2_one();
+  const G2Aff mQ = aff_neg(Q);
+  Fp2 r2 = fp2_sqr(Q.y);
+  Fp2 a, b, c;
+  for (int i = DRX_ATE_NAF_LEN - 1; i > 0; i--) {
+    line_dbl(a, b, c, r, P);
+    if (i != DRX_ATE_NAF_LEN - 1) fp12_sqr(f, f);
+    fp12_mul_line(f, f, c, b, a);
+    const int d = ate_naf(i - 1);
+    if (d == 1) {
+      line_add(a, b, c, r, Q, P, r2);
+      fp12_mul_line(f, f, c, b, a);
+    } else if (d == -1) {
+      line_add(a, b, c, r, mQ, P, r2);
+      fp12_mul_line(f, f, c, b, a);
+    }
+  }
+  // pi(Q) and -pi^2(Q) on the twist
+  G2Aff q1, mq2;
+  q1.x = fp2_mul(fp2_conj(Q.x), K_XI_P_1_3());
+  q1.y = fp2_mul(fp2_conj(Q.y), K_XI_P_1_2());
+  mq2.x = fp2_mul_fp(Q.x, K_XI_P2_1_3());
+  mq2.y = Q.y;
+  r2 = fp2_sqr(q1.y);
+  line_add(a, b, c, r, q1, P, r2);
+  fp12_mul_line(f, f, c, b, a);
+  r2 = fp2_sqr(mq2.y);
+  line_add(a, b, c, r, mq2, P, r2);
+  fp12_mul_line(f, f, c, b, a);
+}
+
+// a^u for a in the cyclotomic subgroup (u = 6518589491078791937, 63 bits)
+DRX_NI void fp12_pow_u(Fp12& r, const Fp12& a) {
+  const uint64_t u = ((uint64_t)DRX_U_HI << 32) | DRX_U_LO;
+  Fp12 acc = a;
+  for (int i = 61; i >= 0; i--) {  // bit 62 is the leading one
+    fp12_cyclo_sqr(acc, acc);
+    if ((u >> i) & 1) fp12_mul(acc, acc, a);
+  }
+  r = acc;
+}
+
+// f^((p^12-1)/n): easy part (p^6-1)(p^2+1), then the Scott et al. addition chain for (p^4-p^2+1)/n.
+DRX_NI void final_exp(Fp12& out, const Fp12& in) {
+  Fp12 t1, t2, inv;
+  fp12_conj(t1, in);
+  fp12_inv(inv, in);
+  fp12_mul(t1, t1, inv);  // in^(p^6-1)
+  fp12_frob2(t2, t1);
+  fp12_mul(t1, t1, t2);   // ^(p^2+1): now in the cyclotomic subgroup
+
+  Fp12 fp1, fp2, fp3, fu, fu2, fu3;
+  fp12_frob1(fp1, t1);
+  fp12_frob2(fp2, t1);
+  fp12_frob1(fp3, fp2);
+  fp12_pow_u(fu, t1);
+  fp12_pow_u(fu2, fu);
+  fp12_pow_u(fu3, fu2);
+
+  Fp12 y0, y1, y2, y3, y4, y5, y6, tmp;
+  fp12_mul(y0, fp1, fp2);
+  fp12_mul(y0, y0, fp3);
+  fp12_conj(y1, t1);
+  fp12_frob2(y2, fu2);
+  fp12_frob1(y3, fu);
+  fp12_conj(y3, y3);
+  fp12_frob1(tmp, fu2);
+  fp12_mul(y4, fu, tmp);
+  fp12_conj(y4, y4);
+  fp12_conj(y5, fu2);
+  fp12_frob1(tmp, fu3);
+  fp12_mul(y6, fu3, tmp);
+  fp12_conj(y6, y6);
+
+  Fp12 t0;
+  fp12_cyclo_sqr(t0, y6);
+  fp12_mul(t0, t0, y4);
+  fp12_mul(t0, t0, y5);
+  fp12_mul(t1, y3, y5);
+  fp12_mul(t1, t1, t0);
+  fp12_mul(t0, t0, y2);
+  fp12_cyclo_sqr(t1, t1);
+  fp12_mul(t1, t1, t0);
+  fp12_cyclo_sqr(t1, t1);
+  fp12_mul(t0, t1, y1);
+  fp12_mul(t1, t1, y0);
+  fp12_cyclo_sqr(t0, t0);
+  fp12_mul(out, t0, t1);
+}
+
+// e(P, Q); either argument at infinity gives 1 (kyber optimalAte)
+DRX_NI void pairing(Fp12& out, const G1Aff& P, const G2Aff& Q) {
+  if (aff_is_inf(P) | aff_is_inf(Q)) {
+    out = fp12_one();
+    return;
+  }
+  Fp12 f;
+  miller_loop(f, P, Q);
+  final_exp(out, f);
+}
+
+// Fixed-base GT exponentiation: table[w * 255 + d - 1] = g^(d * 2^(8w)).
+DRX_NI void gt_comb_pow(Fp12& out, const Fp12* __restrict__ table, const Scalar& k) {
+  Fp12 acc = fp12_one();
+  bool any = false;
+  for (int w = 0; w < DRX_COMB_WINDOWS; w++) {
+    const uint32_t d = (k.v[w >> 2] >> ((w & 3) * 8)) & 0xffu;
+    if (d) {
+      const Fp12* e = &table[w * DRX_COMB_ENTRIES + (int)d - 1];
+      if (any) {
+        fp12_mul(acc, acc, *e);
+      } else {
+        acc = *e;
+        any = true;
+      }
+    }
+  }
+  out = acc;
+}
+
+// ------------------------------------------------------------------ wire helpers for G2 / GT
+// kyber GT MarshalBinary order x.x x.y x.z y.x y.y y.z = w^5 w^3 w^1 w^4 w^2 w^0, each Fp2 as (c1, c0).
+DRX_HD const Fp2& fp12_wire_slot(const Fp12& a, int s) {
+  switch (s) {
+    case 0: return a.c1.c2;
+    case 1: return a.c1.c1;
+    case 2: return a.c1.c0;
+    case 3: return a.c0.c2;
+    case 4: return a.c0.c1;
+    default: return a.c0.c0;
+  }
+}
+DRX_HD Fp2& fp12_wire_slot(Fp12& a, int s) {
+  switch (s) {
+    case 0: return a.c1.c2;
+    case 1: return a.c1.c1;
+    case 2: return a.c1.c0;
+    case 3: return a.c0.c2;
+    case 4: return a.c0.c1;
+    default: return a.c0.c0;
+  }
+}
+
+}  // namespace drx

@@ -1,0 +1,105 @@
+// TEST-ONLY host build of the device headers (drynx_b200/csrc/*.cuh compiled with g++ and DRX_HOST_EMU).
+// The carry-flag wrappers in fp.cuh model PTX add.cc/madc.* in C, so these entry points execute the same
+// instruction sequences the sm_100a kernels run. Nothing in the drynx_b200 package or the shipped
+// libdrynx_gpu.so links or loads this file; it exists so `pytest -m "not gpu"` can check the GPU algorithms
+// against the oracle without a GPU.
+#define DRX_HOST_EMU 1
+#include "wire.cuh"
+#include <cstring>
+using namespace drx;
+
+static void load_words(uint32_t* w, const uint8_t* b, int nbytes) { memcpy(w, b, nbytes); }
+
+extern "C" {
+
+int emu_fp_mul_raw(const uint32_t* a, const uint32_t* b, uint32_t* r, int which) {
+  if (which == 0) mont_mul<ModP>(r, a, b); else mont_mul<ModN>(r, a, b);
+  return 0;
+}
+
+int emu_g1_mul(const uint8_t* k32, const uint8_t* pt64, uint8_t* out64, int method) {
+  uint32_t kw[8], pw[16], ow[16];
+  load_words(kw, k32, 32); load_words(pw, pt64, 64);
+  G1Aff p; if (!g1_from_wire(p, pw)) return -1;
+  Scalar k = sc_from_wire(kw);
+  G1Jac r;
+  if (method == 0) {
+    r = window_mul(jac_from_aff(p), k);
+  } else {  // comb: build the table on the fly
+    static thread_local G1Aff table[DRX_COMB_WINDOWS * DRX_COMB_ENTRIES];
+    G1Jac base = jac_from_aff(p);
+    for (int w = 0; w < DRX_COMB_WINDOWS; w++) {
+      G1Jac acc = base;
+      for (int d = 1; d <= 255; d++) {
+        table[w * 255 + d - 1] = jac_to_aff(acc);
+        acc = jac_add(acc, base);
+      }
+      for (int s = 0; s < 8; s++) base = jac_dbl(base);
+    }
+    r = comb_mul(table, k);
+  }
+  g1_to_wire(ow, jac_to_aff(r)); memcpy(out64, ow, 64);
+  return 0;
+}
+
+int emu_g1_add(const uint8_t* a64, const uint8_t* b64, uint8_t* out64) {
+  uint32_t aw[16], bw[16], ow[16];
+  load_words(aw, a64, 64); load_words(bw, b64, 64);
+  G1Aff a, b; if (!g1_from_wire(a, aw) || !g1_from_wire(b, bw)) return -1;
+  G1Jac r = jac_add_aff(jac_from_aff(a), b);
+  g1_to_wire(ow, jac_to_aff(r)); memcpy(out64, ow, 64);
+  return 0;
+}
+
+int emu_g2_mul(const uint8_t* k32, const uint8_t* pt128, uint8_t* out128) {
+  uint32_t kw[8], pw[32], ow[32];
+  load_words(kw, k32, 32); load_words(pw, pt128, 128);
+  G2Aff p; if (!g2_from_wire(p, pw)) return -1;
+  G2Jac r = window_mul(jac_from_aff(p), sc_from_wire(kw));
+  g2_to_wire(ow, jac_to_aff(r)); memcpy(out128, ow, 128);
+  return 0;
+}
+
+int emu_pair(const uint8_t* g1, const uint8_t* g2, uint8_t* gt384) {
+  uint32_t aw[16], bw[32], ow[96];
+  load_words(aw, g1, 64); load_words(bw, g2, 128);
+  G1Aff p; G2Aff q;
+  if (!g1_from_wire(p, aw) || !g2_from_wire(q, bw)) return -1;
+  Fp12 e; pairing(e, p, q);
+  gt_to_wire(ow, e); memcpy(gt384, ow, 384);
+  return 0;
+}
+
+// checks internal identities that have no wire-level witness: cyclotomic squaring == generic squaring on a
+// pairing value, Frobenius maps compose, inverse. Returns a bitmask of failures.
+int emu_tower_selfcheck(const uint8_t* gt384) {
+  uint32_t w[96]; load_words(w, gt384, 384);
+  Fp12 a; if (!gt_from_wire(a, w)) return -1;
+  int bad = 0;
+  Fp12 s1, s2; fp12_sqr(s1, a); fp12_cyclo_sqr(s2, a); if (!fp12_eq(s1, s2)) bad |= 1;
+  Fp12 m; fp12_mul(m, a, a); if (!fp12_eq(s1, m)) bad |= 2;
+  Fp12 f1, f2, f11; fp12_frob1(f1, a); fp12_frob1(f11, f1); fp12_frob2(f2, a); if (!fp12_eq(f11, f2)) bad |= 4;
+  Fp12 f3, f21; fp12_frob3(f3, a); fp12_frob1(f21, f2); if (!fp12_eq(f3, f21)) bad |= 8;
+  Fp12 iv, one; fp12_inv(iv, a); fp12_mul(one, iv, a); if (!fp12_is_one(one)) bad |= 16;
+  Fp12 cj; fp12_conj(cj, a); fp12_mul(one, cj, a); if (!fp12_is_one(one)) bad |= 32;  // unitary: conj = inverse
+  Fp6 x = a.c0, xi, xo; fp6_inv(xi, x); fp6_mul(xo, xi, x); if (!fp6_eq(xo, fp6_one())) bad |= 64;
+  Fp6 q1, q2; fp6_sqr(q1, x); fp6_mul(q2, x, x); if (!fp6_eq(q1, q2)) bad |= 128;
+  return bad;
+}
+
+int emu_gt_pow(const uint8_t* gt384, const uint8_t* k32, uint8_t* out384) {
+  uint32_t w[96], kw[8], ow[96]; load_words(w, gt384, 384); load_words(kw, k32, 32);
+  Fp12 g; if (!gt_from_wire(g, w)) return -1;
+  static thread_local Fp12 table[DRX_COMB_WINDOWS * DRX_COMB_ENTRIES];
+  Fp12 base = g;
+  for (int win = 0; win < DRX_COMB_WINDOWS; win++) {
+    Fp12 acc = base;
+    for (int d = 1; d <= 255; d++) { table[win * 255 + d - 1] = acc; fp12_mul(acc, acc, base); }
+    base = acc;  // base^256
+  }
+  Fp12 r; gt_comb_pow(r, table, sc_from_wire(kw));
+  gt_to_wire(ow, r); memcpy(out384, ow, 384);
+  return 0;
+}
+
+}  // extern "C"
