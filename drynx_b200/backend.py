@@ -1,0 +1,191 @@
+"""Python host mirror of the reference's call surface over the C ABI (bytes in, bytes out).
+
+Names follow the Go functions they stand in for (libunlynx.EncryptIntVector, CipherVector.Add,
+DecryptIntVectorWithNeg, CreateDecryptionTable; libdrynxrange.InitRangeProofSignature,
+CreatePredicateRangeProofListForAllServers, RangeProofListVerification). Buffers are bytes / numpy arrays;
+no arithmetic happens here."""
+import ctypes
+
+import numpy as np
+
+from . import _lib
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, (bytes, bytearray)):
+        return ctypes.cast(ctypes.c_char_p(bytes(a)), ctypes.c_void_p)
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+def _u8(b):
+    return np.frombuffer(bytes(b), dtype=np.uint8).copy() if not isinstance(b, np.ndarray) else np.ascontiguousarray(b, dtype=np.uint8)
+
+
+class Backend:
+    """One drx_ctx on one GPU."""
+
+    def __init__(self, device=0, g1_base=None, g2_base=None):
+        self.lib = _lib.load()
+        h = ctypes.c_void_p()
+        g1 = _u8(g1_base) if g1_base is not None else None
+        g2 = _u8(g2_base) if g2_base is not None else None
+        _lib.check(self.lib.drx_init(ctypes.byref(h), device, _ptr(g1), _ptr(g2)))
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, 'h', None):
+            self.lib.drx_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- plumbing
+    def set_stream(self, cuda_stream):
+        _lib.check(self.lib.drx_set_stream(self.h, ctypes.c_void_p(cuda_stream)))
+
+    def synchronize(self):
+        _lib.check(self.lib.drx_synchronize(self.h))
+
+    @property
+    def launches(self):
+        return int(self.lib.drx_launch_count(self.h))
+
+    # ---- ElGamal (libunlynx lib/crypto.go call surface)
+    def set_pubkey(self, P):
+        p = _u8(P)
+        _lib.check(self.lib.drx_set_pubkey(self.h, _ptr(p)))
+
+    def encrypt_int_vector(self, m, r):
+        """EncryptIntVectorGetRs with injected scalars: m int64[n], r bytes n*32 -> n*128 bytes."""
+        m = np.ascontiguousarray(m, dtype=np.int64)
+        r = _u8(r)
+        assert r.size == 32 * m.size
+        ct = np.empty(128 * m.size, dtype=np.uint8)
+        _lib.check(self.lib.drx_encrypt(self.h, m.size, _ptr(m), _ptr(r), _ptr(ct)))
+        return ct
+
+    def aggregate(self, vectors):
+        """CipherVector.Add over a list of serialised CipherVectors (each v*128 bytes)."""
+        vs = [_u8(v) for v in vectors]
+        v = vs[0].size // 128 if vs else 0
+        assert all(x.size == v * 128 for x in vs)
+        ptrs = (ctypes.c_void_p * len(vs))(*[x.ctypes.data for x in vs])
+        out = np.empty(128 * v, dtype=np.uint8)
+        _lib.check(self.lib.drx_aggregate(self.h, len(vs), v, ctypes.cast(ptrs, ctypes.c_void_p), _ptr(out)))
+        return out
+
+    def create_decryption_table(self, limit):
+        _lib.check(self.lib.drx_dlog_table(self.h, int(limit)))
+
+    def decrypt_int_vector(self, sk, ct, with_neg=True, return_found=False):
+        ct = _u8(ct)
+        n = ct.size // 128
+        out = np.empty(n, dtype=np.int64)
+        found = np.empty(n, dtype=np.uint8)
+        skb = _u8(sk)
+        _lib.check(self.lib.drx_decrypt(self.h, n, _ptr(skb), _ptr(ct), 1 if with_neg else 0, _ptr(out), _ptr(found)))
+        return (out, found) if return_found else out
+
+    def decrypt_check_zero(self, sk, ct):
+        ct = _u8(ct)
+        n = ct.size // 128
+        out = np.empty(n, dtype=np.int64)
+        skb = _u8(sk)
+        _lib.check(self.lib.drx_decrypt_check_zero(self.h, n, _ptr(skb), _ptr(ct), _ptr(out)))
+        return out
+
+    # ---- range proofs (lib/range/range_proof.go call surface)
+    def init_range_proof_signature(self, x_list, u):
+        """InitRangeProofSignature for len(x_list) servers from caller-drawn private keys: (Y bytes, A bytes)."""
+        ns = len(x_list)
+        x = _u8(b''.join(int(v).to_bytes(32, 'big') for v in x_list))
+        Y = np.empty(64 * ns, dtype=np.uint8)
+        A = np.empty(128 * ns * u, dtype=np.uint8)
+        _lib.check(self.lib.drx_rp_make_sigs(self.h, ns, u, _ptr(x), _ptr(Y), _ptr(A)))
+        return Y, A
+
+    def set_signatures(self, set_id, ns, u, Y, A):
+        Y, A = _u8(Y), _u8(A)
+        assert Y.size == 64 * ns and A.size == 128 * ns * u
+        _lib.check(self.lib.drx_rp_set_sigs(self.h, set_id, ns, u, _ptr(Y), _ptr(A)))
+
+    def ndigits(self, secret, u, l):
+        return int(self.lib.drx_rp_ndigits(secret, u, l))
+
+    def proof_size(self, ns, nd):
+        return int(self.lib.drx_rp_proof_size(ns, nd))
+
+    def create_range_proofs(self, set_ids, ns_of_set, u_of_set, ls, secrets, rs, cts, rnd_list):
+        """CreatePredicateRangeProofListForAllServers. rnd_list[p] = bytes of nd*(3+ns) scalars in draw order.
+        Returns (proof bytes, offsets[n+1])."""
+        n = len(set_ids)
+        set_ids = np.ascontiguousarray(set_ids, dtype=np.int32)
+        ls = np.ascontiguousarray(ls, dtype=np.int64)
+        secrets = np.ascontiguousarray(secrets, dtype=np.int64)
+        rs, cts = _u8(rs), _u8(cts)
+        off = np.zeros(n + 1, dtype=np.uint64)
+        roff = np.zeros(n + 1, dtype=np.uint64)
+        for p in range(n):
+            if set_ids[p] < 0:
+                sz = 128
+            else:
+                nd = self.ndigits(int(secrets[p]), int(u_of_set[int(set_ids[p])]), int(ls[p]))
+                sz = self.proof_size(int(ns_of_set[int(set_ids[p])]), nd)
+            off[p + 1] = off[p] + sz
+            roff[p + 1] = roff[p] + len(rnd_list[p])
+        rnd = _u8(b''.join(bytes(x) for x in rnd_list)) if n else np.empty(0, np.uint8)
+        proofs = np.empty(int(off[n]), dtype=np.uint8)
+        _lib.check(self.lib.drx_rp_create(self.h, n, _ptr(set_ids), _ptr(ls), _ptr(secrets), _ptr(rs), _ptr(cts),
+                                          _ptr(rnd), _ptr(roff), _ptr(proofs), _ptr(off)))
+        return proofs, off
+
+    def verify_range_proofs(self, set_ids, ls, proofs, off):
+        n = len(set_ids)
+        set_ids = np.ascontiguousarray(set_ids, dtype=np.int32)
+        ls = np.ascontiguousarray(ls, dtype=np.int64)
+        proofs = _u8(proofs)
+        off = np.ascontiguousarray(off, dtype=np.uint64)
+        ok = np.empty(n, dtype=np.uint8)
+        _lib.check(self.lib.drx_rp_verify(self.h, n, _ptr(set_ids), _ptr(ls), _ptr(proofs), _ptr(off), _ptr(ok)))
+        return ok
+
+    # ---- diagnostics
+    def pair(self, g1, g2):
+        g1, g2 = _u8(g1), _u8(g2)
+        n = g1.size // 64
+        out = np.empty(384 * n, dtype=np.uint8)
+        _lib.check(self.lib.drx_pair(self.h, n, _ptr(g1), _ptr(g2), _ptr(out)))
+        return out
+
+    def g1_mul(self, k, pt):
+        k, pt = _u8(k), _u8(pt)
+        n = k.size // 32
+        out = np.empty(64 * n, dtype=np.uint8)
+        _lib.check(self.lib.drx_g1_mul(self.h, n, _ptr(k), _ptr(pt), _ptr(out)))
+        return out
+
+    def g2_mul(self, k, pt):
+        k, pt = _u8(k), _u8(pt)
+        n = k.size // 32
+        out = np.empty(128 * n, dtype=np.uint8)
+        _lib.check(self.lib.drx_g2_mul(self.h, n, _ptr(k), _ptr(pt), _ptr(out)))
+        return out
+
+    def mont_mul(self, which, a, b):
+        a = np.ascontiguousarray(a, dtype=np.uint32)
+        b = np.ascontiguousarray(b, dtype=np.uint32)
+        r = np.empty_like(a)
+        _lib.check(self.lib.drx_mont_mul(self.h, a.size // 8, which, _ptr(a), _ptr(b), _ptr(r)))
+        return r
+
+    def microbench(self, kind, iters):
+        ms, work = ctypes.c_double(), ctypes.c_double()
+        _lib.check(self.lib.drx_microbench(self.h, kind, iters, ctypes.byref(ms), ctypes.byref(work)))
+        return ms.value, work.value

@@ -1,0 +1,502 @@
+// C ABI of libdrynx_gpu.so (include/drynx_gpu.h): context, device memory, host<->device staging and the
+// host-side bookkeeping that mirrors state the reference keeps in Go globals (the lazily grown PointToInt map
+// of libunlynx v1.4.0 lib/crypto.go discreteLog). All arithmetic happens in the kernels; there is no CPU
+// implementation behind any entry point.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/drynx_gpu.h"
+#include "launch.h"
+
+using namespace drx;
+
+namespace {
+
+thread_local std::string g_err = "";
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CU(x)                                                                                     \
+  do {                                                                                            \
+    cudaError_t e_ = (x);                                                                         \
+    if (e_ != cudaSuccess) return fail((int)e_, "%s: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+// default generators in wire form: B = (1, -2); g2 = the x/crypto bn256 twist generator (x.i, x.1, y.i, y.1)
+const uint8_t kDefaultG1[64] = {
+    0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1,
+    0x8f, 0xb5, 0x01, 0xe3, 0x4a, 0xa3, 0x87, 0xf9, 0xaa, 0x6f, 0xec, 0xb8, 0x61, 0x84, 0xdc, 0x21,
+    0xee, 0x5b, 0x88, 0xd1, 0x20, 0xb5, 0xb5, 0x9e, 0x18, 0x5c, 0xac, 0x6c, 0x5e, 0x08, 0x96, 0x65};
+#include "g2_default.inc"
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 4 + 4096;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) return fail((int)e, "cudaMalloc(%zu): %s", want, cudaGetErrorString(e));
+    cap = want;
+    return 0;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+// Carves 256-byte aligned regions out of one growable device allocation.
+struct Arena {
+  DevBuf buf;
+  size_t used = 0;
+  std::vector<size_t> sizes;
+  void plan_reset() { used = 0; sizes.clear(); }
+  size_t plan(size_t bytes) {
+    size_t off = used;
+    used += (bytes + 255) & ~(size_t)255;
+    return off;
+  }
+  int commit() { return buf.ensure(used ? used : 256); }
+  template <class T>
+  T* at(size_t off) { return (T*)((char*)buf.p + off); }
+};
+
+// Host model of which integers the reference's lazily grown PointToInt map holds (libunlynx discreteLog).
+struct DlogModel {
+  int64_t pos_hi = -1;                                // map holds 0..pos_hi
+  std::vector<std::pair<int64_t, int64_t>> neg;       // inclusive ranges of i with -i stored
+  bool has_neg(int64_t i) const {
+    for (auto& r : neg)
+      if (i >= r.first && i <= r.second) return true;
+    return false;
+  }
+  void add_neg(int64_t lo, int64_t hi) {
+    if (!neg.empty() && neg.back().second + 1 >= lo && neg.back().first <= lo) {
+      if (hi > neg.back().second) neg.back().second = hi;
+    } else {
+      neg.push_back({lo, hi});
+    }
+  }
+  // raw: true discrete log in (-100000, 100000) or INT64_MIN when outside that range
+  int64_t resolve(int64_t raw, bool check_neg, bool* found) {
+    const bool known = raw != INT64_MIN;
+    if (known && raw >= 0 && raw <= pos_hi) { *found = true; return raw; }
+    if (known && raw < 0 && has_neg(-raw)) { *found = true; return raw; }
+    const int64_t g0 = pos_hi < 0 ? 0 : pos_hi;
+    int64_t stop = kMaxHomomorphicInt - 1;
+    bool hit = false;
+    if (known && raw >= g0) { stop = raw; hit = true; }
+    else if (known && raw < 0 && check_neg && -raw >= g0) { stop = -raw; hit = true; }
+    pos_hi = stop;
+    if (check_neg) add_neg(g0, stop);
+    *found = hit;
+    return hit ? raw : 0;
+  }
+};
+
+struct RpSetHost {
+  int ns = 0;
+  int64_t u = 0;
+  DevBuf tabY, tabA, tabGtA, sumY;
+};
+
+}  // namespace
+
+struct drx_ctx {
+  int device = 0;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  std::mutex mu;
+  uint64_t launches = 0;
+  bool have_pub = false, have_dlog = false;
+  DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
+      sets_dev, sink;
+  Arena arena;
+  DlogModel dlog;
+  std::map<int, RpSetHost> sets;
+  int sets_dev_count = 0;
+};
+
+namespace {
+
+struct Guard {
+  drx_ctx* c;
+  explicit Guard(drx_ctx* ctx) : c(ctx) { c->mu.lock(); cudaSetDevice(c->device); }
+  ~Guard() { c->mu.unlock(); }
+};
+
+int reset_bad(drx_ctx* c) {
+  CU(cudaMemsetAsync(c->bad.p, 0, sizeof(int), c->stream));
+  return 0;
+}
+int read_bad(drx_ctx* c, int* out) {
+  CU(cudaMemcpyAsync(out, c->bad.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail((int)e, "%s launch: %s", what, cudaGetErrorString(e));
+  return 0;
+}
+#define RET(x)            \
+  do {                    \
+    int r_ = (x);         \
+    if (r_) return r_;    \
+  } while (0)
+
+int ensure_dlog(drx_ctx* c) {
+  if (c->have_dlog) return 0;
+  RET(c->dlog_keys.ensure((size_t)kDlogCap * 32));
+  RET(c->dlog_vals.ensure((size_t)kDlogCap * 4));
+  c->launches += launch_dlog_build(c->stream, c->tabB.p, c->baseB_aff.p, c->dlog_keys.p, (uint32_t*)c->dlog_vals.p);
+  RET(check_launch("dlog_build"));
+  c->have_dlog = true;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* drx_last_error(void) { return g_err.c_str(); }
+
+int drx_init(drx_ctx** out, int device, const uint8_t* g1_base, const uint8_t* g2_base) {
+  if (!out) return fail(-1, "drx_init: out is NULL");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(e != cudaSuccess ? (int)e : -3, "drx_init: no CUDA device (%s); this library has no CPU path",
+                cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return fail(-1, "drx_init: device %d out of range (0..%d)", device, ndev - 1);
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(-3, "drx_init: device %d is sm_%d%d; libdrynx_gpu is built for sm_100a only", device, prop.major,
+                prop.minor);
+  CU(cudaSetDevice(device));
+  drx_ctx* c = new drx_ctx();
+  c->device = device;
+  e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { delete c; return fail((int)e, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+  c->stream = c->own_stream;
+  int rc = 0;
+  auto cleanup = [&](int code) { drx_free(c); return code; };
+  if ((rc = c->bad.ensure(256))) return cleanup(rc);
+  if ((rc = c->baseB_wire.ensure(64)) || (rc = c->baseB_aff.ensure(64)) || (rc = c->g2_wire.ensure(128)) ||
+      (rc = c->g2_aff.ensure(128)) || (rc = c->gtB.ensure(kGtBytes)) || (rc = c->tabB.ensure(kCombPoints * 64)) ||
+      (rc = c->tabGtB.ensure(kCombPoints * kGtBytes)) || (rc = c->tabG2.ensure(kCombPoints * 128)))
+    return cleanup(rc);
+  cudaMemcpyAsync(c->baseB_wire.p, g1_base ? g1_base : kDefaultG1, 64, cudaMemcpyHostToDevice, c->stream);
+  cudaMemcpyAsync(c->g2_wire.p, g2_base ? g2_base : kDefaultG2, 128, cudaMemcpyHostToDevice, c->stream);
+  cudaMemsetAsync(c->bad.p, 0, sizeof(int), c->stream);
+  c->launches += launch_g1_from_wire(c->stream, 1, (const uint8_t*)c->baseB_wire.p, c->baseB_aff.p, (int*)c->bad.p);
+  c->launches += launch_g2_from_wire(c->stream, 1, (const uint8_t*)c->g2_wire.p, c->g2_aff.p, (int*)c->bad.p);
+  c->launches += launch_comb_table_g1(c->stream, 1, c->baseB_aff.p, c->tabB.p);
+  c->launches += launch_comb_table_g2(c->stream, 1, c->g2_aff.p, c->tabG2.p);
+  c->launches += launch_pair_aff(c->stream, 1, c->baseB_aff.p, 0, c->g2_aff.p, c->gtB.p);
+  c->launches += launch_comb_table_gt(c->stream, 1, c->gtB.p, c->tabGtB.p);
+  if ((rc = check_launch("init"))) return cleanup(rc);
+  int bad = 0;
+  if ((rc = read_bad(c, &bad))) return cleanup(rc);
+  if (bad) return cleanup(fail(-2, "drx_init: generator bytes are not valid curve points"));
+  *out = c;
+  return 0;
+}
+
+void drx_free(drx_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  for (DevBuf* b : {&c->baseB_aff, &c->baseB_wire, &c->g2_aff, &c->g2_wire, &c->gtB, &c->tabB, &c->tabP, &c->pub_aff,
+                    &c->tabGtB, &c->tabG2, &c->dlog_keys, &c->dlog_vals, &c->bad, &c->sets_dev, &c->sink})
+    b->release();
+  c->arena.buf.release();
+  for (auto& kv : c->sets) {
+    kv.second.tabY.release();
+    kv.second.tabA.release();
+    kv.second.tabGtA.release();
+    kv.second.sumY.release();
+  }
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  delete c;
+}
+
+int drx_set_stream(drx_ctx* c, void* cuda_stream) {
+  if (!c) return fail(-1, "null context");
+  Guard g(c);
+  c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+  return 0;
+}
+int drx_synchronize(drx_ctx* c) {
+  if (!c) return fail(-1, "null context");
+  Guard g(c);
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+uint64_t drx_launch_count(const drx_ctx* c) { return c ? c->launches : 0; }
+
+int drx_set_pubkey(drx_ctx* c, const uint8_t P[64]) {
+  if (!c || !P) return fail(-1, "drx_set_pubkey: null argument");
+  Guard g(c);
+  RET(c->pub_aff.ensure(64));
+  RET(c->tabP.ensure(kCombPoints * 64));
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t o = a.plan(64);
+  RET(a.commit());
+  RET(reset_bad(c));
+  CU(cudaMemcpyAsync(a.at<uint8_t>(o), P, 64, cudaMemcpyHostToDevice, c->stream));
+  c->launches += launch_g1_from_wire(c->stream, 1, a.at<uint8_t>(o), c->pub_aff.p, (int*)c->bad.p);
+  c->launches += launch_comb_table_g1(c->stream, 1, c->pub_aff.p, c->tabP.p);
+  RET(check_launch("set_pubkey"));
+  int bad = 0;
+  RET(read_bad(c, &bad));
+  if (bad) { c->have_pub = false; return fail(-2, "drx_set_pubkey: malformed point"); }
+  c->have_pub = true;
+  return 0;
+}
+
+int drx_encrypt_dev(drx_ctx* c, size_t n, const int64_t* d_m, const uint8_t* d_r, uint8_t* d_ct) {
+  if (!c) return fail(-1, "null context");
+  Guard g(c);
+  if (!c->have_pub) return fail(-1, "drx_encrypt: call drx_set_pubkey first");
+  c->launches += launch_encrypt(c->stream, n, d_m, d_r, c->tabB.p, c->tabP.p, d_ct);
+  return check_launch("encrypt");
+}
+
+int drx_encrypt(drx_ctx* c, size_t n, const int64_t* m, const uint8_t* r, uint8_t* ct) {
+  if (!c) return fail(-1, "null context");
+  if (n == 0) return 0;
+  if (!m || !r || !ct) return fail(-1, "drx_encrypt: null buffer");
+  Guard g(c);
+  if (!c->have_pub) return fail(-1, "drx_encrypt: call drx_set_pubkey first");
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t om = a.plan(n * 8), orr = a.plan(n * 32), oc = a.plan(n * 128);
+  RET(a.commit());
+  CU(cudaMemcpyAsync(a.at<void>(om), m, n * 8, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(a.at<void>(orr), r, n * 32, cudaMemcpyHostToDevice, c->stream));
+  c->launches += launch_encrypt(c->stream, n, a.at<int64_t>(om), a.at<uint8_t>(orr), c->tabB.p, c->tabP.p, a.at<uint8_t>(oc));
+  RET(check_launch("encrypt"));
+  CU(cudaMemcpyAsync(ct, a.at<void>(oc), n * 128, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+static int aggregate_on_device(drx_ctx* c, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
+                               uint8_t* d_out) {
+  c->launches += launch_aggregate(c->stream, ndp, v, d_cts, d_scratch, slices, d_out, (int*)c->bad.p);
+  return check_launch("aggregate");
+}
+
+int drx_aggregate_dev(drx_ctx* c, size_t ndp, size_t v, const uint8_t* d_cts, uint8_t* d_out) {
+  if (!c) return fail(-1, "null context");
+  if (v == 0) return 0;
+  Guard g(c);
+  int slices = 1;
+  size_t sb = aggregate_scratch_bytes(ndp, v, &slices);
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t os = a.plan(sb);
+  RET(a.commit());
+  RET(reset_bad(c));
+  return aggregate_on_device(c, ndp, v, d_cts, a.at<void>(os), slices, d_out);
+}
+
+int drx_aggregate(drx_ctx* c, size_t ndp, size_t v, const uint8_t* const* cts, uint8_t* out) {
+  if (!c) return fail(-1, "null context");
+  if (v == 0) return 0;
+  if (!out || (ndp && !cts)) return fail(-1, "drx_aggregate: null buffer");
+  Guard g(c);
+  int slices = 1;
+  size_t sb = aggregate_scratch_bytes(ndp, v, &slices);
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t oi = a.plan(ndp * v * 128), os = a.plan(sb), oo = a.plan(v * 128);
+  RET(a.commit());
+  RET(reset_bad(c));
+  for (size_t d = 0; d < ndp; d++) {
+    if (!cts[d]) return fail(-1, "drx_aggregate: cts[%zu] is NULL", d);
+    CU(cudaMemcpyAsync(a.at<uint8_t>(oi) + d * v * 128, cts[d], v * 128, cudaMemcpyHostToDevice, c->stream));
+  }
+  RET(aggregate_on_device(c, ndp, v, a.at<uint8_t>(oi), a.at<void>(os), slices, a.at<uint8_t>(oo)));
+  CU(cudaMemcpyAsync(out, a.at<void>(oo), v * 128, cudaMemcpyDeviceToHost, c->stream));
+  int bad = 0;
+  RET(read_bad(c, &bad));
+  if (bad) return fail(-2, "drx_aggregate: %d malformed points", bad);
+  return 0;
+}
+
+int drx_dlog_table(drx_ctx* c, int64_t limit) {
+  if (!c) return fail(-1, "null context");
+  if (limit < 0) return fail(-1, "drx_dlog_table: negative limit");
+  Guard g(c);
+  RET(ensure_dlog(c));
+  bool found;
+  c->dlog.resolve(limit < kMaxHomomorphicInt ? limit : INT64_MIN, true, &found);
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int drx_decrypt_dev(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* d_ct, int64_t* d_out) {
+  if (!c || !sk) return fail(-1, "null argument");
+  Guard g(c);
+  RET(ensure_dlog(c));
+  // the key travels through the tail of the 256-byte flag buffer
+  CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
+  c->launches += launch_decrypt(c->stream, n, (uint8_t*)c->bad.p + 64, d_ct, c->dlog_keys.p, (uint32_t*)c->dlog_vals.p,
+                                d_out, (int*)c->bad.p);
+  return check_launch("decrypt");
+}
+
+static int decrypt_raw(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* ct, std::vector<int64_t>& raw) {
+  RET(ensure_dlog(c));
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t oc = a.plan(n * 128), oo = a.plan(n * 8);
+  RET(a.commit());
+  RET(reset_bad(c));
+  CU(cudaMemcpyAsync(a.at<void>(oc), ct, n * 128, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
+  c->launches += launch_decrypt(c->stream, n, (uint8_t*)c->bad.p + 64, a.at<uint8_t>(oc), c->dlog_keys.p,
+                                (uint32_t*)c->dlog_vals.p, a.at<int64_t>(oo), (int*)c->bad.p);
+  RET(check_launch("decrypt"));
+  raw.resize(n);
+  CU(cudaMemcpyAsync(raw.data(), a.at<void>(oo), n * 8, cudaMemcpyDeviceToHost, c->stream));
+  int bad = 0;
+  RET(read_bad(c, &bad));
+  if (bad) return fail(-2, "drx_decrypt: %d malformed points", bad);
+  return 0;
+}
+
+int drx_decrypt(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* ct, int with_neg, int64_t* out,
+                uint8_t* found) {
+  if (!c) return fail(-1, "null context");
+  if (n == 0) return 0;
+  if (!sk || !ct || !out) return fail(-1, "drx_decrypt: null buffer");
+  Guard g(c);
+  std::vector<int64_t> raw;
+  RET(decrypt_raw(c, n, sk, ct, raw));
+  for (size_t i = 0; i < n; i++) {
+    bool f;
+    out[i] = c->dlog.resolve(raw[i], with_neg != 0, &f);
+    if (found) found[i] = f ? 1 : 0;
+  }
+  return 0;
+}
+
+int drx_decrypt_check_zero(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* ct, int64_t* out) {
+  if (!c) return fail(-1, "null context");
+  if (n == 0) return 0;
+  if (!sk || !ct || !out) return fail(-1, "drx_decrypt_check_zero: null buffer");
+  Guard g(c);
+  std::vector<int64_t> raw;
+  RET(decrypt_raw(c, n, sk, ct, raw));
+  for (size_t i = 0; i < n; i++) out[i] = raw[i] == 0 ? 0 : 1;
+  return 0;
+}
+
+// ------------------------------------------------------------------ diagnostics
+static int run_wire_op(drx_ctx* c, size_t n, const void* in1, size_t s1, const void* in2, size_t s2, void* out,
+                       size_t so, int kind) {
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t o1 = a.plan(n * s1), o2 = a.plan(n * s2), oo = a.plan(n * so);
+  RET(a.commit());
+  RET(reset_bad(c));
+  CU(cudaMemcpyAsync(a.at<void>(o1), in1, n * s1, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(a.at<void>(o2), in2, n * s2, cudaMemcpyHostToDevice, c->stream));
+  int* bad = (int*)c->bad.p;
+  if (kind == 0) c->launches += launch_pair_wire(c->stream, n, a.at<uint8_t>(o1), a.at<uint8_t>(o2), a.at<uint8_t>(oo), bad);
+  if (kind == 1) c->launches += launch_g1_mul(c->stream, n, a.at<uint8_t>(o1), a.at<uint8_t>(o2), a.at<uint8_t>(oo), bad);
+  if (kind == 2) c->launches += launch_g2_mul(c->stream, n, a.at<uint8_t>(o1), a.at<uint8_t>(o2), a.at<uint8_t>(oo), bad);
+  RET(check_launch("wire op"));
+  CU(cudaMemcpyAsync(out, a.at<void>(oo), n * so, cudaMemcpyDeviceToHost, c->stream));
+  int nb = 0;
+  RET(read_bad(c, &nb));
+  if (nb) return fail(-2, "%d malformed points", nb);
+  return 0;
+}
+int drx_pair(drx_ctx* c, size_t n, const uint8_t* g1, const uint8_t* g2, uint8_t* gt) {
+  if (!c) return fail(-1, "null context");
+  if (!n) return 0;
+  Guard g(c);
+  return run_wire_op(c, n, g1, 64, g2, 128, gt, 384, 0);
+}
+int drx_g1_mul(drx_ctx* c, size_t n, const uint8_t* k, const uint8_t* pt, uint8_t* out) {
+  if (!c) return fail(-1, "null context");
+  if (!n) return 0;
+  Guard g(c);
+  return run_wire_op(c, n, k, 32, pt, 64, out, 64, 1);
+}
+int drx_g2_mul(drx_ctx* c, size_t n, const uint8_t* k, const uint8_t* pt, uint8_t* out) {
+  if (!c) return fail(-1, "null context");
+  if (!n) return 0;
+  Guard g(c);
+  return run_wire_op(c, n, k, 32, pt, 128, out, 128, 2);
+}
+int drx_mont_mul(drx_ctx* c, size_t n, int which, const uint32_t* x, const uint32_t* y, uint32_t* r) {
+  if (!c) return fail(-1, "null context");
+  if (!n) return 0;
+  Guard g(c);
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t o1 = a.plan(n * 32), o2 = a.plan(n * 32), oo = a.plan(n * 32);
+  RET(a.commit());
+  CU(cudaMemcpyAsync(a.at<void>(o1), x, n * 32, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(a.at<void>(o2), y, n * 32, cudaMemcpyHostToDevice, c->stream));
+  c->launches += launch_mont_mul(c->stream, n, which, a.at<uint32_t>(o1), a.at<uint32_t>(o2), a.at<uint32_t>(oo));
+  RET(check_launch("mont_mul"));
+  CU(cudaMemcpyAsync(r, a.at<void>(oo), n * 32, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+int drx_microbench(drx_ctx* c, int kind, int iters, double* ms, double* work) {
+  if (!c || !ms || !work) return fail(-1, "null argument");
+  Guard g(c);
+  const int blocks = 148 * 8, threads = 256;
+  RET(c->sink.ensure((size_t)blocks * threads * 4));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0));
+  CU(cudaEventCreate(&e1));
+  launch_microbench(c->stream, kind, iters / 8 + 1, blocks, threads, (uint32_t*)c->sink.p);  // warm-up
+  CU(cudaEventRecord(e0, c->stream));
+  c->launches += 1 + launch_microbench(c->stream, kind, iters, blocks, threads, (uint32_t*)c->sink.p);
+  CU(cudaEventRecord(e1, c->stream));
+  CU(cudaEventSynchronize(e1));
+  float t = 0;
+  CU(cudaEventElapsedTime(&t, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *ms = t;
+  const double per_thread = kind == 0 ? 16.0 * iters : 2.0 * iters;  // MAC32 (wide MACs) or Montgomery products
+  *work = per_thread * blocks * threads;
+  return check_launch("microbench");
+}
+
+}  // extern "C"
+
+// ---- range-proof entry points: see capi_rp.inc
+#include "capi_rp.inc"

@@ -17,7 +17,8 @@
 #include <stdint.h>
 
 #if defined(__CUDACC__)
-#define DRX_HD __host__ __device__ __forceinline__
+// nvcc builds are device-only: the shipped library has no host arithmetic at all
+#define DRX_HD __device__ __forceinline__
 #define DRX_D __device__ __forceinline__
 #else
 #define DRX_HD inline __attribute__((always_inline))
@@ -234,7 +235,7 @@ DRX_HD bool mod_geq(const uint32_t a[8]) {
 }
 
 // ------------------------------------------------------------------ Fp: the base field, Montgomery form
-struct Fp {
+struct alignas(16) Fp {
   uint32_t v[8];
 };
 

@@ -1,0 +1,76 @@
+// Host-side launch wrappers implemented in kernels_g1.cu / kernels_rp.cu and called from capi.cu.
+// Plain pointers only; every function enqueues on `st` and returns the number of kernels it launched.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace drx {
+
+constexpr int kCombWindows = 32;
+constexpr int kCombEntries = 255;
+constexpr size_t kCombPoints = (size_t)kCombWindows * kCombEntries;  // 8160
+constexpr size_t kG1AffBytes = 64, kG2AffBytes = 128, kGtBytes = 384, kG1JacBytes = 96;
+constexpr int64_t kMaxHomomorphicInt = 100000;  // libunlynx.MaxHomomorphicInt
+constexpr uint32_t kDlogCap = 1u << 18;         // open-addressing slots for 100001 keys
+constexpr int kAggMaxSlices = 64;
+
+// ---- kernels_g1.cu
+// wire bytes -> Montgomery affine (returns malformed count in *d_bad)
+int launch_g1_from_wire(cudaStream_t st, size_t n, const uint8_t* d_wire, void* d_aff, int* d_bad);
+int launch_comb_table_g1(cudaStream_t st, int nbases, const void* d_bases_aff, void* d_tables);
+int launch_encrypt(cudaStream_t st, size_t n, const int64_t* d_m, const uint8_t* d_r, const void* d_tabB,
+                   const void* d_tabP, uint8_t* d_ct);
+// scratch: slices * v * 2 Jacobian points
+size_t aggregate_scratch_bytes(size_t ndp, size_t v, int* slices_out);
+int launch_aggregate(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
+                     uint8_t* d_out, int* d_bad);
+int launch_dlog_build(cudaStream_t st, const void* d_tabB, const void* d_baseB_aff, void* d_keys, uint32_t* d_vals);
+int launch_decrypt(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t* d_ct, const void* d_keys,
+                   const uint32_t* d_vals, int64_t* d_out, int* d_bad);
+int launch_g1_mul(cudaStream_t st, size_t n, const uint8_t* d_k, const uint8_t* d_pt, uint8_t* d_out, int* d_bad);
+int launch_mont_mul(cudaStream_t st, size_t n, int which, const uint32_t* d_a, const uint32_t* d_b, uint32_t* d_r);
+int launch_microbench(cudaStream_t st, int kind, int iters, int blocks, int threads, uint32_t* d_sink);
+
+// ---- kernels_rp.cu
+int launch_g2_from_wire(cudaStream_t st, size_t n, const uint8_t* d_wire, void* d_aff, int* d_bad);
+int launch_comb_table_g2(cudaStream_t st, int nbases, const void* d_bases_aff, void* d_tables);
+int launch_pair_aff(cudaStream_t st, size_t n, const void* d_g1_aff, size_t g1_stride_items, const void* d_g2_aff,
+                    void* d_gt);  // g1_stride_items = 0 broadcasts one G1 point
+int launch_comb_table_gt(cudaStream_t st, int nbases, const void* d_bases_gt, void* d_tables);
+int launch_pair_wire(cudaStream_t st, size_t n, const uint8_t* d_g1, const uint8_t* d_g2, uint8_t* d_gt, int* d_bad);
+int launch_g2_mul(cudaStream_t st, size_t n, const uint8_t* d_k, const uint8_t* d_pt, uint8_t* d_out, int* d_bad);
+int launch_make_sigs(cudaStream_t st, int ns, int64_t u, const uint8_t* d_x, const void* d_tabB, const void* d_tabG2,
+                     uint8_t* d_Y, uint8_t* d_A);
+
+struct RpSetDev {        // device-resident per-signature-set data (array indexed by set_id on the device)
+  const void* tabY;      // ns comb tables of Y_i (G1)
+  const void* tabA;      // ns*u comb tables of A_{i,k} (G2)
+  const void* tabGtA;    // ns*u comb tables of e(B, A_{i,k}) (GT)
+  const uint8_t* sumY;   // 64 B wire form of sum_i Y_i
+  int32_t ns;
+  int32_t u;
+};
+
+struct RpBatch {          // one create/verify call
+  size_t n;               // proofs
+  size_t items;           // sum over proofs of ns*nd
+  const int32_t* d_set_id;
+  const int64_t* d_l;
+  const size_t* d_proof_off;   // n+1, or nullptr for a uniform batch
+  const uint32_t* d_item_proof;  // items, or nullptr for a uniform batch
+  const uint32_t* d_item_start;  // n (first item of each proof), or nullptr
+  int uni_ns;             // uniform batch: servers
+  int uni_nd;             // uniform batch: digits
+  size_t uni_size;        // uniform batch: bytes per proof
+};
+
+int launch_rp_create(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                     const uint8_t* d_r, const uint8_t* d_ct, const uint8_t* d_rnd, const size_t* d_rnd_off,
+                     const void* d_tabB, const void* d_tabP, const void* d_tabGtB, const uint8_t* d_baseB_wire,
+                     uint8_t* d_proofs);
+int launch_rp_verify(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB, const void* d_tabP,
+                     const void* d_tabGtB, const void* d_g2_aff, const uint8_t* d_proofs, uint32_t* d_flags,
+                     uint8_t* d_ok);
+
+}  // namespace drx

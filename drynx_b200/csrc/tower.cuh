@@ -11,10 +11,8 @@
 #pragma once
 #include "fp.cuh"
 
-#if defined(__CUDA_ARCH__)
-#define DRX_NI __device__ __noinline__
-#elif defined(__CUDACC__)
-#define DRX_NI __host__ __device__
+#if defined(__CUDACC__)
+#define DRX_NI static __device__ __noinline__
 #else
 #define DRX_NI inline
 #endif

@@ -1,0 +1,133 @@
+/* drynx_gpu.h -- C ABI of the B200 (sm_100a) backend for Drynx's data-provider / verifying-node crypto path.
+ *
+ * The reference (cgrigis/drynx, Go) has no FFI: the seam is ordinary Go functions over kyber.Point /
+ * kyber.Scalar with the global suite bn256.G1 (lib/suite.go:10-15). Every type on the path already has a
+ * fixed-width big-endian byte form, so this ABI is bytes in, bytes out:
+ *
+ *   scalar      32 B  big-endian, reduced mod n on input (kyber Scalar.SetBytes / UnmarshalBinary)
+ *   G1 point    64 B  x || y, infinity = 64 zero bytes (kyber pointG1.MarshalBinary)
+ *   G2 point   128 B  x.i || x.1 || y.i || y.1          (kyber pointG2.MarshalBinary)
+ *   GT element 384 B  12 x 32 B, order x.x.x ... y.z.y  (kyber pointGT.MarshalBinary)
+ *   ciphertext 128 B  K || C                            (libunlynx CipherText.ToBytes)
+ *   range proof       Commit(128) | Challenge(32) | Zr(32) | D(64) | Zphi(32*l) |
+ *                     per server i: V_i(128*l) | A_i(384*l) | Zv_i(32*l)
+ *                     (lib/range/range_proof.go:72-155 field order; 256 + 32*l + 544*ns*l bytes)
+ *
+ * Rules: every pointer is caller-owned memory that is only read or written during the call; nothing is
+ * retained (cgo pointer rules). Randomness is an INPUT: the host draws r, s_j, t_j, m_j, v_ij and passes them
+ * in (the reference draws them from crypto/rand inside goroutines). Return value:
+ * 0 = success, negative = invalid argument / malformed input, positive = CUDA error code; text through
+ * drx_last_error(). Nothing here falls back to the CPU: without a usable sm_100a device drx_init fails.
+ * A context is bound to one device and one stream and serialises its calls with an internal lock.
+ *
+ * Functions ending in _dev take DEVICE pointers on the context's device, enqueue on the context's stream and
+ * return without synchronising; they exist so that a caller that keeps ciphertexts resident in HBM (and the
+ * benchmark's device-resident leg) skips the host staging copies.
+ */
+#ifndef DRYNX_GPU_H
+#define DRYNX_GPU_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct drx_ctx drx_ctx;
+
+/* Creates a context on CUDA device `device`. g1_base / g2_base are the suite generators in wire form as the
+ * Go side sees them (lib.Suite.Point().Base().MarshalBinary(), bn256.NewSuite().G2().Point().Base()); NULL
+ * selects (1, -2) and the x/crypto twist generator that kyber's constants encode. Builds the fixed-base
+ * tables for B and for e(B, g2). Replaces: package init of lib/suite.go:12-15. */
+int drx_init(drx_ctx** out, int device, const uint8_t* g1_base /*64 or NULL*/, const uint8_t* g2_base /*128 or NULL*/);
+void drx_free(drx_ctx* ctx);
+/* Thread-local text of the last failure on this thread; never NULL. */
+const char* drx_last_error(void);
+/* Use an existing cudaStream_t (e.g. torch's current stream) for every later call; NULL restores the
+ * context's own stream. */
+int drx_set_stream(drx_ctx* ctx, void* cuda_stream);
+int drx_synchronize(drx_ctx* ctx);
+/* Number of kernel launches issued by this context so far (for the benchmark's gpu_launches field). */
+uint64_t drx_launch_count(const drx_ctx* ctx);
+
+/* Collective public key P for EncryptInt* and range proofs (CreateProof.CaPub, lib/range/range_proof.go:67);
+ * builds its fixed-base table. */
+int drx_set_pubkey(drx_ctx* ctx, const uint8_t P[64]);
+
+/* libunlynx.EncryptIntGetR / EncryptIntVectorGetRs with the ephemeral scalars injected (call sites
+ * lib/encoding/sum.go:24, mean.go:33, variance.go:36, frequency_count.go:36, linear_regression_dims.go:40-85,
+ * logistic_regression.go:420): ct[i] = (r_i*B) || (m_i*B + r_i*P). Negative m maps to n-|m| (SetInt64). */
+int drx_encrypt(drx_ctx* ctx, size_t n, const int64_t* m, const uint8_t* r /*n*32*/, uint8_t* ct /*n*128*/);
+int drx_encrypt_dev(drx_ctx* ctx, size_t n, const int64_t* d_m, const uint8_t* d_r, uint8_t* d_ct);
+
+/* CipherVector.FromBytes + CipherVector.Add over all data providers
+ * (protocols/data_collection_protocol.go:145-166, lib/structs.go:338-350): out[j] = sum_d cts[d][j].
+ * cts holds ndp pointers to v*128 bytes each. Returns -2 if any point is malformed. */
+int drx_aggregate(drx_ctx* ctx, size_t ndp, size_t v, const uint8_t* const* cts, uint8_t* out /*v*128*/);
+/* Same with the ndp vectors contiguous in device memory (d_cts[d*v*128 ...]). */
+int drx_aggregate_dev(drx_ctx* ctx, size_t ndp, size_t v, const uint8_t* d_cts, uint8_t* d_out);
+
+/* libunlynx.CreateDecryptionTable (services/api.go:50): makes i*B, 0 <= i <= limit, available to drx_decrypt
+ * with negatives. The device table always spans the reference's MaxHomomorphicInt (100000); `limit` only
+ * feeds the host-side model of which entries the reference's lazily grown map would hold. */
+int drx_dlog_table(drx_ctx* ctx, int64_t limit);
+/* libunlynx.DecryptInt / DecryptIntWithNeg / DecryptIntVector(WithNeg) (lib/encoding/sum.go:38, mean.go:66,
+ * variance.go:68, frequency_count.go:70, encode_decode.go:224): M = C - sk*K, then the discrete log by table.
+ * out[i] = value, or 0 with found[i] = 0 when |value| >= 100000 (the reference logs "out of bound" and
+ * returns 0). found may be NULL. */
+int drx_decrypt(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t* ct /*n*128*/, int with_neg,
+                int64_t* out, uint8_t* found);
+int drx_decrypt_dev(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t* d_ct, int64_t* d_out /*raw signed dlog, INT64_MIN = miss*/);
+/* libunlynx.DecryptCheckZero (lib/encoding/OR_AND.go:61,114): out[i] = 0 if the plaintext point is the
+ * identity, else 1. */
+int drx_decrypt_check_zero(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t* ct, int64_t* out);
+
+/* Server signatures for one output column: Y_i and A_{i,k} = (x_i + k)^-1 * g2, k < u
+ * (lib/range/range_proof.go:249-302 InitRangeProofSignature, PublishSignatureBytesToPublishSignatures;
+ * libdrynx.PublishSignatureBytes lib/structs.go:131-141). Builds the per-set tables; set_id is the caller's
+ * handle (0 <= set_id < 65536) used by create/verify. */
+int drx_rp_set_sigs(drx_ctx* ctx, int set_id, int ns, int64_t u, const uint8_t* Y /*ns*64*/,
+                    const uint8_t* A /*ns*u*128*/);
+/* InitRangeProofSignature on the device from caller-drawn private keys x_i (:254-266, :275-287):
+ * Y_out[i] = x_i*B, A_out[i][k] = (x_i + k)^-1 * g2. */
+int drx_rp_make_sigs(drx_ctx* ctx, int ns, int64_t u, const uint8_t* x /*ns*32*/, uint8_t* Y_out /*ns*64*/,
+                     uint8_t* A_out /*ns*u*128*/);
+/* Number of base-u digits ToBase(secret, u, l) yields (lib/range/range_proof.go:584-595): max(l, digits). */
+int64_t drx_rp_ndigits(int64_t secret, int64_t u, int64_t l);
+/* Serialised size of one proof with nd digits for ns servers (128 when set_id < 0: commit only). */
+size_t drx_rp_proof_size(int ns, int64_t nd);
+
+/* CreatePredicateRangeProofListForAllServers (lib/range/range_proof.go:305-407) for n values.
+ * Per proof p: set_id[p] (< 0: u = l = 0, emit the ciphertext only, :322-324), l[p], secret[p], the
+ * encryption scalar r[p], the ciphertext ct[p], and nd*(3+ns) random scalars at rnd + rnd_off[p] in the
+ * reference's draw order: for each digit j: s_j, t_j, m_j (:377-379) then v_0j .. v_{ns-1,j} (:390).
+ * Proof p is written at proofs + proof_off[p]; proof_off[p+1]-proof_off[p] must equal drx_rp_proof_size. */
+int drx_rp_create(drx_ctx* ctx, size_t n, const int32_t* set_id, const int64_t* l, const int64_t* secret,
+                  const uint8_t* r /*n*32*/, const uint8_t* ct /*n*128*/, const uint8_t* rnd,
+                  const size_t* rnd_off /*n+1, bytes*/, uint8_t* proofs, const size_t* proof_off /*n+1*/);
+/* RangeProofVerification for n proofs (lib/range/range_proof.go:504-565; list driver :484-501, caller
+ * lib/proof/structs_proofs.go:171): ok[p] = 1 iff the size check (:512), every pairing equation (:540-549)
+ * and the D check (:561) hold. set_id[p] < 0 means u = l = 0 -> 1 (:508-510). Malformed group elements
+ * yield 0 (the reference aborts in FromBytes, :225-236). */
+int drx_rp_verify(drx_ctx* ctx, size_t n, const int32_t* set_id, const int64_t* l, const uint8_t* proofs,
+                  const size_t* proof_off /*n+1*/, uint8_t* ok /*n*/);
+/* Device-resident uniform batch: n proofs of identical size (ns servers, l digits) back to back. */
+int drx_rp_verify_dev(drx_ctx* ctx, size_t n, const int32_t* d_set_id, int ns, int64_t l, const uint8_t* d_proofs,
+                      uint8_t* d_ok);
+int drx_rp_create_dev(drx_ctx* ctx, size_t n, const int32_t* d_set_id, int ns, int64_t l, const int64_t* d_secret,
+                      const uint8_t* d_r, const uint8_t* d_ct, const uint8_t* d_rnd, uint8_t* d_proofs);
+
+/* Diagnostics used by tests and bench.py: raw pairing / group operations on wire bytes, n items each. */
+int drx_pair(drx_ctx* ctx, size_t n, const uint8_t* g1 /*n*64*/, const uint8_t* g2 /*n*128*/, uint8_t* gt /*n*384*/);
+int drx_g1_mul(drx_ctx* ctx, size_t n, const uint8_t* k /*n*32*/, const uint8_t* pt /*n*64*/, uint8_t* out /*n*64*/);
+int drx_g2_mul(drx_ctx* ctx, size_t n, const uint8_t* k /*n*32*/, const uint8_t* pt /*n*128*/, uint8_t* out /*n*128*/);
+/* Field self-test: r[i] = a[i]*b[i]*2^-256 mod (which ? n : p), raw little-endian limbs, n items. */
+int drx_mont_mul(drx_ctx* ctx, size_t n, int which, const uint32_t* a, const uint32_t* b, uint32_t* r);
+/* Integer-pipe roofline probes: runs `iters` dependent steps per thread over a full grid and returns the
+ * kernel time in ms. kind 0: register-resident IMAD.WIDE chains (64 MAC32 per step per thread);
+ * kind 1: Montgomery products (one per step per thread). *work_per_ms = MAC32 (kind 0) or products (kind 1). */
+int drx_microbench(drx_ctx* ctx, int kind, int iters, double* ms, double* work);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
