@@ -330,3 +330,17 @@ int launch_microbench(cudaStream_t st, int kind, int iters, int blocks, int thre
 }
 
 }  // namespace drx
+
+namespace drx {
+// wire form of the sum of n affine points (sum of the servers' public keys, lib/range/range_proof.go:363-366)
+__global__ void k_g1_sum_wire(int n, const G1Aff* __restrict__ pts, uint32_t* __restrict__ out) {
+  if (blockIdx.x || threadIdx.x) return;
+  G1Jac acc = jac_inf<Fp>();
+  for (int i = 0; i < n; i++) acc = jac_add_aff(acc, pts[i]);
+  g1_to_wire(out, jac_to_aff(acc));
+}
+int launch_g1_sum_wire(cudaStream_t st, int n, const void* d_aff, uint8_t* d_out_wire) {
+  k_g1_sum_wire<<<1, 32, 0, st>>>(n, (const G1Aff*)d_aff, (uint32_t*)d_out_wire);
+  return 1;
+}
+}  // namespace drx

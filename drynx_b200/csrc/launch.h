@@ -31,6 +31,7 @@ int launch_decrypt(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t
 int launch_g1_mul(cudaStream_t st, size_t n, const uint8_t* d_k, const uint8_t* d_pt, uint8_t* d_out, int* d_bad);
 int launch_mont_mul(cudaStream_t st, size_t n, int which, const uint32_t* d_a, const uint32_t* d_b, uint32_t* d_r);
 int launch_microbench(cudaStream_t st, int kind, int iters, int blocks, int threads, uint32_t* d_sink);
+int launch_g1_sum_wire(cudaStream_t st, int n, const void* d_aff, uint8_t* d_out_wire);
 
 // ---- kernels_rp.cu
 int launch_g2_from_wire(cudaStream_t st, size_t n, const uint8_t* d_wire, void* d_aff, int* d_bad);

@@ -1,0 +1,196 @@
+"""-m gpu: the CUDA ElGamal path through the C ABI against the oracle (bit-exact), following the reference's
+round-trip tests (lib/encoding/sum_test.go, mean_test.go, frequency_count_test.go) and adding the byte-level and
+edge cases the reference never pins."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import bn256_ref as R
+from conftest import SplitMix
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), 'golden')
+
+
+def _limbs(x):
+    return [(x >> (32 * k)) & 0xffffffff for k in range(8)]
+
+
+def _keys(rng):
+    sk = rng.scalar()
+    return sk, R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+
+
+def test_field_ops_bit_exact(backend, rng):
+    N = 2048
+    for which, mod in ((0, R.p), (1, R.n)):
+        xs = [rng.scalar() % mod for _ in range(N)]
+        ys = [rng.scalar() % mod for _ in range(N)]
+        xs[:4] = [mod - 1, 0, 1, mod - 1]
+        ys[:4] = [mod - 1, mod - 1, 1, 2 ** 255]
+        a = np.array([_limbs(x) for x in xs], np.uint32).ravel()
+        b = np.array([_limbs(y) for y in ys], np.uint32).ravel()
+        un = lambda r: [sum(int(v) << (32 * k) for k, v in enumerate(row)) for row in r.reshape(N, 8)]
+        rinv = pow(1 << 256, -1, mod)
+        assert un(backend.mont_mul(which, a, b)) == [x * y * rinv % mod for x, y in zip(xs, ys)]
+        assert un(backend.mont_mul(2 + 2 * which, a, b)) == [(x + y) % mod for x, y in zip(xs, ys)]
+        assert un(backend.mont_mul(3 + 2 * which, a, b)) == [(x - y) % mod for x, y in zip(xs, ys)]
+
+
+def test_generators_match_oracle(backend, oracle):
+    g1, g2 = oracle.generators()
+    one = (1).to_bytes(32, 'big')
+    assert backend.g1_mul(one, g1).tobytes() == g1 and backend.g2_mul(one, g2).tobytes() == g2
+
+
+def test_group_ops_and_pairing_match_oracle(backend, oracle, rng):
+    g1, g2 = oracle.generators()
+    ks = [0, 1, 2, R.n - 1] + [rng.scalar() for _ in range(12)]
+    pts1 = [oracle.g1_mul(rng.scalar().to_bytes(32, 'big'), g1) for _ in ks]
+    pts2 = [oracle.g2_mul(rng.scalar().to_bytes(32, 'big'), g2) for _ in ks]
+    kb = b''.join(k.to_bytes(32, 'big') for k in ks)
+    o1 = backend.g1_mul(kb, b''.join(pts1)).tobytes()
+    o2 = backend.g2_mul(kb, b''.join(pts2)).tobytes()
+    e = backend.pair(b''.join(pts1), b''.join(pts2)).tobytes()
+    for i, k in enumerate(ks):
+        assert o1[64 * i:64 * i + 64] == oracle.g1_mul(k.to_bytes(32, 'big'), pts1[i])
+        assert o2[128 * i:128 * i + 128] == oracle.g2_mul(k.to_bytes(32, 'big'), pts2[i])
+        assert e[384 * i:384 * i + 384] == oracle.pair(pts1[i], pts2[i])
+    # infinity in either slot -> 1
+    one = R.f12_to_bytes(R.F12_ONE)
+    assert backend.pair(bytes(64) + pts1[4], pts2[4] + bytes(128)).tobytes() == one + one
+
+
+def test_malformed_points_rejected(backend):
+    from drynx_b200 import DrynxGpuError
+    bad = (5).to_bytes(32, 'big') + (7).to_bytes(32, 'big')
+    with pytest.raises(DrynxGpuError):
+        backend.g1_mul((1).to_bytes(32, 'big'), bad)
+    noncanon = (R.p + 1).to_bytes(32, 'big') + (R.p - 2).to_bytes(32, 'big')
+    with pytest.raises(DrynxGpuError):
+        backend.g1_mul((1).to_bytes(32, 'big'), noncanon)
+    with pytest.raises(DrynxGpuError):
+        backend.set_pubkey(bad)
+    with pytest.raises(DrynxGpuError):
+        backend.aggregate([bad + bad])
+
+
+def test_encrypt_bytes_match_oracle(backend, oracle, rng):
+    sk, P = _keys(rng)
+    backend.set_pubkey(P)
+    ms = [0, 1, -1, 9, -12000, 99999, 100000, 2 ** 40 + 3, -(2 ** 62), 2 ** 63 - 1, -(2 ** 63)]
+    ms += [rng.randint(-10 ** 6, 10 ** 6) for _ in range(500)]
+    rs = [rng.scalar() for _ in ms]
+    rs[3] = 0
+    rs[4] = R.n - 1
+    rb = b''.join(r.to_bytes(32, 'big') for r in rs)
+    got = backend.encrypt_int_vector(ms, rb).tobytes()
+    assert got == oracle.encrypt(P, ms, rb, threads=8)
+    assert backend.encrypt_int_vector([], b'').size == 0
+    # a scalar given unreduced (r + n < 2^256) encrypts like r: kyber SetBytes reduces mod n
+    r_small = 12345
+    a = backend.encrypt_int_vector([7], (r_small + R.n).to_bytes(32, 'big')).tobytes()
+    assert a == oracle.encrypt(P, [7], r_small.to_bytes(32, 'big'))
+
+
+def test_golden_encrypt_vectors(backend):
+    with open(os.path.join(GOLD, 'bn256_golden.json')) as f:
+        g = json.load(f)
+    backend.set_pubkey(bytes.fromhex(g['encrypt'][0]['P']))
+    for v in g['encrypt']:
+        assert backend.encrypt_int_vector([v['m']], bytes.fromhex(v['r'])).tobytes().hex() == v['ct']
+    for v in g['g1_mul']:
+        assert backend.g1_mul(bytes.fromhex(v['k']), bytes.fromhex(v['p'])).tobytes().hex() == v['out']
+    for v in g['g2_mul']:
+        assert backend.g2_mul(bytes.fromhex(v['k']), bytes.fromhex(v['p'])).tobytes().hex() == v['out']
+    for v in g['pair']:
+        assert backend.pair(bytes.fromhex(v['g1']), bytes.fromhex(v['g2'])).tobytes().hex() == v['out']
+
+
+@pytest.mark.parametrize('ndp,v', [(1, 1), (2, 3), (10, 1), (7, 33), (65, 5), (130, 2)])
+def test_aggregate_bytes_match_oracle(backend, oracle, rng, ndp, v):
+    sk, P = _keys(rng)
+    backend.set_pubkey(P)
+    vecs = []
+    for d in range(ndp):
+        m = [rng.randint(-1000, 1000) for _ in range(v)]
+        vecs.append(backend.encrypt_int_vector(m, rng.scalars_bytes(v)).tobytes())
+    rc, want = oracle.aggregate(vecs, threads=8)
+    assert rc == 0
+    assert backend.aggregate(vecs).tobytes() == want
+
+
+def test_aggregate_exceptional_points(backend, oracle, rng):
+    """P + P (doubling inside an add), P + (-P) (identity), identity inputs."""
+    sk, P = _keys(rng)
+    backend.set_pubkey(P)
+    ct = backend.encrypt_int_vector([5], rng.scalars_bytes(1)).tobytes()
+    K, C = R.g1_from_bytes(ct[:64]), R.g1_from_bytes(ct[64:])
+    neg = R.g1_to_bytes(R.g1_neg(K)) + R.g1_to_bytes(R.g1_neg(C))
+    zero = bytes(128)
+    for vecs in ([ct, ct], [ct, neg], [zero, ct], [ct, zero, neg], [zero, zero], [ct, ct, ct, neg]):
+        rc, want = oracle.aggregate(vecs)
+        assert rc == 0
+        assert backend.aggregate(vecs).tobytes() == want
+
+
+def test_sum_mean_frequency_round_trips(backend, oracle, rng):
+    """lib/encoding/sum_test.go:15-31 (-> -11955), mean_test.go:15-32 (sum and count),
+    frequency_count_test.go:15-40 (histogram), with CreateDecryptionTable(10000) as services/api.go:50."""
+    sk, P = _keys(rng)
+    skb = sk.to_bytes(32, 'big')
+    backend.set_pubkey(P)
+    backend.create_decryption_table(10000)
+    inputs = [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, -12000]
+    ct = backend.encrypt_int_vector([sum(inputs)], rng.scalars_bytes(1))
+    assert list(backend.decrypt_int_vector(skb, ct)) == [-11955]
+    ct = backend.encrypt_int_vector([sum(inputs), len(inputs)], rng.scalars_bytes(2))
+    s, cnt = backend.decrypt_int_vector(skb, ct)
+    assert s / cnt == sum(inputs) / len(inputs)
+    data = [1, 2, 2, 3, 5, 5, 5, 9]
+    hist = [data.count(b) for b in range(0, 10)]
+    dps = [backend.encrypt_int_vector(hist, rng.scalars_bytes(10)).tobytes() for _ in range(3)]
+    agg = backend.aggregate(dps)
+    assert list(backend.decrypt_int_vector(skb, agg)) == [3 * h for h in hist]
+    assert list(backend.decrypt_check_zero(skb, agg)) == [0 if h == 0 else 1 for h in hist]
+
+
+def test_decrypt_matches_oracle_including_table_state(oracle, rng):
+    """Fresh contexts on both sides; the same call sequence must give the same values and found flags,
+    including the reference's lazily-grown-table quirks (negatives only stored while checkNeg grew it)."""
+    from drynx_b200 import Backend
+    be = Backend(0)
+    try:
+        sk, P = _keys(rng)
+        skb = sk.to_bytes(32, 'big')
+        be.set_pubkey(P)
+        seq = [([5, 7, 2], False), ([-3, 4], False), ([-3, -20000, 20000], True), ([99999, -99999, 100000, -100000], True),
+               ([-7, 0, 12], True), ([-1], False)]
+        oracle.dlog_reset()
+        for ms, with_neg in seq:
+            ct = oracle.encrypt(P, ms, rng.scalars_bytes(len(ms)))
+            want, wf = oracle.decrypt(skb, ct, with_neg=with_neg)
+            got, gf = be.decrypt_int_vector(skb, ct, with_neg=with_neg, return_found=True)
+            assert list(got) == list(want) and list(gf) == list(wf), (ms, with_neg)
+    finally:
+        be.close()
+
+
+def test_full_size_frequency_count_properties(backend, rng):
+    """BASELINE config 4 shape scaled to what the test budget allows: 200 DPs x 1000 bins. Property check:
+    decrypt(aggregate(encrypt(x_d))) == sum_d x_d, and aggregation is order-independent."""
+    sk, P = _keys(rng)
+    skb = sk.to_bytes(32, 'big')
+    backend.set_pubkey(P)
+    ndp, v = 200, 1000
+    g = np.random.default_rng(4)
+    counts = g.integers(0, 10, size=(ndp, v), dtype=np.int64)
+    r = np.frombuffer(g.bytes(32 * ndp * v), np.uint8).copy()
+    r[::32] &= 0x7f
+    cts = backend.encrypt_int_vector(counts.ravel(), r).reshape(ndp, v * 128)
+    agg = backend.aggregate([cts[d] for d in range(ndp)])
+    assert list(backend.decrypt_int_vector(skb, agg)) == list(counts.sum(axis=0))
+    perm = g.permutation(ndp)
+    assert backend.aggregate([cts[d] for d in perm]).tobytes() == agg.tobytes()

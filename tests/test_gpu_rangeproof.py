@@ -1,0 +1,189 @@
+"""-m gpu: range-proof creation and verification through the C ABI against the oracle.
+Mirrors lib/range/range_proof_test.go:43-77 (create -> bytes -> verify == true) and the *WithProofs encoder tests
+(lib/encoding/sum_test.go:34-57), and adds byte-level equality plus the rejection cases the reference lacks."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import bn256_ref as R
+from conftest import SplitMix
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), 'golden')
+
+
+def _setup(backend, oracle, rng, ns, u, set_id=0):
+    sk = rng.scalar()
+    P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+    backend.set_pubkey(P)
+    xs = [rng.scalar() for _ in range(ns)]
+    Y, A = backend.init_range_proof_signature(xs, u)
+    Yo, Ao = oracle.make_sigs(xs, u)
+    assert Y.tobytes() == Yo and A.tobytes() == Ao
+    backend.set_signatures(set_id, ns, u, Y, A)
+    return sk, P, Yo, Ao
+
+
+def _make(backend, oracle, rng, P, ns, u, l, secrets):
+    rs = b''.join(rng.scalar().to_bytes(32, 'big') for _ in secrets)
+    cts = backend.encrypt_int_vector(secrets, rs).tobytes()
+    rnd = [rng.scalars_bytes(len(R.to_base(s, u, l)) * (3 + ns)) for s in secrets]
+    return rs, cts, rnd
+
+
+def test_deterministic_signature(backend, oracle):
+    """InitRangeProofSignatureDeterministic: x = 12 (lib/range/range_proof.go:249-267)."""
+    Y, A = backend.init_range_proof_signature([12], 16)
+    Yo, Ao = oracle.make_sigs([12], 16)
+    assert Y.tobytes() == Yo and A.tobytes() == Ao
+
+
+@pytest.mark.parametrize('ns,u,l', [(1, 2, 1), (5, 2, 1), (2, 4, 2), (3, 16, 4), (1, 16, 8)])
+def test_create_bytes_match_oracle_and_verify(backend, oracle, rng, ns, u, l):
+    sk, P, Y, A = _setup(backend, oracle, rng, ns, u)
+    secrets = [0, 1, u ** l - 1, (u ** l) // 2] + [rng.randint(0, u ** l - 1) for _ in range(4)]
+    rs, cts, rnd = _make(backend, oracle, rng, P, ns, u, l, secrets)
+    n = len(secrets)
+    proofs, off = backend.create_range_proofs([0] * n, {0: ns}, {0: u}, [l] * n, secrets, rs, cts, rnd)
+    want, woff = oracle.rp_create(ns, u, l, Y, A, P, secrets, rs, cts, rnd, threads=8)
+    assert list(off) == list(woff)
+    assert proofs.tobytes() == want
+    ok = backend.verify_range_proofs([0] * n, [l] * n, proofs, off)
+    assert list(ok) == [1] * n
+    assert list(oracle.rp_verify(ns, u, l, Y, P, proofs.tobytes(), off, threads=8)) == [1] * n
+
+
+def test_out_of_range_secrets_and_negative(backend, oracle, rng):
+    """A secret >= u^l needs more digits (ToBase grows the list) so verification fails the size check (:512);
+    a negative secret gets all-zero digits (:587) and an inconsistent D."""
+    ns, u, l = 2, 4, 2
+    sk, P, Y, A = _setup(backend, oracle, rng, ns, u)
+    secrets = [16, 255, -3, 15]
+    rs, cts, rnd = _make(backend, oracle, rng, P, ns, u, l, secrets)
+    n = len(secrets)
+    proofs, off = backend.create_range_proofs([0] * n, {0: ns}, {0: u}, [l] * n, secrets, rs, cts, rnd)
+    want, woff = oracle.rp_create(ns, u, l, Y, A, P, secrets, rs, cts, rnd)
+    assert proofs.tobytes() == want and list(off) == list(woff)
+    ok = backend.verify_range_proofs([0] * n, [l] * n, proofs, off)
+    assert list(ok) == list(oracle.rp_verify(ns, u, l, Y, P, want, woff)) == [0, 0, 0, 1]
+
+
+def test_tampered_and_malformed_proofs_rejected_like_oracle(backend, oracle, rng):
+    ns, u, l = 3, 16, 2
+    sk, P, Y, A = _setup(backend, oracle, rng, ns, u)
+    rs, cts, rnd = _make(backend, oracle, rng, P, ns, u, l, [77])
+    proof, off = backend.create_range_proofs([0], {0: ns}, {0: u}, [l], [77], rs, cts, rnd)
+    proof = proof.tobytes()
+    size = len(proof)
+    nd = l
+    blk = 256 + 32 * nd
+    positions = [5, 70, 130, 165, 200, 250, 260, 300, blk + 3, blk + 128 + 7, blk + 128 * nd + 5, blk + 128 * nd + 384 + 100,
+                 blk + 512 * nd + 9, blk + 544 * nd + 64, size - 1]
+    batch = [proof]
+    for pos in positions:
+        b = bytearray(proof)
+        b[pos] ^= 0x01
+        batch.append(bytes(b))
+    z = bytearray(proof); z[192:256] = bytes(64); batch.append(bytes(z))           # D = infinity
+    z = bytearray(proof); z[blk:blk + 128] = bytes(128); batch.append(bytes(z))    # V_00 = infinity
+    z = bytearray(proof); z[128:160] = bytes(32); batch.append(bytes(z))           # c = 0
+    n = len(batch)
+    offs = np.arange(n + 1, dtype=np.uint64) * size
+    ok = backend.verify_range_proofs([0] * n, [l] * n, b''.join(batch), offs)
+    want = oracle.rp_verify(ns, u, l, Y, P, b''.join(batch), offs, threads=8)
+    assert list(ok) == list(want)
+    assert ok[0] == 1 and sum(ok[1:]) == 0
+
+
+def test_mixed_batch_sets_sizes_and_bypass(backend, oracle, rng):
+    """Different signature sets / (u, l) per proof (QueryToProofsNbrs-style ranges), commit-only proofs
+    (u = l = 0, lib/range/range_proof.go:322-324 and :508-510) and a wrong-l proof, in one call."""
+    sk = rng.scalar()
+    P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+    backend.set_pubkey(P)
+    sets = {}
+    for sid, (ns, u) in {3: (2, 4), 5: (1, 16), 6: (2, 2)}.items():
+        xs = [rng.scalar() for _ in range(ns)]
+        Y, A = oracle.make_sigs(xs, u)
+        backend.set_signatures(sid, ns, u, Y, A)
+        sets[sid] = (ns, u, Y, A)
+    plan = [(3, 2, 9), (-1, 0, 5), (5, 3, 4000), (6, 4, 13), (3, 3, 63), (-1, 0, 0), (5, 1, 15)]
+    sids = [p[0] for p in plan]; ls = [p[1] for p in plan]; secrets = [p[2] for p in plan]
+    rs = b''.join(rng.scalar().to_bytes(32, 'big') for _ in plan)
+    cts = backend.encrypt_int_vector(secrets, rs).tobytes()
+    rnd = []
+    for sid, l, s in plan:
+        rnd.append(b'' if sid < 0 else rng.scalars_bytes(len(R.to_base(s, sets[sid][1], l)) * (3 + sets[sid][0])))
+    proofs, off = backend.create_range_proofs(sids, {k: v[0] for k, v in sets.items()}, {k: v[1] for k, v in sets.items()},
+                                              ls, secrets, rs, cts, rnd)
+    pb = proofs.tobytes()
+    for i, (sid, l, s) in enumerate(plan):
+        mine = pb[int(off[i]):int(off[i + 1])]
+        if sid < 0:
+            assert mine == cts[128 * i:128 * i + 128]
+            continue
+        ns, u, Y, A = sets[sid]
+        want, _ = oracle.rp_create(ns, u, l, Y, A, P, [s], rs[32 * i:32 * i + 32], cts[128 * i:128 * i + 128], [rnd[i]])
+        assert mine == want
+    ok = backend.verify_range_proofs(sids, ls, proofs, off)
+    assert list(ok) == [1] * len(plan)
+    ls_bad = list(ls); ls_bad[0] = 3; ls_bad[3] = 1
+    ok = backend.verify_range_proofs(sids, ls_bad, proofs, off)
+    assert list(ok) == [0, 1, 1, 0, 1, 1, 1]
+    from drynx_b200 import DrynxGpuError
+    with pytest.raises(DrynxGpuError):
+        backend.verify_range_proofs([9], [2], pb[:int(off[1])], off[:2])  # unknown signature set
+
+
+def test_golden_range_proofs(backend):
+    with open(os.path.join(GOLD, 'bn256_golden.json')) as f:
+        g = json.load(f)
+    for i, v in enumerate(g['range_proof']):
+        backend.set_pubkey(bytes.fromhex(v['P']))
+        Y, A = backend.init_range_proof_signature([int(v['x'][64 * k:64 * k + 64], 16) for k in range(v['ns'])], v['u'])
+        assert Y.tobytes().hex() == v['Y'] and A.tobytes().hex() == v['A']
+        backend.set_signatures(20 + i, v['ns'], v['u'], Y, A)
+        proofs, off = backend.create_range_proofs([20 + i], {20 + i: v['ns']}, {20 + i: v['u']}, [v['l']], [v['secret']],
+                                                  bytes.fromhex(v['r']), bytes.fromhex(v['ct']), [bytes.fromhex(v['rnd'])])
+        assert proofs.tobytes().hex() == v['proof']
+        assert list(backend.verify_range_proofs([20 + i], [v['l']], proofs, off)) == [1 if v['valid'] else 0]
+
+
+def test_config2_shape_create_verify_properties(backend, oracle, rng):
+    """BASELINE config 2 shape: u=16, l=4, ns=3, mean (2 outputs) + variance (3 outputs) per DP, here 40 DPs
+    (200 proofs, 2400 pairing checks). Oracle on a subsample; verify(create) == 1 for all; one flipped byte in
+    1% of the proofs flips exactly those bits."""
+    ns, u, l = 3, 16, 4
+    sk = rng.scalar()
+    P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+    backend.set_pubkey(P)
+    nout, ndp = 5, 40
+    sets = {}
+    for o in range(nout):
+        xs = [rng.scalar() for _ in range(ns)]
+        Y, A = backend.init_range_proof_signature(xs, u)
+        backend.set_signatures(o, ns, u, Y, A)
+        sets[o] = (Y.tobytes(), A.tobytes())
+    g = np.random.default_rng(2)
+    secrets = g.integers(0, 40001, size=ndp * nout).astype(np.int64)
+    sids = [i % nout for i in range(ndp * nout)]
+    n = len(sids)
+    rs = b''.join(rng.scalar().to_bytes(32, 'big') for _ in range(n))
+    cts = backend.encrypt_int_vector(secrets, rs).tobytes()
+    rnd = [rng.scalars_bytes(l * (3 + ns)) for _ in range(n)]
+    proofs, off = backend.create_range_proofs(sids, {o: ns for o in sets}, {o: u for o in sets}, [l] * n, secrets, rs, cts, rnd)
+    pb = proofs.tobytes()
+    for i in (0, 7, 101, n - 1):
+        Y, A = sets[sids[i]]
+        want, _ = oracle.rp_create(ns, u, l, Y, A, P, [int(secrets[i])], rs[32 * i:32 * i + 32], cts[128 * i:128 * i + 128], [rnd[i]])
+        assert pb[int(off[i]):int(off[i + 1])] == want
+    assert list(backend.verify_range_proofs(sids, [l] * n, proofs, off)) == [1] * n
+    bad = bytearray(pb)
+    flipped = [3, 150]
+    size = int(off[1])
+    bad[3 * size + 170] ^= 4          # Zr
+    bad[150 * size + size - 40] ^= 1  # last Zv
+    ok = backend.verify_range_proofs(sids, [l] * n, bytes(bad), off)
+    assert [i for i in range(n) if not ok[i]] == flipped

@@ -1,0 +1,69 @@
+"""Runs the DEVICE headers (drynx_b200/csrc/*.cuh) compiled for the host, where the PTX carry-chain wrappers are
+modelled in C, against the oracle. This checks the GPU algorithms (Montgomery rows, tower, curve, Miller loop,
+final exponentiation, comb tables) on the CPU; the real kernels are checked by the -m gpu tests."""
+import ctypes
+
+import numpy as np
+import pytest
+
+import bn256_ref as R
+
+
+@pytest.fixture(scope='module')
+def emu():
+    from drynx_b200 import build
+    return ctypes.CDLL(build.build_hostemu())
+
+
+def _limbs(x):
+    return [(x >> (32 * k)) & 0xffffffff for k in range(8)]
+
+
+def test_montgomery_rows(emu, rng):
+    for which, mod in ((0, R.p), (1, R.n)):
+        rinv = pow(1 << 256, -1, mod)
+        cases = [(mod - 1, mod - 1), (0, 5), (1, 1), (mod - 1, 2 ** 255), (2 ** 256 - 1 - (2 ** 256 - mod), mod - 2)]
+        cases += [(rng.scalar() % mod, rng.scalar() % mod) for _ in range(300)]
+        for a, b in cases:
+            A = np.array(_limbs(a), np.uint32); B = np.array(_limbs(b), np.uint32); Rr = np.zeros(8, np.uint32)
+            emu.emu_fp_mul_raw(A.ctypes.data, B.ctypes.data, Rr.ctypes.data, which)
+            got = sum(int(v) << (32 * k) for k, v in enumerate(Rr))
+            assert got == a * b * rinv % mod
+
+
+def test_g1_g2_scalar_mult(emu, oracle, rng):
+    for method in (0, 1):
+        for k in (1, 255, 256, R.n - 1, rng.scalar()):
+            P = oracle.g1_mul(rng.scalar().to_bytes(32, 'big'), oracle.generators()[0])
+            out = ctypes.create_string_buffer(64)
+            assert emu.emu_g1_mul(k.to_bytes(32, 'big'), P, out, method) == 0
+            assert out.raw == oracle.g1_mul(k.to_bytes(32, 'big'), P)
+    Q = oracle.g2_mul(rng.scalar().to_bytes(32, 'big'), oracle.generators()[1])
+    k = rng.scalar()
+    out = ctypes.create_string_buffer(128)
+    assert emu.emu_g2_mul(k.to_bytes(32, 'big'), Q, out) == 0
+    assert out.raw == oracle.g2_mul(k.to_bytes(32, 'big'), Q)
+
+
+def test_g1_add_exceptional_cases(emu, rng):
+    P = R.g1_mul(5, R.G1_GEN)
+    for A, B in [(P, P), (P, R.g1_neg(P)), (None, P), (P, None), (None, None), (P, R.g1_mul(7, R.G1_GEN))]:
+        out = ctypes.create_string_buffer(64)
+        assert emu.emu_g1_add(R.g1_to_bytes(A), R.g1_to_bytes(B), out) == 0
+        assert out.raw == R.g1_to_bytes(R.g1_add(A, B))
+
+
+def test_pairing_tower_and_gt_pow(emu, oracle, rng):
+    g1, g2 = oracle.generators()
+    P = oracle.g1_mul(rng.scalar().to_bytes(32, 'big'), g1)
+    Q = oracle.g2_mul(rng.scalar().to_bytes(32, 'big'), g2)
+    out = ctypes.create_string_buffer(384)
+    assert emu.emu_pair(P, Q, out) == 0
+    assert out.raw == oracle.pair(P, Q)
+    assert emu.emu_tower_selfcheck(out.raw) == 0
+    k = rng.scalar()
+    o2 = ctypes.create_string_buffer(384)
+    assert emu.emu_gt_pow(out.raw, k.to_bytes(32, 'big'), o2) == 0
+    assert o2.raw == R.f12_to_bytes(R.f12pow(R.f12_from_bytes(out.raw), k))
+    bad = bytes(63) + b'\x05' + bytes(63) + b'\x07'
+    assert emu.emu_pair(bad[:64], Q, out) == -1

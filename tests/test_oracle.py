@@ -1,0 +1,180 @@
+"""Pins the C++ oracle (oracle/oracle.cpp: kyber / unlynx / lib/range algorithms restated) against the
+mathematical definition in oracle/bn256_ref.py and the committed golden vectors. CPU only."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import bn256_ref as R
+from conftest import SplitMix
+
+GOLD = os.path.join(os.path.dirname(__file__), 'golden')
+
+
+def test_generators_and_order(oracle):
+    g1, g2 = oracle.generators()
+    assert g1 == R.g1_to_bytes(R.G1_GEN) and g2 == R.g2_to_bytes(R.G2_GEN)
+    assert R.g1_on_curve(R.G1_GEN) and R.g2_on_curve(R.G2_GEN)
+    assert oracle.g1_mul(R.n.to_bytes(32, 'big'), g1) == bytes(64)  # n reduces to 0 -> infinity
+    assert oracle.g2_mul((R.n - 1).to_bytes(32, 'big'), g2) == R.g2_to_bytes(R.g2_neg(R.G2_GEN))
+
+
+def test_scalar_mults_match_definition(oracle, rng):
+    for k in [0, 1, 2, 3, 255, 256, R.n - 1, rng.scalar(), rng.scalar()]:
+        P = R.g1_mul(rng.scalar(), R.G1_GEN)
+        Q = R.g2_mul(rng.scalar(), R.G2_GEN)
+        kb = k.to_bytes(32, 'big')
+        assert oracle.g1_mul(kb, R.g1_to_bytes(P)) == R.g1_to_bytes(R.g1_mul(k, P))
+        assert oracle.g2_mul(kb, R.g2_to_bytes(Q)) == R.g2_to_bytes(R.g2_mul(k, Q))
+
+
+def test_pairing_matches_definition_and_is_bilinear(oracle, rng):
+    a, b = rng.scalar(), rng.scalar()
+    P, Q = R.g1_mul(a, R.G1_GEN), R.g2_mul(b, R.G2_GEN)
+    e = oracle.pair(R.g1_to_bytes(P), R.g2_to_bytes(Q))
+    assert e == R.f12_to_bytes(R.pair(P, Q))
+    base = R.f12_from_bytes(oracle.pair(*oracle.generators()))
+    assert R.f12_to_bytes(R.f12pow(base, a * b % R.n)) == e
+    assert R.f12pow(base, R.n) == R.F12_ONE
+    assert oracle.pair(bytes(64), R.g2_to_bytes(Q)) == R.f12_to_bytes(R.F12_ONE)  # infinity -> 1
+
+
+def test_malformed_points_are_rejected(oracle):
+    bad = (5).to_bytes(32, 'big') + (7).to_bytes(32, 'big')
+    out = np.zeros(64, np.uint8)
+    assert oracle.lib.orc_g1_mul((1).to_bytes(32, 'big'), bad, out.ctypes.data) == -1
+    big = (R.p + 1).to_bytes(32, 'big') + (R.p - 2).to_bytes(32, 'big')  # x = p + 1 == 1 mod p, non-canonical
+    assert oracle.lib.orc_g1_mul((1).to_bytes(32, 'big'), big, out.ctypes.data) == -1
+
+
+def test_encrypt_matches_definition(oracle, rng):
+    sk = rng.scalar()
+    P = R.g1_mul(sk, R.G1_GEN)
+    ms = [0, 1, -1, 9, -12000, 2 ** 40, -(2 ** 62)]
+    rs = [rng.scalar() for _ in ms]
+    ct = oracle.encrypt(R.g1_to_bytes(P), ms, b''.join(r.to_bytes(32, 'big') for r in rs))
+    for i, (m, r) in enumerate(zip(ms, rs)):
+        assert ct[128 * i:128 * i + 128] == R.encrypt(P, m, r)
+
+
+def test_sum_round_trip_like_reference_test(oracle, rng):
+    """lib/encoding/sum_test.go:15-31: inputs {0..9, -12000} -> -11955 after encrypt/decrypt."""
+    sk = rng.scalar()
+    P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+    inputs = [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, -12000]
+    ct = oracle.encrypt(P, [sum(inputs)], rng.scalars_bytes(1))
+    oracle.dlog_reset()
+    out, found = oracle.decrypt(sk.to_bytes(32, 'big'), ct, with_neg=True)
+    assert out[0] == -11955 and found[0] == 1
+
+
+def test_aggregate_is_homomorphic(oracle, rng):
+    sk = rng.scalar()
+    P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+    vals = [[rng.randint(-50, 50) for _ in range(4)] for _ in range(3)]
+    vecs = [oracle.encrypt(P, v, rng.scalars_bytes(4)) for v in vals]
+    rc, agg = oracle.aggregate(vecs)
+    assert rc == 0
+    oracle.dlog_reset()
+    out, _ = oracle.decrypt(sk.to_bytes(32, 'big'), agg)
+    assert list(out) == [sum(v[j] for v in vals) for j in range(4)]
+    # definition: component-wise point addition
+    K = None
+    for v in vecs:
+        K = R.g1_add(K, R.g1_from_bytes(v[:64]))
+    assert agg[:64] == R.g1_to_bytes(K)
+
+
+def test_discrete_log_table_semantics(oracle, rng):
+    """unlynx discreteLog: lazily grown table, negatives only while checkNeg extended it, bound 100000."""
+    sk = rng.scalar()
+    P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+    skb = sk.to_bytes(32, 'big')
+    ct = oracle.encrypt(P, [5, -3, 99999, 100000, -7], rng.scalars_bytes(5))
+    oracle.dlog_reset()
+    out, found = oracle.decrypt(skb, ct[:128], with_neg=False)          # grows 0..5 without negatives
+    assert (out[0], found[0]) == (5, 1)
+    out, found = oracle.decrypt(skb, ct[128:256], with_neg=False)       # -3 not stored: walks to the bound
+    assert (out[0], found[0]) == (0, 0)
+    out, found = oracle.decrypt(skb, ct[256:384], with_neg=True)        # 99999 is already in the table
+    assert (out[0], found[0]) == (99999, 1)
+    out, found = oracle.decrypt(skb, ct[384:512], with_neg=True)        # out of bound
+    assert (out[0], found[0]) == (0, 0)
+    out, found = oracle.decrypt(skb, ct[512:640], with_neg=True)        # -7 never stored (table already full)
+    assert (out[0], found[0]) == (0, 0)
+
+
+def test_signatures_match_definition(oracle):
+    Y, A = oracle.make_sigs([12], 4)  # InitRangeProofSignatureDeterministic uses x = 12
+    Yd, Ad = R.init_range_sig(12, 4)
+    assert Y == R.g1_to_bytes(Yd)
+    assert A == b''.join(R.g2_to_bytes(a) for a in Ad)
+
+
+def _small_case(oracle, seed, ns, u, l, secret):
+    rng = SplitMix(seed)
+    sk = rng.scalar()
+    Pp = R.g1_mul(sk, R.G1_GEN)
+    P = R.g1_to_bytes(Pp)
+    xs = [rng.scalar() for _ in range(ns)]
+    Y, A = oracle.make_sigs(xs, u)
+    r = rng.scalar()
+    ct = oracle.encrypt(P, [secret], r.to_bytes(32, 'big'))
+    nd = len(R.to_base(secret, u, l))
+    rnd = [rng.scalar() for _ in range(nd * (3 + ns))]
+    rndb = b''.join(x.to_bytes(32, 'big') for x in rnd)
+    return dict(sk=sk, Pp=Pp, P=P, xs=xs, Y=Y, A=A, r=r, ct=ct, nd=nd, rnd=rnd, rndb=rndb)
+
+
+@pytest.mark.parametrize('ns,u,l,secret', [(1, 2, 1, 1), (2, 4, 2, 11)])
+def test_range_proof_matches_definition(oracle, ns, u, l, secret):
+    c = _small_case(oracle, 99 + ns, ns, u, l, secret)
+    proofs, off = oracle.rp_create(ns, u, l, c['Y'], c['A'], c['P'], [secret], c['r'].to_bytes(32, 'big'), c['ct'], [c['rndb']])
+    sigs = [R.init_range_sig(x, u) for x in c['xs']]
+    want = R.rp_create(sigs, u, l, secret, c['r'], c['Pp'], c['ct'], c['rnd'])
+    assert proofs == want
+    assert len(proofs) == oracle.proof_size(ns, c['nd'])
+    assert list(oracle.rp_verify(ns, u, l, c['Y'], c['P'], proofs, off)) == [1]
+    assert R.rp_verify(proofs, u, l, [s[0] for s in sigs], c['Pp']) is True
+
+
+def test_range_proof_like_reference_test_and_tamper(oracle):
+    """lib/range/range_proof_test.go:43-77 (u=2, l=1, 5 servers, create -> bytes -> verify == true), plus the
+    negative cases the reference never tests."""
+    ns, u, l, secret = 5, 2, 1, 1
+    c = _small_case(oracle, 7, ns, u, l, secret)
+    proofs, off = oracle.rp_create(ns, u, l, c['Y'], c['A'], c['P'], [secret], c['r'].to_bytes(32, 'big'), c['ct'], [c['rndb']])
+    assert list(oracle.rp_verify(ns, u, l, c['Y'], c['P'], proofs, off)) == [1]
+    for pos in (130, 170, 200, 260, 256 + 32 + 5, 256 + 32 + 128 + 9, len(proofs) - 3):
+        bad = bytearray(proofs)
+        bad[pos] ^= 1
+        assert list(oracle.rp_verify(ns, u, l, c['Y'], c['P'], bytes(bad), off)) == [0], pos
+    assert list(oracle.rp_verify(ns, u, 2, c['Y'], c['P'], proofs, off)) == [0]      # size check :512
+    assert list(oracle.rp_verify(ns, 0, 0, c['Y'], c['P'], proofs, off)) == [1]      # u = l = 0 bypass :508
+    # a value outside [0, u^l) needs more digits than l, so its proof fails the size check
+    p2, off2 = oracle.rp_create(ns, u, l, c['Y'], c['A'], c['P'], [2], c['r'].to_bytes(32, 'big'),
+                                oracle.encrypt(c['P'], [2], c['r'].to_bytes(32, 'big')), [c['rndb'] * 2])
+    assert list(oracle.rp_verify(ns, u, l, c['Y'], c['P'], p2, off2)) == [0]
+
+
+def test_golden_vectors(oracle):
+    """tests/golden/*.json were produced by tools/make_golden.py from the Python definition."""
+    with open(os.path.join(GOLD, 'bn256_golden.json')) as f:
+        g = json.load(f)
+    for v in g['g1_mul']:
+        assert oracle.g1_mul(bytes.fromhex(v['k']), bytes.fromhex(v['p'])).hex() == v['out']
+    for v in g['g2_mul']:
+        assert oracle.g2_mul(bytes.fromhex(v['k']), bytes.fromhex(v['p'])).hex() == v['out']
+    for v in g['pair']:
+        assert oracle.pair(bytes.fromhex(v['g1']), bytes.fromhex(v['g2'])).hex() == v['out']
+    for v in g['encrypt']:
+        ct = oracle.encrypt(bytes.fromhex(v['P']), [v['m']], bytes.fromhex(v['r']))
+        assert ct.hex() == v['ct']
+    for v in g['range_proof']:
+        proofs, off = oracle.rp_create(v['ns'], v['u'], v['l'], bytes.fromhex(v['Y']), bytes.fromhex(v['A']),
+                                       bytes.fromhex(v['P']), [v['secret']], bytes.fromhex(v['r']),
+                                       bytes.fromhex(v['ct']), [bytes.fromhex(v['rnd'])])
+        assert proofs.hex() == v['proof']
+        ok = oracle.rp_verify(v['ns'], v['u'], v['l'], bytes.fromhex(v['Y']), bytes.fromhex(v['P']), proofs, off)
+        assert list(ok) == [1 if v['valid'] else 0]
