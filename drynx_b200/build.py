@@ -18,7 +18,7 @@ ORACLE_SO = os.path.join(ROOT, 'oracle', '_build', 'liboracle.so')
 HOSTEMU_SO = os.path.join(ROOT, 'tests', 'hostemu', 'libhostemu.so')
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC',
-              '-Xptxas', '-v']
+              '-Xptxas', '-v'] + (['-DDRX_DEBUG_RP'] if os.environ.get('DRX_DEBUG_RP') else [])
 GPU_SOURCES = ['kernels_g1.cu', 'kernels_rp.cu', 'capi.cu']
 
 

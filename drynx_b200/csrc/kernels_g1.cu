@@ -4,6 +4,7 @@
 // SURVEY.md §8 rows a-1, a-3, a-4, a-5. One thread per ciphertext; fixed-base multiplications walk 8-bit comb
 // tables that stay L2-resident (522 KB each); all kernels are integer-pipe bound.
 #include "launch.h"
+#include "keccak.cuh"
 #include "wire.cuh"
 
 namespace drx {
@@ -278,7 +279,17 @@ __global__ void k_mont_mul(size_t n, int which, const uint32_t* __restrict__ a, 
   else if (which == 2) mod_add<ModP>(z, x, y);
   else if (which == 3) mod_sub<ModP>(z, x, y);
   else if (which == 4) mod_add<ModN>(z, x, y);
-  else mod_sub<ModN>(z, x, y);
+  else if (which == 5) mod_sub<ModN>(z, x, y);
+  else {  // which 6/7: halves of SHA3-512(x || y); 8/9: of SHA3-512((x || y) * 3)
+    uint32_t msg[48], dig[16];
+    for (int rep = 0; rep < 3; rep++)
+      for (int k = 0; k < 8; k++) {
+        msg[16 * rep + k] = x[k];
+        msg[16 * rep + 8 + k] = y[k];
+      }
+    sha3_512_words(dig, msg, which >= 8 ? 48 : 16);
+    for (int k = 0; k < 8; k++) z[k] = dig[((which & 1) ? 8 : 0) + k];
+  }
   for (int k = 0; k < 8; k++) r[8 * i + k] = z[k];
 }
 int launch_mont_mul(cudaStream_t st, size_t n, int which, const uint32_t* d_a, const uint32_t* d_b, uint32_t* d_r) {

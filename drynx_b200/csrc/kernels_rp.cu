@@ -1,6 +1,7 @@
 // BN256 pairing-based range proofs on sm_100a: creation and verification, plus the G2 / GT set-up kernels.
 // Replaces lib/range/range_proof.go:249-288 (signatures), :320-407 (CreatePredicateRangeProofForAllServ) and
 // :504-565 (RangeProofVerification) of the reference, and the kyber pairing/bn256 calls they make.
+#include <cstdio>
 #include "launch.h"
 #include "keccak.cuh"
 #include "wire.cuh"
@@ -273,6 +274,13 @@ k_rp_create_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __r
   }
   sha3_512_words(dig, msg, 48);
   const Scalar c = sc_from_digest(dig);
+#ifdef DRX_DEBUG_RP
+  if (p == 0) {
+    printf("msg %08x %08x | %08x %08x | %08x %08x\n", msg[0], msg[15], msg[16], msg[31], msg[32], msg[47]);
+    printf("dig %08x %08x %08x %08x\n", dig[0], dig[7], dig[8], dig[15]);
+    printf("c   %08x %08x\n", c.v[0], c.v[7]);
+  }
+#endif
   const uint32_t* rp = rnd + (b.d_proof_off ? rnd_off[p] / 4 : p * (size_t)nd * (3 + ns) * 8);
   ProofView pv{ns, nd};
   Scalar msum = sc_zero(), ssum = sc_zero();
