@@ -1,0 +1,457 @@
+#!/usr/bin/env python3
+"""bench.py -- BASELINE.json metric on BASELINE config 2 (mean/variance: 100 DPs x 10k rows, range proofs u=16, l=4).
+
+One "step" = one pass of the hot path for one survey on every rank's shard of data providers:
+  rows -> per-DP reduction (mean: [sum, N]; variance: [sum, N, sum of squares]) -> ElGamal encrypt (5 per DP)
+       -> range-proof creation (5 per DP, ns = 3 servers) -> range-proof verification -> per-rank aggregation
+       -> (N > 1) NCCL all-gather of the per-rank partial aggregates, fold on rank 0 -> decrypt.
+`value` is proofs verified per second of WHOLE step time (every phase inside the timed region), device-resident
+inputs; `e2e` is the same step through the host-buffer C ABI (H2D/D2H inside). ElGamal encryptions/s and the other
+per-kernel rates are reported under `secondary`. `--impl reference` times the CPU restatement (oracle/, all host
+threads) on a bounded sample of the same workload.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NS, U, L = 3, 16, 4
+NOUT = 5  # mean (2 outputs) + variance (3 outputs)
+METRIC = 'range-proof verifies/sec over the full config-2 step (ElGamal encs/sec in secondary)'
+MAC32_PER_M = 128
+# SURVEY.md section 8(d) algorithmic costs in Montgomery products (M)
+M_ENCRYPT = 824
+M_VERIFY_ITEM = 19700                      # per (server, digit): Miller 8,800 + final exp 9,100 + GT fixed 1,728 + 72
+M_VERIFY_PROOF = 3550 + 352 * (NS + L) + M_VERIFY_ITEM * NS * L
+M_CREATE_PROOF = L * (736 + NS * 4458)
+M_AGG_CT = 22
+M_DECRYPT = 2840
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='gpu', choices=['gpu', 'reference'])
+    ap.add_argument('--ndp', type=int, default=100)
+    ap.add_argument('--rows', type=int, default=10000)
+    ap.add_argument('--cpu-sample-ndp', type=int, default=0, help='DPs in the CPU sample (0 = about 3 per host core, at most --ndp)')
+    ap.add_argument('--no-secondary', action='store_true')
+    return ap.parse_args()
+
+
+class Clocks(threading.Thread):
+    """Samples nvidia-smi clocks and throttle reasons during the timed region."""
+    Q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,' \
+        'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.rows = index, False, []
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits'],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(',')])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        if not self.rows:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith('active') for r in self.rows if len(r) > 2 + k)]
+        mx = [int(r[1]) for r in self.rows if r[1].isdigit()]
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None, 'reasons': reasons,
+                'samples': len(self.rows)}
+
+
+def synth(seed, ndp, rows):
+    """Config-2 synthetic input: rows U{0,1,2}; every scalar is 32 random bytes with the top bit cleared (< n)."""
+    g = np.random.default_rng(seed)
+    data = g.integers(0, 3, size=(ndp, rows), dtype=np.int64)
+    n = ndp * NOUT
+
+    def scalars(k):
+        b = np.frombuffer(g.bytes(32 * k), dtype=np.uint8).copy()
+        b[::32] &= 0x7f
+        return b
+    return dict(rows=data, r=scalars(n), rnd=scalars(n * L * (3 + NS)), set_id=(np.arange(n, dtype=np.int32) % NOUT),
+                x=[int.from_bytes(g.bytes(31), 'big') + 1 for _ in range(NOUT * NS)], sk=int.from_bytes(g.bytes(31), 'big') + 1)
+
+
+def host_reduce(rows):
+    """lib/encoding/mean.go:19-24 + variance.go:19-27 on the host: [sum, N, sum, N, sum of squares] per DP."""
+    s = rows.sum(axis=1)
+    q = (rows * rows).sum(axis=1)
+    n = np.full_like(s, rows.shape[1])
+    return np.stack([s, n, s, n, q], axis=1).astype(np.int64).ravel()
+
+
+# ---------------------------------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, 'tests'))
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    from conftest import Oracle
+    orc = Oracle()
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, 'sched_getaffinity') else (os.cpu_count() or 1)
+    ndp = args.cpu_sample_ndp or min(args.ndp, max(2, 3 * cores))
+    d = synth(2, ndp, args.rows)
+    g1, _ = orc.generators()
+    P = orc.g1_mul(d['sk'].to_bytes(32, 'big'), g1)
+    sigs = [orc.make_sigs(d['x'][NS * o:NS * o + NS], U) for o in range(NOUT)]
+    n = ndp * NOUT
+    per_rnd = L * (3 + NS) * 32
+
+    def step():
+        m = host_reduce(d['rows'])
+        ct = orc.encrypt(P, m, d['r'], threads=cores)
+        nver = 0
+        for o in range(NOUT):  # proofs of one output column share a signature set
+            idx = [i for i in range(n) if i % NOUT == o]
+            rs = b''.join(d['r'][32 * i:32 * i + 32].tobytes() for i in idx)
+            cts = b''.join(ct[128 * i:128 * i + 128] for i in idx)
+            rnd = [d['rnd'][per_rnd * i:per_rnd * (i + 1)].tobytes() for i in idx]
+            proofs, off = orc.rp_create(NS, U, L, sigs[o][0], sigs[o][1], P, [int(m[i]) for i in idx], rs, cts, rnd, threads=cores)
+            ok = orc.rp_verify(NS, U, L, sigs[o][0], P, proofs, off, threads=cores)
+            assert ok.all()
+            nver += len(idx)
+        rc, agg = orc.aggregate([ct[128 * NOUT * k:128 * NOUT * (k + 1)] for k in range(ndp)], threads=cores)
+        out, _ = orc.decrypt(d['sk'].to_bytes(32, 'big'), agg, threads=1)
+        return nver, out
+
+    # services/api.go:50 CreateDecryptionTable(10000): once per client, outside the step
+    orc.dlog_reset()
+    orc.decrypt(d['sk'].to_bytes(32, 'big'), orc.encrypt(P, [10000], d['r'][:32]), threads=1)
+
+    for _ in range(max(args.warmup, 0)):
+        step()
+    t0 = time.perf_counter()
+    nver = 0
+    for _ in range(args.steps):
+        k, out = step()
+        nver += k
+    dt = time.perf_counter() - t0
+    val = nver / dt
+    sample = '%d of %d DPs x %d rows (%d proofs/step), oracle/oracle.cpp C++ restatement of the Go path' % (ndp, args.ndp, args.rows, n)
+    print(json.dumps({
+        'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'proofs/s', 'n_gpus': args.gpus, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': dt / args.steps * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'u64 (4x64-bit Montgomery limbs)', 'data': 'synthetic',
+        'config': {'workload': 'config 2: mean+variance, %d DPs x %d rows, u=16 l=4 ns=3 (bounded sample: %d DPs)' % (args.ndp, args.rows, ndp)},
+        'cpu_baseline': {'value': val, 'unit': 'proofs/s', 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': val, 'unit': 'proofs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }))
+
+
+# ---------------------------------------------------------------------------------------------------- GPU arm
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from drynx_b200 import Backend, _lib
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device; the GPU arm has no CPU fallback (use --impl reference)')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    be = Backend(local)
+    lib = be.lib
+    stream = torch.cuda.current_stream()
+    be.set_stream(stream.cuda_stream)
+
+    ndp, rows = args.ndp, args.rows
+    n = ndp * NOUT
+    d = synth(2 + rank, ndp, rows)
+    g1 = bytes(31) + b'\x01' + (65000549695646603732796438742359905742825358107623003571877145026864184071783 - 2).to_bytes(32, 'big')
+    # one survey key for all ranks
+    d0 = synth(2, 1, 1)
+    skb = d0['sk'].to_bytes(32, 'big')
+    P = be.g1_mul(skb, g1).tobytes()
+    be.set_pubkey(P)
+    t_setup = time.perf_counter()
+    for o in range(NOUT):
+        Y, A = be.init_range_proof_signature(d0['x'][NS * o:NS * o + NS], U)
+        be.set_signatures(o, NS, U, Y, A)
+    be.create_decryption_table(10000)
+    be.synchronize()
+    t_setup = time.perf_counter() - t_setup
+
+    proof_size = be.proof_size(NS, L)
+    T = lambda a: torch.from_numpy(a).to(dev)
+    d_rows, d_r, d_rnd, d_sid = T(d['rows']), T(d['r']), T(d['rnd']), T(d['set_id'])
+    d_m = torch.empty(n, dtype=torch.int64, device=dev)
+    d_ct = torch.empty(n * 128, dtype=torch.uint8, device=dev)
+    d_proofs = torch.empty(n * proof_size, dtype=torch.uint8, device=dev)
+    d_ok = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_agg = torch.empty(NOUT * 128, dtype=torch.uint8, device=dev)
+    d_gather = torch.empty(world * NOUT * 128, dtype=torch.uint8, device=dev)
+    d_fold = torch.empty(NOUT * 128, dtype=torch.uint8, device=dev)
+    d_dec = torch.empty(NOUT, dtype=torch.int64, device=dev)
+    d_flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    vp = lambda t: ctypes.c_void_p(t.data_ptr())
+    skbuf = np.frombuffer(skb, np.uint8).copy()
+    skp = ctypes.c_void_p(skbuf.ctypes.data)
+    ck = _lib.check
+
+    def step_dev():
+        d_flush.zero_()
+        ck(lib.drx_reduce_rows_dev(be.h, ndp, rows, vp(d_rows), 3, vp(d_m)))
+        ck(lib.drx_encrypt_dev(be.h, n, vp(d_m), vp(d_r), vp(d_ct)))
+        ck(lib.drx_rp_create_dev(be.h, n, vp(d_sid), NS, L, vp(d_m), vp(d_r), vp(d_ct), vp(d_rnd), vp(d_proofs)))
+        ck(lib.drx_rp_verify_dev(be.h, n, vp(d_sid), NS, L, vp(d_proofs), vp(d_ok)))
+        ck(lib.drx_aggregate_dev(be.h, ndp, NOUT, vp(d_ct), vp(d_agg)))
+        final = d_agg
+        if world > 1:
+            dist.all_gather_into_tensor(d_gather, d_agg)
+            if rank == 0:
+                ck(lib.drx_aggregate_dev(be.h, world, NOUT, vp(d_gather), vp(d_fold)))
+            final = d_fold
+        if rank == 0:
+            ck(lib.drx_decrypt_dev(be.h, NOUT, skp, vp(final), vp(d_dec)))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step_dev()
+    barrier()
+    # correctness of the warm-up result before anything is timed
+    assert bool((d_ok == 1).all()), 'a created proof failed verification'
+    expect = host_reduce(d['rows']).reshape(ndp, NOUT).sum(axis=0)
+    if world > 1:
+        tot = torch.from_numpy(expect).to(dev)
+        dist.all_reduce(tot)
+        expect = tot.cpu().numpy()
+    if rank == 0:
+        got = d_dec.cpu().numpy()
+        want = np.where(np.abs(expect) < 100000, expect, np.iinfo(np.int64).min)
+        assert (got == want).all(), (got, expect)
+
+    clocks = Clocks(local)
+    clocks.start()
+    ck(lib.drx_profile_enable(be.h, 1))
+    launches0 = be.launches
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_dev()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = be.launches - launches0
+    clocks.stop_flag = True
+    prof = {}
+    for k in ('k_reduce_rows', 'k_encrypt', 'k_rp_create_hdr', 'k_rp_create_items', 'k_rp_verify_hdr', 'k_rp_verify_items',
+              'k_rp_flags', 'k_agg_partial', 'k_agg_final', 'k_decrypt'):
+        tms, cnt = ctypes.c_double(), ctypes.c_uint64()
+        ck(lib.drx_profile_get(be.h, k.encode(), ctypes.byref(tms), ctypes.byref(cnt)))
+        if cnt.value:
+            prof[k] = {'ms_per_launch': tms.value / cnt.value, 'launches': cnt.value}
+    ck(lib.drx_profile_enable(be.h, 0))
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * n * args.steps / (ms / 1e3)
+
+    # ------------------------------------------------------------------ e2e: host buffers through the C ABI
+    def pinned(a):
+        t = torch.from_numpy(a).pin_memory()
+        return t, t.numpy()
+    keep = []
+    h = {}
+    for k in ('rows', 'r', 'rnd', 'set_id'):
+        t, h[k] = pinned(d[k])
+        keep.append(t)
+    t_ct, h_ct = pinned(np.empty(n * 128, np.uint8)); keep.append(t_ct)
+    t_pr, h_pr = pinned(np.empty(n * proof_size, np.uint8)); keep.append(t_pr)
+    t_ok, h_ok = pinned(np.empty(n, np.uint8)); keep.append(t_ok)
+    t_ag, h_ag = pinned(np.empty(NOUT * 128, np.uint8)); keep.append(t_ag)
+    h_dec = np.empty(NOUT, np.int64)
+    h_found = np.empty(NOUT, np.uint8)
+    h_l = np.full(n, L, np.int64)
+    poff = (np.arange(n + 1, dtype=np.uint64) * proof_size)
+    roff = (np.arange(n + 1, dtype=np.uint64) * (L * (3 + NS) * 32))
+    np_p = lambda a: ctypes.c_void_p(a.ctypes.data)
+    ptrs = (ctypes.c_void_p * ndp)(*[h_ct.ctypes.data + k * NOUT * 128 for k in range(ndp)])
+    be.set_stream(0)
+
+    def step_e2e():
+        m = host_reduce(h['rows'])
+        ck(lib.drx_encrypt(be.h, n, np_p(m), np_p(h['r']), np_p(h_ct)))
+        ck(lib.drx_rp_create(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(m), np_p(h['r']), np_p(h_ct), np_p(h['rnd']), np_p(roff),
+                             np_p(h_pr), np_p(poff)))
+        ck(lib.drx_rp_verify(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h_pr), np_p(poff), np_p(h_ok)))
+        ck(lib.drx_aggregate(be.h, ndp, NOUT, ctypes.cast(ptrs, ctypes.c_void_p), np_p(h_ag)))
+        if rank == 0 and world == 1:
+            ck(lib.drx_decrypt(be.h, NOUT, skp, np_p(h_ag), 1, np_p(h_dec), np_p(h_found)))
+        return m
+    h2d = (n * 8 + n * 32) + (n * 4 + n * 8 * 2 + n * 32 + n * 128 + h['rnd'].nbytes) + (n * 4 + n * 8 + h_pr.nbytes + n * 4) \
+        + h_ct.nbytes + (NOUT * 128 + 32)  # encrypt + create + verify + aggregate + decrypt inputs
+    d2h = h_ct.nbytes + h_pr.nbytes + n + NOUT * 128 + NOUT * 8
+    for _ in range(3):
+        step_e2e()
+    assert h_ok.all() and h_pr.tobytes() == d_proofs.cpu().numpy().tobytes(), 'e2e and device-resident legs disagree'
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_val = world * n * args.steps / e2e_s
+    be.set_stream(stream.cuda_stream)
+
+    # ------------------------------------------------------------------ roofline of the dominant kernel
+    mac_ms, mac_work = be.microbench(0, 20000)
+    peak_tmac = mac_work / mac_ms / 1e9
+    vi = prof.get('k_rp_verify_items', {'ms_per_launch': float('nan')})
+    alg_mac = n * NS * L * M_VERIFY_ITEM * MAC32_PER_M
+    achieved = alg_mac / (vi['ms_per_launch'] * 1e-3) / 1e12
+    roofline = {'bound': 'int32 IMAD.WIDE pipe', 'kernel': 'k_rp_verify_items', 'achieved': achieved, 'peak': peak_tmac,
+                'unit': 'TMAC32/s', 'frac': achieved / peak_tmac, 'traffic': None,
+                'peak_source': 'measured live: register-resident IMAD.WIDE.U32.X chains (drx_microbench kind 0); MEASURED_PEAKS.json has no integer figure',
+                'algorithmic': '%d proofs x %d (server,digit) pairs x %d M x 128 MAC32 per launch' % (n, NS * L, M_VERIFY_ITEM)}
+
+    secondary = {}
+    if not args.no_secondary and rank == 0:
+        secondary = secondary_rates(be, lib, torch, dev, stream, ck, vp, peak_tmac, skp)
+
+    # ------------------------------------------------------------------ CPU baseline (rank 0, N = 1)
+    cpu = None
+    if rank == 0 and world == 1:
+        cpu = cpu_baseline(args)
+
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    out = {
+        'metric': METRIC, 'value': value, 'unit': 'proofs/s', 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
+        'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'dtype': 'u32 (8x32-bit Montgomery limbs, 256-bit modular integers)', 'data': 'synthetic',
+        'config': {'workload': 'config 2: mean+variance, %d DPs x %d rows per GPU, u=16 l=4 ns=3, %d encryptions + %d proofs created + %d verified per GPU per step'
+                   % (ndp, rows, n, n, n), 'l2': 'flushed between steps (256 MiB memset inside the timed region)', 'sharding': 'DPs per rank; all-gather of 5x128 B partial aggregates'},
+        'clocks': clocks.summary(),
+        'e2e': {'value': e2e_val, 'unit': 'proofs/s', 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h), 'ms_per_step': e2e_s / args.steps * 1e3},
+        'gpu_launches': int(launches),
+        'roofline': roofline,
+        'kernels_ms_per_launch': {k: round(v['ms_per_launch'], 4) for k, v in prof.items()},
+        'setup_s': round(t_setup, 3),
+        'secondary': secondary,
+    }
+    if cpu is not None:
+        out['cpu_baseline'] = cpu
+    print(json.dumps(out))
+
+
+def secondary_rates(be, lib, torch, dev, stream, ck, vp, peak_tmac, skp):
+    """Per-kernel throughputs at sizes that fill the GPU: config 4 (10^6 encryptions, 1000x1000 aggregation,
+    decryption) and config 5 (verification sweep point: 20,000 proofs, u=16 l=4 ns=3)."""
+    out = {}
+    g = np.random.default_rng(4)
+
+    def timed(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    ndp, v = 1000, 1000
+    n = ndp * v
+    m = torch.from_numpy(g.integers(0, 10, size=n, dtype=np.int64)).to(dev)
+    rb = np.frombuffer(g.bytes(32 * n), np.uint8).copy()
+    rb[::32] &= 0x7f
+    r = torch.from_numpy(rb).to(dev)
+    ct = torch.empty(n * 128, dtype=torch.uint8, device=dev)
+    agg = torch.empty(v * 128, dtype=torch.uint8, device=dev)
+    dec = torch.empty(v, dtype=torch.int64, device=dev)
+    ms = timed(lambda: ck(lib.drx_encrypt_dev(be.h, n, vp(m), vp(r), vp(ct))))
+    out['elgamal_encs_per_s'] = n / ms * 1e3
+    out['encrypt_roofline_frac'] = n * M_ENCRYPT * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    ms = timed(lambda: ck(lib.drx_aggregate_dev(be.h, ndp, v, vp(ct), vp(agg))))
+    out['ciphertext_adds_per_s'] = n / ms * 1e3
+    out['aggregate_hbm_gbs'] = n * 128 / (ms * 1e-3) / 1e9
+    out['aggregate_roofline_frac'] = n * M_AGG_CT * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    nd = 1 << 17
+    dec2 = torch.empty(nd, dtype=torch.int64, device=dev)
+    ms = timed(lambda: ck(lib.drx_decrypt_dev(be.h, nd, skp, vp(ct), vp(dec2))))
+    out['decrypts_per_s'] = nd / ms * 1e3
+    out['decrypt_roofline_frac'] = nd * M_DECRYPT * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    # verification sweep point
+    npf = 20000
+    sid = torch.from_numpy((np.arange(npf, dtype=np.int32) % NOUT)).to(dev)
+    sec = torch.from_numpy(g.integers(0, 16 ** L, size=npf, dtype=np.int64)).to(dev)
+    rb2 = np.frombuffer(g.bytes(32 * npf * (1 + L * (3 + NS))), np.uint8).copy()
+    rb2[::32] &= 0x7f
+    r2 = torch.from_numpy(rb2[:32 * npf]).to(dev)
+    rnd = torch.from_numpy(rb2[32 * npf:]).to(dev)
+    ct2 = torch.empty(npf * 128, dtype=torch.uint8, device=dev)
+    size = be.proof_size(NS, L)
+    proofs = torch.empty(npf * size, dtype=torch.uint8, device=dev)
+    ok = torch.empty(npf, dtype=torch.uint8, device=dev)
+    ck(lib.drx_encrypt_dev(be.h, npf, vp(sec), vp(r2), vp(ct2)))
+    ms = timed(lambda: ck(lib.drx_rp_create_dev(be.h, npf, vp(sid), NS, L, vp(sec), vp(r2), vp(ct2), vp(rnd), vp(proofs))), reps=2)
+    out['proofs_created_per_s'] = npf / ms * 1e3
+    out['create_roofline_frac'] = npf * M_CREATE_PROOF * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    ms = timed(lambda: ck(lib.drx_rp_verify_dev(be.h, npf, vp(sid), NS, L, vp(proofs), vp(ok))), reps=2)
+    assert bool((ok == 1).all())
+    out['proofs_verified_per_s_20k_batch'] = npf / ms * 1e3
+    out['verify_roofline_frac_20k_batch'] = npf * M_VERIFY_PROOF * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    return out
+
+
+def cpu_baseline(args):
+    """Times `bench.py --impl reference` logic in-process on a bounded sample (rank 0, N = 1 only)."""
+    p = subprocess.run([sys.executable, os.path.abspath(__file__), '--impl', 'reference', '--steps', '1', '--warmup', '0',
+                        '--ndp', str(args.ndp), '--rows', str(args.rows), '--cpu-sample-ndp', str(args.cpu_sample_ndp)],
+                       capture_output=True, text=True)
+    try:
+        return json.loads(p.stdout.strip().splitlines()[-1])['cpu_baseline']
+    except Exception:
+        return {'value': None, 'unit': 'proofs/s', 'cores': os.cpu_count(), 'kind': 'port', 'sample': 'failed: ' + p.stderr[-200:]}
+
+
+if __name__ == '__main__':
+    a = parse()
+    if a.impl == 'reference':
+        run_reference(a)
+    else:
+        run_gpu(a)

@@ -115,6 +115,17 @@ struct DlogModel {
   }
 };
 
+// Optional per-kernel timing: CUDA event pairs recorded on the launching stream around selected kernels.
+struct ProfSpan {
+  std::string name;
+  cudaEvent_t a, b;
+};
+struct Profiler {
+  bool on = false;
+  std::vector<ProfSpan> spans;
+  std::map<std::string, std::pair<double, uint64_t>> totals;  // name -> (ms, launches)
+};
+
 struct RpSetHost {
   int ns = 0;
   int64_t u = 0;
@@ -132,6 +143,7 @@ struct drx_ctx {
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
       sets_dev, sink;
   Arena arena;
+  Profiler prof;
   DlogModel dlog;
   std::map<int, RpSetHost> sets;
   int sets_dev_count = 0;
@@ -164,6 +176,36 @@ int check_launch(const char* what) {
     int r_ = (x);         \
     if (r_) return r_;    \
   } while (0)
+
+// Brackets the kernels `fn` launches with an event pair when profiling is on; always counts launches.
+template <class Fn>
+void timed(drx_ctx* c, const char* name, Fn fn) {
+  if (!c->prof.on) {
+    c->launches += fn();
+    return;
+  }
+  ProfSpan sp;
+  sp.name = name;
+  cudaEventCreate(&sp.a);
+  cudaEventCreate(&sp.b);
+  cudaEventRecord(sp.a, c->stream);
+  c->launches += fn();
+  cudaEventRecord(sp.b, c->stream);
+  c->prof.spans.push_back(sp);
+}
+void prof_collect(drx_ctx* c) {
+  for (auto& sp : c->prof.spans) {
+    cudaEventSynchronize(sp.b);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, sp.a, sp.b);
+    auto& t = c->prof.totals[sp.name];
+    t.first += ms;
+    t.second += 1;
+    cudaEventDestroy(sp.a);
+    cudaEventDestroy(sp.b);
+  }
+  c->prof.spans.clear();
+}
 
 int ensure_dlog(drx_ctx* c) {
   if (c->have_dlog) return 0;
@@ -257,6 +299,32 @@ int drx_synchronize(drx_ctx* c) {
 }
 uint64_t drx_launch_count(const drx_ctx* c) { return c ? c->launches : 0; }
 
+int drx_profile_enable(drx_ctx* c, int on) {
+  if (!c) return fail(-1, "null context");
+  Guard g(c);
+  prof_collect(c);
+  c->prof.totals.clear();
+  c->prof.on = on != 0;
+  return 0;
+}
+int drx_profile_get(drx_ctx* c, const char* kernel, double* total_ms, uint64_t* launches) {
+  if (!c || !kernel || !total_ms || !launches) return fail(-1, "null argument");
+  Guard g(c);
+  prof_collect(c);
+  auto it = c->prof.totals.find(kernel);
+  *total_ms = it == c->prof.totals.end() ? 0.0 : it->second.first;
+  *launches = it == c->prof.totals.end() ? 0 : it->second.second;
+  return 0;
+}
+
+int drx_reduce_rows_dev(drx_ctx* c, size_t ndp, size_t nrows, const int64_t* d_rows, int mode, int64_t* d_out) {
+  if (!c) return fail(-1, "null context");
+  if (mode < 0 || mode > 3) return fail(-1, "drx_reduce_rows_dev: mode %d", mode);
+  Guard g(c);
+  timed(c, "k_reduce_rows", [&] { return launch_reduce_rows(c->stream, ndp, nrows, d_rows, mode, d_out); });
+  return check_launch("reduce_rows");
+}
+
 int drx_set_pubkey(drx_ctx* c, const uint8_t P[64]) {
   if (!c || !P) return fail(-1, "drx_set_pubkey: null argument");
   Guard g(c);
@@ -282,7 +350,7 @@ int drx_encrypt_dev(drx_ctx* c, size_t n, const int64_t* d_m, const uint8_t* d_r
   if (!c) return fail(-1, "null context");
   Guard g(c);
   if (!c->have_pub) return fail(-1, "drx_encrypt: call drx_set_pubkey first");
-  c->launches += launch_encrypt(c->stream, n, d_m, d_r, c->tabB.p, c->tabP.p, d_ct);
+  timed(c, "k_encrypt", [&] { return launch_encrypt(c->stream, n, d_m, d_r, c->tabB.p, c->tabP.p, d_ct); });
   return check_launch("encrypt");
 }
 
@@ -298,7 +366,9 @@ int drx_encrypt(drx_ctx* c, size_t n, const int64_t* m, const uint8_t* r, uint8_
   RET(a.commit());
   CU(cudaMemcpyAsync(a.at<void>(om), m, n * 8, cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemcpyAsync(a.at<void>(orr), r, n * 32, cudaMemcpyHostToDevice, c->stream));
-  c->launches += launch_encrypt(c->stream, n, a.at<int64_t>(om), a.at<uint8_t>(orr), c->tabB.p, c->tabP.p, a.at<uint8_t>(oc));
+  timed(c, "k_encrypt", [&] {
+    return launch_encrypt(c->stream, n, a.at<int64_t>(om), a.at<uint8_t>(orr), c->tabB.p, c->tabP.p, a.at<uint8_t>(oc));
+  });
   RET(check_launch("encrypt"));
   CU(cudaMemcpyAsync(ct, a.at<void>(oc), n * 128, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -307,7 +377,8 @@ int drx_encrypt(drx_ctx* c, size_t n, const int64_t* m, const uint8_t* r, uint8_
 
 static int aggregate_on_device(drx_ctx* c, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
                                uint8_t* d_out) {
-  c->launches += launch_aggregate(c->stream, ndp, v, d_cts, d_scratch, slices, d_out, (int*)c->bad.p);
+  timed(c, "k_agg_partial", [&] { return launch_agg_partial(c->stream, ndp, v, d_cts, d_scratch, slices, (int*)c->bad.p); });
+  timed(c, "k_agg_final", [&] { return launch_agg_final(c->stream, v, slices, d_scratch, d_out); });
   return check_launch("aggregate");
 }
 
@@ -366,8 +437,10 @@ int drx_decrypt_dev(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* d
   RET(ensure_dlog(c));
   // the key travels through the tail of the 256-byte flag buffer
   CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
-  c->launches += launch_decrypt(c->stream, n, (uint8_t*)c->bad.p + 64, d_ct, c->dlog_keys.p, (uint32_t*)c->dlog_vals.p,
-                                d_out, (int*)c->bad.p);
+  timed(c, "k_decrypt", [&] {
+    return launch_decrypt(c->stream, n, (uint8_t*)c->bad.p + 64, d_ct, c->dlog_keys.p, (uint32_t*)c->dlog_vals.p, d_out,
+                          (int*)c->bad.p);
+  });
   return check_launch("decrypt");
 }
 
@@ -380,8 +453,10 @@ static int decrypt_raw(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t
   RET(reset_bad(c));
   CU(cudaMemcpyAsync(a.at<void>(oc), ct, n * 128, cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
-  c->launches += launch_decrypt(c->stream, n, (uint8_t*)c->bad.p + 64, a.at<uint8_t>(oc), c->dlog_keys.p,
-                                (uint32_t*)c->dlog_vals.p, a.at<int64_t>(oo), (int*)c->bad.p);
+  timed(c, "k_decrypt", [&] {
+    return launch_decrypt(c->stream, n, (uint8_t*)c->bad.p + 64, a.at<uint8_t>(oc), c->dlog_keys.p,
+                          (uint32_t*)c->dlog_vals.p, a.at<int64_t>(oo), (int*)c->bad.p);
+  });
   RET(check_launch("decrypt"));
   raw.resize(n);
   CU(cudaMemcpyAsync(raw.data(), a.at<void>(oo), n * 8, cudaMemcpyDeviceToHost, c->stream));

@@ -144,13 +144,70 @@ size_t aggregate_scratch_bytes(size_t ndp, size_t v, int* slices_out) {
   return want * v * sizeof(AggPartial);
 }
 
-int launch_aggregate(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
-                     uint8_t* d_out, int* d_bad) {
+int launch_agg_partial(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
+                       int* d_bad) {
   if (!v) return 0;
   k_agg_partial<<<grid_for(v * (size_t)slices, 128), 128, 0, st>>>(ndp, v, (const uint32_t*)d_cts, slices,
                                                                   (AggPartial*)d_scratch, d_bad);
+  return 1;
+}
+int launch_agg_final(cudaStream_t st, size_t v, int slices, const void* d_scratch, uint8_t* d_out) {
+  if (!v) return 0;
   k_agg_final<<<grid_for(v, 128), 128, 0, st>>>(v, slices, (const AggPartial*)d_scratch, (uint32_t*)d_out);
-  return 2;
+  return 1;
+}
+
+// ------------------------------------------------------------------ plaintext reduction (a-2)
+// lib/encoding/sum.go:19-23, mean.go:19-24, variance.go:19-27: per data provider sum, count and sum of squares
+// of its int64 rows. One block per provider; HBM-bound (8 bytes per row).
+__global__ void __launch_bounds__(256)
+k_reduce_rows(size_t nrows, const int64_t* __restrict__ rows, int mode, int64_t* __restrict__ out) {
+  const size_t d = blockIdx.x;
+  const int64_t* r = rows + d * nrows;
+  int64_t s = 0, q = 0;
+  for (size_t i = threadIdx.x; i < nrows; i += blockDim.x) {
+    const int64_t x = r[i];
+    s += x;
+    q += x * x;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_down_sync(0xffffffffu, s, o);
+    q += __shfl_down_sync(0xffffffffu, q, o);
+  }
+  __shared__ int64_t ss[8], qq[8];
+  if ((threadIdx.x & 31) == 0) {
+    ss[threadIdx.x >> 5] = s;
+    qq[threadIdx.x >> 5] = q;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; w++) {
+      s += ss[w];
+      q += qq[w];
+    }
+    const int64_t n = (int64_t)nrows;
+    if (mode == 0) {
+      out[d] = s;
+    } else if (mode == 1) {
+      out[2 * d] = s;
+      out[2 * d + 1] = n;
+    } else if (mode == 2) {
+      out[3 * d] = s;
+      out[3 * d + 1] = n;
+      out[3 * d + 2] = q;
+    } else {
+      out[5 * d] = s;
+      out[5 * d + 1] = n;
+      out[5 * d + 2] = s;
+      out[5 * d + 3] = n;
+      out[5 * d + 4] = q;
+    }
+  }
+}
+int launch_reduce_rows(cudaStream_t st, size_t ndp, size_t nrows, const int64_t* d_rows, int mode, int64_t* d_out) {
+  if (!ndp) return 0;
+  k_reduce_rows<<<(unsigned)ndp, 256, 0, st>>>(nrows, d_rows, mode, d_out);
+  return 1;
 }
 
 // ------------------------------------------------------------------ discrete-log table (a-5) and decryption (a-4)

@@ -339,24 +339,22 @@ k_rp_create_items(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* _
   sc_to_wire(out + pv.zv_off(i, j), sc_sub(tj, sc_mul(c, v)));
 }
 
-int launch_rp_create(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                     const uint8_t* d_r, const uint8_t* d_ct, const uint8_t* d_rnd, const size_t* d_rnd_off,
-                     const void* d_tabB, const void* d_tabP, const void* d_tabGtB, const uint8_t* d_baseB_wire,
-                     uint8_t* d_proofs) {
-  int launches = 0;
-  if (b.n) {
-    k_rp_create_hdr<<<grid_for(b.n, 128), 128, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_r, (const uint32_t*)d_ct,
-                                                       (const uint32_t*)d_rnd, d_rnd_off, (const G1Aff*)d_tabB,
-                                                       (const G1Aff*)d_tabP, (const uint32_t*)d_baseB_wire,
-                                                       (uint32_t*)d_proofs);
-    launches++;
-  }
-  if (b.items) {
-    k_rp_create_items<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_rnd, d_rnd_off,
-                                                           (const Fp12*)d_tabGtB, (uint32_t*)d_proofs);
-    launches++;
-  }
-  return launches;
+int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                         const uint8_t* d_r, const uint8_t* d_ct, const uint8_t* d_rnd, const size_t* d_rnd_off,
+                         const void* d_tabB, const void* d_tabP, const uint8_t* d_baseB_wire, uint8_t* d_proofs) {
+  if (!b.n) return 0;
+  k_rp_create_hdr<<<grid_for(b.n, 128), 128, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_r, (const uint32_t*)d_ct,
+                                                     (const uint32_t*)d_rnd, d_rnd_off, (const G1Aff*)d_tabB,
+                                                     (const G1Aff*)d_tabP, (const uint32_t*)d_baseB_wire,
+                                                     (uint32_t*)d_proofs);
+  return 1;
+}
+int launch_rp_create_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB, uint8_t* d_proofs) {
+  if (!b.items) return 0;
+  k_rp_create_items<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_rnd, d_rnd_off,
+                                                         (const Fp12*)d_tabGtB, (uint32_t*)d_proofs);
+  return 1;
 }
 
 // ------------------------------------------------------------------ verification (a-8)
@@ -434,22 +432,24 @@ __global__ void k_flags_to_bytes(size_t n, const uint32_t* __restrict__ flags, u
   if (p < n) ok[p] = flags[p] ? 1 : 0;
 }
 
-int launch_rp_verify(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB, const void* d_tabP,
-                     const void* d_tabGtB, const void* d_g2_aff, const uint8_t* d_proofs, uint32_t* d_flags,
-                     uint8_t* d_ok) {
-  (void)d_g2_aff;
-  int launches = 0;
+int launch_rp_verify_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                         const void* d_tabP, const uint8_t* d_proofs, uint32_t* d_flags) {
   if (!b.n) return 0;
   k_rp_verify_hdr<<<grid_for(b.n, 128), 128, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const G1Aff*)d_tabP,
                                                      (const uint32_t*)d_proofs, d_flags);
-  launches++;
-  if (b.items) {
-    k_rp_verify_items<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const Fp12*)d_tabGtB,
-                                                           (const uint32_t*)d_proofs, d_flags);
-    launches++;
-  }
-  k_flags_to_bytes<<<grid_for(b.n, 256), 256, 0, st>>>(b.n, d_flags, d_ok);
-  return launches + 1;
+  return 1;
+}
+int launch_rp_verify_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                           const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags) {
+  if (!b.items) return 0;
+  k_rp_verify_items<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const Fp12*)d_tabGtB,
+                                                         (const uint32_t*)d_proofs, d_flags);
+  return 1;
+}
+int launch_rp_flags(cudaStream_t st, size_t n, const uint32_t* d_flags, uint8_t* d_ok) {
+  if (!n) return 0;
+  k_flags_to_bytes<<<grid_for(n, 256), 256, 0, st>>>(n, d_flags, d_ok);
+  return 1;
 }
 
 }  // namespace drx

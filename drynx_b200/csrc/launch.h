@@ -23,8 +23,12 @@ int launch_encrypt(cudaStream_t st, size_t n, const int64_t* d_m, const uint8_t*
                    const void* d_tabP, uint8_t* d_ct);
 // scratch: slices * v * 2 Jacobian points
 size_t aggregate_scratch_bytes(size_t ndp, size_t v, int* slices_out);
-int launch_aggregate(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
-                     uint8_t* d_out, int* d_bad);
+int launch_agg_partial(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
+                       int* d_bad);
+int launch_agg_final(cudaStream_t st, size_t v, int slices, const void* d_scratch, uint8_t* d_out);
+// per-provider statistics of int64 rows [ndp][nrows] for the sum / mean / variance encoders:
+// mode 0: [sum]; 1: [sum, N]; 2: [sum, N, sum of squares]; 3: mean then variance = [sum, N, sum, N, sumsq]
+int launch_reduce_rows(cudaStream_t st, size_t ndp, size_t nrows, const int64_t* d_rows, int mode, int64_t* d_out);
 int launch_dlog_build(cudaStream_t st, const void* d_tabB, const void* d_baseB_aff, void* d_keys, uint32_t* d_vals);
 int launch_decrypt(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t* d_ct, const void* d_keys,
                    const uint32_t* d_vals, int64_t* d_out, int* d_bad);
@@ -66,12 +70,15 @@ struct RpBatch {          // one create/verify call
   size_t uni_size;        // uniform batch: bytes per proof
 };
 
-int launch_rp_create(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                     const uint8_t* d_r, const uint8_t* d_ct, const uint8_t* d_rnd, const size_t* d_rnd_off,
-                     const void* d_tabB, const void* d_tabP, const void* d_tabGtB, const uint8_t* d_baseB_wire,
-                     uint8_t* d_proofs);
-int launch_rp_verify(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB, const void* d_tabP,
-                     const void* d_tabGtB, const void* d_g2_aff, const uint8_t* d_proofs, uint32_t* d_flags,
-                     uint8_t* d_ok);
+int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                         const uint8_t* d_r, const uint8_t* d_ct, const uint8_t* d_rnd, const size_t* d_rnd_off,
+                         const void* d_tabB, const void* d_tabP, const uint8_t* d_baseB_wire, uint8_t* d_proofs);
+int launch_rp_create_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB, uint8_t* d_proofs);
+int launch_rp_verify_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                         const void* d_tabP, const uint8_t* d_proofs, uint32_t* d_flags);
+int launch_rp_verify_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                           const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags);
+int launch_rp_flags(cudaStream_t st, size_t n, const uint32_t* d_flags, uint8_t* d_ok);
 
 }  // namespace drx

@@ -49,6 +49,18 @@ int drx_synchronize(drx_ctx* ctx);
 /* Number of kernel launches issued by this context so far (for the benchmark's gpu_launches field). */
 uint64_t drx_launch_count(const drx_ctx* ctx);
 
+/* Per-kernel timing with CUDA events on the launching stream (bench.py's roofline leg): enable (which clears
+ * the totals), run, then read the summed duration and launch count of a kernel by name (k_encrypt,
+ * k_agg_partial, k_agg_final, k_decrypt, k_reduce_rows, k_rp_create_hdr, k_rp_create_items, k_rp_verify_hdr,
+ * k_rp_verify_items, k_rp_flags). No counterpart in the reference (it times with onet monitor.TimeMeasure). */
+int drx_profile_enable(drx_ctx* ctx, int on);
+int drx_profile_get(drx_ctx* ctx, const char* kernel, double* total_ms, uint64_t* launches);
+
+/* Per-provider plaintext reduction of int64 rows resident on the device, d_rows[ndp][nrows]
+ * (lib/encoding/sum.go:19-23, mean.go:19-24, variance.go:19-27). mode 0: [sum]; 1: [sum, N];
+ * 2: [sum, N, sum of squares]; 3: the mean vector followed by the variance vector (5 values). */
+int drx_reduce_rows_dev(drx_ctx* ctx, size_t ndp, size_t nrows, const int64_t* d_rows, int mode, int64_t* d_out);
+
 /* Collective public key P for EncryptInt* and range proofs (CreateProof.CaPub, lib/range/range_proof.go:67);
  * builds its fixed-base table. */
 int drx_set_pubkey(drx_ctx* ctx, const uint8_t P[64]);

@@ -13,6 +13,8 @@
 // MarshalBinary), so it doubles as the timed CPU baseline. It is pinned against oracle/bn256_ref.py (the
 // mathematical definition in Python integers) by tests/test_oracle.py. Only tests/, __graft_entry__.smoke()
 // and bench.py's cpu_baseline / --impl reference legs may load the library built from this file.
+#include <immintrin.h>
+
 #include <algorithm>
 #include <atomic>
 #include <cstdint>
@@ -50,33 +52,35 @@ static inline bool geq(const u64 a[4], const u64 b[4]) {
   return true;
 }
 static inline u64 sub4(u64 r[4], const u64 a[4], const u64 b[4]) {
-  u64 bw = 0;
-  for (int i = 0; i < 4; i++) {
-    u128 t = (u128)a[i] - b[i] - bw;
-    r[i] = (u64)t;
-    bw = (u64)(t >> 64) & 1;
-  }
+  unsigned long long t0, t1, t2, t3;
+  unsigned char bw = _subborrow_u64(0, a[0], b[0], &t0);
+  bw = _subborrow_u64(bw, a[1], b[1], &t1);
+  bw = _subborrow_u64(bw, a[2], b[2], &t2);
+  bw = _subborrow_u64(bw, a[3], b[3], &t3);
+  r[0] = t0; r[1] = t1; r[2] = t2; r[3] = t3;
   return bw;
 }
 static inline u64 add4(u64 r[4], const u64 a[4], const u64 b[4]) {
-  u64 c = 0;
-  for (int i = 0; i < 4; i++) {
-    u128 t = (u128)a[i] + b[i] + c;
-    r[i] = (u64)t;
-    c = (u64)(t >> 64);
-  }
+  unsigned long long t0, t1, t2, t3;
+  unsigned char c = _addcarry_u64(0, a[0], b[0], &t0);
+  c = _addcarry_u64(c, a[1], b[1], &t1);
+  c = _addcarry_u64(c, a[2], b[2], &t2);
+  c = _addcarry_u64(c, a[3], b[3], &t3);
+  r[0] = t0; r[1] = t1; r[2] = t2; r[3] = t3;
   return c;
 }
 static inline void mod_add(const Mod& M, u64 r[4], const u64 a[4], const u64 b[4]) {
   u64 t[4], d[4];
   u64 c = add4(t, a, b);
   u64 bw = sub4(d, t, M.m);
-  memcpy(r, (c || !bw) ? d : t, 32);
+  const u64 use_d = (u64)0 - (u64)(c | !bw);
+  for (int i = 0; i < 4; i++) r[i] = (d[i] & use_d) | (t[i] & ~use_d);
 }
 static inline void mod_sub(const Mod& M, u64 r[4], const u64 a[4], const u64 b[4]) {
-  u64 t[4];
-  if (sub4(t, a, b)) add4(t, t, M.m);
-  memcpy(r, t, 32);
+  u64 t[4], m[4];
+  const u64 mask = (u64)0 - sub4(t, a, b);
+  for (int i = 0; i < 4; i++) m[i] = M.m[i] & mask;
+  add4(r, t, m);
 }
 static inline void mont_mul(const Mod& M, u64 r[4], const u64 a[4], const u64 b[4]) {
   u64 t[6] = {0, 0, 0, 0, 0, 0};
@@ -104,7 +108,8 @@ static inline void mont_mul(const Mod& M, u64 r[4], const u64 a[4], const u64 b[
   }
   u64 d[4];
   u64 bw = sub4(d, t, M.m);
-  memcpy(r, (t[4] || !bw) ? d : t, 32);
+  const u64 use_d = (u64)0 - (u64)((t[4] != 0) | !bw);
+  for (int i = 0; i < 4; i++) r[i] = (d[i] & use_d) | (t[i] & ~use_d);
 }
 
 static inline void gfpAdd(gfP& c, const gfP& a, const gfP& b) { mod_add(MP, c.v, a.v, b.v); }
