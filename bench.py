@@ -181,7 +181,8 @@ def run_gpu(args):
     be = Backend(local)
     lib = be.lib
     stream = torch.cuda.current_stream()
-    be.set_stream(stream.cuda_stream)
+    # the legacy default stream's handle is 0, which drx_set_stream reads as "own stream": pass cudaStreamLegacy (1)
+    be.set_stream(stream.cuda_stream or 1)
 
     ndp, rows = args.ndp, args.rows
     n = ndp * NOUT
@@ -331,7 +332,7 @@ def run_gpu(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     e2e_val = world * n * args.steps / e2e_s
-    be.set_stream(stream.cuda_stream)
+    be.set_stream(stream.cuda_stream or 1)
 
     # ------------------------------------------------------------------ roofline of the dominant kernel
     mac_ms, mac_work = be.microbench(0, 20000)

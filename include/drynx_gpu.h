@@ -43,7 +43,7 @@ void drx_free(drx_ctx* ctx);
 /* Thread-local text of the last failure on this thread; never NULL. */
 const char* drx_last_error(void);
 /* Use an existing cudaStream_t (e.g. torch's current stream) for every later call; NULL restores the
- * context's own stream. */
+ * context's own non-blocking stream. To name the legacy default stream pass cudaStreamLegacy ((void*)1). */
 int drx_set_stream(drx_ctx* ctx, void* cuda_stream);
 int drx_synchronize(drx_ctx* ctx);
 /* Number of kernel launches issued by this context so far (for the benchmark's gpu_launches field). */
