@@ -30,6 +30,7 @@ SIGNATURES = {
     'drx_encrypt_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
     'drx_aggregate': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, VP]),
     'drx_aggregate_dev': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, VP]),
+    'drx_aggregate_noalloc_dev': (ctypes.c_int, [ctypes.c_size_t, ctypes.c_size_t, VP, VP, VP]),
     'drx_dlog_table': (ctypes.c_int, [VP, ctypes.c_int64]),
     'drx_decrypt': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, ctypes.c_int, VP, VP]),
     'drx_decrypt_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),

@@ -420,6 +420,19 @@ int drx_aggregate(drx_ctx* c, size_t ndp, size_t v, const uint8_t* const* cts, u
   return 0;
 }
 
+int drx_aggregate_noalloc_dev(size_t ndp, size_t v, const uint8_t* d_cts, uint8_t* d_out, void* cuda_stream) {
+  if (v == 0) return 0;
+  if (!d_out || (ndp && !d_cts)) return fail(-1, "drx_aggregate_noalloc_dev: null buffer");
+  int n_bad = 0, launches = 0;
+  const int rc = launch_aggregate_static((cudaStream_t)cuda_stream, ndp, v, d_cts, d_out, &n_bad, &launches);
+  if (rc == -5)
+    return fail(-5, "drx_aggregate_noalloc_dev: v = %zu exceeds the fixed scratch array (at most %zu columns per call)", v,
+                aggregate_static_max_columns());
+  if (rc == -2) return fail(-2, "drx_aggregate_noalloc_dev: %d malformed points", n_bad);
+  if (rc > 0) return fail(rc, "drx_aggregate_noalloc_dev: %s", cudaGetErrorString((cudaError_t)rc));
+  return rc;
+}
+
 int drx_dlog_table(drx_ctx* c, int64_t limit) {
   if (!c) return fail(-1, "null context");
   if (limit < 0) return fail(-1, "drx_dlog_table: negative limit");

@@ -3,6 +3,8 @@
 // decryptPoint, discreteLog, CreateDecryptionTable; not in /root/reference) at the call sites listed in
 // SURVEY.md §8 rows a-1, a-3, a-4, a-5. One thread per ciphertext; fixed-base multiplications walk 8-bit comb
 // tables that stay L2-resident (522 KB each); all kernels are integer-pipe bound.
+#include <mutex>
+
 #include "launch.h"
 #include "keccak.cuh"
 #include "wire.cuh"
@@ -155,6 +157,67 @@ int launch_agg_final(cudaStream_t st, size_t v, int slices, const void* d_scratc
   if (!v) return 0;
   k_agg_final<<<grid_for(v, 128), 128, 0, st>>>(v, slices, (const AggPartial*)d_scratch, (uint32_t*)d_out);
   return 1;
+}
+
+// ------------------------------------------------------------------ aggregation without any allocation
+// Same two kernels as above, but the partial sums live in a fixed array that is part of the loaded module, so a
+// caller that must not (or cannot) allocate device memory can still aggregate. The array is shared by every
+// call on a GPU: it holds whatever the previous call left, and two calls in flight at once would overwrite each
+// other's partial sums.
+#define DRX_NOALLOC_MAX_PARTIALS 16384  // (slice, column) pairs: 16384 x 192 B = 3 MiB per GPU
+static __device__ __align__(256) unsigned char g_noalloc_scratch[256 + DRX_NOALLOC_MAX_PARTIALS * sizeof(AggPartial)];
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not a device address; the address each GPU
+// gave the array is looked up once per device (with that device current) and remembered.
+static std::mutex g_noalloc_mu;
+static void* g_noalloc_addr[64];
+
+static cudaError_t noalloc_scratch(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    g_noalloc_addr[dev] = p;
+  }
+  *out = g_noalloc_addr[dev];
+  return cudaSuccess;
+}
+
+size_t aggregate_static_max_columns() { return DRX_NOALLOC_MAX_PARTIALS; }
+
+// Returns 0, -5 (v beyond the fixed array), -2 (malformed input points; *n_bad says how many) or a CUDA error code.
+int launch_aggregate_static(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, uint8_t* d_out, int* n_bad,
+                            int* launches) {
+  *n_bad = 0;
+  *launches = 0;
+  if (!v) return 0;
+  if (v > (size_t)DRX_NOALLOC_MAX_PARTIALS) return -5;
+  size_t slices = (size_t)DRX_NOALLOC_MAX_PARTIALS / v;
+  if (slices > (size_t)kAggMaxSlices) slices = kAggMaxSlices;
+  if (slices > ndp) slices = ndp;
+  if (slices < 1) slices = 1;
+  void* base = nullptr;
+  cudaError_t e = noalloc_scratch(&base);
+  if (e != cudaSuccess) return (int)e;
+  int* d_bad = (int*)base;                                   // first 256 bytes: the malformed-point counter
+  AggPartial* part = (AggPartial*)((unsigned char*)base + 256);
+  e = cudaMemsetAsync(d_bad, 0, 256, st);                    // the counter must start at zero; the partials are
+  if (e != cudaSuccess) return (int)e;                       // all rewritten by stage 1 before stage 2 reads them
+  k_agg_partial<<<grid_for(v * slices, 128), 128, 0, st>>>(ndp, v, (const uint32_t*)d_cts, (int)slices, part, d_bad);
+  k_agg_final<<<grid_for(v, 128), 128, 0, st>>>(v, (int)slices, part, (uint32_t*)d_out);
+  *launches = 2;
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return (int)e;
+  e = cudaMemcpyAsync(n_bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, st);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return (int)e;
+  return *n_bad ? -2 : 0;
 }
 
 // ------------------------------------------------------------------ plaintext reduction (a-2)

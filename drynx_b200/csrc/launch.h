@@ -26,6 +26,10 @@ size_t aggregate_scratch_bytes(size_t ndp, size_t v, int* slices_out);
 int launch_agg_partial(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
                        int* d_bad);
 int launch_agg_final(cudaStream_t st, size_t v, int slices, const void* d_scratch, uint8_t* d_out);
+// allocation-free aggregation over a fixed module-resident scratch array (kernels_g1.cu)
+size_t aggregate_static_max_columns();
+int launch_aggregate_static(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, uint8_t* d_out, int* n_bad,
+                            int* launches);
 // per-provider statistics of int64 rows [ndp][nrows] for the sum / mean / variance encoders:
 // mode 0: [sum]; 1: [sum, N]; 2: [sum, N, sum of squares]; 3: mean then variance = [sum, N, sum, N, sumsq]
 int launch_reduce_rows(cudaStream_t st, size_t ndp, size_t nrows, const int64_t* d_rows, int mode, int64_t* d_out);

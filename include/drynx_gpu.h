@@ -78,6 +78,25 @@ int drx_aggregate(drx_ctx* ctx, size_t ndp, size_t v, const uint8_t* const* cts,
 /* Same with the ndp vectors contiguous in device memory (d_cts[d*v*128 ...]). */
 int drx_aggregate_dev(drx_ctx* ctx, size_t ndp, size_t v, const uint8_t* d_cts, uint8_t* d_out);
 
+/* Aggregation for callers that must not allocate GPU memory. It has no counterpart in the reference; it computes
+ * exactly what drx_aggregate_dev computes (d_cts = ndp vectors of v ciphertexts back to back in device memory,
+ * d_out = v ciphertexts), but needs no context and calls no cudaMalloc/cudaFree or any other allocating routine:
+ * the partial sums go into a fixed 3 MiB array that every GPU holds from the moment it loads this library until
+ * the process exits. Meant for hosts that give the whole GPU to one memory pool at start-up and have nothing left
+ * to allocate from later, for services whose policy is "no allocation after initialisation" because a failed
+ * cudaMalloc in the middle of a survey cannot be handled, and for latency-sensitive loops where the device-wide
+ * synchronisation hidden in cudaMalloc/cudaFree would stall the other streams.
+ *   - runs on the CURRENT device, on `cuda_stream` (NULL = the default stream), and returns after the result is
+ *     complete (it synchronises that stream to read the malformed-point count);
+ *   - limit: v <= 16384 columns per call; larger v returns -5 with a message, split the vector instead;
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress); make that first
+ *     call before starting any stream capture on that device;
+ *   - all calls on one GPU share the array, which still holds the previous call's partial sums: calls must not
+ *     overlap on the GPU (from different streams or threads) or they corrupt each other's results. The one word
+ *     that has to start at zero, the malformed-point counter, is cleared by every call.
+ * Returns 0, -1 (null buffer), -2 (malformed points), -5 (v too large) or a CUDA error code. */
+int drx_aggregate_noalloc_dev(size_t ndp, size_t v, const uint8_t* d_cts, uint8_t* d_out, void* cuda_stream);
+
 /* libunlynx.CreateDecryptionTable (services/api.go:50): makes i*B, 0 <= i <= limit, available to drx_decrypt
  * with negatives. The device table always spans the reference's MaxHomomorphicInt (100000); `limit` only
  * feeds the host-side model of which entries the reference's lazily grown map would hold. */
