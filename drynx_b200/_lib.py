@@ -4,7 +4,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libdrynx_gpu.so')
+LIB_PATH = os.environ.get('DRYNX_LIB', os.path.join(_HERE, 'libdrynx_gpu.so'))  # DRYNX_LIB: experiment builds only
 
 c_u8p = ctypes.POINTER(ctypes.c_uint8)
 c_i64p = ctypes.POINTER(ctypes.c_int64)

@@ -13,13 +13,14 @@ from concurrent.futures import ThreadPoolExecutor
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, 'drynx_b200', 'csrc')
-GPU_SO = os.path.join(ROOT, 'drynx_b200', 'libdrynx_gpu.so')
+GPU_SO = os.environ.get('DRYNX_LIB', os.path.join(ROOT, 'drynx_b200', 'libdrynx_gpu.so'))
 ORACLE_SO = os.path.join(ROOT, 'oracle', '_build', 'liboracle.so')
 HOSTEMU_SO = os.path.join(ROOT, 'tests', 'hostemu', 'libhostemu.so')
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC',
-              '-Xptxas', '-v'] + (['-DDRX_DEBUG_RP'] if os.environ.get('DRX_DEBUG_RP') else [])
-GPU_SOURCES = ['kernels_g1.cu', 'kernels_rp.cu', 'capi.cu']
+              '-Xptxas', '-v'] + (['-DDRX_DEBUG_RP'] if os.environ.get('DRX_DEBUG_RP') else []) + \
+    [f for f in os.environ.get('DRX_NVCC_EXTRA', '').split() if f]
+GPU_SOURCES = ['kernels_g1.cu', 'kernels_rp.cu', 'kernels_rp_coop.cu', 'capi.cu']
 
 
 def _newer(target, sources):
@@ -45,7 +46,7 @@ def _run(cmd, log=None):
 
 
 def build_gpu(force=False):
-    objdir = os.path.join(ROOT, 'build')
+    objdir = os.environ.get('DRX_OBJDIR', os.path.join(ROOT, 'build'))
     os.makedirs(objdir, exist_ok=True)
     hdrs = _headers()
     jobs = []
@@ -78,9 +79,24 @@ def build_hostemu(force=False):
     return HOSTEMU_SO
 
 
+HOST_TEST = os.path.join(ROOT, 'host', 'test_host')
+
+
+def build_host_test(force=False):
+    """host/test_host: the C++ host mirror's reference-style tests, linked against libdrynx_gpu.so."""
+    src = os.path.join(ROOT, 'host', 'test_host.cpp')
+    deps = [src, os.path.join(ROOT, 'host', 'drynx_host.hpp'), os.path.join(ROOT, 'include', 'drynx_gpu.h')]
+    build_gpu()
+    if force or _newer(HOST_TEST, deps + [GPU_SO]):
+        libdir = os.path.dirname(GPU_SO)
+        _run(['g++', '-O2', '-std=c++17', src, '-o', HOST_TEST, '-L', libdir, '-ldrynx_gpu', '-Wl,-rpath,' + libdir,
+              '-Wl,-rpath,$ORIGIN/../drynx_b200', '-L/usr/local/cuda/lib64', '-lcudart', '-Wl,-rpath,/usr/local/cuda/lib64'])
+    return HOST_TEST
+
+
 def build_all(force=False):
     with ThreadPoolExecutor(max_workers=3) as ex:
-        futs = [ex.submit(build_gpu, force), ex.submit(build_hostemu, force)]
+        futs = [ex.submit(build_host_test, force), ex.submit(build_hostemu, force)]
         if os.path.exists(os.path.join(ROOT, 'oracle', 'oracle.cpp')):
             futs.append(ex.submit(build_oracle, force))
         return [f.result() for f in futs]
@@ -89,4 +105,4 @@ def build_all(force=False):
 if __name__ == '__main__':
     what = sys.argv[1] if len(sys.argv) > 1 else 'all'
     force = '--force' in sys.argv
-    print({'gpu': build_gpu, 'oracle': build_oracle, 'hostemu': build_hostemu, 'all': build_all}[what](force))
+    print({'gpu': build_gpu, 'oracle': build_oracle, 'hostemu': build_hostemu, 'host': build_host_test, 'all': build_all}[what](force))

@@ -25,6 +25,29 @@
 #define DRX_D inline __attribute__((always_inline))
 #endif
 
+#if defined(__CUDACC__)
+#define DRX_NI static __device__ __noinline__
+#else
+#define DRX_NI inline
+#endif
+
+// Code-size knobs (the pairing kernels are instruction-fetch bound when everything is inlined):
+//   DRX_FP_OUTLINE >= 1: fp_mul / fp_sqr are out-of-line functions taking their operands by value (registers)
+//   DRX_FP_OUTLINE >= 2: fp_add / fp_sub / fp_neg too
+#ifndef DRX_FP_OUTLINE
+#define DRX_FP_OUTLINE 1
+#endif
+#if DRX_FP_OUTLINE >= 1
+#define DRX_FPMUL_ATTR DRX_NI
+#else
+#define DRX_FPMUL_ATTR DRX_HD
+#endif
+#if DRX_FP_OUTLINE >= 2
+#define DRX_FPADD_ATTR DRX_NI
+#else
+#define DRX_FPADD_ATTR DRX_HD
+#endif
+
 #if defined(__CUDA_ARCH__)
 #define DRX_UNROLL _Pragma("unroll")
 #else
@@ -251,11 +274,20 @@ DRX_HD Fp fp_one() {
   for (int k = 0; k < 8; k++) r.v[k] = ModP::r1(k);
   return r;
 }
-DRX_HD Fp fp_mul(const Fp& a, const Fp& b) { Fp r; mont_mul<ModP>(r.v, a.v, b.v); return r; }
-DRX_HD Fp fp_sqr(const Fp& a) { Fp r; mont_mul<ModP>(r.v, a.v, a.v); return r; }
-DRX_HD Fp fp_add(const Fp& a, const Fp& b) { Fp r; mod_add<ModP>(r.v, a.v, b.v); return r; }
-DRX_HD Fp fp_sub(const Fp& a, const Fp& b) { Fp r; mod_sub<ModP>(r.v, a.v, b.v); return r; }
-DRX_HD Fp fp_neg(const Fp& a) { Fp r; mod_neg<ModP>(r.v, a.v); return r; }
+DRX_FPMUL_ATTR Fp fp_mul(Fp a, Fp b) { Fp r; mont_mul<ModP>(r.v, a.v, b.v); return r; }
+// always-inlined product for the three hot Fp2 leaves, where interleaving independent products pays
+#ifndef DRX_FP2_INLINE_MUL
+#define DRX_FP2_INLINE_MUL 0
+#endif
+#if DRX_FP2_INLINE_MUL
+DRX_HD Fp fp_mul_inl(const Fp& a, const Fp& b) { Fp r; mont_mul<ModP>(r.v, a.v, b.v); return r; }
+#else
+DRX_HD Fp fp_mul_inl(const Fp& a, const Fp& b) { return fp_mul(a, b); }
+#endif
+DRX_HD Fp fp_sqr(const Fp& a) { return fp_mul(a, a); }
+DRX_FPADD_ATTR Fp fp_add(Fp a, Fp b) { Fp r; mod_add<ModP>(r.v, a.v, b.v); return r; }
+DRX_FPADD_ATTR Fp fp_sub(Fp a, Fp b) { Fp r; mod_sub<ModP>(r.v, a.v, b.v); return r; }
+DRX_FPADD_ATTR Fp fp_neg(Fp a) { Fp r; mod_neg<ModP>(r.v, a.v); return r; }
 DRX_HD Fp fp_dbl(const Fp& a) { return fp_add(a, a); }
 DRX_HD bool fp_is_zero(const Fp& a) { return mod_is_zero<ModP>(a.v); }
 DRX_HD bool fp_eq(const Fp& a, const Fp& b) {

@@ -117,50 +117,48 @@ DRX_NI void fp12_pow_u(Fp12& r, const Fp12& a) {
   r = acc;
 }
 
-// f^((p^12-1)/n): easy part (p^6-1)(p^2+1), then the Scott et al. addition chain for (p^4-p^2+1)/n.
+// f^((p^12-1)/n): easy part (p^6-1)(p^2+1), then the Scott et al. addition chain for (p^4-p^2+1)/n
+//   result = y0 * y1^2 * y2^6 * y3^12 * y4^18 * y5^30 * y6^36 with
+//   y0 = a^p a^(p^2) a^(p^3), y1 = 1/a, y2 = (a^(u^2))^(p^2), y3 = 1/(a^u)^p, y4 = 1/(a^u (a^(u^2))^p),
+//   y5 = 1/a^(u^2), y6 = 1/(a^(u^3) (a^(u^3))^p).  Ordered so that at most eight Fp12 values are live (the
+//   stack of this function is the largest contributor to the kernels' thread-local footprint).
 DRX_NI void final_exp(Fp12& out, const Fp12& in) {
-  Fp12 t1, t2, inv;
-  fp12_conj(t1, in);
-  fp12_inv(inv, in);
-  fp12_mul(t1, t1, inv);  // in^(p^6-1)
-  fp12_frob2(t2, t1);
-  fp12_mul(t1, t1, t2);   // ^(p^2+1): now in the cyclotomic subgroup
-
-  Fp12 fp1, fp2, fp3, fu, fu2, fu3;
-  fp12_frob1(fp1, t1);
-  fp12_frob2(fp2, t1);
-  fp12_frob1(fp3, fp2);
-  fp12_pow_u(fu, t1);
+  Fp12 a, fu, fu2, t0, t1, x;
+  fp12_conj(a, in);
+  fp12_inv(x, in);
+  fp12_mul(a, a, x);      // in^(p^6-1)
+  fp12_frob2(x, a);
+  fp12_mul(a, a, x);      // ^(p^2+1): cyclotomic from here on
+  fp12_pow_u(fu, a);
   fp12_pow_u(fu2, fu);
-  fp12_pow_u(fu3, fu2);
-
-  Fp12 y0, y1, y2, y3, y4, y5, y6, tmp;
-  fp12_mul(y0, fp1, fp2);
-  fp12_mul(y0, y0, fp3);
-  fp12_conj(y1, t1);
-  fp12_frob2(y2, fu2);
-  fp12_frob1(y3, fu);
-  fp12_conj(y3, y3);
-  fp12_frob1(tmp, fu2);
-  fp12_mul(y4, fu, tmp);
-  fp12_conj(y4, y4);
-  fp12_conj(y5, fu2);
-  fp12_frob1(tmp, fu3);
-  fp12_mul(y6, fu3, tmp);
-  fp12_conj(y6, y6);
-
-  Fp12 t0;
-  fp12_cyclo_sqr(t0, y6);
-  fp12_mul(t0, t0, y4);
-  fp12_mul(t0, t0, y5);
-  fp12_mul(t1, y3, y5);
-  fp12_mul(t1, t1, t0);
-  fp12_mul(t0, t0, y2);
+  fp12_pow_u(x, fu2);     // fu3
+  fp12_frob1(t0, x);
+  fp12_mul(t0, t0, x);
+  fp12_conj(t0, t0);      // y6
+  fp12_cyclo_sqr(t0, t0);
+  fp12_frob1(x, fu2);
+  fp12_mul(x, x, fu);
+  fp12_conj(x, x);        // y4
+  fp12_mul(t0, t0, x);
+  fp12_conj(x, fu2);      // y5
+  fp12_mul(t0, t0, x);    // t0 = y6^2 y4 y5
+  fp12_frob1(t1, fu);
+  fp12_conj(t1, t1);      // y3
+  fp12_mul(t1, t1, x);
+  fp12_mul(t1, t1, t0);   // t1 = y3 y5 t0
+  fp12_frob2(x, fu2);     // y2
+  fp12_mul(t0, t0, x);
   fp12_cyclo_sqr(t1, t1);
   fp12_mul(t1, t1, t0);
   fp12_cyclo_sqr(t1, t1);
-  fp12_mul(t0, t1, y1);
-  fp12_mul(t1, t1, y0);
+  fp12_conj(x, a);        // y1
+  fp12_mul(t0, t1, x);
+  fp12_frob1(x, a);       // y0 = a^p a^(p^2) a^(p^3)
+  fp12_frob2(fu, a);
+  fp12_mul(x, x, fu);
+  fp12_frob1(fu, fu);
+  fp12_mul(x, x, fu);
+  fp12_mul(t1, t1, x);
   fp12_cyclo_sqr(t0, t0);
   fp12_mul(out, t0, t1);
 }

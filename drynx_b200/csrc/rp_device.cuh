@@ -1,0 +1,171 @@
+// Device-side range-proof logic shared by the one-thread-per-item kernels (kernels_rp.cu) and the four-lane
+// cooperative kernels for small batches (kernels_rp_coop.cu): proof layout, item location, and the bodies of the
+// creation and verification items. lib/range/range_proof.go:320-407 and :504-565.
+#pragma once
+#include "launch.h"
+#include "keccak.cuh"
+#include "wire.cuh"
+
+namespace drx {
+
+// ------------------------------------------------------------------ scalar helpers (mod n)
+__device__ __noinline__ static Scalar sc_inv(const Scalar& a) {  // a^(n-2); 0 -> 0
+  Scalar r2, am, acc;
+  for (int k = 0; k < 8; k++) r2.v[k] = ModN::r2(k);
+  mont_mul<ModN>(am.v, a.v, r2.v);  // Montgomery form
+  for (int k = 0; k < 8; k++) acc.v[k] = ModN::r1(k);
+  for (int bit = 255; bit >= 0; bit--) {
+    mont_mul<ModN>(acc.v, acc.v, acc.v);
+    if ((ModN::pm2(bit >> 5) >> (bit & 31)) & 1u) mont_mul<ModN>(acc.v, acc.v, am.v);
+  }
+  Scalar one = sc_zero();
+  one.v[0] = 1;
+  Scalar out;
+  mont_mul<ModN>(out.v, acc.v, one.v);
+  return out;
+}
+
+// 64-byte SHA3-512 digest (as 16 words in memory order) read as a big-endian integer, reduced mod n
+// (kyber Scalar.SetBytes on hash.Sum, lib/range/range_proof.go:374)
+__device__ __forceinline__ Scalar sc_from_digest(const uint32_t d[16]) {
+  const Scalar hi = sc_from_wire(d);
+  const Scalar lo = sc_from_wire(d + 8);
+  Scalar r2, t;
+  for (int k = 0; k < 8; k++) r2.v[k] = ModN::r2(k);
+  mont_mul<ModN>(t.v, hi.v, r2.v);  // hi * 2^256 mod n
+  return sc_add(t, lo);
+}
+
+// ------------------------------------------------------------------ proof layout (lib/range/range_proof.go:72-155)
+struct ProofView {
+  int ns, nd;
+  __device__ __forceinline__ static int c_off() { return 32; }
+  __device__ __forceinline__ static int zr_off() { return 40; }
+  __device__ __forceinline__ static int d_off() { return 48; }
+  __device__ __forceinline__ int zphi_off(int j) const { return 64 + 8 * j; }
+  __device__ __forceinline__ int blk(int i) const { return 64 + 8 * nd + i * 136 * nd; }
+  __device__ __forceinline__ int v_off(int i, int j) const { return blk(i) + 32 * j; }
+  __device__ __forceinline__ int a_off(int i, int j) const { return blk(i) + 32 * nd + 96 * j; }
+  __device__ __forceinline__ int zv_off(int i, int j) const { return blk(i) + 128 * nd + 8 * j; }
+};
+
+__device__ __forceinline__ int64_t rp_ndigits_dev(int64_t secret, int64_t u, int64_t l) {
+  int64_t d = 0;
+  while (secret > 0 && u > 1) {
+    d++;
+    secret /= u;
+  }
+  return d > l ? d : l;
+}
+__device__ __forceinline__ uint32_t rp_digit(int64_t secret, int64_t u, int j) {
+  if (secret <= 0) return 0;
+  for (int k = 0; k < j; k++) secret /= u;
+  return (uint32_t)(secret % u);
+}
+
+struct ItemRef {
+  size_t p;
+  int i, j, ns, nd;
+  const uint32_t* proof;
+};
+__device__ __forceinline__ bool locate_proof(const RpBatch& b, const RpSetDev* sets, size_t p, int& ns, int& nd,
+                                             size_t& byte_off) {
+  const int sid = b.d_set_id[p];
+  if (b.d_proof_off) {
+    byte_off = b.d_proof_off[p];
+    if (sid < 0) { ns = 0; nd = 0; return false; }
+    ns = sets[sid].ns;
+    nd = (int)((b.d_proof_off[p + 1] - byte_off - 256) / (size_t)(32 + 544 * ns));
+  } else {
+    byte_off = p * b.uni_size;
+    if (sid < 0) { ns = 0; nd = 0; return false; }
+    ns = b.uni_ns;
+    nd = b.uni_nd;
+  }
+  return true;
+}
+__device__ __forceinline__ bool locate_item(const RpBatch& b, const RpSetDev* sets, size_t t, size_t& p, int& i, int& j,
+                                            int& ns, int& nd, size_t& byte_off) {
+  size_t local;
+  if (b.d_item_proof) {
+    p = b.d_item_proof[t];
+    local = t - b.d_item_start[p];
+  } else {
+    const size_t per = (size_t)b.uni_ns * b.uni_nd;
+    p = t / per;
+    local = t - p * per;
+  }
+  if (!locate_proof(b, sets, p, ns, nd, byte_off)) return false;
+  i = (int)(local / nd);
+  j = (int)(local - (size_t)i * nd);
+  return true;
+}
+
+
+// Item thread per (proof, server i, digit j): V_ij, a_ij, Zv_ij.
+__device__ __forceinline__ void rp_create_item(const RpBatch& b, const RpSetDev* __restrict__ sets,
+                                               const int64_t* __restrict__ secret, const uint32_t* __restrict__ rnd,
+                                               const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB,
+                                               uint32_t* __restrict__ proofs, size_t t) {
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  uint32_t* out = proofs + off / 4;
+  const RpSetDev set = sets[b.d_set_id[p]];
+  const int u = set.u;
+  ProofView pv{ns, nd};
+  const uint32_t* rp = rnd + (b.d_proof_off ? rnd_off[p] / 4 : p * (size_t)nd * (3 + ns) * 8);
+  const uint32_t* row = rp + (size_t)j * (3 + ns) * 8;
+  const Scalar sj = sc_from_wire(row);
+  const Scalar tj = sc_from_wire(row + 8);
+  const Scalar v = sc_from_wire(row + 8 * (3 + i));
+  const Scalar c = sc_from_wire(out + ProofView::c_off());
+  const uint32_t phi = rp_digit(secret[p], u, j);
+  const size_t tab = ((size_t)i * u + phi) * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES);
+  // V_ij = v * A_{i,phi}
+  const G2Jac V = comb_mul((const G2Aff*)set.tabA + tab, v);
+  g2_to_wire(out + pv.v_off(i, j), jac_to_aff(V));
+  // a_ij = e(B, A_{i,phi})^(-s_j v) * e(B, g2)^(t_j)
+  Fp12 a, g;
+  gt_comb_pow(a, (const Fp12*)set.tabGtA + tab, sc_neg(sc_mul(sj, v)));
+  gt_comb_pow(g, tabGtB, tj);
+  fp12_mul(a, a, g);
+  gt_to_wire(out + pv.a_off(i, j), a);
+  sc_to_wire(out + pv.zv_off(i, j), sc_sub(tj, sc_mul(c, v)));
+}
+
+
+// Item thread per (proof, i, j): e(c*Y_i - Zphi_j*B, V_ij) * e(B, g2)^Zv_ij == A_ij  (:540-549; the three
+// pairings of the reference collapse by bilinearity, the value compared is the same canonical GT element).
+__device__ __forceinline__ void rp_verify_item(const RpBatch& b, const RpSetDev* __restrict__ sets,
+                                               const G1Aff* __restrict__ tabB, const Fp12* __restrict__ tabGtB,
+                                               const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags,
+                                               size_t t) {
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  const uint32_t* in = proofs + off / 4;
+  const RpSetDev set = sets[b.d_set_id[p]];
+  ProofView pv{ns, nd};
+  G2Aff V;
+  Fp12 A;
+  bool ok = g2_from_wire(V, in + pv.v_off(i, j));
+  ok &= gt_from_wire(A, in + pv.a_off(i, j));
+  if (!ok) {
+    atomicAnd(&flags[p], 0u);
+    return;
+  }
+  const Scalar c = sc_from_wire(in + ProofView::c_off());
+  const Scalar zphi = sc_from_wire(in + pv.zphi_off(j));
+  const Scalar zv = sc_from_wire(in + pv.zv_off(i, j));
+  G1Jac P1 = comb_mul((const G1Aff*)set.tabY + (size_t)i * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES), c);
+  P1 = jac_add(P1, comb_mul(tabB, sc_neg(zphi)));
+  Fp12 e, g;
+  pairing(e, jac_to_aff(P1), V);
+  gt_comb_pow(g, tabGtB, zv);
+  fp12_mul(e, e, g);
+  if (!fp12_eq(e, A)) atomicAnd(&flags[p], 0u);
+}
+
+
+}  // namespace drx

@@ -1,0 +1,641 @@
+// drynx_host.hpp -- C++ host mirror of the reference's call surface over the C ABI (include/drynx_gpu.h).
+//
+// The reference is Go; Go is not installed here, so the host side above the ABI is C++ (header-only). Names,
+// argument meaning and results follow the Go functions so that host/test_host.cpp reads like the reference's own
+// tests:
+//   libunlynx        (unlynx v1.4.0 lib/crypto.go)  CipherText, CipherVector, EncryptInt(GetR), EncryptIntVectorGetRs,
+//                                                   CipherVector Add, DecryptInt(WithNeg), DecryptIntVectorWithNeg,
+//                                                   DecryptCheckZero, CreateDecryptionTable
+//   libdrynxrange    (lib/range/range_proof.go)     ToBase :584, InitRangeProofSignature :270, CreateProof :61,
+//                                                   CreatePredicateRangeProofListForAllServers :305,
+//                                                   RangeProofListVerification :484
+//   libdrynxencoding (lib/encoding/*.go)            Encode*/Decode* for sum, mean, variance, frequency count,
+//                                                   linear regression (dims) and logistic regression
+// No arithmetic on group elements happens here: every such operation is one batched call into libdrynx_gpu.so.
+// The randomness a Go node would draw from crypto/rand comes from a caller-supplied RandomStream.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <functional>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../include/drynx_gpu.h"
+
+namespace drynx {
+
+using Bytes = std::vector<uint8_t>;
+struct Scalar {
+  uint8_t b[32];
+};
+struct Point {
+  uint8_t b[64];
+};
+// Fills 32 bytes with a uniformly random scalar < n, big-endian (kyber Scalar.Pick).
+using RandomStream = std::function<void(uint8_t out[32])>;
+
+struct Error : std::runtime_error {
+  int code;
+  Error(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+inline void check(int rc) {
+  if (rc != 0) throw Error(rc, drx_last_error());
+}
+
+// One context per process, like the package-level suite of lib/suite.go.
+class Gpu {
+ public:
+  static Gpu& get(int device = 0) {
+    static Gpu g(device);
+    return g;
+  }
+  drx_ctx* ctx() const { return c_; }
+  RandomStream random;  // set by the application; used wherever the reference calls RandomStream()
+
+ private:
+  explicit Gpu(int device) { check(drx_init(&c_, device, nullptr, nullptr)); }
+  ~Gpu() { drx_free(c_); }
+  drx_ctx* c_ = nullptr;
+};
+inline Scalar pick() {
+  Scalar s;
+  if (!Gpu::get().random) throw Error(-1, "drynx::Gpu::random is not set");
+  Gpu::get().random(s.b);
+  return s;
+}
+inline Scalar scalar_from_u64(uint64_t v) {
+  Scalar s{};
+  for (int i = 0; i < 8; i++) s.b[31 - i] = (uint8_t)(v >> (8 * i));
+  return s;
+}
+inline Point base_point() {  // SuiTe.Point().Base() = (1, -2)
+  static const uint8_t y[32] = {0x8f, 0xb5, 0x01, 0xe3, 0x4a, 0xa3, 0x87, 0xf9, 0xaa, 0x6f, 0xec, 0xb8, 0x61, 0x84, 0xdc, 0x21,
+                                0xee, 0x5b, 0x88, 0xd1, 0x20, 0xb5, 0xb5, 0x9e, 0x18, 0x5c, 0xac, 0x6c, 0x5e, 0x08, 0x96, 0x65};
+  Point p{};
+  p.b[31] = 1;
+  memcpy(p.b + 32, y, 32);
+  return p;
+}
+inline Point point_mul(const Scalar& k, const Point& p) {
+  Point r;
+  check(drx_g1_mul(Gpu::get().ctx(), 1, k.b, p.b, r.b));
+  return r;
+}
+struct KeyPair {  // key.NewKeyPair(libunlynx.SuiTe)
+  Scalar Private;
+  Point Public;
+};
+inline KeyPair NewKeyPair() {
+  KeyPair k;
+  k.Private = pick();
+  k.Public = point_mul(k.Private, base_point());
+  return k;
+}
+
+}  // namespace drynx
+
+// =====================================================================================================================
+namespace libunlynx {
+using drynx::Gpu;
+using drynx::Point;
+using drynx::Scalar;
+
+constexpr int64_t MaxHomomorphicInt = 100000;
+
+struct CipherText {
+  uint8_t b[128];  // K || C, the ToBytes form
+};
+using CipherVector = std::vector<CipherText>;
+
+// The collective key the following calls encrypt under (the `pubkey` argument of the Go functions; the device
+// keeps one fixed-base table, so switching keys costs a table build).
+inline void use_pubkey(const Point& pub) {
+  static Point cur{};
+  static bool have = false;
+  if (!have || memcmp(cur.b, pub.b, 64)) {
+    drynx::check(drx_set_pubkey(Gpu::get().ctx(), pub.b));
+    cur = pub;
+    have = true;
+  }
+}
+
+// EncryptIntVectorGetRs: one scalar per value drawn from the random stream, one batched encryption.
+inline std::pair<CipherVector, std::vector<Scalar>> EncryptIntVectorGetRs(const Point& pubkey, const std::vector<int64_t>& ints) {
+  use_pubkey(pubkey);
+  std::vector<Scalar> rs(ints.size());
+  for (auto& r : rs) r = drynx::pick();
+  CipherVector cv(ints.size());
+  if (!ints.empty())
+    drynx::check(drx_encrypt(Gpu::get().ctx(), ints.size(), ints.data(), rs[0].b, cv[0].b));
+  return {cv, rs};
+}
+inline CipherVector EncryptIntVector(const Point& pubkey, const std::vector<int64_t>& ints) {
+  return EncryptIntVectorGetRs(pubkey, ints).first;
+}
+inline std::pair<CipherText, Scalar> EncryptIntGetR(const Point& pubkey, int64_t v) {
+  auto r = EncryptIntVectorGetRs(pubkey, {v});
+  return {r.first[0], r.second[0]};
+}
+inline CipherText EncryptInt(const Point& pubkey, int64_t v) { return EncryptIntGetR(pubkey, v).first; }
+
+// CipherVector.Add over any number of vectors (the root node's fold, protocols/data_collection_protocol.go:145-166).
+inline CipherVector AddAll(const std::vector<CipherVector>& vs) {
+  if (vs.empty()) return {};
+  const size_t v = vs[0].size();
+  std::vector<const uint8_t*> ptrs;
+  for (auto& x : vs) {
+    if (x.size() != v) throw drynx::Error(-1, "CipherVector.Add: length mismatch");
+    ptrs.push_back(v ? x[0].b : nullptr);
+  }
+  CipherVector out(v);
+  if (v) drynx::check(drx_aggregate(Gpu::get().ctx(), vs.size(), v, ptrs.data(), out[0].b));
+  return out;
+}
+inline CipherVector Add(const CipherVector& a, const CipherVector& b) { return AddAll({a, b}); }
+
+inline std::vector<int64_t> DecryptIntVectorImpl(const Scalar& sk, const CipherVector& cv, bool neg) {
+  std::vector<int64_t> out(cv.size());
+  if (!cv.empty()) drynx::check(drx_decrypt(Gpu::get().ctx(), cv.size(), sk.b, cv[0].b, neg ? 1 : 0, out.data(), nullptr));
+  return out;
+}
+inline std::vector<int64_t> DecryptIntVector(const Scalar& sk, const CipherVector& cv) { return DecryptIntVectorImpl(sk, cv, false); }
+inline std::vector<int64_t> DecryptIntVectorWithNeg(const Scalar& sk, const CipherVector& cv) { return DecryptIntVectorImpl(sk, cv, true); }
+inline int64_t DecryptInt(const Scalar& sk, const CipherText& c) { return DecryptIntVector(sk, {c})[0]; }
+inline int64_t DecryptIntWithNeg(const Scalar& sk, const CipherText& c) { return DecryptIntVectorWithNeg(sk, {c})[0]; }
+inline int64_t DecryptCheckZero(const Scalar& sk, const CipherText& c) {
+  int64_t out;
+  drynx::check(drx_decrypt_check_zero(Gpu::get().ctx(), 1, sk.b, c.b, &out));
+  return out;
+}
+// CreateDecryptionTable(limit, pub, priv): the reference encrypts and decrypts `limit`; here the table is built
+// directly, the keys are accepted for signature compatibility.
+inline void CreateDecryptionTable(int64_t limit, const Point&, const Scalar&) {
+  drynx::check(drx_dlog_table(Gpu::get().ctx(), limit));
+}
+
+}  // namespace libunlynx
+
+// =====================================================================================================================
+namespace libdrynx {
+// PublishSignatureBytes (lib/structs.go:131-141): one server's public key and its u signatures A_k, in wire form.
+struct PublishSignatureBytes {
+  drynx::Point Public;
+  drynx::Bytes Signature;  // u * 128 bytes
+};
+}  // namespace libdrynx
+
+namespace libdrynxrange {
+using drynx::Gpu;
+using drynx::Point;
+using drynx::Scalar;
+
+// ToBase (lib/range/range_proof.go:584-595)
+inline std::vector<int64_t> ToBase(int64_t n, int64_t b, int l) {
+  std::vector<int64_t> digits;
+  while (n > 0) {
+    digits.push_back(n % b);
+    n /= b;
+  }
+  while ((int)digits.size() < l) digits.push_back(0);
+  return digits;
+}
+
+// InitRangeProofSignature(u) (:270-288): draws the server's private key from the random stream.
+inline libdrynx::PublishSignatureBytes InitRangeProofSignatureFromKey(const Scalar& x, int64_t u) {
+  libdrynx::PublishSignatureBytes s;
+  s.Signature.resize((size_t)u * 128);
+  drynx::check(drx_rp_make_sigs(Gpu::get().ctx(), 1, u, x.b, s.Public.b, s.Signature.data()));
+  return s;
+}
+inline libdrynx::PublishSignatureBytes InitRangeProofSignature(int64_t u) { return InitRangeProofSignatureFromKey(drynx::pick(), u); }
+// InitRangeProofSignatureDeterministic (:249-267): x = 12
+inline libdrynx::PublishSignatureBytes InitRangeProofSignatureDeterministic(int64_t u) {
+  return InitRangeProofSignatureFromKey(drynx::scalar_from_u64(12), u);
+}
+
+// The signatures of all servers for one output column, registered with the device (ReadColumn(sigs, i), :598-612).
+struct SignatureColumn {
+  int set_id = -1;
+  int ns = 0;
+  int64_t u = 0;
+  std::vector<Point> Ys;
+};
+inline SignatureColumn RegisterColumn(const std::vector<libdrynx::PublishSignatureBytes>& servers, int64_t u) {
+  static int next_id = 0;
+  SignatureColumn c;
+  c.set_id = next_id++;
+  c.ns = (int)servers.size();
+  c.u = u;
+  drynx::Bytes Y, A;
+  for (auto& s : servers) {
+    Y.insert(Y.end(), s.Public.b, s.Public.b + 64);
+    A.insert(A.end(), s.Signature.begin(), s.Signature.end());
+    c.Ys.push_back(s.Public);
+  }
+  drynx::check(drx_rp_set_sigs(Gpu::get().ctx(), c.set_id, c.ns, u, Y.data(), A.data()));
+  return c;
+}
+
+// CreateProof (:61-69). Sigs is the registered column; U = L = 0 means "no proof" (:322).
+struct CreateProof {
+  SignatureColumn Sigs;
+  int64_t U = 0, L = 0, Secret = 0;
+  Scalar R{};
+  Point CaPub{};
+  libunlynx::CipherText Cipher{};
+};
+// RangeProof in its serialised form (RangeProofBytes field order, :88-155).
+struct RangeProof {
+  drynx::Bytes bytes;
+};
+struct RangeProofList {
+  std::vector<RangeProof> Data;
+};
+
+// CreatePredicateRangeProofListForAllServers (:305-317): one batched creation for the whole list.
+inline std::vector<RangeProof> CreatePredicateRangeProofListForAllServers(const std::vector<CreateProof>& cps) {
+  const size_t n = cps.size();
+  std::vector<RangeProof> out(n);
+  if (!n) return out;
+  libunlynx::use_pubkey(cps[0].CaPub);
+  std::vector<int32_t> sid(n);
+  std::vector<int64_t> l(n), secret(n);
+  std::vector<size_t> poff(n + 1, 0), roff(n + 1, 0);
+  drynx::Bytes r(32 * n), ct(128 * n), rnd;
+  for (size_t p = 0; p < n; p++) {
+    const CreateProof& c = cps[p];
+    const bool none = c.U == 0 && c.L == 0;
+    sid[p] = none ? -1 : c.Sigs.set_id;
+    l[p] = c.L;
+    secret[p] = c.Secret;
+    memcpy(&r[32 * p], c.R.b, 32);
+    memcpy(&ct[128 * p], c.Cipher.b, 128);
+    int64_t nd = none ? 0 : drx_rp_ndigits(c.Secret, c.U, c.L);
+    poff[p + 1] = poff[p] + (none ? 128 : drx_rp_proof_size(c.Sigs.ns, nd));
+    // draw order of :377-379 and :390: per digit s_j, t_j, m_j, then one v per server
+    for (int64_t k = 0; k < nd * (3 + (none ? 0 : c.Sigs.ns)); k++) {
+      Scalar s = drynx::pick();
+      rnd.insert(rnd.end(), s.b, s.b + 32);
+    }
+    roff[p + 1] = rnd.size();
+  }
+  drynx::Bytes proofs(poff[n]);
+  rnd.push_back(0);
+  drynx::check(drx_rp_create(Gpu::get().ctx(), n, sid.data(), l.data(), secret.data(), r.data(), ct.data(), rnd.data(), roff.data(),
+                             proofs.data(), poff.data()));
+  for (size_t p = 0; p < n; p++) out[p].bytes.assign(proofs.begin() + poff[p], proofs.begin() + poff[p + 1]);
+  return out;
+}
+inline RangeProof CreatePredicateRangeProofForAllServ(const CreateProof& cp) {
+  return CreatePredicateRangeProofListForAllServers({cp})[0];
+}
+
+// RangeProofListVerification (:484-501): verifies the first ceil(threshold * N) proofs; ranges[i] = {u, l};
+// columns[i] = the signature column of proof i (its Ys are what ReadColumnYs returns).
+inline std::vector<uint8_t> VerifyEach(const RangeProofList& list, const std::vector<std::pair<int64_t, int64_t>>& ranges,
+                                       const std::vector<SignatureColumn>& columns, const Point& P, size_t count) {
+  std::vector<uint8_t> ok(count);
+  if (!count) return ok;
+  libunlynx::use_pubkey(P);
+  std::vector<int32_t> sid(count);
+  std::vector<int64_t> l(count);
+  std::vector<size_t> off(count + 1, 0);
+  drynx::Bytes all;
+  for (size_t i = 0; i < count; i++) {
+    const bool none = ranges[i].first == 0 && ranges[i].second == 0;
+    sid[i] = none ? -1 : columns[i].set_id;
+    l[i] = ranges[i].second;
+    // a commit-only proof carries 128 bytes; anything else is passed through as received
+    if (none && list.Data[i].bytes.size() != 128) {
+      all.insert(all.end(), list.Data[i].bytes.begin(), list.Data[i].bytes.begin() + 128);
+    } else {
+      all.insert(all.end(), list.Data[i].bytes.begin(), list.Data[i].bytes.end());
+    }
+    off[i + 1] = all.size();
+  }
+  drynx::check(drx_rp_verify(Gpu::get().ctx(), count, sid.data(), l.data(), all.data(), off.data(), ok.data()));
+  return ok;
+}
+inline bool RangeProofListVerification(const RangeProofList& list, const std::vector<std::pair<int64_t, int64_t>>& ranges,
+                                       const std::vector<SignatureColumn>& columns, const Point& P, double verifThreshold) {
+  const size_t nbr = (size_t)std::ceil(verifThreshold * (double)list.Data.size());
+  bool result = true;
+  for (uint8_t v : VerifyEach(list, ranges, columns, P, nbr)) result = result && v;
+  return result;
+}
+inline bool RangeProofVerification(const RangeProof& rp, int64_t u, int64_t l, const SignatureColumn& col, const Point& P) {
+  RangeProofList lst;
+  lst.Data.push_back(rp);
+  return RangeProofListVerification(lst, {{u, l}}, {col}, P, 1.0);
+}
+
+}  // namespace libdrynxrange
+
+// =====================================================================================================================
+namespace libdrynxencoding {
+using drynx::Point;
+using drynx::Scalar;
+using libdrynxrange::CreateProof;
+using libdrynxrange::SignatureColumn;
+using libunlynx::CipherText;
+using libunlynx::CipherVector;
+
+struct Encoded {
+  CipherVector enc;
+  std::vector<int64_t> clear;
+  std::vector<CreateProof> proofs;
+};
+using Ranges = std::vector<std::pair<int64_t, int64_t>>;  // lu[i] = {u, l}
+
+// Shared tail of every Encode*WithProofs: encrypt the plaintext vector in one call, then describe the proofs.
+inline Encoded encrypt_and_describe(const std::vector<int64_t>& clear, const Point& pubKey, const std::vector<SignatureColumn>* sigs,
+                                    const Ranges* lu) {
+  Encoded e;
+  e.clear = clear;
+  auto er = libunlynx::EncryptIntVectorGetRs(pubKey, clear);
+  e.enc = er.first;
+  if (!sigs) return e;
+  e.proofs.resize(clear.size());
+  for (size_t i = 0; i < clear.size(); i++) {
+    CreateProof& cp = e.proofs[i];
+    cp.Sigs = (*sigs)[i];
+    cp.U = (*lu)[i].first;
+    cp.L = (*lu)[i].second;
+    cp.Secret = clear[i];
+    cp.R = er.second[i];
+    cp.CaPub = pubKey;
+    cp.Cipher = e.enc[i];
+  }
+  return e;
+}
+
+// ---- sum (lib/encoding/sum.go:17-43)
+inline Encoded EncodeSumWithProofs(const std::vector<int64_t>& input, const Point& pubKey, const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  int64_t sum = 0;
+  for (int64_t el : input) sum += el;
+  return encrypt_and_describe({sum}, pubKey, sigs, lu);
+}
+inline Encoded EncodeSum(const std::vector<int64_t>& input, const Point& pubKey) { return EncodeSumWithProofs(input, pubKey, nullptr, nullptr); }
+inline int64_t DecodeSum(const CipherText& result, const Scalar& secKey) { return libunlynx::DecryptIntWithNeg(secKey, result); }
+
+// ---- mean (mean.go:17-70): [sum, N]
+inline Encoded EncodeMeanWithProofs(const std::vector<int64_t>& input, const Point& pubKey, const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  int64_t sum = 0;
+  for (int64_t el : input) sum += el;
+  return encrypt_and_describe({sum, (int64_t)input.size()}, pubKey, sigs, lu);
+}
+inline Encoded EncodeMean(const std::vector<int64_t>& input, const Point& pubKey) { return EncodeMeanWithProofs(input, pubKey, nullptr, nullptr); }
+inline double DecodeMean(const CipherVector& result, const Scalar& secKey) {
+  auto c = libunlynx::DecryptIntVectorWithNeg(secKey, result);
+  return (double)c[0] / (double)c[1];
+}
+
+// ---- variance (variance.go:17-75): [sum, N, sum of squares]; Var = E[x^2] - E[x]^2
+inline Encoded EncodeVarianceWithProofs(const std::vector<int64_t>& input, const Point& pubKey, const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  int64_t sum = 0, sq = 0;
+  for (int64_t el : input) {
+    sum += el;
+    sq += el * el;
+  }
+  return encrypt_and_describe({sum, (int64_t)input.size(), sq}, pubKey, sigs, lu);
+}
+inline Encoded EncodeVariance(const std::vector<int64_t>& input, const Point& pubKey) { return EncodeVarianceWithProofs(input, pubKey, nullptr, nullptr); }
+inline double DecodeVariance(const CipherVector& result, const Scalar& secKey) {
+  auto c = libunlynx::DecryptIntVectorWithNeg(secKey, result);
+  const double mean = (double)c[0] / (double)c[1];
+  return (double)c[2] / (double)c[1] - mean * mean;
+}
+
+// ---- frequency count (frequency_count.go:18-78): one counter per value in [min, max]
+inline Encoded EncodeFreqCountWithProofs(const std::vector<int64_t>& input, int64_t min, int64_t max, const Point& pubKey,
+                                         const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  std::vector<int64_t> freq((size_t)(max - min + 1), 0);
+  for (int64_t el : input) freq[(size_t)(el - min)]++;
+  return encrypt_and_describe(freq, pubKey, sigs, lu);
+}
+inline Encoded EncodeFreqCount(const std::vector<int64_t>& input, int64_t min, int64_t max, const Point& pubKey) {
+  return EncodeFreqCountWithProofs(input, min, max, pubKey, nullptr, nullptr);
+}
+inline std::vector<int64_t> DecodeFreqCount(const CipherVector& result, const Scalar& secKey) {
+  return libunlynx::DecryptIntVectorWithNeg(secKey, result);
+}
+
+// ---- linear regression, d dimensions (linear_regression_dims.go:23-106)
+// plaintext order: N | sum x_j (d) | sum x_j x_k for j <= k | sum y | sum x_j y (d)   -> (d^2 + 5d + 4) / 2 values
+inline std::vector<int64_t> LinearRegressionDimsPlaintext(const std::vector<std::vector<int64_t>>& X, const std::vector<int64_t>& y) {
+  const size_t d = X[0].size(), N = X.size();
+  std::vector<int64_t> out, stored;
+  out.push_back((int64_t)N);
+  for (size_t j = 0; j < d; j++) {
+    int64_t sx = 0, sxy = 0;
+    for (size_t i = 0; i < N; i++) {
+      sx += X[i][j];
+      sxy += y[i] * X[i][j];
+    }
+    out.push_back(sx);
+    stored.push_back(sxy);
+  }
+  for (size_t j = 0; j < d; j++)
+    for (size_t k = j; k < d; k++) {
+      int64_t s = 0;
+      for (size_t i = 0; i < N; i++) s += X[i][j] * X[i][k];
+      out.push_back(s);
+    }
+  int64_t sy = 0;
+  for (int64_t el : y) sy += el;
+  out.push_back(sy);
+  out.insert(out.end(), stored.begin(), stored.end());
+  return out;
+}
+inline Encoded EncodeLinearRegressionDimsWithProofs(const std::vector<std::vector<int64_t>>& X, const std::vector<int64_t>& y, const Point& pubKey,
+                                                    const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  Encoded e = encrypt_and_describe(LinearRegressionDimsPlaintext(X, y), pubKey, sigs, lu);
+  e.clear = {0};  // the reference returns []int64{0} as the clear result (:94, :105)
+  return e;
+}
+inline Encoded EncodeLinearRegressionDims(const std::vector<std::vector<int64_t>>& X, const std::vector<int64_t>& y, const Point& pubKey) {
+  return EncodeLinearRegressionDimsWithProofs(X, y, pubKey, nullptr, nullptr);
+}
+// DecodeLinearRegressionDims (:110-163): rebuild the symmetric normal-equation matrix and solve it. The reference
+// solves over the rationals; this mirror uses Gaussian elimination with partial pivoting in long double.
+inline std::vector<double> DecodeLinearRegressionDims(const CipherVector& result, const Scalar& secKey) {
+  const auto v = libunlynx::DecryptIntVectorWithNeg(secKey, result);
+  const int len = (int)v.size();
+  const int d = (int)std::llround((-5.0 + std::sqrt(25.0 - 4.0 * (4.0 - 2.0 * len))) / 2.0);
+  std::vector<std::vector<long double>> M(d + 1, std::vector<long double>(d + 2, 0));
+  int s = 0, l = d + 1, k = d + 1, i = 0;
+  for (int j = 0; j < len - d - 1; j++) {
+    if (j == l) {
+      k--;
+      l += k;
+      i++;
+      s = 0;
+    }
+    M[i][i + s] = (long double)v[j];
+    if (s != 0) M[i + s][i] = (long double)v[j];
+    s++;
+  }
+  for (int j = len - d - 1; j < len; j++) M[j - len + d + 1][d + 1] = (long double)v[j];
+  const int n = d + 1;
+  for (int c = 0; c < n; c++) {
+    int piv = c;
+    for (int r = c + 1; r < n; r++)
+      if (fabsl(M[r][c]) > fabsl(M[piv][c])) piv = r;
+    std::swap(M[c], M[piv]);
+    for (int r = 0; r < n; r++) {
+      if (r == c || M[c][c] == 0) continue;
+      const long double f = M[r][c] / M[c][c];
+      for (int q = c; q <= n; q++) M[r][q] -= f * M[c][q];
+    }
+  }
+  std::vector<double> coeffs(n);
+  for (int r = 0; r < n; r++) coeffs[r] = (double)(M[r][n] / M[r][r]);
+  return coeffs;
+}
+
+// ---- logistic regression pre-pass (logistic_regression.go; float64, evaluated in the reference's order)
+struct LogisticRegressionParameters {  // the fields of libdrynx.LogisticRegressionParameters this path reads
+  int64_t NbrFeatures = 0;
+  int64_t NbrRecords = 0;
+  int K = 2;
+  double PrecisionApproxCoefficients = 1;
+  std::vector<double> Means, StandardDeviations;
+};
+inline int64_t Factorial(int64_t n) { return n > 0 ? n * Factorial(n - 1) : 1; }
+// CombinationsWithRepetition (:281-303) = C(n + k - 1, k)
+inline int64_t CombinationsWithRepetition(int64_t n, int64_t k) {
+  if (k > n) {  // the reference's reduction loop only runs for k <= n and otherwise returns 1
+    return 1;
+  }
+  int64_t numerator = 1, denominator = Factorial(k), divisor = 2;
+  for (int64_t i = 1; i <= k; i++) {
+    numerator *= (n + k - i);
+    while (divisor <= k && numerator % divisor == 0 && denominator % divisor == 0) {
+      numerator /= divisor;
+      denominator /= divisor;
+      divisor++;
+    }
+  }
+  return numerator / denominator;
+}
+inline int getNumberApproxCoefficients(int64_t d, int level) { return (int)std::pow((double)(d + 1), (double)(level + 1)); }
+inline int getTotalNumberApproxCoefficients(int64_t d, int k) {
+  int c = 0;
+  for (int j = 0; j < k; j++) c += (int)std::pow((double)(d + 1), (double)(j + 1));
+  return c;
+}
+// CartesianProduct(start, end, dim): all index tuples in lexicographic order (logistic_regression_test.go:544-558)
+inline std::vector<std::vector<int64_t>> CartesianProduct(int64_t start, int64_t end, int dim) {
+  std::vector<std::vector<int64_t>> out;
+  std::vector<int64_t> cur((size_t)dim, start);
+  if (end <= start) return out;
+  for (;;) {
+    out.push_back(cur);
+    int pos = dim - 1;
+    while (pos >= 0 && ++cur[(size_t)pos] == end) cur[(size_t)pos--] = start;
+    if (pos < 0) break;
+  }
+  return out;
+}
+// ComputeDistinctApproxCoefficients (:322-364)
+inline std::vector<std::vector<double>> ComputeDistinctApproxCoefficients(const std::vector<double>& X, int64_t y, int k) {
+  const int d = (int)X.size() - 1;
+  std::vector<std::vector<double>> a((size_t)k);
+  for (int j = 0; j < k; j++) a[(size_t)j].assign((size_t)CombinationsWithRepetition(d + 1, j + 1), 0.0);
+  for (int s = 0; s <= d; s++) a[0][(size_t)s] = X[(size_t)s] * (2 * (double)y - 1);
+  for (int j = 1; j < k; j++) {
+    const int total = (int)a[(size_t)j].size();
+    const int64_t ypart = y - y * (int64_t)std::pow(-1.0, (double)(j + 1)) - 1;
+    int idx1 = 0, idx2 = 0;
+    int64_t c = CombinationsWithRepetition(d + 1 - idx2, j), cPrev = c;
+    for (int ri = 0; ri < total; ri++) {
+      a[(size_t)j][(size_t)ri] = a[(size_t)j - 1][(size_t)idx1] * X[(size_t)idx2] * (double)ypart;
+      idx1++;
+      c--;
+      if (c == 0) {
+        idx2++;
+        c = CombinationsWithRepetition(d + 1 - idx2, j);
+        idx1 = (int)(cPrev - c);
+      }
+    }
+  }
+  return a;
+}
+// ComputeAllApproxCoefficients (:367-403)
+inline std::vector<std::vector<double>> ComputeAllApproxCoefficients(const std::vector<double>& X, int64_t y, int k) {
+  const int d = (int)X.size() - 1;
+  std::vector<std::vector<double>> a((size_t)k);
+  for (int j = 0; j < k; j++) a[(size_t)j].assign((size_t)std::pow((double)(d + 1), (double)(j + 1)), 0.0);
+  for (int s = 0; s <= d; s++) a[0][(size_t)s] = X[(size_t)s] * (2 * (double)y - 1);
+  for (int j = 2; j <= k; j++) {
+    const double ypart = (double)(y - y * (int64_t)std::pow(-1.0, (double)j) - 1);
+    const auto comb = CartesianProduct(0, d + 1, j);
+    for (size_t ri = 0; ri < comb.size(); ri++) {
+      double xp = 1.0;
+      for (int64_t idx : comb[ri]) xp *= X[(size_t)idx];
+      a[(size_t)j - 1][ri] = ypart * xp;
+    }
+  }
+  return a;
+}
+// AggregateApproxCoefficients (:433-455): record-by-record sums in index order (the float64 order is part of the result)
+inline std::vector<std::vector<double>> AggregateApproxCoefficients(const std::vector<std::vector<std::vector<double>>>& all) {
+  std::vector<std::vector<double>> agg(all[0].size());
+  for (size_t j = 0; j < agg.size(); j++) agg[j].assign(all[0][j].size(), 0.0);
+  for (auto& rec : all)
+    for (size_t j = 0; j < rec.size(); j++)
+      for (size_t ri = 0; ri < rec[j].size(); ri++) agg[j][ri] += rec[j][ri];
+  return agg;
+}
+inline std::vector<std::vector<double>> StandardiseWith(const std::vector<std::vector<double>>& data, const std::vector<double>& means,
+                                                        const std::vector<double>& sds) {
+  auto out = data;
+  for (auto& rec : out)
+    for (size_t i = 0; i < rec.size(); i++) rec[i] = (rec[i] - means[i]) / sds[i];
+  return out;
+}
+inline std::vector<std::vector<double>> Augment(const std::vector<std::vector<double>>& m) {
+  auto out = m;
+  for (auto& rec : out) rec.insert(rec.begin(), 1.0);
+  return out;
+}
+inline std::vector<std::vector<int64_t>> Float64ToInt642DArrayWithPrecision(const std::vector<std::vector<double>>& a, double precision) {
+  std::vector<std::vector<int64_t>> out(a.size());
+  for (size_t i = 0; i < a.size(); i++)
+    for (double x : a[i]) out[i].push_back((int64_t)std::round(x * precision));
+  return out;
+}
+// The packed int64 coefficient vector of EncodeLogisticRegression (:46-118): level j at offset j * (d+1)^j.
+inline std::vector<int64_t> LogisticRegressionPlaintext(const std::vector<std::vector<double>>& xData, const std::vector<int64_t>& yData,
+                                                        const LogisticRegressionParameters& lr) {
+  const int64_t d = lr.NbrFeatures;
+  std::vector<int64_t> packed((size_t)getTotalNumberApproxCoefficients(d, lr.K), 0);
+  if (xData.empty()) return packed;
+  auto Xs = Augment(StandardiseWith(xData, lr.Means, lr.StandardDeviations));
+  std::vector<std::vector<std::vector<double>>> all;
+  for (size_t i = 0; i < Xs.size(); i++) all.push_back(ComputeAllApproxCoefficients(Xs[i], yData[i], lr.K));
+  const auto ints = Float64ToInt642DArrayWithPrecision(AggregateApproxCoefficients(all), lr.PrecisionApproxCoefficients);
+  for (int j = 0; j < lr.K; j++) {
+    const int nLevel = getNumberApproxCoefficients(d, j), nPrev = getNumberApproxCoefficients(d, j - 1);
+    for (int i = 0; i < nLevel; i++) packed[(size_t)(j * nPrev + i)] = ints[(size_t)j][(size_t)i];
+  }
+  return packed;
+}
+inline Encoded EncodeLogisticRegressionWithProofs(const std::vector<std::vector<double>>& xData, const std::vector<int64_t>& yData,
+                                                  const LogisticRegressionParameters& lr, const Point& pubKey,
+                                                  const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  const auto packed = LogisticRegressionPlaintext(xData, yData, lr);
+  for (int64_t v : packed)
+    if (v > libunlynx::MaxHomomorphicInt) throw drynx::Error(-1, "coefficient exceeds MaxHomomorphicInt");  // log.Fatalf at :415
+  return encrypt_and_describe(packed, pubKey, sigs, lu);
+}
+inline Encoded EncodeLogisticRegression(const std::vector<std::vector<double>>& xData, const std::vector<int64_t>& yData,
+                                        const LogisticRegressionParameters& lr, const Point& pubKey) {
+  return EncodeLogisticRegressionWithProofs(xData, yData, lr, pubKey, nullptr, nullptr);
+}
+
+}  // namespace libdrynxencoding
