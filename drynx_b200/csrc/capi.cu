@@ -137,7 +137,8 @@ struct RpSetHost {
 
 struct drx_ctx {
   int device = 0;
-  cudaStream_t own_stream = nullptr, stream = nullptr;
+  cudaStream_t own_stream = nullptr, stream = nullptr, side_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;  // fork/join of the side stream (independent small kernels)
   std::mutex mu;
   uint64_t launches = 0;
   bool have_pub = false, have_dlog = false;
@@ -180,7 +181,7 @@ int check_launch(const char* what) {
 
 // Brackets the kernels `fn` launches with an event pair when profiling is on; always counts launches.
 template <class Fn>
-void timed(drx_ctx* c, const char* name, Fn fn) {
+void timed_on(drx_ctx* c, cudaStream_t st, const char* name, Fn fn) {
   if (!c->prof.on) {
     c->launches += fn();
     return;
@@ -189,10 +190,14 @@ void timed(drx_ctx* c, const char* name, Fn fn) {
   sp.name = name;
   cudaEventCreate(&sp.a);
   cudaEventCreate(&sp.b);
-  cudaEventRecord(sp.a, c->stream);
+  cudaEventRecord(sp.a, st);
   c->launches += fn();
-  cudaEventRecord(sp.b, c->stream);
+  cudaEventRecord(sp.b, st);
   c->prof.spans.push_back(sp);
+}
+template <class Fn>
+void timed(drx_ctx* c, const char* name, Fn fn) {
+  timed_on(c, c->stream, name, fn);
 }
 void prof_collect(drx_ctx* c) {
   for (auto& sp : c->prof.spans) {
@@ -244,6 +249,12 @@ int drx_init(drx_ctx** out, int device, const uint8_t* g1_base, const uint8_t* g
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { delete c; return fail((int)e, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
   c->stream = c->own_stream;
+  if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+    drx_free(c);
+    return fail(-3, "drx_init: cannot create side stream");
+  }
   int rc = 0;
   auto cleanup = [&](int code) { drx_free(c); return code; };
   if ((rc = c->bad.ensure(256))) return cleanup(rc);
@@ -283,6 +294,9 @@ void drx_free(drx_ctx* c) {
     kv.second.sumY.release();
   }
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  if (c->side_stream) cudaStreamDestroy(c->side_stream);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   delete c;
 }
 

@@ -106,13 +106,16 @@ DRX_NI void miller_loop(Fp12& f, const G1Aff& P, const G2Aff& Q) {
   fp12_mul_line(f, f, c, b, a);
 }
 
-// a^u for a in the cyclotomic subgroup (u = 6518589491078791937, 63 bits)
+// a^u for a in the cyclotomic subgroup (u = 6518589491078791937): signed-digit (NAF, weight 23 instead of 30)
+// square-and-multiply; a^-1 is the conjugate there, so negative digits cost the same as positive ones.
 DRX_NI void fp12_pow_u(Fp12& r, const Fp12& a) {
-  const uint64_t u = ((uint64_t)DRX_U_HI << 32) | DRX_U_LO;
-  Fp12 acc = a;
-  for (int i = 61; i >= 0; i--) {  // bit 62 is the leading one
+  Fp12 acc = a, inv;
+  fp12_conj(inv, a);
+  for (int i = DRX_U_NAF_LEN - 2; i >= 0; i--) {  // the top digit is +1
     fp12_cyclo_sqr(acc, acc);
-    if ((u >> i) & 1) fp12_mul(acc, acc, a);
+    const int d = u_naf(i);
+    if (d > 0) fp12_mul(acc, acc, a);
+    else if (d < 0) fp12_mul(acc, acc, inv);
   }
   r = acc;
 }
