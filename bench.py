@@ -322,15 +322,24 @@ def run_gpu(args):
     ptrs = (ctypes.c_void_p * ndp)(*[h_ct.ctypes.data + k * NOUT * 128 for k in range(ndp)])
     be.set_stream(0)
 
+    be2.set_stream(0)
+
+    def agg_dec():
+        ck(lib.drx_aggregate(be2.h, ndp, NOUT, ctypes.cast(ptrs, ctypes.c_void_p), np_p(h_ag)))
+        if rank == 0 and world == 1:
+            ck(lib.drx_decrypt(be2.h, NOUT, skp, np_p(h_ag), 1, np_p(h_dec), np_p(h_found)))
+
     def step_e2e():
+        # what a Go data provider / root / verifying node would do with two goroutines and one context each:
+        # aggregation + decryption only need the ciphertexts and run next to proof creation + verification
         m = host_reduce(h['rows'])
         ck(lib.drx_encrypt(be.h, n, np_p(m), np_p(h['r']), np_p(h_ct)))
+        side = threading.Thread(target=agg_dec)
+        side.start()
         ck(lib.drx_rp_create(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(m), np_p(h['r']), np_p(h_ct), np_p(h['rnd']), np_p(roff),
                              np_p(h_pr), np_p(poff)))
         ck(lib.drx_rp_verify(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h_pr), np_p(poff), np_p(h_ok)))
-        ck(lib.drx_aggregate(be.h, ndp, NOUT, ctypes.cast(ptrs, ctypes.c_void_p), np_p(h_ag)))
-        if rank == 0 and world == 1:
-            ck(lib.drx_decrypt(be.h, NOUT, skp, np_p(h_ag), 1, np_p(h_dec), np_p(h_found)))
+        side.join()
         return m
     h2d = (n * 8 + n * 32) + (n * 4 + n * 8 * 2 + n * 32 + n * 128 + h['rnd'].nbytes) + (n * 4 + n * 8 + h_pr.nbytes + n * 4) \
         + h_ct.nbytes + (NOUT * 128 + 32)  # encrypt + create + verify + aggregate + decrypt inputs
@@ -350,6 +359,7 @@ def run_gpu(args):
         e2e_s = float(t.item())
     e2e_val = world * n * args.steps / e2e_s
     be.set_stream(stream.cuda_stream or 1)
+    be2.set_stream(stream2.cuda_stream)
 
     # ------------------------------------------------------------------ roofline of the dominant kernel
     mac_ms, mac_work = be.microbench(0, 20000)

@@ -124,16 +124,39 @@ k_agg_partial(size_t ndp, size_t v, const uint32_t* __restrict__ cts, int slices
   if (nbad) atomicAdd(bad, nbad);
 }
 
+// Stage 2, one warp per column: lane l folds slices l, l+32, ... and a five-level butterfly of full additions
+// leaves the column sum in every lane; lane 0 converts to affine and serialises. (A single thread per column
+// would walk all slices serially: 63 dependent additions for the 64-slice case.)
+__device__ __forceinline__ G1Jac jac_shfl_xor(const G1Jac& p, int m) {
+  G1Jac r;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    r.x.v[k] = __shfl_xor_sync(0xffffffffu, p.x.v[k], m);
+    r.y.v[k] = __shfl_xor_sync(0xffffffffu, p.y.v[k], m);
+    r.z.v[k] = __shfl_xor_sync(0xffffffffu, p.z.v[k], m);
+  }
+  return r;
+}
 __global__ void __launch_bounds__(128)
 k_agg_final(size_t v, int slices, const AggPartial* __restrict__ part, uint32_t* __restrict__ out) {
-  const size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= v) return;
-  G1Jac aK = part[j].K, aC = part[j].C;
-  for (int s = 1; s < slices; s++) {
+  const size_t j = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (j >= v) return;  // whole warps leave together
+  G1Jac aK = jac_inf<Fp>(), aC = jac_inf<Fp>();
+  for (int s = lane; s < slices; s += 32) {
     aK = jac_add(aK, part[(size_t)s * v + j].K);
     aC = jac_add(aC, part[(size_t)s * v + j].C);
   }
-  store_pair_wire(out + 32 * j, aK, aC);
+  for (int m = 16; m >= 1; m >>= 1) {
+    if (m < slices) {  // uniform across the warp
+      const G1Jac oK = jac_shfl_xor(aK, m), oC = jac_shfl_xor(aC, m);
+      // same operand order on both partners keeps their copies bit-identical
+      const bool low = (lane & m) == 0;
+      aK = low ? jac_add(aK, oK) : jac_add(oK, aK);
+      aC = low ? jac_add(aC, oC) : jac_add(oC, aC);
+    }
+  }
+  if (lane == 0) store_pair_wire(out + 32 * j, aK, aC);
 }
 
 size_t aggregate_scratch_bytes(size_t ndp, size_t v, int* slices_out) {
@@ -155,7 +178,7 @@ int launch_agg_partial(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_c
 }
 int launch_agg_final(cudaStream_t st, size_t v, int slices, const void* d_scratch, uint8_t* d_out) {
   if (!v) return 0;
-  k_agg_final<<<grid_for(v, 128), 128, 0, st>>>(v, slices, (const AggPartial*)d_scratch, (uint32_t*)d_out);
+  k_agg_final<<<grid_for(v * 32, 128), 128, 0, st>>>(v, slices, (const AggPartial*)d_scratch, (uint32_t*)d_out);
   return 1;
 }
 
@@ -209,7 +232,7 @@ int launch_aggregate_static(cudaStream_t st, size_t ndp, size_t v, const uint8_t
   e = cudaMemsetAsync(d_bad, 0, 256, st);                    // the counter must start at zero; the partials are
   if (e != cudaSuccess) return (int)e;                       // all rewritten by stage 1 before stage 2 reads them
   k_agg_partial<<<grid_for(v * slices, 128), 128, 0, st>>>(ndp, v, (const uint32_t*)d_cts, (int)slices, part, d_bad);
-  k_agg_final<<<grid_for(v, 128), 128, 0, st>>>(v, (int)slices, part, (uint32_t*)d_out);
+  k_agg_final<<<grid_for(v * 32, 128), 128, 0, st>>>(v, (int)slices, part, (uint32_t*)d_out);
   *launches = 2;
   e = cudaGetLastError();
   if (e != cudaSuccess) return (int)e;

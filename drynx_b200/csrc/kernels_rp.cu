@@ -172,21 +172,7 @@ k_rp_create_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __r
   const int64_t u = set.u;
   const int64_t sec = secret[p];
   // c = SHA3-512(B || C || sum Y) mod n
-  uint32_t msg[48], dig[16];
-  for (int k = 0; k < 16; k++) {
-    msg[k] = baseB_wire[k];
-    msg[16 + k] = ct[32 * p + 16 + k];
-    msg[32 + k] = ((const uint32_t*)set.sumY)[k];
-  }
-  sha3_512_words(dig, msg, 48);
-  const Scalar c = sc_from_digest(dig);
-#ifdef DRX_DEBUG_RP
-  if (p == 0) {
-    printf("msg %08x %08x | %08x %08x | %08x %08x\n", msg[0], msg[15], msg[16], msg[31], msg[32], msg[47]);
-    printf("dig %08x %08x %08x %08x\n", dig[0], dig[7], dig[8], dig[15]);
-    printf("c   %08x %08x\n", c.v[0], c.v[7]);
-  }
-#endif
+  const Scalar c = rp_challenge(baseB_wire, ct + 32 * p, set.sumY);
   const uint32_t* rp = rnd + (b.d_proof_off ? rnd_off[p] / 4 : p * (size_t)nd * (3 + ns) * 8);
   ProofView pv{ns, nd};
   Scalar msum = sc_zero(), ssum = sc_zero();
@@ -215,10 +201,11 @@ k_rp_create_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __r
 __global__ void __launch_bounds__(64)
 k_rp_create_items(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
                   const uint32_t* __restrict__ rnd, const size_t* __restrict__ rnd_off,
-                  const Fp12* __restrict__ tabGtB, uint32_t* __restrict__ proofs) {
+                  const Fp12* __restrict__ tabGtB, const uint32_t* __restrict__ baseB_wire,
+                  const uint32_t* __restrict__ ct, uint32_t* __restrict__ proofs) {
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= b.items) return;
-  rp_create_item(b, sets, secret, rnd, rnd_off, tabGtB, proofs, t);
+  rp_create_item(b, sets, secret, rnd, rnd_off, tabGtB, baseB_wire, ct, proofs, t);
 }
 
 int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
@@ -232,10 +219,12 @@ int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_se
   return 1;
 }
 int launch_rp_create_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB, uint8_t* d_proofs) {
+                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
+                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs) {
   if (!b.items) return 0;
   k_rp_create_items<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_rnd, d_rnd_off,
-                                                         (const Fp12*)d_tabGtB, (uint32_t*)d_proofs);
+                                                         (const Fp12*)d_tabGtB, (const uint32_t*)d_baseB_wire,
+                                                         (const uint32_t*)d_ct, (uint32_t*)d_proofs);
   return 1;
 }
 

@@ -23,10 +23,11 @@ k_rp_verify_items_coop4(RpBatch b, const RpSetDev* __restrict__ sets, const G1Af
 __global__ void __launch_bounds__(64)
 k_rp_create_items_coop4(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
                         const uint32_t* __restrict__ rnd, const size_t* __restrict__ rnd_off,
-                        const Fp12* __restrict__ tabGtB, uint32_t* __restrict__ proofs) {
+                        const Fp12* __restrict__ tabGtB, const uint32_t* __restrict__ baseB_wire,
+                        const uint32_t* __restrict__ ct, uint32_t* __restrict__ proofs) {
   const size_t t = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 2;
   if (t >= b.items) return;
-  rp_create_item(b, sets, secret, rnd, rnd_off, tabGtB, proofs, t);  // the four lanes store identical bytes
+  rp_create_item(b, sets, secret, rnd, rnd_off, tabGtB, baseB_wire, ct, proofs, t);  // the four lanes store identical bytes
 }
 
 int launch_rp_verify_items_coop4(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
@@ -38,10 +39,12 @@ int launch_rp_verify_items_coop4(cudaStream_t st, const RpBatch& b, const RpSetD
   return 1;
 }
 int launch_rp_create_items_coop4(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                                 const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB, uint8_t* d_proofs) {
+                                 const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
+                                 const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs) {
   if (!b.items) return 0;
   k_rp_create_items_coop4<<<grid_for(b.items * 4, 64), 64, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_rnd,
                                                                    d_rnd_off, (const Fp12*)d_tabGtB,
+                                                                   (const uint32_t*)d_baseB_wire, (const uint32_t*)d_ct,
                                                                    (uint32_t*)d_proofs);
   return 1;
 }

@@ -78,7 +78,8 @@ int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_se
                          const uint8_t* d_r, const uint8_t* d_ct, const uint8_t* d_rnd, const size_t* d_rnd_off,
                          const void* d_tabB, const void* d_tabP, const uint8_t* d_baseB_wire, uint8_t* d_proofs);
 int launch_rp_create_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB, uint8_t* d_proofs);
+                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
+                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs);
 int launch_rp_verify_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                          const void* d_tabP, const uint8_t* d_proofs, uint32_t* d_flags);
 int launch_rp_verify_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
@@ -89,6 +90,7 @@ constexpr size_t kCoopMaxItems = 0;  // off by default: measured no faster than 
 int launch_rp_verify_items_coop4(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                                  const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags);
 int launch_rp_create_items_coop4(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                                 const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB, uint8_t* d_proofs);
+                                 const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
+                                 const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs);
 
 }  // namespace drx

@@ -36,6 +36,19 @@ __device__ __forceinline__ Scalar sc_from_digest(const uint32_t d[16]) {
   return sc_add(t, lo);
 }
 
+// c = SHA3-512(B || C || sum Y) mod n (lib/range/range_proof.go:349-374); C is the second half of the ciphertext.
+__device__ __forceinline__ Scalar rp_challenge(const uint32_t* __restrict__ baseB_wire, const uint32_t* __restrict__ ct,
+                                              const uint8_t* __restrict__ sumY) {
+  uint32_t msg[48], dig[16];
+  for (int k = 0; k < 16; k++) {
+    msg[k] = baseB_wire[k];
+    msg[16 + k] = ct[16 + k];
+    msg[32 + k] = ((const uint32_t*)sumY)[k];
+  }
+  sha3_512_words(dig, msg, 48);
+  return sc_from_digest(dig);
+}
+
 // ------------------------------------------------------------------ proof layout (lib/range/range_proof.go:72-155)
 struct ProofView {
   int ns, nd;
@@ -106,6 +119,7 @@ __device__ __forceinline__ bool locate_item(const RpBatch& b, const RpSetDev* se
 __device__ __forceinline__ void rp_create_item(const RpBatch& b, const RpSetDev* __restrict__ sets,
                                                const int64_t* __restrict__ secret, const uint32_t* __restrict__ rnd,
                                                const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB,
+                                               const uint32_t* __restrict__ baseB_wire, const uint32_t* __restrict__ ct,
                                                uint32_t* __restrict__ proofs, size_t t) {
   size_t p, off;
   int i, j, ns, nd;
@@ -119,7 +133,9 @@ __device__ __forceinline__ void rp_create_item(const RpBatch& b, const RpSetDev*
   const Scalar sj = sc_from_wire(row);
   const Scalar tj = sc_from_wire(row + 8);
   const Scalar v = sc_from_wire(row + 8 * (3 + i));
-  const Scalar c = sc_from_wire(out + ProofView::c_off());
+  // the challenge is recomputed here rather than read from the header so that the header kernel can run
+  // concurrently on the side stream
+  const Scalar c = rp_challenge(baseB_wire, ct + 32 * p, set.sumY);
   const uint32_t phi = rp_digit(secret[p], u, j);
   const size_t tab = ((size_t)i * u + phi) * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES);
   // V_ij = v * A_{i,phi}
