@@ -208,6 +208,36 @@ k_rp_create_items(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* _
   rp_create_item(b, sets, secret, rnd, rnd_off, tabGtB, baseB_wire, ct, proofs, t);
 }
 
+// Role-split creation: blockIdx.y = role (see rp_device.cuh).
+__global__ void __launch_bounds__(64)
+k_rp_create_roles(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
+                  const uint32_t* __restrict__ rnd, const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB,
+                  const uint32_t* __restrict__ baseB_wire, const uint32_t* __restrict__ ct, uint32_t* __restrict__ proofs,
+                  GtPair* __restrict__ scratch) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= b.items) return;
+  rp_create_role(b, sets, secret, rnd, rnd_off, tabGtB, baseB_wire, ct, proofs, scratch, t, (int)blockIdx.y);
+}
+__global__ void __launch_bounds__(64)
+k_rp_create_finish(RpBatch b, const RpSetDev* __restrict__ sets, const GtPair* __restrict__ scratch,
+                   uint32_t* __restrict__ proofs) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= b.items) return;
+  rp_create_finish(b, sets, scratch, proofs, t);
+}
+size_t rp_scratch_bytes(size_t items) { return items * sizeof(GtPair); }
+int launch_rp_create_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
+                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch) {
+  if (!b.items) return 0;
+  dim3 grid(grid_for(b.items, 64), 3);
+  k_rp_create_roles<<<grid, 64, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_rnd, d_rnd_off, (const Fp12*)d_tabGtB,
+                                         (const uint32_t*)d_baseB_wire, (const uint32_t*)d_ct, (uint32_t*)d_proofs,
+                                         (GtPair*)d_scratch);
+  k_rp_create_finish<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, (const GtPair*)d_scratch, (uint32_t*)d_proofs);
+  return 2;
+}
+
 int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
                          const uint8_t* d_r, const uint8_t* d_ct, const uint8_t* d_rnd, const size_t* d_rnd_off,
                          const void* d_tabB, const void* d_tabP, const uint8_t* d_baseB_wire, uint8_t* d_proofs) {
@@ -302,6 +332,32 @@ int launch_rp_verify_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_
                                                             (const uint32_t*)d_proofs, d_flags);
   return 1;
 }
+// Role-split verification: blockIdx.y = role.
+__global__ void __launch_bounds__(64, DRX_VERIFY_MINBLOCKS)
+k_rp_verify_roles(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __restrict__ tabB,
+                  const Fp12* __restrict__ tabGtB, const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags,
+                  GtPair* __restrict__ scratch) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= b.items) return;
+  rp_verify_role(b, sets, tabB, tabGtB, proofs, flags, scratch, t, (int)blockIdx.y);
+}
+__global__ void __launch_bounds__(128)
+k_rp_verify_finish(RpBatch b, const RpSetDev* __restrict__ sets, const GtPair* __restrict__ scratch,
+                   uint32_t* __restrict__ flags) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= b.items) return;
+  rp_verify_finish(b, sets, scratch, flags, t);
+}
+int launch_rp_verify_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                           const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch) {
+  if (!b.items) return 0;
+  dim3 grid(grid_for(b.items, 64), 2);
+  k_rp_verify_roles<<<grid, 64, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const Fp12*)d_tabGtB,
+                                         (const uint32_t*)d_proofs, d_flags, (GtPair*)d_scratch);
+  k_rp_verify_finish<<<grid_for(b.items, 128), 128, 0, st>>>(b, d_sets, (const GtPair*)d_scratch, d_flags);
+  return 2;
+}
+
 int launch_rp_flags(cudaStream_t st, size_t n, const uint32_t* d_flags, uint8_t* d_ok) {
   if (!n) return 0;
   k_flags_to_bytes<<<grid_for(n, 256), 256, 0, st>>>(n, d_flags, d_ok);

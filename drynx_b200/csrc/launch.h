@@ -85,6 +85,14 @@ int launch_rp_verify_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_se
 int launch_rp_verify_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                            const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags);
 int launch_rp_flags(cudaStream_t st, size_t n, const uint32_t* d_flags, uint8_t* d_ok);
+// role-split item kernels (independent parts of one item in different thread blocks) + their finish kernels;
+// d_scratch holds rp_scratch_bytes(items) bytes (two GT elements per item)
+size_t rp_scratch_bytes(size_t items);
+int launch_rp_create_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
+                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch);
+int launch_rp_verify_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                           const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 // four lanes per item, for small batches (kernels_rp_coop.cu)
 constexpr size_t kCoopMaxItems = 0;  // off by default: measured no faster than one thread per item
 int launch_rp_verify_items_coop4(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,

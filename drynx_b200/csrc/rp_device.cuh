@@ -151,6 +151,101 @@ __device__ __forceinline__ void rp_create_item(const RpBatch& b, const RpSetDev*
 }
 
 
+// The same item split into independent roles that run in different thread blocks (three times the threads, a
+// third of the latency): role 0 writes V_ij and Zv_ij, role 1 computes e(B, A_{i,phi})^(-s_j v), role 2 computes
+// e(B, g2)^(t_j); the two GT factors go to scratch and rp_create_finish multiplies and serialises them.
+struct GtPair {
+  Fp12 a, b;
+};
+__device__ __forceinline__ void rp_create_role(const RpBatch& b, const RpSetDev* __restrict__ sets,
+                                               const int64_t* __restrict__ secret, const uint32_t* __restrict__ rnd,
+                                               const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB,
+                                               const uint32_t* __restrict__ baseB_wire, const uint32_t* __restrict__ ct,
+                                               uint32_t* __restrict__ proofs, GtPair* __restrict__ scratch, size_t t,
+                                               int role) {
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  uint32_t* out = proofs + off / 4;
+  const RpSetDev set = sets[b.d_set_id[p]];
+  const int u = set.u;
+  ProofView pv{ns, nd};
+  const uint32_t* rp = rnd + (b.d_proof_off ? rnd_off[p] / 4 : p * (size_t)nd * (3 + ns) * 8);
+  const uint32_t* row = rp + (size_t)j * (3 + ns) * 8;
+  const Scalar v = sc_from_wire(row + 8 * (3 + i));
+  const uint32_t phi = rp_digit(secret[p], u, j);
+  const size_t tab = ((size_t)i * u + phi) * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES);
+  if (role == 0) {
+    const Scalar tj = sc_from_wire(row + 8);
+    const Scalar c = rp_challenge(baseB_wire, ct + 32 * p, set.sumY);
+    const G2Jac V = comb_mul((const G2Aff*)set.tabA + tab, v);
+    g2_to_wire(out + pv.v_off(i, j), jac_to_aff(V));
+    sc_to_wire(out + pv.zv_off(i, j), sc_sub(tj, sc_mul(c, v)));
+  } else if (role == 1) {
+    const Scalar sj = sc_from_wire(row);
+    gt_comb_pow(scratch[t].a, (const Fp12*)set.tabGtA + tab, sc_neg(sc_mul(sj, v)));
+  } else {
+    const Scalar tj = sc_from_wire(row + 8);
+    gt_comb_pow(scratch[t].b, tabGtB, tj);
+  }
+}
+__device__ __forceinline__ void rp_create_finish(const RpBatch& b, const RpSetDev* __restrict__ sets,
+                                                 const GtPair* __restrict__ scratch, uint32_t* __restrict__ proofs,
+                                                 size_t t) {
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  ProofView pv{ns, nd};
+  Fp12 a;
+  fp12_mul(a, scratch[t].a, scratch[t].b);
+  gt_to_wire(proofs + off / 4 + pv.a_off(i, j), a);
+}
+
+// Verification item in two roles: role 0 computes e = e(c*Y_i - Zphi_j*B, V_ij), role 1 computes
+// T = A_ij * e(B, g2)^(-Zv_ij); rp_verify_finish accepts iff e == T (the same equation as below, moved across).
+__device__ __forceinline__ void rp_verify_role(const RpBatch& b, const RpSetDev* __restrict__ sets,
+                                               const G1Aff* __restrict__ tabB, const Fp12* __restrict__ tabGtB,
+                                               const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags,
+                                               GtPair* __restrict__ scratch, size_t t, int role) {
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  const uint32_t* in = proofs + off / 4;
+  const RpSetDev set = sets[b.d_set_id[p]];
+  ProofView pv{ns, nd};
+  if (role == 0) {
+    G2Aff V;
+    if (!g2_from_wire(V, in + pv.v_off(i, j))) {
+      atomicAnd(&flags[p], 0u);
+      scratch[t].a = fp12_one();
+      return;
+    }
+    const Scalar c = sc_from_wire(in + ProofView::c_off());
+    const Scalar zphi = sc_from_wire(in + pv.zphi_off(j));
+    G1Jac P1 = comb_mul((const G1Aff*)set.tabY + (size_t)i * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES), c);
+    P1 = jac_add(P1, comb_mul(tabB, sc_neg(zphi)));
+    pairing(scratch[t].a, jac_to_aff(P1), V);
+  } else {
+    Fp12 A, g;
+    if (!gt_from_wire(A, in + pv.a_off(i, j))) {
+      atomicAnd(&flags[p], 0u);
+      scratch[t].b = fp12_one();
+      return;
+    }
+    const Scalar zv = sc_from_wire(in + pv.zv_off(i, j));
+    gt_comb_pow(g, tabGtB, sc_neg(zv));
+    fp12_mul(scratch[t].b, A, g);
+  }
+}
+__device__ __forceinline__ void rp_verify_finish(const RpBatch& b, const RpSetDev* __restrict__ sets,
+                                                 const GtPair* __restrict__ scratch, uint32_t* __restrict__ flags,
+                                                 size_t t) {
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  if (!fp12_eq(scratch[t].a, scratch[t].b)) atomicAnd(&flags[p], 0u);
+}
+
 // Item thread per (proof, i, j): e(c*Y_i - Zphi_j*B, V_ij) * e(B, g2)^Zv_ij == A_ij  (:540-549; the three
 // pairings of the reference collapse by bilinearity, the value compared is the same canonical GT element).
 __device__ __forceinline__ void rp_verify_item(const RpBatch& b, const RpSetDev* __restrict__ sets,
