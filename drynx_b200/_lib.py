@@ -22,6 +22,7 @@ SIGNATURES = {
     'drx_set_stream': (ctypes.c_int, [VP, VP]),
     'drx_synchronize': (ctypes.c_int, [VP]),
     'drx_launch_count': (ctypes.c_uint64, [VP]),
+    'drx_set_option': (ctypes.c_int, [VP, ctypes.c_char_p, ctypes.c_int]),
     'drx_profile_enable': (ctypes.c_int, [VP, ctypes.c_int]),
     'drx_profile_get': (ctypes.c_int, [VP, ctypes.c_char_p, c_dp, ctypes.POINTER(ctypes.c_uint64)]),
     'drx_reduce_rows_dev': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, ctypes.c_int, VP]),

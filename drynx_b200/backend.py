@@ -50,6 +50,9 @@ class Backend:
     def set_stream(self, cuda_stream):
         _lib.check(self.lib.drx_set_stream(self.h, ctypes.c_void_p(cuda_stream)))
 
+    def set_option(self, name, value):
+        _lib.check(self.lib.drx_set_option(self.h, name.encode(), int(value)))
+
     def synchronize(self):
         _lib.check(self.lib.drx_synchronize(self.h))
 

@@ -142,6 +142,7 @@ struct drx_ctx {
   std::mutex mu;
   uint64_t launches = 0;
   bool have_pub = false, have_dlog = false;
+  int opt_verify_path = 0;  // drx_set_option "rp_verify_path"
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
       sets_dev, sink;
   Arena arena;
@@ -313,6 +314,17 @@ int drx_synchronize(drx_ctx* c) {
   return 0;
 }
 uint64_t drx_launch_count(const drx_ctx* c) { return c ? c->launches : 0; }
+
+int drx_set_option(drx_ctx* c, const char* name, int value) {
+  if (!c || !name) return fail(-1, "null argument");
+  Guard g(c);
+  if (!strcmp(name, "rp_verify_path")) {
+    if (value < 0 || value > 2) return fail(-1, "rp_verify_path must be 0 (auto), 1 (thread per item) or 2 (lane groups)");
+    c->opt_verify_path = value;
+    return 0;
+  }
+  return fail(-1, "unknown option %s", name);
+}
 
 int drx_profile_enable(drx_ctx* c, int on) {
   if (!c) return fail(-1, "null context");

@@ -358,6 +358,29 @@ int launch_rp_verify_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_
   return 2;
 }
 
+// The GT factor alone (role 1) and the final comparison, used when the pairing runs in the cooperative kernel.
+__global__ void __launch_bounds__(64)
+k_rp_verify_gt(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __restrict__ tabB,
+               const Fp12* __restrict__ tabGtB, const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags,
+               GtPair* __restrict__ scratch) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= b.items) return;
+  rp_verify_role(b, sets, tabB, tabGtB, proofs, flags, scratch, t, 1);
+}
+int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                        const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch) {
+  if (!b.items) return 0;
+  k_rp_verify_gt<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const Fp12*)d_tabGtB,
+                                                      (const uint32_t*)d_proofs, d_flags, (GtPair*)d_scratch);
+  return 1;
+}
+int launch_rp_verify_finish(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_scratch,
+                            uint32_t* d_flags) {
+  if (!b.items) return 0;
+  k_rp_verify_finish<<<grid_for(b.items, 128), 128, 0, st>>>(b, d_sets, (const GtPair*)d_scratch, d_flags);
+  return 1;
+}
+
 int launch_rp_flags(cudaStream_t st, size_t n, const uint32_t* d_flags, uint8_t* d_ok) {
   if (!n) return 0;
   k_flags_to_bytes<<<grid_for(n, 256), 256, 0, st>>>(n, d_flags, d_ok);

@@ -14,6 +14,7 @@ constexpr size_t kG1AffBytes = 64, kG2AffBytes = 128, kGtBytes = 384, kG1JacByte
 constexpr int64_t kMaxHomomorphicInt = 100000;  // libunlynx.MaxHomomorphicInt
 constexpr uint32_t kDlogCap = 1u << 18;         // open-addressing slots for 100001 keys
 constexpr int kAggMaxSlices = 64;
+constexpr size_t kUcodeAutoMaxItems = 12288;  // batches up to this many pairing checks take the lane-group path
 
 // ---- kernels_g1.cu
 // wire bytes -> Montgomery affine (returns malformed count in *d_bad)
@@ -93,12 +94,20 @@ int launch_rp_create_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_
                            const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch);
 int launch_rp_verify_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                            const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
-// four lanes per item, for small batches (kernels_rp_coop.cu)
-constexpr size_t kCoopMaxItems = 0;  // off by default: measured no faster than one thread per item
-int launch_rp_verify_items_coop4(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
-                                 const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags);
-int launch_rp_create_items_coop4(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                                 const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
-                                 const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs);
-
+// cooperative lane-group pairing driven by a generated micro-program (kernels_rp_ucode.cu)
+size_t rp_ucode_prep_bytes(size_t items);
+int launch_rp_verify_pair_ucode(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                                const uint8_t* d_proofs, uint32_t* d_flags, void* d_prep, void* d_scratch);
+int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                        const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
+int launch_rp_verify_finish(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_scratch,
+                            uint32_t* d_flags);
+// role-split item kernels (independent parts of one item in different thread blocks) + their finish kernels;
+// d_scratch holds rp_scratch_bytes(items) bytes (two GT elements per item)
+size_t rp_scratch_bytes(size_t items);
+int launch_rp_create_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
+                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch);
+int launch_rp_verify_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                           const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 }  // namespace drx

@@ -1,6 +1,6 @@
-// Device-side range-proof logic shared by the one-thread-per-item kernels (kernels_rp.cu) and the four-lane
-// cooperative kernels for small batches (kernels_rp_coop.cu): proof layout, item location, and the bodies of the
-// creation and verification items. lib/range/range_proof.go:320-407 and :504-565.
+// Device-side range-proof logic shared by the one-thread-per-item kernels (kernels_rp.cu) and the cooperative
+// lane-group pairing (kernels_rp_ucode.cu): proof layout, item location, and the bodies of the creation and
+// verification items. lib/range/range_proof.go:320-407 and :504-565.
 #pragma once
 #include "launch.h"
 #include "keccak.cuh"

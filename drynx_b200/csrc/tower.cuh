@@ -45,52 +45,13 @@ DRX_FP2_ATTR Fp2 fp2_conj(const Fp2& a) { return Fp2{a.c0, fp_neg(a.c1)}; }
 DRX_HD bool fp2_is_zero(const Fp2& a) { return fp_is_zero(a.c0) & fp_is_zero(a.c1); }
 DRX_HD bool fp2_eq(const Fp2& a, const Fp2& b) { return fp_eq(a.c0, b.c0) & fp_eq(a.c1, b.c1); }
 DRX_HD Fp2 fp2_sel(bool c, const Fp2& a, const Fp2& b) { return Fp2{fp_sel(c, a.c0, b.c0), fp_sel(c, a.c1, b.c1)}; }
-#if defined(DRX_COOP4) && defined(__CUDA_ARCH__)
-DRX_NI Fp2 fp2_mul_fp(const Fp2& a, const Fp& k);  // defined with the cooperative products below
-#else
 DRX_FP2_ATTR Fp2 fp2_mul_fp(const Fp2& a, const Fp& k) { return Fp2{fp_mul_inl(a.c0, k), fp_mul_inl(a.c1, k)}; }
-#endif
 // (c0 + c1 i)(3 + i) = (3c0 - c1) + (c0 + 3c1) i
 DRX_FP2_ATTR Fp2 fp2_mul_xi(const Fp2& a) {
   const Fp t0 = fp_add(fp_dbl(a.c0), a.c0);
   const Fp t1 = fp_add(fp_dbl(a.c1), a.c1);
   return Fp2{fp_sub(t0, a.c1), fp_add(t1, a.c0)};
 }
-#if defined(DRX_COOP4) && defined(__CUDA_ARCH__)
-// Four-lane cooperative mode (kernels_rp_coop.cu): the four threads of an aligned lane quad work on ONE item and
-// hold identical copies of its state. Only the Fp2 products are split: each lane computes one of the four
-// schoolbook products a0b0, a1b1, a0b1, a1b0, and two butterfly exchanges rebuild the full result on all four
-// lanes. Everything else runs replicated, so control flow is identical inside a quad and the shuffles always
-// find their partners. Per lane an Fp2 product costs one Montgomery product instead of three.
-DRX_D uint32_t coop_lane() { return threadIdx.x & 3u; }
-DRX_D uint32_t coop_mask() { return 0xFu << (threadIdx.x & 28u); }
-DRX_D Fp fp_shfl_xor(const Fp& a, int m) {
-  Fp r;
-  const uint32_t mask = coop_mask();
-  DRX_UNROLL
-  for (int k = 0; k < 8; k++) r.v[k] = __shfl_xor_sync(mask, a.v[k], m);
-  return r;
-}
-DRX_NI Fp2 fp2_mul(const Fp2& a, const Fp2& b) {
-  const uint32_t l = coop_lane();
-  const bool odd = (l & 1u) != 0, lo = l < 2u;
-  const Fp x = fp_sel(odd, a.c1, a.c0);
-  const Fp y = fp_sel(((l ^ (l >> 1)) & 1u) != 0, b.c1, b.c0);
-  const Fp p = fp_mul_inl(x, y);  // lane 0: a0b0, 1: a1b1, 2: a0b1, 3: a1b0
-  const Fp q = fp_shfl_xor(p, 1);
-  const Fp u = fp_sel(odd, q, p), v = fp_sel(odd, p, q);
-  const Fp r = fp_add(u, fp_sel(lo, fp_neg(v), v));  // lanes 0,1: a0b0 - a1b1; lanes 2,3: a0b1 + a1b0
-  const Fp s = fp_shfl_xor(r, 2);
-  return Fp2{fp_sel(lo, r, s), fp_sel(lo, s, r)};
-}
-DRX_NI Fp2 fp2_sqr(const Fp2& a) { return fp2_mul(a, a); }
-DRX_NI Fp2 fp2_mul_fp(const Fp2& a, const Fp& k) {
-  const bool odd = (coop_lane() & 1u) != 0;
-  const Fp p = fp_mul_inl(fp_sel(odd, a.c1, a.c0), k);
-  const Fp q = fp_shfl_xor(p, 1);
-  return Fp2{fp_sel(odd, q, p), fp_sel(odd, p, q)};
-}
-#else
 DRX_NI Fp2 fp2_mul(const Fp2& a, const Fp2& b) {
   const Fp v0 = fp_mul_inl(a.c0, b.c0);
   const Fp v1 = fp_mul_inl(a.c1, b.c1);
@@ -102,7 +63,6 @@ DRX_NI Fp2 fp2_sqr(const Fp2& a) {
   const Fp c0 = fp_mul_inl(fp_add(a.c0, a.c1), fp_sub(a.c0, a.c1));
   return Fp2{c0, fp_dbl(t)};
 }
-#endif
 DRX_NI Fp2 fp2_inv(const Fp2& a) {
   const Fp d = fp_inv(fp_add(fp_sqr(a.c0), fp_sqr(a.c1)));
   return Fp2{fp_mul(a.c0, d), fp_neg(fp_mul(a.c1, d))};

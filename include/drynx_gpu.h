@@ -49,6 +49,10 @@ int drx_synchronize(drx_ctx* ctx);
 /* Number of kernel launches issued by this context so far (for the benchmark's gpu_launches field). */
 uint64_t drx_launch_count(const drx_ctx* ctx);
 
+/* Tuning knobs (no counterpart in the reference). "rp_verify_path": 0 = choose by batch size (default),
+ * 1 = one thread per pairing check, 2 = cooperative lane groups. Results are identical on every path. */
+int drx_set_option(drx_ctx* ctx, const char* name, int value);
+
 /* Per-kernel timing with CUDA events on the launching stream (bench.py's roofline leg): enable (which clears
  * the totals), run, then read the summed duration and launch count of a kernel by name (k_encrypt,
  * k_agg_partial, k_agg_final, k_decrypt, k_reduce_rows, k_rp_create_hdr, k_rp_create_items, k_rp_verify_hdr,

@@ -187,3 +187,31 @@ def test_config2_shape_create_verify_properties(backend, oracle, rng):
     bad[150 * size + size - 40] ^= 1  # last Zv
     ok = backend.verify_range_proofs(sids, [l] * n, bytes(bad), off)
     assert [i for i in range(n) if not ok[i]] == flipped
+
+
+@pytest.mark.parametrize('path', [1, 2])
+def test_both_verification_paths_match_oracle(backend, oracle, rng, path):
+    """rp_verify_path 1 (one thread per pairing check) and 2 (cooperative lane groups running the generated
+    micro-program) must give the oracle's accept / reject bits on valid, tampered and degenerate proofs."""
+    ns, u, l = 3, 16, 2
+    sk, P, Y, A = _setup(backend, oracle, rng, ns, u, set_id=60)
+    secrets = [0, 1, 77, 255, 200, 13, 99, 254]
+    rs, cts, rnd = _make(backend, oracle, rng, P, ns, u, l, secrets)
+    n = len(secrets)
+    proofs, off = backend.create_range_proofs([60] * n, {60: ns}, {60: u}, [l] * n, secrets, rs, cts, rnd)
+    size = int(off[1])
+    blk = 256 + 32 * l
+    bad = bytearray(proofs.tobytes())
+    bad[1 * size + 170] ^= 1                                  # Zr
+    bad[2 * size + blk + 128 * l + 5] ^= 1                    # A_00
+    bad[3 * size + blk + 544 * l + 128 * l + 384 + 100] ^= 1  # A_11
+    bad[4 * size + blk + 3] ^= 1                              # V_00 leaves the curve
+    bad[5 * size + blk:5 * size + blk + 128] = bytes(128)     # V_00 = infinity
+    bad[6 * size + blk + 512 * l + 9] ^= 1                    # Zv_00
+    want = oracle.rp_verify(ns, u, l, Y, P, bytes(bad), off, threads=8)
+    backend.set_option('rp_verify_path', path)
+    try:
+        ok = backend.verify_range_proofs([60] * n, [l] * n, bytes(bad), off)
+    finally:
+        backend.set_option('rp_verify_path', 0)
+    assert list(ok) == list(want) == [1, 0, 0, 0, 0, 0, 0, 1]

@@ -1,0 +1,532 @@
+#!/usr/bin/env python3
+"""Generates the lane-group micro-program for the optimal ate pairing (drynx_b200/csrc/pairing_ucode.inc).
+
+The cooperative pairing kernel (kernels_rp_ucode.cu) keeps ONE copy of an item's state as an array of Fp2 slots in
+shared memory and lets a group of G lanes execute a static schedule over it: every phase all lanes run the same
+Fp2 operation (MUL, ADD, ...) on their own (dst, a, b) slots. This script
+
+  1. traces the pairing (the same formulas as csrc/tower.cuh / pairing.cuh) on symbolic Fp2 values into a DAG,
+  2. list-schedules the DAG onto G lanes, one opcode per phase, and allocates slots by liveness,
+  3. EXECUTES the emitted program with Python integers and checks it against oracle/bn256_ref.pair, and
+  4. writes the tables as a C include.
+
+Nothing here is copied from the reference; the formulas are the ones already used and tested in this repo.
+"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+import bn256_ref as R  # noqa: E402
+
+# ---------------------------------------------------------------------------------------------- symbolic Fp2 DAG
+OPS = ['NOP', 'MUL', 'ADD', 'SUB', 'DBL', 'NEG', 'MULXI', 'CONJ', 'MULC', 'MULFP0', 'MULFP1', 'INV', 'COPY', 'CONJMULC', 'MULFPC']
+OPC = {n: i for i, n in enumerate(OPS)}
+COST = {'MUL': 10, 'INV': 120, 'MULC': 10, 'CONJMULC': 10, 'MULFP0': 7, 'MULFP1': 7, 'MULFPC': 7}
+
+
+class Node:
+    __slots__ = ('op', 'a', 'b', 'imm', 'id', 'users', 'name', 'prio', 'slot', 'phase')
+
+    def __init__(self, g, op, a=None, b=None, imm=0, name=None):
+        self.op, self.a, self.b, self.imm, self.name = op, a, b, imm, name
+        self.id = len(g.nodes)
+        self.users = []
+        self.slot = None
+        self.phase = None
+        g.nodes.append(self)
+        for x in (a, b):
+            if x is not None:
+                x.users.append(self)
+
+
+class Graph:
+    def __init__(self):
+        self.nodes = []
+        self.inputs = {}
+        self.outputs = {}
+        self.consts2 = []   # Fp2 constants (c0, c1)
+        self.constsp = []   # Fp constants
+
+    def inp(self, name):
+        n = Node(self, 'IN', name=name)
+        self.inputs[name] = n
+        return n
+
+    def out(self, name, node):
+        self.outputs[name] = node
+
+    def c2(self, val):
+        if val not in self.consts2:
+            self.consts2.append(val)
+        return self.consts2.index(val)
+
+    def cp(self, val):
+        if val not in self.constsp:
+            self.constsp.append(val)
+        return self.constsp.index(val)
+
+
+class S:
+    """Symbolic Fp2 value."""
+
+    def __init__(self, g, n):
+        self.g, self.n = g, n
+
+    def _bin(self, op, o):
+        return S(self.g, Node(self.g, op, self.n, o.n))
+
+    def _un(self, op, imm=0):
+        return S(self.g, Node(self.g, op, self.n, None, imm))
+
+    def __mul__(self, o): return self._bin('MUL', o)
+    def __add__(self, o): return self._bin('ADD', o)
+    def __sub__(self, o): return self._bin('SUB', o)
+    def sqr(self): return self._bin('MUL', self)
+    def dbl(self): return self._bin('ADD', self)            # same opcode as ADD: fuller phases
+    def neg(self): return S(self.g, Node(self.g, 'SUB', self.g.inputs['ZERO'], self.n))
+    def xi(self): return self._un('MULXI')
+    def conj(self): return self._un('CONJ')
+    def inv(self): return self._un('INV')
+    def mulc(self, val): return self._un('MULC', self.g.c2(val))
+    def conjmulc(self, val): return self._un('CONJMULC', self.g.c2(val))
+    def mulfpc(self, val): return self._un('MULFPC', self.g.cp(val))
+    def mulfp(self, pt, which): return S(self.g, Node(self.g, 'MULFP%d' % which, self.n, pt.n))
+
+
+# ---------------------------------------------------------------------------------------------- tower formulas
+def f6_add(a, b): return [a[i] + b[i] for i in range(3)]
+def f6_sub(a, b): return [a[i] - b[i] for i in range(3)]
+def f6_mul_tau(a): return [a[2].xi(), a[0], a[1]]
+
+
+def f6_mul(a, b):
+    v0, v1, v2 = a[0] * b[0], a[1] * b[1], a[2] * b[2]
+    t0 = (a[1] + a[2]) * (b[1] + b[2]) - v1 - v2
+    t1 = (a[0] + a[1]) * (b[0] + b[1]) - v0 - v1
+    t2 = (a[0] + a[2]) * (b[0] + b[2]) - v0 - v2
+    return [v0 + t0.xi(), t1 + v2.xi(), t2 + v1]
+
+
+def f6_mul_fp2(a, k): return [a[0] * k, a[1] * k, a[2] * k]
+
+
+def f6_mul_01(a, b0, b1):
+    v0, v1 = a[0] * b0, a[1] * b1
+    t = (a[0] + a[1]) * (b0 + b1) - v0 - v1
+    return [v0 + (a[2] * b1).xi(), t, v1 + a[2] * b0]
+
+
+def f12_mul(a, b):  # a = (c0[3], c1[3])
+    v0, v1 = f6_mul(a[0], b[0]), f6_mul(a[1], b[1])
+    t = f6_mul(f6_add(a[0], a[1]), f6_add(b[0], b[1]))
+    return (f6_add(v0, f6_mul_tau(v1)), f6_sub(f6_sub(t, v0), v1))
+
+
+def f12_sqr(a):
+    v = f6_mul(a[0], a[1])
+    t = f6_mul(f6_add(a[0], a[1]), f6_add(a[0], f6_mul_tau(a[1])))
+    return (f6_sub(f6_sub(t, v), f6_mul_tau(v)), [x.dbl() for x in v])
+
+
+def f12_mul_line(a, l0, l1, l3):
+    t0 = f6_mul_fp2(a[0], l0)
+    t1 = f6_mul_01(a[1], l1, l3)
+    t2 = f6_mul_01(f6_add(a[0], a[1]), l0 + l1, l3)
+    return (f6_add(t0, f6_mul_tau(t1)), f6_sub(f6_sub(t2, t0), t1))
+
+
+def f4_sqr(a, b):
+    a2, b2 = a.sqr(), b.sqr()
+    return a2 + b2.xi(), (a + b).sqr() - a2 - b2
+
+
+def f12_cyclo_sqr(a):
+    g0, g1, g2, g3, g4, g5 = a[0][0], a[1][0], a[0][1], a[1][1], a[0][2], a[1][2]
+    t00, t01 = f4_sqr(g0, g3)
+    t10, t11 = f4_sqr(g1, g4)
+    t20, t21 = f4_sqr(g2, g5)
+    x = t21.xi()
+    c00 = (t00 - g0).dbl() + t00
+    c11 = (t01 + g3).dbl() + t01
+    c01 = (t10 - g2).dbl() + t10
+    c12 = (t11 + g5).dbl() + t11
+    c02 = (t20 - g4).dbl() + t20
+    c10 = (x + g1).dbl() + x
+    return ([c00, c01, c02], [c10, c11, c12])
+
+
+def f12_conj(a): return (a[0], [x.neg() for x in a[1]])
+
+
+def f6_sqr(a):
+    s0 = a[0].sqr()
+    s1 = (a[0] * a[1]).dbl()
+    s2 = (a[0] - a[1] + a[2]).sqr()
+    s3 = (a[1] * a[2]).dbl()
+    s4 = a[2].sqr()
+    return [s0 + s3.xi(), s1 + s4.xi(), s1 + s2 + s3 - s0 - s4]
+
+
+def f6_inv(a):
+    A = a[0].sqr() - (a[1] * a[2]).xi()
+    B = a[2].sqr().xi() - a[0] * a[1]
+    C = a[1].sqr() - a[0] * a[2]
+    F = ((a[2] * B + a[1] * C).xi() + a[0] * A).inv()
+    return [A * F, B * F, C * F]
+
+
+def f12_inv(a):
+    t = f6_inv(f6_sub(f6_sqr(a[0]), f6_mul_tau(f6_sqr(a[1]))))
+    return (f6_mul(a[0], t), [x.neg() for x in f6_mul(a[1], t)])
+
+
+def frob_consts(e):
+    xi = R.XI
+    return [R.f2pow(xi, k * (R.p ** e - 1) // 6) for k in range(6)]
+
+
+def f12_frob(a, e):
+    g = frob_consts(e)
+    w = [a[0][0], a[1][0], a[0][1], a[1][1], a[0][2], a[1][2]]
+    out = []
+    for k in range(6):
+        if e % 2 == 1:
+            out.append(w[k].conj() if k == 0 else w[k].conjmulc(g[k]))
+        else:
+            out.append(w[k] if k == 0 else w[k].mulfpc(g[k][0]))
+    return ([out[0], out[2], out[4]], [out[1], out[3], out[5]])
+
+
+def line_dbl(r, P):
+    x, y, z, t = r
+    A, B = x.sqr(), y.sqr()
+    C = B.sqr()
+    D = ((x + B).sqr() - A - C).dbl()
+    E = A.dbl() + A
+    G = E.sqr()
+    ox = G - D - D
+    oz = (y + z).sqr() - B - t
+    oy = (D - ox) * E - C.dbl().dbl().dbl()
+    ot = oz.sqr()
+    b = (E * t).dbl().neg().mulfp(P, 0)
+    a = (x + E).sqr() - A - G - B.dbl().dbl()
+    c = (oz * t).dbl().mulfp(P, 1)
+    return (ox, oy, oz, ot), (a, b, c)
+
+
+def line_add(r, q, r2, P):
+    x, y, z, t = r
+    B = q[0] * t
+    D = ((q[1] + z).sqr() - r2 - t) * t
+    H = B - x
+    I = H.sqr()
+    E = I.dbl().dbl()
+    J = H * E
+    L1 = D - y - y
+    V = x * E
+    ox = L1.sqr() - J - V - V
+    oz = (z + H).sqr() - t - I
+    oy = (V - ox) * L1 - (y * J).dbl()
+    ot = oz.sqr()
+    tt = (q[1] + oz).sqr() - r2 - ot
+    a = (L1 * q[0]).dbl() - tt
+    c = oz.mulfp(P, 1).dbl()
+    b = L1.neg().mulfp(P, 0).dbl()
+    return (ox, oy, oz, ot), (a, b, c)
+
+
+def naf(x):
+    d = []
+    while x:
+        if x & 1:
+            z = 2 - (x & 3)
+            x -= z
+        else:
+            z = 0
+        d.append(z)
+        x >>= 1
+    return d
+
+
+def f12_pow_u(a):
+    digits = naf(R.u)
+    acc = a
+    inv = f12_conj(a)
+    for i in range(len(digits) - 2, -1, -1):
+        acc = f12_cyclo_sqr(acc)
+        if digits[i] > 0:
+            acc = f12_mul(acc, a)
+        elif digits[i] < 0:
+            acc = f12_mul(acc, inv)
+    return acc
+
+
+def final_exp(f):
+    a = f12_mul(f12_conj(f), f12_inv(f))
+    a = f12_mul(a, f12_frob(a, 2))
+    fu = f12_pow_u(a)
+    fu2 = f12_pow_u(fu)
+    fu3 = f12_pow_u(fu2)
+    y6 = f12_conj(f12_mul(f12_frob(fu3, 1), fu3))
+    y4 = f12_conj(f12_mul(f12_frob(fu2, 1), fu))
+    y5 = f12_conj(fu2)
+    t0 = f12_mul(f12_mul(f12_cyclo_sqr(y6), y4), y5)
+    y3 = f12_conj(f12_frob(fu, 1))
+    t1 = f12_mul(f12_mul(y3, y5), t0)
+    t0 = f12_mul(t0, f12_frob(fu2, 2))
+    t1 = f12_cyclo_sqr(f12_mul(f12_cyclo_sqr(t1), t0))
+    t0 = f12_mul(t1, f12_conj(a))
+    y0 = f12_mul(f12_mul(f12_frob(a, 1), f12_frob(a, 2)), f12_frob(a, 3))
+    t1 = f12_mul(t1, y0)
+    return f12_mul(f12_cyclo_sqr(t0), t1)
+
+
+def build_pairing(g):
+    """Inputs: P (one slot: c0 = x, c1 = y), QX, QY, ONE. Output: 6 Fp2 of e(P, Q) in w-power order pairs."""
+    P, qx, qy, one, zero = (S(g, g.inp(n)) for n in ('P', 'QX', 'QY', 'ONE', 'ZERO'))
+    mqy = qy.neg()
+    r = (qx, qy, one, one)
+    r2 = qy.sqr()
+    f = ([one, zero, zero], [zero, zero, zero])
+    digits = naf(6 * R.u + 2)
+    L = len(digits)
+    first = True
+    for i in range(L - 1, 0, -1):
+        r, (a, b, c) = line_dbl(r, P)
+        if first:
+            # f = 1: the first line is f itself (c + b w + a w^3)
+            f = ([c, zero, zero], [b, a, zero])
+            first = False
+        else:
+            f = f12_mul_line(f12_sqr(f), c, b, a)
+        d = digits[i - 1]
+        if d:
+            r, (a, b, c) = line_add(r, (qx, qy if d > 0 else mqy), r2, P)
+            f = f12_mul_line(f, c, b, a)
+    q1 = (qx.conjmulc(R.XI_P_1_3), qy.conjmulc(R.XI_P_1_2))
+    mq2 = (qx.mulfpc(R.f2pow(R.XI, (R.p * R.p - 1) // 3)[0]), qy)
+    r, (a, b, c) = line_add(r, q1, q1[1].sqr(), P)
+    f = f12_mul_line(f, c, b, a)
+    r, (a, b, c) = line_add(r, mq2, mq2[1].sqr(), P)
+    f = f12_mul_line(f, c, b, a)
+    e = final_exp(f)
+    names = ['E00', 'E01', 'E02', 'E10', 'E11', 'E12']
+    vals = e[0] + e[1]
+    for n, v in zip(names, vals):
+        g.out(n, v.n)
+
+
+# ---------------------------------------------------------------------------------------------- evaluation
+def eval_node(n, val, g, P):
+    a = val[n.a.id] if n.a is not None else None
+    b = val[n.b.id] if n.b is not None else None
+    op = n.op
+    if op == 'MUL': return R.f2mul(a, b)
+    if op == 'ADD': return R.f2add(a, b)
+    if op == 'SUB': return R.f2sub(a, b)
+    if op == 'DBL': return R.f2add(a, a)
+    if op == 'NEG': return R.f2neg(a)
+    if op == 'MULXI': return R.f2mul(a, R.XI)
+    if op == 'CONJ': return R.f2conj(a)
+    if op == 'MULC': return R.f2mul(a, g.consts2[n.imm])
+    if op == 'CONJMULC': return R.f2mul(R.f2conj(a), g.consts2[n.imm])
+    if op == 'MULFPC': return R.f2scal(a, g.constsp[n.imm])
+    if op == 'MULFP0': return R.f2scal(a, b[0])
+    if op == 'MULFP1': return R.f2scal(a, b[1])
+    if op == 'INV': return R.f2inv(a)
+    if op == 'COPY': return a
+    raise ValueError(op)
+
+
+# ---------------------------------------------------------------------------------------------- scheduling
+def schedule(g, G, nslots, window=96):
+    nodes = [n for n in g.nodes]
+    # dead-code elimination from outputs
+    live = set()
+    stack = [n for n in g.outputs.values()]
+    while stack:
+        n = stack.pop()
+        if n.id in live:
+            continue
+        live.add(n.id)
+        for x in (n.a, n.b):
+            if x is not None:
+                stack.append(x)
+    ops = [n for n in nodes if n.id in live and n.op != 'IN']
+    # critical-path priority
+    prio = {}
+    for n in reversed(nodes):
+        if n.id not in live:
+            continue
+        best = 0
+        for u_ in n.users:
+            if u_.id in live:
+                best = max(best, prio[u_.id])
+        prio[n.id] = best + COST.get(n.op, 1)
+    remaining_users = {n.id: sum(1 for u_ in n.users if u_.id in live) for n in nodes if n.id in live}
+    out_ids = set(n.id for n in g.outputs.values())
+    # slots: inputs pinned first
+    slot_of = {}
+    free = list(range(nslots - 1, -1, -1))
+    for name, n in g.inputs.items():
+        slot_of[n.id] = free.pop()
+    done = set(n.id for n in g.inputs.values())
+    pending = {n.id: n for n in ops}
+    phases = []
+    max_used = len(slot_of)
+    while pending:
+        lo = min(pending)  # ids are in trace order: only look `window` ops ahead so the live set stays small
+        ready = [n for i, n in pending.items() if i < lo + window and all(x is None or x.id in done for x in (n.a, n.b))]
+        by_op = {}
+        for n in ready:
+            by_op.setdefault(n.op, []).append(n)
+        # choose the opcode whose best-G ready ops carry the most critical work
+        mul_ops = [o for o in by_op if o in COST]
+        lin_ops = [o for o in by_op if o not in COST]
+        full_mul = [o for o in mul_ops if len(by_op[o]) >= G]
+        if full_mul:          # a full multiplication phase is always worth issuing
+            op = max(full_mul, key=lambda o: max(prio[n.id] for n in by_op[o]))
+        elif lin_ops:         # otherwise drain the cheap linear ops first: they unlock further products
+            op = max(lin_ops, key=lambda o: (len(by_op[o]) >= G, max(prio[n.id] for n in by_op[o]), len(by_op[o])))
+        else:
+            op = max(mul_ops, key=lambda o: (len(by_op[o]), max(prio[n.id] for n in by_op[o])))
+        chosen = sorted(by_op[op], key=lambda n: -prio[n.id])[:G]
+        lanes = []
+        to_free = []
+        for n in chosen:
+            if not free:
+                raise RuntimeError('out of slots (%d)' % nslots)
+            s = free.pop()
+            slot_of[n.id] = s
+            max_used = max(max_used, nslots - len(free))
+            lanes.append(n)
+            for x in set(y for y in (n.a, n.b) if y is not None):
+                remaining_users[x.id] -= sum(1 for y in (n.a, n.b) if y is x) if False else 1
+                if remaining_users[x.id] == 0 and x.id not in out_ids and x.op != 'IN':
+                    to_free.append(slot_of[x.id])
+        phases.append((op, lanes))
+        for n in chosen:
+            done.add(n.id)
+            del pending[n.id]
+        for s in to_free:   # reusable from the next phase on (no write-after-read inside a phase)
+            free.append(s)
+    return phases, slot_of, max_used
+
+
+def fix_user_counts(g):
+    """A node used twice by the same consumer (a*a) must count once per consumer."""
+    for n in g.nodes:
+        seen = []
+        for u_ in n.users:
+            if u_ not in seen:
+                seen.append(u_)
+        n.users = seen
+
+
+def run_program(g, phases, slot_of, nslots, inputs):
+    slots = [None] * nslots
+    for name, n in g.inputs.items():
+        slots[slot_of[n.id]] = inputs[name]
+    P = inputs['P']
+    for op, lanes in phases:
+        reads = []
+        for n in lanes:
+            a = slots[slot_of[n.a.id]] if n.a is not None else None
+            b = slots[slot_of[n.b.id]] if n.b is not None else None
+            reads.append((a, b))
+        writes = []
+        for n, (a, b) in zip(lanes, reads):
+            class V:  # minimal adapter for eval_node
+                pass
+            val = {}
+            if n.a is not None:
+                val[n.a.id] = a
+            if n.b is not None:
+                val[n.b.id] = b
+            writes.append((slot_of[n.id], eval_node(n, val, g, P)))
+        for s, v in writes:
+            slots[s] = v
+    return {name: slots[slot_of[n.id]] for name, n in g.outputs.items()}
+
+
+def main():
+    G = int(sys.argv[1]) if len(sys.argv) > 1 else 4
+    nslots = int(sys.argv[2]) if len(sys.argv) > 2 else 96
+    window = int(sys.argv[3]) if len(sys.argv) > 3 else 96
+    g = Graph()
+    build_pairing(g)
+    fix_user_counts(g)
+    phases, slot_of, used = schedule(g, G, nslots, window)
+    nops = sum(len(l) for _, l in phases)
+    nmul = sum(len(l) for o, l in phases if o in COST)
+    mulph = sum(1 for o, _ in phases if o in COST)
+    print('G=%d: %d ops (%d mul-class) in %d phases (%d mul-class phases), %d slots used' % (G, nops, nmul, len(phases), mulph, used))
+    print('mul-class lane utilisation %.2f' % (nmul / (mulph * G)))
+    # execute and compare with the definition
+    import random
+    rng = random.Random(5)
+    for _ in range(1 if '--quick' in sys.argv else 2):
+        a, b = rng.randrange(1, R.n), rng.randrange(1, R.n)
+        Pp, Q = R.g1_mul(a, R.G1_GEN), R.g2_mul(b, R.G2_GEN)
+        out = run_program(g, phases, slot_of, nslots, {'P': (Pp[0], Pp[1]), 'QX': Q[0], 'QY': Q[1], 'ONE': (1, 0), 'ZERO': (0, 0)})
+        e = R.pair(Pp, Q)
+        got = [out['E00'], out['E10'], out['E01'], out['E11'], out['E02'], out['E12']]
+        assert got == e, 'micro-program disagrees with the definition'
+    print('micro-program == bn256_ref.pair on random inputs')
+    if '--emit' in sys.argv:
+        emit(g, phases, slot_of, used, G)
+    return g, phases, slot_of, used, G
+
+
+def limbs(x):
+    return ', '.join('0x%08xu' % ((x >> (32 * k)) & 0xffffffff) for k in range(8))
+
+
+def mont(x):
+    return (x % R.p) * (1 << 256) % R.p
+
+
+def emit(g, phases, slot_of, used, G):
+    path = os.path.join(ROOT, 'drynx_b200', 'csrc', 'pairing_ucode.inc')
+    with open(path, 'w') as f:
+        f.write('// GENERATED by tools/microcode/gen.py %d %d ... --emit -- do not edit.\n' % (G, used))
+        f.write('// Lane-group micro-program of the optimal ate pairing: %d Fp2 operations in %d phases for %d lanes,\n'
+                % (sum(len(l) for _, l in phases), len(phases), G))
+        f.write('// %d Fp2 slots per item. Checked against oracle/bn256_ref.pair by the generator before emission.\n' % used)
+        f.write('#define UC_G %d\n#define UC_NSLOTS %d\n#define UC_NPHASES %d\n' % (G, used, len(phases)))
+        for i, name in enumerate(OPS):
+            f.write('#define UC_%s %d\n' % (name, i))
+        for name, n in g.inputs.items():
+            f.write('#define UC_IN_%s %d\n' % (name, slot_of[n.id]))
+        for name, n in g.outputs.items():
+            f.write('#define UC_OUT_%s %d\n' % (name, slot_of[n.id]))
+        f.write('__device__ const uint32_t uc_const2[%d][16] = {\n' % max(1, len(g.consts2)))
+        for c in g.consts2:
+            f.write('  {%s, %s},\n' % (limbs(mont(c[0])), limbs(mont(c[1]))))
+        f.write('};\n__device__ const uint32_t uc_constp[%d][8] = {\n' % max(1, len(g.constsp)))
+        for c in g.constsp:
+            f.write('  {%s},\n' % limbs(mont(c)))
+        f.write('};\n__device__ const uint8_t uc_ops[UC_NPHASES] = {\n')
+        for k in range(0, len(phases), 32):
+            f.write('  ' + ', '.join(str(OPC[o]) for o, _ in phases[k:k + 32]) + ',\n')
+        f.write('};\n// per lane: dst | a << 10 | b << 20 | active << 31 (b = constant index for MULC / CONJMULC / MULFPC)\n')
+        f.write('__device__ const uint32_t uc_lanes[UC_NPHASES * UC_G] = {\n')
+        for op, lanes in phases:
+            words = []
+            for k in range(G):
+                if k < len(lanes):
+                    n = lanes[k]
+                    a = slot_of[n.a.id] if n.a is not None else 0
+                    b = slot_of[n.b.id] if n.b is not None else n.imm
+                    assert slot_of[n.id] < 1024 and a < 1024 and b < 1024
+                    words.append('0x%08xu' % (slot_of[n.id] | a << 10 | b << 20 | 1 << 31))
+                else:
+                    words.append('0u')
+            f.write('  ' + ', '.join(words) + ',\n')
+        f.write('};\n')
+    print('wrote', path, os.path.getsize(path), 'bytes')
+
+
+if __name__ == '__main__':
+    main()
