@@ -6,6 +6,7 @@
 // (DESIGN.md section 5). Replaces kyber pairing/bn256 optate.go for lib/range/range_proof.go:540-544.
 #include <cstdlib>
 
+#define DRX_FP2_INLINE_MUL 1
 #include "rp_device.cuh"
 
 namespace drx {
@@ -51,9 +52,10 @@ k_rp_verify_prep(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __re
 
 // ---- Fp2 operations on register values (products go through the shared out-of-line fp_mul)
 __device__ __forceinline__ Fp2 uc_mul(const Fp2& a, const Fp2& b) {
-  const Fp v0 = fp_mul(a.c0, b.c0);
-  const Fp v1 = fp_mul(a.c1, b.c1);
-  const Fp s = fp_mul(fp_add(a.c0, a.c1), fp_add(b.c0, b.c1));
+  // the three products are inlined here (and only here) so that ptxas interleaves their carry chains
+  const Fp v0 = fp_mul_inl(a.c0, b.c0);
+  const Fp v1 = fp_mul_inl(a.c1, b.c1);
+  const Fp s = fp_mul_inl(fp_add(a.c0, a.c1), fp_add(b.c0, b.c1));
   return Fp2{fp_sub(v0, v1), fp_sub(fp_sub(s, v0), v1)};
 }
 __device__ __forceinline__ Fp2 uc_add(const Fp2& a, const Fp2& b) { return Fp2{fp_add(a.c0, b.c0), fp_add(a.c1, b.c1)}; }
@@ -79,6 +81,31 @@ __device__ __forceinline__ Fp uc_constp_(uint32_t k) {
   return r;
 }
 
+// Shared-memory slot access. A slot is 64 bytes = four 16-byte chunks; logical chunk c of slot s lives at physical
+// chunk (c + s) & 3, and the per-item slot count is odd. A 128-bit shared load is served a quarter-warp (two lane
+// groups) at a time: the two groups run the same micro-instruction, so lane l of both reads the same slot number,
+// which lands in opposite bank halves (odd stride), and inside a group the generator keeps the slots touched
+// together distinct mod 4, so the eight 16-byte accesses hit eight different bank groups.
+__device__ __forceinline__ Fp2 uc_load(const Fp2* S, uint32_t s) {
+  const uint4* base = reinterpret_cast<const uint4*>(S + s);
+  Fp2 r;
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    const uint4 v = base[(c + s) & 3u];
+    uint32_t* dst = c < 2 ? &r.c0.v[4 * c] : &r.c1.v[4 * (c - 2)];
+    dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+  }
+  return r;
+}
+__device__ __forceinline__ void uc_store(Fp2* S, uint32_t s, const Fp2& r) {
+  uint4* base = reinterpret_cast<uint4*>(S + s);
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    const uint32_t* src = c < 2 ? &r.c0.v[4 * c] : &r.c1.v[4 * (c - 2)];
+    base[(c + s) & 3u] = make_uint4(src[0], src[1], src[2], src[3]);
+  }
+}
+
 #define UC_ITEMS_PER_BLOCK (64 / UC_G)
 
 __global__ void __launch_bounds__(64)
@@ -90,11 +117,11 @@ k_pair_ucode(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__
   const bool alive = t < items && prep[t].state == 0;
   Fp2* S = slots + grp * UC_NSLOTS;
   if (alive && lane == 0) {
-    S[UC_IN_P] = Fp2{prep[t].P.x, prep[t].P.y};
-    S[UC_IN_QX] = prep[t].V.x;
-    S[UC_IN_QY] = prep[t].V.y;
-    S[UC_IN_ONE] = fp2_one();
-    S[UC_IN_ZERO] = fp2_zero();
+    uc_store(S, UC_IN_P, Fp2{prep[t].P.x, prep[t].P.y});
+    uc_store(S, UC_IN_QX, prep[t].V.x);
+    uc_store(S, UC_IN_QY, prep[t].V.y);
+    uc_store(S, UC_IN_ONE, fp2_one());
+    uc_store(S, UC_IN_ZERO, fp2_zero());
   }
   __syncwarp();
   uint32_t op = uc_ops[0], w = uc_lanes[lane];
@@ -104,12 +131,12 @@ k_pair_ucode(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__
     const uint32_t op_n = uc_ops[nx], w_n = uc_lanes[nx * UC_G + lane];
     if (alive && (w >> 31)) {
       const uint32_t d = w & 1023u, ia = (w >> 10) & 1023u, ib = (w >> 20) & 1023u;
-      const Fp2 a = S[ia];
+      const Fp2 a = uc_load(S, ia);
       Fp2 r;
       switch (op) {
-        case UC_MUL: r = uc_mul(a, S[ib]); break;
-        case UC_ADD: r = uc_add(a, S[ib]); break;
-        case UC_SUB: r = uc_sub(a, S[ib]); break;
+        case UC_MUL: r = uc_mul(a, uc_load(S, ib)); break;
+        case UC_ADD: r = uc_add(a, uc_load(S, ib)); break;
+        case UC_SUB: r = uc_sub(a, uc_load(S, ib)); break;
         case UC_MULXI: r = uc_xi(a); break;
         case UC_CONJ: r = Fp2{a.c0, fp_neg(a.c1)}; break;
         case UC_MULC: r = uc_mul(a, uc_load_const2(ib)); break;
@@ -120,19 +147,19 @@ k_pair_ucode(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__
           break;
         }
         case UC_MULFP0: {
-          const Fp k = S[ib].c0;
+          const Fp k = uc_load(S, ib).c0;
           r = Fp2{fp_mul(a.c0, k), fp_mul(a.c1, k)};
           break;
         }
         case UC_MULFP1: {
-          const Fp k = S[ib].c1;
+          const Fp k = uc_load(S, ib).c1;
           r = Fp2{fp_mul(a.c0, k), fp_mul(a.c1, k)};
           break;
         }
         case UC_INV: r = fp2_inv(a); break;
         default: r = a; break;  // UC_COPY
       }
-      S[d] = r;
+      uc_store(S, d, r);
     }
     __syncwarp();
     op = op_n;
@@ -141,12 +168,12 @@ k_pair_ucode(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__
   if (t < items && lane == 0) {
     Fp12 e = fp12_one();
     if (alive) {
-      e.c0.c0 = S[UC_OUT_E00];
-      e.c0.c1 = S[UC_OUT_E01];
-      e.c0.c2 = S[UC_OUT_E02];
-      e.c1.c0 = S[UC_OUT_E10];
-      e.c1.c1 = S[UC_OUT_E11];
-      e.c1.c2 = S[UC_OUT_E12];
+      e.c0.c0 = uc_load(S, UC_OUT_E00);
+      e.c0.c1 = uc_load(S, UC_OUT_E01);
+      e.c0.c2 = uc_load(S, UC_OUT_E02);
+      e.c1.c0 = uc_load(S, UC_OUT_E10);
+      e.c1.c1 = uc_load(S, UC_OUT_E11);
+      e.c1.c2 = uc_load(S, UC_OUT_E12);
     }
     scratch[t].a = e;
   }

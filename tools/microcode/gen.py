@@ -392,17 +392,47 @@ def schedule(g, G, nslots, window=96):
         else:
             op = max(mul_ops, key=lambda o: (len(by_op[o]), max(prio[n.id] for n in by_op[o])))
         chosen = sorted(by_op[op], key=lambda n: -prio[n.id])[:G]
+        # shared-memory banks: a slot's 16-byte chunks are rotated by (slot & 3), so the four lanes of a group are
+        # conflict-free when the slots they touch at the same time differ mod 4. Pick the lane order that spreads the
+        # operand slots best, then give every lane a destination slot of its own class when one is free.
+        import itertools
+
+        def conflicts(order):
+            c = 0
+            for sel in ('a', 'b'):
+                seen = {}
+                for n in order:
+                    if n is None:
+                        continue
+                    x = getattr(n, sel)
+                    if x is None or (sel == 'b' and n.op in ('MULC', 'CONJMULC', 'MULFPC')):
+                        continue
+                    k = slot_of[x.id] & 3
+                    seen[k] = seen.get(k, 0) + 1
+                c += sum(v - 1 for v in seen.values())
+            return c
+        padded = chosen + [None] * (G - len(chosen))
+        if G <= 4:
+            padded = list(min(itertools.permutations(padded), key=conflicts))
         lanes = []
         to_free = []
-        for n in chosen:
+        for lane_id, n in enumerate(padded):
+            if n is None:
+                lanes.append(None)
+                continue
             if not free:
                 raise RuntimeError('out of slots (%d)' % nslots)
-            s = free.pop()
+            pick = None
+            for idx in range(len(free) - 1, -1, -1):
+                if free[idx] & 3 == lane_id & 3:
+                    pick = idx
+                    break
+            s = free.pop(pick if pick is not None else -1)
             slot_of[n.id] = s
-            max_used = max(max_used, nslots - len(free))
+            max_used = max(max_used, max(slot_of.values()) + 1)
             lanes.append(n)
             for x in set(y for y in (n.a, n.b) if y is not None):
-                remaining_users[x.id] -= sum(1 for y in (n.a, n.b) if y is x) if False else 1
+                remaining_users[x.id] -= 1
                 if remaining_users[x.id] == 0 and x.id not in out_ids and x.op != 'IN':
                     to_free.append(slot_of[x.id])
         phases.append((op, lanes))
@@ -430,6 +460,7 @@ def run_program(g, phases, slot_of, nslots, inputs):
         slots[slot_of[n.id]] = inputs[name]
     P = inputs['P']
     for op, lanes in phases:
+        lanes = [n for n in lanes if n is not None]
         reads = []
         for n in lanes:
             a = slots[slot_of[n.a.id]] if n.a is not None else None
@@ -458,8 +489,9 @@ def main():
     build_pairing(g)
     fix_user_counts(g)
     phases, slot_of, used = schedule(g, G, nslots, window)
-    nops = sum(len(l) for _, l in phases)
-    nmul = sum(len(l) for o, l in phases if o in COST)
+    cnt = lambda l: sum(1 for n in l if n is not None)
+    nops = sum(cnt(l) for _, l in phases)
+    nmul = sum(cnt(l) for o, l in phases if o in COST)
     mulph = sum(1 for o, _ in phases if o in COST)
     print('G=%d: %d ops (%d mul-class) in %d phases (%d mul-class phases), %d slots used' % (G, nops, nmul, len(phases), mulph, used))
     print('mul-class lane utilisation %.2f' % (nmul / (mulph * G)))
@@ -492,8 +524,9 @@ def emit(g, phases, slot_of, used, G):
     with open(path, 'w') as f:
         f.write('// GENERATED by tools/microcode/gen.py %d %d ... --emit -- do not edit.\n' % (G, used))
         f.write('// Lane-group micro-program of the optimal ate pairing: %d Fp2 operations in %d phases for %d lanes,\n'
-                % (sum(len(l) for _, l in phases), len(phases), G))
+                % (sum(1 for _, l in phases for n in l if n is not None), len(phases), G))
         f.write('// %d Fp2 slots per item. Checked against oracle/bn256_ref.pair by the generator before emission.\n' % used)
+        used |= 1  # odd slot count per item: adjacent lane groups then sit in opposite bank halves
         f.write('#define UC_G %d\n#define UC_NSLOTS %d\n#define UC_NPHASES %d\n' % (G, used, len(phases)))
         for i, name in enumerate(OPS):
             f.write('#define UC_%s %d\n' % (name, i))
@@ -515,7 +548,7 @@ def emit(g, phases, slot_of, used, G):
         for op, lanes in phases:
             words = []
             for k in range(G):
-                if k < len(lanes):
+                if k < len(lanes) and lanes[k] is not None:
                     n = lanes[k]
                     a = slot_of[n.a.id] if n.a is not None else 0
                     b = slot_of[n.b.id] if n.b is not None else n.imm
