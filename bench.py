@@ -285,7 +285,8 @@ def run_gpu(args):
     clocks.stop_flag = True
     prof = {}
     for k in ('k_reduce_rows', 'k_encrypt', 'k_rp_create_hdr', 'k_rp_create_items', 'k_rp_verify_hdr', 'k_rp_verify_items',
-              'k_rp_flags', 'k_agg_partial', 'k_agg_final', 'k_decrypt'):
+              'k_rp_verify_prep', 'k_pair_ucode', 'k_rp_verify_gt', 'k_rp_verify_finish', 'k_rp_flags', 'k_agg_partial',
+              'k_agg_final', 'k_decrypt'):
         tms, cnt = ctypes.c_double(), ctypes.c_uint64()
         ck(lib.drx_profile_get(be.h, k.encode(), ctypes.byref(tms), ctypes.byref(cnt)))
         if not cnt.value:
@@ -364,10 +365,11 @@ def run_gpu(args):
     # ------------------------------------------------------------------ roofline of the dominant kernel
     mac_ms, mac_work = be.microbench(0, 20000)
     peak_tmac = mac_work / mac_ms / 1e9
-    vi = prof.get('k_rp_verify_items', {'ms_per_launch': float('nan')})
+    dom = 'k_pair_ucode' if 'k_pair_ucode' in prof else 'k_rp_verify_items'
+    vi = prof.get(dom, {'ms_per_launch': float('nan')})
     alg_mac = n * NS * L * M_VERIFY_ITEM * MAC32_PER_M
     achieved = alg_mac / (vi['ms_per_launch'] * 1e-3) / 1e12
-    roofline = {'bound': 'int32 IMAD.WIDE pipe', 'kernel': 'k_rp_verify_items', 'achieved': achieved, 'peak': peak_tmac,
+    roofline = {'bound': 'int32 IMAD.WIDE pipe', 'kernel': dom, 'achieved': achieved, 'peak': peak_tmac,
                 'unit': 'TMAC32/s', 'frac': achieved / peak_tmac, 'traffic': None,
                 'peak_source': 'measured live: register-resident IMAD.WIDE.U32.X chains (drx_microbench kind 0); MEASURED_PEAKS.json has no integer figure',
                 'algorithmic': '%d proofs x %d (server,digit) pairs x %d M x 128 MAC32 per launch' % (n, NS * L, M_VERIFY_ITEM)}

@@ -106,9 +106,12 @@ __device__ __forceinline__ void uc_store(Fp2* S, uint32_t s, const Fp2& r) {
   }
 }
 
-#define UC_ITEMS_PER_BLOCK (64 / UC_G)
+#ifndef UC_BLOCK
+#define UC_BLOCK 64
+#endif
+#define UC_ITEMS_PER_BLOCK (UC_BLOCK / UC_G)
 
-__global__ void __launch_bounds__(64)
+__global__ void __launch_bounds__(UC_BLOCK)
 k_pair_ucode(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ scratch) {
   extern __shared__ __align__(16) unsigned char uc_smem[];
   Fp2* slots = (Fp2*)uc_smem;
@@ -129,35 +132,55 @@ k_pair_ucode(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__
     // fetch the next phase's words while this one computes
     const int nx = ph + 1 < UC_NPHASES ? ph + 1 : ph;
     const uint32_t op_n = uc_ops[nx], w_n = uc_lanes[nx * UC_G + lane];
-    if (alive && (w >> 31)) {
-      const uint32_t d = w & 1023u, ia = (w >> 10) & 1023u, ib = (w >> 20) & 1023u;
+    if (alive && w != 0xffffffffu) {
+      const uint32_t d = w & 255u, ia = (w >> 8) & 255u, ib = (w >> 16) & 255u, ic = w >> 24;
       const Fp2 a = uc_load(S, ia);
       Fp2 r;
-      switch (op) {
-        case UC_MUL: r = uc_mul(a, uc_load(S, ib)); break;
-        case UC_ADD: r = uc_add(a, uc_load(S, ib)); break;
-        case UC_SUB: r = uc_sub(a, uc_load(S, ib)); break;
-        case UC_MULXI: r = uc_xi(a); break;
-        case UC_CONJ: r = Fp2{a.c0, fp_neg(a.c1)}; break;
-        case UC_MULC: r = uc_mul(a, uc_load_const2(ib)); break;
-        case UC_CONJMULC: r = uc_mul(Fp2{a.c0, fp_neg(a.c1)}, uc_load_const2(ib)); break;
-        case UC_MULFPC: {
-          const Fp k = uc_constp_(ib);
-          r = Fp2{fp_mul(a.c0, k), fp_mul(a.c1, k)};
-          break;
+      // ordered by how often the generated program uses each operation (a compare-and-branch chain is cheaper
+      // than the balanced search ptxas builds for a switch, and the hot cases come first)
+      if (op == UC_ADD) {
+        r = uc_add(a, uc_load(S, ib));
+      } else if (op == UC_MUL) {
+        r = uc_mul(a, uc_load(S, ib));
+      } else if (op == UC_SUB2) {
+        r = uc_sub(uc_sub(a, uc_load(S, ib)), uc_load(S, ic));
+      } else if (op == UC_AXI) {
+        r = uc_add(a, uc_xi(uc_load(S, ib)));
+      } else if (op == UC_SUB) {
+        r = uc_sub(a, uc_load(S, ib));
+      } else if (op == UC_CYCP) {
+        r = uc_add(a, uc_load(S, ib));
+        r = uc_add(uc_add(r, r), a);
+      } else if (op == UC_CYCM) {
+        r = uc_sub(a, uc_load(S, ib));
+        r = uc_add(uc_add(r, r), a);
+      } else if (op == UC_MULXI) {
+        r = uc_xi(a);
+      } else if (op == UC_MULFP0 || op == UC_MULFP1) {
+        const Fp2 pt = uc_load(S, ib);
+        const Fp k = op == UC_MULFP0 ? pt.c0 : pt.c1;
+        r = Fp2{fp_mul(a.c0, k), fp_mul(a.c1, k)};
+      } else if (op == UC_X4 || op == UC_X8 || op == UC_X3) {
+        const Fp2 d2 = uc_add(a, a);
+        if (op == UC_X3) {
+          r = uc_add(d2, a);
+        } else {
+          r = uc_add(d2, d2);
+          if (op == UC_X8) r = uc_add(r, r);
         }
-        case UC_MULFP0: {
-          const Fp k = uc_load(S, ib).c0;
-          r = Fp2{fp_mul(a.c0, k), fp_mul(a.c1, k)};
-          break;
-        }
-        case UC_MULFP1: {
-          const Fp k = uc_load(S, ib).c1;
-          r = Fp2{fp_mul(a.c0, k), fp_mul(a.c1, k)};
-          break;
-        }
-        case UC_INV: r = fp2_inv(a); break;
-        default: r = a; break;  // UC_COPY
+      } else if (op == UC_CONJMULC || op == UC_MULC) {
+        const Fp2 x = op == UC_CONJMULC ? Fp2{a.c0, fp_neg(a.c1)} : a;
+        r = uc_mul(x, uc_load_const2(ib));
+      } else if (op == UC_MULFPC) {
+        const Fp k = uc_constp_(ib);
+        r = Fp2{fp_mul(a.c0, k), fp_mul(a.c1, k)};
+      } else if (op == UC_CONJ) {
+        r = Fp2{a.c0, fp_neg(a.c1)};
+      } else if (op == UC_INV) {
+        Fp2 tmp = a;  // only this copy has its address taken (fp2_inv is out of line)
+        r = fp2_inv(tmp);
+      } else {
+        r = a;  // UC_COPY
       }
       uc_store(S, d, r);
     }
@@ -181,29 +204,23 @@ k_pair_ucode(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__
 
 size_t rp_ucode_prep_bytes(size_t items) { return items * sizeof(UcPrep); }
 
-// prep -> cooperative pairing; writes e into scratch[t].a (the same slot role 0 of k_rp_verify_roles fills)
-int launch_rp_verify_pair_ucode(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
-                                const uint8_t* d_proofs, uint32_t* d_flags, void* d_prep, void* d_scratch) {
+int launch_rp_verify_prep(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                          const uint8_t* d_proofs, uint32_t* d_flags, void* d_prep) {
   if (!b.items) return 0;
+  k_rp_verify_prep<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const uint32_t*)d_proofs,
+                                                        d_flags, (UcPrep*)d_prep);
+  return 1;
+}
+// cooperative pairing over prepared items; writes e into scratch[t].a (the slot role 0 of k_rp_verify_roles fills)
+int launch_pair_ucode(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch) {
+  if (!items) return 0;
   static bool configured = false;
   const int smem = UC_ITEMS_PER_BLOCK * UC_NSLOTS * (int)sizeof(Fp2);
   if (!configured) {
     cudaFuncSetAttribute(k_pair_ucode, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     configured = true;
   }
-  k_rp_verify_prep<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const uint32_t*)d_proofs,
-                                                        d_flags, (UcPrep*)d_prep);
-  k_pair_ucode<<<grid_for(b.items, UC_ITEMS_PER_BLOCK), 64, smem, st>>>(b.items, (const UcPrep*)d_prep,
-                                                                       (GtPair*)d_scratch);
-  return 2;
-}
-
-// Diagnostic: e(P, Q) for affine Montgomery inputs already in UcPrep form
-int launch_pair_ucode_raw(cudaStream_t st, size_t n, const void* d_prep, void* d_scratch) {
-  if (!n) return 0;
-  const int smem = UC_ITEMS_PER_BLOCK * UC_NSLOTS * (int)sizeof(Fp2);
-  cudaFuncSetAttribute(k_pair_ucode, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  k_pair_ucode<<<grid_for(n, UC_ITEMS_PER_BLOCK), 64, smem, st>>>(n, (const UcPrep*)d_prep, (GtPair*)d_scratch);
+  k_pair_ucode<<<grid_for(items, UC_ITEMS_PER_BLOCK), UC_BLOCK, smem, st>>>(items, (const UcPrep*)d_prep, (GtPair*)d_scratch);
   return 1;
 }
 

@@ -96,8 +96,9 @@ int launch_rp_verify_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_
                            const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 // cooperative lane-group pairing driven by a generated micro-program (kernels_rp_ucode.cu)
 size_t rp_ucode_prep_bytes(size_t items);
-int launch_rp_verify_pair_ucode(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
-                                const uint8_t* d_proofs, uint32_t* d_flags, void* d_prep, void* d_scratch);
+int launch_rp_verify_prep(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                          const uint8_t* d_proofs, uint32_t* d_flags, void* d_prep);
+int launch_pair_ucode(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch);
 int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                         const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 int launch_rp_verify_finish(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_scratch,

@@ -20,16 +20,19 @@ sys.path.insert(0, os.path.join(ROOT, 'oracle'))
 import bn256_ref as R  # noqa: E402
 
 # ---------------------------------------------------------------------------------------------- symbolic Fp2 DAG
-OPS = ['NOP', 'MUL', 'ADD', 'SUB', 'DBL', 'NEG', 'MULXI', 'CONJ', 'MULC', 'MULFP0', 'MULFP1', 'INV', 'COPY', 'CONJMULC', 'MULFPC']
+OPS = ['NOP', 'MUL', 'ADD', 'SUB', 'DBL', 'NEG', 'MULXI', 'CONJ', 'MULC', 'MULFP0', 'MULFP1', 'INV', 'COPY', 'CONJMULC', 'MULFPC',
+       'SUB2', 'AXI', 'X3', 'X4', 'X8', 'CYCM', 'CYCP']
 OPC = {n: i for i, n in enumerate(OPS)}
 COST = {'MUL': 10, 'INV': 120, 'MULC': 10, 'CONJMULC': 10, 'MULFP0': 7, 'MULFP1': 7, 'MULFPC': 7}
 
 
 class Node:
-    __slots__ = ('op', 'a', 'b', 'imm', 'id', 'users', 'name', 'prio', 'slot', 'phase')
+    __slots__ = ('op', 'a', 'b', 'c', 'imm', 'id', 'users', 'name', 'prio', 'slot', 'phase', '_dead')
 
     def __init__(self, g, op, a=None, b=None, imm=0, name=None):
         self.op, self.a, self.b, self.imm, self.name = op, a, b, imm, name
+        self.c = None
+        self._dead = False
         self.id = len(g.nodes)
         self.users = []
         self.slot = None
@@ -317,11 +320,83 @@ def build_pairing(g):
         g.out(n, v.n)
 
 
+# ---------------------------------------------------------------------------------------------- linear-op fusion
+def fuse(g):
+    """Peephole fusion of chains of cheap linear operations into single micro-ops (fewer phases, fewer slot
+    round trips): a-b-c, a+xi*b, 3a, 4a, 8a, 3a-2b, 3a+2b. Only single-use intermediates are folded."""
+    def users(n):
+        return [u_ for u_ in n.users if not getattr(u_, '_dead', False)]
+
+    def rewire(n, op, a, b=None, c=None):
+        for x in (n.a, n.b, n.c):
+            if x is not None and n in x.users:
+                x.users.remove(n)
+        n.op, n.a, n.b, n.c = op, a, b, c
+        for x in set(y for y in (a, b, c) if y is not None):
+            if n not in x.users:
+                x.users.append(n)
+
+    changed = True
+    while changed:
+        changed = False
+        for n in g.nodes:
+            if getattr(n, '_dead', False):
+                continue
+            a, b = n.a, n.b
+            if n.op == 'SUB' and a is not None and a.op == 'SUB' and users(a) == [n] and a is not b:
+                a._dead = True
+                rewire(n, 'SUB2', a.a, a.b, b)
+                changed = True
+            elif n.op == 'ADD' and a is not b and b.op == 'MULXI' and users(b) == [n]:
+                b._dead = True
+                rewire(n, 'AXI', a, b.a)
+                changed = True
+            elif n.op == 'ADD' and a is not b and a.op == 'MULXI' and users(a) == [n]:
+                a._dead = True
+                rewire(n, 'AXI', b, a.a)
+                changed = True
+            elif n.op == 'ADD' and a is b and a.op == 'ADD' and a.a is a.b and users(a) == [n]:
+                a._dead = True
+                rewire(n, 'X4', a.a)
+                changed = True
+            elif n.op == 'ADD' and a is b and a.op == 'X4' and users(a) == [n]:
+                a._dead = True
+                rewire(n, 'X8', a.a)
+                changed = True
+            elif n.op == 'ADD' and a is not b and a.op == 'ADD' and a.a is a.b and users(a) == [n]:
+                d = a.a  # n = 2d + b
+                if d is b:
+                    a._dead = True
+                    rewire(n, 'X3', b)
+                    changed = True
+                elif d.op == 'SUB' and d.a is b and users(d) == [a]:
+                    a._dead = True
+                    d._dead = True
+                    rewire(n, 'CYCM', b, d.b)      # 2(b - g) + b = 3b - 2g
+                    changed = True
+                elif d.op == 'ADD' and d.a is not d.b and (d.a is b or d.b is b) and users(d) == [a]:
+                    other = d.b if d.a is b else d.a
+                    a._dead = True
+                    d._dead = True
+                    rewire(n, 'CYCP', b, other)    # 2(b + g) + b = 3b + 2g
+                    changed = True
+    for n in g.nodes:
+        n.users = [u_ for u_ in n.users if not getattr(u_, '_dead', False)]
+
+
 # ---------------------------------------------------------------------------------------------- evaluation
 def eval_node(n, val, g, P):
     a = val[n.a.id] if n.a is not None else None
     b = val[n.b.id] if n.b is not None else None
+    c = val[n.c.id] if n.c is not None else None
     op = n.op
+    if op == 'SUB2': return R.f2sub(R.f2sub(a, b), c)
+    if op == 'AXI': return R.f2add(a, R.f2mul(b, R.XI))
+    if op == 'X3': return R.f2scal(a, 3)
+    if op == 'X4': return R.f2scal(a, 4)
+    if op == 'X8': return R.f2scal(a, 8)
+    if op == 'CYCM': return R.f2sub(R.f2scal(a, 3), R.f2scal(b, 2))
+    if op == 'CYCP': return R.f2add(R.f2scal(a, 3), R.f2scal(b, 2))
     if op == 'MUL': return R.f2mul(a, b)
     if op == 'ADD': return R.f2add(a, b)
     if op == 'SUB': return R.f2sub(a, b)
@@ -350,10 +425,10 @@ def schedule(g, G, nslots, window=96):
         if n.id in live:
             continue
         live.add(n.id)
-        for x in (n.a, n.b):
+        for x in (n.a, n.b, n.c):
             if x is not None:
                 stack.append(x)
-    ops = [n for n in nodes if n.id in live and n.op != 'IN']
+    ops = [n for n in nodes if n.id in live and n.op != 'IN' and not getattr(n, '_dead', False)]
     # critical-path priority
     prio = {}
     for n in reversed(nodes):
@@ -377,7 +452,7 @@ def schedule(g, G, nslots, window=96):
     max_used = len(slot_of)
     while pending:
         lo = min(pending)  # ids are in trace order: only look `window` ops ahead so the live set stays small
-        ready = [n for i, n in pending.items() if i < lo + window and all(x is None or x.id in done for x in (n.a, n.b))]
+        ready = [n for i, n in pending.items() if i < lo + window and all(x is None or x.id in done for x in (n.a, n.b, n.c))]
         by_op = {}
         for n in ready:
             by_op.setdefault(n.op, []).append(n)
@@ -399,7 +474,7 @@ def schedule(g, G, nslots, window=96):
 
         def conflicts(order):
             c = 0
-            for sel in ('a', 'b'):
+            for sel in ('a', 'b', 'c'):
                 seen = {}
                 for n in order:
                     if n is None:
@@ -416,22 +491,40 @@ def schedule(g, G, nslots, window=96):
             padded = list(min(itertools.permutations(padded), key=conflicts))
         lanes = []
         to_free = []
+        # operands read in this phase, by how many of the phase's ops
+        readers = {}
+        for n in padded:
+            if n is None:
+                continue
+            for x in set(y for y in (n.a, n.b, n.c) if y is not None):
+                readers[x.id] = readers.get(x.id, 0) + 1
         for lane_id, n in enumerate(padded):
             if n is None:
                 lanes.append(None)
                 continue
-            if not free:
-                raise RuntimeError('out of slots (%d)' % nslots)
-            pick = None
-            for idx in range(len(free) - 1, -1, -1):
-                if free[idx] & 3 == lane_id & 3:
-                    pick = idx
+            # in-place: an operand that dies here and that no other lane reads this phase lends its slot to the result
+            s = None
+            for x in (n.a, n.b, n.c):
+                if x is not None and x.op != 'IN' and x.id not in out_ids and remaining_users[x.id] == 1 \
+                        and readers[x.id] == 1 and slot_of[x.id] not in [slot_of.get(m.id) for m in lanes if m is not None]:
+                    s = slot_of[x.id]
+                    remaining_users[x.id] = -1  # consumed, slot handed over
                     break
-            s = free.pop(pick if pick is not None else -1)
+            if s is None:
+                if not free:
+                    raise RuntimeError('out of slots (%d)' % nslots)
+                pick = None
+                for idx in range(len(free) - 1, -1, -1):
+                    if free[idx] & 3 == lane_id & 3:
+                        pick = idx
+                        break
+                s = free.pop(pick if pick is not None else -1)
             slot_of[n.id] = s
             max_used = max(max_used, max(slot_of.values()) + 1)
             lanes.append(n)
-            for x in set(y for y in (n.a, n.b) if y is not None):
+            for x in set(y for y in (n.a, n.b, n.c) if y is not None):
+                if remaining_users[x.id] == -1:
+                    continue
                 remaining_users[x.id] -= 1
                 if remaining_users[x.id] == 0 and x.id not in out_ids and x.op != 'IN':
                     to_free.append(slot_of[x.id])
@@ -465,9 +558,10 @@ def run_program(g, phases, slot_of, nslots, inputs):
         for n in lanes:
             a = slots[slot_of[n.a.id]] if n.a is not None else None
             b = slots[slot_of[n.b.id]] if n.b is not None else None
-            reads.append((a, b))
+            c = slots[slot_of[n.c.id]] if n.c is not None else None
+            reads.append((a, b, c))
         writes = []
-        for n, (a, b) in zip(lanes, reads):
+        for n, (a, b, c) in zip(lanes, reads):
             class V:  # minimal adapter for eval_node
                 pass
             val = {}
@@ -475,6 +569,8 @@ def run_program(g, phases, slot_of, nslots, inputs):
                 val[n.a.id] = a
             if n.b is not None:
                 val[n.b.id] = b
+            if n.c is not None:
+                val[n.c.id] = c
             writes.append((slot_of[n.id], eval_node(n, val, g, P)))
         for s, v in writes:
             slots[s] = v
@@ -488,6 +584,7 @@ def main():
     g = Graph()
     build_pairing(g)
     fix_user_counts(g)
+    fuse(g)
     phases, slot_of, used = schedule(g, G, nslots, window)
     cnt = lambda l: sum(1 for n in l if n is not None)
     nops = sum(cnt(l) for _, l in phases)
@@ -543,7 +640,7 @@ def emit(g, phases, slot_of, used, G):
         f.write('};\n__device__ const uint8_t uc_ops[UC_NPHASES] = {\n')
         for k in range(0, len(phases), 32):
             f.write('  ' + ', '.join(str(OPC[o]) for o, _ in phases[k:k + 32]) + ',\n')
-        f.write('};\n// per lane: dst | a << 10 | b << 20 | active << 31 (b = constant index for MULC / CONJMULC / MULFPC)\n')
+        f.write('};\n// per lane: dst | a << 8 | b << 16 | c << 24, 0xffffffff = idle (b = constant index for MULC / CONJMULC / MULFPC)\n')
         f.write('__device__ const uint32_t uc_lanes[UC_NPHASES * UC_G] = {\n')
         for op, lanes in phases:
             words = []
@@ -552,10 +649,11 @@ def emit(g, phases, slot_of, used, G):
                     n = lanes[k]
                     a = slot_of[n.a.id] if n.a is not None else 0
                     b = slot_of[n.b.id] if n.b is not None else n.imm
-                    assert slot_of[n.id] < 1024 and a < 1024 and b < 1024
-                    words.append('0x%08xu' % (slot_of[n.id] | a << 10 | b << 20 | 1 << 31))
+                    c = slot_of[n.c.id] if n.c is not None else 0
+                    assert slot_of[n.id] < 255 and a < 256 and b < 256 and c < 256
+                    words.append('0x%08xu' % (slot_of[n.id] | a << 8 | b << 16 | c << 24))
                 else:
-                    words.append('0u')
+                    words.append('0xffffffffu')
             f.write('  ' + ', '.join(words) + ',\n')
         f.write('};\n')
     print('wrote', path, os.path.getsize(path), 'bytes')
