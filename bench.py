@@ -31,6 +31,7 @@ MAC32_PER_M = 128
 # SURVEY.md section 8(d) algorithmic costs in Montgomery products (M)
 M_ENCRYPT = 824
 M_VERIFY_ITEM = 19700                      # per (server, digit): Miller 8,800 + final exp 9,100 + GT fixed 1,728 + 72
+M_PAIRING = 17900                          # Miller loop + final exponentiation alone (the cooperative kernel's share)
 M_VERIFY_PROOF = 3550 + 352 * (NS + L) + M_VERIFY_ITEM * NS * L
 M_CREATE_PROOF = L * (736 + NS * 4458)
 M_AGG_CT = 22
@@ -367,12 +368,13 @@ def run_gpu(args):
     peak_tmac = mac_work / mac_ms / 1e9
     dom = 'k_pair_ucode' if 'k_pair_ucode' in prof else 'k_rp_verify_items'
     vi = prof.get(dom, {'ms_per_launch': float('nan')})
-    alg_mac = n * NS * L * M_VERIFY_ITEM * MAC32_PER_M
+    per_item = M_PAIRING if dom == 'k_pair_ucode' else M_VERIFY_ITEM
+    alg_mac = n * NS * L * per_item * MAC32_PER_M
     achieved = alg_mac / (vi['ms_per_launch'] * 1e-3) / 1e12
     roofline = {'bound': 'int32 IMAD.WIDE pipe', 'kernel': dom, 'achieved': achieved, 'peak': peak_tmac,
                 'unit': 'TMAC32/s', 'frac': achieved / peak_tmac, 'traffic': None,
                 'peak_source': 'measured live: register-resident IMAD.WIDE.U32.X chains (drx_microbench kind 0); MEASURED_PEAKS.json has no integer figure',
-                'algorithmic': '%d proofs x %d (server,digit) pairs x %d M x 128 MAC32 per launch' % (n, NS * L, M_VERIFY_ITEM)}
+                'algorithmic': '%d proofs x %d (server,digit) pairs x %d M x 128 MAC32 per launch' % (n, NS * L, per_item)}
 
     secondary = {}
     if not args.no_secondary and rank == 0:

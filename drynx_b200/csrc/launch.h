@@ -14,7 +14,7 @@ constexpr size_t kG1AffBytes = 64, kG2AffBytes = 128, kGtBytes = 384, kG1JacByte
 constexpr int64_t kMaxHomomorphicInt = 100000;  // libunlynx.MaxHomomorphicInt
 constexpr uint32_t kDlogCap = 1u << 18;         // open-addressing slots for 100001 keys
 constexpr int kAggMaxSlices = 64;
-constexpr size_t kUcodeAutoMaxItems = 12288;  // batches up to this many pairing checks take the lane-group path
+constexpr size_t kUcodeAutoMaxItems = 36000;  // batches up to this many pairing checks take the lane-group path
 
 // ---- kernels_g1.cu
 // wire bytes -> Montgomery affine (returns malformed count in *d_bad)
