@@ -143,6 +143,7 @@ struct drx_ctx {
   uint64_t launches = 0;
   bool have_pub = false, have_dlog = false;
   int opt_verify_path = 0;  // drx_set_option "rp_verify_path"
+  int opt_ucode_lanes = 0;  // drx_set_option "rp_ucode_lanes": 0 = by batch size, 4 or 8
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
       sets_dev, sink;
   Arena arena;
@@ -321,6 +322,11 @@ int drx_set_option(drx_ctx* c, const char* name, int value) {
   if (!strcmp(name, "rp_verify_path")) {
     if (value < 0 || value > 2) return fail(-1, "rp_verify_path must be 0 (auto), 1 (thread per item) or 2 (lane groups)");
     c->opt_verify_path = value;
+    return 0;
+  }
+  if (!strcmp(name, "rp_ucode_lanes")) {
+    if (value != 0 && value != 4 && value != 8) return fail(-1, "rp_ucode_lanes must be 0 (auto), 4 or 8");
+    c->opt_ucode_lanes = value;
     return 0;
   }
   return fail(-1, "unknown option %s", name);

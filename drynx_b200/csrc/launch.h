@@ -15,6 +15,7 @@ constexpr int64_t kMaxHomomorphicInt = 100000;  // libunlynx.MaxHomomorphicInt
 constexpr uint32_t kDlogCap = 1u << 18;         // open-addressing slots for 100001 keys
 constexpr int kAggMaxSlices = 64;
 constexpr size_t kUcodeAutoMaxItems = 36000;  // batches up to this many pairing checks take the lane-group path
+constexpr size_t kUcodeG8MaxItems = 2400;     // ... and up to this many use eight lanes per check instead of four
 
 // ---- kernels_g1.cu
 // wire bytes -> Montgomery affine (returns malformed count in *d_bad)
@@ -98,7 +99,8 @@ int launch_rp_verify_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_
 size_t rp_ucode_prep_bytes(size_t items);
 int launch_rp_verify_prep(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                           const uint8_t* d_proofs, uint32_t* d_flags, void* d_prep);
-int launch_pair_ucode(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch);
+int launch_pair_ucode_g4(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch);
+int launch_pair_ucode_g8(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch);
 int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                         const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 int launch_rp_verify_finish(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_scratch,

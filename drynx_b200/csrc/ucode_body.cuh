@@ -1,0 +1,235 @@
+// Cooperative pairing for range-proof verification: a group of UC_G lanes per (proof, server, digit) item, the
+// item's state held ONCE as Fp2 slots in shared memory, the whole optimal ate pairing (Miller loop and final
+// exponentiation) executed as a static schedule of Fp2 operations (pairing_ucode.inc, generated and checked against
+// the big-integer definition by tools/microcode/gen.py). Every phase all lanes run the same operation on their own
+// (dst, a, b) slots; no thread-local stack is involved, which is what bounded the one-thread-per-item kernel
+// (DESIGN.md section 5). Replaces kyber pairing/bn256 optate.go for lib/range/range_proof.go:540-544.
+#pragma once
+#include <cstdlib>
+
+#define DRX_FP2_INLINE_MUL 1
+#include "rp_device.cuh"
+
+namespace drx {
+
+#include UC_PROGRAM_INC
+
+static inline int grid_for(size_t n, int threads) { return (int)((n + threads - 1) / threads); }
+
+struct UcPrep {      // per item: the two pairing arguments in Montgomery affine form
+  G1Aff P;           // c*Y_i - Zphi_j*B
+  G2Aff V;
+  uint32_t state;    // 0: run the pairing, 1: an argument is the point at infinity (value 1), 2: malformed V
+  uint32_t pad[3];
+};
+
+#ifdef UC_WITH_PREP
+// ---- one thread per item: parse V_ij and build the G1 argument (two comb walks, one inversion)
+__global__ void __launch_bounds__(64)
+k_rp_verify_prep(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __restrict__ tabB,
+                 const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags, UcPrep* __restrict__ prep) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= b.items) return;
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  const uint32_t* in = proofs + off / 4;
+  const RpSetDev set = sets[b.d_set_id[p]];
+  ProofView pv{ns, nd};
+  G2Aff V;
+  if (!g2_from_wire(V, in + pv.v_off(i, j))) {
+    atomicAnd(&flags[p], 0u);
+    prep[t].state = 2;
+    return;
+  }
+  const Scalar c = sc_from_wire(in + ProofView::c_off());
+  const Scalar zphi = sc_from_wire(in + pv.zphi_off(j));
+  G1Jac P1 = comb_mul((const G1Aff*)set.tabY + (size_t)i * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES), c);
+  P1 = jac_add(P1, comb_mul(tabB, sc_neg(zphi)));
+  const G1Aff P = jac_to_aff(P1);
+  prep[t].P = P;
+  prep[t].V = V;
+  prep[t].state = (aff_is_inf(P) | aff_is_inf(V)) ? 1u : 0u;
+}
+
+#endif
+
+// ---- Fp2 operations on register values (products go through the shared out-of-line fp_mul)
+__device__ __forceinline__ Fp2 uc_mul(const Fp2& a, const Fp2& b) {
+  // the three products are inlined here (and only here) so that ptxas interleaves their carry chains
+  const Fp v0 = fp_mul_inl(a.c0, b.c0);
+  const Fp v1 = fp_mul_inl(a.c1, b.c1);
+  const Fp s = fp_mul_inl(fp_add(a.c0, a.c1), fp_add(b.c0, b.c1));
+  return Fp2{fp_sub(v0, v1), fp_sub(fp_sub(s, v0), v1)};
+}
+__device__ __forceinline__ Fp2 uc_add(const Fp2& a, const Fp2& b) { return Fp2{fp_add(a.c0, b.c0), fp_add(a.c1, b.c1)}; }
+__device__ __forceinline__ Fp2 uc_sub(const Fp2& a, const Fp2& b) { return Fp2{fp_sub(a.c0, b.c0), fp_sub(a.c1, b.c1)}; }
+__device__ __forceinline__ Fp2 uc_xi(const Fp2& a) {
+  const Fp t0 = fp_add(fp_add(a.c0, a.c0), a.c0);
+  const Fp t1 = fp_add(fp_add(a.c1, a.c1), a.c1);
+  return Fp2{fp_sub(t0, a.c1), fp_add(t1, a.c0)};
+}
+__device__ __forceinline__ Fp2 uc_load_const2(uint32_t k) {
+  Fp2 r;
+#pragma unroll
+  for (int q = 0; q < 8; q++) {
+    r.c0.v[q] = uc_const2[k][q];
+    r.c1.v[q] = uc_const2[k][8 + q];
+  }
+  return r;
+}
+__device__ __forceinline__ Fp uc_constp_(uint32_t k) {
+  Fp r;
+#pragma unroll
+  for (int q = 0; q < 8; q++) r.v[q] = uc_constp[k][q];
+  return r;
+}
+
+// Shared-memory slot access. A slot is 64 bytes = four 16-byte chunks; logical chunk c of slot s lives at physical
+// chunk (c + s) & 3, and the per-item slot count is odd. A 128-bit shared load is served a quarter-warp (two lane
+// groups) at a time: the two groups run the same micro-instruction, so lane l of both reads the same slot number,
+// which lands in opposite bank halves (odd stride), and inside a group the generator keeps the slots touched
+// together distinct mod 4, so the eight 16-byte accesses hit eight different bank groups.
+__device__ __forceinline__ Fp2 uc_load(const Fp2* S, uint32_t s) {
+  const uint4* base = reinterpret_cast<const uint4*>(S + s);
+  Fp2 r;
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    const uint4 v = base[(c + UC_ROT(s)) & 3u];
+    uint32_t* dst = c < 2 ? &r.c0.v[4 * c] : &r.c1.v[4 * (c - 2)];
+    dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+  }
+  return r;
+}
+__device__ __forceinline__ void uc_store(Fp2* S, uint32_t s, const Fp2& r) {
+  uint4* base = reinterpret_cast<uint4*>(S + s);
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    const uint32_t* src = c < 2 ? &r.c0.v[4 * c] : &r.c1.v[4 * (c - 2)];
+    base[(c + UC_ROT(s)) & 3u] = make_uint4(src[0], src[1], src[2], src[3]);
+  }
+}
+
+#ifndef UC_BLOCK
+#define UC_BLOCK 64
+#endif
+#define UC_ITEMS_PER_BLOCK (UC_BLOCK / UC_G)
+
+__global__ void __launch_bounds__(UC_BLOCK)
+UC_KERNEL(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ scratch) {
+  extern __shared__ __align__(16) unsigned char uc_smem[];
+  Fp2* slots = (Fp2*)uc_smem;
+  const int grp = threadIdx.x / UC_G, lane = threadIdx.x % UC_G;
+  const size_t t = (size_t)blockIdx.x * UC_ITEMS_PER_BLOCK + grp;
+  const bool alive = t < items && prep[t].state == 0;
+  Fp2* S = slots + grp * UC_NSLOTS;
+  if (alive && lane == 0) {
+    uc_store(S, UC_IN_P, Fp2{prep[t].P.x, prep[t].P.y});
+    uc_store(S, UC_IN_QX, prep[t].V.x);
+    uc_store(S, UC_IN_QY, prep[t].V.y);
+    uc_store(S, UC_IN_ONE, fp2_one());
+    uc_store(S, UC_IN_ZERO, fp2_zero());
+  }
+  __syncwarp();
+  uint32_t op = uc_ops[0], w = uc_lanes[lane];
+  for (int ph = 0; ph < UC_NPHASES; ph++) {
+    // fetch the next phase's words while this one computes
+    const int nx = ph + 1 < UC_NPHASES ? ph + 1 : ph;
+    const uint32_t op_n = uc_ops[nx], w_n = uc_lanes[nx * UC_G + lane];
+    if (alive && w != 0xffffffffu) {
+      const uint32_t d = w & 255u, ia = (w >> 8) & 255u, ib = (w >> 16) & 255u, ic = w >> 24;
+      const Fp2 a = uc_load(S, ia);
+      Fp2 r;
+      // ordered by how often the generated program uses each operation (a compare-and-branch chain is cheaper
+      // than the balanced search ptxas builds for a switch, and the hot cases come first)
+      if (op == UC_ADD) {
+        r = uc_add(a, uc_load(S, ib));
+      } else if (op == UC_MUL) {
+        r = uc_mul(a, uc_load(S, ib));
+      } else if (op == UC_SUB2) {
+        r = uc_sub(uc_sub(a, uc_load(S, ib)), uc_load(S, ic));
+      } else if (op == UC_AXI) {
+        r = uc_add(a, uc_xi(uc_load(S, ib)));
+      } else if (op == UC_SUB) {
+        r = uc_sub(a, uc_load(S, ib));
+      } else if (op == UC_CYCP) {
+        r = uc_add(a, uc_load(S, ib));
+        r = uc_add(uc_add(r, r), a);
+      } else if (op == UC_CYCM) {
+        r = uc_sub(a, uc_load(S, ib));
+        r = uc_add(uc_add(r, r), a);
+      } else if (op == UC_MULXI) {
+        r = uc_xi(a);
+      } else if (op == UC_MULFP0 || op == UC_MULFP1) {
+        const Fp2 pt = uc_load(S, ib);
+        const Fp k = op == UC_MULFP0 ? pt.c0 : pt.c1;
+        r = Fp2{fp_mul(a.c0, k), fp_mul(a.c1, k)};
+      } else if (op == UC_X4 || op == UC_X8 || op == UC_X3) {
+        const Fp2 d2 = uc_add(a, a);
+        if (op == UC_X3) {
+          r = uc_add(d2, a);
+        } else {
+          r = uc_add(d2, d2);
+          if (op == UC_X8) r = uc_add(r, r);
+        }
+      } else if (op == UC_CONJMULC || op == UC_MULC) {
+        const Fp2 x = op == UC_CONJMULC ? Fp2{a.c0, fp_neg(a.c1)} : a;
+        r = uc_mul(x, uc_load_const2(ib));
+      } else if (op == UC_MULFPC) {
+        const Fp k = uc_constp_(ib);
+        r = Fp2{fp_mul(a.c0, k), fp_mul(a.c1, k)};
+      } else if (op == UC_CONJ) {
+        r = Fp2{a.c0, fp_neg(a.c1)};
+      } else if (op == UC_INV) {
+        Fp2 tmp = a;  // only this copy has its address taken (fp2_inv is out of line)
+        r = fp2_inv(tmp);
+      } else {
+        r = a;  // UC_COPY
+      }
+      uc_store(S, d, r);
+    }
+    __syncwarp();
+    op = op_n;
+    w = w_n;
+  }
+  if (t < items && lane == 0) {
+    Fp12 e = fp12_one();
+    if (alive) {
+      e.c0.c0 = uc_load(S, UC_OUT_E00);
+      e.c0.c1 = uc_load(S, UC_OUT_E01);
+      e.c0.c2 = uc_load(S, UC_OUT_E02);
+      e.c1.c0 = uc_load(S, UC_OUT_E10);
+      e.c1.c1 = uc_load(S, UC_OUT_E11);
+      e.c1.c2 = uc_load(S, UC_OUT_E12);
+    }
+    scratch[t].a = e;
+  }
+}
+
+#ifdef UC_WITH_PREP
+size_t rp_ucode_prep_bytes(size_t items) { return items * sizeof(UcPrep); }
+#endif
+
+#ifdef UC_WITH_PREP
+int launch_rp_verify_prep(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
+                          const uint8_t* d_proofs, uint32_t* d_flags, void* d_prep) {
+  if (!b.items) return 0;
+  k_rp_verify_prep<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const uint32_t*)d_proofs,
+                                                        d_flags, (UcPrep*)d_prep);
+  return 1;
+}
+#endif
+// cooperative pairing over prepared items; writes e into scratch[t].a (the slot role 0 of k_rp_verify_roles fills)
+int UC_LAUNCH(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch) {
+  if (!items) return 0;
+  static bool configured = false;
+  const int smem = UC_ITEMS_PER_BLOCK * UC_NSLOTS * (int)sizeof(Fp2);
+  if (!configured) {
+    cudaFuncSetAttribute(UC_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    configured = true;
+  }
+  UC_KERNEL<<<grid_for(items, UC_ITEMS_PER_BLOCK), UC_BLOCK, smem, st>>>(items, (const UcPrep*)d_prep, (GtPair*)d_scratch);
+  return 1;
+}
+
+}  // namespace drx

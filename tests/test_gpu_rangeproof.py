@@ -189,8 +189,8 @@ def test_config2_shape_create_verify_properties(backend, oracle, rng):
     assert [i for i in range(n) if not ok[i]] == flipped
 
 
-@pytest.mark.parametrize('path', [1, 2])
-def test_both_verification_paths_match_oracle(backend, oracle, rng, path):
+@pytest.mark.parametrize('path,lanes', [(1, 0), (2, 4), (2, 8)])
+def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes):
     """rp_verify_path 1 (one thread per pairing check) and 2 (cooperative lane groups running the generated
     micro-program) must give the oracle's accept / reject bits on valid, tampered and degenerate proofs."""
     ns, u, l = 3, 16, 2
@@ -210,8 +210,10 @@ def test_both_verification_paths_match_oracle(backend, oracle, rng, path):
     bad[6 * size + blk + 512 * l + 9] ^= 1                    # Zv_00
     want = oracle.rp_verify(ns, u, l, Y, P, bytes(bad), off, threads=8)
     backend.set_option('rp_verify_path', path)
+    backend.set_option('rp_ucode_lanes', lanes)
     try:
         ok = backend.verify_range_proofs([60] * n, [l] * n, bytes(bad), off)
     finally:
         backend.set_option('rp_verify_path', 0)
+        backend.set_option('rp_ucode_lanes', 0)
     assert list(ok) == list(want) == [1, 0, 0, 0, 0, 0, 0, 1]

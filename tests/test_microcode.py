@@ -19,7 +19,7 @@ def _gen():
 
 def test_scheduled_program_computes_the_pairing_and_matches_committed_tables(rng):
     gen = _gen()
-    inc = open(os.path.join(ROOT, 'drynx_b200', 'csrc', 'pairing_ucode.inc')).read()
+    inc = open(os.path.join(ROOT, 'drynx_b200', 'csrc', 'pairing_ucode_g4.inc')).read()
     G = int(re.search(r'#define UC_G (\d+)', inc).group(1))
     nslots = int(re.search(r'#define UC_NSLOTS (\d+)', inc).group(1))
     nphases = int(re.search(r'#define UC_NPHASES (\d+)', inc).group(1))

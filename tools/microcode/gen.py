@@ -472,6 +472,8 @@ def schedule(g, G, nslots, window=96):
         # operand slots best, then give every lane a destination slot of its own class when one is free.
         import itertools
 
+        CLS = 4 if G <= 4 else 8
+
         def conflicts(order):
             c = 0
             for sel in ('a', 'b', 'c'):
@@ -482,10 +484,11 @@ def schedule(g, G, nslots, window=96):
                     x = getattr(n, sel)
                     if x is None or (sel == 'b' and n.op in ('MULC', 'CONJMULC', 'MULFPC')):
                         continue
-                    k = slot_of[x.id] & 3
+                    k = slot_of[x.id] & (CLS - 1)
                     seen[k] = seen.get(k, 0) + 1
                 c += sum(v - 1 for v in seen.values())
             return c
+        CLS = 4 if G <= 4 else 8
         padded = chosen + [None] * (G - len(chosen))
         if G <= 4:
             padded = list(min(itertools.permutations(padded), key=conflicts))
@@ -515,7 +518,7 @@ def schedule(g, G, nslots, window=96):
                     raise RuntimeError('out of slots (%d)' % nslots)
                 pick = None
                 for idx in range(len(free) - 1, -1, -1):
-                    if free[idx] & 3 == lane_id & 3:
+                    if free[idx] & (CLS - 1) == lane_id & (CLS - 1):
                         pick = idx
                         break
                 s = free.pop(pick if pick is not None else -1)
@@ -617,7 +620,7 @@ def mont(x):
 
 
 def emit(g, phases, slot_of, used, G):
-    path = os.path.join(ROOT, 'drynx_b200', 'csrc', 'pairing_ucode.inc')
+    path = os.path.join(ROOT, 'drynx_b200', 'csrc', 'pairing_ucode_g%d.inc' % G)
     with open(path, 'w') as f:
         f.write('// GENERATED by tools/microcode/gen.py %d %d ... --emit -- do not edit.\n' % (G, used))
         f.write('// Lane-group micro-program of the optimal ate pairing: %d Fp2 operations in %d phases for %d lanes,\n'
@@ -625,6 +628,8 @@ def emit(g, phases, slot_of, used, G):
         f.write('// %d Fp2 slots per item. Checked against oracle/bn256_ref.pair by the generator before emission.\n' % used)
         used |= 1  # odd slot count per item: adjacent lane groups then sit in opposite bank halves
         f.write('#define UC_G %d\n#define UC_NSLOTS %d\n#define UC_NPHASES %d\n' % (G, used, len(phases)))
+        f.write('// physical 16-byte chunk of logical chunk c of slot s (bank swizzle, see kernels_rp_ucode.cuh)\n')
+        f.write('#define UC_ROT(s) %s\n' % ('((s) & 3u)' if G <= 4 else '(((s) >> 1) & 3u)'))
         for i, name in enumerate(OPS):
             f.write('#define UC_%s %d\n' % (name, i))
         for name, n in g.inputs.items():
