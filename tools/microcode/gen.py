@@ -625,7 +625,7 @@ def emit(g, phases, slot_of, used, G):
         f.write('// GENERATED by tools/microcode/gen.py %d %d ... --emit -- do not edit.\n' % (G, used))
         f.write('// Lane-group micro-program of the optimal ate pairing: %d Fp2 operations in %d phases for %d lanes,\n'
                 % (sum(1 for _, l in phases for n in l if n is not None), len(phases), G))
-        f.write('// %d Fp2 slots per item. Checked against oracle/bn256_ref.pair by the generator before emission.\n' % used)
+        f.write('// %d Fp2 slots per item. Executed with Python integers against the definition of the pairing by the generator before emission.\n' % used)
         used |= 1  # odd slot count per item: adjacent lane groups then sit in opposite bank halves
         f.write('#define UC_G %d\n#define UC_NSLOTS %d\n#define UC_NPHASES %d\n' % (G, used, len(phases)))
         f.write('// physical 16-byte chunk of logical chunk c of slot s (bank swizzle, see kernels_rp_ucode.cuh)\n')
