@@ -225,7 +225,37 @@ k_rp_create_finish(RpBatch b, const RpSetDev* __restrict__ sets, const GtPair* _
   if (t >= b.items) return;
   rp_create_finish(b, sets, scratch, proofs, t);
 }
-size_t rp_scratch_bytes(size_t items) { return items * sizeof(GtPair); }
+__global__ void __launch_bounds__(64)
+k_rp_create_fine(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
+                 const uint32_t* __restrict__ rnd, const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB,
+                 const uint32_t* __restrict__ baseB_wire, const uint32_t* __restrict__ ct, uint32_t* __restrict__ proofs,
+                 CreateFine* __restrict__ scratch) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= b.items) return;
+  rp_create_fine_role(b, sets, secret, rnd, rnd_off, tabGtB, baseB_wire, ct, proofs, scratch, t, (int)blockIdx.y);
+}
+__global__ void __launch_bounds__(64)
+k_rp_create_fine_finish(RpBatch b, const RpSetDev* __restrict__ sets, const CreateFine* __restrict__ scratch,
+                        uint32_t* __restrict__ proofs) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= b.items) return;
+  rp_create_fine_finish(b, sets, scratch, proofs, t, (int)blockIdx.y);
+}
+// scratch for either creation path (the fine one needs 3,840 B per item, the role-split one 768 B)
+size_t rp_scratch_bytes(size_t items) {
+  return items * (items <= kCreateFineMaxItems ? sizeof(CreateFine) : sizeof(GtPair));
+}
+int launch_rp_create_fine(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                          const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
+                          const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch) {
+  if (!b.items) return 0;
+  dim3 grid(grid_for(b.items, 64), 12), fin(grid_for(b.items, 64), 2);
+  k_rp_create_fine<<<grid, 64, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_rnd, d_rnd_off, (const Fp12*)d_tabGtB,
+                                        (const uint32_t*)d_baseB_wire, (const uint32_t*)d_ct, (uint32_t*)d_proofs,
+                                        (CreateFine*)d_scratch);
+  k_rp_create_fine_finish<<<fin, 64, 0, st>>>(b, d_sets, (const CreateFine*)d_scratch, (uint32_t*)d_proofs);
+  return 2;
+}
 int launch_rp_create_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
                            const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
                            const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch) {

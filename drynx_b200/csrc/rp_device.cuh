@@ -201,6 +201,92 @@ __device__ __forceinline__ void rp_create_finish(const RpBatch& b, const RpSetDe
   gt_to_wire(proofs + off / 4 + pv.a_off(i, j), a);
 }
 
+// Finer split for small batches, where creation is pure latency: the 32 comb windows of each of the three
+// fixed-base walks (V_ij in G2, the two GT factors) are dealt to four thread blocks each; partial results go to
+// scratch and two finish roles fold them (3 G2 additions + one inversion; 7 GT products).
+struct CreateFine {
+  Fp12 g[8];     // g[0..3]: partial products of e(B, A_{i,phi})^(-s v); g[4..7]: of e(B, g2)^t
+  G2Jac vp[4];   // partial sums of v * A_{i,phi}
+};
+__device__ __forceinline__ void gt_comb_partial(Fp12& out, const Fp12* __restrict__ table, const Scalar& k, int first) {
+  Fp12 acc = fp12_one();
+  bool any = false;
+  for (int w = first; w < DRX_COMB_WINDOWS; w += 4) {
+    const uint32_t d = (k.v[w >> 2] >> ((w & 3) * 8)) & 0xffu;
+    if (d) {
+      const Fp12* e = &table[w * DRX_COMB_ENTRIES + (int)d - 1];
+      if (any) {
+        fp12_mul(acc, acc, *e);
+      } else {
+        acc = *e;
+        any = true;
+      }
+    }
+  }
+  out = acc;
+}
+__device__ __forceinline__ void rp_create_fine_role(const RpBatch& b, const RpSetDev* __restrict__ sets,
+                                                    const int64_t* __restrict__ secret, const uint32_t* __restrict__ rnd,
+                                                    const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB,
+                                                    const uint32_t* __restrict__ baseB_wire,
+                                                    const uint32_t* __restrict__ ct, uint32_t* __restrict__ proofs,
+                                                    CreateFine* __restrict__ scratch, size_t t, int role) {
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  const RpSetDev set = sets[b.d_set_id[p]];
+  const int u = set.u;
+  ProofView pv{ns, nd};
+  const uint32_t* rp = rnd + (b.d_proof_off ? rnd_off[p] / 4 : p * (size_t)nd * (3 + ns) * 8);
+  const uint32_t* row = rp + (size_t)j * (3 + ns) * 8;
+  const Scalar v = sc_from_wire(row + 8 * (3 + i));
+  const uint32_t phi = rp_digit(secret[p], u, j);
+  const size_t tab = ((size_t)i * u + phi) * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES);
+  if (role < 4) {
+    const G2Aff* tA = (const G2Aff*)set.tabA + tab;
+    G2Jac acc = jac_inf<Fp2>();
+    for (int w = role; w < DRX_COMB_WINDOWS; w += 4) {
+      const uint32_t d = (v.v[w >> 2] >> ((w & 3) * 8)) & 0xffu;
+      if (d) acc = jac_add_aff(acc, tA[w * DRX_COMB_ENTRIES + (int)d - 1]);
+    }
+    scratch[t].vp[role] = acc;
+    if (role == 3) {  // the scalar Zv_ij = t_j - c v rides along
+      const Scalar tj = sc_from_wire(row + 8);
+      const Scalar c = rp_challenge(baseB_wire, ct + 32 * p, set.sumY);
+      sc_to_wire(proofs + off / 4 + pv.zv_off(i, j), sc_sub(tj, sc_mul(c, v)));
+    }
+  } else if (role < 8) {
+    const Scalar sj = sc_from_wire(row);
+    gt_comb_partial(scratch[t].g[role - 4], (const Fp12*)set.tabGtA + tab, sc_neg(sc_mul(sj, v)), role - 4);
+  } else {
+    const Scalar tj = sc_from_wire(row + 8);
+    gt_comb_partial(scratch[t].g[role - 4], tabGtB, tj, role - 8);
+  }
+}
+__device__ __forceinline__ void rp_create_fine_finish(const RpBatch& b, const RpSetDev* __restrict__ sets,
+                                                      const CreateFine* __restrict__ scratch,
+                                                      uint32_t* __restrict__ proofs, size_t t, int role) {
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  ProofView pv{ns, nd};
+  uint32_t* out = proofs + off / 4;
+  if (role == 0) {
+    G2Jac V = jac_add(jac_add(scratch[t].vp[0], scratch[t].vp[1]), jac_add(scratch[t].vp[2], scratch[t].vp[3]));
+    g2_to_wire(out + pv.v_off(i, j), jac_to_aff(V));
+  } else {
+    Fp12 a, c2;
+    fp12_mul(a, scratch[t].g[0], scratch[t].g[1]);
+    fp12_mul(c2, scratch[t].g[2], scratch[t].g[3]);
+    fp12_mul(a, a, c2);
+    fp12_mul(c2, scratch[t].g[4], scratch[t].g[5]);
+    fp12_mul(a, a, c2);
+    fp12_mul(c2, scratch[t].g[6], scratch[t].g[7]);
+    fp12_mul(a, a, c2);
+    gt_to_wire(out + pv.a_off(i, j), a);
+  }
+}
+
 // Verification item in two roles: role 0 computes e = e(c*Y_i - Zphi_j*B, V_ij), role 1 computes
 // T = A_ij * e(B, g2)^(-Zv_ij); rp_verify_finish accepts iff e == T (the same equation as below, moved across).
 __device__ __forceinline__ void rp_verify_role(const RpBatch& b, const RpSetDev* __restrict__ sets,
