@@ -372,7 +372,10 @@ def run_gpu(args):
     alg_mac = n * NS * L * per_item * MAC32_PER_M
     achieved = alg_mac / (vi['ms_per_launch'] * 1e-3) / 1e12
     roofline = {'bound': 'int32 IMAD.WIDE pipe', 'kernel': dom, 'achieved': achieved, 'peak': peak_tmac,
-                'unit': 'TMAC32/s', 'frac': achieved / peak_tmac, 'traffic': None,
+                'unit': 'TMAC32/s', 'frac': achieved / peak_tmac,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this size, from the committed ncu --set full
+                # capture profiles/r01_ncu_pair_ucode.txt (algorithmic bytes: 6,000 x 208 B in, 384 B out = 3.6 MB)
+                'traffic': 15508224 if dom == 'k_pair_ucode' else None,
                 'peak_source': 'measured live: register-resident IMAD.WIDE.U32.X chains (drx_microbench kind 0); MEASURED_PEAKS.json has no integer figure',
                 'algorithmic': '%d proofs x %d (server,digit) pairs x %d M x 128 MAC32 per launch' % (n, NS * L, per_item)}
 
