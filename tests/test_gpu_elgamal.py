@@ -179,12 +179,14 @@ def test_decrypt_matches_oracle_including_table_state(oracle, rng):
 
 
 def test_full_size_frequency_count_properties(backend, rng):
-    """BASELINE config 4 shape scaled to what the test budget allows: 200 DPs x 1000 bins. Property check:
+    """BASELINE config 4 at full size: 1,000 DPs x 1,000 bins = 10^6 encryptions (128 MB of ciphertexts), root
+    aggregation 1000 x 1000 -> 1000, decryption with the 10,000-entry table request. Property checks:
     decrypt(aggregate(encrypt(x_d))) == sum_d x_d, and aggregation is order-independent."""
     sk, P = _keys(rng)
     skb = sk.to_bytes(32, 'big')
     backend.set_pubkey(P)
-    ndp, v = 200, 1000
+    ndp, v = 1000, 1000
+    backend.create_decryption_table(10000)
     g = np.random.default_rng(4)
     counts = g.integers(0, 10, size=(ndp, v), dtype=np.int64)
     r = np.frombuffer(g.bytes(32 * ndp * v), np.uint8).copy()

@@ -217,3 +217,37 @@ def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes):
         backend.set_option('rp_verify_path', 0)
         backend.set_option('rp_ucode_lanes', 0)
     assert list(ok) == list(want) == [1, 0, 0, 0, 0, 0, 0, 1]
+
+
+def test_config5_ten_thousand_proofs(backend, rng):
+    """Config 5 at 10^4 proofs (u=16, l=4, ns=3: 120,000 pairing checks, 69 MB of proofs, the one-thread-per-check
+    path): every created proof verifies, and exactly the 1 % that get one byte flipped are rejected."""
+    ns, u, l, n = 3, 16, 4, 10000
+    sk = rng.scalar()
+    P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+    backend.set_pubkey(P)
+    Y, A = backend.init_range_proof_signature([rng.scalar() for _ in range(ns)], u)
+    backend.set_signatures(70, ns, u, Y, A)
+    g = np.random.default_rng(55)
+    secrets = g.integers(0, u ** l, size=n, dtype=np.int64)
+
+    def scal(k):
+        b = np.frombuffer(g.bytes(32 * k), np.uint8).copy()
+        b[::32] &= 0x7f
+        return b
+    rs = scal(n)
+    cts = backend.encrypt_int_vector(secrets, rs)
+    per = l * (3 + ns) * 32
+    rnd_all = scal(n * l * (3 + ns)).tobytes()
+    rnd = [rnd_all[per * i:per * (i + 1)] for i in range(n)]
+    proofs, off = backend.create_range_proofs([70] * n, {70: ns}, {70: u}, [l] * n, secrets, rs, cts, rnd)
+    ok = backend.verify_range_proofs([70] * n, [l] * n, proofs, off)
+    assert int(ok.sum()) == n
+    size = int(off[1])
+    bad = proofs.copy()
+    flipped = sorted(set(int(x) for x in g.integers(0, n, size=n // 100)))
+    for i in flipped:
+        pos = [170, 300, size - 40, 256 + 32 * l + 200][i % 4]
+        bad[i * size + pos] ^= 1
+    ok = backend.verify_range_proofs([70] * n, [l] * n, bad, off)
+    assert [i for i in range(n) if not ok[i]] == flipped
