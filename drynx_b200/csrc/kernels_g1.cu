@@ -87,9 +87,63 @@ k_encrypt(size_t n, const int64_t* __restrict__ m, const uint32_t* __restrict__ 
   store_pair_wire(ct + 32 * i, K, C);
 }
 
+// Small batches: eight lanes per ciphertext. Lanes 0-3 walk every fourth window of r*B, lanes 4-7 every fourth
+// window of r*K plus their share of the message windows of m*B; a two-level butterfly of full additions joins
+// each half, lane 0 fetches C from lane 4 and serialises both points with one shared inversion. Each lane runs
+// 8-10 dependent mixed additions instead of 66-72; the sums are the same group elements, so the bytes match the
+// one-thread kernel's.
+__device__ __forceinline__ G1Jac jac_shfl_xor_mask(const G1Jac& p, int m, uint32_t mask) {
+  G1Jac r;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    r.x.v[k] = __shfl_xor_sync(mask, p.x.v[k], m);
+    r.y.v[k] = __shfl_xor_sync(mask, p.y.v[k], m);
+    r.z.v[k] = __shfl_xor_sync(mask, p.z.v[k], m);
+  }
+  return r;
+}
+__global__ void __launch_bounds__(64)
+k_encrypt_lanes(size_t n, const int64_t* __restrict__ m, const uint32_t* __restrict__ r,
+                const G1Aff* __restrict__ tabB, const G1Aff* __restrict__ tabP, uint32_t* __restrict__ ct) {
+  const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  const int lane = threadIdx.x & 7, sub = lane & 3;
+  const uint32_t mask = 0xFFu << (threadIdx.x & 24u);
+  if (i >= n) return;  // whole groups of eight leave together
+  const Scalar ri = sc_from_wire(r + 8 * i);
+  const G1Aff* tab = lane < 4 ? tabB : tabP;
+  G1Jac acc = jac_inf<Fp>();
+  for (int w = sub; w < DRX_COMB_WINDOWS; w += 4) {
+    const uint32_t d = (ri.v[w >> 2] >> ((w & 3) * 8)) & 0xffu;
+    if (d) acc = jac_add_aff(acc, tab[w * DRX_COMB_ENTRIES + (int)d - 1]);
+  }
+  if (lane >= 4) {
+    const int64_t mi = m[i];
+    const uint64_t am = mi < 0 ? (uint64_t)0 - (uint64_t)mi : (uint64_t)mi;
+    for (int w = sub; w < 8; w += 4) {
+      const uint32_t d = (uint32_t)(am >> (8 * w)) & 0xffu;
+      if (d) {
+        const G1Aff q = tabB[w * DRX_COMB_ENTRIES + (int)d - 1];
+        acc = jac_add_aff(acc, mi < 0 ? aff_neg(q) : q);
+      }
+    }
+  }
+#pragma unroll
+  for (int s = 1; s <= 2; s <<= 1) {
+    const G1Jac o = jac_shfl_xor_mask(acc, s, mask);
+    acc = (lane & s) ? jac_add(o, acc) : jac_add(acc, o);
+  }
+  const G1Jac other = jac_shfl_xor_mask(acc, 4, mask);
+  if (lane == 0) store_pair_wire(ct + 32 * i, acc, other);
+}
+
 int launch_encrypt(cudaStream_t st, size_t n, const int64_t* d_m, const uint8_t* d_r, const void* d_tabB,
                    const void* d_tabP, uint8_t* d_ct) {
   if (!n) return 0;
+  if (n <= kEncryptLanesMaxItems) {
+    k_encrypt_lanes<<<grid_for(n * 8, 64), 64, 0, st>>>(n, d_m, (const uint32_t*)d_r, (const G1Aff*)d_tabB,
+                                                         (const G1Aff*)d_tabP, (uint32_t*)d_ct);
+    return 1;
+  }
   k_encrypt<<<grid_for(n, 128), 128, 0, st>>>(n, d_m, (const uint32_t*)d_r, (const G1Aff*)d_tabB,
                                              (const G1Aff*)d_tabP, (uint32_t*)d_ct);
   return 1;

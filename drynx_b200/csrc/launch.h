@@ -15,6 +15,7 @@ constexpr int64_t kMaxHomomorphicInt = 100000;  // libunlynx.MaxHomomorphicInt
 constexpr uint32_t kDlogCap = 1u << 18;         // open-addressing slots for 100001 keys
 constexpr int kAggMaxSlices = 64;
 constexpr size_t kUcodeAutoMaxItems = 36000;  // batches up to this many pairing checks take the lane-group path
+constexpr size_t kEncryptLanesMaxItems = 16384; // encryptions up to this many use eight lanes each (latency)
 constexpr size_t kCreateFineMaxItems = 36000; // creation items up to this many are split twelve ways (latency)
 constexpr size_t kUcodeG8MaxItems = 2400;     // ... and up to this many use eight lanes per check instead of four
 

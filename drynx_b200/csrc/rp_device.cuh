@@ -9,19 +9,9 @@
 namespace drx {
 
 // ------------------------------------------------------------------ scalar helpers (mod n)
-__device__ __noinline__ static Scalar sc_inv(const Scalar& a) {  // a^(n-2); 0 -> 0
-  Scalar r2, am, acc;
-  for (int k = 0; k < 8; k++) r2.v[k] = ModN::r2(k);
-  mont_mul<ModN>(am.v, a.v, r2.v);  // Montgomery form
-  for (int k = 0; k < 8; k++) acc.v[k] = ModN::r1(k);
-  for (int bit = 255; bit >= 0; bit--) {
-    mont_mul<ModN>(acc.v, acc.v, acc.v);
-    if ((ModN::pm2(bit >> 5) >> (bit & 31)) & 1u) mont_mul<ModN>(acc.v, acc.v, am.v);
-  }
-  Scalar one = sc_zero();
-  one.v[0] = 1;
+__device__ __noinline__ static Scalar sc_inv(const Scalar& a) {  // a^-1 mod n (division steps, fp.cuh); 0 -> 0
   Scalar out;
-  mont_mul<ModN>(out.v, acc.v, one.v);
+  mod_inv_plain<ModN>(out.v, a.v);
   return out;
 }
 

@@ -17,6 +17,19 @@ int emu_fp_mul_raw(const uint32_t* a, const uint32_t* b, uint32_t* r, int which)
   return 0;
 }
 
+// which: 0 = plain inverse mod p, 1 = plain inverse mod n (division steps); 2 = Montgomery fp_inv (division steps),
+// 3 = Montgomery a^(p-2) (the cross-check)
+int emu_mod_inv(const uint32_t* a, uint32_t* r, int which) {
+  if (which == 0) mod_inv_plain<ModP>(r, a);
+  else if (which == 1) mod_inv_plain<ModN>(r, a);
+  else {
+    Fp x; memcpy(x.v, a, 32);
+    const Fp y = which == 2 ? fp_inv(x) : fp_inv_fermat(x);
+    memcpy(r, y.v, 32);
+  }
+  return 0;
+}
+
 int emu_g1_mul(const uint8_t* k32, const uint8_t* pt64, uint8_t* out64, int method) {
   uint32_t kw[8], pw[16], ow[16];
   load_words(kw, k32, 32); load_words(pw, pt64, 64);

@@ -95,6 +95,23 @@ def test_encrypt_bytes_match_oracle(backend, oracle, rng):
     assert a == oracle.encrypt(P, [7], r_small.to_bytes(32, 'big'))
 
 
+def test_encrypt_lane_split_and_one_thread_kernels_agree(backend, oracle, rng):
+    """Up to 16384 encryptions per call run eight lanes each (k_encrypt_lanes), more run one thread each
+    (k_encrypt). The same 17000 inputs through one call and through two calls of 8500 give the same bytes, and
+    a sample of them matches the oracle."""
+    sk, P = _keys(rng)
+    backend.set_pubkey(P)
+    n = 17000
+    ms = np.array([rng.randint(-10 ** 9, 10 ** 9) for _ in range(n)], np.int64)
+    ms[:6] = [0, -1, 2 ** 63 - 1, -(2 ** 63), 255, 256]
+    rb = rng.scalars_bytes(n)
+    one = backend.encrypt_int_vector(ms, rb).tobytes()
+    h = n // 2
+    two = backend.encrypt_int_vector(ms[:h], rb[:32 * h]).tobytes() + backend.encrypt_int_vector(ms[h:], rb[32 * h:]).tobytes()
+    assert one == two
+    assert one[:128 * 64] == oracle.encrypt(P, [int(x) for x in ms[:64]], rb[:32 * 64], threads=8)
+
+
 def test_golden_encrypt_vectors(backend):
     with open(os.path.join(GOLD, 'bn256_golden.json')) as f:
         g = json.load(f)

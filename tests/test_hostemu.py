@@ -31,6 +31,25 @@ def test_montgomery_rows(emu, rng):
             assert got == a * b * rinv % mod
 
 
+def test_division_step_inverse(emu, rng):
+    """fp.cuh mod_inv_plain (batched division steps, 20 x 30) against Python's pow(a, -1, m) for both moduli, on the
+    boundary values and 2000 random residues each; the Montgomery wrapper against a^(p-2) on the same inputs."""
+    def call(a, which):
+        A = np.array(_limbs(a), np.uint32); Rr = np.zeros(8, np.uint32)
+        emu.emu_mod_inv(A.ctypes.data, Rr.ctypes.data, which)
+        return sum(int(v) << (32 * k) for k, v in enumerate(Rr))
+    for which, mod in ((0, R.p), (1, R.n)):
+        edge = [0, 1, 2, 3, mod - 1, mod - 2, (mod + 1) // 2, (mod - 1) // 2, 2 ** 255, 2 ** 254 - 1, 2 ** 30, 2 ** 30 - 1,
+                2 ** 60, 2 ** 240, (1 << 255) - 19, mod - 2 ** 30, mod - 2 ** 128]
+        edge += [2 ** k for k in range(0, 256, 7)] + [mod - 2 ** k for k in range(1, 255, 11)]
+        for a in edge + [rng.scalar() % mod for _ in range(2000)]:
+            a %= mod
+            got = call(a, which)
+            assert got == (pow(a, -1, mod) if a else 0), hex(a)
+    for a in [0, 1, R.p - 1] + [rng.scalar() % R.p for _ in range(200)]:
+        assert call(a, 2) == call(a, 3)
+
+
 def test_g1_g2_scalar_mult(emu, oracle, rng):
     for method in (0, 1):
         for k in (1, 255, 256, R.n - 1, rng.scalar()):
