@@ -315,6 +315,7 @@ def run_gpu(args):
     t_pr, h_pr = pinned(np.empty(n * proof_size, np.uint8)); keep.append(t_pr)
     t_ok, h_ok = pinned(np.empty(n, np.uint8)); keep.append(t_ok)
     t_ag, h_ag = pinned(np.empty(NOUT * 128, np.uint8)); keep.append(t_ag)
+    t_m, h_m = pinned(np.empty(n, np.int64)); keep.append(t_m)
     h_dec = np.empty(NOUT, np.int64)
     h_found = np.empty(NOUT, np.uint8)
     h_l = np.full(n, L, np.int64)
@@ -334,7 +335,8 @@ def run_gpu(args):
     def step_e2e():
         # what a Go data provider / root / verifying node would do with two goroutines and one context each:
         # aggregation + decryption only need the ciphertexts and run next to proof creation + verification
-        m = host_reduce(h['rows'])
+        ck(lib.drx_reduce_rows(be.h, ndp, rows, np_p(h['rows']), 3, np_p(h_m)))
+        m = h_m
         ck(lib.drx_encrypt(be.h, n, np_p(m), np_p(h['r']), np_p(h_ct)))
         side = threading.Thread(target=agg_dec)
         side.start()
@@ -343,9 +345,9 @@ def run_gpu(args):
         ck(lib.drx_rp_verify(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h_pr), np_p(poff), np_p(h_ok)))
         side.join()
         return m
-    h2d = (n * 8 + n * 32) + (n * 4 + n * 8 * 2 + n * 32 + n * 128 + h['rnd'].nbytes) + (n * 4 + n * 8 + h_pr.nbytes + n * 4) \
+    h2d = h['rows'].nbytes + (n * 8 + n * 32) + (n * 4 + n * 8 * 2 + n * 32 + n * 128 + h['rnd'].nbytes) + (n * 4 + n * 8 + h_pr.nbytes + n * 4) \
         + h_ct.nbytes + (NOUT * 128 + 32)  # encrypt + create + verify + aggregate + decrypt inputs
-    d2h = h_ct.nbytes + h_pr.nbytes + n + NOUT * 128 + NOUT * 8
+    d2h = n * 8 + h_ct.nbytes + h_pr.nbytes + n + NOUT * 128 + NOUT * 8
     for _ in range(3):
         step_e2e()
     assert h_ok.all() and h_pr.tobytes() == d_proofs.cpu().numpy().tobytes(), 'e2e and device-resident legs disagree'

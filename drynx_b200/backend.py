@@ -65,6 +65,17 @@ class Backend:
         p = _u8(P)
         _lib.check(self.lib.drx_set_pubkey(self.h, _ptr(p)))
 
+    def reduce_rows(self, rows, mode):
+        """Per-provider plaintext reduction (EncodeSum / EncodeMean / EncodeVariance before encryption):
+        rows int64[ndp][nrows] -> int64[ndp][w]; mode 0 [sum], 1 [sum, N], 2 [sum, N, sum of squares],
+        3 mean vector followed by variance vector."""
+        rows = np.ascontiguousarray(rows, dtype=np.int64)
+        assert rows.ndim == 2
+        w = (1, 2, 3, 5)[mode]
+        out = np.empty((rows.shape[0], w), dtype=np.int64)
+        _lib.check(self.lib.drx_reduce_rows(self.h, rows.shape[0], rows.shape[1], _ptr(rows), mode, _ptr(out)))
+        return out
+
     def encrypt_int_vector(self, m, r):
         """EncryptIntVectorGetRs with injected scalars: m int64[n], r bytes n*32 -> n*128 bytes."""
         m = np.ascontiguousarray(m, dtype=np.int64)

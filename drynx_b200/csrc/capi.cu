@@ -143,6 +143,7 @@ struct drx_ctx {
   uint64_t launches = 0;
   bool have_pub = false, have_dlog = false;
   int opt_verify_path = 0;  // drx_set_option "rp_verify_path"
+  int opt_create_path = 0;  // drx_set_option "rp_create_path": 0 = by batch size, 1 = never the lane-cooperative kernel
   int opt_ucode_lanes = 0;  // drx_set_option "rp_ucode_lanes": 0 = by batch size, 4 or 8
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
       sets_dev, sink;
@@ -324,6 +325,11 @@ int drx_set_option(drx_ctx* c, const char* name, int value) {
     c->opt_verify_path = value;
     return 0;
   }
+  if (!strcmp(name, "rp_create_path")) {
+    if (value < 0 || value > 2) return fail(-1, "rp_create_path must be 0 (auto), 1 (scratch-based split) or 2 (lane-cooperative)");
+    c->opt_create_path = value;
+    return 0;
+  }
   if (!strcmp(name, "rp_ucode_lanes")) {
     if (value != 0 && value != 4 && value != 8) return fail(-1, "rp_ucode_lanes must be 0 (auto), 4 or 8");
     c->opt_ucode_lanes = value;
@@ -356,6 +362,26 @@ int drx_reduce_rows_dev(drx_ctx* c, size_t ndp, size_t nrows, const int64_t* d_r
   Guard g(c);
   timed(c, "k_reduce_rows", [&] { return launch_reduce_rows(c->stream, ndp, nrows, d_rows, mode, d_out); });
   return check_launch("reduce_rows");
+}
+
+int drx_reduce_rows(drx_ctx* c, size_t ndp, size_t nrows, const int64_t* rows, int mode, int64_t* out) {
+  if (!c) return fail(-1, "null context");
+  if (mode < 0 || mode > 3) return fail(-1, "drx_reduce_rows: mode %d", mode);
+  if (ndp == 0) return 0;
+  if (!rows || !out) return fail(-1, "drx_reduce_rows: null buffer");
+  Guard g(c);
+  static const size_t width[4] = {1, 2, 3, 5};
+  const size_t w = width[mode];
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t oi = a.plan(ndp * nrows * 8), oo = a.plan(ndp * w * 8);
+  RET(a.commit());
+  if (nrows) CU(cudaMemcpyAsync(a.at<void>(oi), rows, ndp * nrows * 8, cudaMemcpyHostToDevice, c->stream));
+  timed(c, "k_reduce_rows", [&] { return launch_reduce_rows(c->stream, ndp, nrows, a.at<int64_t>(oi), mode, a.at<int64_t>(oo)); });
+  RET(check_launch("reduce_rows"));
+  CU(cudaMemcpyAsync(out, a.at<void>(oo), ndp * w * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
 }
 
 int drx_set_pubkey(drx_ctx* c, const uint8_t P[64]) {

@@ -154,20 +154,21 @@ int launch_make_sigs(cudaStream_t st, int ns, int64_t u, const uint8_t* d_x, con
 }
 
 // ------------------------------------------------------------------ creation (a-6)
-// Header thread per proof: Commit, Challenge, Zr, D, Zphi.
-__global__ void __launch_bounds__(128)
-k_rp_create_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
-                const uint32_t* __restrict__ r, const uint32_t* __restrict__ ct, const uint32_t* __restrict__ rnd,
-                const size_t* __restrict__ rnd_off, const G1Aff* __restrict__ tabB, const G1Aff* __restrict__ tabP,
-                const uint32_t* __restrict__ baseB_wire, uint32_t* __restrict__ proofs) {
-  const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= b.n) return;
+// Header per proof: Commit, Challenge, Zr, D, Zphi. The scalar part (challenge hash, Zphi_j, Zr, the two exponents
+// of D) is shared by the one-thread kernel and the eight-lane kernel; `write` selects the lane that stores.
+__device__ __forceinline__ bool rp_create_hdr_scalars(const RpBatch& b, const RpSetDev* __restrict__ sets,
+                                                      const int64_t* __restrict__ secret, const uint32_t* __restrict__ r,
+                                                      const uint32_t* __restrict__ ct, const uint32_t* __restrict__ rnd,
+                                                      const size_t* __restrict__ rnd_off,
+                                                      const uint32_t* __restrict__ baseB_wire, uint32_t* __restrict__ proofs,
+                                                      size_t p, bool write, Scalar& ssum, Scalar& msum, uint32_t*& out) {
   int ns, nd;
   size_t off;
   const bool ranged = locate_proof(b, sets, p, ns, nd, off);
-  uint32_t* out = proofs + off / 4;
-  for (int k = 0; k < 32; k++) out[k] = ct[32 * p + k];
-  if (!ranged) return;
+  out = proofs + off / 4;
+  if (write)
+    for (int k = 0; k < 32; k++) out[k] = ct[32 * p + k];
+  if (!ranged) return false;
   const RpSetDev set = sets[b.d_set_id[p]];
   const int64_t u = set.u;
   const int64_t sec = secret[p];
@@ -175,7 +176,8 @@ k_rp_create_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __r
   const Scalar c = rp_challenge(baseB_wire, ct + 32 * p, set.sumY);
   const uint32_t* rp = rnd + (b.d_proof_off ? rnd_off[p] / 4 : p * (size_t)nd * (3 + ns) * 8);
   ProofView pv{ns, nd};
-  Scalar msum = sc_zero(), ssum = sc_zero();
+  msum = sc_zero();
+  ssum = sc_zero();
   uint64_t upow = 1;
   int64_t rest = sec > 0 ? sec : 0;
   for (int j = 0; j < nd; j++) {
@@ -187,14 +189,64 @@ k_rp_create_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __r
     const uint64_t phi = (uint64_t)(rest % u);
     rest /= u;
     const Scalar zphi = sc_sub(sj, sc_mul(c, sc_from_u64(phi)));
-    sc_to_wire(out + pv.zphi_off(j), zphi);
+    if (write) sc_to_wire(out + pv.zphi_off(j), zphi);
     upow *= (uint64_t)u;
   }
+  if (write) {
+    const Scalar zr = sc_sub(msum, sc_mul(c, sc_from_wire(r + 8 * p)));
+    sc_to_wire(out + ProofView::zr_off(), zr);
+    sc_to_wire(out + ProofView::c_off(), c);
+  }
+  return true;
+}
+__global__ void __launch_bounds__(128)
+k_rp_create_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
+                const uint32_t* __restrict__ r, const uint32_t* __restrict__ ct, const uint32_t* __restrict__ rnd,
+                const size_t* __restrict__ rnd_off, const G1Aff* __restrict__ tabB, const G1Aff* __restrict__ tabP,
+                const uint32_t* __restrict__ baseB_wire, uint32_t* __restrict__ proofs) {
+  const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= b.n) return;
+  Scalar ssum, msum;
+  uint32_t* out;
+  if (!rp_create_hdr_scalars(b, sets, secret, r, ct, rnd, rnd_off, baseB_wire, proofs, p, true, ssum, msum, out)) return;
   const G1Jac D = jac_add(comb_mul(tabB, ssum), comb_mul(tabP, msum));
   g1_to_wire(out + ProofView::d_off(), jac_to_aff(D));
-  const Scalar zr = sc_sub(msum, sc_mul(c, sc_from_wire(r + 8 * p)));
-  sc_to_wire(out + ProofView::zr_off(), zr);
-  sc_to_wire(out + ProofView::c_off(), c);
+}
+// Small batches: eight lanes per proof; lanes 0-3 walk every fourth window of ssum*B, lanes 4-7 of msum*P, a
+// butterfly of full additions joins them (the scalars are computed by every lane, stored by lane 0).
+__global__ void __launch_bounds__(64)
+k_rp_create_hdr_lanes(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
+                      const uint32_t* __restrict__ r, const uint32_t* __restrict__ ct, const uint32_t* __restrict__ rnd,
+                      const size_t* __restrict__ rnd_off, const G1Aff* __restrict__ tabB,
+                      const G1Aff* __restrict__ tabP, const uint32_t* __restrict__ baseB_wire,
+                      uint32_t* __restrict__ proofs) {
+  const size_t p = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  const int lane = threadIdx.x & 7;
+  const uint32_t mask = 0xFFu << (threadIdx.x & 24u);
+  if (p >= b.n) return;  // whole groups of eight leave together
+  Scalar ssum, msum;
+  uint32_t* out;
+  if (!rp_create_hdr_scalars(b, sets, secret, r, ct, rnd, rnd_off, baseB_wire, proofs, p, lane == 0, ssum, msum, out))
+    return;  // uniform across the eight lanes
+  const Scalar k = lane < 4 ? ssum : msum;
+  const G1Aff* tab = lane < 4 ? tabB : tabP;
+  G1Jac acc = jac_inf<Fp>();
+  for (int w = lane & 3; w < DRX_COMB_WINDOWS; w += 4) {
+    const uint32_t d = (k.v[w >> 2] >> ((w & 3) * 8)) & 0xffu;
+    if (d) acc = jac_add_aff(acc, tab[w * DRX_COMB_ENTRIES + (int)d - 1]);
+  }
+#pragma unroll
+  for (int s = 1; s <= 4; s <<= 1) {
+    G1Jac o;
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+      o.x.v[q] = __shfl_xor_sync(mask, acc.x.v[q], s);
+      o.y.v[q] = __shfl_xor_sync(mask, acc.y.v[q], s);
+      o.z.v[q] = __shfl_xor_sync(mask, acc.z.v[q], s);
+    }
+    acc = (lane & s) ? jac_add(o, acc) : jac_add(acc, o);
+  }
+  if (lane == 0) g1_to_wire(out + ProofView::d_off(), jac_to_aff(acc));
 }
 
 // Item thread per (proof, server i, digit j): V_ij, a_ij, Zv_ij (body in rp_device.cuh).
@@ -256,6 +308,21 @@ int launch_rp_create_fine(cudaStream_t st, const RpBatch& b, const RpSetDev* d_s
   k_rp_create_fine_finish<<<fin, 64, 0, st>>>(b, d_sets, (const CreateFine*)d_scratch, (uint32_t*)d_proofs);
   return 2;
 }
+__global__ void __launch_bounds__(64)
+k_rp_create_lanes(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
+                  const uint32_t* __restrict__ rnd, const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB,
+                  const uint32_t* __restrict__ baseB_wire, const uint32_t* __restrict__ ct, uint32_t* __restrict__ proofs) {
+  rp_create_lanes(b, sets, secret, rnd, rnd_off, tabGtB, baseB_wire, ct, proofs, (int)blockIdx.y);
+}
+int launch_rp_create_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
+                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs) {
+  if (!b.items) return 0;
+  dim3 grid(grid_for(b.items * 16, 64), 3);  // sized for the sixteen-lane part; the other parts' spare blocks exit
+  k_rp_create_lanes<<<grid, 64, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_rnd, d_rnd_off, (const Fp12*)d_tabGtB,
+                                         (const uint32_t*)d_baseB_wire, (const uint32_t*)d_ct, (uint32_t*)d_proofs);
+  return 1;
+}
 int launch_rp_create_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
                            const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
                            const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch) {
@@ -272,6 +339,13 @@ int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_se
                          const uint8_t* d_r, const uint8_t* d_ct, const uint8_t* d_rnd, const size_t* d_rnd_off,
                          const void* d_tabB, const void* d_tabP, const uint8_t* d_baseB_wire, uint8_t* d_proofs) {
   if (!b.n) return 0;
+  if (b.n <= kEncryptLanesMaxItems) {
+    k_rp_create_hdr_lanes<<<grid_for(b.n * 8, 64), 64, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_r,
+                                                               (const uint32_t*)d_ct, (const uint32_t*)d_rnd, d_rnd_off,
+                                                               (const G1Aff*)d_tabB, (const G1Aff*)d_tabP,
+                                                               (const uint32_t*)d_baseB_wire, (uint32_t*)d_proofs);
+    return 1;
+  }
   k_rp_create_hdr<<<grid_for(b.n, 128), 128, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_r, (const uint32_t*)d_ct,
                                                      (const uint32_t*)d_rnd, d_rnd_off, (const G1Aff*)d_tabB,
                                                      (const G1Aff*)d_tabP, (const uint32_t*)d_baseB_wire,

@@ -16,6 +16,7 @@ constexpr uint32_t kDlogCap = 1u << 18;         // open-addressing slots for 100
 constexpr int kAggMaxSlices = 64;
 constexpr size_t kUcodeAutoMaxItems = 36000;  // batches up to this many pairing checks take the lane-group path
 constexpr size_t kEncryptLanesMaxItems = 16384; // encryptions up to this many use eight lanes each (latency)
+constexpr size_t kCreateLanesMaxItems = 800;   // creation items up to this many: lane-cooperative kernel (8 / 16 lanes per item)
 constexpr size_t kCreateFineMaxItems = 36000; // creation items up to this many are split twelve ways (latency)
 constexpr size_t kUcodeG8MaxItems = 2400;     // ... and up to this many use eight lanes per check instead of four
 
@@ -92,6 +93,9 @@ int launch_rp_flags(cudaStream_t st, size_t n, const uint32_t* d_flags, uint8_t*
 // role-split item kernels (independent parts of one item in different thread blocks) + their finish kernels;
 // d_scratch holds rp_scratch_bytes(items) bytes (two GT elements per item)
 size_t rp_scratch_bytes(size_t items);
+int launch_rp_create_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
+                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs);
 int launch_rp_create_fine(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch);
@@ -110,15 +114,4 @@ int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_set
                         const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 int launch_rp_verify_finish(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_scratch,
                             uint32_t* d_flags);
-// role-split item kernels (independent parts of one item in different thread blocks) + their finish kernels;
-// d_scratch holds rp_scratch_bytes(items) bytes (two GT elements per item)
-size_t rp_scratch_bytes(size_t items);
-int launch_rp_create_fine(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                          const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
-                          const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch);
-int launch_rp_create_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
-                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch);
-int launch_rp_verify_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
-                           const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 }  // namespace drx

@@ -198,10 +198,11 @@ struct CreateFine {
   Fp12 g[8];     // g[0..3]: partial products of e(B, A_{i,phi})^(-s v); g[4..7]: of e(B, g2)^t
   G2Jac vp[4];   // partial sums of v * A_{i,phi}
 };
-__device__ __forceinline__ void gt_comb_partial(Fp12& out, const Fp12* __restrict__ table, const Scalar& k, int first) {
+__device__ __forceinline__ void gt_comb_partial(Fp12& out, const Fp12* __restrict__ table, const Scalar& k, int first,
+                                                int stride = 4) {
   Fp12 acc = fp12_one();
   bool any = false;
-  for (int w = first; w < DRX_COMB_WINDOWS; w += 4) {
+  for (int w = first; w < DRX_COMB_WINDOWS; w += stride) {
     const uint32_t d = (k.v[w >> 2] >> ((w & 3) * 8)) & 0xffu;
     if (d) {
       const Fp12* e = &table[w * DRX_COMB_ENTRIES + (int)d - 1];
@@ -274,6 +275,81 @@ __device__ __forceinline__ void rp_create_fine_finish(const RpBatch& b, const Rp
     fp12_mul(c2, scratch[t].g[6], scratch[t].g[7]);
     fp12_mul(a, a, c2);
     gt_to_wire(out + pv.a_off(i, j), a);
+  }
+}
+
+// Lane-cooperative creation for small batches (one launch, no scratch). blockIdx.y selects the part of the item:
+//   0: V_ij = v * A_{i,phi} in G2, eight lanes per item: four comb windows each, then a three-level butterfly of
+//      full additions over warp shuffles; lane 0 converts to affine and serialises.
+//   1: a_ij = e(B, A_{i,phi})^(-s v) * e(B, g2)^t, sixteen lanes per item: lanes 0-7 take four windows each of the
+//      first power, lanes 8-15 of the second, then a four-level butterfly of Fp12 products (7 dependent products
+//      per item instead of 15 through the scratch-based split, 62 on one thread).
+//   2: Zv_ij = t_j - c v, one thread per item.
+template <int NW, class T>
+__device__ __forceinline__ T shfl_xor_words(const T& x, int m, uint32_t mask) {
+  static_assert(sizeof(T) == NW * 4, "word count");
+  T r;
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(&x);
+  uint32_t* dst = reinterpret_cast<uint32_t*>(&r);
+#pragma unroll 8
+  for (int k = 0; k < NW; k++) dst[k] = __shfl_xor_sync(mask, src[k], m);
+  return r;
+}
+__device__ __forceinline__ void rp_create_lanes(const RpBatch& b, const RpSetDev* __restrict__ sets,
+                                                const int64_t* __restrict__ secret, const uint32_t* __restrict__ rnd,
+                                                const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB,
+                                                const uint32_t* __restrict__ baseB_wire, const uint32_t* __restrict__ ct,
+                                                uint32_t* __restrict__ proofs, int role) {
+  const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int shift = role == 0 ? 3 : role == 1 ? 4 : 0;
+  const size_t t = gtid >> shift;
+  if (t >= b.items) return;  // whole lane groups leave together
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  const RpSetDev set = sets[b.d_set_id[p]];
+  ProofView pv{ns, nd};
+  uint32_t* out = proofs + off / 4;
+  const uint32_t* rp = rnd + (b.d_proof_off ? rnd_off[p] / 4 : p * (size_t)nd * (3 + ns) * 8);
+  const uint32_t* row = rp + (size_t)j * (3 + ns) * 8;
+  const Scalar v = sc_from_wire(row + 8 * (3 + i));
+  if (role == 2) {
+    const Scalar tj = sc_from_wire(row + 8);
+    const Scalar c = rp_challenge(baseB_wire, ct + 32 * p, set.sumY);
+    sc_to_wire(out + pv.zv_off(i, j), sc_sub(tj, sc_mul(c, v)));
+    return;
+  }
+  const uint32_t phi = rp_digit(secret[p], set.u, j);
+  const size_t tab = ((size_t)i * set.u + phi) * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES);
+  if (role == 0) {
+    const int lane = threadIdx.x & 7;
+    const uint32_t mask = 0xFFu << (threadIdx.x & 24u);
+    const G2Aff* tA = (const G2Aff*)set.tabA + tab;
+    G2Jac acc = jac_inf<Fp2>();
+    for (int w = lane; w < DRX_COMB_WINDOWS; w += 8) {
+      const uint32_t d = (v.v[w >> 2] >> ((w & 3) * 8)) & 0xffu;
+      if (d) acc = jac_add_aff(acc, tA[w * DRX_COMB_ENTRIES + (int)d - 1]);
+    }
+    for (int s = 1; s <= 4; s <<= 1) {
+      const G2Jac o = shfl_xor_words<48>(acc, s, mask);
+      acc = (lane & s) ? jac_add(o, acc) : jac_add(acc, o);
+    }
+    if (lane == 0) g2_to_wire(out + pv.v_off(i, j), jac_to_aff(acc));
+  } else {
+    const int lane = threadIdx.x & 15;
+    const uint32_t mask = 0xFFFFu << (threadIdx.x & 16u);
+    Fp12 acc;
+    if (lane < 8) {
+      const Scalar sj = sc_from_wire(row);
+      gt_comb_partial(acc, (const Fp12*)set.tabGtA + tab, sc_neg(sc_mul(sj, v)), lane, 8);
+    } else {
+      gt_comb_partial(acc, tabGtB, sc_from_wire(row + 8), lane - 8, 8);
+    }
+    for (int s = 1; s <= 8; s <<= 1) {
+      const Fp12 o = shfl_xor_words<96>(acc, s, mask);
+      fp12_mul(acc, acc, o);
+    }
+    if (lane == 0) gt_to_wire(out + pv.a_off(i, j), acc);
   }
 }
 

@@ -64,6 +64,9 @@ int drx_profile_get(drx_ctx* ctx, const char* kernel, double* total_ms, uint64_t
  * (lib/encoding/sum.go:19-23, mean.go:19-24, variance.go:19-27). mode 0: [sum]; 1: [sum, N];
  * 2: [sum, N, sum of squares]; 3: the mean vector followed by the variance vector (5 values). */
 int drx_reduce_rows_dev(drx_ctx* ctx, size_t ndp, size_t nrows, const int64_t* d_rows, int mode, int64_t* d_out);
+/* The same with host buffers: rows[ndp][nrows] in, out[ndp][w] back, w = 1, 2, 3 or 5 by mode (what a data
+ * provider calls in place of the Go loops of EncodeSum / EncodeMean / EncodeVariance before it encrypts). */
+int drx_reduce_rows(drx_ctx* ctx, size_t ndp, size_t nrows, const int64_t* rows, int mode, int64_t* out);
 
 /* Collective public key P for EncryptInt* and range proofs (CreateProof.CaPub, lib/range/range_proof.go:67);
  * builds its fixed-base table. */

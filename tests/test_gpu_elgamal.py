@@ -112,6 +112,22 @@ def test_encrypt_lane_split_and_one_thread_kernels_agree(backend, oracle, rng):
     assert one[:128 * 64] == oracle.encrypt(P, [int(x) for x in ms[:64]], rb[:32 * 64], threads=8)
 
 
+def test_reduce_rows_host_buffers(backend):
+    """drx_reduce_rows against the Go loops' arithmetic (sum.go:19-23, mean.go:19-24, variance.go:19-27), wrap-around
+    of int64 included, ragged sizes and an empty provider list."""
+    g = np.random.default_rng(3)
+    for ndp, nrows in [(1, 1), (3, 7), (100, 10000), (5, 0), (2, 257)]:
+        rows = g.integers(-2 ** 40, 2 ** 40, size=(ndp, nrows), dtype=np.int64)
+        s = rows.sum(axis=1)
+        q = (rows * rows).sum(axis=1)  # wraps like Go's int64
+        cnt = np.full(ndp, nrows, np.int64)
+        assert (backend.reduce_rows(rows, 0) == s[:, None]).all()
+        assert (backend.reduce_rows(rows, 1) == np.stack([s, cnt], 1)).all()
+        assert (backend.reduce_rows(rows, 2) == np.stack([s, cnt, q], 1)).all()
+        assert (backend.reduce_rows(rows, 3) == np.stack([s, cnt, s, cnt, q], 1)).all()
+    assert backend.reduce_rows(np.empty((0, 4), np.int64), 3).shape == (0, 5)
+
+
 def test_golden_encrypt_vectors(backend):
     with open(os.path.join(GOLD, 'bn256_golden.json')) as f:
         g = json.load(f)

@@ -219,6 +219,27 @@ def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes):
     assert list(ok) == list(want) == [1, 0, 0, 0, 0, 0, 0, 1]
 
 
+def test_creation_kernels_agree(backend, oracle, rng):
+    """The smallest batches are created by the lane-cooperative kernel (eight lanes per V_ij, sixteen per a_ij;
+    rp_create_path 2 forces it), mid-size ones by the scratch-based twelve-way split (rp_create_path 1); both must
+    give the oracle's bytes."""
+    ns, u, l = 2, 8, 3
+    sk, P, Y, A = _setup(backend, oracle, rng, ns, u, set_id=61)
+    secrets = [0, 1, 7, 8, 63, 64, 100, 511, 300]
+    rs, cts, rnd = _make(backend, oracle, rng, P, ns, u, l, secrets)
+    n = len(secrets)
+    backend.set_option('rp_create_path', 2)
+    try:
+        a, off = backend.create_range_proofs([61] * n, {61: ns}, {61: u}, [l] * n, secrets, rs, cts, rnd)
+        backend.set_option('rp_create_path', 1)
+        b, _ = backend.create_range_proofs([61] * n, {61: ns}, {61: u}, [l] * n, secrets, rs, cts, rnd)
+    finally:
+        backend.set_option('rp_create_path', 0)
+    assert a.tobytes() == b.tobytes()
+    want, _ = oracle.rp_create(ns, u, l, Y, A, P, secrets, rs, cts, rnd, threads=8)
+    assert a.tobytes() == bytes(want)
+
+
 def test_config5_ten_thousand_proofs(backend, rng):
     """Config 5 at 10^4 proofs (u=16, l=4, ns=3: 120,000 pairing checks, 69 MB of proofs, the one-thread-per-check
     path): every created proof verifies, and exactly the 1 % that get one byte flipped are rejected."""

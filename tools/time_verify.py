@@ -14,6 +14,7 @@ Y, A = be.init_range_proof_signature([int.from_bytes(g.bytes(31), 'big') + 1 for
 be.set_signatures(0, NS, U, Y, A)
 be.set_option('rp_verify_path', int(os.environ.get('DRX_RP_PATH', '0')))
 be.set_option('rp_ucode_lanes', int(os.environ.get('DRX_UC_LANES', '0')))
+be.set_option('rp_create_path', int(os.environ.get('DRX_CREATE_PATH', '0')))
 dev = torch.device('cuda', 0)
 st = torch.cuda.current_stream(); be.set_stream(st.cuda_stream or 1)
 vp = lambda t: ctypes.c_void_p(t.data_ptr())
