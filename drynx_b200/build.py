@@ -64,11 +64,12 @@ def build_gpu(force=False):
 
 
 def build_oracle(force=False):
-    src = os.path.join(ROOT, 'oracle', 'oracle.cpp')
+    srcs = [os.path.join(ROOT, 'oracle', 'oracle.cpp'), os.path.join(ROOT, 'oracle', 'oracle_ed.cpp')]
     os.makedirs(os.path.dirname(ORACLE_SO), exist_ok=True)
-    deps = [src] + [os.path.join(ROOT, 'oracle', f) for f in os.listdir(os.path.join(ROOT, 'oracle')) if f.endswith('.hpp')]
+    deps = srcs + [os.path.join(ROOT, 'oracle', f) for f in os.listdir(os.path.join(ROOT, 'oracle'))
+                   if f.endswith('.hpp') or f.endswith('.inc')]
     if force or _newer(ORACLE_SO, deps):
-        _run(['g++', '-O3', '-march=native', '-std=c++17', '-shared', '-fPIC', '-pthread', src, '-o', ORACLE_SO])
+        _run(['g++', '-O3', '-march=native', '-std=c++17', '-shared', '-fPIC', '-pthread'] + srcs + ['-o', ORACLE_SO])
     return ORACLE_SO
 
 

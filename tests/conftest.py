@@ -141,6 +141,44 @@ class Oracle:
         return ok
 
 
+    # ---- edwards25519 suite (oracle/oracle_ed.cpp)
+    def ed_mul(self, k, pt=None):
+        out = np.zeros(32, np.uint8)
+        rc = self.lib.orc_ed_mul(bytes(k), None if pt is None else bytes(pt), self._p(out))
+        return None if rc else out.tobytes()
+
+    def ed_add(self, a, b):
+        out = np.zeros(32, np.uint8)
+        rc = self.lib.orc_ed_add(bytes(a), bytes(b), self._p(out))
+        return None if rc else out.tobytes()
+
+    def ed_encrypt(self, P, m, r, threads=1):
+        m = np.ascontiguousarray(m, dtype=np.int64)
+        r = np.frombuffer(bytes(r), np.uint8).copy()
+        ct = np.zeros(64 * m.size, np.uint8)
+        assert self.lib.orc_ed_encrypt(ctypes.c_size_t(m.size), self._p(m), self._p(r), bytes(P), self._p(ct), threads) == 0
+        return ct.tobytes()
+
+    def ed_aggregate(self, vectors, threads=1):
+        v = len(vectors[0]) // 64
+        cts = np.frombuffer(b''.join(bytes(x) for x in vectors), np.uint8).copy()
+        out = np.zeros(64 * v, np.uint8)
+        rc = self.lib.orc_ed_aggregate(ctypes.c_size_t(len(vectors)), ctypes.c_size_t(v), self._p(cts), self._p(out), threads)
+        return rc, out.tobytes()
+
+    def ed_dlog_reset(self):
+        self.lib.orc_ed_dlog_reset()
+
+    def ed_decrypt(self, sk, ct, with_neg=True, threads=1):
+        ct = np.frombuffer(bytes(ct), np.uint8).copy()
+        n = ct.size // 64
+        out = np.zeros(n, np.int64)
+        found = np.zeros(n, np.uint8)
+        rc = self.lib.orc_ed_decrypt(ctypes.c_size_t(n), bytes(sk), self._p(ct), 1 if with_neg else 0, self._p(out),
+                                     self._p(found), threads)
+        return rc, out, found
+
+
 @pytest.fixture(scope='session')
 def oracle():
     return Oracle()

@@ -1,0 +1,99 @@
+"""The edwards25519 ElGamal oracle (oracle/oracle_ed.cpp, C++ restatement of kyber group/edwards25519 + unlynx
+lib/crypto.go) pinned against published known answers (RFC 8032 section 7.1) and against the big-integer definition
+oracle/ed25519_ref.py. CPU only."""
+import hashlib
+
+import numpy as np
+
+import ed25519_ref as E
+
+from conftest import SplitMix
+
+
+def _sc(v):
+    return int(v).to_bytes(32, 'little')
+
+
+def test_definition_pins_rfc8032():
+    E.self_check()
+
+
+def test_rfc8032_public_keys_through_the_cpp_oracle(oracle):
+    """A = s*B with the clamped SHA-512 half as the scalar. The oracle reduces scalars mod l, and B has order l, so
+    (s mod l)*B is the same point as the RFC's unreduced s*B."""
+    for sk, pk in [('9d61b19deffd5a60ba844af492ec2cc44449c5697b326919703bac031cae7f60',
+                    'd75a980182b10ab7d54bfed3c964073a0ee172f3daa62325af021a68f707511a'),
+                   ('4ccd089b28ff96da9db6c346ec114e0f5b8a319f35aba624da8cf6ed4fb8a6fb',
+                    '3d4017c3e843895a92b70aa74d1b7ebc9c982ccf2ec4968cc0cd55f12af4660c'),
+                   ('c5aa8df43f9f837bedb7442f31dcb7b166d38535076f094b85ce3a2e0b4458f7',
+                    'fc51cd8e6218a1a38da47ed00230f0580816ed13ba3303ac5deb911548908025')]:
+        h = hashlib.sha512(bytes.fromhex(sk)).digest()
+        a = int.from_bytes(h[:32], 'little')
+        a &= (1 << 254) - 8
+        a |= 1 << 254
+        assert oracle.ed_mul(_sc(a % E.l)).hex() == pk          # fixed-base path (geScalarMultBase)
+        assert oracle.ed_mul(_sc(a % E.l), E.to_bytes(E.BASE)).hex() == pk  # variable-base path (geScalarMult)
+
+
+def test_scalar_mult_and_add_match_definition(oracle):
+    rng = SplitMix(11)
+    B = E.to_bytes(E.BASE)
+    ks = [0, 1, 2, 15, 16, 255, 256, E.l - 1, E.l, E.l + 5, 2 ** 255 - 1, 2 ** 256 - 1]
+    ks += [rng.u64() | (rng.u64() << 64) | (rng.u64() << 128) | (rng.u64() << 192) for _ in range(12)]
+    for k in ks:
+        want = E.to_bytes(E.mul(k, E.BASE))
+        assert oracle.ed_mul(_sc(k)) == want
+        assert oracle.ed_mul(_sc(k), B) == want
+    P = E.mul(123456789, E.BASE)
+    Q = E.mul(rng.u64(), E.BASE)
+    for A, C in [(P, Q), (P, P), (P, E.neg(P)), (E.IDENT, P), (E.IDENT, E.IDENT)]:
+        assert oracle.ed_add(E.to_bytes(A), E.to_bytes(C)) == E.to_bytes(E.add(A, C))
+    k = rng.u64() << 100
+    assert oracle.ed_mul(_sc(k), E.to_bytes(Q)) == E.to_bytes(E.mul(k, Q))
+
+
+def test_decoding_edge_cases(oracle):
+    one = _sc(1)
+    # not on the curve: y = 2 has no x
+    assert E.from_bytes(_sc(2)) is None and oracle.ed_mul(one, _sc(2)) is None
+    # non-canonical y = p + 1 decodes like y = 1 (ref10 does not reject it)
+    assert oracle.ed_mul(one, _sc(E.p + 1)) == E.to_bytes(E.IDENT)
+    # "negative zero": y = 1 with the sign bit set is accepted as the identity
+    assert oracle.ed_mul(one, _sc(1 | (1 << 255))) == E.to_bytes(E.IDENT)
+    # a point of order 8 survives scalar multiplication by l+1... as itself times (l+1 mod l) = 1
+    for y in range(3, 40):
+        T = E.from_bytes(_sc(y))
+        if T is not None:
+            assert oracle.ed_mul(_sc(7), _sc(y)) == E.to_bytes(E.mul_raw(7, T))
+            break
+
+
+def test_elgamal_round_trip_matches_definition(oracle):
+    rng = SplitMix(12)
+    sk = rng.u64() | (rng.u64() << 64) | (rng.u64() << 128)
+    P = E.mul(sk, E.BASE)
+    ms = [0, 1, -1, 7, -12000, 99999, 2 ** 40 + 3, -(2 ** 62), 2 ** 63 - 1, -(2 ** 63)]
+    rs = [(rng.u64() << 192 | rng.u64() << 128 | rng.u64() << 64 | rng.u64()) for _ in ms]
+    rs[2] = 0
+    rs[3] = E.l - 1
+    rb = b''.join(_sc(r) for r in rs)
+    got = oracle.ed_encrypt(E.to_bytes(P), ms, rb, threads=4)
+    want = b''.join(E.ct_to_bytes(E.encrypt(P, m, r % E.l)) for m, r in zip(ms, rs))
+    assert got == want
+    # aggregate three copies of the first eight
+    rc, agg = oracle.ed_aggregate([got[:512], got[:512], got[:512]], threads=2)
+    assert rc == 0
+    for j in range(8):
+        ct = E.ct_from_bytes(got[64 * j:64 * j + 64])
+        s = E.ct_add(E.ct_add(ct, ct), ct)
+        assert agg[64 * j:64 * j + 64] == E.ct_to_bytes(s)
+    # decrypt: small values come back, large ones are reported as not found (value 0)
+    oracle.ed_dlog_reset()
+    small = [0, 5, -3, 250, -251]
+    rb2 = b''.join(_sc(rng.u64()) for _ in small)
+    ct = oracle.ed_encrypt(E.to_bytes(P), small, rb2)
+    rc, out, found = oracle.ed_decrypt(_sc(sk), ct)
+    assert rc == 0 and list(out) == small and list(found) == [1] * 5
+    rc, out, found = oracle.ed_decrypt(_sc(sk), got[6 * 64:7 * 64])
+    assert rc == 0 and list(out) == [0] and list(found) == [0]
+    oracle.ed_dlog_reset()
