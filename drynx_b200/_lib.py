@@ -26,6 +26,15 @@ SIGNATURES = {
     'drx_profile_enable': (ctypes.c_int, [VP, ctypes.c_int]),
     'drx_profile_get': (ctypes.c_int, [VP, ctypes.c_char_p, c_dp, ctypes.POINTER(ctypes.c_uint64)]),
     'drx_reduce_rows_dev': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, ctypes.c_int, VP]),
+    'drx_ed_set_pubkey': (ctypes.c_int, [VP, VP]),
+    'drx_ed_encrypt': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
+    'drx_ed_encrypt_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
+    'drx_ed_aggregate': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, VP]),
+    'drx_ed_aggregate_dev': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, VP]),
+    'drx_ed_dlog_table': (ctypes.c_int, [VP, ctypes.c_int64]),
+    'drx_ed_decrypt': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, ctypes.c_int, VP, VP]),
+    'drx_ed_decrypt_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
+    'drx_ed_point_mul': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
     'drx_reduce_rows': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, ctypes.c_int, VP]),
     'drx_set_pubkey': (ctypes.c_int, [VP, VP]),
     'drx_encrypt': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),

@@ -115,6 +115,50 @@ class Backend:
         _lib.check(self.lib.drx_decrypt_check_zero(self.h, n, _ptr(skb), _ptr(ct), _ptr(out)))
         return out
 
+    # ---- the same ElGamal operations over edwards25519 (UnLynx's default suite): 32-byte points, 64-byte ciphertexts,
+    # 32-byte little-endian scalars
+    def ed_set_pubkey(self, P):
+        p = _u8(P)
+        assert p.size == 32
+        _lib.check(self.lib.drx_ed_set_pubkey(self.h, _ptr(p)))
+
+    def ed_encrypt_int_vector(self, m, r):
+        m = np.ascontiguousarray(m, dtype=np.int64)
+        r = _u8(r)
+        assert r.size == 32 * m.size
+        ct = np.empty(64 * m.size, dtype=np.uint8)
+        _lib.check(self.lib.drx_ed_encrypt(self.h, m.size, _ptr(m), _ptr(r), _ptr(ct)))
+        return ct
+
+    def ed_aggregate(self, vectors):
+        vs = [_u8(v) for v in vectors]
+        v = vs[0].size // 64 if vs else 0
+        assert all(x.size == v * 64 for x in vs)
+        ptrs = (ctypes.c_void_p * len(vs))(*[x.ctypes.data for x in vs])
+        out = np.empty(64 * v, dtype=np.uint8)
+        _lib.check(self.lib.drx_ed_aggregate(self.h, len(vs), v, ctypes.cast(ptrs, ctypes.c_void_p), _ptr(out)))
+        return out
+
+    def ed_create_decryption_table(self, limit):
+        _lib.check(self.lib.drx_ed_dlog_table(self.h, int(limit)))
+
+    def ed_decrypt_int_vector(self, sk, ct, with_neg=True, return_found=False):
+        ct = _u8(ct)
+        n = ct.size // 64
+        out = np.empty(n, dtype=np.int64)
+        found = np.empty(n, dtype=np.uint8)
+        skb = _u8(sk)
+        _lib.check(self.lib.drx_ed_decrypt(self.h, n, _ptr(skb), _ptr(ct), 1 if with_neg else 0, _ptr(out), _ptr(found)))
+        return (out, found) if return_found else out
+
+    def ed_point_mul(self, k, pt):
+        k, pt = _u8(k), _u8(pt)
+        n = k.size // 32
+        assert pt.size == 32 * n
+        out = np.empty(32 * n, dtype=np.uint8)
+        _lib.check(self.lib.drx_ed_point_mul(self.h, n, _ptr(k), _ptr(pt), _ptr(out)))
+        return out
+
     # ---- range proofs (lib/range/range_proof.go call surface)
     def init_range_proof_signature(self, x_list, u):
         """InitRangeProofSignature for len(x_list) servers from caller-drawn private keys: (Y bytes, A bytes)."""

@@ -152,6 +152,10 @@ struct drx_ctx {
   DlogModel dlog;
   std::map<int, RpSetHost> sets;
   int sets_dev_count = 0;
+  // edwards25519 suite (capi_ed.inc): its own base table, key table and discrete-log table
+  bool ed_have_base = false, ed_have_pub = false, ed_have_dlog = false;
+  DevBuf ed_pt, ed_tabB, ed_tabP, ed_dlog_keys, ed_dlog_vals;
+  DlogModel ed_dlog;
 };
 
 namespace {
@@ -287,7 +291,8 @@ void drx_free(drx_ctx* c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   for (DevBuf* b : {&c->baseB_aff, &c->baseB_wire, &c->g2_aff, &c->g2_wire, &c->gtB, &c->tabB, &c->tabP, &c->pub_aff,
-                    &c->tabGtB, &c->tabG2, &c->dlog_keys, &c->dlog_vals, &c->bad, &c->sets_dev, &c->sink})
+                    &c->tabGtB, &c->tabG2, &c->dlog_keys, &c->dlog_vals, &c->bad, &c->sets_dev, &c->sink, &c->ed_pt,
+                    &c->ed_tabB, &c->ed_tabP, &c->ed_dlog_keys, &c->ed_dlog_vals})
     b->release();
   c->arena.buf.release();
   for (auto& kv : c->sets) {
@@ -647,3 +652,5 @@ int drx_microbench(drx_ctx* c, int kind, int iters, double* ms, double* work) {
 
 // ---- range-proof entry points: see capi_rp.inc
 #include "capi_rp.inc"
+// ---- edwards25519 ElGamal entry points: see capi_ed.inc
+#include "capi_ed.inc"

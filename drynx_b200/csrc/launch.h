@@ -114,4 +114,17 @@ int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_set
                         const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 int launch_rp_verify_finish(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_scratch,
                             uint32_t* d_flags);
+// edwards25519 ElGamal (kernels_ed.cu); points travel as 32-byte compressed encodings, ciphertexts as K || C (64 B)
+int launch_ed_from_wire(cudaStream_t st, size_t n, const uint8_t* d_wire, void* d_pts, int* d_bad);
+int launch_ed_comb_table(cudaStream_t st, const void* d_base_pt, void* d_table);
+int launch_ed_encrypt(cudaStream_t st, size_t n, const int64_t* d_m, const uint8_t* d_r, const void* d_tabB,
+                      const void* d_tabP, uint8_t* d_ct);
+size_t ed_aggregate_scratch_bytes(size_t ndp, size_t v, int* slices_out);
+int launch_ed_aggregate(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
+                        uint8_t* d_out, int* d_bad);
+int launch_ed_dlog_build(cudaStream_t st, const void* d_tabB, void* d_keys, uint32_t* d_vals);
+int launch_ed_decrypt(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t* d_ct, const void* d_keys,
+                      const uint32_t* d_vals, int64_t* d_out, int* d_bad);
+int launch_ed_mul(cudaStream_t st, size_t n, const uint8_t* d_k, const uint8_t* d_pt, uint8_t* d_out, int* d_bad);
+constexpr size_t kEdNielsBytes = 96, kEdExtBytes = 128;
 }  // namespace drx

@@ -165,6 +165,27 @@ int drx_mont_mul(drx_ctx* ctx, size_t n, int which, const uint32_t* a, const uin
  * kind 1: Montgomery products (one per step per thread). *work_per_ms = MAC32 (kind 0) or products (kind 1). */
 int drx_microbench(drx_ctx* ctx, int kind, int iters, double* ms, double* work);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * The same ElGamal operations over edwards25519, UnLynx's default suite (libunlynx.SuiTe = Ed25519 in
+ * github.com/ldsec/unlynx v1.4.0 lib/crypto.go; kyber v3.0.8 group/edwards25519 -- go.mod:14,26, not under
+ * /root/reference). Drynx itself fixes bn256 (lib/suite.go:10), so these replace the UnLynx functions as UnLynx's own
+ * protocols call them; argument meaning is that of the entry points above. Wire forms: point = 32 bytes (y little-
+ * endian, bit 255 = parity of x, RFC 8032 5.1.2); scalar = 32 bytes little-endian, reduced mod l on input;
+ * ciphertext = K || C = 64 bytes. Decoding follows ref10 ge_frombytes: y >= p and "negative zero" are accepted,
+ * an encoding with no x on the curve is an error (-2). */
+int drx_ed_set_pubkey(drx_ctx* ctx, const uint8_t P[32]);
+int drx_ed_encrypt(drx_ctx* ctx, size_t n, const int64_t* m, const uint8_t* r /*n*32*/, uint8_t* ct /*n*64*/);
+int drx_ed_encrypt_dev(drx_ctx* ctx, size_t n, const int64_t* d_m, const uint8_t* d_r, uint8_t* d_ct);
+int drx_ed_aggregate(drx_ctx* ctx, size_t ndp, size_t v, const uint8_t* const* cts /*ndp x (v*64)*/, uint8_t* out /*v*64*/);
+int drx_ed_aggregate_dev(drx_ctx* ctx, size_t ndp, size_t v, const uint8_t* d_cts /*[ndp][v][64]*/, uint8_t* d_out);
+int drx_ed_dlog_table(drx_ctx* ctx, int64_t limit);
+int drx_ed_decrypt(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t* ct /*n*64*/, int with_neg, int64_t* out,
+                   uint8_t* found);
+/* raw discrete logs on the device: d_out[i] in (-100000, 100000), or INT64_MIN when outside or malformed */
+int drx_ed_decrypt_dev(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t* d_ct, int64_t* d_out);
+/* Diagnostics: out[i] = k[i] * pt[i]. */
+int drx_ed_point_mul(drx_ctx* ctx, size_t n, const uint8_t* k /*n*32*/, const uint8_t* pt /*n*32*/, uint8_t* out /*n*32*/);
+
 #ifdef __cplusplus
 }
 #endif

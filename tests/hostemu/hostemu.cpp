@@ -5,6 +5,7 @@
 // against the oracle without a GPU.
 #define DRX_HOST_EMU 1
 #include "wire.cuh"
+#include "ed25519.cuh"
 #include <cstring>
 using namespace drx;
 
@@ -27,6 +28,61 @@ int emu_mod_inv(const uint32_t* a, uint32_t* r, int which) {
     const Fp y = which == 2 ? fp_inv(x) : fp_inv_fermat(x);
     memcpy(r, y.v, 32);
   }
+  return 0;
+}
+
+// ---- edwards25519 (fe25519.cuh / ed25519.cuh). op 0: a*b, 1: a+b, 2: a-b, 3: canonical form of a, 4: 1/a,
+// 5: a^((p-5)/8); raw little-endian limbs in, weakly reduced limbs out (the test reduces mod p)
+int emu_fe25519(const uint32_t* a, const uint32_t* b, uint32_t* r, int op) {
+  Fe x, y, z;
+  memcpy(x.v, a, 32); memcpy(y.v, b, 32);
+  if (op == 0) z = fe_mul(x, y);
+  else if (op == 1) z = fe_add(x, y);
+  else if (op == 2) z = fe_sub(x, y);
+  else if (op == 3) z = fe_canon(x);
+  else if (op == 4) z = fe_inv(x);
+  else z = fe_pow22523(x);
+  memcpy(r, z.v, 32);
+  return 0;
+}
+// out = k * P (method 0: 4-bit window; 1: comb table built on the fly); -1 when P does not decode
+int emu_ed_mul(const uint8_t* k32, const uint8_t* pt32, uint8_t* out32, int method) {
+  uint32_t kw[8], pw[8], ow[8];
+  load_words(kw, k32, 32); load_words(pw, pt32, 32);
+  EdExt p;
+  if (!ed_from_wire(p, pw)) return -1;
+  const Scalar k = ed_sc_from_wire(kw);
+  EdExt r;
+  if (method == 0) {
+    r = ed_window_mul(p, k);
+  } else {
+    static thread_local EdNiels table[DRX_COMB_WINDOWS * DRX_COMB_ENTRIES];
+    EdExt base = p;
+    for (int w = 0; w < DRX_COMB_WINDOWS; w++) {
+      EdExt acc = base;
+      for (int d = 1; d <= 255; d++) {
+        table[w * 255 + d - 1] = ed_to_niels_zinv(acc, fe_inv(acc.Z));
+        acc = ed_add(acc, base);
+      }
+      for (int s = 0; s < 8; s++) base = ed_dbl(base);
+    }
+    r = ed_comb_mul(table, k);
+  }
+  ed_to_wire(ow, r); memcpy(out32, ow, 32);
+  return 0;
+}
+// ciphertext of m under P with the scalar r, the way k_ed_encrypt computes it from comb tables of B and P
+int emu_ed_scalar_i64(int64_t m, uint8_t* out32) {
+  const Scalar s = ed_sc_from_i64(m);
+  memcpy(out32, s.v, 32);
+  return 0;
+}
+int emu_ed_add(const uint8_t* a32, const uint8_t* b32, uint8_t* out32) {
+  uint32_t aw[8], bw[8], ow[8];
+  load_words(aw, a32, 32); load_words(bw, b32, 32);
+  EdExt a, b;
+  if (!ed_from_wire(a, aw) || !ed_from_wire(b, bw)) return -1;
+  ed_to_wire(ow, ed_add(a, b)); memcpy(out32, ow, 32);
   return 0;
 }
 

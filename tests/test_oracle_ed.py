@@ -97,3 +97,16 @@ def test_elgamal_round_trip_matches_definition(oracle):
     rc, out, found = oracle.ed_decrypt(_sc(sk), got[6 * 64:7 * 64])
     assert rc == 0 and list(out) == [0] and list(found) == [0]
     oracle.ed_dlog_reset()
+
+
+def test_cpp_oracle_reproduces_golden_vectors(oracle):
+    import json
+    import os
+    with open(os.path.join(os.path.dirname(__file__), 'golden', 'ed25519_golden.json')) as f:
+        g = json.load(f)
+    for v in g['mul']:
+        assert oracle.ed_mul(bytes.fromhex(v['k']), bytes.fromhex(v['p'])).hex() == v['out']
+    for v in g['encrypt']:
+        assert oracle.ed_encrypt(bytes.fromhex(v['P']), [v['m']], bytes.fromhex(v['r'])).hex() == v['ct']
+    rc, agg = oracle.ed_aggregate([bytes.fromhex(x) for x in g['aggregate']['inputs']])
+    assert rc == 0 and agg.hex() == g['aggregate']['out']
