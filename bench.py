@@ -152,13 +152,22 @@ def run_reference(args):
         nver += k
     dt = time.perf_counter() - t0
     val = nver / dt
+    # the edwards25519 ElGamal suite, timed outside the step: 4,096 encryptions on all cores
+    ed_n = 4096
+    ed_P = orc.ed_mul((12345).to_bytes(32, 'little'))
+    ed_m = np.arange(ed_n, dtype=np.int64) % 10
+    ed_r = np.random.default_rng(7).bytes(32 * ed_n)
+    t1 = time.perf_counter()
+    orc.ed_encrypt(ed_P, ed_m, ed_r, threads=cores)
+    ed_rate = ed_n / (time.perf_counter() - t1)
     sample = '%d of %d DPs x %d rows (%d proofs/step), oracle/oracle.cpp C++ restatement of the Go path' % (ndp, args.ndp, args.rows, n)
     print(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'proofs/s', 'n_gpus': args.gpus, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': dt / args.steps * 1e3, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'u64 (4x64-bit Montgomery limbs)', 'data': 'synthetic',
         'config': {'workload': 'config 2: mean+variance, %d DPs x %d rows, u=16 l=4 ns=3 (bounded sample: %d DPs)' % (args.ndp, args.rows, ndp)},
-        'cpu_baseline': {'value': val, 'unit': 'proofs/s', 'cores': cores, 'kind': 'port', 'sample': sample},
+        'cpu_baseline': {'value': val, 'unit': 'proofs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
+                         'ed25519_encs_per_s': ed_rate},
         'e2e': {'value': val, 'unit': 'proofs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }))
@@ -472,6 +481,45 @@ def secondary_rates(be, lib, torch, dev, stream, ck, vp, peak_tmac, skp):
     assert bool((ok == 1).all())
     out['proofs_verified_per_s_20k_batch'] = npf / ms * 1e3
     out['verify_roofline_frac_20k_batch'] = npf * M_VERIFY_PROOF * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    out.update(secondary_rates_ed(be, lib, torch, dev, timed, ck, vp, peak_tmac, g))
+    return out
+
+
+# edwards25519 suite: algorithmic field products (72 MAC32 each: 64 + 8 for the 38-fold) per unit
+MAC32_PER_M_ED = 72
+M_ED_ENCRYPT = 72 * 7 + 8 + 265      # 72 comb additions, two serialisations sharing one inversion (a^(p-2): 265)
+M_ED_AGG_CT = 2 * (276 + 9)          # two point decodings (square root: 252 squarings + 24 products) + two additions
+M_ED_DECRYPT = 2 * 276 + 252 * 8 + 78 * 9 + 9 + 265 + 2   # decodings, 4-bit window multiplication, one serialisation
+
+
+def secondary_rates_ed(be, lib, torch, dev, timed, ck, vp, peak_tmac, g):
+    out = {}
+    sk = (987654321).to_bytes(32, 'little')
+    base = bytes([0x58] + [0x66] * 31)
+    be.ed_set_pubkey(be.ed_point_mul(sk, base))
+    ndp, v = 1000, 1000
+    n = ndp * v
+    m = torch.from_numpy(g.integers(0, 10, size=n, dtype=np.int64)).to(dev)
+    r = torch.from_numpy(np.frombuffer(g.bytes(32 * n), np.uint8).copy()).to(dev)
+    ct = torch.empty(n * 64, dtype=torch.uint8, device=dev)
+    agg = torch.empty(v * 64, dtype=torch.uint8, device=dev)
+    ms = timed(lambda: ck(lib.drx_ed_encrypt_dev(be.h, n, vp(m), vp(r), vp(ct))))
+    out['ed25519_encs_per_s'] = n / ms * 1e3
+    out['ed25519_encrypt_roofline_frac'] = n * M_ED_ENCRYPT * MAC32_PER_M_ED / (ms * 1e-3) / 1e12 / peak_tmac
+    ms = timed(lambda: ck(lib.drx_ed_aggregate_dev(be.h, ndp, v, vp(ct), vp(agg))))
+    out['ed25519_ciphertext_adds_per_s'] = n / ms * 1e3
+    out['ed25519_aggregate_roofline_frac'] = n * M_ED_AGG_CT * MAC32_PER_M_ED / (ms * 1e-3) / 1e12 / peak_tmac
+    nd = 1 << 17
+    dec = torch.empty(nd, dtype=torch.int64, device=dev)
+    skp = ctypes.c_char_p(sk)
+    ms = timed(lambda: ck(lib.drx_ed_decrypt_dev(be.h, nd, skp, vp(ct), vp(dec))))
+    out['ed25519_decrypts_per_s'] = nd / ms * 1e3
+    out['ed25519_decrypt_roofline_frac'] = nd * M_ED_DECRYPT * MAC32_PER_M_ED / (ms * 1e-3) / 1e12 / peak_tmac
+    # the aggregate of 1,000 providers' 0..9 counts decrypts to the column sums
+    be.synchronize()
+    want = m.view(ndp, v).sum(dim=0).cpu().numpy()
+    got = be.ed_decrypt_int_vector(sk, agg.cpu().numpy())
+    assert (got == want).all(), 'edwards25519 aggregate does not decrypt to the column sums'
     return out
 
 
