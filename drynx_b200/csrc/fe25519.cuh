@@ -71,6 +71,26 @@ DRX_HD void fe_sub_raw(uint32_t r[8], const uint32_t a[8], const uint32_t b[8]) 
   for (int k = 0; k < 8; k++) r[k] = t[k];
 }
 
+// lo + 38 * hi of a 16-limb value (shared tail of the product and the square)
+DRX_HD void fe_fold16(uint32_t r[8], const uint32_t t[16]) {
+  uint32_t s[9];
+  s[0] = mad_lo_cc(t[8], 38u, t[0]);
+  DRX_UNROLL
+  for (int k = 1; k < 8; k++) s[k] = madc_lo_cc(t[8 + k], 38u, t[k]);
+  s[8] = addc(0, 0);
+  s[1] = add_cc(s[1], mul_hi(t[8], 38u));
+  DRX_UNROLL
+  for (int k = 2; k < 8; k++) s[k] = addc_cc(s[k], mul_hi(t[7 + k], 38u));
+  s[8] = addc(s[8], mul_hi(t[15], 38u));
+  s[0] = add_cc(s[0], s[8] * 38u);
+  DRX_UNROLL
+  for (int k = 1; k < 8; k++) s[k] = addc_cc(s[k], 0);
+  const uint32_t c2 = addc(0, 0);
+  s[0] += c2 * 38u;
+  DRX_UNROLL
+  for (int k = 0; k < 8; k++) r[k] = s[k];
+}
+
 // 16-limb product, even/odd accumulators (see fp.cuh mont_mul): E collects a[even] * b[i], O collects a[odd] * b[i],
 // each row one carry chain over positions i .. i+8
 DRX_HD void fe_mul_raw(uint32_t r[8], const uint32_t a[8], const uint32_t b[8]) {
@@ -108,28 +128,81 @@ DRX_HD void fe_mul_raw(uint32_t r[8], const uint32_t a[8], const uint32_t b[8]) 
   t[1] = add_cc(e[1], o[1]);
   DRX_UNROLL
   for (int k = 2; k < 16; k++) t[k] = addc_cc(e[k], o[k]);
-  // fold: lo + 38 * hi, two chains (low and high halves of the 38 * hi[k] products)
-  uint32_t s[9];
-  s[0] = mad_lo_cc(t[8], 38u, t[0]);
+  fe_fold16(r, t);
+}
+
+// Square: the 28 cross products a_i a_j (i < j) once, doubled by a one-bit shift, plus the 8 squares: 36 wide
+// multiply-accumulates instead of 64. Cross products with i + j even collect in E, with i + j odd in O (so every
+// lo/hi couple stays pair-aligned); a row's carry lands on a limb that so far holds at most earlier rows' carries.
+DRX_HD void fe_sqr_raw(uint32_t r[8], const uint32_t a[8]) {
+  uint32_t e[16], o[16];
   DRX_UNROLL
-  for (int k = 1; k < 8; k++) s[k] = madc_lo_cc(t[8 + k], 38u, t[k]);
-  s[8] = addc(0, 0);
-  s[1] = add_cc(s[1], mul_hi(t[8], 38u));
+  for (int k = 0; k < 16; k++) {
+    e[k] = 0;
+    o[k] = 0;
+  }
   DRX_UNROLL
-  for (int k = 2; k < 8; k++) s[k] = addc_cc(s[k], mul_hi(t[7 + k], 38u));
-  s[8] = addc(s[8], mul_hi(t[15], 38u));
-  // s[8] < 2^7: fold it once more, then the possible last wrap
-  s[0] = add_cc(s[0], s[8] * 38u);
+  for (int i = 0; i < 7; i++) {
+    // i + j odd: j = i+1, i+3, ...
+    {
+      const int j0 = i + 1;
+      o[i + j0] = mad_lo_cc(a[i], a[j0], o[i + j0]);
+      o[i + j0 + 1] = madc_hi_cc(a[i], a[j0], o[i + j0 + 1]);
+      int top = i + j0 + 2;
+      DRX_UNROLL
+      for (int j = j0 + 2; j < 8; j += 2) {
+        o[i + j] = madc_lo_cc(a[i], a[j], o[i + j]);
+        o[i + j + 1] = madc_hi_cc(a[i], a[j], o[i + j + 1]);
+        top = i + j + 2;
+      }
+      if (top < 16) o[top] = addc(o[top], 0);
+    }
+    // i + j even: j = i+2, i+4, ...
+    if (i + 2 < 8) {
+      const int j0 = i + 2;
+      e[i + j0] = mad_lo_cc(a[i], a[j0], e[i + j0]);
+      e[i + j0 + 1] = madc_hi_cc(a[i], a[j0], e[i + j0 + 1]);
+      int top = i + j0 + 2;
+      DRX_UNROLL
+      for (int j = j0 + 2; j < 8; j += 2) {
+        e[i + j] = madc_lo_cc(a[i], a[j], e[i + j]);
+        e[i + j + 1] = madc_hi_cc(a[i], a[j], e[i + j + 1]);
+        top = i + j + 2;
+      }
+      if (top < 16) e[top] = addc(e[top], 0);
+    }
+  }
+  // x = E + O (limb 0 is empty: the lowest cross product sits at position 1)
+  uint32_t x[16];
+  x[0] = 0;
+  x[1] = o[1];
+  x[2] = add_cc(e[2], o[2]);
   DRX_UNROLL
-  for (int k = 1; k < 8; k++) s[k] = addc_cc(s[k], 0);
-  const uint32_t c2 = addc(0, 0);
-  s[0] += c2 * 38u;
+  for (int k = 3; k < 16; k++) x[k] = addc_cc(e[k], o[k]);
+  // t = 2x + sum a_i^2 2^(64 i)
+  uint32_t d[16], t[16];
+  d[0] = 0;
   DRX_UNROLL
-  for (int k = 0; k < 8; k++) r[k] = s[k];
+  for (int k = 1; k < 16; k++) d[k] = (x[k] << 1) | (x[k - 1] >> 31);
+  t[0] = mad_lo_cc(a[0], a[0], d[0]);
+  t[1] = madc_hi_cc(a[0], a[0], d[1]);
+  DRX_UNROLL
+  for (int i = 1; i < 8; i++) {
+    t[2 * i] = madc_lo_cc(a[i], a[i], d[2 * i]);
+    t[2 * i + 1] = madc_hi_cc(a[i], a[i], d[2 * i + 1]);
+  }
+  fe_fold16(r, t);
 }
 
 DRX_FPMUL_ATTR Fe fe_mul(Fe a, Fe b) { Fe r; fe_mul_raw(r.v, a.v, b.v); return r; }
+#ifndef DRX_FE_SQR_DEDICATED
+#define DRX_FE_SQR_DEDICATED 1
+#endif
+#if DRX_FE_SQR_DEDICATED
+DRX_FPMUL_ATTR Fe fe_sqr(Fe a) { Fe r; fe_sqr_raw(r.v, a.v); return r; }
+#else
 DRX_HD Fe fe_sqr(const Fe& a) { return fe_mul(a, a); }
+#endif
 DRX_HD Fe fe_add(const Fe& a, const Fe& b) { Fe r; fe_add_raw(r.v, a.v, b.v); return r; }
 DRX_HD Fe fe_sub(const Fe& a, const Fe& b) { Fe r; fe_sub_raw(r.v, a.v, b.v); return r; }
 DRX_HD Fe fe_neg(const Fe& a) { return fe_sub(fe_zero(), a); }

@@ -32,7 +32,7 @@ int emu_mod_inv(const uint32_t* a, uint32_t* r, int which) {
 }
 
 // ---- edwards25519 (fe25519.cuh / ed25519.cuh). op 0: a*b, 1: a+b, 2: a-b, 3: canonical form of a, 4: 1/a,
-// 5: a^((p-5)/8); raw little-endian limbs in, weakly reduced limbs out (the test reduces mod p)
+// 5: a^((p-5)/8), 6: a^2 (dedicated squaring); raw little-endian limbs in, weakly reduced limbs out (the test reduces mod p)
 int emu_fe25519(const uint32_t* a, const uint32_t* b, uint32_t* r, int op) {
   Fe x, y, z;
   memcpy(x.v, a, 32); memcpy(y.v, b, 32);
@@ -41,6 +41,7 @@ int emu_fe25519(const uint32_t* a, const uint32_t* b, uint32_t* r, int op) {
   else if (op == 2) z = fe_sub(x, y);
   else if (op == 3) z = fe_canon(x);
   else if (op == 4) z = fe_inv(x);
+  else if (op == 6) z = fe_sqr(x);
   else z = fe_pow22523(x);
   memcpy(r, z.v, 32);
   return 0;

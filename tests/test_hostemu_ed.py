@@ -38,6 +38,7 @@ def test_field_ops_on_weakly_reduced_inputs(emu, rng):
     vals = edge + [rng.scalar() | (rng.u64() << 192) for _ in range(60)]
     for a in vals:
         assert _fe(emu, 3, a) == a % p                       # canonical form
+        assert _fe(emu, 6, a) % p == a * a % p               # dedicated squaring
         for b in edge[:19:3] + vals[-6:]:
             assert _fe(emu, 0, a, b) % p == a * b % p
             assert _fe(emu, 1, a, b) % p == (a + b) % p
