@@ -249,17 +249,6 @@ k_rp_create_hdr_lanes(RpBatch b, const RpSetDev* __restrict__ sets, const int64_
   if (lane == 0) g1_to_wire(out + ProofView::d_off(), jac_to_aff(acc));
 }
 
-// Item thread per (proof, server i, digit j): V_ij, a_ij, Zv_ij (body in rp_device.cuh).
-__global__ void __launch_bounds__(64)
-k_rp_create_items(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
-                  const uint32_t* __restrict__ rnd, const size_t* __restrict__ rnd_off,
-                  const Fp12* __restrict__ tabGtB, const uint32_t* __restrict__ baseB_wire,
-                  const uint32_t* __restrict__ ct, uint32_t* __restrict__ proofs) {
-  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= b.items) return;
-  rp_create_item(b, sets, secret, rnd, rnd_off, tabGtB, baseB_wire, ct, proofs, t);
-}
-
 // Role-split creation: blockIdx.y = role (see rp_device.cuh).
 __global__ void __launch_bounds__(64)
 k_rp_create_roles(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
@@ -352,15 +341,6 @@ int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_se
                                                      (uint32_t*)d_proofs);
   return 1;
 }
-int launch_rp_create_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
-                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs) {
-  if (!b.items) return 0;
-  k_rp_create_items<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_rnd, d_rnd_off,
-                                                         (const Fp12*)d_tabGtB, (const uint32_t*)d_baseB_wire,
-                                                         (const uint32_t*)d_ct, (uint32_t*)d_proofs);
-  return 1;
-}
 
 // ------------------------------------------------------------------ verification (a-8)
 // Header thread per proof: parse, D check (lib/range/range_proof.go:520-529, :561). flags[p] starts at the
@@ -399,18 +379,9 @@ k_rp_verify_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __res
   if (!jac_eq_aff(Dp, D)) flags[p] = 0;
 }
 
-// Item thread per (proof, i, j): one pairing check (body in rp_device.cuh).
 #ifndef DRX_VERIFY_MINBLOCKS
 #define DRX_VERIFY_MINBLOCKS 5
 #endif
-__global__ void __launch_bounds__(64, DRX_VERIFY_MINBLOCKS)
-k_rp_verify_items(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __restrict__ tabB,
-                  const Fp12* __restrict__ tabGtB, const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags) {
-  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= b.items) return;
-  rp_verify_item(b, sets, tabB, tabGtB, proofs, flags, t);
-}
-
 __global__ void k_flags_to_bytes(size_t n, const uint32_t* __restrict__ flags, uint8_t* __restrict__ ok) {
   const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p < n) ok[p] = flags[p] ? 1 : 0;
@@ -421,19 +392,6 @@ int launch_rp_verify_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_se
   if (!b.n) return 0;
   k_rp_verify_hdr<<<grid_for(b.n, 128), 128, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const G1Aff*)d_tabP,
                                                      (const uint32_t*)d_proofs, d_flags);
-  return 1;
-}
-int launch_rp_verify_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
-                           const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags) {
-  if (!b.items) return 0;
-  static int smem = -1;
-  if (smem < 0) {
-    const char* e = getenv("DRX_VERIFY_SMEM");
-    smem = e ? atoi(e) : 0;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(k_rp_verify_items, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  }
-  k_rp_verify_items<<<grid_for(b.items, 64), 64, smem, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const Fp12*)d_tabGtB,
-                                                            (const uint32_t*)d_proofs, d_flags);
   return 1;
 }
 // Role-split verification: blockIdx.y = role.

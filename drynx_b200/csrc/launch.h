@@ -82,13 +82,8 @@ struct RpBatch {          // one create/verify call
 int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
                          const uint8_t* d_r, const uint8_t* d_ct, const uint8_t* d_rnd, const size_t* d_rnd_off,
                          const void* d_tabB, const void* d_tabP, const uint8_t* d_baseB_wire, uint8_t* d_proofs);
-int launch_rp_create_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
-                           const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs);
 int launch_rp_verify_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                          const void* d_tabP, const uint8_t* d_proofs, uint32_t* d_flags);
-int launch_rp_verify_items(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
-                           const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags);
 int launch_rp_flags(cudaStream_t st, size_t n, const uint32_t* d_flags, uint8_t* d_ok);
 // role-split item kernels (independent parts of one item in different thread blocks) + their finish kernels;
 // d_scratch holds rp_scratch_bytes(items) bytes (two GT elements per item)

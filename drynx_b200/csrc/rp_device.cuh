@@ -105,40 +105,6 @@ __device__ __forceinline__ bool locate_item(const RpBatch& b, const RpSetDev* se
 }
 
 
-// Item thread per (proof, server i, digit j): V_ij, a_ij, Zv_ij.
-__device__ __forceinline__ void rp_create_item(const RpBatch& b, const RpSetDev* __restrict__ sets,
-                                               const int64_t* __restrict__ secret, const uint32_t* __restrict__ rnd,
-                                               const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB,
-                                               const uint32_t* __restrict__ baseB_wire, const uint32_t* __restrict__ ct,
-                                               uint32_t* __restrict__ proofs, size_t t) {
-  size_t p, off;
-  int i, j, ns, nd;
-  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
-  uint32_t* out = proofs + off / 4;
-  const RpSetDev set = sets[b.d_set_id[p]];
-  const int u = set.u;
-  ProofView pv{ns, nd};
-  const uint32_t* rp = rnd + (b.d_proof_off ? rnd_off[p] / 4 : p * (size_t)nd * (3 + ns) * 8);
-  const uint32_t* row = rp + (size_t)j * (3 + ns) * 8;
-  const Scalar sj = sc_from_wire(row);
-  const Scalar tj = sc_from_wire(row + 8);
-  const Scalar v = sc_from_wire(row + 8 * (3 + i));
-  // the challenge is recomputed here rather than read from the header so that the header kernel can run
-  // concurrently on the side stream
-  const Scalar c = rp_challenge(baseB_wire, ct + 32 * p, set.sumY);
-  const uint32_t phi = rp_digit(secret[p], u, j);
-  const size_t tab = ((size_t)i * u + phi) * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES);
-  // V_ij = v * A_{i,phi}
-  const G2Jac V = comb_mul((const G2Aff*)set.tabA + tab, v);
-  g2_to_wire(out + pv.v_off(i, j), jac_to_aff(V));
-  // a_ij = e(B, A_{i,phi})^(-s_j v) * e(B, g2)^(t_j)
-  Fp12 a, g;
-  gt_comb_pow(a, (const Fp12*)set.tabGtA + tab, sc_neg(sc_mul(sj, v)));
-  gt_comb_pow(g, tabGtB, tj);
-  fp12_mul(a, a, g);
-  gt_to_wire(out + pv.a_off(i, j), a);
-  sc_to_wire(out + pv.zv_off(i, j), sc_sub(tj, sc_mul(c, v)));
-}
 
 
 // The same item split into independent roles that run in different thread blocks (three times the threads, a
@@ -398,37 +364,6 @@ __device__ __forceinline__ void rp_verify_finish(const RpBatch& b, const RpSetDe
   if (!fp12_eq(scratch[t].a, scratch[t].b)) atomicAnd(&flags[p], 0u);
 }
 
-// Item thread per (proof, i, j): e(c*Y_i - Zphi_j*B, V_ij) * e(B, g2)^Zv_ij == A_ij  (:540-549; the three
-// pairings of the reference collapse by bilinearity, the value compared is the same canonical GT element).
-__device__ __forceinline__ void rp_verify_item(const RpBatch& b, const RpSetDev* __restrict__ sets,
-                                               const G1Aff* __restrict__ tabB, const Fp12* __restrict__ tabGtB,
-                                               const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags,
-                                               size_t t) {
-  size_t p, off;
-  int i, j, ns, nd;
-  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
-  const uint32_t* in = proofs + off / 4;
-  const RpSetDev set = sets[b.d_set_id[p]];
-  ProofView pv{ns, nd};
-  G2Aff V;
-  Fp12 A;
-  bool ok = g2_from_wire(V, in + pv.v_off(i, j));
-  ok &= gt_from_wire(A, in + pv.a_off(i, j));
-  if (!ok) {
-    atomicAnd(&flags[p], 0u);
-    return;
-  }
-  const Scalar c = sc_from_wire(in + ProofView::c_off());
-  const Scalar zphi = sc_from_wire(in + pv.zphi_off(j));
-  const Scalar zv = sc_from_wire(in + pv.zv_off(i, j));
-  G1Jac P1 = comb_mul((const G1Aff*)set.tabY + (size_t)i * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES), c);
-  P1 = jac_add(P1, comb_mul(tabB, sc_neg(zphi)));
-  Fp12 e, g;
-  pairing(e, jac_to_aff(P1), V);
-  gt_comb_pow(g, tabGtB, zv);
-  fp12_mul(e, e, g);
-  if (!fp12_eq(e, A)) atomicAnd(&flags[p], 0u);
-}
 
 
 }  // namespace drx
