@@ -85,6 +85,14 @@ class Backend:
         _lib.check(self.lib.drx_encrypt(self.h, m.size, _ptr(m), _ptr(r), _ptr(ct)))
         return ct
 
+    def encrypt_scalar_vector(self, m, r):
+        """libunlynx.EncryptScalar per element: m and r are n*32 bytes of big-endian scalars -> n*128 bytes."""
+        m, r = _u8(m), _u8(r)
+        assert m.size == r.size and m.size % 32 == 0
+        ct = np.empty(4 * m.size, dtype=np.uint8)
+        _lib.check(self.lib.drx_encrypt_scalar(self.h, m.size // 32, _ptr(m), _ptr(r), _ptr(ct)))
+        return ct
+
     def aggregate(self, vectors):
         """CipherVector.Add over a list of serialised CipherVectors (each v*128 bytes)."""
         vs = [_u8(v) for v in vectors]

@@ -439,6 +439,27 @@ int drx_encrypt(drx_ctx* c, size_t n, const int64_t* m, const uint8_t* r, uint8_
   return 0;
 }
 
+int drx_encrypt_scalar(drx_ctx* c, size_t n, const uint8_t* m, const uint8_t* r, uint8_t* ct) {
+  if (!c) return fail(-1, "null context");
+  if (n == 0) return 0;
+  if (!m || !r || !ct) return fail(-1, "drx_encrypt_scalar: null buffer");
+  Guard g(c);
+  if (!c->have_pub) return fail(-1, "drx_encrypt_scalar: call drx_set_pubkey first");
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t om = a.plan(n * 32), orr = a.plan(n * 32), oc = a.plan(n * 128);
+  RET(a.commit());
+  CU(cudaMemcpyAsync(a.at<void>(om), m, n * 32, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(a.at<void>(orr), r, n * 32, cudaMemcpyHostToDevice, c->stream));
+  timed(c, "k_encrypt", [&] {
+    return launch_encrypt_scalar(c->stream, n, a.at<uint8_t>(om), a.at<uint8_t>(orr), c->tabB.p, c->tabP.p, a.at<uint8_t>(oc));
+  });
+  RET(check_launch("encrypt_scalar"));
+  CU(cudaMemcpyAsync(ct, a.at<void>(oc), n * 128, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
 static int aggregate_on_device(drx_ctx* c, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
                                uint8_t* d_out) {
   timed(c, "k_agg_partial", [&] { return launch_agg_partial(c->stream, ndp, v, d_cts, d_scratch, slices, (int*)c->bad.p); });

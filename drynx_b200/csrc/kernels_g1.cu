@@ -87,6 +87,26 @@ k_encrypt(size_t n, const int64_t* __restrict__ m, const uint32_t* __restrict__ 
   store_pair_wire(ct + 32 * i, K, C);
 }
 
+// libunlynx.EncryptScalar: the message is a full scalar (32 comb windows instead of 8)
+__global__ void __launch_bounds__(128)
+k_encrypt_scalar(size_t n, const uint32_t* __restrict__ m, const uint32_t* __restrict__ r,
+                 const G1Aff* __restrict__ tabB, const G1Aff* __restrict__ tabP, uint32_t* __restrict__ ct) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const Scalar ri = sc_from_wire(r + 8 * i);
+  const G1Jac K = comb_mul(tabB, ri);
+  const G1Jac S = comb_mul(tabP, ri);
+  const G1Jac M = comb_mul(tabB, sc_from_wire(m + 8 * i));
+  store_pair_wire(ct + 32 * i, K, jac_add(S, M));
+}
+int launch_encrypt_scalar(cudaStream_t st, size_t n, const uint8_t* d_m, const uint8_t* d_r, const void* d_tabB,
+                          const void* d_tabP, uint8_t* d_ct) {
+  if (!n) return 0;
+  k_encrypt_scalar<<<grid_for(n, 128), 128, 0, st>>>(n, (const uint32_t*)d_m, (const uint32_t*)d_r, (const G1Aff*)d_tabB,
+                                                    (const G1Aff*)d_tabP, (uint32_t*)d_ct);
+  return 1;
+}
+
 // Small batches: eight lanes per ciphertext. Lanes 0-3 walk every fourth window of r*B, lanes 4-7 every fourth
 // window of r*K plus their share of the message windows of m*B; a two-level butterfly of full additions joins
 // each half, lane 0 fetches C from lane 4 and serialises both points with one shared inversion. Each lane runs

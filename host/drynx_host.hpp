@@ -142,6 +142,17 @@ inline std::pair<CipherText, Scalar> EncryptIntGetR(const Point& pubkey, int64_t
 }
 inline CipherText EncryptInt(const Point& pubkey, int64_t v) { return EncryptIntGetR(pubkey, v).first; }
 
+// EncryptScalar per element (lib/encoding/OR_AND.go:52,105): the message is a scalar, one batched call
+inline CipherVector EncryptScalarVector(const Point& pubkey, const std::vector<Scalar>& ms) {
+  use_pubkey(pubkey);
+  std::vector<Scalar> rs(ms.size());
+  for (auto& r : rs) r = drynx::pick();
+  CipherVector cv(ms.size());
+  if (!ms.empty()) drynx::check(drx_encrypt_scalar(Gpu::get().ctx(), ms.size(), ms[0].b, rs[0].b, cv[0].b));
+  return cv;
+}
+inline CipherText EncryptScalar(const Point& pubkey, const Scalar& m) { return EncryptScalarVector(pubkey, {m})[0]; }
+
 // CipherVector.Add over any number of vectors (the root node's fold, protocols/data_collection_protocol.go:145-166).
 inline CipherVector AddAll(const std::vector<CipherVector>& vs) {
   if (vs.empty()) return {};
@@ -166,6 +177,11 @@ inline std::vector<int64_t> DecryptIntVector(const Scalar& sk, const CipherVecto
 inline std::vector<int64_t> DecryptIntVectorWithNeg(const Scalar& sk, const CipherVector& cv) { return DecryptIntVectorImpl(sk, cv, true); }
 inline int64_t DecryptInt(const Scalar& sk, const CipherText& c) { return DecryptIntVector(sk, {c})[0]; }
 inline int64_t DecryptIntWithNeg(const Scalar& sk, const CipherText& c) { return DecryptIntVectorWithNeg(sk, {c})[0]; }
+inline std::vector<int64_t> DecryptCheckZeroVector(const Scalar& sk, const CipherVector& cv) {
+  std::vector<int64_t> out(cv.size());
+  if (!cv.empty()) drynx::check(drx_decrypt_check_zero(Gpu::get().ctx(), cv.size(), sk.b, cv[0].b, out.data()));
+  return out;
+}
 inline int64_t DecryptCheckZero(const Scalar& sk, const CipherText& c) {
   int64_t out;
   drynx::check(drx_decrypt_check_zero(Gpu::get().ctx(), 1, sk.b, c.b, &out));
@@ -422,6 +438,174 @@ inline Encoded EncodeFreqCount(const std::vector<int64_t>& input, int64_t min, i
 }
 inline std::vector<int64_t> DecodeFreqCount(const CipherVector& result, const Scalar& secKey) {
   return libunlynx::DecryptIntVectorWithNeg(secKey, result);
+}
+
+// ---- bits under OR / AND (OR_AND.go:17-144). Without signatures a set OR-bit (a cleared AND-bit) is the encryption
+// of a random non-zero scalar and the other value the encryption of zero; with signatures it is the integer 1 / 0
+// (AND: the complement) so that the range proof applies. A whole vector of bits is one batched encryption.
+enum class BitOp { Or, And };
+inline Scalar nonzero_scalar() {
+  for (;;) {
+    Scalar s = drynx::pick();
+    for (int i = 0; i < 32; i++)
+      if (s.b[i]) return s;
+  }
+}
+inline Encoded EncodeBits(const std::vector<bool>& input, BitOp op, const Point& pubKey, const std::vector<SignatureColumn>* sigs,
+                          const Ranges* lu) {
+  std::vector<int64_t> clear(input.size());
+  for (size_t i = 0; i < input.size(); i++)  // OR: toEncrypt = input ? 1 : 0 (:30-33); AND: input ? 0 : 1 (:83-86)
+    clear[i] = sigs ? ((op == BitOp::Or) == input[i] ? 1 : 0) : (op == BitOp::Or ? 0 : 1);
+  if (sigs) return encrypt_and_describe(clear, pubKey, sigs, lu);
+  std::vector<Scalar> ms(input.size());
+  for (size_t i = 0; i < input.size(); i++) {
+    const bool random = op == BitOp::Or ? input[i] : !input[i];  // :42, :95
+    if (random) ms[i] = nonzero_scalar(); else memset(ms[i].b, 0, 32);
+  }
+  Encoded e;
+  e.clear = clear;  // the reference returns its initial toEncrypt here (0 for OR, 1 for AND), whatever the bit
+  e.enc = libunlynx::EncryptScalarVector(pubKey, ms);
+  return e;
+}
+inline std::pair<CipherText, int64_t> EncodeBitOr(bool input, const Point& pubKey) {
+  auto e = EncodeBits({input}, BitOp::Or, pubKey, nullptr, nullptr);
+  return {e.enc[0], e.clear[0]};
+}
+inline std::pair<CipherText, int64_t> EncodeBitAND(bool input, const Point& pubKey) {
+  auto e = EncodeBits({input}, BitOp::And, pubKey, nullptr, nullptr);
+  return {e.enc[0], e.clear[0]};
+}
+inline Encoded EncodeBitOrWithProof(bool input, const Point& pubKey, const SignatureColumn& sigs, int64_t l, int64_t u) {
+  std::vector<SignatureColumn> s = {sigs};
+  Ranges lu = {{u, l}};
+  return EncodeBits({input}, BitOp::Or, pubKey, &s, &lu);
+}
+inline Encoded EncodeBitANDWithProof(bool input, const Point& pubKey, const SignatureColumn& sigs, int64_t l, int64_t u) {
+  std::vector<SignatureColumn> s = {sigs};
+  Ranges lu = {{u, l}};
+  return EncodeBits({input}, BitOp::And, pubKey, &s, &lu);
+}
+inline bool DecodeBitOR(const CipherText& result, const Scalar& secKey) { return libunlynx::DecryptCheckZero(secKey, result) != 0; }
+inline bool DecodeBitAND(const CipherText& result, const Scalar& secKey) { return libunlynx::DecryptCheckZero(secKey, result) == 0; }
+inline bool LocalResultOR(const std::vector<bool>& input) {
+  for (bool b : input)
+    if (b) return true;
+  return false;
+}
+inline bool LocalResultAND(const std::vector<bool>& input) {
+  for (bool b : input)
+    if (!b) return false;
+  return true;
+}
+
+// ---- min / max (min_max.go:12-146): one OR-bit (min) or AND-bit (max) per value of [min, max]; bit i is
+// "i >= local extreme". The reference takes (max, min) in that order.
+inline Encoded EncodeMinWithProofs(const std::vector<int64_t>& input, int64_t max, int64_t min, const Point& pubKey,
+                                   const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  int64_t localMin = input[0];
+  for (int64_t v : input) localMin = v < localMin ? v : localMin;
+  std::vector<bool> bits((size_t)(max - min + 1));
+  for (int64_t i = min; i <= max; i++) bits[(size_t)(i - min)] = i >= localMin;
+  return EncodeBits(bits, BitOp::Or, pubKey, sigs, lu);
+}
+inline Encoded EncodeMin(const std::vector<int64_t>& input, int64_t max, int64_t min, const Point& pubKey) {
+  return EncodeMinWithProofs(input, max, min, pubKey, nullptr, nullptr);
+}
+inline int64_t DecodeMin(const CipherVector& result, int64_t globalMin, const Scalar& secKey) {
+  auto z = libunlynx::DecryptCheckZeroVector(secKey, result);
+  for (size_t i = 0; i < z.size(); i++)
+    if (z[i] != 0) return (int64_t)i + globalMin;  // first set OR-bit
+  return 0;
+}
+inline Encoded EncodeMaxWithProofs(const std::vector<int64_t>& input, int64_t max, int64_t min, const Point& pubKey,
+                                   const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  int64_t localMax = input[0];
+  for (int64_t v : input) localMax = v > localMax ? v : localMax;
+  std::vector<bool> bits((size_t)(max - min + 1));
+  for (int64_t i = min; i <= max; i++) bits[(size_t)(i - min)] = i >= localMax;
+  return EncodeBits(bits, BitOp::And, pubKey, sigs, lu);
+}
+inline Encoded EncodeMax(const std::vector<int64_t>& input, int64_t max, int64_t min, const Point& pubKey) {
+  return EncodeMaxWithProofs(input, max, min, pubKey, nullptr, nullptr);
+}
+inline int64_t DecodeMax(const CipherVector& result, int64_t globalMin, const Scalar& secKey) {
+  auto z = libunlynx::DecryptCheckZeroVector(secKey, result);
+  for (size_t i = 0; i < z.size(); i++)
+    if (z[i] == 0) return (int64_t)i + globalMin;  // first set AND-bit
+  return 0;
+}
+
+// ---- set union / intersection (set_union_intersection.go:12-169): membership bits over [min, max]
+inline std::vector<int64_t> Unique(const std::vector<int64_t>& in) {
+  std::vector<int64_t> out;
+  for (int64_t v : in) {
+    bool seen = false;
+    for (int64_t w : out) seen |= w == v;
+    if (!seen) out.push_back(v);
+  }
+  return out;
+}
+inline Encoded EncodeSetWithProofs(const std::vector<int64_t>& input, int64_t min, int64_t max, BitOp op, const Point& pubKey,
+                                   const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  std::vector<bool> bits((size_t)(max - min + 1), false);
+  for (int64_t v : Unique(input)) bits[(size_t)(v - min)] = true;
+  return EncodeBits(bits, op, pubKey, sigs, lu);
+}
+inline Encoded EncodeUnion(const std::vector<int64_t>& input, int64_t min, int64_t max, const Point& pubKey) {
+  return EncodeSetWithProofs(input, min, max, BitOp::Or, pubKey, nullptr, nullptr);
+}
+inline Encoded EncodeInter(const std::vector<int64_t>& input, int64_t min, int64_t max, const Point& pubKey) {
+  return EncodeSetWithProofs(input, min, max, BitOp::And, pubKey, nullptr, nullptr);
+}
+inline std::vector<int64_t> DecodeUnion(const CipherVector& result, const Scalar& secKey) {
+  auto z = libunlynx::DecryptCheckZeroVector(secKey, result);
+  for (auto& v : z) v = v != 0 ? 1 : 0;
+  return z;
+}
+inline std::vector<int64_t> DecodeInter(const CipherVector& result, const Scalar& secKey) {
+  auto z = libunlynx::DecryptCheckZeroVector(secKey, result);
+  for (auto& v : z) v = v == 0 ? 1 : 0;
+  return z;
+}
+
+// ---- cosine similarity (cosim.go:11-86): [sum a, sum b, sum a^2, sum b^2, sum ab]
+inline Encoded EncodeCosimWithProofs(const std::vector<int64_t>& rijs, const std::vector<int64_t>& riks, const Point& pubKey,
+                                     const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  int64_t sa = 0, sb = 0, sa2 = 0, sb2 = 0, sab = 0;
+  for (size_t i = 0; i < rijs.size(); i++) {
+    const int64_t a = rijs[i], b = riks[i];
+    sa += a; sb += b; sa2 += a * a; sb2 += b * b; sab += a * b;
+  }
+  return encrypt_and_describe({sa, sb, sa2, sb2, sab}, pubKey, sigs, lu);
+}
+inline Encoded EncodeCosim(const std::vector<int64_t>& rijs, const std::vector<int64_t>& riks, const Point& pubKey) {
+  return EncodeCosimWithProofs(rijs, riks, pubKey, nullptr, nullptr);
+}
+inline double DecodeCosim(const CipherVector& result, const Scalar& secKey) {
+  auto c = libunlynx::DecryptIntVectorWithNeg(secKey, result);
+  return (double)c[4] / (std::sqrt((double)c[2]) * std::sqrt((double)c[3]));
+}
+
+// ---- model evaluation, R^2 (model_evaluation.go:11-96): [N, sum y, sum y^2, sum (pred - y)^2]
+inline Encoded EncodeModelEvaluationWithProofs(const std::vector<int64_t>& y, const std::vector<int64_t>& preds, const Point& pubKey,
+                                               const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
+  int64_t sy = 0, sy2 = 0, sd2 = 0;
+  for (size_t i = 0; i < y.size(); i++) {
+    sy += y[i];
+    sy2 += y[i] * y[i];
+    sd2 += (preds[i] - y[i]) * (preds[i] - y[i]);
+  }
+  Encoded e = encrypt_and_describe({(int64_t)y.size(), sy, sy2, sd2}, pubKey, sigs, lu);
+  e.clear = {0};  // the reference returns []int64{0} as the clear vector (:63, :76)
+  return e;
+}
+inline Encoded EncodeModelEvaluation(const std::vector<int64_t>& y, const std::vector<int64_t>& preds, const Point& pubKey) {
+  return EncodeModelEvaluationWithProofs(y, preds, pubKey, nullptr, nullptr);
+}
+inline double DecodeModelEvaluation(const CipherVector& result, const Scalar& secKey) {
+  auto c = libunlynx::DecryptIntVectorWithNeg(secKey, result);
+  const double B = (double)c[2] - (double)(c[1] * c[1] / c[0]);  // integer division, as in the reference (:93)
+  return 1.0 - (double)c[3] / B;
 }
 
 // ---- linear regression, d dimensions (linear_regression_dims.go:23-106)

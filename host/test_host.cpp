@@ -160,6 +160,80 @@ static void TestLogisticRegressionAggregation() {  // logistic_regression_test.g
   EXPECT(libunlynx::DecryptCheckZero(keys.Private, libunlynx::EncryptInt(keys.Public, 7)) == 1);
 }
 
+static void TestEncodeDecodeBit() {  // OR_AND_test.go:14-38 and :40-69 (u = 2, l = 1, one server)
+  auto keys = drynx::NewKeyPair();
+  for (auto in : {std::vector<bool>{false, true, false}, std::vector<bool>{true, true}, std::vector<bool>{false, false}}) {
+    const bool expectOr = LocalResultOR(in), expectAnd = LocalResultAND(in);
+    EXPECT(DecodeBitOR(EncodeBitOr(expectOr, keys.Public).first, keys.Private) == expectOr);
+    EXPECT(DecodeBitAND(EncodeBitAND(expectAnd, keys.Public).first, keys.Private) == expectAnd);
+    const int64_t u = 2, l = 1;
+    auto col = libdrynxrange::RegisterColumn({libdrynxrange::InitRangeProofSignature(u)}, u);
+    auto eo = EncodeBitOrWithProof(expectOr, keys.Public, col, l, u), ea = EncodeBitANDWithProof(expectAnd, keys.Public, col, l, u);
+    EXPECT(DecodeBitOR(eo.enc[0], keys.Private) == expectOr);
+    EXPECT(DecodeBitAND(ea.enc[0], keys.Private) == expectAnd);
+    EXPECT(libdrynxrange::RangeProofVerification(libdrynxrange::CreatePredicateRangeProofForAllServ(eo.proofs[0]), u, l, col, keys.Public));
+    EXPECT(libdrynxrange::RangeProofVerification(libdrynxrange::CreatePredicateRangeProofForAllServ(ea.proofs[0]), u, l, col, keys.Public));
+  }
+}
+static void TestEncodeDecodeMinMax() {  // min_max_test.go:14-47 (401 bits) and :49-116 (two servers, u = 2, l = 1)
+  auto keys = drynx::NewKeyPair();
+  std::vector<int64_t> in = {1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 12, 3, 2, 15, 6, 17, 2, -5, 72, -20, 100, -190, 200};
+  const int64_t gmax = 200, gmin = -200;
+  EXPECT(DecodeMin(EncodeMin(in, gmax, gmin, keys.Public).enc, gmin, keys.Private) == -190);
+  EXPECT(DecodeMax(EncodeMax(in, gmax, gmin, keys.Public).enc, gmin, keys.Private) == 200);
+  // the aggregate of two providers' encodings decodes to the global extreme (what the protocol does with them)
+  auto a = EncodeMin({5, 9}, 20, 0, keys.Public), b = EncodeMin({7, 3, 11}, 20, 0, keys.Public);
+  EXPECT(DecodeMin(libunlynx::Add(a.enc, b.enc), 0, keys.Private) == 3);
+  auto c = EncodeMax({5, 9}, 20, 0, keys.Public), d = EncodeMax({7, 3, 11}, 20, 0, keys.Public);
+  EXPECT(DecodeMax(libunlynx::Add(c.enc, d.enc), 0, keys.Private) == 11);
+  const int64_t u = 2, l = 1, lo = 0, hi = 10;
+  std::vector<libdrynxrange::SignatureColumn> sigs;
+  Ranges lu;
+  for (int64_t i = lo; i <= hi; i++) {
+    sigs.push_back(libdrynxrange::RegisterColumn({libdrynxrange::InitRangeProofSignature(u), libdrynxrange::InitRangeProofSignature(u)}, u));
+    lu.push_back({u, l});
+  }
+  auto emin = EncodeMinWithProofs({1, 2, 10}, hi, lo, keys.Public, &sigs, &lu);
+  auto emax = EncodeMaxWithProofs({1, 2, 10}, hi, lo, keys.Public, &sigs, &lu);
+  EXPECT(DecodeMin(emin.enc, lo, keys.Private) == 1);
+  EXPECT(DecodeMax(emax.enc, lo, keys.Private) == 10);
+  libdrynxrange::RangeProofList lmin, lmax;
+  lmin.Data = libdrynxrange::CreatePredicateRangeProofListForAllServers(emin.proofs);
+  lmax.Data = libdrynxrange::CreatePredicateRangeProofListForAllServers(emax.proofs);
+  EXPECT(libdrynxrange::RangeProofListVerification(lmin, lu, sigs, keys.Public, 1.0));
+  EXPECT(libdrynxrange::RangeProofListVerification(lmax, lu, sigs, keys.Public, 1.0));
+}
+static void TestEncodeDecodeUnionInter() {  // set_union_intersection_test.go:15-50
+  auto keys = drynx::NewKeyPair();
+  std::vector<int64_t> in = {1, 2, 3, 1, 5, 1, 2, 3};
+  const int64_t min = 0, max = 10;
+  std::vector<int64_t> expect((size_t)(max - min + 1), 0);
+  for (auto v : Unique(in)) expect[(size_t)(v - min)] = 1;
+  EXPECT(Unique(in) == std::vector<int64_t>({1, 2, 3, 5}));
+  EXPECT(DecodeUnion(EncodeUnion(in, min, max, keys.Public).enc, keys.Private) == expect);
+  EXPECT(DecodeInter(EncodeInter(in, min, max, keys.Public).enc, keys.Private) == expect);
+  // two providers: union = either has it, intersection = both have it
+  auto u1 = EncodeUnion({1, 2}, min, max, keys.Public), u2 = EncodeUnion({2, 7}, min, max, keys.Public);
+  EXPECT(DecodeUnion(libunlynx::Add(u1.enc, u2.enc), keys.Private) == std::vector<int64_t>({0, 1, 1, 0, 0, 0, 0, 1, 0, 0, 0}));
+  auto i1 = EncodeInter({1, 2}, min, max, keys.Public), i2 = EncodeInter({2, 7}, min, max, keys.Public);
+  EXPECT(DecodeInter(libunlynx::Add(i1.enc, i2.enc), keys.Private) == std::vector<int64_t>({0, 0, 1, 0, 0, 0, 0, 0, 0, 0, 0}));
+}
+static void TestEncodeDecodeCosimAndModelEvaluation() {  // cosim_test.go:17-55, model_evaluation_test.go:14-50
+  auto keys = drynx::NewKeyPair();
+  libunlynx::CreateDecryptionTable(10000, keys.Public, keys.Private);
+  std::vector<int64_t> a = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 12};
+  auto e = EncodeCosim(a, a, keys.Public);
+  EXPECT(e.clear == std::vector<int64_t>({57, 57, 429, 429, 429}));
+  EXPECT(DecodeCosim(e.enc, keys.Private) == 429.0 / (std::sqrt(429.0) * std::sqrt(429.0)));
+  std::vector<int64_t> y = {1, 2, 3, 4, 5, 6, 7, 8, 1, 67, -72}, preds = {32, 12, 23, 4, 13, -72, 12, 8, 23, 67, 2};
+  int64_t sy = 0, sy2 = 0, sd2 = 0;
+  for (size_t i = 0; i < y.size(); i++) { sy += y[i]; sy2 += y[i] * y[i]; sd2 += (preds[i] - y[i]) * (preds[i] - y[i]); }
+  const double B = (double)sy2 - (double)(sy * sy / (int64_t)y.size());
+  auto m = EncodeModelEvaluation(y, preds, keys.Public);
+  EXPECT(m.clear == std::vector<int64_t>({0}));
+  EXPECT(DecodeModelEvaluation(m.enc, keys.Private) == 1.0 - (double)sd2 / B);
+}
+
 int main(int argc, char** argv) {
   const bool cpu_only = argc > 1 && !strcmp(argv[1], "--cpu");
   TestComputeApproxCoefficients();
@@ -174,6 +248,10 @@ int main(int argc, char** argv) {
       TestEncodeDecodeFrequencyCountWithProofs();
       TestEncodeDecodeLinearRegressionDims();
       TestLogisticRegressionAggregation();
+      TestEncodeDecodeBit();
+      TestEncodeDecodeMinMax();
+      TestEncodeDecodeUnionInter();
+      TestEncodeDecodeCosimAndModelEvaluation();
     } catch (const drynx::Error& e) {
       printf("FAIL: exception %d: %s\n", e.code, e.what());
       failures++;

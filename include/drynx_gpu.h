@@ -77,6 +77,9 @@ int drx_set_pubkey(drx_ctx* ctx, const uint8_t P[64]);
  * logistic_regression.go:420): ct[i] = (r_i*B) || (m_i*B + r_i*P). Negative m maps to n-|m| (SetInt64). */
 int drx_encrypt(drx_ctx* ctx, size_t n, const int64_t* m, const uint8_t* r /*n*32*/, uint8_t* ct /*n*128*/);
 int drx_encrypt_dev(drx_ctx* ctx, size_t n, const int64_t* d_m, const uint8_t* d_r, uint8_t* d_ct);
+/* libunlynx.EncryptScalar (call sites lib/encoding/OR_AND.go:52,105: the bit encodings of OR / AND / min / max /
+ * set union / intersection): the message is a scalar (32 bytes big-endian, reduced mod n), C = m*B + r*P. */
+int drx_encrypt_scalar(drx_ctx* ctx, size_t n, const uint8_t* m /*n*32*/, const uint8_t* r /*n*32*/, uint8_t* ct /*n*128*/);
 
 /* CipherVector.FromBytes + CipherVector.Add over all data providers
  * (protocols/data_collection_protocol.go:145-166, lib/structs.go:338-350): out[j] = sum_d cts[d][j].

@@ -288,6 +288,13 @@ def encrypt(pub, m, r):
     return g1_to_bytes(K) + g1_to_bytes(C)
 
 
+def encrypt_scalar(pub, m, r):
+    """libunlynx.EncryptScalar: the message is a full scalar, C = m*B + r*P (lib/encoding/OR_AND.go:52,105)."""
+    K = g1_mul(r, G1_GEN)
+    C = g1_add(g1_mul(m % n, G1_GEN), g1_mul(r, pub))
+    return g1_to_bytes(K) + g1_to_bytes(C)
+
+
 def decrypt_point(sk, ct):
     K, C = g1_from_bytes(ct[:64]), g1_from_bytes(ct[64:128])
     return g1_add(C, g1_neg(g1_mul(sk, K)))

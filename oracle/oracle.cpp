@@ -1168,6 +1168,20 @@ static void encrypt_one(uint8_t ct[128], const curvePoint& pub, int64_t m, const
   g1_marshal(ct + 64, C);
 }
 
+// libunlynx.EncryptScalar: IntToPoint replaced by scalar * B (lib/encoding/OR_AND.go:52,105)
+static void encrypt_scalar_one(uint8_t ct[128], const curvePoint& pub, const uint8_t m32[32], const uint8_t r32[32]) {
+  Sc r, ms;
+  sc_from_bytes(r, r32);
+  sc_from_bytes(ms, m32);
+  curvePoint K, S, M, C;
+  K.Mul(curveGen, r.v);
+  S.Mul(pub, r.v);
+  M.Mul(curveGen, ms.v);
+  C.Add(S, M);
+  g1_marshal(ct, K);
+  g1_marshal(ct + 64, C);
+}
+
 struct DlogTable {  // PointToInt map keyed by the marshalled point, grown lazily like discreteLog
   std::unordered_map<std::string, int64_t> map;
   curvePoint currentGreatestM;
@@ -1412,6 +1426,14 @@ int orc_encrypt(size_t n, const int64_t* m, const uint8_t* r, const uint8_t* P, 
   curvePoint pub;
   if (!g1_unmarshal(pub, P)) return -1;
   parallel_for(n, threads, [&](size_t i) { encrypt_one(ct + 128 * i, pub, m[i], r + 32 * i); });
+  return 0;
+}
+
+int orc_encrypt_scalar(size_t n, const uint8_t* m, const uint8_t* r, const uint8_t* P, uint8_t* ct, int threads) {
+  ensure_init();
+  curvePoint pub;
+  if (!g1_unmarshal(pub, P)) return -2;
+  parallel_for(n, threads, [&](size_t i) { encrypt_scalar_one(ct + 128 * i, pub, m + 32 * i, r + 32 * i); });
   return 0;
 }
 

@@ -74,6 +74,14 @@ class Oracle:
         assert self.lib.orc_encrypt(ctypes.c_size_t(m.size), self._p(m), self._p(r), bytes(P), self._p(ct), threads) == 0
         return ct.tobytes()
 
+    def encrypt_scalar(self, P, m, r, threads=1):
+        m = np.frombuffer(bytes(m), np.uint8).copy()
+        r = np.frombuffer(bytes(r), np.uint8).copy()
+        n = m.size // 32
+        ct = np.zeros(128 * n, np.uint8)
+        assert self.lib.orc_encrypt_scalar(ctypes.c_size_t(n), self._p(m), self._p(r), bytes(P), self._p(ct), threads) == 0
+        return ct.tobytes()
+
     def aggregate(self, vectors, threads=1):
         v = len(vectors[0]) // 128
         cts = np.frombuffer(b''.join(bytes(x) for x in vectors), np.uint8).copy()

@@ -112,6 +112,24 @@ def test_encrypt_lane_split_and_one_thread_kernels_agree(backend, oracle, rng):
     assert one[:128 * 64] == oracle.encrypt(P, [int(x) for x in ms[:64]], rb[:32 * 64], threads=8)
 
 
+def test_encrypt_scalar_matches_oracle_and_definition(backend, oracle, rng):
+    """libunlynx.EncryptScalar (OR_AND.go:52,105): full-width scalar messages, incl. 0, n-1 and an unreduced value."""
+    sk, P = _keys(rng)
+    backend.set_pubkey(P)
+    ms = [0, 1, R.n - 1, R.n + 5, 2 ** 255] + [rng.scalar() for _ in range(40)]
+    rs = [rng.scalar() for _ in ms]
+    mb = b''.join(m.to_bytes(32, 'big') for m in ms)
+    rb = b''.join(r.to_bytes(32, 'big') for r in rs)
+    got = backend.encrypt_scalar_vector(mb, rb).tobytes()
+    assert got == oracle.encrypt_scalar(P, mb, rb, threads=8)
+    Pp = R.g1_from_bytes(P)
+    for i in (0, 2, 3, 7):
+        assert got[128 * i:128 * i + 128] == R.encrypt_scalar(Pp, ms[i], rs[i])
+    # DecryptCheckZero semantics of the OR / AND encodings: zero scalar <-> identity after decryption
+    z = backend.decrypt_check_zero(sk.to_bytes(32, 'big'), got[:128 * 6])
+    assert list(z) == [0, 1, 1, 1, 1, 1]
+
+
 def test_reduce_rows_host_buffers(backend):
     """drx_reduce_rows against the Go loops' arithmetic (sum.go:19-23, mean.go:19-24, variance.go:19-27), wrap-around
     of int64 included, ragged sizes and an empty provider list."""

@@ -58,6 +58,18 @@ def test_encrypt_matches_definition(oracle, rng):
         assert ct[128 * i:128 * i + 128] == R.encrypt(P, m, r)
 
 
+def test_encrypt_scalar_matches_definition(oracle, rng):
+    """libunlynx.EncryptScalar (lib/encoding/OR_AND.go:52,105): scalar messages incl. zero and an unreduced value."""
+    sk = rng.scalar()
+    Pp = R.g1_mul(sk, R.G1_GEN)
+    ms = [0, 1, R.n - 1, R.n + 3, rng.scalar()]
+    rs = [rng.scalar() for _ in ms]
+    got = oracle.encrypt_scalar(R.g1_to_bytes(Pp), b''.join(m.to_bytes(32, 'big') for m in ms),
+                                b''.join(r.to_bytes(32, 'big') for r in rs), threads=2)
+    assert got == b''.join(R.encrypt_scalar(Pp, m, r) for m, r in zip(ms, rs))
+    assert list(oracle.decrypt_check_zero(sk.to_bytes(32, 'big'), got)) == [0, 1, 1, 1, 1]
+
+
 def test_sum_round_trip_like_reference_test(oracle, rng):
     """lib/encoding/sum_test.go:15-31: inputs {0..9, -12000} -> -11955 after encrypt/decrypt."""
     sk = rng.scalar()
