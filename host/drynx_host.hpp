@@ -822,4 +822,58 @@ inline Encoded EncodeLogisticRegression(const std::vector<std::vector<double>>& 
   return EncodeLogisticRegressionWithProofs(xData, yData, lr, pubKey, nullptr, nullptr);
 }
 
+// ---- the dispatcher (encode_decode.go:14-160 Encode, :163-240 Decode): what a data provider / the querier calls
+struct Operation {  // the fields of libdrynx.Operation this path reads
+  std::string NameOp;
+  int64_t QueryMin = 0, QueryMax = 0;
+};
+inline Encoded Encode(const std::vector<std::vector<int64_t>>& datas, const Point& pubKey, const std::vector<SignatureColumn>* signatures,
+                      const Ranges* ranges, const Operation& operation) {
+  const bool withProofs = signatures && ranges && !signatures->empty() && !ranges->empty();
+  const std::vector<SignatureColumn>* sg = withProofs ? signatures : nullptr;
+  const Ranges* lu = withProofs ? ranges : nullptr;
+  const std::string& op = operation.NameOp;
+  if (op == "sum") return EncodeSumWithProofs(datas[0], pubKey, sg, lu);
+  if (op == "cosim") return EncodeCosimWithProofs(datas[0], datas[1], pubKey, sg, lu);
+  if (op == "mean") return EncodeMeanWithProofs(datas[0], pubKey, sg, lu);
+  if (op == "variance") return EncodeVarianceWithProofs(datas[0], pubKey, sg, lu);
+  if (op == "lin_reg") {  // datas is column-major: d-1 feature columns, then y (:56-66)
+    const size_t d = datas.size(), n = datas[0].size();
+    std::vector<std::vector<int64_t>> X(n, std::vector<int64_t>(d - 1));
+    std::vector<int64_t> y(n);
+    for (size_t j = 0; j < n; j++) {
+      for (size_t i = 0; i + 1 < d; i++) X[j][i] = datas[i][j];
+      y[j] = datas[d - 1][j];
+    }
+    return EncodeLinearRegressionDimsWithProofs(X, y, pubKey, sg, lu);
+  }
+  if (op == "frequencyCount") return EncodeFreqCountWithProofs(datas[0], operation.QueryMin, operation.QueryMax, pubKey, sg, lu);
+  if (op == "bool_AND") return EncodeBits({datas[0][0] == 1}, BitOp::And, pubKey, sg, lu);
+  if (op == "bool_OR") return EncodeBits({datas[0][0] == 1}, BitOp::Or, pubKey, sg, lu);
+  if (op == "min") return EncodeMinWithProofs(datas[0], operation.QueryMax, operation.QueryMin, pubKey, sg, lu);
+  if (op == "max") return EncodeMaxWithProofs(datas[0], operation.QueryMax, operation.QueryMin, pubKey, sg, lu);
+  if (op == "union") return EncodeSetWithProofs(datas[0], operation.QueryMin, operation.QueryMax, BitOp::Or, pubKey, sg, lu);
+  if (op == "inter") return EncodeSetWithProofs(datas[0], operation.QueryMin, operation.QueryMax, BitOp::And, pubKey, sg, lu);
+  if (op == "MLeval") return EncodeModelEvaluationWithProofs(datas[0], datas[1], pubKey, sg, lu);
+  return Encoded{};  // unknown operation: empty response, as the Go switch falls through
+}
+inline std::vector<double> Decode(const CipherVector& ciphers, const Scalar& secKey, const Operation& operation) {
+  const std::string& op = operation.NameOp;
+  auto as_doubles = [](const std::vector<int64_t>& v) { return std::vector<double>(v.begin(), v.end()); };
+  if (op == "sum") return {(double)DecodeSum(ciphers[0], secKey)};
+  if (op == "cosim") return {DecodeCosim(ciphers, secKey)};
+  if (op == "mean") return {DecodeMean(ciphers, secKey)};
+  if (op == "variance") return {DecodeVariance(ciphers, secKey)};
+  if (op == "lin_reg") return DecodeLinearRegressionDims(ciphers, secKey);
+  if (op == "frequencyCount") return as_doubles(DecodeFreqCount(ciphers, secKey));
+  if (op == "min") return {(double)DecodeMin(ciphers, operation.QueryMin, secKey)};
+  if (op == "max") return {(double)DecodeMax(ciphers, operation.QueryMin, secKey)};
+  if (op == "bool_AND") return {DecodeBitAND(ciphers[0], secKey) ? 1.0 : 0.0};
+  if (op == "bool_OR") return {DecodeBitOR(ciphers[0], secKey) ? 1.0 : 0.0};
+  if (op == "union") return as_doubles(DecodeUnion(ciphers, secKey));
+  if (op == "inter") return as_doubles(DecodeInter(ciphers, secKey));
+  if (op == "MLeval") return {DecodeModelEvaluation(ciphers, secKey)};
+  return as_doubles(libunlynx::DecryptIntVectorWithNeg(secKey, ciphers));  // default branch (:228-237)
+}
+
 }  // namespace libdrynxencoding

@@ -234,6 +234,49 @@ static void TestEncodeDecodeCosimAndModelEvaluation() {  // cosim_test.go:17-55,
   EXPECT(DecodeModelEvaluation(m.enc, keys.Private) == 1.0 - (double)sd2 / B);
 }
 
+static void TestEncodeDecodeDispatcher() {  // encode_decode.go Encode / Decode over every operation name
+  auto keys = drynx::NewKeyPair();
+  libunlynx::CreateDecryptionTable(10000, keys.Public, keys.Private);
+  std::vector<std::vector<int64_t>> one = {{3, 1, 4, 1, 5, 9, 2, 6}};
+  auto run = [&](const char* name, const std::vector<std::vector<int64_t>>& datas, int64_t qmin = 0, int64_t qmax = 0) {
+    Operation op;
+    op.NameOp = name;
+    op.QueryMin = qmin;
+    op.QueryMax = qmax;
+    return Decode(Encode(datas, keys.Public, nullptr, nullptr, op).enc, keys.Private, op);
+  };
+  EXPECT(run("sum", one) == std::vector<double>({31}));
+  EXPECT(run("mean", one) == std::vector<double>({31.0 / 8}));
+  EXPECT(run("variance", one) == std::vector<double>({173.0 / 8 - (31.0 / 8) * (31.0 / 8)}));
+  EXPECT(run("min", one, 0, 12) == std::vector<double>({1}));
+  EXPECT(run("max", one, 0, 12) == std::vector<double>({9}));
+  EXPECT(run("frequencyCount", one, 0, 9) == std::vector<double>({0, 2, 1, 1, 1, 1, 1, 0, 0, 1}));
+  EXPECT(run("union", one, 0, 9) == std::vector<double>({0, 1, 1, 1, 1, 1, 1, 0, 0, 1}));
+  EXPECT(run("inter", one, 0, 9) == std::vector<double>({0, 1, 1, 1, 1, 1, 1, 0, 0, 1}));
+  EXPECT(run("bool_OR", {{1}}) == std::vector<double>({1}) && run("bool_OR", {{0}}) == std::vector<double>({0}));
+  EXPECT(run("bool_AND", {{1}}) == std::vector<double>({1}) && run("bool_AND", {{0}}) == std::vector<double>({0}));
+  EXPECT(run("cosim", {{1, 2, 3}, {1, 2, 3}}) == std::vector<double>({14.0 / (std::sqrt(14.0) * std::sqrt(14.0))}));
+  EXPECT(run("MLeval", {{1, 2, 3, 4}, {1, 2, 3, 4}}) == std::vector<double>({1.0}));
+  // lin_reg takes columns: two feature columns then y = 1 + 2 x1 + 4 x2
+  auto c = run("lin_reg", {{1, 0, 1, 2, 3}, {2, 1, 0, 1, 5}, {11, 5, 3, 9, 27}});
+  EXPECT(c.size() == 3 && fabs(c[0] - 1) < 1e-9 && fabs(c[1] - 2) < 1e-9 && fabs(c[2] - 4) < 1e-9);
+  // with proofs through the dispatcher: mean = [sum, N], u = 4, l = 3 (values below 64)
+  const int64_t u = 4, l = 3;
+  std::vector<libdrynxrange::SignatureColumn> sigs;
+  Ranges lu;
+  for (int i = 0; i < 2; i++) {
+    sigs.push_back(libdrynxrange::RegisterColumn({libdrynxrange::InitRangeProofSignature(u)}, u));
+    lu.push_back({u, l});
+  }
+  Operation op;
+  op.NameOp = "mean";
+  auto e = Encode(one, keys.Public, &sigs, &lu, op);
+  EXPECT(e.proofs.size() == 2 && e.clear == std::vector<int64_t>({31, 8}));
+  libdrynxrange::RangeProofList list;
+  list.Data = libdrynxrange::CreatePredicateRangeProofListForAllServers(e.proofs);
+  EXPECT(libdrynxrange::RangeProofListVerification(list, lu, sigs, keys.Public, 1.0));
+}
+
 int main(int argc, char** argv) {
   const bool cpu_only = argc > 1 && !strcmp(argv[1], "--cpu");
   TestComputeApproxCoefficients();
@@ -252,6 +295,7 @@ int main(int argc, char** argv) {
       TestEncodeDecodeMinMax();
       TestEncodeDecodeUnionInter();
       TestEncodeDecodeCosimAndModelEvaluation();
+      TestEncodeDecodeDispatcher();
     } catch (const drynx::Error& e) {
       printf("FAIL: exception %d: %s\n", e.code, e.what());
       failures++;
