@@ -107,6 +107,17 @@ __device__ __forceinline__ bool locate_item(const RpBatch& b, const RpSetDev* se
 
 
 
+// Threads that compute a per-(proof, digit) value (the factor e(B, g2)^(t_j), shared by all servers): in a uniform
+// batch thread k handles (proof k / nd, digit k % nd) and `t` becomes server 0's item of that pair, so the threads
+// stay dense; in a ragged batch every item thread comes here and the callers drop those with i != 0.
+__device__ __forceinline__ bool rp_shared_factor_item(const RpBatch& b, size_t& t) {
+  if (b.d_item_proof) return t < b.items;
+  const size_t nd = (size_t)b.uni_nd;
+  if (t >= b.n * nd) return false;
+  t = (t / nd) * (size_t)b.uni_ns * nd + (t % nd);
+  return true;
+}
+
 // The same item split into independent roles that run in different thread blocks (three times the threads, a
 // third of the latency): role 0 writes V_ij and Zv_ij, role 1 computes e(B, A_{i,phi})^(-s_j v), role 2 computes
 // e(B, g2)^(t_j); the two GT factors go to scratch and rp_create_finish multiplies and serialises them.
@@ -121,7 +132,9 @@ __device__ __forceinline__ void rp_create_role(const RpBatch& b, const RpSetDev*
                                                int role) {
   size_t p, off;
   int i, j, ns, nd;
+  if (role == 2 && !rp_shared_factor_item(b, t)) return;
   if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  if (role == 2 && i != 0) return;  // e(B, g2)^(t_j) does not depend on the server: computed once per (proof, digit)
   uint32_t* out = proofs + off / 4;
   const RpSetDev set = sets[b.d_set_id[p]];
   const int u = set.u;
@@ -153,7 +166,7 @@ __device__ __forceinline__ void rp_create_finish(const RpBatch& b, const RpSetDe
   if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
   ProofView pv{ns, nd};
   Fp12 a;
-  fp12_mul(a, scratch[t].a, scratch[t].b);
+  fp12_mul(a, scratch[t].a, scratch[t - (size_t)i * nd].b);  // the t_j factor lives with server 0's item
   gt_to_wire(proofs + off / 4 + pv.a_off(i, j), a);
 }
 
@@ -190,7 +203,9 @@ __device__ __forceinline__ void rp_create_fine_role(const RpBatch& b, const RpSe
                                                     CreateFine* __restrict__ scratch, size_t t, int role) {
   size_t p, off;
   int i, j, ns, nd;
+  if (role >= 8 && !rp_shared_factor_item(b, t)) return;
   if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  if (role >= 8 && i != 0) return;  // the e(B, g2)^(t_j) partials: once per (proof, digit)
   const RpSetDev set = sets[b.d_set_id[p]];
   const int u = set.u;
   ProofView pv{ns, nd};
@@ -232,13 +247,14 @@ __device__ __forceinline__ void rp_create_fine_finish(const RpBatch& b, const Rp
     G2Jac V = jac_add(jac_add(scratch[t].vp[0], scratch[t].vp[1]), jac_add(scratch[t].vp[2], scratch[t].vp[3]));
     g2_to_wire(out + pv.v_off(i, j), jac_to_aff(V));
   } else {
+    const size_t t0 = t - (size_t)i * nd;  // server 0's item of this digit holds the t_j partials
     Fp12 a, c2;
     fp12_mul(a, scratch[t].g[0], scratch[t].g[1]);
     fp12_mul(c2, scratch[t].g[2], scratch[t].g[3]);
     fp12_mul(a, a, c2);
-    fp12_mul(c2, scratch[t].g[4], scratch[t].g[5]);
+    fp12_mul(c2, scratch[t0].g[4], scratch[t0].g[5]);
     fp12_mul(a, a, c2);
-    fp12_mul(c2, scratch[t].g[6], scratch[t].g[7]);
+    fp12_mul(c2, scratch[t0].g[6], scratch[t0].g[7]);
     fp12_mul(a, a, c2);
     gt_to_wire(out + pv.a_off(i, j), a);
   }
