@@ -160,6 +160,14 @@ def run_reference(args):
     t1 = time.perf_counter()
     orc.ed_encrypt(ed_P, ed_m, ed_r, threads=cores)
     ed_rate = ed_n / (time.perf_counter() - t1)
+    # config 3 pre-pass on the host: the numpy restatement on one provider's 10^5 records
+    import logreg_ref
+    gl = np.random.default_rng(3)
+    lx = gl.integers(0, 4, size=(100000, 8)).astype(np.float64)
+    ly = gl.integers(0, 2, size=100000)
+    t1 = time.perf_counter()
+    logreg_ref.coefficients(lx, ly, [0.0] * 8, [100.0] * 8, 2, 1.0)
+    lr_rate = 100000 / (time.perf_counter() - t1)
     sample = '%d of %d DPs x %d rows (%d proofs/step), oracle/oracle.cpp C++ restatement of the Go path' % (ndp, args.ndp, args.rows, n)
     print(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'proofs/s', 'n_gpus': args.gpus, 'steps': args.steps,
@@ -167,7 +175,7 @@ def run_reference(args):
         'vs_baseline': None, 'dtype': 'u64 (4x64-bit Montgomery limbs)', 'data': 'synthetic',
         'config': {'workload': 'config 2: mean+variance, %d DPs x %d rows, u=16 l=4 ns=3 (bounded sample: %d DPs)' % (args.ndp, args.rows, ndp)},
         'cpu_baseline': {'value': val, 'unit': 'proofs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
-                         'ed25519_encs_per_s': ed_rate},
+                         'ed25519_encs_per_s': ed_rate, 'logreg_prepass_records_per_s': lr_rate},
         'e2e': {'value': val, 'unit': 'proofs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }))
@@ -515,6 +523,18 @@ def secondary_rates_ed(be, lib, torch, dev, timed, ck, vp, peak_tmac, g):
     ms = timed(lambda: ck(lib.drx_ed_decrypt_dev(be.h, nd, skp, vp(ct), vp(dec))))
     out['ed25519_decrypts_per_s'] = nd / ms * 1e3
     out['ed25519_decrypt_roofline_frac'] = nd * M_ED_DECRYPT * MAC32_PER_M_ED / (ms * 1e-3) / 1e12 / peak_tmac
+    # config 3: the float64 pre-pass of logistic regression, 10 providers x 10^5 records x 8 features, k = 2
+    nprov, nrec, dfeat = 10, 100000, 8
+    xr = torch.from_numpy(g.integers(0, 4, size=(nprov * nrec, dfeat)).astype(np.float64)).to(dev)
+    yr = torch.from_numpy(g.integers(0, 2, size=nprov * nrec).astype(np.int64)).to(dev)
+    offs = torch.from_numpy((np.arange(nprov + 1, dtype=np.uint64) * nrec).astype(np.int64)).to(dev)
+    mean_t = torch.zeros(dfeat, dtype=torch.float64, device=dev)
+    sd_t = torch.full((dfeat,), 100.0, dtype=torch.float64, device=dev)
+    coef = torch.empty(nprov * 90, dtype=torch.int64, device=dev)
+    ms = timed(lambda: ck(lib.drx_logreg_coefficients_dev(be.h, nprov, vp(offs), dfeat, 2, vp(xr), vp(yr), vp(mean_t), vp(sd_t),
+                                                          ctypes.c_double(1.0), vp(coef))))
+    out['logreg_prepass_records_per_s'] = nprov * nrec / ms * 1e3
+    out['logreg_prepass_hbm_gbs'] = nprov * nrec * (dfeat + 1) * 8 / (ms * 1e-3) / 1e9
     # the aggregate of 1,000 providers' 0..9 counts decrypts to the column sums
     be.synchronize()
     want = m.view(ndp, v).sum(dim=0).cpu().numpy()

@@ -76,6 +76,24 @@ class Backend:
         _lib.check(self.lib.drx_reduce_rows(self.h, rows.shape[0], rows.shape[1], _ptr(rows), mode, _ptr(out)))
         return out
 
+    def logreg_coefficients(self, x_list, y_list, means, sds, k, precision):
+        """EncodeLogisticRegression's plaintext step for several data providers: x_list[p] float64[n_p][d],
+        y_list[p] int64[n_p] -> int64[ndp][(d+1) + (d+1)^2] (k = 2) packed coefficient vectors."""
+        d = len(means)
+        ndp = len(x_list)
+        off = np.zeros(ndp + 1, dtype=np.uint64)
+        for p in range(ndp):
+            off[p + 1] = off[p] + len(y_list[p])
+        x = np.ascontiguousarray(np.concatenate([np.asarray(a, np.float64).reshape(-1, d) for a in x_list]) if ndp else np.zeros((0, d)))
+        y = np.ascontiguousarray(np.concatenate([np.asarray(a, np.int64) for a in y_list]) if ndp else np.zeros(0, np.int64))
+        m = np.ascontiguousarray(means, dtype=np.float64)
+        s = np.ascontiguousarray(sds, dtype=np.float64)
+        ncoef = (d + 1) + ((d + 1) ** 2 if k >= 2 else 0)
+        out = np.empty((ndp, ncoef), dtype=np.int64)
+        _lib.check(self.lib.drx_logreg_coefficients(self.h, ndp, _ptr(off), d, k, _ptr(x), _ptr(y), _ptr(m), _ptr(s),
+                                                    float(precision), _ptr(out)))
+        return out
+
     def encrypt_int_vector(self, m, r):
         """EncryptIntVectorGetRs with injected scalars: m int64[n], r bytes n*32 -> n*128 bytes."""
         m = np.ascontiguousarray(m, dtype=np.int64)

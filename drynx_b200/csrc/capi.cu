@@ -389,6 +389,57 @@ int drx_reduce_rows(drx_ctx* c, size_t ndp, size_t nrows, const int64_t* rows, i
   return 0;
 }
 
+int drx_logreg_coefficients(drx_ctx* c, size_t ndp, const size_t* rec_off, int d, int k, const double* x, const int64_t* y,
+                            const double* means, const double* sds, double precision, int64_t* out) {
+  if (!c) return fail(-1, "null context");
+  if (ndp == 0) return 0;
+  if (!rec_off || !means || !sds || !out) return fail(-1, "drx_logreg_coefficients: null buffer");
+  if (d < 1 || d > kLogRegMaxFeatures) return fail(-1, "drx_logreg_coefficients: d = %d outside 1..%d", d, kLogRegMaxFeatures);
+  if (k < 1 || k > 2) return fail(-1, "drx_logreg_coefficients: k = %d (the reference's coefficient packing is only defined for k <= 2)", k);
+  for (size_t i = 0; i < ndp; i++)
+    if (rec_off[i + 1] < rec_off[i]) return fail(-1, "drx_logreg_coefficients: record offsets must not decrease");
+  const size_t nrec = rec_off[ndp] - rec_off[0], d1 = (size_t)d + 1, ncoef = d1 + (k >= 2 ? d1 * d1 : 0);
+  if (nrec && (!x || !y)) return fail(-1, "drx_logreg_coefficients: null records");
+  Guard g(c);
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t oo = a.plan((ndp + 1) * 8), ox = a.plan(nrec * d * 8), oy = a.plan(nrec * 8), om = a.plan(d * 8), os = a.plan(d * 8),
+         oc = a.plan(ndp * ncoef * 8);
+  RET(a.commit());
+  std::vector<size_t> off(rec_off, rec_off + ndp + 1);
+  for (auto& v : off) v -= rec_off[0];
+  cudaStream_t st = c->stream;
+  CU(cudaMemcpyAsync(a.at<void>(oo), off.data(), (ndp + 1) * 8, cudaMemcpyHostToDevice, st));
+  if (nrec) {
+    CU(cudaMemcpyAsync(a.at<void>(ox), x + rec_off[0] * d, nrec * d * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(a.at<void>(oy), y + rec_off[0], nrec * 8, cudaMemcpyHostToDevice, st));
+  }
+  CU(cudaMemcpyAsync(a.at<void>(om), means, d * 8, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(a.at<void>(os), sds, d * 8, cudaMemcpyHostToDevice, st));
+  CU(cudaStreamSynchronize(st));  // `off` is a stack-owned staging vector
+  timed(c, "k_logreg_coeffs", [&] {
+    return launch_logreg_coeffs(st, ndp, a.at<size_t>(oo), d, k, a.at<double>(ox), a.at<int64_t>(oy), a.at<double>(om),
+                                a.at<double>(os), precision, a.at<int64_t>(oc));
+  });
+  RET(check_launch("logreg_coefficients"));
+  CU(cudaMemcpyAsync(out, a.at<void>(oc), ndp * ncoef * 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int drx_logreg_coefficients_dev(drx_ctx* c, size_t ndp, const size_t* d_rec_off, int d, int k, const double* d_x,
+                                const int64_t* d_y, const double* d_means, const double* d_sds, double precision,
+                                int64_t* d_out) {
+  if (!c) return fail(-1, "null context");
+  if (d < 1 || d > kLogRegMaxFeatures) return fail(-1, "drx_logreg_coefficients_dev: d = %d outside 1..%d", d, kLogRegMaxFeatures);
+  if (k < 1 || k > 2) return fail(-1, "drx_logreg_coefficients_dev: k = %d (only k <= 2)", k);
+  Guard g(c);
+  timed(c, "k_logreg_coeffs", [&] {
+    return launch_logreg_coeffs(c->stream, ndp, d_rec_off, d, k, d_x, d_y, d_means, d_sds, precision, d_out);
+  });
+  return check_launch("logreg_coefficients");
+}
+
 int drx_set_pubkey(drx_ctx* c, const uint8_t P[64]) {
   if (!c || !P) return fail(-1, "drx_set_pubkey: null argument");
   Guard g(c);

@@ -370,6 +370,69 @@ int launch_reduce_rows(cudaStream_t st, size_t ndp, size_t nrows, const int64_t*
   return 1;
 }
 
+// ------------------------------------------------------------------ logistic-regression pre-pass (a-7)
+// lib/encoding/logistic_regression.go: StandardiseWith (:964-978), Augment (:1014-1023), ComputeAllApproxCoefficients
+// (:367-403), AggregateApproxCoefficients (:433-455), Float64ToInt642DArrayWithPrecision (:1558-1574). The result
+// depends on the order of the float64 operations, so every (provider, coefficient) pair is ONE thread that adds
+// its provider's records in index order with explicitly rounded, never fused operations (__dmul_rn / __dadd_rn /
+// __ddiv_rn). A block serves one provider and up to 64 coefficients; all its threads stage tiles of standardised,
+// augmented records in shared memory, then each walks the tile for its own coefficient. HBM-bound in principle
+// (8(d+1) bytes per record and block), latency-bound in practice (one dependent addition per record).
+#define DRX_LR_TILE 128
+#define DRX_LR_MAXD 31
+__global__ void __launch_bounds__(64)
+k_logreg_coeffs(const size_t* __restrict__ rec_off, int d, int k, const double* __restrict__ x,
+                const int64_t* __restrict__ y, const double* __restrict__ means, const double* __restrict__ sds,
+                double precision, int64_t* __restrict__ out) {
+  __shared__ double X[DRX_LR_TILE * (DRX_LR_MAXD + 1)];
+  __shared__ double ys[DRX_LR_TILE];
+  const int dp = blockIdx.x, d1 = d + 1;
+  const int ncoef = d1 + (k >= 2 ? d1 * d1 : 0);
+  const int coef = blockIdx.y * 64 + threadIdx.x;
+  const size_t r0 = rec_off[dp], r1 = rec_off[dp + 1];
+  // which product this thread accumulates: level 1 -> X[s] * (2y - 1); level 2 -> ypart * ((1.0 * X[i1]) * X[i2])
+  const bool active = coef < ncoef, lvl2 = coef >= d1;
+  const int i1 = lvl2 ? (coef - d1) / d1 : coef, i2 = lvl2 ? (coef - d1) % d1 : 0;
+  double acc = 0.0;
+  for (size_t base = r0; base < r1; base += DRX_LR_TILE) {
+    const int cnt = (int)((r1 - base) < (size_t)DRX_LR_TILE ? (r1 - base) : (size_t)DRX_LR_TILE);
+    __syncthreads();
+    for (int e = threadIdx.x; e < cnt * d1; e += 64) {
+      const int r = e / d1, f = e - r * d1;
+      X[r * d1 + f] = f == 0 ? 1.0 : __ddiv_rn(__dsub_rn(x[(base + r) * (size_t)d + (f - 1)], means[f - 1]), sds[f - 1]);
+    }
+    for (int r = threadIdx.x; r < cnt; r += 64) ys[r] = (double)y[base + r];
+    __syncthreads();
+    if (active) {
+      for (int r = 0; r < cnt; r++) {
+        const double yy = ys[r];
+        double term;
+        if (!lvl2) {
+          term = __dmul_rn(X[r * d1 + i1], __dsub_rn(__dmul_rn(2.0, yy), 1.0));
+        } else {
+          const double ypart = __dsub_rn(__dsub_rn(yy, yy), 1.0);  // y - y*(-1)^2 - 1
+          term = __dmul_rn(ypart, __dmul_rn(__dmul_rn(1.0, X[r * d1 + i1]), X[r * d1 + i2]));
+        }
+        acc = __dadd_rn(acc, term);
+      }
+    }
+  }
+  if (active) {
+    // level j sits at offset j * (d+1)^j of the packed vector (logistic_regression.go:306-313)
+    const int pos = lvl2 ? d1 + (coef - d1) : coef;
+    out[(size_t)dp * ncoef + pos] = (int64_t)round(__dmul_rn(acc, precision));  // math.Round: halves away from zero
+  }
+}
+int launch_logreg_coeffs(cudaStream_t st, size_t ndp, const size_t* d_rec_off, int d, int k, const double* d_x,
+                         const int64_t* d_y, const double* d_means, const double* d_sds, double precision,
+                         int64_t* d_out) {
+  if (!ndp) return 0;
+  const int d1 = d + 1, ncoef = d1 + (k >= 2 ? d1 * d1 : 0);
+  dim3 grid((unsigned)ndp, (unsigned)((ncoef + 63) / 64));
+  k_logreg_coeffs<<<grid, 64, 0, st>>>(d_rec_off, d, k, d_x, d_y, d_means, d_sds, precision, d_out);
+  return 1;
+}
+
 // ------------------------------------------------------------------ discrete-log table (a-5) and decryption (a-4)
 // Open addressing, linear probing. Key = Montgomery-form x coordinate of i*B (8 words); value word =
 // (i << 1) | parity(y), 0xffffffff = empty. -i*B shares the x coordinate and has the other y parity.

@@ -24,6 +24,10 @@ constexpr size_t kUcodeG8MaxItems = 2400;     // ... and up to this many use eig
 // wire bytes -> Montgomery affine (returns malformed count in *d_bad)
 int launch_g1_from_wire(cudaStream_t st, size_t n, const uint8_t* d_wire, void* d_aff, int* d_bad);
 int launch_comb_table_g1(cudaStream_t st, int nbases, const void* d_bases_aff, void* d_tables);
+constexpr int kLogRegMaxFeatures = 31;
+int launch_logreg_coeffs(cudaStream_t st, size_t ndp, const size_t* d_rec_off, int d, int k, const double* d_x,
+                         const int64_t* d_y, const double* d_means, const double* d_sds, double precision,
+                         int64_t* d_out);
 int launch_encrypt_scalar(cudaStream_t st, size_t n, const uint8_t* d_m, const uint8_t* d_r, const void* d_tabB,
                           const void* d_tabP, uint8_t* d_ct);
 int launch_encrypt(cudaStream_t st, size_t n, const int64_t* d_m, const uint8_t* d_r, const void* d_tabB,

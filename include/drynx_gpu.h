@@ -68,6 +68,20 @@ int drx_reduce_rows_dev(drx_ctx* ctx, size_t ndp, size_t nrows, const int64_t* d
  * provider calls in place of the Go loops of EncodeSum / EncodeMean / EncodeVariance before it encrypts). */
 int drx_reduce_rows(drx_ctx* ctx, size_t ndp, size_t nrows, const int64_t* rows, int mode, int64_t* out);
 
+/* The float64 pre-pass of logistic regression (lib/encoding/logistic_regression.go:46-118: StandardiseWith :964-978,
+ * Augment :1014-1023, ComputeAllApproxCoefficients :367-403, AggregateApproxCoefficients :433-455,
+ * Float64ToInt642DArrayWithPrecision :1558-1574) for ndp data providers at once. Provider p owns records
+ * rec_off[p] .. rec_off[p+1]-1 of x[record][d] (float64) and y[record] (0/1); out[p] is its packed vector of
+ * (d+1) + (d+1)^2 int64 coefficients for k = 2 (d+1 for k = 1), ready for drx_encrypt. Every sum runs in record
+ * order with correctly rounded, unfused float64 operations: the integers equal the Go loop's bit for bit.
+ * d <= 31, k <= 2 (the reference's packing offset j*(d+1)^j is only consistent up to k = 2). */
+int drx_logreg_coefficients(drx_ctx* ctx, size_t ndp, const size_t* rec_off /*ndp+1*/, int d, int k, const double* x,
+                            const int64_t* y, const double* means /*d*/, const double* sds /*d*/, double precision,
+                            int64_t* out);
+int drx_logreg_coefficients_dev(drx_ctx* ctx, size_t ndp, const size_t* d_rec_off, int d, int k, const double* d_x,
+                                const int64_t* d_y, const double* d_means, const double* d_sds, double precision,
+                                int64_t* d_out);
+
 /* Collective public key P for EncryptInt* and range proofs (CreateProof.CaPub, lib/range/range_proof.go:67);
  * builds its fixed-base table. */
 int drx_set_pubkey(drx_ctx* ctx, const uint8_t P[64]);
