@@ -531,7 +531,7 @@ def secondary_rates_ed(be, lib, torch, dev, timed, ck, vp, peak_tmac, g):
     mean_t = torch.zeros(dfeat, dtype=torch.float64, device=dev)
     sd_t = torch.full((dfeat,), 100.0, dtype=torch.float64, device=dev)
     coef = torch.empty(nprov * 90, dtype=torch.int64, device=dev)
-    ms = timed(lambda: ck(lib.drx_logreg_coefficients_dev(be.h, nprov, vp(offs), dfeat, 2, vp(xr), vp(yr), vp(mean_t), vp(sd_t),
+    ms = timed(lambda: ck(lib.drx_logreg_coefficients_dev(be.h, nprov, nprov * nrec, vp(offs), dfeat, 2, vp(xr), vp(yr), vp(mean_t), vp(sd_t),
                                                           ctypes.c_double(1.0), vp(coef))))
     out['logreg_prepass_records_per_s'] = nprov * nrec / ms * 1e3
     out['logreg_prepass_hbm_gbs'] = nprov * nrec * (dfeat + 1) * 8 / (ms * 1e-3) / 1e9

@@ -36,7 +36,7 @@ SIGNATURES = {
     'drx_ed_decrypt_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
     'drx_ed_point_mul': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
     'drx_logreg_coefficients': (ctypes.c_int, [VP, ctypes.c_size_t, VP, ctypes.c_int, ctypes.c_int, VP, VP, VP, VP, ctypes.c_double, VP]),
-    'drx_logreg_coefficients_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, ctypes.c_int, ctypes.c_int, VP, VP, VP, VP, ctypes.c_double, VP]),
+    'drx_logreg_coefficients_dev': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, ctypes.c_int, ctypes.c_int, VP, VP, VP, VP, ctypes.c_double, VP]),
     'drx_encrypt_scalar': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
     'drx_reduce_rows': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, ctypes.c_int, VP]),
     'drx_set_pubkey': (ctypes.c_int, [VP, VP]),

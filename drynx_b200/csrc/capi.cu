@@ -404,7 +404,7 @@ int drx_logreg_coefficients(drx_ctx* c, size_t ndp, const size_t* rec_off, int d
   Arena& a = c->arena;
   a.plan_reset();
   size_t oo = a.plan((ndp + 1) * 8), ox = a.plan(nrec * d * 8), oy = a.plan(nrec * 8), om = a.plan(d * 8), os = a.plan(d * 8),
-         oc = a.plan(ndp * ncoef * 8);
+         oc = a.plan(ndp * ncoef * 8), oxs = a.plan(nrec * d * 8);
   RET(a.commit());
   std::vector<size_t> off(rec_off, rec_off + ndp + 1);
   for (auto& v : off) v -= rec_off[0];
@@ -418,8 +418,8 @@ int drx_logreg_coefficients(drx_ctx* c, size_t ndp, const size_t* rec_off, int d
   CU(cudaMemcpyAsync(a.at<void>(os), sds, d * 8, cudaMemcpyHostToDevice, st));
   CU(cudaStreamSynchronize(st));  // `off` is a stack-owned staging vector
   timed(c, "k_logreg_coeffs", [&] {
-    return launch_logreg_coeffs(st, ndp, a.at<size_t>(oo), d, k, a.at<double>(ox), a.at<int64_t>(oy), a.at<double>(om),
-                                a.at<double>(os), precision, a.at<int64_t>(oc));
+    return launch_logreg_coeffs(st, ndp, nrec, a.at<size_t>(oo), d, k, a.at<double>(ox), a.at<int64_t>(oy), a.at<double>(om),
+                                a.at<double>(os), precision, a.at<double>(oxs), a.at<int64_t>(oc));
   });
   RET(check_launch("logreg_coefficients"));
   CU(cudaMemcpyAsync(out, a.at<void>(oc), ndp * ncoef * 8, cudaMemcpyDeviceToHost, st));
@@ -427,15 +427,20 @@ int drx_logreg_coefficients(drx_ctx* c, size_t ndp, const size_t* rec_off, int d
   return 0;
 }
 
-int drx_logreg_coefficients_dev(drx_ctx* c, size_t ndp, const size_t* d_rec_off, int d, int k, const double* d_x,
-                                const int64_t* d_y, const double* d_means, const double* d_sds, double precision,
-                                int64_t* d_out) {
+int drx_logreg_coefficients_dev(drx_ctx* c, size_t ndp, size_t nrec, const size_t* d_rec_off, int d, int k,
+                                const double* d_x, const int64_t* d_y, const double* d_means, const double* d_sds,
+                                double precision, int64_t* d_out) {
   if (!c) return fail(-1, "null context");
   if (d < 1 || d > kLogRegMaxFeatures) return fail(-1, "drx_logreg_coefficients_dev: d = %d outside 1..%d", d, kLogRegMaxFeatures);
   if (k < 1 || k > 2) return fail(-1, "drx_logreg_coefficients_dev: k = %d (only k <= 2)", k);
   Guard g(c);
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t oxs = a.plan(nrec * (size_t)d * 8);  // the standardised records
+  RET(a.commit());
   timed(c, "k_logreg_coeffs", [&] {
-    return launch_logreg_coeffs(c->stream, ndp, d_rec_off, d, k, d_x, d_y, d_means, d_sds, precision, d_out);
+    return launch_logreg_coeffs(c->stream, ndp, nrec, d_rec_off, d, k, d_x, d_y, d_means, d_sds, precision, a.at<double>(oxs),
+                                d_out);
   });
   return check_launch("logreg_coefficients");
 }

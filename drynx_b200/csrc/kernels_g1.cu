@@ -373,22 +373,34 @@ int launch_reduce_rows(cudaStream_t st, size_t ndp, size_t nrows, const int64_t*
 // ------------------------------------------------------------------ logistic-regression pre-pass (a-7)
 // lib/encoding/logistic_regression.go: StandardiseWith (:964-978), Augment (:1014-1023), ComputeAllApproxCoefficients
 // (:367-403), AggregateApproxCoefficients (:433-455), Float64ToInt642DArrayWithPrecision (:1558-1574). The result
-// depends on the order of the float64 operations, so every (provider, coefficient) pair is ONE thread that adds
+// depends on the order of the float64 operations. k_logreg_standardise does the divisions once, one thread per
+// (record, feature); then every (provider, coefficient) pair is ONE thread that adds
 // its provider's records in index order with explicitly rounded, never fused operations (__dmul_rn / __dadd_rn /
-// __ddiv_rn). A block serves one provider and up to 64 coefficients; all its threads stage tiles of standardised,
-// augmented records in shared memory, then each walks the tile for its own coefficient. HBM-bound in principle
-// (8(d+1) bytes per record and block), latency-bound in practice (one dependent addition per record).
+// __ddiv_rn). A block (one warp) serves one provider and 32 coefficients; all its threads stage tiles of standardised,
+// augmented records in shared memory, then each walks the tile for its own coefficient: two float64 operations per
+// record and thread, the addition dependent on the previous one (latency-bound; HBM only sees 8(d+1) bytes per
+// record and block).
 #define DRX_LR_TILE 128
 #define DRX_LR_MAXD 31
-__global__ void __launch_bounds__(64)
-k_logreg_coeffs(const size_t* __restrict__ rec_off, int d, int k, const double* __restrict__ x,
-                const int64_t* __restrict__ y, const double* __restrict__ means, const double* __restrict__ sds,
-                double precision, int64_t* __restrict__ out) {
+#define DRX_LR_BLOCK 32
+// StandardiseWith, one thread per (record, feature): the divisions are the expensive float64 operations of the
+// pre-pass and every block of the accumulation kernel would otherwise repeat them
+__global__ void __launch_bounds__(256)
+k_logreg_standardise(size_t n, int d, const double* __restrict__ x, const double* __restrict__ means,
+                     const double* __restrict__ sds, double* __restrict__ xs) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n * (size_t)d) return;
+  const int f = (int)(e % (size_t)d);
+  xs[e] = __ddiv_rn(__dsub_rn(x[e], means[f]), sds[f]);
+}
+__global__ void __launch_bounds__(DRX_LR_BLOCK)
+k_logreg_coeffs(const size_t* __restrict__ rec_off, int d, int k, const double* __restrict__ xs,
+                const int64_t* __restrict__ y, double precision, int64_t* __restrict__ out) {
   __shared__ double X[DRX_LR_TILE * (DRX_LR_MAXD + 1)];
   __shared__ double ys[DRX_LR_TILE];
   const int dp = blockIdx.x, d1 = d + 1;
   const int ncoef = d1 + (k >= 2 ? d1 * d1 : 0);
-  const int coef = blockIdx.y * 64 + threadIdx.x;
+  const int coef = blockIdx.y * DRX_LR_BLOCK + threadIdx.x;
   const size_t r0 = rec_off[dp], r1 = rec_off[dp + 1];
   // which product this thread accumulates: level 1 -> X[s] * (2y - 1); level 2 -> ypart * ((1.0 * X[i1]) * X[i2])
   const bool active = coef < ncoef, lvl2 = coef >= d1;
@@ -397,23 +409,24 @@ k_logreg_coeffs(const size_t* __restrict__ rec_off, int d, int k, const double* 
   for (size_t base = r0; base < r1; base += DRX_LR_TILE) {
     const int cnt = (int)((r1 - base) < (size_t)DRX_LR_TILE ? (r1 - base) : (size_t)DRX_LR_TILE);
     __syncthreads();
-    for (int e = threadIdx.x; e < cnt * d1; e += 64) {
-      const int r = e / d1, f = e - r * d1;
-      X[r * d1 + f] = f == 0 ? 1.0 : __ddiv_rn(__dsub_rn(x[(base + r) * (size_t)d + (f - 1)], means[f - 1]), sds[f - 1]);
+    for (int e = threadIdx.x; e < cnt * d; e += DRX_LR_BLOCK) {  // coalesced copy of the tile, Augment's 1.0 in column 0
+      const int r = e / d, f = e - r * d;
+      X[r * d1 + 1 + f] = xs[base * (size_t)d + e];
     }
-    for (int r = threadIdx.x; r < cnt; r += 64) ys[r] = (double)y[base + r];
+    for (int r = threadIdx.x; r < cnt; r += DRX_LR_BLOCK) {
+      X[r * d1] = 1.0;
+      ys[r] = __dsub_rn(__dmul_rn(2.0, (double)y[base + r]), 1.0);  // 2y - 1
+    }
     __syncthreads();
     if (active) {
-      for (int r = 0; r < cnt; r++) {
-        const double yy = ys[r];
-        double term;
-        if (!lvl2) {
-          term = __dmul_rn(X[r * d1 + i1], __dsub_rn(__dmul_rn(2.0, yy), 1.0));
-        } else {
-          const double ypart = __dsub_rn(__dsub_rn(yy, yy), 1.0);  // y - y*(-1)^2 - 1
-          term = __dmul_rn(ypart, __dmul_rn(__dmul_rn(1.0, X[r * d1 + i1]), X[r * d1 + i2]));
-        }
-        acc = __dadd_rn(acc, term);
+      // Exact shortcuts, each giving the same double as the reference's expression: 1.0 * X = X; for level 2
+      // ypart = y - y*(-1)^2 - 1 = -1.0 whatever y is, and (-1.0) * p is p with its sign flipped.
+      if (!lvl2) {
+#pragma unroll 4
+        for (int r = 0; r < cnt; r++) acc = __dadd_rn(acc, __dmul_rn(X[r * d1 + i1], ys[r]));
+      } else {
+#pragma unroll 4
+        for (int r = 0; r < cnt; r++) acc = __dadd_rn(acc, -__dmul_rn(X[r * d1 + i1], X[r * d1 + i2]));
       }
     }
   }
@@ -423,14 +436,19 @@ k_logreg_coeffs(const size_t* __restrict__ rec_off, int d, int k, const double* 
     out[(size_t)dp * ncoef + pos] = (int64_t)round(__dmul_rn(acc, precision));  // math.Round: halves away from zero
   }
 }
-int launch_logreg_coeffs(cudaStream_t st, size_t ndp, const size_t* d_rec_off, int d, int k, const double* d_x,
-                         const int64_t* d_y, const double* d_means, const double* d_sds, double precision,
+int launch_logreg_coeffs(cudaStream_t st, size_t ndp, size_t nrec, const size_t* d_rec_off, int d, int k, const double* d_x,
+                         const int64_t* d_y, const double* d_means, const double* d_sds, double precision, double* d_xs,
                          int64_t* d_out) {
   if (!ndp) return 0;
   const int d1 = d + 1, ncoef = d1 + (k >= 2 ? d1 * d1 : 0);
-  dim3 grid((unsigned)ndp, (unsigned)((ncoef + 63) / 64));
-  k_logreg_coeffs<<<grid, 64, 0, st>>>(d_rec_off, d, k, d_x, d_y, d_means, d_sds, precision, d_out);
-  return 1;
+  int launches = 1;
+  if (nrec) {
+    k_logreg_standardise<<<grid_for(nrec * (size_t)d, 256), 256, 0, st>>>(nrec, d, d_x, d_means, d_sds, d_xs);
+    launches++;
+  }
+  dim3 grid((unsigned)ndp, (unsigned)((ncoef + DRX_LR_BLOCK - 1) / DRX_LR_BLOCK));
+  k_logreg_coeffs<<<grid, DRX_LR_BLOCK, 0, st>>>(d_rec_off, d, k, d_xs, d_y, precision, d_out);
+  return launches;
 }
 
 // ------------------------------------------------------------------ discrete-log table (a-5) and decryption (a-4)

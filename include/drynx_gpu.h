@@ -78,9 +78,10 @@ int drx_reduce_rows(drx_ctx* ctx, size_t ndp, size_t nrows, const int64_t* rows,
 int drx_logreg_coefficients(drx_ctx* ctx, size_t ndp, const size_t* rec_off /*ndp+1*/, int d, int k, const double* x,
                             const int64_t* y, const double* means /*d*/, const double* sds /*d*/, double precision,
                             int64_t* out);
-int drx_logreg_coefficients_dev(drx_ctx* ctx, size_t ndp, const size_t* d_rec_off, int d, int k, const double* d_x,
-                                const int64_t* d_y, const double* d_means, const double* d_sds, double precision,
-                                int64_t* d_out);
+/* device-resident form; nrec = total number of records = d_rec_off[ndp] (d_rec_off[0] must be 0) */
+int drx_logreg_coefficients_dev(drx_ctx* ctx, size_t ndp, size_t nrec, const size_t* d_rec_off, int d, int k,
+                                const double* d_x, const int64_t* d_y, const double* d_means, const double* d_sds,
+                                double precision, int64_t* d_out);
 
 /* Collective public key P for EncryptInt* and range proofs (CreateProof.CaPub, lib/range/range_proof.go:67);
  * builds its fixed-base table. */
