@@ -90,7 +90,7 @@ def build_host_test(force=False):
     build_gpu()
     if force or _newer(HOST_TEST, deps + [GPU_SO]):
         libdir = os.path.dirname(GPU_SO)
-        _run(['g++', '-O2', '-std=c++17', src, '-o', HOST_TEST, '-L', libdir, '-ldrynx_gpu', '-Wl,-rpath,' + libdir,
+        _run(['g++', '-O2', '-ffp-contract=off', '-std=c++17', src, '-o', HOST_TEST, '-L', libdir, '-ldrynx_gpu', '-Wl,-rpath,' + libdir,
               '-Wl,-rpath,$ORIGIN/../drynx_b200', '-L/usr/local/cuda/lib64', '-lcudart', '-Wl,-rpath,/usr/local/cuda/lib64'])
     return HOST_TEST
 

@@ -797,6 +797,8 @@ inline std::vector<std::vector<int64_t>> Float64ToInt642DArrayWithPrecision(cons
 inline std::vector<int64_t> LogisticRegressionPlaintext(const std::vector<std::vector<double>>& xData, const std::vector<int64_t>& yData,
                                                         const LogisticRegressionParameters& lr) {
   const int64_t d = lr.NbrFeatures;
+  // the reference places level j at offset j * (d+1)^j (:306-313), which only tiles the vector up to k = 2
+  if (lr.K < 1 || lr.K > 2) throw drynx::Error(-1, "logistic regression: the coefficient packing is only defined for k <= 2");
   std::vector<int64_t> packed((size_t)getTotalNumberApproxCoefficients(d, lr.K), 0);
   if (xData.empty()) return packed;
   auto Xs = Augment(StandardiseWith(xData, lr.Means, lr.StandardDeviations));
