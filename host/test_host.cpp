@@ -160,6 +160,35 @@ static void TestLogisticRegressionAggregation() {  // logistic_regression_test.g
   EXPECT(libunlynx::DecryptCheckZero(keys.Private, libunlynx::EncryptInt(keys.Public, 7)) == 1);
 }
 
+static void TestLogisticRegressionDevicePrepass() {  // drx_logreg_coefficients == the host's float64 loop, bit for bit
+  LogisticRegressionParameters lr;
+  lr.NbrFeatures = 3;
+  lr.K = 2;
+  lr.Means = {0.25, 1.5, -0.75};
+  lr.StandardDeviations = {3.0, 7.0, 0.3};
+  lr.PrecisionApproxCoefficients = 1000.0;
+  std::vector<std::vector<double>> x[2];
+  std::vector<int64_t> y[2];
+  std::vector<double> flat;
+  std::vector<int64_t> yflat;
+  for (int p = 0; p < 2; p++)
+    for (int r = 0; r < 500 + 37 * p; r++) {
+      std::vector<double> rec(3);
+      for (auto& v : rec) v = (double)(sm_next() % 4000) / 997.0;
+      x[p].push_back(rec);
+      y[p].push_back((int64_t)(sm_next() & 1));
+      flat.insert(flat.end(), rec.begin(), rec.end());
+      yflat.push_back(y[p].back());
+    }
+  const size_t off[3] = {0, x[0].size(), x[0].size() + x[1].size()};
+  std::vector<int64_t> out(2 * 20);
+  drynx::check(drx_logreg_coefficients(drynx::Gpu::get().ctx(), 2, off, 3, 2, flat.data(), yflat.data(), lr.Means.data(),
+                                       lr.StandardDeviations.data(), lr.PrecisionApproxCoefficients, out.data()));
+  for (int p = 0; p < 2; p++) {
+    const auto want = LogisticRegressionPlaintext(x[p], y[p], lr);
+    EXPECT(want.size() == 20 && std::vector<int64_t>(out.begin() + 20 * p, out.begin() + 20 * (p + 1)) == want);
+  }
+}
 static void TestEncodeDecodeBit() {  // OR_AND_test.go:14-38 and :40-69 (u = 2, l = 1, one server)
   auto keys = drynx::NewKeyPair();
   for (auto in : {std::vector<bool>{false, true, false}, std::vector<bool>{true, true}, std::vector<bool>{false, false}}) {
@@ -291,6 +320,7 @@ int main(int argc, char** argv) {
       TestEncodeDecodeFrequencyCountWithProofs();
       TestEncodeDecodeLinearRegressionDims();
       TestLogisticRegressionAggregation();
+      TestLogisticRegressionDevicePrepass();
       TestEncodeDecodeBit();
       TestEncodeDecodeMinMax();
       TestEncodeDecodeUnionInter();
