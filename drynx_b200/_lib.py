@@ -35,6 +35,7 @@ SIGNATURES = {
     'drx_ed_decrypt': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, ctypes.c_int, VP, VP]),
     'drx_ed_decrypt_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
     'drx_ed_point_mul': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
+    'drx_freq_count': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, ctypes.c_int64, ctypes.c_int64, VP]),
     'drx_logreg_coefficients': (ctypes.c_int, [VP, ctypes.c_size_t, VP, ctypes.c_int, ctypes.c_int, VP, VP, VP, VP, ctypes.c_double, VP]),
     'drx_logreg_coefficients_dev': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, ctypes.c_int, ctypes.c_int, VP, VP, VP, VP, ctypes.c_double, VP]),
     'drx_encrypt_scalar': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),

@@ -76,6 +76,14 @@ class Backend:
         _lib.check(self.lib.drx_reduce_rows(self.h, rows.shape[0], rows.shape[1], _ptr(rows), mode, _ptr(out)))
         return out
 
+    def freq_count(self, rows, qmin, qmax):
+        """EncodeFreqCount's histogram per provider: rows int64[ndp][nrows] -> int64[ndp][qmax - qmin + 1]."""
+        rows = np.ascontiguousarray(rows, dtype=np.int64)
+        assert rows.ndim == 2
+        out = np.empty((rows.shape[0], int(qmax - qmin + 1)), dtype=np.int64)
+        _lib.check(self.lib.drx_freq_count(self.h, rows.shape[0], rows.shape[1], _ptr(rows), int(qmin), int(qmax), _ptr(out)))
+        return out
+
     def logreg_coefficients(self, x_list, y_list, means, sds, k, precision):
         """EncodeLogisticRegression's plaintext step for several data providers: x_list[p] float64[n_p][d],
         y_list[p] int64[n_p] -> int64[ndp][(d+1) + (d+1)^2] (k = 2) packed coefficient vectors."""

@@ -389,6 +389,31 @@ int drx_reduce_rows(drx_ctx* c, size_t ndp, size_t nrows, const int64_t* rows, i
   return 0;
 }
 
+int drx_freq_count(drx_ctx* c, size_t ndp, size_t nrows, const int64_t* rows, int64_t qmin, int64_t qmax, int64_t* out) {
+  if (!c) return fail(-1, "null context");
+  if (qmax < qmin || qmax - qmin + 1 > kFreqCountMaxBins)
+    return fail(-1, "drx_freq_count: range [%lld, %lld] must hold 1..%d values", (long long)qmin, (long long)qmax, kFreqCountMaxBins);
+  if (ndp == 0) return 0;
+  if (!out || (nrows && !rows)) return fail(-1, "drx_freq_count: null buffer");
+  Guard g(c);
+  const int nbins = (int)(qmax - qmin + 1);
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t oi = a.plan(ndp * nrows * 8), oo = a.plan(ndp * (size_t)nbins * 8);
+  RET(a.commit());
+  RET(reset_bad(c));
+  if (nrows) CU(cudaMemcpyAsync(a.at<void>(oi), rows, ndp * nrows * 8, cudaMemcpyHostToDevice, c->stream));
+  timed(c, "k_freq_count", [&] {
+    return launch_freq_count(c->stream, ndp, nrows, a.at<int64_t>(oi), qmin, nbins, a.at<int64_t>(oo), (int*)c->bad.p);
+  });
+  RET(check_launch("freq_count"));
+  CU(cudaMemcpyAsync(out, a.at<void>(oo), ndp * (size_t)nbins * 8, cudaMemcpyDeviceToHost, c->stream));
+  int bad = 0;
+  RET(read_bad(c, &bad));
+  if (bad) return fail(-2, "drx_freq_count: %d values outside [%lld, %lld]", bad, (long long)qmin, (long long)qmax);
+  return 0;
+}
+
 int drx_logreg_coefficients(drx_ctx* c, size_t ndp, const size_t* rec_off, int d, int k, const double* x, const int64_t* y,
                             const double* means, const double* sds, double precision, int64_t* out) {
   if (!c) return fail(-1, "null context");

@@ -370,6 +370,34 @@ int launch_reduce_rows(cudaStream_t st, size_t ndp, size_t nrows, const int64_t*
   return 1;
 }
 
+// lib/encoding/frequency_count.go:18-36: per provider, one counter per value of [min, max]. One block per provider
+// with a shared-memory histogram (32-bit counters: a provider has fewer than 2^31 rows); a value outside the
+// range is an index panic in the Go loop and an error here.
+#define DRX_FC_MAXBINS 12000
+__global__ void __launch_bounds__(256)
+k_freq_count(size_t nrows, const int64_t* __restrict__ rows, int64_t qmin, int nbins, int64_t* __restrict__ out, int* bad) {
+  __shared__ unsigned int hist[DRX_FC_MAXBINS];
+  const size_t dp = blockIdx.x;
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x) hist[b] = 0;
+  __syncthreads();
+  const int64_t* r = rows + dp * nrows;
+  int nbad = 0;
+  for (size_t i = threadIdx.x; i < nrows; i += blockDim.x) {
+    const int64_t v = r[i] - qmin;
+    if (v < 0 || v >= nbins) nbad++;
+    else atomicAdd(&hist[(int)v], 1u);
+  }
+  if (nbad) atomicAdd(bad, nbad);
+  __syncthreads();
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x) out[dp * (size_t)nbins + b] = (int64_t)hist[b];
+}
+int launch_freq_count(cudaStream_t st, size_t ndp, size_t nrows, const int64_t* d_rows, int64_t qmin, int nbins,
+                      int64_t* d_out, int* d_bad) {
+  if (!ndp) return 0;
+  k_freq_count<<<(unsigned)ndp, 256, 0, st>>>(nrows, d_rows, qmin, nbins, d_out, d_bad);
+  return 1;
+}
+
 // ------------------------------------------------------------------ logistic-regression pre-pass (a-7)
 // lib/encoding/logistic_regression.go: StandardiseWith (:964-978), Augment (:1014-1023), ComputeAllApproxCoefficients
 // (:367-403), AggregateApproxCoefficients (:433-455), Float64ToInt642DArrayWithPrecision (:1558-1574). The result

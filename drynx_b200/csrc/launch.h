@@ -24,6 +24,9 @@ constexpr size_t kUcodeG8MaxItems = 2400;     // ... and up to this many use eig
 // wire bytes -> Montgomery affine (returns malformed count in *d_bad)
 int launch_g1_from_wire(cudaStream_t st, size_t n, const uint8_t* d_wire, void* d_aff, int* d_bad);
 int launch_comb_table_g1(cudaStream_t st, int nbases, const void* d_bases_aff, void* d_tables);
+constexpr int kFreqCountMaxBins = 12000;
+int launch_freq_count(cudaStream_t st, size_t ndp, size_t nrows, const int64_t* d_rows, int64_t qmin, int nbins,
+                      int64_t* d_out, int* d_bad);
 constexpr int kLogRegMaxFeatures = 31;
 int launch_logreg_coeffs(cudaStream_t st, size_t ndp, size_t nrec, const size_t* d_rec_off, int d, int k, const double* d_x,
                          const int64_t* d_y, const double* d_means, const double* d_sds, double precision, double* d_xs,

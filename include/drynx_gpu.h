@@ -68,6 +68,11 @@ int drx_reduce_rows_dev(drx_ctx* ctx, size_t ndp, size_t nrows, const int64_t* d
  * provider calls in place of the Go loops of EncodeSum / EncodeMean / EncodeVariance before it encrypts). */
 int drx_reduce_rows(drx_ctx* ctx, size_t ndp, size_t nrows, const int64_t* rows, int mode, int64_t* out);
 
+/* EncodeFreqCount's plaintext step (lib/encoding/frequency_count.go:18-36) for ndp providers of nrows rows each:
+ * out[p][v - qmin] = number of rows of provider p equal to v, for v in [qmin, qmax] (at most 12,000 values). A row
+ * outside the range (an index panic in the Go loop) is error -2. */
+int drx_freq_count(drx_ctx* ctx, size_t ndp, size_t nrows, const int64_t* rows, int64_t qmin, int64_t qmax, int64_t* out);
+
 /* The float64 pre-pass of logistic regression (lib/encoding/logistic_regression.go:46-118: StandardiseWith :964-978,
  * Augment :1014-1023, ComputeAllApproxCoefficients :367-403, AggregateApproxCoefficients :433-455,
  * Float64ToInt642DArrayWithPrecision :1558-1574) for ndp data providers at once. Provider p owns records

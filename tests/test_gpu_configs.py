@@ -35,6 +35,58 @@ def test_config1_sum_10_dps_100_rows(backend, oracle, rng):
     assert list(got) == list(want) == [int(rows.sum())]
 
 
+def test_config1_over_edwards25519(backend, oracle):
+    """Config 1 as BASELINE.json words it (Ed25519 ElGamal, proofs off): 10 DPs x 100 rows U{1,2}, per-provider sum on
+    the device, encrypt(10) -> aggregate(10 x 1) -> decrypt(1); bytes equal the edwards25519 oracle's at every stage."""
+    import ed25519_ref as E
+    g = np.random.default_rng(1)
+    sk = int.from_bytes(g.bytes(31), 'little') % E.l
+    skb = sk.to_bytes(32, 'little')
+    P = oracle.ed_mul(skb)
+    backend.ed_set_pubkey(P)
+    backend.ed_create_decryption_table(10000)
+    rows = g.integers(1, 3, size=(10, 100), dtype=np.int64)
+    sums = backend.reduce_rows(rows, 0).ravel()
+    assert list(sums) == list(rows.sum(axis=1))
+    rs = g.bytes(32 * 10)
+    cts = backend.ed_encrypt_int_vector(sums, rs).tobytes()
+    assert cts == oracle.ed_encrypt(P, sums, rs)
+    vecs = [cts[64 * d:64 * d + 64] for d in range(10)]
+    agg = backend.ed_aggregate(vecs).tobytes()
+    assert agg == oracle.ed_aggregate(vecs)[1]
+    oracle.ed_dlog_reset()
+    rc, want, _ = oracle.ed_decrypt(skb, agg)
+    assert rc == 0
+    assert list(backend.ed_decrypt_int_vector(skb, agg)) == list(want) == [int(rows.sum())]
+    oracle.ed_dlog_reset()
+
+
+def test_config4_from_rows(backend, rng):
+    """Config 4 from raw rows: 200 providers x 5,000 rows over 1,000 bins -> per-provider histogram on the device
+    (frequency_count.go:18-36) -> encrypt -> aggregate -> decrypt == the global histogram; out-of-range rows are an
+    error like the Go index panic."""
+    from drynx_b200 import DrynxGpuError
+    sk, P = _keys(rng)
+    backend.set_pubkey(P)
+    backend.create_decryption_table(10000)
+    g = np.random.default_rng(44)
+    ndp, nrows, lo, hi = 200, 5000, -3, 996
+    rows = g.integers(lo, hi + 1, size=(ndp, nrows), dtype=np.int64)
+    counts = backend.freq_count(rows, lo, hi)
+    want = np.stack([np.bincount(rows[d] - lo, minlength=hi - lo + 1) for d in range(ndp)])
+    assert (counts == want).all()
+    rb = np.frombuffer(g.bytes(32 * counts.size), np.uint8).copy()
+    rb[::32] &= 0x7f
+    cts = backend.encrypt_int_vector(counts.ravel(), rb).reshape(ndp, -1)
+    agg = backend.aggregate([cts[d] for d in range(ndp)])
+    assert list(backend.decrypt_int_vector(sk.to_bytes(32, 'big'), agg)) == list(want.sum(axis=0))
+    assert backend.freq_count(np.empty((0, 7), np.int64), 0, 3).shape == (0, 4)
+    assert (backend.freq_count(np.empty((2, 0), np.int64), 0, 3) == 0).all()
+    rows[5, 17] = hi + 1
+    with pytest.raises(DrynxGpuError):
+        backend.freq_count(rows, lo, hi)
+
+
 def _all_coeffs(x, y, k=2):
     """logistic_regression.go:367-403 for k = 2 on an augmented record: level 1 = x(2y-1), level 2 = -(x_a x_b)."""
     lvl1 = x * (2.0 * y - 1.0)
