@@ -545,7 +545,7 @@ def secondary_rates_ed(be, lib, torch, dev, timed, ck, vp, peak_tmac, g):
 
 def cpu_baseline(args):
     """Times `bench.py --impl reference` logic in-process on a bounded sample (rank 0, N = 1 only)."""
-    p = subprocess.run([sys.executable, os.path.abspath(__file__), '--impl', 'reference', '--steps', '1', '--warmup', '0',
+    p = subprocess.run([sys.executable, os.path.abspath(__file__), '--impl', 'reference', '--steps', '2', '--warmup', '1',
                         '--ndp', str(args.ndp), '--rows', str(args.rows), '--cpu-sample-ndp', str(args.cpu_sample_ndp)],
                        capture_output=True, text=True)
     try:
