@@ -49,6 +49,20 @@ WORKER = textwrap.dedent('''
         out, _ = orc.decrypt(sk.to_bytes(32, 'big'), total)
         assert list(out) == [sum(vals[d][j] for d in range(ndp)) for j in range(v)]
         print('SHARD_OK')
+    # the same plumbing carries edwards25519 ciphertexts (64 bytes each): config 1 / 4 over UnLynx's default suite
+    import ed25519_ref as E
+    esk = (rng.scalar() % E.l).to_bytes(32, 'little'); eP = orc.ed_mul(esk)
+    ers = [rng.scalars_bytes(v) for _ in range(ndp)]
+    emine = [orc.ed_encrypt(eP, vals[d], ers[d]) for d in range(lo, hi)]
+    epartial = np.frombuffer(orc.ed_aggregate(emine)[1], np.uint8)
+    egathered = gather_partials(epartial, world, dist)
+    etotal = fold_on_root(egathered, rank, lambda vecs: orc.ed_aggregate([x.tobytes() for x in vecs])[1])
+    if rank == 0:
+        assert etotal == orc.ed_aggregate([orc.ed_encrypt(eP, vals[d], ers[d]) for d in range(ndp)])[1]
+        orc.ed_dlog_reset()
+        rc, out, _ = orc.ed_decrypt(esk, etotal)
+        assert rc == 0 and list(out) == [sum(vals[d][j] for d in range(ndp)) for j in range(v)]
+        print('SHARD_ED_OK')
     dist.barrier(); dist.destroy_process_group()
 ''')
 
@@ -62,4 +76,4 @@ def test_two_rank_gather_and_fold(tmp_path):
     p = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr',
                         '127.0.0.1', '--master-port', str(port), str(script)], capture_output=True, text=True, timeout=600)
     assert p.returncode == 0, p.stderr[-2000:]
-    assert 'SHARD_OK' in p.stdout
+    assert 'SHARD_OK' in p.stdout and 'SHARD_ED_OK' in p.stdout
