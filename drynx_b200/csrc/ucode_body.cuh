@@ -89,6 +89,13 @@ __device__ __forceinline__ Fp2 uc_mul(const Fp2& a, const Fp2& b) {
   const Fp s = fp_mul_inl(fp_add(a.c0, a.c1), fp_add(b.c0, b.c1));
   return Fp2{fp_sub(v0, v1), fp_sub(fp_sub(s, v0), v1)};
 }
+// a^2 = (a0 + a1)(a0 - a1) + 2 a0 a1 i: two products instead of three; only reached when every lane of the phase
+// squares (the generator labels such phases UC_SQR), so the warp never runs both forms
+__device__ __forceinline__ Fp2 uc_sqr(const Fp2& a) {
+  const Fp m = fp_mul_inl(a.c0, a.c1);
+  const Fp d = fp_mul_inl(fp_add(a.c0, a.c1), fp_sub(a.c0, a.c1));
+  return Fp2{d, fp_add(m, m)};
+}
 __device__ __forceinline__ Fp2 uc_add(const Fp2& a, const Fp2& b) { return Fp2{fp_add(a.c0, b.c0), fp_add(a.c1, b.c1)}; }
 __device__ __forceinline__ Fp2 uc_sub(const Fp2& a, const Fp2& b) { return Fp2{fp_sub(a.c0, b.c0), fp_sub(a.c1, b.c1)}; }
 __device__ __forceinline__ Fp2 uc_xi(const Fp2& a) {
@@ -173,6 +180,8 @@ UC_KERNEL(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ sc
         r = uc_add(a, uc_load(S, ib));
       } else if (op == UC_MUL) {
         r = uc_mul(a, uc_load(S, ib));
+      } else if (op == UC_SQR) {
+        r = uc_sqr(a);
       } else if (op == UC_SUB2) {
         r = uc_sub(uc_sub(a, uc_load(S, ib)), uc_load(S, ic));
       } else if (op == UC_AXI) {

@@ -21,9 +21,9 @@ import bn256_ref as R  # noqa: E402
 
 # ---------------------------------------------------------------------------------------------- symbolic Fp2 DAG
 OPS = ['NOP', 'MUL', 'ADD', 'SUB', 'DBL', 'NEG', 'MULXI', 'CONJ', 'MULC', 'MULFP0', 'MULFP1', 'INV', 'COPY', 'CONJMULC', 'MULFPC',
-       'SUB2', 'AXI', 'X3', 'X4', 'X8', 'CYCM', 'CYCP']
+       'SUB2', 'AXI', 'X3', 'X4', 'X8', 'CYCM', 'CYCP', 'SQR']
 OPC = {n: i for i, n in enumerate(OPS)}
-COST = {'MUL': 10, 'INV': 120, 'MULC': 10, 'CONJMULC': 10, 'MULFP0': 7, 'MULFP1': 7, 'MULFPC': 7}
+COST = {'MUL': 10, 'SQR': 7, 'INV': 120, 'MULC': 10, 'CONJMULC': 10, 'MULFP0': 7, 'MULFP1': 7, 'MULFPC': 7}
 
 
 class Node:
@@ -467,6 +467,21 @@ def schedule(g, G, nslots, window=96):
         else:
             op = max(mul_ops, key=lambda o: (len(by_op[o]), max(prio[n.id] for n in by_op[o])))
         chosen = sorted(by_op[op], key=lambda n: -prio[n.id])[:G]
+        phase_op = op
+        if op == 'MUL':
+            # squarings (a * a) need two Fp products instead of three, but only when the whole phase squares (the
+            # lanes of a warp run one code path): fill a phase with squarings, or with none, whenever the ready list
+            # allows it without leaving a lane idle that the mixed choice would have filled
+            ready_mul = sorted(by_op[op], key=lambda n: -prio[n.id])
+            sq = [n for n in ready_mul if n.a is n.b]
+            nsq = [n for n in ready_mul if n.a is not n.b]
+            want = min(G, len(ready_mul))
+            if G <= 4 and len(sq) >= want:      # (with eight lanes the regrouping costs more phases than it saves)
+                chosen = sq[:want]
+            elif G <= 4 and len(nsq) >= want:
+                chosen = nsq[:want]
+            if all(n.a is n.b for n in chosen):
+                phase_op = 'SQR'
         # shared-memory banks: a slot's 16-byte chunks are rotated by (slot & 3), so the four lanes of a group are
         # conflict-free when the slots they touch at the same time differ mod 4. Pick the lane order that spreads the
         # operand slots best, then give every lane a destination slot of its own class when one is free.
@@ -531,7 +546,7 @@ def schedule(g, G, nslots, window=96):
                 remaining_users[x.id] -= 1
                 if remaining_users[x.id] == 0 and x.id not in out_ids and x.op != 'IN':
                     to_free.append(slot_of[x.id])
-        phases.append((op, lanes))
+        phases.append((phase_op, lanes))
         for n in chosen:
             done.add(n.id)
             del pending[n.id]
