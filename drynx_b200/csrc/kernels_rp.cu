@@ -390,7 +390,9 @@ __global__ void k_flags_to_bytes(size_t n, const uint32_t* __restrict__ flags, u
 int launch_rp_verify_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                          const void* d_tabP, const uint8_t* d_proofs, uint32_t* d_flags) {
   if (!b.n) return 0;
-  k_rp_verify_hdr<<<grid_for(b.n, 128), 128, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const G1Aff*)d_tabP,
+  // one warp per block: these kernels run next to the lane-group pairing, whose pace is set by its most loaded SM;
+  // small blocks spread the extra warps over many SMs instead of stacking four on a few
+  k_rp_verify_hdr<<<grid_for(b.n, 32), 32, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const G1Aff*)d_tabP,
                                                      (const uint32_t*)d_proofs, d_flags);
   return 1;
 }
@@ -432,7 +434,7 @@ k_rp_verify_gt(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __rest
 int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                         const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch) {
   if (!b.items) return 0;
-  k_rp_verify_gt<<<grid_for(b.items, 64), 64, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const Fp12*)d_tabGtB,
+  k_rp_verify_gt<<<grid_for(b.items, 32), 32, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const Fp12*)d_tabGtB,
                                                       (const uint32_t*)d_proofs, d_flags, (GtPair*)d_scratch);
   return 1;
 }
