@@ -277,9 +277,10 @@ int UC_LAUNCH(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch
     uc_smem_optin = optin;
   }
   const int nblocks = grid_for(items, UC_ITEMS_PER_BLOCK);
-  // 5 % of the SMs are left out of the count: an exact fit (blocks = c * SMs) leaves no room for an SM that is busy
-  // with the side-stream kernels when the blocks are dealt, and the block that finds no SM waits for a whole wave
-  const int usable = nsm - (nsm + 19) / 20;
+  // 10 % of the SMs are left out of the count: a (nearly) exact fit (blocks = c * SMs) leaves no room for the SMs
+  // the side-stream kernels configured for L1 before the pairing blocks arrived (an SM changes its L1 / shared split
+  // only when it is empty), and a block that finds no SM waits for a whole wave (measured: 5.6 -> 7.2 ms)
+  const int usable = nsm - (nsm + 9) / 10;
   const int cap = (nblocks + usable - 1) / usable;
   int smem = natural;
   if (cap >= 1 && cap * (natural + 1024) <= smem_sm) {
