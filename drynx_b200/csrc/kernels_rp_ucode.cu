@@ -3,4 +3,6 @@
 #define UC_KERNEL k_pair_ucode_g4
 #define UC_LAUNCH launch_pair_ucode_g4
 #define UC_WITH_PREP 1
+#define UC_WITH_DYN 1
+#define UC_KERNEL_DYN k_pair_ucode_g4_dyn
 #include "ucode_body.cuh"

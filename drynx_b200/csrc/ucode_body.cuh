@@ -149,26 +149,12 @@ __device__ __forceinline__ void uc_store(Fp2* S, uint32_t s, const Fp2& r) {
 #endif
 #define UC_ITEMS_PER_BLOCK (UC_BLOCK / UC_G)
 
-__global__ void __launch_bounds__(UC_BLOCK)
-UC_KERNEL(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ scratch) {
-  extern __shared__ __align__(16) unsigned char uc_smem[];
-  Fp2* slots = (Fp2*)uc_smem;
-  const int grp = threadIdx.x / UC_G, lane = threadIdx.x % UC_G;
-  const size_t t = (size_t)blockIdx.x * UC_ITEMS_PER_BLOCK + grp;
-  const bool alive = t < items && prep[t].state == 0;
-  Fp2* S = slots + grp * UC_NSLOTS;
-  if (alive && lane == 0) {
-    uc_store(S, UC_IN_P, Fp2{prep[t].P.x, prep[t].P.y});
-    uc_store(S, UC_IN_QX, prep[t].V.x);
-    uc_store(S, UC_IN_QY, prep[t].V.y);
-    uc_store(S, UC_IN_ONE, fp2_one());
-    uc_store(S, UC_IN_ZERO, fp2_zero());
-  }
-  __syncwarp();
-  uint32_t op = uc_ops[0], w = uc_lanes[lane];
-  for (int ph = 0; ph < UC_NPHASES; ph++) {
+// Phases [ph0, ph1) of the program on one item's slots (S); all lanes of the warp call it together.
+__device__ __forceinline__ void uc_run(Fp2* S, int lane, bool alive, int ph0, int ph1) {
+  uint32_t op = uc_ops[ph0], w = uc_lanes[ph0 * UC_G + lane];
+  for (int ph = ph0; ph < ph1; ph++) {
     // fetch the next phase's words while this one computes
-    const int nx = ph + 1 < UC_NPHASES ? ph + 1 : ph;
+    const int nx = ph + 1 < ph1 ? ph + 1 : ph;
     const uint32_t op_n = uc_ops[nx], w_n = uc_lanes[nx * UC_G + lane];
     if (alive && w != 0xffffffffu) {
       const uint32_t d = w & 255u, ia = (w >> 8) & 255u, ib = (w >> 16) & 255u, ic = w >> 24;
@@ -228,22 +214,108 @@ UC_KERNEL(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ sc
     op = op_n;
     w = w_n;
   }
-  if (t < items && lane == 0) {
-    Fp12 e = fp12_one();
-    if (alive) {
-      e.c0.c0 = uc_load(S, UC_OUT_E00);
-      e.c0.c1 = uc_load(S, UC_OUT_E01);
-      e.c0.c2 = uc_load(S, UC_OUT_E02);
-      e.c1.c0 = uc_load(S, UC_OUT_E10);
-      e.c1.c1 = uc_load(S, UC_OUT_E11);
-      e.c1.c2 = uc_load(S, UC_OUT_E12);
-    }
-    scratch[t].a = e;
-  }
+}
+__device__ __forceinline__ void uc_put_inputs(Fp2* S, const UcPrep& in) {
+  uc_store(S, UC_IN_P, Fp2{in.P.x, in.P.y});
+  uc_store(S, UC_IN_QX, in.V.x);
+  uc_store(S, UC_IN_QY, in.V.y);
+  uc_store(S, UC_IN_ONE, fp2_one());
+  uc_store(S, UC_IN_ZERO, fp2_zero());
+}
+__device__ __forceinline__ Fp12 uc_get_output(const Fp2* S) {
+  Fp12 e;
+  e.c0.c0 = uc_load(S, UC_OUT_E00);
+  e.c0.c1 = uc_load(S, UC_OUT_E01);
+  e.c0.c2 = uc_load(S, UC_OUT_E02);
+  e.c1.c0 = uc_load(S, UC_OUT_E10);
+  e.c1.c1 = uc_load(S, UC_OUT_E11);
+  e.c1.c2 = uc_load(S, UC_OUT_E12);
+  return e;
 }
 
+__global__ void __launch_bounds__(UC_BLOCK)
+UC_KERNEL(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ scratch) {
+  extern __shared__ __align__(16) unsigned char uc_smem[];
+  Fp2* slots = (Fp2*)uc_smem;
+  const int grp = threadIdx.x / UC_G, lane = threadIdx.x % UC_G;
+  const size_t t = (size_t)blockIdx.x * UC_ITEMS_PER_BLOCK + grp;
+  const bool alive = t < items && prep[t].state == 0;
+  Fp2* S = slots + grp * UC_NSLOTS;
+  if (alive && lane == 0) uc_put_inputs(S, prep[t]);
+  __syncwarp();
+  uc_run(S, lane, alive, 0, UC_NPHASES);
+  if (t < items && lane == 0) scratch[t].a = alive ? uc_get_output(S) : fp12_one();
+}
+
+#ifdef UC_WITH_DYN
+// Dynamic variant for batches that would need a fourth block per SM or a second wave. The program is cut into UC_NSEG
+// segments of equal phase count; a task is (group of 32 / UC_G items, segment). Persistent warps (three blocks per
+// SM) take tasks from one atomic counter, segment-major, so every SM stays busy until the queue is empty instead of
+// the kernel running wave after wave at the pace of its fullest SM (measured, static -> dynamic: 789 proofs
+// 8.8 -> 7.1 ms, 1,000 proofs 10.3 -> 9.0 ms; at 500 proofs the static launch is faster, 5.45 against 5.56 ms). Between segments the
+// group's slots travel through global memory (the shared-memory image, copied as it is). A task waits for the
+// previous segment of its group on a flag word; that segment was handed out earlier, so its warp is already
+// running and the wait is bounded (it traps instead of spinning forever).
+#define UC_NSEG 32
+#define UC_GROUP_ITEMS (32 / UC_G)
+#define UC_GROUP_U4 (UC_GROUP_ITEMS * UC_NSLOTS * 4)  // uint4 words of one group's slots
+__global__ void __launch_bounds__(UC_BLOCK)
+UC_KERNEL_DYN(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ scratch, uint4* __restrict__ state,
+              unsigned int* __restrict__ ctrl, unsigned int nseg) {
+  extern __shared__ __align__(16) unsigned char uc_smem[];
+  Fp2* slots = (Fp2*)uc_smem;
+  const int grp = threadIdx.x / UC_G, lane = threadIdx.x % UC_G, wl = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  Fp2* S = slots + grp * UC_NSLOTS;
+  uint4* W = reinterpret_cast<uint4*>(slots + warp * UC_GROUP_ITEMS * UC_NSLOTS);
+  const unsigned int ngroups = (unsigned int)((items + UC_GROUP_ITEMS - 1) / UC_GROUP_ITEMS);
+  const unsigned int ntasks = ngroups * nseg;
+  volatile unsigned int* done = ctrl + 4;
+  for (;;) {
+    unsigned int task = 0;
+    if (wl == 0) task = atomicAdd(&ctrl[0], 1u);
+    task = __shfl_sync(0xffffffffu, task, 0);
+    if (task >= ntasks) break;
+    const unsigned int g = task % ngroups, seg = task / ngroups;
+    const size_t t = (size_t)g * UC_GROUP_ITEMS + wl / UC_G;
+    const bool alive = t < items && prep[t].state == 0;
+    if (seg == 0) {
+      if (alive && lane == 0) uc_put_inputs(S, prep[t]);
+    } else {
+      if (wl == 0) {
+        unsigned int polls = 0;
+        while (done[g] < seg) {
+          __nanosleep(200);
+          if (++polls > (1u << 24)) __trap();
+        }
+      }
+      __syncwarp();
+      __threadfence();
+      const uint4* src = state + (size_t)g * UC_GROUP_U4;
+      for (int i = wl; i < UC_GROUP_U4; i += 32) W[i] = __ldcg(src + i);
+    }
+    __syncwarp();
+    uc_run(S, lane, alive, (int)(seg * UC_NPHASES / nseg), (int)((seg + 1) * UC_NPHASES / nseg));
+    if (seg + 1 < nseg) {
+      uint4* dst = state + (size_t)g * UC_GROUP_U4;
+      for (int i = wl; i < UC_GROUP_U4; i += 32) __stcg(dst + i, W[i]);
+      __threadfence();
+      __syncwarp();
+      if (wl == 0) done[g] = seg + 1;
+    } else if (t < items && lane == 0) {
+      scratch[t].a = alive ? uc_get_output(S) : fp12_one();
+    }
+    __syncwarp();
+  }
+}
+#endif
+
 #ifdef UC_WITH_PREP
-size_t rp_ucode_prep_bytes(size_t items) { return items * sizeof(UcPrep); }
+// prepared arguments, then (dynamic kernel only) the control words and the groups' slot images
+static size_t uc_align256(size_t x) { return (x + 255) & ~(size_t)255; }
+size_t rp_ucode_prep_bytes(size_t items) {
+  const size_t ngroups = (items + UC_GROUP_ITEMS - 1) / UC_GROUP_ITEMS;
+  return uc_align256(items * sizeof(UcPrep)) + uc_align256(16 + 4 * ngroups) + ngroups * UC_GROUP_U4 * 16;
+}
 #endif
 
 #ifdef UC_WITH_PREP
@@ -288,6 +360,28 @@ int UC_LAUNCH(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch
     if (want > uc_smem_optin) want = uc_smem_optin;
     if (want > smem) smem = want;
   }
+#ifdef UC_WITH_DYN
+  // more than three blocks per usable SM: deal the work dynamically over three persistent blocks per SM (the
+  // occupancy with the best aggregate rate: 3 blocks in 5.4 ms against 2 in 4.1 ms or 4 in 8.8 ms)
+  if (nblocks > 3 * usable) {
+    static bool dyn_configured = false;
+    if (!dyn_configured) {
+      cudaFuncSetAttribute(UC_KERNEL_DYN, cudaFuncAttributeMaxDynamicSharedMemorySize, uc_smem_optin);
+      dyn_configured = true;
+    }
+    const size_t ngroups = (items + UC_GROUP_ITEMS - 1) / UC_GROUP_ITEMS;
+    unsigned char* base = (unsigned char*)d_prep + uc_align256(items * sizeof(UcPrep));
+    unsigned int* ctrl = (unsigned int*)base;
+    uint4* state = (uint4*)(base + uc_align256(16 + 4 * ngroups));
+    cudaMemsetAsync(ctrl, 0, 16 + 4 * ngroups, st);
+    const int smem3 = (smem_sm / 3 - 1024) & ~127;
+    int grid = 3 * nsm;
+    if (grid > nblocks) grid = nblocks;
+    const unsigned int nseg = UC_NSEG;
+    UC_KERNEL_DYN<<<grid, UC_BLOCK, smem3, st>>>(items, (const UcPrep*)d_prep, (GtPair*)d_scratch, state, ctrl, nseg);
+    return 1;
+  }
+#endif
   UC_KERNEL<<<grid_for(items, UC_ITEMS_PER_BLOCK), UC_BLOCK, smem, st>>>(items, (const UcPrep*)d_prep, (GtPair*)d_scratch);
   return 1;
 }

@@ -240,6 +240,39 @@ def test_creation_kernels_agree(backend, oracle, rng):
     assert a.tobytes() == bytes(want)
 
 
+def test_dynamic_segment_kernel_600_proofs(backend, oracle, rng):
+    """600 proofs x 12 checks = 7,200 pairing checks: more than three lane-group blocks per SM, so verification runs
+    the dynamic kernel (32 program segments dealt from a queue, slot images handed over through global memory). Every
+    proof verifies, the tampered ones (one per kind of field) are rejected, and a sample is checked against the oracle."""
+    ns, u, l, n = 3, 16, 4, 600
+    sk, P, Y, A = _setup(backend, oracle, rng, ns, u, set_id=62)
+    g = np.random.default_rng(62)
+    secrets = [int(x) for x in g.integers(0, u ** l, size=n)]
+    rs, cts, rnd = _make(backend, oracle, rng, P, ns, u, l, secrets)
+    proofs, off = backend.create_range_proofs([62] * n, {62: ns}, {62: u}, [l] * n, secrets, rs, cts, rnd)
+    size = int(off[1])
+    blk = 256 + 32 * l
+    bad = bytearray(proofs.tobytes())
+    flipped = {7: 170, 123: blk + 5, 300: blk + 128 * l + 77, 451: blk + 512 * l + 9, 599: size - 40}
+    for p_, o_ in flipped.items():
+        bad[p_ * size + o_] ^= 1
+    backend.set_option('rp_verify_path', 2)
+    backend.set_option('rp_ucode_lanes', 4)
+    try:
+        ok = backend.verify_range_proofs([62] * n, [l] * n, bytes(bad), off)
+        ok_clean = backend.verify_range_proofs([62] * n, [l] * n, proofs, off)
+    finally:
+        backend.set_option('rp_verify_path', 0)
+        backend.set_option('rp_ucode_lanes', 0)
+    assert list(ok_clean) == [1] * n
+    assert [i for i in range(n) if not ok[i]] == sorted(flipped)
+    idx = [5, 6, 7, 8, 122, 123, 124, 450, 451, 598, 599]
+    sub = b''.join(bytes(bad[i * size:(i + 1) * size]) for i in idx)
+    suboff = np.arange(len(idx) + 1, dtype=np.uint64) * size
+    want = oracle.rp_verify(ns, u, l, Y, P, sub, suboff, threads=8)
+    assert [int(ok[i]) for i in idx] == list(want)
+
+
 def test_config5_ten_thousand_proofs(backend, rng):
     """Config 5 at 10^4 proofs (u=16, l=4, ns=3: 120,000 pairing checks, 69 MB of proofs, the one-thread-per-check
     path): every created proof verifies, and exactly the 1 % that get one byte flipped are rejected."""
