@@ -349,18 +349,37 @@ def run_gpu(args):
         if rank == 0 and world == 1:
             ck(lib.drx_decrypt(be2.h, NOUT, skp, np_p(h_ag), 1, np_p(h_dec), np_p(h_found)))
 
+    # the second goroutine: a long-lived worker thread woken once per step (ctypes calls release the GIL)
+    go, done_ev, quit_flag, side_err = threading.Event(), threading.Event(), [False], []
+
+    def side_worker():
+        while True:
+            go.wait()
+            go.clear()
+            if quit_flag[0]:
+                return
+            try:
+                agg_dec()
+            except Exception as e:  # surfaced by the main thread after the join
+                side_err.append(e)
+            done_ev.set()
+    side_thread = threading.Thread(target=side_worker, daemon=True)
+    side_thread.start()
+
     def step_e2e():
         # what a Go data provider / root / verifying node would do with two goroutines and one context each:
         # aggregation + decryption only need the ciphertexts and run next to proof creation + verification
         ck(lib.drx_reduce_rows(be.h, ndp, rows, np_p(h['rows']), 3, np_p(h_m)))
         m = h_m
         ck(lib.drx_encrypt(be.h, n, np_p(m), np_p(h['r']), np_p(h_ct)))
-        side = threading.Thread(target=agg_dec)
-        side.start()
+        go.set()
         ck(lib.drx_rp_create(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(m), np_p(h['r']), np_p(h_ct), np_p(h['rnd']), np_p(roff),
                              np_p(h_pr), np_p(poff)))
         ck(lib.drx_rp_verify(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h_pr), np_p(poff), np_p(h_ok)))
-        side.join()
+        done_ev.wait()
+        done_ev.clear()
+        if side_err:
+            raise side_err[0]
         return m
     h2d = h['rows'].nbytes + (n * 8 + n * 32) + (n * 4 + n * 8 * 2 + n * 32 + n * 128 + h['rnd'].nbytes) + (n * 4 + n * 8 + h_pr.nbytes + n * 4) \
         + h_ct.nbytes + (NOUT * 128 + 32)  # encrypt + create + verify + aggregate + decrypt inputs
@@ -379,6 +398,8 @@ def run_gpu(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     e2e_val = world * n * args.steps / e2e_s
+    quit_flag[0] = True
+    go.set()
     be.set_stream(stream.cuda_stream or 1)
     be2.set_stream(stream2.cuda_stream)
 
