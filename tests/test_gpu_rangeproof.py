@@ -273,6 +273,66 @@ def test_dynamic_segment_kernel_600_proofs(backend, oracle, rng):
     assert [int(ok[i]) for i in idx] == list(want)
 
 
+def test_ragged_batch_through_every_path(backend, oracle, rng):
+    """A ragged batch large enough for the dynamic lane-group kernel (1,200 proofs over three signature sets with
+    different server counts, bases and digit counts, commit-only proofs in between, 7,200 pairing checks): the
+    one-thread path, the lane-group path and the oracle (on a sample) agree on every accept / reject bit."""
+    sk = rng.scalar()
+    P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+    backend.set_pubkey(P)
+    sets = {}
+    for sid, (ns, u) in {80: (3, 16), 81: (1, 4), 82: (2, 8)}.items():
+        xs = [rng.scalar() for _ in range(ns)]
+        Y, A = oracle.make_sigs(xs, u)
+        backend.set_signatures(sid, ns, u, Y, A)
+        sets[sid] = (ns, u, Y, A)
+    g = np.random.default_rng(80)
+    n = 1200
+    kinds = [(80, 4), (81, 6), (82, 3), (-1, 0), (80, 2)]
+    plan = []
+    for i in range(n):
+        sid, l = kinds[i % len(kinds)]
+        top = sets[sid][1] ** l if sid >= 0 else 10
+        plan.append((sid, l, int(g.integers(0, top))))
+    sids = [p[0] for p in plan]; ls = [p[1] for p in plan]; secrets = [p[2] for p in plan]
+    rb = np.frombuffer(g.bytes(32 * n), np.uint8).copy()
+    rb[::32] &= 0x7f
+    rs = rb.tobytes()
+    cts = backend.encrypt_int_vector(secrets, rs).tobytes()
+    rnd = []
+    for sid, l, s_ in plan:
+        if sid < 0:
+            rnd.append(b'')
+        else:
+            k = np.frombuffer(g.bytes(32 * l * (3 + sets[sid][0])), np.uint8).copy()
+            k[::32] &= 0x7f
+            rnd.append(k.tobytes())
+    proofs, off = backend.create_range_proofs(sids, {k: v[0] for k, v in sets.items()}, {k: v[1] for k, v in sets.items()},
+                                              ls, secrets, rs, cts, rnd)
+    bad = bytearray(proofs.tobytes())
+    flipped = [0, 11, 101, 452, 1197]      # proofs of sets 80, 81, 81, 82, 82 (no commit-only ones)
+    for i in flipped:
+        assert sids[i] >= 0
+        bad[int(off[i + 1]) - 40] ^= 1      # inside the last Zv of the proof
+    results = {}
+    for path, lanes in ((1, 0), (2, 4)):
+        backend.set_option('rp_verify_path', path)
+        backend.set_option('rp_ucode_lanes', lanes)
+        try:
+            results[path] = list(backend.verify_range_proofs(sids, ls, bytes(bad), off))
+        finally:
+            backend.set_option('rp_verify_path', 0)
+            backend.set_option('rp_ucode_lanes', 0)
+    assert results[1] == results[2]
+    assert [i for i in range(n) if not results[2][i]] == flipped
+    for i in (0, 1, 2, 11, 452):
+        sid, l, s_ = plan[i]
+        ns, u, Y, A = sets[sid]
+        one = bytes(bad[int(off[i]):int(off[i + 1])])
+        want = oracle.rp_verify(ns, u, l, Y, P, one, np.array([0, len(one)], np.uint64))
+        assert int(want[0]) == results[2][i]
+
+
 def test_config5_ten_thousand_proofs(backend, rng):
     """Config 5 at 10^4 proofs (u=16, l=4, ns=3: 120,000 pairing checks, 69 MB of proofs, the one-thread-per-check
     path): every created proof verifies, and exactly the 1 % that get one byte flipped are rejected."""
