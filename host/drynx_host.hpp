@@ -814,7 +814,19 @@ inline std::vector<int64_t> LogisticRegressionPlaintext(const std::vector<std::v
 inline Encoded EncodeLogisticRegressionWithProofs(const std::vector<std::vector<double>>& xData, const std::vector<int64_t>& yData,
                                                   const LogisticRegressionParameters& lr, const Point& pubKey,
                                                   const std::vector<SignatureColumn>* sigs, const Ranges* lu) {
-  const auto packed = LogisticRegressionPlaintext(xData, yData, lr);
+  // the float64 pre-pass runs on the device (k_logreg_coeffs adds in record order with unfused, correctly rounded
+  // operations: the integers equal LogisticRegressionPlaintext's, which host/test_host.cpp checks)
+  if (lr.K < 1 || lr.K > 2) throw drynx::Error(-1, "logistic regression: the coefficient packing is only defined for k <= 2");
+  const size_t d = (size_t)lr.NbrFeatures;
+  std::vector<int64_t> packed((size_t)getTotalNumberApproxCoefficients(lr.NbrFeatures, lr.K), 0);
+  if (!xData.empty()) {
+    std::vector<double> flat;
+    flat.reserve(xData.size() * d);
+    for (auto& rec : xData) flat.insert(flat.end(), rec.begin(), rec.end());
+    const size_t off[2] = {0, xData.size()};
+    drynx::check(drx_logreg_coefficients(drynx::Gpu::get().ctx(), 1, off, (int)d, lr.K, flat.data(), yData.data(), lr.Means.data(),
+                                         lr.StandardDeviations.data(), lr.PrecisionApproxCoefficients, packed.data()));
+  }
   for (int64_t v : packed)
     if (v > libunlynx::MaxHomomorphicInt) throw drynx::Error(-1, "coefficient exceeds MaxHomomorphicInt");  // log.Fatalf at :415
   return encrypt_and_describe(packed, pubKey, sigs, lu);
