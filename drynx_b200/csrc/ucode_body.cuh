@@ -5,6 +5,7 @@
 // (dst, a, b) slots; no thread-local stack is involved, which is what bounded the one-thread-per-item kernel
 // (DESIGN.md section 5). Replaces kyber pairing/bn256 optate.go for lib/range/range_proof.go:540-544.
 #pragma once
+#include <cstdio>
 #include <cstdlib>
 
 #define DRX_FP2_INLINE_MUL 1
@@ -149,16 +150,37 @@ __device__ __forceinline__ void uc_store(Fp2* S, uint32_t s, const Fp2& r) {
 #endif
 #define UC_ITEMS_PER_BLOCK (UC_BLOCK / UC_G)
 
+#ifdef UC_CLOCKS
+// Experiment build (-DUC_CLOCKS, never the shipped library): cycle accounting of the phase loop for thread 0 of
+// block 0, printed when the kernel ends. The clock reads take a data dependence on the values they follow, so
+// "operand" ends when the first operand has arrived and "compute" when the result exists.
+__device__ __forceinline__ long long uc_clk(uint32_t dep) {
+  long long t;
+  asm volatile("mov.u64 %0, %%clock64; // %1" : "=l"(t) : "r"(dep) : "memory");
+  return t;
+}
+#endif
+
 // Phases [ph0, ph1) of the program on one item's slots (S); all lanes of the warp call it together.
 __device__ __forceinline__ void uc_run(Fp2* S, int lane, bool alive, int ph0, int ph1) {
   uint32_t op = uc_ops[ph0], w = uc_lanes[ph0 * UC_G + lane];
+#ifdef UC_CLOCKS
+  long long acc[3][3] = {{0}}, whole = 0;
+  int cnt[3] = {0, 0, 0};
+#endif
   for (int ph = ph0; ph < ph1; ph++) {
+#ifdef UC_CLOCKS
+    const long long c0 = uc_clk(op);
+#endif
     // fetch the next phase's words while this one computes
     const int nx = ph + 1 < ph1 ? ph + 1 : ph;
     const uint32_t op_n = uc_ops[nx], w_n = uc_lanes[nx * UC_G + lane];
     if (alive && w != 0xffffffffu) {
       const uint32_t d = w & 255u, ia = (w >> 8) & 255u, ib = (w >> 16) & 255u, ic = w >> 24;
       const Fp2 a = uc_load(S, ia);
+#ifdef UC_CLOCKS
+      const long long c1 = uc_clk(a.c0.v[0] ^ a.c1.v[7]);
+#endif
       Fp2 r;
       // ordered by how often the generated program uses each operation (a compare-and-branch chain is cheaper
       // than the balanced search ptxas builds for a switch, and the hot cases come first)
@@ -208,12 +230,32 @@ __device__ __forceinline__ void uc_run(Fp2* S, int lane, bool alive, int ph0, in
       } else {
         r = a;  // UC_COPY
       }
+#ifdef UC_CLOCKS
+      const long long c2 = uc_clk(r.c0.v[0] ^ r.c1.v[7] ^ r.c1.v[0] ^ r.c0.v[7]);
+#endif
       uc_store(S, d, r);
+#ifdef UC_CLOCKS
+      const long long c3 = uc_clk(d);
+      const int cls = op == UC_ADD ? 0 : op == UC_MUL ? 1 : 2;
+      acc[cls][0] += c1 - c0;
+      acc[cls][1] += c2 - c1;
+      acc[cls][2] += c3 - c2;
+      cnt[cls]++;
+#endif
     }
     __syncwarp();
     op = op_n;
     w = w_n;
+#ifdef UC_CLOCKS
+    whole += uc_clk(op) - c0;
+#endif
   }
+#ifdef UC_CLOCKS
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    printf("UC_CLOCKS G=%d cycles (operand / compute / store) | ADD n=%d %lld %lld %lld | MUL n=%d %lld %lld %lld | other n=%d %lld "
+           "%lld %lld | all phases %lld\n", UC_G, cnt[0], acc[0][0], acc[0][1], acc[0][2], cnt[1], acc[1][0], acc[1][1], acc[1][2],
+           cnt[2], acc[2][0], acc[2][1], acc[2][2], whole);
+#endif
 }
 __device__ __forceinline__ void uc_put_inputs(Fp2* S, const UcPrep& in) {
   uc_store(S, UC_IN_P, Fp2{in.P.x, in.P.y});
