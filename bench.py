@@ -36,6 +36,8 @@ M_VERIFY_PROOF = 3550 + 352 * (NS + L) + M_VERIFY_ITEM * NS * L
 M_CREATE_PROOF = L * (736 + NS * 4458)
 M_AGG_CT = 22
 M_DECRYPT = 2840
+G1_BYTES = bytes(31) + b'\x01' + (65000549695646603732796438742359905742825358107623003571877145026864184071783 - 2).to_bytes(32, 'big')
+M_KEYSWITCH = 352 + 352 + 2816 + 16 + 16   # v*B and v*Q by comb, x*rB by 4-bit windows, one addition, two affine outputs
 
 
 def parse():
@@ -168,6 +170,15 @@ def run_reference(args):
     t1 = time.perf_counter()
     logreg_ref.coefficients(lx, ly, [0.0] * 8, [100.0] * 8, 2, 1.0)
     lr_rate = 100000 / (time.perf_counter() - t1)
+    # key switching: one server's contribution for 2,048 ciphertexts on all cores
+    ks_n = 2048
+    ks_ct = orc.encrypt(P, np.arange(ks_n, dtype=np.int64) % 10, np.random.default_rng(8).bytes(32 * ks_n), threads=cores)
+    ks_rb = b''.join(ks_ct[128 * i:128 * i + 64] for i in range(ks_n))
+    ks_v = np.random.default_rng(9).bytes(32 * ks_n)   # Scalar.SetBytes reduces mod n
+    t1 = time.perf_counter()
+    rc, _, _ = orc.key_switch(P, d['sk'].to_bytes(32, 'big'), ks_rb, ks_v, threads=cores)
+    ks_rate = ks_n / (time.perf_counter() - t1)
+    assert rc == 0
     sample = '%d of %d DPs x %d rows (%d proofs/step), oracle/oracle.cpp C++ restatement of the Go path' % (ndp, args.ndp, args.rows, n)
     print(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'proofs/s', 'n_gpus': args.gpus, 'steps': args.steps,
@@ -175,7 +186,8 @@ def run_reference(args):
         'vs_baseline': None, 'dtype': 'u64 (4x64-bit Montgomery limbs)', 'data': 'synthetic',
         'config': {'workload': 'config 2: mean+variance, %d DPs x %d rows, u=16 l=4 ns=3 (bounded sample: %d DPs)' % (args.ndp, args.rows, ndp)},
         'cpu_baseline': {'value': val, 'unit': 'proofs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
-                         'ed25519_encs_per_s': ed_rate, 'logreg_prepass_records_per_s': lr_rate},
+                         'ed25519_encs_per_s': ed_rate, 'logreg_prepass_records_per_s': lr_rate,
+                         'keyswitch_cts_per_s': ks_rate},
         'e2e': {'value': val, 'unit': 'proofs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }))
@@ -490,6 +502,13 @@ def secondary_rates(be, lib, torch, dev, stream, ck, vp, peak_tmac, skp):
     ms = timed(lambda: ck(lib.drx_decrypt_dev(be.h, nd, skp, vp(ct), vp(dec2))))
     out['decrypts_per_s'] = nd / ms * 1e3
     out['decrypt_roofline_frac'] = nd * M_DECRYPT * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    # key switching: one server's contribution for 2^17 ciphertexts, K components taken from ct
+    be.set_target_pubkey(be.g1_mul((0x7654321).to_bytes(32, 'big'), G1_BYTES))
+    rbk = ct[:nd * 128].view(nd, 128)[:, :64].contiguous()
+    cv = torch.empty(nd * 128, dtype=torch.uint8, device=dev)
+    ms = timed(lambda: ck(lib.drx_keyswitch_dev(be.h, nd, skp, vp(rbk), vp(r), vp(cv), None)))
+    out['keyswitch_cts_per_s'] = nd / ms * 1e3
+    out['keyswitch_roofline_frac'] = nd * M_KEYSWITCH * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
     # verification sweep point
     npf = 20000
     sid = torch.from_numpy((np.arange(npf, dtype=np.int32) % NOUT)).to(dev)

@@ -119,6 +119,24 @@ class Backend:
         _lib.check(self.lib.drx_encrypt_scalar(self.h, m.size // 32, _ptr(m), _ptr(r), _ptr(ct)))
         return ct
 
+    def set_target_pubkey(self, Q):
+        """The querier's public key (64 bytes) for key switching."""
+        q = _u8(Q)
+        assert q.size == 64
+        _lib.check(self.lib.drx_set_target_pubkey(self.h, _ptr(q)))
+
+    def key_switch(self, sk, rbs, vs, want_rb_neg=False):
+        """libunlynxkeyswitch.KeySwitchSequence with injected vi: rbs n*64 bytes (K components), vs n*32 bytes ->
+        n*128 bytes of contributions (vi*B || vi*Q - sk*rB), plus n*64 bytes of -rB when asked."""
+        rb, v, k = _u8(rbs), _u8(vs), _u8(sk)
+        n = rb.size // 64
+        assert rb.size == 64 * n and v.size == 32 * n and k.size == 32
+        cv = np.empty(128 * n, dtype=np.uint8)
+        neg = np.empty(64 * n, dtype=np.uint8) if want_rb_neg else None
+        _lib.check(self.lib.drx_keyswitch(self.h, n, _ptr(k), _ptr(rb), _ptr(v), _ptr(cv),
+                                          _ptr(neg) if want_rb_neg else None))
+        return (cv, neg) if want_rb_neg else cv
+
     def aggregate(self, vectors):
         """CipherVector.Add over a list of serialised CipherVectors (each v*128 bytes)."""
         vs = [_u8(v) for v in vectors]

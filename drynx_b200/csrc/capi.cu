@@ -141,12 +141,12 @@ struct drx_ctx {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;  // fork/join of the side stream (independent small kernels)
   std::mutex mu;
   uint64_t launches = 0;
-  bool have_pub = false, have_dlog = false;
+  bool have_pub = false, have_dlog = false, have_target = false;
   int opt_verify_path = 0;  // drx_set_option "rp_verify_path"
   int opt_create_path = 0;  // drx_set_option "rp_create_path": 0 = by batch size, 1 = never the lane-cooperative kernel
   int opt_ucode_lanes = 0;  // drx_set_option "rp_ucode_lanes": 0 = by batch size, 4 or 8
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
-      sets_dev, sink;
+      sets_dev, sink, tabQ, target_aff;  // tabQ: comb table of the key-switching target key
   Arena arena;
   Profiler prof;
   DlogModel dlog;
@@ -291,7 +291,8 @@ void drx_free(drx_ctx* c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   for (DevBuf* b : {&c->baseB_aff, &c->baseB_wire, &c->g2_aff, &c->g2_wire, &c->gtB, &c->tabB, &c->tabP, &c->pub_aff,
-                    &c->tabGtB, &c->tabG2, &c->dlog_keys, &c->dlog_vals, &c->bad, &c->sets_dev, &c->sink, &c->ed_pt,
+                    &c->tabGtB, &c->tabG2, &c->dlog_keys, &c->dlog_vals, &c->bad, &c->sets_dev, &c->sink, &c->tabQ,
+                    &c->target_aff, &c->ed_pt,
                     &c->ed_tabB, &c->ed_tabP, &c->ed_dlog_keys, &c->ed_dlog_vals})
     b->release();
   c->arena.buf.release();
@@ -607,6 +608,70 @@ int drx_dlog_table(drx_ctx* c, int64_t limit) {
   bool found;
   c->dlog.resolve(limit < kMaxHomomorphicInt ? limit : INT64_MIN, true, &found);
   CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// ---- key switching: libunlynxkeyswitch.KeySwitchSequence(targetPubKey, rBs, secretKey)
+int drx_set_target_pubkey(drx_ctx* c, const uint8_t Q[64]) {
+  if (!c || !Q) return fail(-1, "drx_set_target_pubkey: null argument");
+  Guard g(c);
+  RET(c->target_aff.ensure(64));
+  RET(c->tabQ.ensure(kCombPoints * 64));
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t o = a.plan(64);
+  RET(a.commit());
+  RET(reset_bad(c));
+  CU(cudaMemcpyAsync(a.at<uint8_t>(o), Q, 64, cudaMemcpyHostToDevice, c->stream));
+  c->launches += launch_g1_from_wire(c->stream, 1, a.at<uint8_t>(o), c->target_aff.p, (int*)c->bad.p);
+  c->launches += launch_comb_table_g1(c->stream, 1, c->target_aff.p, c->tabQ.p);
+  RET(check_launch("set_target_pubkey"));
+  int bad = 0;
+  RET(read_bad(c, &bad));
+  if (bad) { c->have_target = false; return fail(-2, "drx_set_target_pubkey: malformed point"); }
+  c->have_target = true;
+  return 0;
+}
+
+int drx_keyswitch_dev(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* d_rb, const uint8_t* d_v, uint8_t* d_cv,
+                      uint8_t* d_rb_neg) {
+  if (!c || !sk) return fail(-1, "null argument");
+  Guard g(c);
+  if (!c->have_target) return fail(-1, "drx_keyswitch: call drx_set_target_pubkey first");
+  // the key travels through the tail of the 256-byte flag buffer
+  CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
+  timed(c, "k_keyswitch", [&] {
+    return launch_keyswitch(c->stream, n, (uint8_t*)c->bad.p + 64, d_rb, d_v, c->tabB.p, c->tabQ.p, d_cv, d_rb_neg,
+                            (int*)c->bad.p);
+  });
+  return check_launch("keyswitch");
+}
+
+int drx_keyswitch(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* rb, const uint8_t* v, uint8_t* cv,
+                  uint8_t* rb_neg) {
+  if (!c) return fail(-1, "null context");
+  if (n == 0) return 0;
+  if (!sk || !rb || !v || !cv) return fail(-1, "drx_keyswitch: null buffer");
+  Guard g(c);
+  if (!c->have_target) return fail(-1, "drx_keyswitch: call drx_set_target_pubkey first");
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t orb = a.plan(n * 64), ov = a.plan(n * 32), oc = a.plan(n * 128), on = a.plan(rb_neg ? n * 64 : 0);
+  RET(a.commit());
+  RET(reset_bad(c));
+  CU(cudaMemcpyAsync(a.at<void>(orb), rb, n * 64, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(a.at<void>(ov), v, n * 32, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
+  timed(c, "k_keyswitch", [&] {
+    return launch_keyswitch(c->stream, n, (uint8_t*)c->bad.p + 64, a.at<uint8_t>(orb), a.at<uint8_t>(ov), c->tabB.p,
+                            c->tabQ.p, a.at<uint8_t>(oc), rb_neg ? a.at<uint8_t>(on) : nullptr, (int*)c->bad.p);
+  });
+  RET(check_launch("keyswitch"));
+  CU(cudaMemcpyAsync(cv, a.at<void>(oc), n * 128, cudaMemcpyDeviceToHost, c->stream));
+  if (rb_neg) CU(cudaMemcpyAsync(rb_neg, a.at<void>(on), n * 64, cudaMemcpyDeviceToHost, c->stream));
+  int bad = 0;
+  RET(read_bad(c, &bad));
+  if (bad) return fail(-2, "drx_keyswitch: %d malformed points", bad);
   return 0;
 }
 

@@ -575,6 +575,40 @@ int launch_decrypt(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t
   return 1;
 }
 
+// ------------------------------------------------------------------ key switching
+// One server's contribution to switching ciphertext i from the collective key to the target key Q
+// (libunlynxkeyswitch.KeySwitchSequence, unlynx v1.4.0; call sites data/data.go:80, services/service.go:565-616):
+// K' = v_i*B, C' = v_i*Q - x*rB_i with rB_i the K component of the ciphertext, x the server's secret and v_i the
+// injected randomness. Two comb walks and one windowed variable-base product per thread, one shared inversion;
+// -rB_i (needed by the proof) costs a field negation on the way out.
+__global__ void __launch_bounds__(128)
+k_keyswitch(size_t n, const uint32_t* __restrict__ sk, const uint32_t* __restrict__ rb, const uint32_t* __restrict__ v,
+            const G1Aff* __restrict__ tabB, const G1Aff* __restrict__ tabQ, uint32_t* __restrict__ cv,
+            uint32_t* __restrict__ rb_neg, int* bad) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  G1Aff R;
+  if (!g1_from_wire(R, rb + 16 * i)) {
+    atomicAdd(bad, 1);
+    return;
+  }
+  const G1Aff Rn = aff_neg(R);
+  if (rb_neg) g1_to_wire(rb_neg + 16 * i, Rn);
+  const Scalar vi = sc_from_wire(v + 8 * i);
+  const G1Jac K = comb_mul(tabB, vi);
+  const G1Jac S = comb_mul(tabQ, vi);
+  const G1Jac X = window_mul(jac_from_aff(Rn), sc_from_wire(sk));
+  store_pair_wire(cv + 32 * i, K, jac_add(X, S));
+}
+int launch_keyswitch(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t* d_rb, const uint8_t* d_v,
+                     const void* d_tabB, const void* d_tabQ, uint8_t* d_cv, uint8_t* d_rb_neg, int* d_bad) {
+  if (!n) return 0;
+  k_keyswitch<<<grid_for(n, 128), 128, 0, st>>>(n, (const uint32_t*)d_sk, (const uint32_t*)d_rb, (const uint32_t*)d_v,
+                                               (const G1Aff*)d_tabB, (const G1Aff*)d_tabQ, (uint32_t*)d_cv,
+                                               (uint32_t*)d_rb_neg, d_bad);
+  return 1;
+}
+
 // ------------------------------------------------------------------ diagnostics
 __global__ void k_g1_mul(size_t n, const uint32_t* __restrict__ k, const uint32_t* __restrict__ pt,
                          uint32_t* __restrict__ out, int* bad) {

@@ -50,6 +50,9 @@ int launch_reduce_rows(cudaStream_t st, size_t ndp, size_t nrows, const int64_t*
 int launch_dlog_build(cudaStream_t st, const void* d_tabB, const void* d_baseB_aff, void* d_keys, uint32_t* d_vals);
 int launch_decrypt(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t* d_ct, const void* d_keys,
                    const uint32_t* d_vals, int64_t* d_out, int* d_bad);
+// key switching: cv[i] = (v_i*B) || (v_i*Q - sk*rb_i), rb_neg[i] = -rb_i (optional)
+int launch_keyswitch(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t* d_rb, const uint8_t* d_v,
+                     const void* d_tabB, const void* d_tabQ, uint8_t* d_cv, uint8_t* d_rb_neg, int* d_bad);
 int launch_g1_mul(cudaStream_t st, size_t n, const uint8_t* d_k, const uint8_t* d_pt, uint8_t* d_out, int* d_bad);
 int launch_mont_mul(cudaStream_t st, size_t n, int which, const uint32_t* d_a, const uint32_t* d_b, uint32_t* d_r);
 int launch_microbench(cudaStream_t st, int kind, int iters, int blocks, int threads, uint32_t* d_sink);

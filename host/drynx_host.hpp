@@ -196,6 +196,50 @@ inline void CreateDecryptionTable(int64_t limit, const Point&, const Scalar&) {
 }  // namespace libunlynx
 
 // =====================================================================================================================
+namespace libunlynxkeyswitch {
+using drynx::Gpu;
+using drynx::Point;
+using drynx::Scalar;
+
+struct Sequence {  // the four return values of KeySwitchSequence
+  libunlynx::CipherVector cv;   // (vi*B, ks2_i)
+  std::vector<Point> ks2s;      // vi*targetPubKey - secretKey*rB_i
+  std::vector<Point> rBNegs;    // -rB_i
+  std::vector<Scalar> vis;
+};
+// KeySwitchSequence(targetPubKey, rBs, secretKey) (unlynx lib/key_switch/key_switch.go; data/data.go:80,
+// services/service.go:565-616): vi drawn from the random stream per element, one batched device call.
+inline Sequence KeySwitchSequence(const Point& targetPubKey, const std::vector<Point>& rBs, const Scalar& secretKey) {
+  static Point cur{};
+  static bool have = false;
+  if (!have || memcmp(cur.b, targetPubKey.b, 64)) {
+    drynx::check(drx_set_target_pubkey(Gpu::get().ctx(), targetPubKey.b));
+    cur = targetPubKey;
+    have = true;
+  }
+  Sequence s;
+  const size_t n = rBs.size();
+  s.vis.resize(n);
+  for (auto& v : s.vis) v = drynx::pick();
+  s.cv.resize(n);
+  s.ks2s.resize(n);
+  s.rBNegs.resize(n);
+  if (n) drynx::check(drx_keyswitch(Gpu::get().ctx(), n, secretKey.b, rBs[0].b, s.vis[0].b, s.cv[0].b, s.rBNegs[0].b));
+  for (size_t i = 0; i < n; i++) memcpy(s.ks2s[i].b, s.cv[i].b + 64, 64);
+  return s;
+}
+// What the root of protocolsunlynx.KeySwitchingProtocol ends with: (0, C_i) plus every server's contribution.
+inline libunlynx::CipherVector Combine(const libunlynx::CipherVector& original, const std::vector<libunlynx::CipherVector>& contributions) {
+  libunlynx::CipherVector start = original;
+  for (auto& c : start) memset(c.b, 0, 64);
+  std::vector<libunlynx::CipherVector> all{start};
+  all.insert(all.end(), contributions.begin(), contributions.end());
+  return libunlynx::AddAll(all);
+}
+
+}  // namespace libunlynxkeyswitch
+
+// =====================================================================================================================
 namespace libdrynx {
 // PublishSignatureBytes (lib/structs.go:131-141): one server's public key and its u signatures A_k, in wire form.
 struct PublishSignatureBytes {

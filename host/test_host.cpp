@@ -306,6 +306,47 @@ static void TestEncodeDecodeDispatcher() {  // encode_decode.go Encode / Decode 
   EXPECT(libdrynxrange::RangeProofListVerification(list, lu, sigs, keys.Public, 1.0));
 }
 
+// The UnLynx key-switching protocol as Drynx runs it (services/service.go:565-616, 853-862; data/data.go:73-83):
+// the aggregate is encrypted under the collective key of three servers; every server contributes
+// KeySwitchSequence(querierKey, rBs, itsSecret); the root adds the contributions to (0, C); the querier decrypts.
+static void TestKeySwitching() {
+  std::vector<drynx::KeyPair> servers = {drynx::NewKeyPair(), drynx::NewKeyPair(), drynx::NewKeyPair()};
+  // collective key = sum of the servers' public keys (summed as the two halves of ciphertext-shaped values)
+  std::vector<libunlynx::CipherVector> shaped;
+  for (auto& k : servers) {
+    libunlynx::CipherText c;
+    memcpy(c.b, k.Public.b, 64);
+    memcpy(c.b + 64, k.Public.b, 64);
+    shaped.push_back({c});
+  }
+  drynx::Point collective;
+  memcpy(collective.b, libunlynx::AddAll(shaped)[0].b, 64);
+  auto querier = drynx::NewKeyPair();
+  libunlynx::CreateDecryptionTable(10000, querier.Public, querier.Private);
+  std::vector<int64_t> values = {1, 2, 0, -3, 9999};
+  auto cv = libunlynx::EncryptIntVector(collective, values);
+  std::vector<drynx::Point> rBs(cv.size());
+  for (size_t i = 0; i < cv.size(); i++) memcpy(rBs[i].b, cv[i].b, 64);
+  std::vector<libunlynx::CipherVector> contributions;
+  for (auto& k : servers) {
+    auto seq = libunlynxkeyswitch::KeySwitchSequence(querier.Public, rBs, k.Private);
+    EXPECT(seq.cv.size() == values.size() && seq.ks2s.size() == values.size() && seq.rBNegs.size() == values.size() &&
+           seq.vis.size() == values.size());
+    EXPECT(!memcmp(seq.ks2s[1].b, seq.cv[1].b + 64, 64));
+    // rBNeg + rB = identity: adding them as ciphertext halves gives 128 zero bytes
+    libunlynx::CipherText a, b;
+    memcpy(a.b, rBs[0].b, 64); memcpy(a.b + 64, rBs[0].b, 64);
+    memcpy(b.b, seq.rBNegs[0].b, 64); memcpy(b.b + 64, seq.rBNegs[0].b, 64);
+    uint8_t zero[128] = {0};
+    EXPECT(!memcmp(libunlynx::Add({a}, {b})[0].b, zero, 128));
+    contributions.push_back(seq.cv);
+  }
+  auto switched = libunlynxkeyswitch::Combine(cv, contributions);
+  EXPECT(libunlynx::DecryptIntVectorWithNeg(querier.Private, switched) == values);
+  // not decryptable by a single server, nor by the querier before switching
+  EXPECT(libunlynx::DecryptIntVectorWithNeg(querier.Private, cv) != values);
+}
+
 int main(int argc, char** argv) {
   const bool cpu_only = argc > 1 && !strcmp(argv[1], "--cpu");
   TestComputeApproxCoefficients();
@@ -326,6 +367,7 @@ int main(int argc, char** argv) {
       TestEncodeDecodeUnionInter();
       TestEncodeDecodeCosimAndModelEvaluation();
       TestEncodeDecodeDispatcher();
+      TestKeySwitching();
     } catch (const drynx::Error& e) {
       printf("FAIL: exception %d: %s\n", e.code, e.what());
       failures++;

@@ -142,6 +142,19 @@ int drx_decrypt_dev(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t*
  * identity, else 1. */
 int drx_decrypt_check_zero(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t* ct, int64_t* out);
 
+/* Key switching: one server's contribution to moving n ciphertexts from the collective
+ * key to the querier's key Q. Replaces libunlynxkeyswitch.KeySwitchSequence(targetPubKey, rBs, secretKey)
+ * (github.com/ldsec/unlynx v1.4.0 lib/key_switch/key_switch.go; call sites data/data.go:80 and, through
+ * protocolsunlynx.KeySwitchingProtocol, services/service.go:565-616, 853-862) with the per-element randomness vi
+ * injected: cv[i] = (v_i*B) || (v_i*Q - sk*rb_i), where rb_i is the K component of ciphertext i; rb_neg[i] = -rb_i
+ * (the proof's rBNegs; may be NULL). The root adds the contributions of all servers to (0, C_i) with
+ * drx_aggregate; the result decrypts under the querier's secret. Returns -2 on a malformed point. */
+int drx_set_target_pubkey(drx_ctx* ctx, const uint8_t Q[64]);
+int drx_keyswitch(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t* rb /*n*64*/, const uint8_t* v /*n*32*/,
+                  uint8_t* cv /*n*128*/, uint8_t* rb_neg /*n*64 or NULL*/);
+int drx_keyswitch_dev(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t* d_rb, const uint8_t* d_v, uint8_t* d_cv,
+                      uint8_t* d_rb_neg);
+
 /* Server signatures for one output column: Y_i and A_{i,k} = (x_i + k)^-1 * g2, k < u
  * (lib/range/range_proof.go:249-302 InitRangeProofSignature, PublishSignatureBytesToPublishSignatures;
  * libdrynx.PublishSignatureBytes lib/structs.go:131-141). Builds the per-set tables; set_id is the caller's

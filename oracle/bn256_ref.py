@@ -300,6 +300,14 @@ def decrypt_point(sk, ct):
     return g1_add(C, g1_neg(g1_mul(sk, K)))
 
 
+def key_switch(target_pub, rb, sk, v):
+    """libunlynxkeyswitch.KeySwitchSequence for one element (unlynx v1.4.0 lib/key_switch/key_switch.go, recalled;
+    call sites data/data.go:80, services/service.go:565-616): contribution (v*B, v*Q - sk*rB) and -rB."""
+    rb_neg = g1_neg(rb)
+    ks2 = g1_add(g1_mul(sk, rb_neg), g1_mul(v, target_pub))
+    return g1_to_bytes(g1_mul(v, G1_GEN)) + g1_to_bytes(ks2), g1_to_bytes(rb_neg)
+
+
 # ------------------------------------------------------------------ range proof (lib/range/range_proof.go)
 def to_base(v, b, l):
     """lib/range/range_proof.go:584-595."""

@@ -1182,6 +1182,29 @@ static void encrypt_scalar_one(uint8_t ct[128], const curvePoint& pub, const uin
   g1_marshal(ct + 64, C);
 }
 
+// libunlynxkeyswitch.KeySwitchSequence (github.com/ldsec/unlynx v1.4.0 lib/key_switch/key_switch.go, not under
+// /root/reference; call sites data/data.go:80 and, through protocolsunlynx.KeySwitchingProtocol,
+// services/service.go:565-616), restated as recalled, one element: vi <- random (injected here);
+// rbNeg = -rB; rbkNeg = secretKey * rbNeg; viB = vi * B; viNewK = vi * targetPubKey; ks2 = rbkNeg + viNewK;
+// the contribution is the ciphertext (K, C) = (viB, ks2); rbNeg is returned for the proof.
+static bool keyswitch_one(uint8_t cv[128], uint8_t* rbneg64, const curvePoint& target, const Sc& x, const uint8_t rb64[64],
+                          const uint8_t v32[32]) {
+  curvePoint rB;
+  if (!g1_unmarshal(rB, rb64)) return false;
+  Sc vi;
+  sc_from_bytes(vi, v32);
+  curvePoint rbNeg, rbkNeg, viB, viNewK, ks2;
+  rbNeg.Neg(rB);
+  rbkNeg.Mul(rbNeg, x.v);
+  viB.Mul(curveGen, vi.v);
+  viNewK.Mul(target, vi.v);
+  ks2.Add(rbkNeg, viNewK);
+  g1_marshal(cv, viB);
+  g1_marshal(cv + 64, ks2);
+  if (rbneg64) g1_marshal(rbneg64, rbNeg);
+  return true;
+}
+
 struct DlogTable {  // PointToInt map keyed by the marshalled point, grown lazily like discreteLog
   std::unordered_map<std::string, int64_t> map;
   curvePoint currentGreatestM;
@@ -1435,6 +1458,21 @@ int orc_encrypt_scalar(size_t n, const uint8_t* m, const uint8_t* r, const uint8
   if (!g1_unmarshal(pub, P)) return -2;
   parallel_for(n, threads, [&](size_t i) { encrypt_scalar_one(ct + 128 * i, pub, m + 32 * i, r + 32 * i); });
   return 0;
+}
+
+// KeySwitchSequence over n ciphertexts' K components (rb: n x 64 B) with injected randomness v (n x 32 B)
+int orc_keyswitch(size_t n, const uint8_t* target, const uint8_t* sk32, const uint8_t* rb, const uint8_t* v, uint8_t* cv,
+                  uint8_t* rb_neg, int threads) {
+  ensure_init();
+  curvePoint Q;
+  if (!g1_unmarshal(Q, target)) return -2;
+  Sc x;
+  sc_from_bytes(x, sk32);
+  std::atomic<int> bad(0);
+  parallel_for(n, threads, [&](size_t i) {
+    if (!keyswitch_one(cv + 128 * i, rb_neg ? rb_neg + 64 * i : nullptr, Q, x, rb + 64 * i, v + 32 * i)) bad++;
+  });
+  return bad ? -2 : 0;
 }
 
 // FromBytes + CipherVector.Add folded over ndp providers (protocols/data_collection_protocol.go:145-166);

@@ -82,6 +82,15 @@ class Oracle:
         assert self.lib.orc_encrypt_scalar(ctypes.c_size_t(n), self._p(m), self._p(r), bytes(P), self._p(ct), threads) == 0
         return ct.tobytes()
 
+    def key_switch(self, Q, sk, rbs, vs, threads=1):
+        rb = np.frombuffer(bytes(rbs), np.uint8).copy()
+        v = np.frombuffer(bytes(vs), np.uint8).copy()
+        n = rb.size // 64
+        cv, neg = np.zeros(128 * n, np.uint8), np.zeros(64 * n, np.uint8)
+        rc = self.lib.orc_keyswitch(ctypes.c_size_t(n), bytes(Q), bytes(sk), self._p(rb), self._p(v), self._p(cv),
+                                    self._p(neg), threads)
+        return rc, cv.tobytes(), neg.tobytes()
+
     def aggregate(self, vectors, threads=1):
         v = len(vectors[0]) // 128
         cts = np.frombuffer(b''.join(bytes(x) for x in vectors), np.uint8).copy()

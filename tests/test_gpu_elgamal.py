@@ -130,6 +130,53 @@ def test_encrypt_scalar_matches_oracle_and_definition(backend, oracle, rng):
     assert list(z) == [0, 1, 1, 1, 1, 1]
 
 
+def test_key_switch_matches_oracle_and_decrypts_under_target_key(backend, oracle, rng):
+    """SURVEY 8(f)-3, libunlynxkeyswitch.KeySwitchSequence: bytes identical to the oracle for 300 ciphertexts (with
+    the identity, a repeated point and an unreduced v among them), -rB as well; then the whole protocol on the device
+    entry points: three servers' contributions summed onto (0, C) by drx_aggregate decrypt under the querier's key."""
+    xs = [rng.scalar() for _ in range(3)]
+    coll = None
+    for x in xs:
+        coll = R.g1_add(coll, R.g1_mul(x, R.G1_GEN))
+    P = R.g1_to_bytes(coll)
+    q = rng.scalar()
+    Q = R.g1_to_bytes(R.g1_mul(q, R.G1_GEN))
+    backend.set_pubkey(P)
+    backend.set_target_pubkey(Q)
+    n = 300
+    g = np.random.default_rng(33)
+    ms = [int(v) for v in g.integers(-5000, 5000, size=n)]
+    rs = rng.scalars_bytes(n)
+    cts = backend.encrypt_int_vector(ms, rs).tobytes()
+    rbs = bytearray(b''.join(cts[128 * i:128 * i + 64] for i in range(n)))
+    rbs[64:128] = bytes(64)                 # K = identity
+    rbs[128:192] = rbs[0:64]                # a repeated point
+    rbs = bytes(rbs)
+    contribs = [b''.join(bytes(64) + cts[128 * i + 64:128 * i + 128] for i in range(n))]
+    for k, x in enumerate(xs):
+        vs = bytearray(rng.scalars_bytes(n))
+        vs[0:32] = (R.n + 9).to_bytes(32, 'big')   # reduced mod n like Scalar.SetBytes
+        vs[32:64] = bytes(32)                       # v = 0
+        cv, neg = backend.key_switch(x.to_bytes(32, 'big'), rbs, bytes(vs), want_rb_neg=True)
+        rc, want_cv, want_neg = oracle.key_switch(Q, x.to_bytes(32, 'big'), rbs, bytes(vs), threads=8)
+        assert rc == 0
+        assert cv.tobytes() == want_cv and neg.tobytes() == want_neg
+        if k == 0:
+            one, _ = R.key_switch(R.g1_from_bytes(Q), R.g1_from_bytes(rbs[192:256]), x, int.from_bytes(vs[96:128], 'big'))
+            assert cv.tobytes()[384:512] == one
+        # the protocol uses the true K components
+        true_rbs = b''.join(cts[128 * i:128 * i + 64] for i in range(n))
+        contribs.append(backend.key_switch(x.to_bytes(32, 'big'), true_rbs, bytes(vs)).tobytes())
+    switched = backend.aggregate(contribs)
+    backend.create_decryption_table(10000)
+    assert list(backend.decrypt_int_vector(q.to_bytes(32, 'big'), switched)) == ms
+    # malformed K component -> -2, like a failed UnmarshalBinary
+    bad = bytearray(rbs)
+    bad[200] ^= 1
+    with pytest.raises(RuntimeError):
+        backend.key_switch(xs[0].to_bytes(32, 'big'), bytes(bad), rng.scalars_bytes(n))
+
+
 def test_reduce_rows_host_buffers(backend):
     """drx_reduce_rows against the Go loops' arithmetic (sum.go:19-23, mean.go:19-24, variance.go:19-27), wrap-around
     of int64 included, ragged sizes and an empty provider list."""

@@ -190,3 +190,39 @@ def test_golden_vectors(oracle):
         assert proofs.hex() == v['proof']
         ok = oracle.rp_verify(v['ns'], v['u'], v['l'], bytes.fromhex(v['Y']), bytes.fromhex(v['P']), proofs, off)
         assert list(ok) == [1 if v['valid'] else 0]
+
+
+def test_key_switch_matches_definition_and_decrypts_under_target_key(oracle, rng):
+    """libunlynxkeyswitch.KeySwitchSequence (call sites data/data.go:80, services/service.go:565-616): the C++
+    restatement against the big-integer definition, then the protocol's point: ciphertexts under the collective key
+    of three servers, switched by each server's contribution and summed at the root, decrypt under the querier's key."""
+    xs = [rng.scalar() for _ in range(3)]
+    coll = None
+    for x in xs:
+        coll = R.g1_add(coll, R.g1_mul(x, R.G1_GEN))
+    q = rng.scalar()
+    Q = R.g1_mul(q, R.G1_GEN)
+    ms = [0, 5, -7, 1234]
+    rs = [rng.scalar() for _ in ms]
+    cts = [R.encrypt(coll, m, r) for m, r in zip(ms, rs)]
+    rbs = b''.join(ct[:64] for ct in cts)
+    contribs = [b''.join(b'\0' * 64 + ct[64:] for ct in cts)]     # the root starts from (0, C)
+    for x in xs:
+        vs = [rng.scalar() for _ in ms]
+        vb = b''.join(v.to_bytes(32, 'big') for v in vs)
+        rc, cv, neg = oracle.key_switch(R.g1_to_bytes(Q), x.to_bytes(32, 'big'), rbs, vb, threads=2)
+        assert rc == 0
+        for i, v in enumerate(vs):
+            want_cv, want_neg = R.key_switch(Q, R.g1_from_bytes(rbs[64 * i:64 * i + 64]), x, v)
+            assert cv[128 * i:128 * i + 128] == want_cv and neg[64 * i:64 * i + 64] == want_neg
+        contribs.append(cv)
+    rc, switched = oracle.aggregate(contribs, threads=2)
+    assert rc == 0
+    oracle.dlog_reset()
+    vals, found = oracle.decrypt(q.to_bytes(32, 'big'), switched)
+    assert list(vals) == ms and all(found)
+    # a malformed K component is reported, not switched
+    bad = bytearray(rbs)
+    bad[5] ^= 1
+    rc, _, _ = oracle.key_switch(R.g1_to_bytes(Q), xs[0].to_bytes(32, 'big'), bytes(bad), b'\0' * 31 + b'\1' + vb[32:])
+    assert rc == -2
