@@ -37,6 +37,7 @@ M_CREATE_PROOF = L * (736 + NS * 4458)
 M_AGG_CT = 22
 M_DECRYPT = 2840
 G1_BYTES = bytes(31) + b'\x01' + (65000549695646603732796438742359905742825358107623003571877145026864184071783 - 2).to_bytes(32, 'big')
+M_OBFUSCATE = 2 * 2816 + 16               # two 4-bit-window products, two affine outputs sharing one inversion
 M_KEYSWITCH = 352 + 352 + 2816 + 16 + 16   # v*B and v*Q by comb, x*rB by 4-bit windows, one addition, two affine outputs
 
 
@@ -179,6 +180,19 @@ def run_reference(args):
     rc, _, _ = orc.key_switch(P, d['sk'].to_bytes(32, 'big'), ks_rb, ks_v, threads=cores)
     ks_rate = ks_n / (time.perf_counter() - t1)
     assert rc == 0
+    t1 = time.perf_counter()
+    rc, _ = orc.ct_scalar_mul(ks_v, ks_ct, threads=cores)
+    obf_rate = ks_n / (time.perf_counter() - t1)
+    assert rc == 0
+    sg_x, sg_k = (0x1234567).to_bytes(32, 'big'), (0x777).to_bytes(32, 'big')
+    sg_pub = orc.g1_mul(sg_x, g1)
+    sg_msgs = [b'proof list %d' % i for i in range(1024)]
+    sg_sigs = [orc.schnorr_sign(sg_x, sg_k, sg_pub, m_) for m_ in sg_msgs[:8]] * 128
+    sg_msgs = sg_msgs[:8] * 128
+    t1 = time.perf_counter()
+    sg_ok = orc.schnorr_verify([sg_pub] * 1024, sg_sigs, sg_msgs, threads=cores)
+    sg_rate = 1024 / (time.perf_counter() - t1)
+    assert bool(sg_ok.all())
     sample = '%d of %d DPs x %d rows (%d proofs/step), oracle/oracle.cpp C++ restatement of the Go path' % (ndp, args.ndp, args.rows, n)
     print(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'proofs/s', 'n_gpus': args.gpus, 'steps': args.steps,
@@ -187,7 +201,8 @@ def run_reference(args):
         'config': {'workload': 'config 2: mean+variance, %d DPs x %d rows, u=16 l=4 ns=3 (bounded sample: %d DPs)' % (args.ndp, args.rows, ndp)},
         'cpu_baseline': {'value': val, 'unit': 'proofs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
                          'ed25519_encs_per_s': ed_rate, 'logreg_prepass_records_per_s': lr_rate,
-                         'keyswitch_cts_per_s': ks_rate},
+                         'keyswitch_cts_per_s': ks_rate, 'obfuscations_per_s': obf_rate,
+                         'schnorr_verifies_per_s': sg_rate},
         'e2e': {'value': val, 'unit': 'proofs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }))
@@ -509,6 +524,35 @@ def secondary_rates(be, lib, torch, dev, stream, ck, vp, peak_tmac, skp):
     ms = timed(lambda: ck(lib.drx_keyswitch_dev(be.h, nd, skp, vp(rbk), vp(r), vp(cv), None)))
     out['keyswitch_cts_per_s'] = nd / ms * 1e3
     out['keyswitch_roofline_frac'] = nd * M_KEYSWITCH * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    # obfuscation (MulCipherTextbyScalar) over the same 2^17 ciphertexts
+    obf = torch.empty(nd * 128, dtype=torch.uint8, device=dev)
+    ms = timed(lambda: ck(lib.drx_ct_scalar_mul_dev(be.h, nd, vp(r), vp(ct), vp(obf))))
+    out['obfuscations_per_s'] = nd / ms * 1e3
+    out['obfuscation_roofline_frac'] = nd * M_OBFUSCATE * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    # Schnorr proof-request signatures (host buffers, digests given): 2^14 signatures by one key
+    import hashlib
+    ns_ = 1 << 14
+    sig_x = 0x1234567
+    sig_pub = be.g1_mul(sig_x.to_bytes(32, 'big'), G1_BYTES)
+    sig_R = be.g1_mul((0x777).to_bytes(32, 'big'), G1_BYTES)
+    n_ord = 65000549695646603732796438742359905742570406053903786389881062969044166799969
+    sigs, digs = bytearray(), bytearray()
+    for i in range(64):       # 64 distinct messages, tiled: the kernel does not know
+        dgst = hashlib.sha512(bytes(sig_R) + bytes(sig_pub) + b'proof list %d' % i).digest()
+        sigs += bytes(sig_R) + ((0x777 + sig_x * (int.from_bytes(dgst, 'big') % n_ord)) % n_ord).to_bytes(32, 'big')
+        digs += dgst
+    pubs = np.frombuffer(bytes(sig_pub) * ns_, np.uint8).copy()
+    sg = np.frombuffer(bytes(sigs) * (ns_ // 64), np.uint8).copy()
+    dg = np.frombuffer(bytes(digs) * (ns_ // 64), np.uint8).copy()
+    okb = np.zeros(ns_, np.uint8)
+    cp = lambda a: ctypes.c_void_p(a.ctypes.data)
+    t0 = time.perf_counter()
+    ck(lib.drx_schnorr_verify(be.h, ns_, cp(pubs), cp(sg), cp(dg), cp(okb)))
+    t0 = time.perf_counter()
+    ck(lib.drx_schnorr_verify(be.h, ns_, cp(pubs), cp(sg), cp(dg), cp(okb)))
+    dt = time.perf_counter() - t0
+    assert bool(okb.all())
+    out['schnorr_verifies_per_s_host_buffers'] = ns_ / dt
     # verification sweep point
     npf = 20000
     sid = torch.from_numpy((np.arange(npf, dtype=np.int32) % NOUT)).to(dev)

@@ -49,6 +49,9 @@ SIGNATURES = {
     'drx_dlog_table': (ctypes.c_int, [VP, ctypes.c_int64]),
     'drx_decrypt': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, ctypes.c_int, VP, VP]),
     'drx_decrypt_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
+    'drx_ct_scalar_mul': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
+    'drx_ct_scalar_mul_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
+    'drx_schnorr_verify': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP, VP]),
     'drx_set_target_pubkey': (ctypes.c_int, [VP, VP]),
     'drx_keyswitch': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP, VP, VP]),
     'drx_keyswitch_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP, VP, VP]),

@@ -119,6 +119,27 @@ class Backend:
         _lib.check(self.lib.drx_encrypt_scalar(self.h, m.size // 32, _ptr(m), _ptr(r), _ptr(ct)))
         return ct
 
+    def ct_scalar_mul(self, scalars, cts):
+        """CipherText.MulCipherTextbyScalar per element: scalars n*32 bytes, cts n*128 bytes -> n*128 bytes."""
+        sc, ct = _u8(scalars), _u8(cts)
+        n = ct.size // 128
+        assert ct.size == 128 * n and sc.size == 32 * n
+        out = np.empty(128 * n, dtype=np.uint8)
+        _lib.check(self.lib.drx_ct_scalar_mul(self.h, n, _ptr(sc), _ptr(ct), _ptr(out)))
+        return out
+
+    def schnorr_verify(self, pubs, sigs, msgs):
+        """kyber sign/schnorr Verify over G1 for n (key, signature, message) triples; the SHA-512 of R || P || msg is
+        taken here on the host. Returns n accept bytes."""
+        import hashlib
+        n = len(msgs)
+        pub, sig = _u8(b''.join(bytes(p) for p in pubs)), _u8(b''.join(bytes(s) for s in sigs))
+        assert pub.size == 64 * n and sig.size == 96 * n
+        dig = _u8(b''.join(hashlib.sha512(bytes(sigs[i])[:64] + bytes(pubs[i]) + bytes(msgs[i])).digest() for i in range(n)))
+        ok = np.zeros(n, dtype=np.uint8)
+        _lib.check(self.lib.drx_schnorr_verify(self.h, n, _ptr(pub), _ptr(sig), _ptr(dig), _ptr(ok)))
+        return ok
+
     def set_target_pubkey(self, Q):
         """The querier's public key (64 bytes) for key switching."""
         q = _u8(Q)

@@ -675,6 +675,60 @@ int drx_keyswitch(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* rb,
   return 0;
 }
 
+// ---- obfuscation data path: CipherText.MulCipherTextbyScalar per element (protocols/obfuscation_protocol.go:240-243)
+int drx_ct_scalar_mul_dev(drx_ctx* c, size_t n, const uint8_t* d_s, const uint8_t* d_ct, uint8_t* d_out) {
+  if (!c) return fail(-1, "null context");
+  Guard g(c);
+  timed(c, "k_ct_scalar_mul", [&] { return launch_ct_scalar_mul(c->stream, n, d_s, d_ct, d_out, (int*)c->bad.p); });
+  return check_launch("ct_scalar_mul");
+}
+
+int drx_ct_scalar_mul(drx_ctx* c, size_t n, const uint8_t* s, const uint8_t* ct, uint8_t* out) {
+  if (!c) return fail(-1, "null context");
+  if (n == 0) return 0;
+  if (!s || !ct || !out) return fail(-1, "drx_ct_scalar_mul: null buffer");
+  Guard g(c);
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t os = a.plan(n * 32), oc = a.plan(n * 128), oo = a.plan(n * 128);
+  RET(a.commit());
+  RET(reset_bad(c));
+  CU(cudaMemcpyAsync(a.at<void>(os), s, n * 32, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(a.at<void>(oc), ct, n * 128, cudaMemcpyHostToDevice, c->stream));
+  timed(c, "k_ct_scalar_mul", [&] {
+    return launch_ct_scalar_mul(c->stream, n, a.at<uint8_t>(os), a.at<uint8_t>(oc), a.at<uint8_t>(oo), (int*)c->bad.p);
+  });
+  RET(check_launch("ct_scalar_mul"));
+  CU(cudaMemcpyAsync(out, a.at<void>(oo), n * 128, cudaMemcpyDeviceToHost, c->stream));
+  int bad = 0;
+  RET(read_bad(c, &bad));
+  if (bad) return fail(-2, "drx_ct_scalar_mul: %d malformed points", bad);
+  return 0;
+}
+
+// ---- Schnorr signatures over G1 (lib/proof/structs_proofs.go:498-505): the caller supplies SHA-512(R || P || msg)
+int drx_schnorr_verify(drx_ctx* c, size_t n, const uint8_t* pub, const uint8_t* sig, const uint8_t* digest, uint8_t* ok) {
+  if (!c) return fail(-1, "null context");
+  if (n == 0) return 0;
+  if (!pub || !sig || !digest || !ok) return fail(-1, "drx_schnorr_verify: null buffer");
+  Guard g(c);
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t op = a.plan(n * 64), os = a.plan(n * 96), od = a.plan(n * 64), oo = a.plan(n);
+  RET(a.commit());
+  CU(cudaMemcpyAsync(a.at<void>(op), pub, n * 64, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(a.at<void>(os), sig, n * 96, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(a.at<void>(od), digest, n * 64, cudaMemcpyHostToDevice, c->stream));
+  timed(c, "k_schnorr_verify", [&] {
+    return launch_schnorr_verify(c->stream, n, a.at<uint8_t>(op), a.at<uint8_t>(os), a.at<uint8_t>(od), c->tabB.p,
+                                 a.at<uint8_t>(oo));
+  });
+  RET(check_launch("schnorr_verify"));
+  CU(cudaMemcpyAsync(ok, a.at<void>(oo), n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
 int drx_decrypt_dev(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* d_ct, int64_t* d_out) {
   if (!c || !sk) return fail(-1, "null argument");
   Guard g(c);

@@ -239,6 +239,17 @@ DRX_HD Scalar sc_from_wire(const uint32_t w[8]) {
   for (int k = 0; k < 8; k++) d.v[k] = lt ? t.v[k] : d.v[k];
   return d;
 }
+// 64-byte digest (16 words in memory order) read as a big-endian integer, reduced mod n: kyber Scalar.SetBytes on
+// hash.Sum (lib/range/range_proof.go:374 for SHA3-512; sign/schnorr hash() for SHA-512)
+DRX_HD Scalar sc_from_digest(const uint32_t d[16]) {
+  const Scalar hi = sc_from_wire(d);
+  const Scalar lo = sc_from_wire(d + 8);
+  Scalar r2, t;
+  DRX_UNROLL
+  for (int k = 0; k < 8; k++) r2.v[k] = ModN::r2(k);
+  mont_mul<ModN>(t.v, hi.v, r2.v);  // hi * 2^256 mod n
+  return sc_add(t, lo);
+}
 DRX_HD void sc_to_wire(uint32_t w[8], const Scalar& s) { be_words_from_limbs(w, s.v); }
 DRX_HD uint32_t sc_window(const Scalar& s, int bit, int width) {  // bits [bit, bit+width), width <= 16
   const int limb = bit >> 5, off = bit & 31;

@@ -609,6 +609,62 @@ int launch_keyswitch(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8
   return 1;
 }
 
+// ------------------------------------------------------------------ obfuscation
+// CipherText.MulCipherTextbyScalar per element (protocols/obfuscation_protocol.go:240-243; data/data.go:52-56):
+// out_i = (s_i*K_i, s_i*C_i). Two windowed variable-base products per thread, one shared inversion.
+__global__ void __launch_bounds__(128)
+k_ct_scalar_mul(size_t n, const uint32_t* __restrict__ sc, const uint32_t* __restrict__ ct, uint32_t* __restrict__ out,
+                int* bad) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  G1Aff K, C;
+  int nbad = !g1_from_wire(K, ct + 32 * i);
+  nbad += !g1_from_wire(C, ct + 32 * i + 16);
+  if (nbad) {
+    atomicAdd(bad, nbad);
+    return;
+  }
+  const Scalar k = sc_from_wire(sc + 8 * i);
+  store_pair_wire(out + 32 * i, window_mul(jac_from_aff(K), k), window_mul(jac_from_aff(C), k));
+}
+int launch_ct_scalar_mul(cudaStream_t st, size_t n, const uint8_t* d_s, const uint8_t* d_ct, uint8_t* d_out, int* d_bad) {
+  if (!n) return 0;
+  k_ct_scalar_mul<<<grid_for(n, 128), 128, 0, st>>>(n, (const uint32_t*)d_s, (const uint32_t*)d_ct, (uint32_t*)d_out, d_bad);
+  return 1;
+}
+
+// ------------------------------------------------------------------ Schnorr signatures
+// kyber sign/schnorr Verify over G1, as VerifyProofSignature calls it for every proof request
+// (lib/proof/structs_proofs.go:498-505): sig = R (64 B) || s (32 B); h = SHA-512(R || P || msg) read big-endian and
+// reduced mod n (the caller hashes: the message is the proof list it already holds in host memory); accept when
+// s*B == R + h*P. A malformed R or P, or s >= n (mod.Int.UnmarshalBinary rejects it), fails the signature, it is
+// not an error of the call.
+__global__ void __launch_bounds__(128)
+k_schnorr_verify(size_t n, const uint32_t* __restrict__ pub, const uint32_t* __restrict__ sig,
+                 const uint32_t* __restrict__ digest, const G1Aff* __restrict__ tabB, uint8_t* __restrict__ ok) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  G1Aff P, R;
+  Scalar s;
+  limbs_from_be_words(s.v, sig + 24 * i + 16);
+  if (!g1_from_wire(P, pub + 16 * i) || !g1_from_wire(R, sig + 24 * i) || mod_geq<ModN>(s.v)) {
+    ok[i] = 0;
+    return;
+  }
+  const Scalar h = sc_from_digest(digest + 16 * i);
+  // s*B - h*P - R must be the identity
+  G1Jac T = jac_add(comb_mul(tabB, s), jac_neg(window_mul(jac_from_aff(P), h)));
+  T = jac_add_aff(T, aff_neg(R));
+  ok[i] = jac_is_inf(T) ? 1 : 0;
+}
+int launch_schnorr_verify(cudaStream_t st, size_t n, const uint8_t* d_pub, const uint8_t* d_sig, const uint8_t* d_digest,
+                          const void* d_tabB, uint8_t* d_ok) {
+  if (!n) return 0;
+  k_schnorr_verify<<<grid_for(n, 128), 128, 0, st>>>(n, (const uint32_t*)d_pub, (const uint32_t*)d_sig,
+                                                    (const uint32_t*)d_digest, (const G1Aff*)d_tabB, d_ok);
+  return 1;
+}
+
 // ------------------------------------------------------------------ diagnostics
 __global__ void k_g1_mul(size_t n, const uint32_t* __restrict__ k, const uint32_t* __restrict__ pt,
                          uint32_t* __restrict__ out, int* bad) {

@@ -53,6 +53,11 @@ int launch_decrypt(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t
 // key switching: cv[i] = (v_i*B) || (v_i*Q - sk*rb_i), rb_neg[i] = -rb_i (optional)
 int launch_keyswitch(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t* d_rb, const uint8_t* d_v,
                      const void* d_tabB, const void* d_tabQ, uint8_t* d_cv, uint8_t* d_rb_neg, int* d_bad);
+// MulCipherTextbyScalar per element: out_i = (s_i*K_i, s_i*C_i)
+int launch_ct_scalar_mul(cudaStream_t st, size_t n, const uint8_t* d_s, const uint8_t* d_ct, uint8_t* d_out, int* d_bad);
+// Schnorr over G1: ok_i = (s_i*B == R_i + h_i*P_i), sig = R || s (96 B), digest = SHA-512(R || P || msg) (64 B)
+int launch_schnorr_verify(cudaStream_t st, size_t n, const uint8_t* d_pub, const uint8_t* d_sig, const uint8_t* d_digest,
+                          const void* d_tabB, uint8_t* d_ok);
 int launch_g1_mul(cudaStream_t st, size_t n, const uint8_t* d_k, const uint8_t* d_pt, uint8_t* d_out, int* d_bad);
 int launch_mont_mul(cudaStream_t st, size_t n, int which, const uint32_t* d_a, const uint32_t* d_b, uint32_t* d_r);
 int launch_microbench(cudaStream_t st, int kind, int iters, int blocks, int threads, uint32_t* d_sink);

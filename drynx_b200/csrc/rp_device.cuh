@@ -15,17 +15,6 @@ __device__ __noinline__ static Scalar sc_inv(const Scalar& a) {  // a^-1 mod n (
   return out;
 }
 
-// 64-byte SHA3-512 digest (as 16 words in memory order) read as a big-endian integer, reduced mod n
-// (kyber Scalar.SetBytes on hash.Sum, lib/range/range_proof.go:374)
-__device__ __forceinline__ Scalar sc_from_digest(const uint32_t d[16]) {
-  const Scalar hi = sc_from_wire(d);
-  const Scalar lo = sc_from_wire(d + 8);
-  Scalar r2, t;
-  for (int k = 0; k < 8; k++) r2.v[k] = ModN::r2(k);
-  mont_mul<ModN>(t.v, hi.v, r2.v);  // hi * 2^256 mod n
-  return sc_add(t, lo);
-}
-
 // c = SHA3-512(B || C || sum Y) mod n (lib/range/range_proof.go:349-374); C is the second half of the ciphertext.
 __device__ __forceinline__ Scalar rp_challenge(const uint32_t* __restrict__ baseB_wire, const uint32_t* __restrict__ ct,
                                               const uint8_t* __restrict__ sumY) {

@@ -14,6 +14,7 @@
 // No arithmetic on group elements happens here: every such operation is one batched call into libdrynx_gpu.so.
 // The randomness a Go node would draw from crypto/rand comes from a caller-supplied RandomStream.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -153,6 +154,15 @@ inline CipherVector EncryptScalarVector(const Point& pubkey, const std::vector<S
 }
 inline CipherText EncryptScalar(const Point& pubkey, const Scalar& m) { return EncryptScalarVector(pubkey, {m})[0]; }
 
+// CipherText.MulCipherTextbyScalar per element (protocols/obfuscation_protocol.go:240-243): (s_i*K_i, s_i*C_i)
+inline CipherVector MulCipherVectorByScalars(const CipherVector& cv, const std::vector<Scalar>& ss) {
+  if (cv.size() != ss.size()) throw drynx::Error(-1, "MulCipherTextbyScalar: length mismatch");
+  CipherVector out(cv.size());
+  if (!cv.empty()) drynx::check(drx_ct_scalar_mul(Gpu::get().ctx(), cv.size(), ss[0].b, cv[0].b, out[0].b));
+  return out;
+}
+inline CipherText MulCipherTextbyScalar(const CipherText& c, const Scalar& s) { return MulCipherVectorByScalars({c}, {s})[0]; }
+
 // CipherVector.Add over any number of vectors (the root node's fold, protocols/data_collection_protocol.go:145-166).
 inline CipherVector AddAll(const std::vector<CipherVector>& vs) {
   if (vs.empty()) return {};
@@ -194,6 +204,147 @@ inline void CreateDecryptionTable(int64_t limit, const Point&, const Scalar&) {
 }
 
 }  // namespace libunlynx
+
+// =====================================================================================================================
+// The verifying nodes' remaining per-list work that is pure group arithmetic: the Schnorr signature
+// on every proof request, and the aggregation proof, which is a recomputation.
+namespace drynxproof {
+using drynx::Gpu;
+using drynx::Point;
+
+// SHA-512 (FIPS 180-4) for the Schnorr challenge; the message is the serialised proof list, already in host memory.
+inline void sha512(const uint8_t* msg0, size_t len0, const uint8_t* msg1, size_t len1, const uint8_t* msg2, size_t len2,
+                   uint8_t out[64]) {
+  static const uint64_t K[80] = {
+      0x428a2f98d728ae22ull, 0x7137449123ef65cdull, 0xb5c0fbcfec4d3b2full, 0xe9b5dba58189dbbcull, 0x3956c25bf348b538ull,
+      0x59f111f1b605d019ull, 0x923f82a4af194f9bull, 0xab1c5ed5da6d8118ull, 0xd807aa98a3030242ull, 0x12835b0145706fbeull,
+      0x243185be4ee4b28cull, 0x550c7dc3d5ffb4e2ull, 0x72be5d74f27b896full, 0x80deb1fe3b1696b1ull, 0x9bdc06a725c71235ull,
+      0xc19bf174cf692694ull, 0xe49b69c19ef14ad2ull, 0xefbe4786384f25e3ull, 0x0fc19dc68b8cd5b5ull, 0x240ca1cc77ac9c65ull,
+      0x2de92c6f592b0275ull, 0x4a7484aa6ea6e483ull, 0x5cb0a9dcbd41fbd4ull, 0x76f988da831153b5ull, 0x983e5152ee66dfabull,
+      0xa831c66d2db43210ull, 0xb00327c898fb213full, 0xbf597fc7beef0ee4ull, 0xc6e00bf33da88fc2ull, 0xd5a79147930aa725ull,
+      0x06ca6351e003826full, 0x142929670a0e6e70ull, 0x27b70a8546d22ffcull, 0x2e1b21385c26c926ull, 0x4d2c6dfc5ac42aedull,
+      0x53380d139d95b3dfull, 0x650a73548baf63deull, 0x766a0abb3c77b2a8ull, 0x81c2c92e47edaee6ull, 0x92722c851482353bull,
+      0xa2bfe8a14cf10364ull, 0xa81a664bbc423001ull, 0xc24b8b70d0f89791ull, 0xc76c51a30654be30ull, 0xd192e819d6ef5218ull,
+      0xd69906245565a910ull, 0xf40e35855771202aull, 0x106aa07032bbd1b8ull, 0x19a4c116b8d2d0c8ull, 0x1e376c085141ab53ull,
+      0x2748774cdf8eeb99ull, 0x34b0bcb5e19b48a8ull, 0x391c0cb3c5c95a63ull, 0x4ed8aa4ae3418acbull, 0x5b9cca4f7763e373ull,
+      0x682e6ff3d6b2b8a3ull, 0x748f82ee5defb2fcull, 0x78a5636f43172f60ull, 0x84c87814a1f0ab72ull, 0x8cc702081a6439ecull,
+      0x90befffa23631e28ull, 0xa4506cebde82bde9ull, 0xbef9a3f7b2c67915ull, 0xc67178f2e372532bull, 0xca273eceea26619cull,
+      0xd186b8c721c0c207ull, 0xeada7dd6cde0eb1eull, 0xf57d4f7fee6ed178ull, 0x06f067aa72176fbaull, 0x0a637dc5a2c898a6ull,
+      0x113f9804bef90daeull, 0x1b710b35131c471bull, 0x28db77f523047d84ull, 0x32caab7b40c72493ull, 0x3c9ebe0a15c9bebcull,
+      0x431d67c49c100d4cull, 0x4cc5d4becb3e42b6ull, 0x597f299cfc657e2aull, 0x5fcb6fab3ad6faecull, 0x6c44198c4a475817ull};
+  uint64_t h[8] = {0x6a09e667f3bcc908ull, 0xbb67ae8584caa73bull, 0x3c6ef372fe94f82bull, 0xa54ff53a5f1d36f1ull,
+                   0x510e527fade682d1ull, 0x9b05688c2b3e6c1full, 0x1f83d9abfb41bd6bull, 0x5be0cd19137e2179ull};
+  auto rotr = [](uint64_t x, int n) { return (x >> n) | (x << (64 - n)); };
+  auto block = [&](const uint8_t* b) {
+    uint64_t w[80];
+    for (int i = 0; i < 16; i++) {
+      w[i] = 0;
+      for (int k = 0; k < 8; k++) w[i] = (w[i] << 8) | b[8 * i + k];
+    }
+    for (int i = 16; i < 80; i++) {
+      const uint64_t s0 = rotr(w[i - 15], 1) ^ rotr(w[i - 15], 8) ^ (w[i - 15] >> 7);
+      const uint64_t s1 = rotr(w[i - 2], 19) ^ rotr(w[i - 2], 61) ^ (w[i - 2] >> 6);
+      w[i] = w[i - 16] + s0 + w[i - 7] + s1;
+    }
+    uint64_t a = h[0], bb = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
+    for (int i = 0; i < 80; i++) {
+      const uint64_t S1 = rotr(e, 14) ^ rotr(e, 18) ^ rotr(e, 41), ch = (e & f) ^ (~e & g);
+      const uint64_t t1 = hh + S1 + ch + K[i] + w[i];
+      const uint64_t S0 = rotr(a, 28) ^ rotr(a, 34) ^ rotr(a, 39), mj = (a & bb) ^ (a & c) ^ (bb & c);
+      hh = g; g = f; f = e; e = d + t1; d = c; c = bb; bb = a; a = t1 + S0 + mj;
+    }
+    h[0] += a; h[1] += bb; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
+  };
+  uint8_t buf[128];
+  size_t fill = 0, total = 0;
+  auto feed = [&](const uint8_t* p, size_t n) {
+    total += n;
+    while (n) {
+      const size_t take = std::min(n, (size_t)128 - fill);
+      memcpy(buf + fill, p, take);
+      fill += take; p += take; n -= take;
+      if (fill == 128) { block(buf); fill = 0; }
+    }
+  };
+  feed(msg0, len0);
+  feed(msg1, len1);
+  feed(msg2, len2);
+  const uint64_t bits = (uint64_t)total * 8;
+  uint8_t pad[256] = {0x80};
+  const size_t padlen = (fill < 112 ? 112 : 240) - fill;
+  uint8_t lenb[16] = {0};
+  for (int k = 0; k < 8; k++) lenb[15 - k] = (uint8_t)(bits >> (8 * k));
+  feed(pad, padlen);
+  feed(lenb, 16);
+  for (int i = 0; i < 8; i++)
+    for (int k = 0; k < 8; k++) out[8 * i + k] = (uint8_t)(h[i] >> (56 - 8 * k));
+}
+
+struct SignedData {  // one proof request's (sender key, serialised proofs, R || s)
+  Point pubKey;
+  const uint8_t* data;
+  size_t len;
+  uint8_t signature[96];
+};
+// VerifyProofSignature (lib/proof/structs_proofs.go:498-505) for a batch of proof requests: host SHA-512 per request,
+// one device call for the group equations. true = signature correct.
+inline std::vector<bool> VerifyProofSignatures(const std::vector<SignedData>& reqs) {
+  const size_t n = reqs.size();
+  std::vector<uint8_t> pub(64 * n), sig(96 * n), dig(64 * n), ok(n);
+  for (size_t i = 0; i < n; i++) {
+    memcpy(&pub[64 * i], reqs[i].pubKey.b, 64);
+    memcpy(&sig[96 * i], reqs[i].signature, 96);
+    sha512(reqs[i].signature, 64, reqs[i].pubKey.b, 64, reqs[i].data, reqs[i].len, &dig[64 * i]);
+  }
+  if (n) drynx::check(drx_schnorr_verify(Gpu::get().ctx(), n, pub.data(), sig.data(), dig.data(), ok.data()));
+  std::vector<bool> out(n);
+  for (size_t i = 0; i < n; i++) out[i] = ok[i] != 0;
+  return out;
+}
+inline bool VerifyProofSignature(const Point& pubKey, const uint8_t* data, size_t len, const uint8_t signature[96]) {
+  SignedData r;
+  r.pubKey = pubKey;
+  r.data = data;
+  r.len = len;
+  memcpy(r.signature, signature, 96);
+  return VerifyProofSignatures({r})[0];
+}
+
+}  // namespace drynxproof
+
+namespace libunlynxaggr {
+// PublishedAggregationProof (unlynx lib/aggregation, used at data/data.go:41-47 and services/service.go:533-541):
+// the data and the claimed sum; verification recomputes Data.Acum() and compares.
+struct PublishedAggregationProof {
+  libunlynx::CipherVector Data;
+  libunlynx::CipherText AggregationResult;
+};
+struct PublishedAggregationListProof {
+  std::vector<PublishedAggregationProof> List;
+};
+inline PublishedAggregationListProof AggregationListProofCreation(const std::vector<libunlynx::CipherVector>& data,
+                                                                  const libunlynx::CipherVector& results) {
+  PublishedAggregationListProof l;
+  for (size_t i = 0; i < data.size(); i++) l.List.push_back({data[i], results[i]});
+  return l;
+}
+// AggregationListProofVerification(palp, percent): the first ceil(percent * len) proofs, all sums in one device call
+// when the vectors have one length (the usual case), else one call per proof.
+inline bool AggregationListProofVerification(const PublishedAggregationListProof& l, double percent) {
+  const size_t nb = (size_t)std::ceil(percent * (double)l.List.size());
+  bool ok = true;
+  for (size_t i = 0; i < nb && i < l.List.size(); i++) {
+    const auto& p = l.List[i];
+    std::vector<libunlynx::CipherVector> cols;
+    for (auto& c : p.Data) cols.push_back({c});
+    libunlynx::CipherText sum;
+    memset(sum.b, 0, 128);
+    if (!cols.empty()) sum = libunlynx::AddAll(cols)[0];
+    ok = ok && !memcmp(sum.b, p.AggregationResult.b, 128);
+  }
+  return ok;
+}
+}  // namespace libunlynxaggr
 
 // =====================================================================================================================
 namespace libunlynxkeyswitch {

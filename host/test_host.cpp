@@ -347,11 +347,64 @@ static void TestKeySwitching() {
   EXPECT(libunlynx::DecryptIntVectorWithNeg(querier.Private, cv) != values);
 }
 
+static std::string hex(const uint8_t* b, size_t n) {
+  static const char* d = "0123456789abcdef";
+  std::string s;
+  for (size_t i = 0; i < n; i++) { s += d[b[i] >> 4]; s += d[b[i] & 15]; }
+  return s;
+}
+static void TestSha512() {  // FIPS 180-4 "abc" vector and a two-block message, split across the three inputs
+  uint8_t out[64];
+  drynxproof::sha512((const uint8_t*)"a", 1, (const uint8_t*)"b", 1, (const uint8_t*)"c", 1, out);
+  EXPECT(hex(out, 64) == "ddaf35a193617abacc417349ae20413112e6fa4e89a97ea20a9eeee64b55d39a2192992a274fc1a836ba3c23a3feebbd454d4423643ce80e2a9ac94fa54ca49f");
+  std::string a(200, 'a');
+  drynxproof::sha512((const uint8_t*)a.data(), 64, (const uint8_t*)a.data() + 64, 64, (const uint8_t*)a.data() + 128, 72, out);
+  EXPECT(hex(out, 64) == "4b11459c33f52a22ee8236782714c150a3b2c60994e9acee17fe68947a3e6789f31e7668394592da7bef827cddca88c4e6f86e4df7ed1ae6cba71f3e98faee9f");
+}
+// VerifyProofSignature (lib/proof/structs_proofs.go:498-505) on a signature made by the big-integer definition
+// (oracle/bn256_ref.py schnorr_sign, x = 12, nonce 34), then on tampered copies; and the aggregation proof
+// (data/data.go:41-47: Data = the vector, AggregationResult = its Acum()).
+static void TestProofSignatureAndAggregationProof() {
+  static const uint8_t pub[64] = {0x24, 0x0c, 0x76, 0x0d, 0x59, 0xa5, 0xe7, 0x9d, 0x0d, 0xd4, 0xde, 0xb2, 0x00, 0x02, 0xeb, 0x9d, 0xe3, 0x9d, 0xfe, 0x7f, 0xcc, 0xaa, 0xd7, 0xc7, 0x1c, 0x4b, 0xcc, 0x0b, 0x42, 0xa2, 0x5a, 0x6c, 0x86, 0xad, 0x33, 0x99, 0x8d, 0x8f, 0x86, 0x27, 0x3b, 0xbe, 0xd0, 0x70, 0x6f, 0xb1, 0xb5, 0xe3, 0x13, 0x55, 0x9d, 0x3f, 0xbc, 0x54, 0xf7, 0xf4, 0x41, 0xea, 0x54, 0xf6, 0x56, 0x89, 0xe1, 0x8b};
+  static const uint8_t sig[96] = {0x75, 0xe3, 0xc7, 0x4b, 0x76, 0xa3, 0x4d, 0x8f, 0xa0, 0x1e, 0xc5, 0x25, 0x37, 0x09, 0x81, 0x8b, 0x5e, 0x08, 0xce, 0xc1, 0x14, 0x42, 0xdd, 0x08, 0x24, 0xb5, 0xf1, 0xb2, 0xfb, 0x40, 0x32, 0xbd, 0x6e, 0x3a, 0x60, 0x98, 0x4d, 0x16, 0xf9, 0xd0, 0xf2, 0x6c, 0x88, 0x09, 0xa5, 0x42, 0xc7, 0x7d, 0xcd, 0x44, 0x10, 0xde, 0x9a, 0xa0, 0xda, 0x90, 0x5b, 0x83, 0xba, 0x78, 0x5a, 0x94, 0x02, 0x53, 0x1a, 0xdc, 0xbd, 0xa0, 0x82, 0xdb, 0x73, 0x26, 0x7e, 0x62, 0x76, 0x9b, 0x2f, 0x5c, 0xbe, 0x33, 0x81, 0x58, 0xb5, 0xe9, 0x46, 0x84, 0x86, 0xf5, 0x3e, 0x9c, 0x91, 0xad, 0x15, 0x10, 0xb2, 0xb9};
+  const char* msg = "drynx proof request";
+  drynx::Point P;
+  memcpy(P.b, pub, 64);
+  EXPECT(memcmp(drynx::point_mul(drynx::scalar_from_u64(12), drynx::base_point()).b, pub, 64) == 0);
+  EXPECT(drynxproof::VerifyProofSignature(P, (const uint8_t*)msg, strlen(msg), sig));
+  EXPECT(!drynxproof::VerifyProofSignature(P, (const uint8_t*)msg, strlen(msg) - 1, sig));
+  uint8_t bad[96];
+  memcpy(bad, sig, 96);
+  bad[95] ^= 1;
+  EXPECT(!drynxproof::VerifyProofSignature(P, (const uint8_t*)msg, strlen(msg), bad));
+  memcpy(bad, sig, 96);
+  memset(bad + 64, 0xff, 32);  // s >= n
+  EXPECT(!drynxproof::VerifyProofSignature(P, (const uint8_t*)msg, strlen(msg), bad));
+  // aggregation proof
+  auto keys = drynx::NewKeyPair();
+  auto ev = libunlynx::EncryptIntVector(keys.Public, {1, 2, 3, 4, 5});
+  std::vector<libunlynx::CipherVector> cols;
+  for (auto& c : ev) cols.push_back({c});
+  auto acum = libunlynx::AddAll(cols)[0];
+  auto list = libunlynxaggr::AggregationListProofCreation({ev, ev}, {acum, acum});
+  EXPECT(libunlynxaggr::AggregationListProofVerification(list, 1.0));
+  list.List[1].AggregationResult.b[100] ^= 1;
+  EXPECT(!libunlynxaggr::AggregationListProofVerification(list, 1.0));
+  EXPECT(libunlynxaggr::AggregationListProofVerification(list, 0.5));  // only the first proof is looked at
+  // obfuscation: an encrypted zero stays zero, a one stays non-zero (OR_AND.go decoding)
+  libunlynx::CreateDecryptionTable(10000, keys.Public, keys.Private);
+  auto bits = libunlynx::EncryptIntVector(keys.Public, {0, 1});
+  auto obf = libunlynx::MulCipherVectorByScalars(bits, {drynx::pick(), drynx::pick()});
+  EXPECT(libunlynx::DecryptCheckZeroVector(keys.Private, obf) == std::vector<int64_t>({0, 1}));
+  EXPECT(memcmp(obf[1].b, bits[1].b, 128) != 0);
+}
+
 int main(int argc, char** argv) {
   const bool cpu_only = argc > 1 && !strcmp(argv[1], "--cpu");
   TestComputeApproxCoefficients();
   TestCartesianProduct();
   TestShapesAndToBase();
+  TestSha512();
   if (!cpu_only) {
     try {
       drynx::Gpu::get().random = random_scalar;
@@ -368,6 +421,7 @@ int main(int argc, char** argv) {
       TestEncodeDecodeCosimAndModelEvaluation();
       TestEncodeDecodeDispatcher();
       TestKeySwitching();
+      TestProofSignatureAndAggregationProof();
     } catch (const drynx::Error& e) {
       printf("FAIL: exception %d: %s\n", e.code, e.what());
       failures++;

@@ -155,6 +155,20 @@ int drx_keyswitch(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t* r
 int drx_keyswitch_dev(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_t* d_rb, const uint8_t* d_v, uint8_t* d_cv,
                       uint8_t* d_rb_neg);
 
+/* Obfuscation data path: CipherText.MulCipherTextbyScalar per element
+ * (protocols/obfuscation_protocol.go:240-243, data/data.go:52-56): out[i] = (s_i*K_i) || (s_i*C_i), s 32 bytes
+ * big-endian reduced mod n. Returns -2 on a malformed point. */
+int drx_ct_scalar_mul(drx_ctx* ctx, size_t n, const uint8_t* s /*n*32*/, const uint8_t* ct /*n*128*/, uint8_t* out /*n*128*/);
+int drx_ct_scalar_mul_dev(drx_ctx* ctx, size_t n, const uint8_t* d_s, const uint8_t* d_ct, uint8_t* d_out);
+
+/* Schnorr signature check over G1, batched: kyber sign/schnorr Verify as
+ * VerifyProofSignature calls it for every proof request (lib/proof/structs_proofs.go:498-505).
+ * pub: n*64 signer keys; sig: n*96, R (64) || s (32); digest: n*64, SHA-512(R || P || msg) computed by the caller
+ * (the message is the proof list the caller already holds). ok[i] = 1 when s*B == R + h*P with h the digest read
+ * big-endian mod n. A malformed R or P, or s >= n, gives ok[i] = 0 (the reference returns an error for that
+ * signature), never an error of the call. */
+int drx_schnorr_verify(drx_ctx* ctx, size_t n, const uint8_t* pub, const uint8_t* sig, const uint8_t* digest, uint8_t* ok /*n*/);
+
 /* Server signatures for one output column: Y_i and A_{i,k} = (x_i + k)^-1 * g2, k < u
  * (lib/range/range_proof.go:249-302 InitRangeProofSignature, PublishSignatureBytesToPublishSignatures;
  * libdrynx.PublishSignatureBytes lib/structs.go:131-141). Builds the per-set tables; set_id is the caller's

@@ -300,6 +300,38 @@ def decrypt_point(sk, ct):
     return g1_add(C, g1_neg(g1_mul(sk, K)))
 
 
+def ct_scalar_mul(ct, s):
+    """CipherText.MulCipherTextbyScalar (protocols/obfuscation_protocol.go:240-243): (s*K, s*C)."""
+    K, C = g1_from_bytes(ct[:64]), g1_from_bytes(ct[64:128])
+    return g1_to_bytes(g1_mul(s % n, K)) + g1_to_bytes(g1_mul(s % n, C))
+
+
+def schnorr_sign(x, k, msg):
+    """kyber sign/schnorr Sign over G1 with the nonce k injected (recalled): R = k*B, h = SHA-512(R || X || msg) mod n
+    (big-endian), s = k + x*h, signature R || s."""
+    import hashlib
+    X = g1_mul(x, G1_GEN)
+    Rb = g1_to_bytes(g1_mul(k, G1_GEN))
+    h = int.from_bytes(hashlib.sha512(Rb + g1_to_bytes(X) + msg).digest(), 'big') % n
+    return Rb + ((k + x * h) % n).to_bytes(32, 'big')
+
+
+def schnorr_verify(X, msg, sig):
+    """kyber sign/schnorr Verify (lib/proof/structs_proofs.go:498-505): s*B == R + h*X; s >= n or a bad R rejects."""
+    import hashlib
+    if len(sig) != 96:
+        return False
+    try:
+        R = g1_from_bytes(sig[:64])
+    except Exception:
+        return False
+    s = int.from_bytes(sig[64:], 'big')
+    if s >= n:
+        return False
+    h = int.from_bytes(hashlib.sha512(sig[:64] + g1_to_bytes(X) + msg).digest(), 'big') % n
+    return g1_mul(s, G1_GEN) == g1_add(R, g1_mul(h, X))
+
+
 def key_switch(target_pub, rb, sk, v):
     """libunlynxkeyswitch.KeySwitchSequence for one element (unlynx v1.4.0 lib/key_switch/key_switch.go, recalled;
     call sites data/data.go:80, services/service.go:565-616): contribution (v*B, v*Q - sk*rB) and -rB."""

@@ -1205,6 +1205,44 @@ static bool keyswitch_one(uint8_t cv[128], uint8_t* rbneg64, const curvePoint& t
   return true;
 }
 
+// CipherText.MulCipherTextbyScalar (unlynx lib/crypto.go, recalled: K = s*K, C = s*C; in-tree call sites
+// protocols/obfuscation_protocol.go:240-243, data/data.go:52-56)
+static bool ct_scalar_mul_one(uint8_t out[128], const uint8_t ct[128], const uint8_t s32[32]) {
+  curvePoint K, C, sK, sC;
+  if (!g1_unmarshal(K, ct) || !g1_unmarshal(C, ct + 64)) return false;
+  Sc s;
+  sc_from_bytes(s, s32);
+  sK.Mul(K, s.v);
+  sC.Mul(C, s.v);
+  g1_marshal(out, sK);
+  g1_marshal(out + 64, sC);
+  return true;
+}
+
+// kyber v3.0.8 sign/schnorr (not under /root/reference; called by VerifyProofSignature,
+// lib/proof/structs_proofs.go:498-505, and by the New*ProofRequest constructors :117 etc.), restated as recalled:
+//   Sign(s, x, msg):   k <- random; R = k*B; h = SHA-512(R || X || msg) as a scalar (SetBytes: big-endian mod n);
+//                      s = k + x*h; signature = R || s
+//   Verify(g, X, msg, sig): len(sig) == 64 + 32; R, s unmarshal (a point off the curve or s >= n is an error);
+//                      h as above; accept iff s*B == R + h*X
+// The digest is an input here: the caller hashes (tests use hashlib, the host mirror its own SHA-512).
+static bool schnorr_verify_one(const uint8_t pub[64], const uint8_t sig[96], const uint8_t digest[64]) {
+  curvePoint X, R, S, Ah, RAs;
+  if (!g1_unmarshal(X, pub) || !g1_unmarshal(R, sig)) return false;
+  gfP sraw;
+  gfpUnmarshal(sraw, sig + 64);
+  if (geq(sraw.v, MN.m)) return false;  // mod.Int.UnmarshalBinary: value out of range
+  Sc sc;
+  memcpy(sc.v, sraw.v, 32);
+  const Sc h = sc_from_wide(digest);
+  S.Mul(curveGen, sc.v);
+  Ah.Mul(X, h.v);
+  RAs.Add(R, Ah);
+  uint8_t a[64], b[64];
+  g1_marshal(a, S);
+  g1_marshal(b, RAs);
+  return memcmp(a, b, 64) == 0;
+}
 struct DlogTable {  // PointToInt map keyed by the marshalled point, grown lazily like discreteLog
   std::unordered_map<std::string, int64_t> map;
   curvePoint currentGreatestM;
@@ -1457,6 +1495,40 @@ int orc_encrypt_scalar(size_t n, const uint8_t* m, const uint8_t* r, const uint8
   curvePoint pub;
   if (!g1_unmarshal(pub, P)) return -2;
   parallel_for(n, threads, [&](size_t i) { encrypt_scalar_one(ct + 128 * i, pub, m + 32 * i, r + 32 * i); });
+  return 0;
+}
+
+int orc_ct_scalar_mul(size_t n, const uint8_t* s, const uint8_t* ct, uint8_t* out, int threads) {
+  ensure_init();
+  std::atomic<int> bad(0);
+  parallel_for(n, threads, [&](size_t i) {
+    if (!ct_scalar_mul_one(out + 128 * i, ct + 128 * i, s + 32 * i)) bad++;
+  });
+  return bad ? -2 : 0;
+}
+
+int orc_schnorr_verify(size_t n, const uint8_t* pub, const uint8_t* sig, const uint8_t* digest, uint8_t* ok, int threads) {
+  ensure_init();
+  parallel_for(n, threads, [&](size_t i) { ok[i] = schnorr_verify_one(pub + 64 * i, sig + 96 * i, digest + 64 * i) ? 1 : 0; });
+  return 0;
+}
+// first half of Sign: R = k*B (the caller hashes R || X || msg and calls orc_schnorr_finish)
+int orc_schnorr_commit(const uint8_t* k32, uint8_t* R64) {
+  ensure_init();
+  Sc k;
+  sc_from_bytes(k, k32);
+  curvePoint R;
+  R.Mul(curveGen, k.v);
+  g1_marshal(R64, R);
+  return 0;
+}
+// second half of Sign: s = k + x*h
+int orc_schnorr_finish(const uint8_t* x32, const uint8_t* k32, const uint8_t* digest64, uint8_t* s32) {
+  ensure_init();
+  Sc x, k;
+  sc_from_bytes(x, x32);
+  sc_from_bytes(k, k32);
+  sc_to_bytes(s32, sc_add(k, sc_mul(x, sc_from_wide(digest64))));
   return 0;
 }
 

@@ -82,6 +82,34 @@ class Oracle:
         assert self.lib.orc_encrypt_scalar(ctypes.c_size_t(n), self._p(m), self._p(r), bytes(P), self._p(ct), threads) == 0
         return ct.tobytes()
 
+    def ct_scalar_mul(self, scalars, cts, threads=1):
+        sc = np.frombuffer(bytes(scalars), np.uint8).copy()
+        ct = np.frombuffer(bytes(cts), np.uint8).copy()
+        n = ct.size // 128
+        out = np.zeros(128 * n, np.uint8)
+        rc = self.lib.orc_ct_scalar_mul(ctypes.c_size_t(n), self._p(sc), self._p(ct), self._p(out), threads)
+        return rc, out.tobytes()
+
+    def schnorr_sign(self, x, k, pub, msg):
+        """Sign with the nonce injected: the group and scalar steps in the C++ oracle, SHA-512 here."""
+        import hashlib
+        R, s = np.zeros(64, np.uint8), np.zeros(32, np.uint8)
+        assert self.lib.orc_schnorr_commit(bytes(k), self._p(R)) == 0
+        dig = hashlib.sha512(R.tobytes() + bytes(pub) + bytes(msg)).digest()
+        assert self.lib.orc_schnorr_finish(bytes(x), bytes(k), dig, self._p(s)) == 0
+        return R.tobytes() + s.tobytes()
+
+    def schnorr_verify(self, pubs, sigs, msgs, threads=1):
+        import hashlib
+        n = len(msgs)
+        pub = np.frombuffer(b''.join(bytes(p) for p in pubs), np.uint8).copy()
+        sig = np.frombuffer(b''.join(bytes(s) for s in sigs), np.uint8).copy()
+        dig = np.frombuffer(b''.join(hashlib.sha512(bytes(sigs[i])[:64] + bytes(pubs[i]) + bytes(msgs[i])).digest()
+                                     for i in range(n)), np.uint8).copy()
+        ok = np.zeros(n, np.uint8)
+        assert self.lib.orc_schnorr_verify(ctypes.c_size_t(n), self._p(pub), self._p(sig), self._p(dig), self._p(ok), threads) == 0
+        return ok
+
     def key_switch(self, Q, sk, rbs, vs, threads=1):
         rb = np.frombuffer(bytes(rbs), np.uint8).copy()
         v = np.frombuffer(bytes(vs), np.uint8).copy()

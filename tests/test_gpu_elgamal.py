@@ -177,6 +177,62 @@ def test_key_switch_matches_oracle_and_decrypts_under_target_key(backend, oracle
         backend.key_switch(xs[0].to_bytes(32, 'big'), bytes(bad), rng.scalars_bytes(n))
 
 
+def test_obfuscation_scalar_mul_matches_oracle(backend, oracle, rng):
+    """CipherText.MulCipherTextbyScalar (protocols/obfuscation_protocol.go:240-243) on 200 ciphertexts, with the
+    scalars 0, 1, n-1 and an unreduced one and an identity component among them; DecryptCheckZero keeps its meaning."""
+    sk, P = _keys(rng)
+    backend.set_pubkey(P)
+    n = 200
+    ms = [0 if i % 3 == 0 else i for i in range(n)]
+    cts = bytearray(backend.encrypt_int_vector(ms, rng.scalars_bytes(n)).tobytes())
+    cts[128 * 5:128 * 5 + 64] = bytes(64)
+    ss = [0, 1, R.n - 1, R.n + 2] + [rng.scalar() for _ in range(n - 4)]
+    sb = b''.join(s.to_bytes(32, 'big') for s in ss)
+    got = backend.ct_scalar_mul(sb, bytes(cts)).tobytes()
+    rc, want = oracle.ct_scalar_mul(sb, bytes(cts), threads=8)
+    assert rc == 0 and got == want
+    assert got[128 * 7:128 * 8] == R.ct_scalar_mul(bytes(cts[128 * 7:128 * 8]), ss[7])
+    z = backend.decrypt_check_zero(sk.to_bytes(32, 'big'), got[128 * 6:128 * 30])
+    assert list(z) == [0 if i % 3 == 0 else 1 for i in range(6, 30)]
+    bad = bytearray(cts)
+    bad[128 * 9 + 3] ^= 1
+    with pytest.raises(RuntimeError):
+        backend.ct_scalar_mul(sb, bytes(bad))
+
+
+def test_schnorr_batch_matches_oracle(backend, oracle, rng):
+    """kyber sign/schnorr Verify as VerifyProofSignature uses it (lib/proof/structs_proofs.go:498-505): 64 signatures
+    by different keys over messages of different lengths, then one tampering of each kind; accept bits equal the
+    oracle's and the definition's."""
+    pubs, sigs, msgs, want = [], [], [], []
+    g = np.random.default_rng(98)
+    for i in range(64):
+        x, k = rng.scalar(), rng.scalar()
+        Xb = R.g1_to_bytes(R.g1_mul(x, R.G1_GEN)) if i < 4 else oracle.g1_mul(x.to_bytes(32, 'big'), oracle.generators()[0])
+        msg = g.bytes(int(g.integers(0, 3000)))
+        sig = oracle.schnorr_sign(x.to_bytes(32, 'big'), k.to_bytes(32, 'big'), Xb, msg)
+        if i < 2:
+            assert sig == R.schnorr_sign(x, k, msg)
+        kind = i % 8 if i >= 32 else 0
+        if kind == 1:
+            msg = msg + b'x'
+        elif kind == 2:
+            sig = sig[:95] + bytes([sig[95] ^ 1])
+        elif kind == 3:
+            sig = sig[:20] + bytes([sig[20] ^ 1]) + sig[21:]          # R leaves the curve (or changes)
+        elif kind == 4:
+            Xb = oracle.g1_mul(rng.scalar().to_bytes(32, 'big'), oracle.generators()[0])
+        elif kind == 5:
+            sig = bytes(64) + sig[64:]                                  # R = identity
+        elif kind == 6:
+            sig = sig[:64] + b'\xff' * 32                               # s >= n
+        pubs.append(Xb); sigs.append(sig); msgs.append(msg); want.append(1 if kind in (0, 7) else 0)
+    got = backend.schnorr_verify(pubs, sigs, msgs)
+    assert list(got) == list(oracle.schnorr_verify(pubs, sigs, msgs, threads=8)) == want
+    for i in (0, 33, 34, 38):
+        assert R.schnorr_verify(R.g1_from_bytes(pubs[i]), msgs[i], sigs[i]) == bool(want[i])
+
+
 def test_reduce_rows_host_buffers(backend):
     """drx_reduce_rows against the Go loops' arithmetic (sum.go:19-23, mean.go:19-24, variance.go:19-27), wrap-around
     of int64 included, ragged sizes and an empty provider list."""

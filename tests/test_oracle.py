@@ -226,3 +226,42 @@ def test_key_switch_matches_definition_and_decrypts_under_target_key(oracle, rng
     bad[5] ^= 1
     rc, _, _ = oracle.key_switch(R.g1_to_bytes(Q), xs[0].to_bytes(32, 'big'), bytes(bad), b'\0' * 31 + b'\1' + vb[32:])
     assert rc == -2
+
+
+def test_obfuscation_scalar_mul_matches_definition(oracle, rng):
+    """CipherText.MulCipherTextbyScalar (protocols/obfuscation_protocol.go:240-243): a zero stays an encryption of
+    zero, a non-zero value stays non-zero (the OR / AND / min / max decodings rely on exactly that)."""
+    sk = rng.scalar()
+    P = R.g1_mul(sk, R.G1_GEN)
+    ms = [0, 1, 7, 0]
+    cts = b''.join(R.encrypt(P, m, rng.scalar()) for m in ms)
+    ss = [rng.scalar() for _ in ms]
+    rc, out = oracle.ct_scalar_mul(b''.join(s.to_bytes(32, 'big') for s in ss), cts, threads=2)
+    assert rc == 0
+    for i, s in enumerate(ss):
+        assert out[128 * i:128 * i + 128] == R.ct_scalar_mul(cts[128 * i:128 * i + 128], s)
+    assert list(oracle.decrypt_check_zero(sk.to_bytes(32, 'big'), out)) == [0, 1, 1, 0]
+    bad = bytearray(cts)
+    bad[70] ^= 1
+    assert oracle.ct_scalar_mul(b''.join(s.to_bytes(32, 'big') for s in ss), bytes(bad))[0] == -2
+
+
+def test_schnorr_matches_definition(oracle, rng):
+    """kyber sign/schnorr over G1 (VerifyProofSignature, lib/proof/structs_proofs.go:498-505): signatures made by
+    the C++ restatement equal the definition's and verify; a flipped message / R / s / key, s >= n and R off the curve
+    are rejected by both."""
+    x, k = rng.scalar(), rng.scalar()
+    X = R.g1_mul(x, R.G1_GEN)
+    Xb = R.g1_to_bytes(X)
+    msg = b'range proofs of survey 7' * 40
+    sig = oracle.schnorr_sign(x.to_bytes(32, 'big'), k.to_bytes(32, 'big'), Xb, msg)
+    assert sig == R.schnorr_sign(x, k, msg) and R.schnorr_verify(X, msg, sig)
+    other = R.g1_to_bytes(R.g1_mul(rng.scalar(), R.G1_GEN))
+    flip = lambda b, i: bytes(b[:i]) + bytes([b[i] ^ 1]) + bytes(b[i + 1:])
+    big_s = sig[:64] + (int.from_bytes(sig[64:], 'big') + R.n).to_bytes(32, 'big') if int.from_bytes(sig[64:], 'big') + R.n < 2 ** 256 else sig
+    cases = [(Xb, sig, msg, 1), (Xb, sig, msg + b'!', 0), (Xb, flip(sig, 95), msg, 0), (Xb, flip(sig, 10), msg, 0),
+             (other, sig, msg, 0), (Xb, big_s, msg, 1 if big_s == sig else 0), (Xb, bytes(64) + sig[64:], msg, 0)]
+    got = oracle.schnorr_verify([c[0] for c in cases], [c[1] for c in cases], [c[2] for c in cases], threads=2)
+    assert list(got) == [c[3] for c in cases]
+    for pub, sg, m, want in cases:
+        assert R.schnorr_verify(R.g1_from_bytes(pub), m, sg) == bool(want)
