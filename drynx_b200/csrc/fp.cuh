@@ -198,6 +198,118 @@ DRX_HD void mont_mul(uint32_t r[8], const uint32_t a[8], const uint32_t b[8]) {
   for (int k = 0; k < 8; k++) r[k] = use_d ? d[k] : t[k];
 }
 
+// r = (a*b + c*d) / 2^256 mod M: one Montgomery pass over the sum of two products (the two halves of an Fp2
+// product, c0 = a0*b0 + a1*(p - b1) and c1 = a0*b1 + a1*b0, need no Karatsuba pre-additions, no subtractions of
+// reduced products and one reduction each: the same 384 multiply-accumulates as three Montgomery products, about
+// 120 fewer carry-chain instructions and a shorter dependent tail).
+// Requires a, c < M (b and d may be any 256-bit values, e.g. p - 0 = p). Bounds: before each row t < 3M; a row adds
+// a*b_i + c*d_i + m*M < 3M(2^32 - 1), so t stays below 3M*2^32 < 2^290 inside the row -- position 8 can carry into
+// position 9 in every sweep, which is why each sweep ends by collecting its carry in hi9 -- and below 3M after the
+// shift. Two conditional subtractions at the end. Same even / odd accumulator layout as mont_mul: E holds positions
+// 0..7, O positions 1..8, hi9 position 9.
+template <class M>
+DRX_HD void mont_mul2(uint32_t r[8], const uint32_t a[8], const uint32_t b[8], const uint32_t c[8], const uint32_t d[8]) {
+  uint32_t e[8], o[8], hi9 = 0;
+  DRX_UNROLL
+  for (int k = 0; k < 8; k++) {
+    e[k] = 0;
+    o[k] = 0;
+  }
+  DRX_UNROLL
+  for (int i = 0; i < 8; i++) {
+    const uint32_t bi = b[i], di = d[i];
+    // shift one limb: positions 1..8 (o) become 0..7 (ne); e[2..7] become positions 1..6, hi9 position 8
+    uint32_t ne[8], no[8], top;
+    DRX_UNROLL
+    for (int k = 0; k < 8; k++) ne[k] = o[k];
+    DRX_UNROLL
+    for (int k = 0; k < 6; k++) no[k] = e[k + 2];
+    no[6] = 0;
+    no[7] = hi9;
+    ne[0] = add_cc(ne[0], e[1]);
+    // odd limbs of a (carry-in from the position-0 add), positions 1..8
+    DRX_UNROLL
+    for (int j = 0; j < 8; j += 2) {
+      no[j] = madc_lo_cc(a[j + 1], bi, no[j]);
+      no[j + 1] = madc_hi_cc(a[j + 1], bi, no[j + 1]);
+    }
+    top = addc(0, 0);
+    // even limbs of a, positions 0..7, carry into position 8
+    ne[0] = mad_lo_cc(a[0], bi, ne[0]);
+    ne[1] = madc_hi_cc(a[0], bi, ne[1]);
+    DRX_UNROLL
+    for (int j = 2; j < 8; j += 2) {
+      ne[j] = madc_lo_cc(a[j], bi, ne[j]);
+      ne[j + 1] = madc_hi_cc(a[j], bi, ne[j + 1]);
+    }
+    no[7] = addc_cc(no[7], 0);
+    top = addc(top, 0);
+    // second product: odd limbs of c
+    no[0] = mad_lo_cc(c[1], di, no[0]);
+    no[1] = madc_hi_cc(c[1], di, no[1]);
+    DRX_UNROLL
+    for (int j = 2; j < 8; j += 2) {
+      no[j] = madc_lo_cc(c[j + 1], di, no[j]);
+      no[j + 1] = madc_hi_cc(c[j + 1], di, no[j + 1]);
+    }
+    top = addc(top, 0);
+    // even limbs of c
+    ne[0] = mad_lo_cc(c[0], di, ne[0]);
+    ne[1] = madc_hi_cc(c[0], di, ne[1]);
+    DRX_UNROLL
+    for (int j = 2; j < 8; j += 2) {
+      ne[j] = madc_lo_cc(c[j], di, ne[j]);
+      ne[j + 1] = madc_hi_cc(c[j], di, ne[j + 1]);
+    }
+    no[7] = addc_cc(no[7], 0);
+    top = addc(top, 0);
+    // reduction row
+    const uint32_t m = mul_lo(ne[0], M::np0());
+    no[0] = mad_lo_cc(M::mod(1), m, no[0]);
+    no[1] = madc_hi_cc(M::mod(1), m, no[1]);
+    DRX_UNROLL
+    for (int j = 2; j < 8; j += 2) {
+      no[j] = madc_lo_cc(M::mod(j + 1), m, no[j]);
+      no[j + 1] = madc_hi_cc(M::mod(j + 1), m, no[j + 1]);
+    }
+    top = addc(top, 0);
+    ne[0] = mad_lo_cc(M::mod(0), m, ne[0]);
+    ne[1] = madc_hi_cc(M::mod(0), m, ne[1]);
+    DRX_UNROLL
+    for (int j = 2; j < 8; j += 2) {
+      ne[j] = madc_lo_cc(M::mod(j), m, ne[j]);
+      ne[j + 1] = madc_hi_cc(M::mod(j), m, ne[j + 1]);
+    }
+    no[7] = addc_cc(no[7], 0);
+    hi9 = addc(top, 0);
+    DRX_UNROLL
+    for (int k = 0; k < 8; k++) {
+      e[k] = ne[k];
+      o[k] = no[k];
+    }
+  }
+  // merge (drop the zero limb at position 0); the value is below 3M: subtract M up to twice
+  uint32_t t[8], s[8], top, bw;
+  t[0] = add_cc(o[0], e[1]);
+  DRX_UNROLL
+  for (int k = 1; k < 7; k++) t[k] = addc_cc(o[k], e[k + 1]);
+  t[7] = addc_cc(o[7], 0);
+  top = addc(hi9, 0);
+  DRX_UNROLL
+  for (int pass = 0; pass < 2; pass++) {
+    s[0] = sub_cc(t[0], M::mod(0));
+    DRX_UNROLL
+    for (int k = 1; k < 8; k++) s[k] = subc_cc(t[k], M::mod(k));
+    bw = subc(0, 0);  // 0xffffffff when t (low 256 bits) < mod
+    const bool use_s = (top != 0) | (bw == 0);
+    DRX_UNROLL
+    for (int k = 0; k < 8; k++) t[k] = use_s ? s[k] : t[k];
+    top = use_s ? top + bw : top;  // the borrow comes out of the ninth limb
+  }
+  DRX_UNROLL
+  for (int k = 0; k < 8; k++) r[k] = t[k];
+}
+
 template <class M>
 DRX_HD void mod_add(uint32_t r[8], const uint32_t a[8], const uint32_t b[8]) {
   uint32_t t[8], d[8];

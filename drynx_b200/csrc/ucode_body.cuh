@@ -84,6 +84,9 @@ k_rp_verify_prep(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __re
 
 // ---- Fp2 operations on register values (products go through the shared out-of-line fp_mul)
 __device__ __forceinline__ Fp2 uc_mul(const Fp2& a, const Fp2& b) {
+#if DRX_FP2_DUAL >= 1
+  return fp2_mul_dual(a, b);
+#endif
   // the three products are inlined here (and only here) so that ptxas interleaves their carry chains
   const Fp v0 = fp_mul_inl(a.c0, b.c0);
   const Fp v1 = fp_mul_inl(a.c1, b.c1);

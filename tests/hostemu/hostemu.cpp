@@ -18,6 +18,21 @@ int emu_fp_mul_raw(const uint32_t* a, const uint32_t* b, uint32_t* r, int which)
   return 0;
 }
 
+// r = (a*b + c*d) / 2^256 mod p (fp.cuh mont_mul2: the dual-product Montgomery pass behind the Fp2 product)
+int emu_fp_mul2_raw(const uint32_t* a, const uint32_t* b, const uint32_t* c, const uint32_t* d, uint32_t* r) {
+  mont_mul2<ModP>(r, a, b, c, d);
+  return 0;
+}
+
+// Fp2 product by the dual-product passes (tower.cuh fp2_mul_dual) and by Karatsuba (fp2_mul): 16 words each
+int emu_fp2_mul(const uint32_t* a, const uint32_t* b, uint32_t* r_dual, uint32_t* r_kara) {
+  Fp2 x, y;
+  memcpy(&x, a, 64); memcpy(&y, b, 64);
+  const Fp2 u = fp2_mul_dual(x, y), v = fp2_mul(x, y);
+  memcpy(r_dual, &u, 64); memcpy(r_kara, &v, 64);
+  return 0;
+}
+
 // which: 0 = plain inverse mod p, 1 = plain inverse mod n (division steps); 2 = Montgomery fp_inv (division steps),
 // 3 = Montgomery a^(p-2) (the cross-check)
 int emu_mod_inv(const uint32_t* a, uint32_t* r, int which) {

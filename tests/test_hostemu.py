@@ -31,6 +31,39 @@ def test_montgomery_rows(emu, rng):
             assert got == a * b * rinv % mod
 
 
+def test_dual_product_montgomery_pass(emu, rng):
+    """fp.cuh mont_mul2: (a*b + c*d) / R mod p in one pass, a, c < p and b, d any 256-bit value (the Fp2 product passes
+    p - b1, which is p itself for b1 = 0). The extreme operands drive the accumulator to its 3p bound."""
+    mod = R.p
+    rinv = pow(1 << 256, -1, mod)
+    top = 2 ** 256 - 1
+    cases = [(mod - 1, top, mod - 1, top), (mod - 1, mod - 1, mod - 1, mod - 1), (0, 0, 0, 0), (1, 1, 0, 5), (mod - 1, top, 0, 0),
+             (0, 7, mod - 1, top), (mod - 1, mod, mod - 1, mod), (5, mod, 7, 0), (mod - 1, 2 ** 255, mod - 2, 2 ** 255 + 12345)]
+    cases += [(rng.scalar() % mod, rng.scalar() % (1 << 256), rng.scalar() % mod, (rng.scalar() * 3) % (1 << 256)) for _ in range(600)]
+    for a, b, c, d in cases:
+        arrs = [np.array(_limbs(v), np.uint32) for v in (a, b, c, d)]
+        out = np.zeros(8, np.uint32)
+        emu.emu_fp_mul2_raw(arrs[0].ctypes.data, arrs[1].ctypes.data, arrs[2].ctypes.data, arrs[3].ctypes.data, out.ctypes.data)
+        got = sum(int(v) << (32 * k) for k, v in enumerate(out))
+        assert got == (a * b + c * d) * rinv % mod, (a, b, c, d)
+
+
+def test_fp2_product_dual_equals_karatsuba(emu, rng):
+    """tower.cuh fp2_mul_dual against fp2_mul (Karatsuba) and the definition, incl. zero and p - 1 components."""
+    mod = R.p
+    rinv = pow(1 << 256, -1, mod)
+    edge = [0, 1, mod - 1, mod - 2, 2 ** 255]
+    cases = [(a0, a1, b0, b1) for a0 in edge for a1 in (0, mod - 1) for b0 in (0, mod - 1, 5) for b1 in edge]
+    cases += [tuple(rng.scalar() % mod for _ in range(4)) for _ in range(300)]
+    for a0, a1, b0, b1 in cases:
+        A = np.array(_limbs(a0) + _limbs(a1), np.uint32); B = np.array(_limbs(b0) + _limbs(b1), np.uint32)
+        d, k = np.zeros(16, np.uint32), np.zeros(16, np.uint32)
+        emu.emu_fp2_mul(A.ctypes.data, B.ctypes.data, d.ctypes.data, k.ctypes.data)
+        assert (d == k).all()
+        c0 = sum(int(v) << (32 * i) for i, v in enumerate(d[:8])); c1 = sum(int(v) << (32 * i) for i, v in enumerate(d[8:]))
+        assert c0 == (a0 * b0 - a1 * b1) * rinv % mod and c1 == (a0 * b1 + a1 * b0) * rinv % mod
+
+
 def test_division_step_inverse(emu, rng):
     """fp.cuh mod_inv_plain (batched division steps, 20 x 30) against Python's pow(a, -1, m) for both moduli, on the
     boundary values and 2000 random residues each; the Montgomery wrapper against a^(p-2) on the same inputs."""
