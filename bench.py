@@ -442,7 +442,7 @@ def run_gpu(args):
                 'unit': 'TMAC32/s', 'frac': achieved / peak_tmac,
                 # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this size, from the committed ncu --set full
                 # capture profiles/r01_ncu_pair_ucode.txt (algorithmic bytes: 6,000 x 208 B in, 384 B out = 3.6 MB)
-                'traffic': 1540096 if dom == 'k_pair_ucode' else None,  # profiles/r01_ncu_pair_ucode.txt: dram read + write per launch
+                'traffic': 1544704 if dom == 'k_pair_ucode' else None,  # profiles/r01_ncu_pair_ucode.txt: dram read + write per launch
                 'peak_source': 'measured live: register-resident IMAD.WIDE.U32.X chains (drx_microbench kind 0); MEASURED_PEAKS.json has no integer figure',
                 'algorithmic': '%d proofs x %d (server,digit) pairs x %d M x 128 MAC32 per launch' % (n, NS * L, per_item)}
 
