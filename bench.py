@@ -38,6 +38,7 @@ M_AGG_CT = 22
 M_DECRYPT = 2840
 G1_BYTES = bytes(31) + b'\x01' + (65000549695646603732796438742359905742825358107623003571877145026864184071783 - 2).to_bytes(32, 'big')
 M_OBFUSCATE = 2 * 2816 + 16               # two 4-bit-window products, two affine outputs sharing one inversion
+M_SHUFFLE = 352 + 352 + 11 + 11 + 16       # two comb walks, two mixed additions, two affine outputs
 M_KEYSWITCH = 352 + 352 + 2816 + 16 + 16   # v*B and v*Q by comb, x*rB by 4-bit windows, one addition, two affine outputs
 
 
@@ -529,6 +530,11 @@ def secondary_rates(be, lib, torch, dev, stream, ck, vp, peak_tmac, skp):
     ms = timed(lambda: ck(lib.drx_ct_scalar_mul_dev(be.h, nd, vp(r), vp(ct), vp(obf))))
     out['obfuscations_per_s'] = nd / ms * 1e3
     out['obfuscation_roofline_frac'] = nd * M_OBFUSCATE * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    # shuffling (ShuffleSequence re-randomisation) of the same ciphertexts as 2^10 lines of 2^7
+    perm = torch.from_numpy(np.random.default_rng(6).permutation(1 << 10).astype(np.int32)).to(dev)
+    ms = timed(lambda: ck(lib.drx_shuffle_rerandomize_dev(be.h, 1 << 10, 1 << 7, vp(perm), vp(ct), vp(r), vp(obf))))
+    out['shuffle_rerandomizations_per_s'] = nd / ms * 1e3
+    out['shuffle_roofline_frac'] = nd * M_SHUFFLE * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
     # Schnorr proof-request signatures (host buffers, digests given): 2^14 signatures by one key
     import hashlib
     ns_ = 1 << 14

@@ -51,6 +51,8 @@ SIGNATURES = {
     'drx_decrypt_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
     'drx_ct_scalar_mul': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
     'drx_ct_scalar_mul_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP]),
+    'drx_shuffle_rerandomize': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, VP, VP, VP]),
+    'drx_shuffle_rerandomize_dev': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, VP, VP, VP]),
     'drx_schnorr_verify': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP, VP]),
     'drx_set_target_pubkey': (ctypes.c_int, [VP, VP]),
     'drx_keyswitch': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP, VP, VP]),

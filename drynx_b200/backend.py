@@ -128,6 +128,18 @@ class Backend:
         _lib.check(self.lib.drx_ct_scalar_mul(self.h, n, _ptr(sc), _ptr(ct), _ptr(out)))
         return out
 
+    def shuffle_rerandomize(self, lines, betas, pi):
+        """libunlynxshuffle.ShuffleSequence with beta and pi injected: lines = list of serialised CipherVectors of one
+        length, betas = list of nq*32-byte scalar blocks (indexed like lines), pi = permutation of the lines."""
+        k = len(lines)
+        nq = len(bytes(lines[0])) // 128 if k else 0
+        data, beta = _u8(b''.join(bytes(x) for x in lines)), _u8(b''.join(bytes(x) for x in betas))
+        assert data.size == k * nq * 128 and beta.size == k * nq * 32
+        perm = np.ascontiguousarray(pi, dtype=np.int32)
+        out = np.empty(k * nq * 128, dtype=np.uint8)
+        _lib.check(self.lib.drx_shuffle_rerandomize(self.h, k, nq, _ptr(perm), _ptr(data), _ptr(beta), _ptr(out)))
+        return [out[i * nq * 128:(i + 1) * nq * 128] for i in range(k)]
+
     def schnorr_verify(self, pubs, sigs, msgs):
         """kyber sign/schnorr Verify over G1 for n (key, signature, message) triples; the SHA-512 of R || P || msg is
         taken here on the host. Returns n accept bytes."""

@@ -706,6 +706,50 @@ int drx_ct_scalar_mul(drx_ctx* c, size_t n, const uint8_t* s, const uint8_t* ct,
   return 0;
 }
 
+// ---- shuffling data path: libunlynxshuffle.ShuffleSequence with beta and pi injected
+int drx_shuffle_rerandomize(drx_ctx* c, size_t lines, size_t nq, const int32_t* pi, const uint8_t* in, const uint8_t* beta,
+                            uint8_t* out) {
+  if (!c) return fail(-1, "null context");
+  const size_t n = lines * nq;
+  if (n == 0) return 0;
+  if (!pi || !in || !beta || !out) return fail(-1, "drx_shuffle_rerandomize: null buffer");
+  Guard g(c);
+  if (!c->have_pub) return fail(-1, "drx_shuffle_rerandomize: call drx_set_pubkey first");
+  std::vector<char> seen(lines, 0);
+  for (size_t i = 0; i < lines; i++) {
+    if (pi[i] < 0 || (size_t)pi[i] >= lines || seen[pi[i]]) return fail(-1, "drx_shuffle_rerandomize: pi is not a permutation");
+    seen[pi[i]] = 1;
+  }
+  Arena& a = c->arena;
+  a.plan_reset();
+  size_t op = a.plan(lines * 4), oi = a.plan(n * 128), ob = a.plan(n * 32), oo = a.plan(n * 128);
+  RET(a.commit());
+  RET(reset_bad(c));
+  CU(cudaMemcpyAsync(a.at<void>(op), pi, lines * 4, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(a.at<void>(oi), in, n * 128, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(a.at<void>(ob), beta, n * 32, cudaMemcpyHostToDevice, c->stream));
+  timed(c, "k_shuffle_rerandomize", [&] {
+    return launch_shuffle_rerandomize(c->stream, lines, nq, a.at<int32_t>(op), a.at<uint8_t>(oi), a.at<uint8_t>(ob),
+                                      c->tabB.p, c->tabP.p, a.at<uint8_t>(oo), (int*)c->bad.p);
+  });
+  RET(check_launch("shuffle_rerandomize"));
+  CU(cudaMemcpyAsync(out, a.at<void>(oo), n * 128, cudaMemcpyDeviceToHost, c->stream));
+  int bad = 0;
+  RET(read_bad(c, &bad));
+  if (bad) return fail(-2, "drx_shuffle_rerandomize: %d malformed points", bad);
+  return 0;
+}
+int drx_shuffle_rerandomize_dev(drx_ctx* c, size_t lines, size_t nq, const int32_t* d_pi, const uint8_t* d_in,
+                                const uint8_t* d_beta, uint8_t* d_out) {
+  if (!c) return fail(-1, "null context");
+  Guard g(c);
+  if (!c->have_pub) return fail(-1, "drx_shuffle_rerandomize: call drx_set_pubkey first");
+  timed(c, "k_shuffle_rerandomize", [&] {
+    return launch_shuffle_rerandomize(c->stream, lines, nq, d_pi, d_in, d_beta, c->tabB.p, c->tabP.p, d_out, (int*)c->bad.p);
+  });
+  return check_launch("shuffle_rerandomize");
+}
+
 // ---- Schnorr signatures over G1 (lib/proof/structs_proofs.go:498-505): the caller supplies SHA-512(R || P || msg)
 int drx_schnorr_verify(drx_ctx* c, size_t n, const uint8_t* pub, const uint8_t* sig, const uint8_t* digest, uint8_t* ok) {
   if (!c) return fail(-1, "null context");

@@ -633,6 +633,38 @@ int launch_ct_scalar_mul(cudaStream_t st, size_t n, const uint8_t* d_s, const ui
   return 1;
 }
 
+// ------------------------------------------------------------------ shuffling
+// libunlynxshuffle.ShuffleSequence (unlynx lib/shuffle; call sites data/data.go:68 and, through
+// protocolsunlynx.ShufflingProtocol, services/service.go:618-660): line i of the output is line pi[i] of the input with
+// every ciphertext re-randomised, CipherText.Rerandomize: K' = K + beta*g, C' = C + beta*h with g the base point and
+// h the collective key. Two comb walks and two mixed additions per thread, one shared inversion.
+__global__ void __launch_bounds__(128)
+k_shuffle_rerandomize(size_t lines, size_t nq, const int32_t* __restrict__ pi, const uint32_t* __restrict__ in,
+                      const uint32_t* __restrict__ beta, const G1Aff* __restrict__ tabB, const G1Aff* __restrict__ tabP,
+                      uint32_t* __restrict__ out, int* bad) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= lines * nq) return;
+  const size_t i = t / nq, j = t - i * nq;
+  const size_t src = (size_t)pi[i] * nq + j;
+  G1Aff K, C;
+  int nbad = !g1_from_wire(K, in + 32 * src);
+  nbad += !g1_from_wire(C, in + 32 * src + 16);
+  if (nbad) {
+    atomicAdd(bad, nbad);
+    return;
+  }
+  const Scalar b = sc_from_wire(beta + 8 * src);
+  store_pair_wire(out + 32 * t, jac_add_aff(comb_mul(tabB, b), K), jac_add_aff(comb_mul(tabP, b), C));
+}
+int launch_shuffle_rerandomize(cudaStream_t st, size_t lines, size_t nq, const int32_t* d_pi, const uint8_t* d_in,
+                               const uint8_t* d_beta, const void* d_tabB, const void* d_tabP, uint8_t* d_out, int* d_bad) {
+  if (!lines || !nq) return 0;
+  k_shuffle_rerandomize<<<grid_for(lines * nq, 128), 128, 0, st>>>(lines, nq, d_pi, (const uint32_t*)d_in,
+                                                                  (const uint32_t*)d_beta, (const G1Aff*)d_tabB,
+                                                                  (const G1Aff*)d_tabP, (uint32_t*)d_out, d_bad);
+  return 1;
+}
+
 // ------------------------------------------------------------------ Schnorr signatures
 // kyber sign/schnorr Verify over G1, as VerifyProofSignature calls it for every proof request
 // (lib/proof/structs_proofs.go:498-505): sig = R (64 B) || s (32 B); h = SHA-512(R || P || msg) read big-endian and

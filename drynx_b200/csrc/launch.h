@@ -53,6 +53,9 @@ int launch_decrypt(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t
 // key switching: cv[i] = (v_i*B) || (v_i*Q - sk*rb_i), rb_neg[i] = -rb_i (optional)
 int launch_keyswitch(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t* d_rb, const uint8_t* d_v,
                      const void* d_tabB, const void* d_tabQ, uint8_t* d_cv, uint8_t* d_rb_neg, int* d_bad);
+// ShuffleSequence: out line i = in line pi[i], every ciphertext re-randomised with beta[pi[i]][j]
+int launch_shuffle_rerandomize(cudaStream_t st, size_t lines, size_t nq, const int32_t* d_pi, const uint8_t* d_in,
+                               const uint8_t* d_beta, const void* d_tabB, const void* d_tabP, uint8_t* d_out, int* d_bad);
 // MulCipherTextbyScalar per element: out_i = (s_i*K_i, s_i*C_i)
 int launch_ct_scalar_mul(cudaStream_t st, size_t n, const uint8_t* d_s, const uint8_t* d_ct, uint8_t* d_out, int* d_bad);
 // Schnorr over G1: ok_i = (s_i*B == R_i + h_i*P_i), sig = R || s (96 B), digest = SHA-512(R || P || msg) (64 B)

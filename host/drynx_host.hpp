@@ -347,6 +347,52 @@ inline bool AggregationListProofVerification(const PublishedAggregationListProof
 }  // namespace libunlynxaggr
 
 // =====================================================================================================================
+namespace libunlynxshuffle {
+using drynx::Gpu;
+using drynx::Point;
+using drynx::Scalar;
+
+struct Shuffled {  // the three return values of ShuffleSequence
+  std::vector<libunlynx::CipherVector> outputList;
+  std::vector<int> pi;
+  std::vector<std::vector<Scalar>> beta;
+};
+// ShuffleSequence(inputList, g = B, h, nil) (unlynx lib/shuffle; data/data.go:68, services/service.go:618-660): a fresh
+// blinding factor per ciphertext from the random stream, a random permutation of the lines (Fisher-Yates over the
+// same stream), one device call for the re-randomisation. `h` is the collective key.
+inline Shuffled ShuffleSequence(const std::vector<libunlynx::CipherVector>& inputList, const Point& h) {
+  libunlynx::use_pubkey(h);
+  Shuffled s;
+  const size_t k = inputList.size(), nq = k ? inputList[0].size() : 0;
+  s.beta.assign(k, std::vector<Scalar>(nq));
+  std::vector<uint8_t> in(k * nq * 128), beta(k * nq * 32), out(k * nq * 128);
+  for (size_t i = 0; i < k; i++) {
+    if (inputList[i].size() != nq) throw drynx::Error(-1, "ShuffleSequence: lines of different lengths");
+    for (size_t j = 0; j < nq; j++) {
+      s.beta[i][j] = drynx::pick();
+      memcpy(&in[(i * nq + j) * 128], inputList[i][j].b, 128);
+      memcpy(&beta[(i * nq + j) * 32], s.beta[i][j].b, 32);
+    }
+  }
+  s.pi.resize(k);
+  for (size_t i = 0; i < k; i++) s.pi[i] = (int)i;
+  for (size_t i = k; i > 1; i--) {
+    const Scalar r = drynx::pick();
+    uint64_t v = 0;
+    for (int b = 24; b < 32; b++) v = (v << 8) | r.b[b];
+    std::swap(s.pi[i - 1], s.pi[v % i]);
+  }
+  std::vector<int32_t> pi32(s.pi.begin(), s.pi.end());
+  if (k && nq)
+    drynx::check(drx_shuffle_rerandomize(Gpu::get().ctx(), k, nq, pi32.data(), in.data(), beta.data(), out.data()));
+  s.outputList.assign(k, libunlynx::CipherVector(nq));
+  for (size_t i = 0; i < k; i++)
+    for (size_t j = 0; j < nq; j++) memcpy(s.outputList[i][j].b, &out[(i * nq + j) * 128], 128);
+  return s;
+}
+}  // namespace libunlynxshuffle
+
+// =====================================================================================================================
 namespace libunlynxkeyswitch {
 using drynx::Gpu;
 using drynx::Point;

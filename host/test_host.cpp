@@ -347,6 +347,24 @@ static void TestKeySwitching() {
   EXPECT(libunlynx::DecryptIntVectorWithNeg(querier.Private, cv) != values);
 }
 
+static void TestShuffleSequence() {  // data/data.go:60-70: two lines shuffled under the collective key
+  auto keys = drynx::NewKeyPair();
+  libunlynx::CreateDecryptionTable(10000, keys.Public, keys.Private);
+  std::vector<std::vector<int64_t>> tabs = {{1, 2, 3, 6}, {2, 4, 8, 6}, {0, -5, 7, 7}};
+  std::vector<libunlynx::CipherVector> responses;
+  for (auto& t : tabs) responses.push_back(libunlynx::EncryptIntVector(keys.Public, t));
+  auto sh = libunlynxshuffle::ShuffleSequence(responses, keys.Public);
+  EXPECT(sh.outputList.size() == 3 && sh.pi.size() == 3 && sh.beta.size() == 3 && sh.beta[0].size() == 4);
+  std::vector<int> seen(3, 0);
+  for (size_t i = 0; i < 3; i++) {
+    EXPECT(sh.pi[i] >= 0 && sh.pi[i] < 3);
+    seen[(size_t)sh.pi[i]]++;
+    EXPECT(libunlynx::DecryptIntVectorWithNeg(keys.Private, sh.outputList[i]) == tabs[(size_t)sh.pi[i]]);
+    EXPECT(memcmp(sh.outputList[i][0].b, responses[(size_t)sh.pi[i]][0].b, 128) != 0);
+  }
+  EXPECT(seen == std::vector<int>({1, 1, 1}));
+}
+
 static std::string hex(const uint8_t* b, size_t n) {
   static const char* d = "0123456789abcdef";
   std::string s;
@@ -422,6 +440,7 @@ int main(int argc, char** argv) {
       TestEncodeDecodeDispatcher();
       TestKeySwitching();
       TestProofSignatureAndAggregationProof();
+      TestShuffleSequence();
     } catch (const drynx::Error& e) {
       printf("FAIL: exception %d: %s\n", e.code, e.what());
       failures++;

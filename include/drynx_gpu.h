@@ -161,6 +161,17 @@ int drx_keyswitch_dev(drx_ctx* ctx, size_t n, const uint8_t sk[32], const uint8_
 int drx_ct_scalar_mul(drx_ctx* ctx, size_t n, const uint8_t* s /*n*32*/, const uint8_t* ct /*n*128*/, uint8_t* out /*n*128*/);
 int drx_ct_scalar_mul_dev(drx_ctx* ctx, size_t n, const uint8_t* d_s, const uint8_t* d_ct, uint8_t* d_out);
 
+/* Shuffling data path: libunlynxshuffle.ShuffleSequence(inputList, g, h, nil) with the
+ * blinding factors and the permutation injected (unlynx v1.4.0 lib/shuffle; call sites data/data.go:68 and, through
+ * protocolsunlynx.ShufflingProtocol, services/service.go:618-660). `in` holds `lines` CipherVectors of `nq` ciphertexts;
+ * out line i = in line pi[i] with every ciphertext re-randomised (CipherText.Rerandomize):
+ * K' = K + beta[pi[i]][j]*B, C' = C + beta[pi[i]][j]*P, P the key of drx_set_pubkey. beta is indexed like `in`.
+ * Returns -1 when pi is not a permutation of 0..lines-1 (host-buffer form), -2 on a malformed point. */
+int drx_shuffle_rerandomize(drx_ctx* ctx, size_t lines, size_t nq, const int32_t* pi, const uint8_t* in /*lines*nq*128*/,
+                            const uint8_t* beta /*lines*nq*32*/, uint8_t* out /*lines*nq*128*/);
+int drx_shuffle_rerandomize_dev(drx_ctx* ctx, size_t lines, size_t nq, const int32_t* d_pi, const uint8_t* d_in,
+                                const uint8_t* d_beta, uint8_t* d_out);
+
 /* Schnorr signature check over G1, batched: kyber sign/schnorr Verify as
  * VerifyProofSignature calls it for every proof request (lib/proof/structs_proofs.go:498-505).
  * pub: n*64 signer keys; sig: n*96, R (64) || s (32); digest: n*64, SHA-512(R || P || msg) computed by the caller

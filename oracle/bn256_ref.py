@@ -306,6 +306,12 @@ def ct_scalar_mul(ct, s):
     return g1_to_bytes(g1_mul(s % n, K)) + g1_to_bytes(g1_mul(s % n, C))
 
 
+def rerandomize(ct, pub, b):
+    """CipherText.Rerandomize as ShuffleSequence uses it (data/data.go:68): (K + b*B, C + b*P)."""
+    K, C = g1_from_bytes(ct[:64]), g1_from_bytes(ct[64:128])
+    return g1_to_bytes(g1_add(K, g1_mul(b, G1_GEN))) + g1_to_bytes(g1_add(C, g1_mul(b, pub)))
+
+
 def schnorr_sign(x, k, msg):
     """kyber sign/schnorr Sign over G1 with the nonce k injected (recalled): R = k*B, h = SHA-512(R || X || msg) mod n
     (big-endian), s = k + x*h, signature R || s."""

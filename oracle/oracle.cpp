@@ -1507,6 +1507,31 @@ int orc_ct_scalar_mul(size_t n, const uint8_t* s, const uint8_t* ct, uint8_t* ou
   return bad ? -2 : 0;
 }
 
+// libunlynxshuffle.ShuffleSequence(inputList, g, h, nil) with beta and pi injected (unlynx v1.4.0 lib/shuffle, recalled;
+// call sites data/data.go:68, services/service.go:618-660): outputList[i][j].Rerandomize(inputList[pi[i]][j], b, b, _, g, h)
+// with b = beta[pi[i]][j]: K = K1 + b*g, C = C1 + b*h
+int orc_shuffle_rerandomize(size_t lines, size_t nq, const int32_t* pi, const uint8_t* in, const uint8_t* beta,
+                            const uint8_t* P, uint8_t* out, int threads) {
+  ensure_init();
+  curvePoint h;
+  if (!g1_unmarshal(h, P)) return -2;
+  std::atomic<int> bad(0);
+  parallel_for(lines * nq, threads, [&](size_t t) {
+    const size_t i = t / nq, j = t % nq, src = (size_t)pi[i] * nq + j;
+    curvePoint K1, C1, tmp1, tmp2, K, C;
+    if (!g1_unmarshal(K1, in + 128 * src) || !g1_unmarshal(C1, in + 128 * src + 64)) { bad++; return; }
+    Sc b;
+    sc_from_bytes(b, beta + 32 * src);
+    tmp1.Mul(curveGen, b.v);
+    tmp2.Mul(h, b.v);
+    K.Add(K1, tmp1);
+    C.Add(C1, tmp2);
+    g1_marshal(out + 128 * t, K);
+    g1_marshal(out + 128 * t + 64, C);
+  });
+  return bad ? -2 : 0;
+}
+
 int orc_schnorr_verify(size_t n, const uint8_t* pub, const uint8_t* sig, const uint8_t* digest, uint8_t* ok, int threads) {
   ensure_init();
   parallel_for(n, threads, [&](size_t i) { ok[i] = schnorr_verify_one(pub + 64 * i, sig + 96 * i, digest + 64 * i) ? 1 : 0; });

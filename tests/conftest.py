@@ -90,6 +90,17 @@ class Oracle:
         rc = self.lib.orc_ct_scalar_mul(ctypes.c_size_t(n), self._p(sc), self._p(ct), self._p(out), threads)
         return rc, out.tobytes()
 
+    def shuffle_rerandomize(self, P, lines, betas, pi, threads=1):
+        k = len(lines)
+        nq = len(bytes(lines[0])) // 128
+        data = np.frombuffer(b''.join(bytes(x) for x in lines), np.uint8).copy()
+        beta = np.frombuffer(b''.join(bytes(x) for x in betas), np.uint8).copy()
+        perm = np.ascontiguousarray(pi, dtype=np.int32)
+        out = np.zeros(k * nq * 128, np.uint8)
+        rc = self.lib.orc_shuffle_rerandomize(ctypes.c_size_t(k), ctypes.c_size_t(nq), self._p(perm), self._p(data),
+                                              self._p(beta), bytes(P), self._p(out), threads)
+        return rc, [out[i * nq * 128:(i + 1) * nq * 128].tobytes() for i in range(k)]
+
     def schnorr_sign(self, x, k, pub, msg):
         """Sign with the nonce injected: the group and scalar steps in the C++ oracle, SHA-512 here."""
         import hashlib

@@ -200,6 +200,37 @@ def test_obfuscation_scalar_mul_matches_oracle(backend, oracle, rng):
         backend.ct_scalar_mul(sb, bytes(bad))
 
 
+def test_shuffle_rerandomize_matches_oracle(backend, oracle, rng):
+    """libunlynxshuffle.ShuffleSequence with beta and pi injected (data/data.go:68, services/service.go:618-660): 40
+    lines of 25 ciphertexts; bytes equal the oracle's, plaintexts come back in permuted order, beta = 0 leaves a
+    ciphertext unchanged, a non-permutation and a malformed point are refused."""
+    sk, P = _keys(rng)
+    backend.set_pubkey(P)
+    k, nq = 40, 25
+    g = np.random.default_rng(41)
+    vals = g.integers(-100, 100, size=(k, nq))
+    lines = [backend.encrypt_int_vector([int(v) for v in vals[i]], rng.scalars_bytes(nq)).tobytes() for i in range(k)]
+    betas = [bytearray(rng.scalars_bytes(nq)) for _ in range(k)]
+    betas[3][0:32] = bytes(32)
+    betas[4][0:32] = (R.n + 1).to_bytes(32, 'big')
+    pi = [int(v) for v in g.permutation(k)]
+    out = backend.shuffle_rerandomize(lines, betas, pi)
+    rc, want = oracle.shuffle_rerandomize(P, lines, betas, pi, threads=8)
+    assert rc == 0 and [o.tobytes() for o in out] == want
+    at3 = pi.index(3)
+    assert out[at3].tobytes()[:128] == lines[3][:128] and out[at3].tobytes()[128:256] != lines[3][128:256]
+    assert out[0].tobytes()[:128] == R.rerandomize(lines[pi[0]][:128], R.g1_from_bytes(P), int.from_bytes(betas[pi[0]][:32], 'big'))
+    backend.create_decryption_table(10000)
+    for i in (0, 7, 39):
+        assert list(backend.decrypt_int_vector(sk.to_bytes(32, 'big'), out[i])) == [int(v) for v in vals[pi[i]]]
+    with pytest.raises(RuntimeError):
+        backend.shuffle_rerandomize(lines, betas, [0] * k)
+    bad = [bytearray(x) for x in lines]
+    bad[5][130] ^= 1
+    with pytest.raises(RuntimeError):
+        backend.shuffle_rerandomize(bad, betas, pi)
+
+
 def test_schnorr_batch_matches_oracle(backend, oracle, rng):
     """kyber sign/schnorr Verify as VerifyProofSignature uses it (lib/proof/structs_proofs.go:498-505): 64 signatures
     by different keys over messages of different lengths, then one tampering of each kind; accept bits equal the

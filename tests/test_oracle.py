@@ -265,3 +265,24 @@ def test_schnorr_matches_definition(oracle, rng):
     assert list(got) == [c[3] for c in cases]
     for pub, sg, m, want in cases:
         assert R.schnorr_verify(R.g1_from_bytes(pub), m, sg) == bool(want)
+
+
+def test_shuffle_rerandomize_matches_definition(oracle, rng):
+    """libunlynxshuffle.ShuffleSequence (data/data.go:68): lines permuted as a whole, every ciphertext re-randomised;
+    the plaintexts survive in permuted order."""
+    sk = rng.scalar()
+    P = R.g1_mul(sk, R.G1_GEN)
+    vals = [[1, 2, 3], [4, 5, 6], [7, 8, 9], [0, -1, 99]]
+    lines = [b''.join(R.encrypt(P, m, rng.scalar()) for m in row) for row in vals]
+    betas = [[rng.scalar() for _ in row] for row in vals]
+    pi = [2, 0, 3, 1]
+    rc, out = oracle.shuffle_rerandomize(R.g1_to_bytes(P), lines, [b''.join(b.to_bytes(32, 'big') for b in row) for row in betas], pi, threads=2)
+    assert rc == 0
+    for i in range(4):
+        for j in range(3):
+            assert out[i][128 * j:128 * j + 128] == R.rerandomize(lines[pi[i]][128 * j:128 * j + 128], P, betas[pi[i]][j])
+        assert out[i] != lines[pi[i]]
+    oracle.dlog_reset()
+    for i in range(4):
+        got, found = oracle.decrypt(sk.to_bytes(32, 'big'), out[i])
+        assert list(got) == vals[pi[i]] and all(found)
