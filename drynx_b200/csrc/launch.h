@@ -14,7 +14,7 @@ constexpr size_t kG1AffBytes = 64, kG2AffBytes = 128, kGtBytes = 384, kG1JacByte
 constexpr int64_t kMaxHomomorphicInt = 100000;  // libunlynx.MaxHomomorphicInt
 constexpr uint32_t kDlogCap = 1u << 18;         // open-addressing slots for 100001 keys
 constexpr int kAggMaxSlices = 64;
-constexpr size_t kUcodeAutoMaxItems = 27000;  // batches up to this many pairing checks take the lane-group path (measured crossover: 2,000 proofs x 12 checks 20.8 vs 21.4 ms, 3,000 proofs 29.6 vs 27.5 ms)
+constexpr size_t kUcodeAutoMaxItems = 42000;  // batches up to this many pairing checks take the lane-group path (measured crossover with four persistent blocks per SM: 3,000 proofs x 12 checks 25.4 vs 27.5 ms, 4,096 proofs 33.7 vs 31.6 ms)
 constexpr size_t kEncryptLanesMaxItems = 16384; // encryptions up to this many use eight lanes each (latency)
 constexpr size_t kCreateLanesMaxItems = 800;   // creation items up to this many: lane-cooperative kernel (8 / 16 lanes per item)
 constexpr size_t kCreateFineMaxItems = 36000; // creation items up to this many are split twelve ways (latency)

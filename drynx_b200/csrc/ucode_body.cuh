@@ -406,8 +406,7 @@ int UC_LAUNCH(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch
     if (want > smem) smem = want;
   }
 #ifdef UC_WITH_DYN
-  // more than three blocks per usable SM: deal the work dynamically over three persistent blocks per SM (the
-  // occupancy with the best aggregate rate: 3 blocks in 5.4 ms against 2 in 4.1 ms or 4 in 8.8 ms)
+  // more than three blocks per usable SM: deal the work dynamically over three or four persistent blocks per SM
   if (nblocks > 3 * usable) {
     static bool dyn_configured = false;
     if (!dyn_configured) {
@@ -419,8 +418,12 @@ int UC_LAUNCH(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch
     unsigned int* ctrl = (unsigned int*)base;
     uint4* state = (uint4*)(base + uc_align256(16 + 4 * ngroups));
     cudaMemsetAsync(ctrl, 0, 16 + 4 * ngroups, st);
-    const int smem3 = (smem_sm / 3 - 1024) & ~127;
-    int grid = 3 * nsm;
+    // persistent blocks per SM: three up to ~1,000 warp tasks, four above (measured after the dual-product Fp2
+    // form: 900 tasks 5.51 against 6.29 ms, 1,050 tasks 6.16 against 5.89, 3,000 tasks 17.3 against 14.5)
+    int resident = ngroups >= 1000 ? 4 : 3;
+    if (resident * (natural + 1024) > smem_sm) resident = 3;
+    const int smem3 = (smem_sm / resident - 1024) & ~127;
+    int grid = resident * nsm;
     if (grid > nblocks) grid = nblocks;
     const unsigned int nseg = UC_NSEG;
     UC_KERNEL_DYN<<<grid, UC_BLOCK, smem3, st>>>(items, (const UcPrep*)d_prep, (GtPair*)d_scratch, state, ctrl, nseg);

@@ -240,11 +240,13 @@ def test_creation_kernels_agree(backend, oracle, rng):
     assert a.tobytes() == bytes(want)
 
 
-def test_dynamic_segment_kernel_600_proofs(backend, oracle, rng):
-    """600 proofs x 12 checks = 7,200 pairing checks: more than three lane-group blocks per SM, so verification runs
-    the dynamic kernel (32 program segments dealt from a queue, slot images handed over through global memory). Every
-    proof verifies, the tampered ones (one per kind of field) are rejected, and a sample is checked against the oracle."""
-    ns, u, l, n = 3, 16, 4, 600
+@pytest.mark.parametrize('n', [600, 700])
+def test_dynamic_segment_kernel(backend, oracle, rng, n):
+    """600 proofs x 12 checks = 7,200 pairing checks (900 warp tasks: three persistent blocks per SM) and 700 x 12 =
+    8,400 (1,050 warp tasks: four): more than three lane-group blocks per SM, so verification runs the dynamic kernel
+    (32 program segments dealt from a queue, slot images handed over through global memory). Every proof verifies, the
+    tampered ones (one per kind of field) are rejected, and a sample is checked against the oracle."""
+    ns, u, l = 3, 16, 4
     sk, P, Y, A = _setup(backend, oracle, rng, ns, u, set_id=62)
     g = np.random.default_rng(62)
     secrets = [int(x) for x in g.integers(0, u ** l, size=n)]
