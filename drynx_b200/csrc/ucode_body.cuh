@@ -407,7 +407,9 @@ int UC_LAUNCH(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch
   }
 #ifdef UC_WITH_DYN
   // more than three blocks per usable SM: deal the work dynamically over three or four persistent blocks per SM
-  if (nblocks > 3 * usable) {
+  // (a few blocks early: within eight blocks of three per usable SM the static launch already loses a block to a
+  // second wave -- 390 blocks 5.29 ms, 395 blocks 6.59, 399 blocks 7.15 against 5.3-5.4 dynamic)
+  if (nblocks > 3 * usable - 8) {
     static bool dyn_configured = false;
     if (!dyn_configured) {
       cudaFuncSetAttribute(UC_KERNEL_DYN, cudaFuncAttributeMaxDynamicSharedMemorySize, uc_smem_optin);
