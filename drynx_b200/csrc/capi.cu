@@ -893,8 +893,16 @@ int drx_mont_mul(drx_ctx* c, size_t n, int which, const uint32_t* x, const uint3
 int drx_microbench(drx_ctx* c, int kind, int iters, double* ms, double* work) {
   if (!c || !ms || !work) return fail(-1, "null argument");
   Guard g(c);
-  const int blocks = 148 * 8, threads = 256;
-  RET(c->sink.ensure((size_t)blocks * threads * 4));
+  // kind 0: wide multiply-accumulate chains, 1: dependent Montgomery products (both fill the GPU: the roofline peaks);
+  // kinds 10 + k / 20 + k / 30 + k: probe k (1: one chain of products, 2: three chains) with one warp per SM / one
+  // warp per sub-partition / two warps per sub-partition (latency probes, profiles/r01_experiments.md)
+  int blocks = 148 * 8, threads = 256;
+  if (kind >= 10) {
+    blocks = 148;
+    threads = kind >= 30 ? 256 : kind >= 20 ? 128 : 32;
+    kind %= 10;
+  }
+  RET(c->sink.ensure((size_t)148 * 8 * 256 * 4));
   cudaEvent_t e0, e1;
   CU(cudaEventCreate(&e0));
   CU(cudaEventCreate(&e1));
@@ -908,7 +916,7 @@ int drx_microbench(drx_ctx* c, int kind, int iters, double* ms, double* work) {
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   *ms = t;
-  const double per_thread = kind == 0 ? 16.0 * iters : 2.0 * iters;  // MAC32 (wide MACs) or Montgomery products
+  const double per_thread = kind == 0 ? 16.0 * iters : kind == 2 ? 3.0 * iters : 2.0 * iters;  // wide MACs or Montgomery products
   *work = per_thread * blocks * threads;
   return check_launch("microbench");
 }

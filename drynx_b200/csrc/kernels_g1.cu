@@ -782,8 +782,26 @@ __global__ void __launch_bounds__(256) k_probe_montmul(int iters, uint32_t* sink
   for (int k = 0; k < 8; k++) s ^= x.v[k] ^ y.v[k];
   sink[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
+// three independent chains of dependent Montgomery products per thread (what an Fp2 product offers the scheduler)
+__global__ void __launch_bounds__(256) k_probe_montmul3(int iters, uint32_t* sink) {
+  Fp x[3], y;
+  for (int k = 0; k < 8; k++) {
+    for (int q = 0; q < 3; q++) x[q].v[k] = (threadIdx.x + 1 + q) * 2654435761u + k;
+    y.v[k] = (blockIdx.x + 1) * 40503u + k * 77u;
+  }
+  for (int q = 0; q < 3; q++) x[q].v[7] &= 0x7fffffffu;
+  y.v[7] &= 0x7fffffffu;
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int q = 0; q < 3; q++) mont_mul<ModP>(x[q].v, x[q].v, y.v);
+  }
+  uint32_t s = 0;
+  for (int k = 0; k < 8; k++) s ^= x[0].v[k] ^ x[1].v[k] ^ x[2].v[k];
+  sink[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
 int launch_microbench(cudaStream_t st, int kind, int iters, int blocks, int threads, uint32_t* d_sink) {
   if (kind == 0) k_probe_imad<<<blocks, threads, 0, st>>>(iters, d_sink);
+  else if (kind == 2) k_probe_montmul3<<<blocks, threads, 0, st>>>(iters, d_sink);
   else k_probe_montmul<<<blocks, threads, 0, st>>>(iters, d_sink);
   return 1;
 }
