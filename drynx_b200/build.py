@@ -20,7 +20,7 @@ NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC',
               '-Xptxas', '-v'] + (['-DDRX_DEBUG_RP'] if os.environ.get('DRX_DEBUG_RP') else []) + \
     [f for f in os.environ.get('DRX_NVCC_EXTRA', '').split() if f]
-GPU_SOURCES = ['kernels_g1.cu', 'kernels_rp.cu', 'kernels_rp_ucode.cu', 'kernels_rp_ucode8.cu', 'kernels_ed.cu', 'capi.cu']
+GPU_SOURCES = ['kernels_g1.cu', 'kernels_rp.cu', 'kernels_rp_ucode.cu', 'kernels_rp_ucode_s4.cu', 'kernels_rp_ucode_s8.cu', 'kernels_ed.cu', 'capi.cu']
 
 
 def _newer(target, sources):
@@ -55,7 +55,7 @@ def build_gpu(force=False):
         o = os.path.join(objdir, src.replace('.cu', '.o'))
         if force or _newer(o, [s] + hdrs):
             jobs.append((NVCC_FLAGS and [NVCC] + NVCC_FLAGS + ['-I', CSRC, '-c', s, '-o', o], o + '.log'))
-    with ThreadPoolExecutor(max_workers=4) as ex:
+    with ThreadPoolExecutor(max_workers=8) as ex:
         list(ex.map(lambda j: _run(*j), jobs))
     objs = [os.path.join(objdir, s.replace('.cu', '.o')) for s in GPU_SOURCES]
     if force or jobs or _newer(GPU_SO, objs):

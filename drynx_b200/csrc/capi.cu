@@ -137,14 +137,15 @@ struct RpSetHost {
 
 struct drx_ctx {
   int device = 0;
-  cudaStream_t own_stream = nullptr, stream = nullptr, side_stream = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;  // fork/join of the side stream (independent small kernels)
+  cudaStream_t own_stream = nullptr, stream = nullptr, side_stream = nullptr, side_stream2 = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr;  // fork/join of the side streams (independent small kernels)
   std::mutex mu;
   uint64_t launches = 0;
   bool have_pub = false, have_dlog = false, have_target = false;
   int opt_verify_path = 0;  // drx_set_option "rp_verify_path"
   int opt_create_path = 0;  // drx_set_option "rp_create_path": 0 = by batch size, 1 = never the lane-cooperative kernel
   int opt_ucode_lanes = 0;  // drx_set_option "rp_ucode_lanes": 0 = by batch size, 4 or 8
+  UcTune uc_tune;           // drx_set_option "rp_ucode_mode" / "rp_ucode_resident" / "rp_ucode_nseg"
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
       sets_dev, sink, tabQ, target_aff;  // tabQ: comb table of the key-switching target key
   Arena arena;
@@ -257,6 +258,8 @@ int drx_init(drx_ctx** out, int device, const uint8_t* g1_base, const uint8_t* g
   if (e != cudaSuccess) { delete c; return fail((int)e, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
   c->stream = c->own_stream;
   if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&c->side_stream2, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_join2, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
     drx_free(c);
@@ -271,7 +274,7 @@ int drx_init(drx_ctx** out, int device, const uint8_t* g1_base, const uint8_t* g
     return cleanup(rc);
   cudaMemcpyAsync(c->baseB_wire.p, g1_base ? g1_base : kDefaultG1, 64, cudaMemcpyHostToDevice, c->stream);
   cudaMemcpyAsync(c->g2_wire.p, g2_base ? g2_base : kDefaultG2, 128, cudaMemcpyHostToDevice, c->stream);
-  cudaMemsetAsync(c->bad.p, 0, sizeof(int), c->stream);
+  cudaMemsetAsync(c->bad.p, 0, 256, c->stream);  // word 0: malformed-input counter; word 16: lane-group pairing error word
   c->launches += launch_g1_from_wire(c->stream, 1, (const uint8_t*)c->baseB_wire.p, c->baseB_aff.p, (int*)c->bad.p);
   c->launches += launch_g2_from_wire(c->stream, 1, (const uint8_t*)c->g2_wire.p, c->g2_aff.p, (int*)c->bad.p);
   c->launches += launch_comb_table_g1(c->stream, 1, c->baseB_aff.p, c->tabB.p);
@@ -304,6 +307,8 @@ void drx_free(drx_ctx* c) {
   }
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   if (c->side_stream) cudaStreamDestroy(c->side_stream);
+  if (c->side_stream2) cudaStreamDestroy(c->side_stream2);
+  if (c->ev_join2) cudaEventDestroy(c->ev_join2);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
   delete c;
@@ -315,11 +320,22 @@ int drx_set_stream(drx_ctx* c, void* cuda_stream) {
   c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
   return 0;
 }
+// Reads and clears the word a task-queue launch of the lane-group pairing raises when one of its warps gave up
+// waiting for a predecessor task (ucode_common.cuh): the verification results of that call are not valid then.
+static int take_pairing_error(drx_ctx* c) {
+  unsigned int err = 0;
+  unsigned int* d_err = (unsigned int*)c->bad.p + 16;
+  CU(cudaMemcpyAsync(&err, d_err, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  if (!err) return 0;
+  CU(cudaMemsetAsync(d_err, 0, sizeof(err), c->stream));
+  return fail(-5, "range-proof verification: the pairing kernel abandoned a wait on the device (results invalid; retry the call)");
+}
 int drx_synchronize(drx_ctx* c) {
   if (!c) return fail(-1, "null context");
   Guard g(c);
   CU(cudaStreamSynchronize(c->stream));
-  return 0;
+  return take_pairing_error(c);
 }
 uint64_t drx_launch_count(const drx_ctx* c) { return c ? c->launches : 0; }
 
@@ -339,6 +355,21 @@ int drx_set_option(drx_ctx* c, const char* name, int value) {
   if (!strcmp(name, "rp_ucode_lanes")) {
     if (value != 0 && value != 4 && value != 8) return fail(-1, "rp_ucode_lanes must be 0 (auto), 4 or 8");
     c->opt_ucode_lanes = value;
+    return 0;
+  }
+  if (!strcmp(name, "rp_ucode_mode")) {
+    if (value < 0 || value > 2) return fail(-1, "rp_ucode_mode must be 0 (auto), 1 (static launch) or 2 (task queue)");
+    c->uc_tune.mode = value;
+    return 0;
+  }
+  if (!strcmp(name, "rp_ucode_resident")) {
+    if (value < 0 || value > 32) return fail(-1, "rp_ucode_resident must be 0 (auto) .. 32 blocks per SM");
+    c->uc_tune.resident = value;
+    return 0;
+  }
+  if (!strcmp(name, "rp_ucode_nseg")) {
+    if (value < 0 || value > 1024) return fail(-1, "rp_ucode_nseg must be 0 (auto) .. 1024");
+    c->uc_tune.nseg = value;
     return 0;
   }
   return fail(-1, "unknown option %s", name);

@@ -3,11 +3,26 @@
 // :504-565 (RangeProofVerification) of the reference, and the kyber pairing/bn256 calls they make.
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include "rp_device.cuh"
 
 namespace drx {
 
 static inline int grid_for(size_t n, int threads) { return (int)((n + threads - 1) / threads); }
+
+// Kernels that run beside the lane-group pairing ask for the shared-memory-heavy L1 split (they use no shared memory
+// themselves): an SM they reach first then still has room for pairing blocks. Per device, once (a hint, errors ignored).
+template <class K>
+static void prefer_shared_carveout(K kernel, bool (&done)[64]) {
+  static std::mutex mu;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return;
+  std::lock_guard<std::mutex> lk(mu);
+  if (done[dev]) return;
+  if (cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared) != cudaSuccess)
+    cudaGetLastError();
+  done[dev] = true;
+}
 
 
 // ------------------------------------------------------------------ set-up
@@ -15,7 +30,7 @@ __global__ void k_g2_from_wire(size_t n, const uint32_t* __restrict__ wire, G2Af
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   G2Aff p;
-  if (!g2_from_wire(p, wire + 32 * i)) atomicAdd(bad, 1);
+  if (!g2_from_wire_checked(p, wire + 32 * i)) atomicAdd(bad, 1);
   aff[i] = p;
 }
 int launch_g2_from_wire(cudaStream_t st, size_t n, const uint8_t* d_wire, void* d_aff, int* d_bad) {
@@ -97,7 +112,7 @@ k_pair_wire(size_t n, const uint32_t* __restrict__ g1, const uint32_t* __restric
   G1Aff P;
   G2Aff Q;
   int nbad = !g1_from_wire(P, g1 + 16 * i);
-  nbad += !g2_from_wire(Q, g2 + 32 * i);
+  nbad += !g2_from_wire_checked(Q, g2 + 32 * i);
   if (nbad) atomicAdd(bad, nbad);
   Fp12 e;
   pairing(e, P, Q);
@@ -114,7 +129,7 @@ k_g2_mul(size_t n, const uint32_t* __restrict__ k, const uint32_t* __restrict__ 
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   G2Aff p;
-  if (!g2_from_wire(p, pt + 32 * i)) atomicAdd(bad, 1);
+  if (!g2_from_wire_checked(p, pt + 32 * i)) atomicAdd(bad, 1);
   const G2Jac r = window_mul(jac_from_aff(p), sc_from_wire(k + 8 * i));
   g2_to_wire(out + 32 * i, jac_to_aff(r));
 }
@@ -392,6 +407,8 @@ int launch_rp_verify_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_se
   if (!b.n) return 0;
   // one warp per block: these kernels run next to the lane-group pairing, whose pace is set by its most loaded SM;
   // small blocks spread the extra warps over many SMs instead of stacking four on a few
+  static bool carveout_set[64] = {false};
+  prefer_shared_carveout(k_rp_verify_hdr, carveout_set);
   k_rp_verify_hdr<<<grid_for(b.n, 32), 32, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const G1Aff*)d_tabP,
                                                      (const uint32_t*)d_proofs, d_flags);
   return 1;
@@ -434,6 +451,8 @@ k_rp_verify_gt(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __rest
 int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                         const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch) {
   if (!b.items) return 0;
+  static bool carveout_set[64] = {false};
+  prefer_shared_carveout(k_rp_verify_gt, carveout_set);
   k_rp_verify_gt<<<grid_for(b.items, 32), 32, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const Fp12*)d_tabGtB,
                                                       (const uint32_t*)d_proofs, d_flags, (GtPair*)d_scratch);
   return 1;

@@ -14,11 +14,10 @@ constexpr size_t kG1AffBytes = 64, kG2AffBytes = 128, kGtBytes = 384, kG1JacByte
 constexpr int64_t kMaxHomomorphicInt = 100000;  // libunlynx.MaxHomomorphicInt
 constexpr uint32_t kDlogCap = 1u << 18;         // open-addressing slots for 100001 keys
 constexpr int kAggMaxSlices = 64;
-constexpr size_t kUcodeAutoMaxItems = 42000;  // batches up to this many pairing checks take the lane-group path (measured crossover with four persistent blocks per SM: 3,000 proofs x 12 checks 25.4 vs 27.5 ms, 4,096 proofs 33.7 vs 31.6 ms)
 constexpr size_t kEncryptLanesMaxItems = 16384; // encryptions up to this many use eight lanes each (latency)
 constexpr size_t kCreateLanesMaxItems = 800;   // creation items up to this many: lane-cooperative kernel (8 / 16 lanes per item)
 constexpr size_t kCreateFineMaxItems = 36000; // creation items up to this many are split twelve ways (latency)
-constexpr size_t kUcodeG8MaxItems = 2400;     // ... and up to this many use eight lanes per check instead of four
+constexpr size_t kUcodeG8MaxItems = 1000;      // pairing checks up to this many use eight program lanes per check instead of four (measured, pairing kernel: 480 checks 2.00 against 2.56 ms, 1,200 checks 2.61 against 2.60)
 
 // ---- kernels_g1.cu
 // wire bytes -> Montgomery affine (returns malformed count in *d_bad)
@@ -123,8 +122,17 @@ int launch_rp_verify_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_
 size_t rp_ucode_prep_bytes(size_t items);
 int launch_rp_verify_prep(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                           const uint8_t* d_proofs, uint32_t* d_flags, void* d_prep);
-int launch_pair_ucode_g4(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch);
-int launch_pair_ucode_g8(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch);
+// four / eight program lanes of two threads each per pairing check (kernels_rp_ucode_s4.cu / _s8.cu);
+// d_err: one device word; bit 0 is raised if a dynamic launch gave up waiting (see ucode_common.cuh)
+struct UcTune {
+  int mode = 0;      // 0 = by batch size, 1 = static launch, 2 = dynamic (task queue) launch
+  int resident = 0;  // dynamic launch: persistent blocks per SM (0 = as many as fit)
+  int nseg = 0;      // dynamic launch: program segments (0 = 32)
+};
+int launch_pair_ucode_s4(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch, unsigned int* d_err,
+                         const UcTune& tune);
+int launch_pair_ucode_s8(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch, unsigned int* d_err,
+                         const UcTune& tune);
 int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                         const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 int launch_rp_verify_finish(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_scratch,

@@ -68,8 +68,16 @@ DRX_NI void line_add(Fp2& a, Fp2& b, Fp2& c, TwistJ& r, const G2Aff& p, const G1
   r = o;
 }
 
-// Miller function value for affine, finite P in G1 and Q in G2.
-DRX_NI void miller_loop(Fp12& f, const G1Aff& P, const G2Aff& Q) {
+// Miller function value for affine, finite P in G1 and Q on the twist. Returns whether Q lies in G2 (the order-n
+// subgroup), which the loop decides on the side: after the last two line steps r = [6u+2]Q + pi(Q) - pi^2(Q), and
+// r = -pi^3(Q) exactly when Q has order n. (6u+2 + p - p^2 + p^3 = 0 mod n is the relation the optimal ate pairing
+// rests on, so the equality holds on G2; conversely the resultant of X^3 - X^2 + X + 6u+2 with the characteristic
+// polynomial of pi shares only the factor n with #E'(Fp2) = n (2p - n) on this curve -- checked with integers in
+// tests/test_oracle.py -- so any twist point passing the test has order n.) The line formulas are incomplete, but
+// only a point outside G2 can reach one of their exceptional cases, and those leave z = 0 for good, which fails
+// the test as well. kyber's UnmarshalBinary rejects such points ([n]Q != O in twistPoint.IsOnCurve), so
+// lib/range/range_proof.go:225-236 never hands one to the pairing.
+DRX_NI bool miller_loop(Fp12& f, const G1Aff& P, const G2Aff& Q) {
   f = fp12_one();
   TwistJ r;
   r.x = Q.x;
@@ -104,6 +112,33 @@ DRX_NI void miller_loop(Fp12& f, const G1Aff& P, const G2Aff& Q) {
   r2 = fp2_sqr(mq2.y);
   line_add(a, b, c, r, mq2, P, r2);
   fp12_mul_line(f, f, c, b, a);
+  // r == -pi^3(Q), compared projectively (r.t = r.z^2)
+  const Fp2 x3 = fp2_mul(fp2_mul(fp2_conj(Q.x), K_FROB3_2()), r.t);
+  const Fp2 y3 = fp2_mul(fp2_mul(fp2_conj(Q.y), K_FROB3_3()), fp2_mul(r.t, r.z));
+  return fp2_eq(r.x, x3) & fp2_eq(r.y, fp2_neg(y3)) & !fp2_is_zero(r.z);
+}
+
+// Membership in G2 alone (set-up and diagnostic paths; verification gets it from its Miller loop): the same relation
+// [6u+2]Q + pi(Q) - pi^2(Q) + pi^3(Q) = O, evaluated with the complete group law.
+DRX_NI bool g2_in_subgroup(const G2Aff& Q) {
+  if (aff_is_inf(Q)) return true;
+  const G2Aff mQ = aff_neg(Q);
+  G2Jac r = jac_from_aff(Q);
+  for (int i = DRX_ATE_NAF_LEN - 1; i > 0; i--) {
+    r = jac_dbl(r);
+    const int d = ate_naf(i - 1);
+    if (d == 1) r = jac_add_aff(r, Q);
+    else if (d == -1) r = jac_add_aff(r, mQ);
+  }
+  G2Aff q1, mq2, q3;
+  q1.x = fp2_mul(fp2_conj(Q.x), K_XI_P_1_3());
+  q1.y = fp2_mul(fp2_conj(Q.y), K_XI_P_1_2());
+  mq2.x = fp2_mul_fp(Q.x, K_XI_P2_1_3());
+  mq2.y = Q.y;
+  q3.x = fp2_mul(fp2_conj(Q.x), K_FROB3_2());
+  q3.y = fp2_mul(fp2_conj(Q.y), K_FROB3_3());
+  r = jac_add_aff(jac_add_aff(jac_add_aff(r, q1), mq2), q3);
+  return jac_is_inf(r);
 }
 
 // a^u for a in the cyclotomic subgroup (u = 6518589491078791937): signed-digit (NAF, weight 23 instead of 30)
@@ -166,15 +201,24 @@ DRX_NI void final_exp(Fp12& out, const Fp12& in) {
   fp12_mul(out, t0, t1);
 }
 
-// e(P, Q); either argument at infinity gives 1 (kyber optimalAte)
-DRX_NI void pairing(Fp12& out, const G1Aff& P, const G2Aff& Q) {
-  if (aff_is_inf(P) | aff_is_inf(Q)) {
+// e(P, Q); either argument at infinity gives 1 (kyber optimalAte). Returns false, and leaves out = 1, when Q is a
+// twist point outside G2 (no such point can come out of kyber's UnmarshalBinary, see miller_loop).
+DRX_NI bool pairing(Fp12& out, const G1Aff& P, const G2Aff& Q) {
+  if (aff_is_inf(Q)) {
     out = fp12_one();
-    return;
+    return true;
+  }
+  if (aff_is_inf(P)) {
+    out = fp12_one();
+    return g2_in_subgroup(Q);
   }
   Fp12 f;
-  miller_loop(f, P, Q);
+  if (!miller_loop(f, P, Q)) {
+    out = fp12_one();
+    return false;
+  }
   final_exp(out, f);
+  return true;
 }
 
 // Fixed-base GT exponentiation: table[w * 255 + d - 1] = g^(d * 2^(8w)).

@@ -347,7 +347,7 @@ __device__ __forceinline__ void rp_verify_role(const RpBatch& b, const RpSetDev*
     const Scalar zphi = sc_from_wire(in + pv.zphi_off(j));
     G1Jac P1 = comb_mul((const G1Aff*)set.tabY + (size_t)i * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES), c);
     P1 = jac_add(P1, comb_mul(tabB, sc_neg(zphi)));
-    pairing(scratch[t].a, jac_to_aff(P1), V);
+    if (!pairing(scratch[t].a, jac_to_aff(P1), V)) atomicAnd(&flags[p], 0u);  // V_ij outside G2: malformed for kyber
   } else {
     Fp12 A, g;
     if (!gt_from_wire(A, in + pv.a_off(i, j))) {

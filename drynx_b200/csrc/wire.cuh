@@ -54,6 +54,14 @@ DRX_HD bool g2_from_wire(G2Aff& out, const uint32_t* w) {
   if (!ok) { out.x = fp2_zero(); out.y = fp2_zero(); }
   return ok;
 }
+// g2_from_wire plus membership in the order-n subgroup: what kyber's UnmarshalBinary accepts. For the set-up and
+// diagnostic paths; range-proof verification takes the verdict from its Miller loop instead (pairing.cuh).
+DRX_HD bool g2_from_wire_checked(G2Aff& out, const uint32_t* w) {
+  bool ok = g2_from_wire(out, w);
+  ok = ok && g2_in_subgroup(out);
+  if (!ok) { out.x = fp2_zero(); out.y = fp2_zero(); }
+  return ok;
+}
 DRX_HD void g2_to_wire(uint32_t* w, const G2Aff& p) {
   fp2_to_wire(w, p.x);
   fp2_to_wire(w + 16, p.y);

@@ -198,6 +198,56 @@ def g2_mul(k, P):
     return R
 
 
+def g2_mul_raw(k, P):
+    """[k]P without reducing k mod n (P may lie outside the order-n subgroup)."""
+    R = None
+    while k:
+        if k & 1:
+            R = g2_add(R, P)
+        P = g2_add(P, P)
+        k >>= 1
+    return R
+
+
+def g2_in_subgroup(Q):
+    """Membership in G2 = E'(Fp2)[n], by definition: [n]Q = O. kyber's twistPoint.IsOnCurve (pairing/bn256 twist.go,
+    recalled; not in /root/reference) multiplies by Order after the curve equation and rejects otherwise, so
+    UnmarshalBinary fails for a twist point outside the subgroup and lib/range/range_proof.go:225-236 aborts."""
+    return g2_mul_raw(n, Q) is None
+
+
+def f2sqrt(a):
+    """A square root in Fp2 (p = 3 mod 4), or None."""
+    if a == F2_ZERO:
+        return a
+    s = pow((a[0] * a[0] + a[1] * a[1]) % p, (p + 1) // 4, p)
+    if (s * s - a[0] * a[0] - a[1] * a[1]) % p:
+        return None
+    for t in (s, -s):
+        h = (a[0] + t) * pow(2, -1, p) % p
+        x0 = pow(h, (p + 1) // 4, p)
+        if (x0 * x0 - h) % p == 0 and x0:
+            r = (x0, a[1] * pow(2 * x0, -1, p) % p)
+            if f2mul(r, r) == a:
+                return r
+    return None
+
+
+def g2_twist_point(seed):
+    """A deterministic point on the twist curve E'(Fp2) (almost surely OUTSIDE the order-n subgroup: #E' = n (2p - n))."""
+    k = 0
+    while True:
+        h = hashlib.sha256(b'twist point %d %d' % (seed, k)).digest()
+        x = (int.from_bytes(h, 'big') % p, int.from_bytes(hashlib.sha256(h).digest(), 'big') % p)
+        y = f2sqrt(f2add(f2mul(f2mul(x, x), x), B2))
+        if y is not None:
+            return (x, y)
+        k += 1
+
+
+TWIST_COFACTOR = 2 * p - n   # = 13 * 7369 * ...: points of small order exist on the twist
+
+
 def g2_to_bytes(Q):
     if Q is None:
         return bytes(128)
@@ -210,7 +260,7 @@ def g2_from_bytes(b):
     if not any(v):
         return None
     Q = ((v[1], v[0]), (v[3], v[2]))
-    if max(v) >= p or not g2_on_curve(Q):
+    if max(v) >= p or not g2_on_curve(Q) or not g2_in_subgroup(Q):
         raise ValueError("bn256.G2: malformed point")
     return Q
 

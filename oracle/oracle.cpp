@@ -524,16 +524,10 @@ struct twistPoint {
   gfP2 x, y, z, t;
   bool IsInfinity() const { return z.IsZero(); }
   void SetInfinity() { x.SetZero(); y.SetOne(); z.SetZero(); t.SetZero(); }
-  bool IsOnCurve() {
-    MakeAffine();
-    if (IsInfinity()) return true;
-    gfP2 y2, x3;
-    y2.Square(y);
-    x3.Square(x);
-    x3.Mul(x3, x);
-    x3.Add(x3, twistB);
-    return y2 == x3;
-  }
+  // kyber pairing/bn256 twist.go IsOnCurve (recalled; the module is not in /root/reference): the curve equation, then
+  // `cneg.Mul(c, Order); return cneg.z.IsZero()` -- a twist point outside the order-n subgroup is NOT "on the curve"
+  // for kyber, so UnmarshalBinary fails on it and lib/range/range_proof.go:225-236 aborts. Defined after Mul below.
+  bool IsOnCurve();
   void Double(const twistPoint& a) {
     gfP2 A, B, C, t, t2, d, e, f, nx, ny, nz;
     A.Square(a.x);
@@ -630,6 +624,21 @@ struct twistPoint {
   }
   void Neg(const twistPoint& a) { x = a.x; y.Neg(a.y); z = a.z; t.SetZero(); }
 };
+
+bool twistPoint::IsOnCurve() {
+  MakeAffine();
+  if (IsInfinity()) return true;
+  gfP2 y2, x3;
+  y2.Square(y);
+  x3.Square(x);
+  x3.Mul(x3, x);
+  x3.Add(x3, twistB);
+  if (!(y2 == x3)) return false;
+  static const u64 order[4] = {0x1a2ef45b57ac7261ULL, 0x2e8d8e12f82b3924ULL, 0xaa6fecb86184dc21ULL, 0x8fb501e34aa387f9ULL};
+  twistPoint cneg;
+  cneg.Mul(*this, order);
+  return cneg.z.IsZero();
+}
 
 // ------------------------------------------------------------------ optimal ate (kyber optate.go)
 static void lineFunctionAdd(const twistPoint& r, const twistPoint& p, const curvePoint& q, const gfP2& r2, gfP2& a,

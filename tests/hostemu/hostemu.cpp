@@ -155,6 +155,17 @@ int emu_pair(const uint8_t* g1, const uint8_t* g2, uint8_t* gt384) {
   return 0;
 }
 
+// G2 membership two ways: bit 0 = the stand-alone test (complete group law), bit 1 = the verdict the Miller loop
+// produces on the side (incomplete line formulas). -1: not even on the twist.
+int emu_g2_membership(const uint8_t* g1, const uint8_t* g2) {
+  uint32_t aw[16], bw[32];
+  load_words(aw, g1, 64); load_words(bw, g2, 128);
+  G1Aff p; G2Aff q;
+  if (!g1_from_wire(p, aw) || !g2_from_wire(q, bw)) return -1;
+  Fp12 f;
+  return (g2_in_subgroup(q) ? 1 : 0) | (miller_loop(f, p, q) ? 2 : 0);
+}
+
 // checks internal identities that have no wire-level witness: cyclotomic squaring == generic squaring on a
 // pairing value, Frobenius maps compose, inverse. Returns a bitmask of failures.
 int emu_tower_selfcheck(const uint8_t* gt384) {

@@ -189,13 +189,23 @@ def test_config2_shape_create_verify_properties(backend, oracle, rng):
     assert [i for i in range(n) if not ok[i]] == flipped
 
 
-@pytest.mark.parametrize('path,lanes', [(1, 0), (2, 4), (2, 8)])
-def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes):
-    """rp_verify_path 1 (one thread per pairing check) and 2 (cooperative lane groups running the generated
-    micro-program) must give the oracle's accept / reject bits on valid, tampered and degenerate proofs."""
+def _outside_g2(seed):
+    """Twist points outside the order-n subgroup: generic (composite order), cofactor order, order 13, 13 * generic."""
+    T = R.g2_twist_point(seed)
+    pts = [T, R.g2_mul_raw(R.n, T), R.g2_mul_raw(R.n * R.TWIST_COFACTOR // 13, T), R.g2_mul_raw(13, T)]
+    assert all(Q is not None and R.g2_on_curve(Q) and not R.g2_in_subgroup(Q) for Q in pts)
+    return [R.g2_to_bytes(Q) for Q in pts]
+
+
+@pytest.mark.parametrize('path,lanes,mode', [(1, 0, 0), (2, 4, 1), (2, 8, 1), (2, 4, 2), (2, 8, 2)])
+def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes, mode):
+    """rp_verify_path 1 (one thread per pairing check) and 2 (lane groups running the generated micro-program, four or
+    eight program lanes, static or task-queue launch) must give the oracle's accept / reject bits on valid, tampered
+    and degenerate proofs -- including V_ij that lie on the twist but outside G2, which kyber's UnmarshalBinary refuses
+    (lib/range/range_proof.go:225-236 aborts there; here the proof is rejected)."""
     ns, u, l = 3, 16, 2
     sk, P, Y, A = _setup(backend, oracle, rng, ns, u, set_id=60)
-    secrets = [0, 1, 77, 255, 200, 13, 99, 254]
+    secrets = [0, 1, 77, 255, 200, 13, 99, 254, 5, 6, 7, 8, 9]
     rs, cts, rnd = _make(backend, oracle, rng, P, ns, u, l, secrets)
     n = len(secrets)
     proofs, off = backend.create_range_proofs([60] * n, {60: ns}, {60: u}, [l] * n, secrets, rs, cts, rnd)
@@ -208,15 +218,43 @@ def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes):
     bad[4 * size + blk + 3] ^= 1                              # V_00 leaves the curve
     bad[5 * size + blk:5 * size + blk + 128] = bytes(128)     # V_00 = infinity
     bad[6 * size + blk + 512 * l + 9] ^= 1                    # Zv_00
+    outside = _outside_g2(60 + path)
+    for k, Q in enumerate(outside):                           # V_00, V_11, V_20, V_01 outside G2
+        i, j = [(0, 0), (1, 1), (2, 0), (0, 1)][k]
+        pos = (8 + k) * size + blk + i * 544 * l + 128 * j
+        bad[pos:pos + 128] = Q
     want = oracle.rp_verify(ns, u, l, Y, P, bytes(bad), off, threads=8)
     backend.set_option('rp_verify_path', path)
     backend.set_option('rp_ucode_lanes', lanes)
+    backend.set_option('rp_ucode_mode', mode)
     try:
         ok = backend.verify_range_proofs([60] * n, [l] * n, bytes(bad), off)
     finally:
         backend.set_option('rp_verify_path', 0)
         backend.set_option('rp_ucode_lanes', 0)
-    assert list(ok) == list(want) == [1, 0, 0, 0, 0, 0, 0, 1]
+        backend.set_option('rp_ucode_mode', 0)
+    assert list(ok) == list(want) == [1, 0, 0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1]
+
+
+def test_g2_inputs_outside_the_subgroup_are_malformed(backend, oracle, rng):
+    """Everywhere a G2 point crosses the ABI it must be a point kyber can unmarshal: on the twist AND of order n."""
+    from drynx_b200._lib import DrynxGpuError
+    one = (1).to_bytes(32, 'big')
+    g1 = R.g1_to_bytes(R.G1_GEN)
+    good = R.g2_to_bytes(R.g2_mul(rng.scalar(), R.G2_GEN))
+    assert backend.g2_mul(one, good).tobytes() == good
+    for Q in _outside_g2(3):
+        with pytest.raises(DrynxGpuError):
+            backend.g2_mul(one, Q)
+        with pytest.raises(DrynxGpuError):
+            backend.pair(g1, Q)
+    ns, u = 2, 4
+    Y, A = oracle.make_sigs([rng.scalar() for _ in range(ns)], u)
+    Ab = bytearray(A)
+    Ab[128 * 5:128 * 6] = _outside_g2(4)[0]
+    with pytest.raises(DrynxGpuError):
+        backend.set_signatures(63, ns, u, Y, bytes(Ab))
+    backend.set_signatures(63, ns, u, Y, A)
 
 
 def test_creation_kernels_agree(backend, oracle, rng):
@@ -242,10 +280,9 @@ def test_creation_kernels_agree(backend, oracle, rng):
 
 @pytest.mark.parametrize('n', [600, 700])
 def test_dynamic_segment_kernel(backend, oracle, rng, n):
-    """600 proofs x 12 checks = 7,200 pairing checks (900 warp tasks: three persistent blocks per SM) and 700 x 12 =
-    8,400 (1,050 warp tasks: four): more than three lane-group blocks per SM, so verification runs the dynamic kernel
-    (32 program segments dealt from a queue, slot images handed over through global memory). Every proof verifies, the
-    tampered ones (one per kind of field) are rejected, and a sample is checked against the oracle."""
+    """600 and 700 proofs x 12 checks through the task-queue launch of the lane-group kernel (rp_ucode_mode 2: 32 program
+    segments dealt from a queue to persistent blocks, slot images handed over through global memory). Every proof
+    verifies, the tampered ones (one per kind of field) are rejected, and a sample is checked against the oracle."""
     ns, u, l = 3, 16, 4
     sk, P, Y, A = _setup(backend, oracle, rng, ns, u, set_id=62)
     g = np.random.default_rng(62)
@@ -260,12 +297,14 @@ def test_dynamic_segment_kernel(backend, oracle, rng, n):
         bad[p_ * size + o_] ^= 1
     backend.set_option('rp_verify_path', 2)
     backend.set_option('rp_ucode_lanes', 4)
+    backend.set_option('rp_ucode_mode', 2)
     try:
         ok = backend.verify_range_proofs([62] * n, [l] * n, bytes(bad), off)
         ok_clean = backend.verify_range_proofs([62] * n, [l] * n, proofs, off)
     finally:
         backend.set_option('rp_verify_path', 0)
         backend.set_option('rp_ucode_lanes', 0)
+        backend.set_option('rp_ucode_mode', 0)
     assert list(ok_clean) == [1] * n
     assert [i for i in range(n) if not ok[i]] == sorted(flipped)
     idx = [5, 6, 7, 8, 122, 123, 124, 450, 451, 598, 599]
@@ -335,9 +374,10 @@ def test_ragged_batch_through_every_path(backend, oracle, rng):
         assert int(want[0]) == results[2][i]
 
 
-def test_config5_ten_thousand_proofs(backend, rng):
-    """Config 5 at 10^4 proofs (u=16, l=4, ns=3: 120,000 pairing checks, 69 MB of proofs, the one-thread-per-check
-    path): every created proof verifies, and exactly the 1 % that get one byte flipped are rejected."""
+def test_config5_ten_thousand_proofs(backend, oracle, rng):
+    """Config 5 at 10^4 proofs (u=16, l=4, ns=3: 120,000 pairing checks, 69 MB of proofs): every created proof
+    verifies, exactly the 1 % that get one byte flipped are rejected, on the automatic path and on both forced paths,
+    and a sample of 128 proofs (every tampered one among the first 4,000 plus their neighbours) is judged by the oracle."""
     ns, u, l, n = 3, 16, 4, 10000
     sk = rng.scalar()
     P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
@@ -365,5 +405,20 @@ def test_config5_ten_thousand_proofs(backend, rng):
     for i in flipped:
         pos = [170, 300, size - 40, 256 + 32 * l + 200][i % 4]
         bad[i * size + pos] ^= 1
-    ok = backend.verify_range_proofs([70] * n, [l] * n, bad, off)
-    assert [i for i in range(n) if not ok[i]] == flipped
+    results = {}
+    for path in (0, 1, 2):
+        backend.set_option('rp_verify_path', path)
+        try:
+            results[path] = backend.verify_range_proofs([70] * n, [l] * n, bad, off)
+        finally:
+            backend.set_option('rp_verify_path', 0)
+        assert [i for i in range(n) if not results[path][i]] == flipped, path
+    sample = []
+    for i in flipped:
+        if i < 4000:
+            sample += [i, i + 1]
+    sample = sorted(set(sample + list(range(0, 128))))[:128]
+    sub = b''.join(bad[i * size:(i + 1) * size].tobytes() for i in sample)
+    want = oracle.rp_verify(ns, u, l, Y.tobytes(), P, sub, np.arange(len(sample) + 1, dtype=np.uint64) * size, threads=16)
+    assert [int(results[0][i]) for i in sample] == list(want)
+    assert 0 < sum(want) < len(sample)

@@ -119,3 +119,16 @@ def test_pairing_tower_and_gt_pow(emu, oracle, rng):
     assert o2.raw == R.f12_to_bytes(R.f12pow(R.f12_from_bytes(out.raw), k))
     bad = bytes(63) + b'\x05' + bytes(63) + b'\x07'
     assert emu.emu_pair(bad[:64], Q, out) == -1
+
+
+def test_g2_membership_verdicts(emu, rng):
+    """Device headers on the CPU: both forms of the G2 membership test accept points of G2 and reject twist points
+    outside it (composite order, cofactor order, order 13), like kyber's [n]Q == O in twistPoint.IsOnCurve."""
+    import bn256_ref as R
+    P = R.g1_to_bytes(R.g1_mul(rng.scalar(), R.G1_GEN))
+    for k in (1, 2, rng.scalar()):
+        assert emu.emu_g2_membership(P, R.g2_to_bytes(R.g2_mul(k, R.G2_GEN))) == 3
+    T = R.g2_twist_point(7)
+    for Q in (T, R.g2_mul_raw(R.n, T), R.g2_mul_raw(R.n * R.TWIST_COFACTOR // 13, T), R.g2_mul_raw(13, T)):
+        assert Q is not None and R.g2_on_curve(Q) and not R.g2_in_subgroup(Q)
+        assert emu.emu_g2_membership(P, R.g2_to_bytes(Q)) == 0

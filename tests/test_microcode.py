@@ -23,11 +23,13 @@ def test_scheduled_program_computes_the_pairing_and_matches_committed_tables(rng
     G = int(re.search(r'#define UC_G (\d+)', inc).group(1))
     nslots = int(re.search(r'#define UC_NSLOTS (\d+)', inc).group(1))
     nphases = int(re.search(r'#define UC_NPHASES (\d+)', inc).group(1))
+    gen_slots = int(re.search(r'#define UC_GEN_SLOTS (\d+)', inc).group(1))
+    gen_window = int(re.search(r'#define UC_GEN_WINDOW (\d+)', inc).group(1))
     g = gen.Graph()
     gen.build_pairing(g)
     gen.fix_user_counts(g)
     gen.fuse(g)
-    phases, slot_of, used = gen.schedule(g, G, nslots, 60)
+    phases, slot_of, used = gen.schedule(g, G, gen_slots, gen_window)
     assert len(phases) == nphases and (used | 1) == nslots
     # no phase writes a slot that another lane of the same phase reads (the kernel only synchronises between phases)
     for op, lanes in phases:
@@ -38,9 +40,16 @@ def test_scheduled_program_computes_the_pairing_and_matches_committed_tables(rng
                     assert slot_of[n.id] not in [slot_of[x.id] for x in (m.a, m.b, m.c) if x is not None]
     a, b = rng.scalar(), rng.scalar()
     P, Q = R.g1_mul(a, R.G1_GEN), R.g2_mul(b, R.G2_GEN)
-    out = gen.run_program(g, phases, slot_of, nslots, {'P': (P[0], P[1]), 'QX': Q[0], 'QY': Q[1], 'ONE': (1, 0), 'ZERO': (0, 0)})
+    run = lambda P_, Q_: gen.run_program(g, phases, slot_of, nslots, {'P': ((-P_[0]) % R.p, P_[1]), 'QX': Q_[0], 'QY': Q_[1]})
+    out = run(P, Q)
     got = [out['E00'], out['E10'], out['E01'], out['E11'], out['E02'], out['E12']]
     assert got == R.pair(P, Q)
+    # the G2 membership verdict the program computes on the side: zero for G2, non-zero for twist points outside it
+    assert out['SG'] == (0, 0)
+    T = R.g2_twist_point(int(a % 1000))
+    for Qo in (T, R.g2_mul_raw(R.n, T), R.g2_mul_raw(R.n * R.TWIST_COFACTOR // 13, T)):
+        assert R.g2_on_curve(Qo) and not R.g2_in_subgroup(Qo)
+        assert run(P, Qo)['SG'] != (0, 0)
     # the committed opcode stream is the one just generated
     committed = [int(x) for x in re.findall(r'\d+', re.search(r'uc_ops\[UC_NPHASES\] = \{(.*?)\};', inc, re.S).group(1))]
     assert committed == [gen.OPC[o] for o, _ in phases]

@@ -286,3 +286,71 @@ def test_shuffle_rerandomize_matches_definition(oracle, rng):
     for i in range(4):
         got, found = oracle.decrypt(sk.to_bytes(32, 'big'), out[i])
         assert list(got) == vals[pi[i]] and all(found)
+
+
+# ---------------------------------------------------------------------------------------------- G2 membership
+def _twist_points_outside_g2(seed):
+    T = R.g2_twist_point(seed)
+    pts = [T, R.g2_mul_raw(R.n, T), R.g2_mul_raw(R.n * R.TWIST_COFACTOR // 13, T), R.g2_mul_raw(13, T)]
+    for Q in pts:
+        assert Q is not None and R.g2_on_curve(Q) and not R.g2_in_subgroup(Q)
+    return pts
+
+
+def test_g2_membership_relation_is_sound_on_this_curve():
+    """The GPU decides membership in G2 by [6u+2]Q + pi(Q) - pi^2(Q) + pi^3(Q) == O instead of kyber's [n]Q == O.
+    Any Q on the twist is killed by the characteristic polynomial chi(X) = X^2 - tX + p of pi; a Q passing the test
+    is also killed by h(X) = X^3 - X^2 + X + 6u+2, hence by the integer Res(h, chi). The order of Q then divides
+    gcd(Res, #E'(Fp2)), and #E'(Fp2) = n (2p - n): if that gcd is n the two tests accept the same points."""
+    from fractions import Fraction
+    from math import gcd
+    u, p, n = R.u, R.p, R.n
+    t = 6 * u * u + 1
+    assert n == p + 1 - t and (p ** 3 - p ** 2 + p + 6 * u + 2) % n == 0
+    h, chi = [1, -1, 1, 6 * u + 2], [1, -t, p]
+    M = [[Fraction(x) for x in row] for row in (h + [0], [0] + h, chi + [0, 0], [0] + chi + [0], [0, 0] + chi)]
+    det = Fraction(1)
+    for i in range(5):
+        piv = next(r for r in range(i, 5) if M[r][i] != 0)
+        if piv != i:
+            M[i], M[piv] = M[piv], M[i]
+            det = -det
+        det *= M[i][i]
+        for r in range(i + 1, 5):
+            f = M[r][i] / M[i][i]
+            M[r] = [x - f * y for x, y in zip(M[r], M[i])]
+    res = abs(int(det))
+    assert det.denominator == 1 and gcd(res, n * (2 * p - n)) == n
+    # and the twist's group order really is n (2p - n): a random twist point is killed by it
+    assert R.g2_mul_raw(n * (2 * p - n), R.g2_twist_point(3)) is None
+
+
+def test_twist_points_outside_g2_are_malformed(oracle):
+    """kyber's twistPoint.IsOnCurve multiplies by Order (recalled), so UnmarshalBinary rejects these: the C++ oracle and
+    the Python definition must both refuse them wherever a G2 point is parsed."""
+    one = (1).to_bytes(32, 'big')
+    out128, out384 = np.zeros(128, np.uint8), np.zeros(384, np.uint8)
+    g1 = R.g1_to_bytes(R.G1_GEN)
+    for Q in _twist_points_outside_g2(11):
+        b = R.g2_to_bytes(Q)
+        with pytest.raises(ValueError):
+            R.g2_from_bytes(b)
+        assert oracle.lib.orc_g2_mul(one, b, out128.ctypes.data) == -1
+        assert oracle.lib.orc_pair(g1, b, out384.ctypes.data) == -1
+    good = R.g2_to_bytes(R.g2_mul(5, R.G2_GEN))
+    assert oracle.lib.orc_g2_mul(one, good, out128.ctypes.data) == 0
+
+
+def test_range_proof_with_v_outside_g2_is_rejected(oracle):
+    """lib/range/range_proof.go:225-236: FromBytes aborts on a V_ij that kyber cannot unmarshal; here the proof is
+    reported invalid. Every other field of the proof is left as the prover made it."""
+    ns, u, l, secret = 2, 4, 2, 9
+    c = _small_case(oracle, 21, ns, u, l, secret)
+    proofs, off = oracle.rp_create(ns, u, l, c['Y'], c['A'], c['P'], [secret], c['r'].to_bytes(32, 'big'), c['ct'], [c['rndb']])
+    assert list(oracle.rp_verify(ns, u, l, c['Y'], c['P'], proofs, off)) == [1]
+    v00 = 256 + 32 * l
+    for Q in _twist_points_outside_g2(5):
+        bad = bytearray(proofs)
+        bad[v00:v00 + 128] = R.g2_to_bytes(Q)
+        assert list(oracle.rp_verify(ns, u, l, c['Y'], c['P'], bytes(bad), off)) == [0]
+        assert R.rp_verify(bytes(bad), u, l, [R.g1_from_bytes(c['Y'][64 * i:64 * i + 64]) for i in range(ns)], c['Pp']) is False

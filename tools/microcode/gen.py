@@ -21,7 +21,7 @@ import bn256_ref as R  # noqa: E402
 
 # ---------------------------------------------------------------------------------------------- symbolic Fp2 DAG
 OPS = ['NOP', 'MUL', 'ADD', 'SUB', 'DBL', 'NEG', 'MULXI', 'CONJ', 'MULC', 'MULFP0', 'MULFP1', 'INV', 'COPY', 'CONJMULC', 'MULFPC',
-       'SUB2', 'AXI', 'X3', 'X4', 'X8', 'CYCM', 'CYCP', 'SQR']
+       'SUB2', 'AXI', 'X3', 'X4', 'X8', 'CYCM', 'CYCP', 'SQR', 'CHK']
 OPC = {n: i for i, n in enumerate(OPS)}
 COST = {'MUL': 10, 'SQR': 7, 'INV': 120, 'MULC': 10, 'CONJMULC': 10, 'MULFP0': 7, 'MULFP1': 7, 'MULFPC': 7}
 
@@ -71,10 +71,17 @@ class Graph:
 
 
 class S:
-    """Symbolic Fp2 value."""
+    """Symbolic Fp2 value. The inputs named ZERO and ONE are folded away wherever an identity applies, so they only
+    cost a slot if some operation really needs them as an operand."""
 
     def __init__(self, g, n):
         self.g, self.n = g, n
+
+    def _is(self, name):
+        return self.n is self.g.inputs.get(name)
+
+    def _const(self, name):
+        return S(self.g, self.g.inputs[name])
 
     def _bin(self, op, o):
         return S(self.g, Node(self.g, op, self.n, o.n))
@@ -82,19 +89,67 @@ class S:
     def _un(self, op, imm=0):
         return S(self.g, Node(self.g, op, self.n, None, imm))
 
-    def __mul__(self, o): return self._bin('MUL', o)
-    def __add__(self, o): return self._bin('ADD', o)
-    def __sub__(self, o): return self._bin('SUB', o)
-    def sqr(self): return self._bin('MUL', self)
-    def dbl(self): return self._bin('ADD', self)            # same opcode as ADD: fuller phases
-    def neg(self): return S(self.g, Node(self.g, 'SUB', self.g.inputs['ZERO'], self.n))
-    def xi(self): return self._un('MULXI')
-    def conj(self): return self._un('CONJ')
+    def __mul__(self, o):
+        if self._is('ZERO') or o._is('ZERO'): return self._const('ZERO')
+        if self._is('ONE'): return o
+        if o._is('ONE'): return self
+        return self._bin('MUL', o)
+
+    def __add__(self, o):
+        if self._is('ZERO'): return o
+        if o._is('ZERO'): return self
+        return self._bin('ADD', o)
+
+    def __sub__(self, o):
+        if o._is('ZERO'): return self
+        if self._is('ZERO'): return o.neg()
+        return self._bin('SUB', o)
+
+    def sqr(self):
+        if self._is('ZERO') or self._is('ONE'): return self
+        return self._bin('MUL', self)
+
+    def dbl(self):
+        if self._is('ZERO'): return self
+        return self._bin('ADD', self)            # same opcode as ADD: fuller phases
+
+    def neg(self):
+        if self._is('ZERO'): return self
+        return self._un('NEG')
+
+    def xi(self):
+        if self._is('ZERO'): return self
+        return self._un('MULXI')
+
+    def conj(self):
+        if self._is('ZERO') or self._is('ONE'): return self
+        return self._un('CONJ')
+
     def inv(self): return self._un('INV')
-    def mulc(self, val): return self._un('MULC', self.g.c2(val))
-    def conjmulc(self, val): return self._un('CONJMULC', self.g.c2(val))
-    def mulfpc(self, val): return self._un('MULFPC', self.g.cp(val))
-    def mulfp(self, pt, which): return S(self.g, Node(self.g, 'MULFP%d' % which, self.n, pt.n))
+
+    def mulc(self, val):
+        if self._is('ZERO'): return self
+        return self._un('MULC', self.g.c2(val))
+
+    def conjmulc(self, val):
+        if self._is('ZERO'): return self
+        return self._un('CONJMULC', self.g.c2(val))
+
+    def mulfpc(self, val):
+        if self._is('ZERO'): return self
+        return self._un('MULFPC', self.g.cp(val))
+
+    def mulfp(self, pt, which):
+        if self._is('ZERO'): return self
+        return S(self.g, Node(self.g, 'MULFP%d' % which, self.n, pt.n))
+
+
+def chk(dx, dy, z):
+    """(1, 0) unless dx == 0, dy == 0 and z != 0, then (0, 0): the verdict of the subgroup test as one slot."""
+    n = Node(dx.g, 'CHK', dx.n, dy.n)
+    n.c = z.n
+    z.n.users.append(n)
+    return S(dx.g, n)
 
 
 # ---------------------------------------------------------------------------------------------- tower formulas
@@ -209,10 +264,10 @@ def line_dbl(r, P):
     E = A.dbl() + A
     G = E.sqr()
     ox = G - D - D
-    oz = (y + z).sqr() - B - t
+    oz = y.dbl() if z._is('ONE') else (y + z).sqr() - B - t   # (y + 1)^2 - y^2 - 1
     oy = (D - ox) * E - C.dbl().dbl().dbl()
     ot = oz.sqr()
-    b = (E * t).dbl().neg().mulfp(P, 0)
+    b = (E * t).dbl().mulfp(P, 0)            # P holds (-x_P, y_P)
     a = (x + E).sqr() - A - G - B.dbl().dbl()
     c = (oz * t).dbl().mulfp(P, 1)
     return (ox, oy, oz, ot), (a, b, c)
@@ -235,7 +290,7 @@ def line_add(r, q, r2, P):
     tt = (q[1] + oz).sqr() - r2 - ot
     a = (L1 * q[0]).dbl() - tt
     c = oz.mulfp(P, 1).dbl()
-    b = L1.neg().mulfp(P, 0).dbl()
+    b = L1.mulfp(P, 0).dbl()
     return (ox, oy, oz, ot), (a, b, c)
 
 
@@ -286,7 +341,8 @@ def final_exp(f):
 
 
 def build_pairing(g):
-    """Inputs: P (one slot: c0 = x, c1 = y), QX, QY, ONE. Output: 6 Fp2 of e(P, Q) in w-power order pairs."""
+    """Inputs: P (one slot: c0 = -x_P, c1 = y_P; the line functions only ever need -x_P), QX, QY; ONE and ZERO are
+    folded away. Outputs: 6 Fp2 of e(P, Q) in w-power order pairs, and SG = (0, 0) iff Q lies in G2."""
     P, qx, qy, one, zero = (S(g, g.inp(n)) for n in ('P', 'QX', 'QY', 'ONE', 'ZERO'))
     mqy = qy.neg()
     r = (qx, qy, one, one)
@@ -313,11 +369,21 @@ def build_pairing(g):
     f = f12_mul_line(f, c, b, a)
     r, (a, b, c) = line_add(r, mq2, mq2[1].sqr(), P)
     f = f12_mul_line(f, c, b, a)
+    # G2 membership for free: r is now [6u+2]Q + pi(Q) - pi^2(Q), which equals -pi^3(Q) exactly when Q has order n
+    # (6u+2 + p - p^2 + p^3 = 0 mod n is the relation the optimal ate pairing is built on; the resultant of
+    # X^3 - X^2 + X + 6u+2 and the characteristic polynomial of pi shares only the factor n with #E'(Fp2), checked in
+    # tests/test_oracle.py, so the converse holds on this curve). An exceptional case of the incomplete addition
+    # formulas, which only a point outside G2 can trigger, leaves z = 0 for good, and z != 0 is part of the test.
+    g3 = frob_consts(3)
+    q3 = (qx.conjmulc(g3[2]), qy.conjmulc(g3[3]))
+    rx, ry, rz, rt = r
+    sg = chk(rx - q3[0] * rt, ry + q3[1] * (rt * rz), rz)
     e = final_exp(f)
     names = ['E00', 'E01', 'E02', 'E10', 'E11', 'E12']
     vals = e[0] + e[1]
     for n, v in zip(names, vals):
         g.out(n, v.n)
+    g.out('SG', sg.n)
 
 
 # ---------------------------------------------------------------------------------------------- linear-op fusion
@@ -409,8 +475,9 @@ def eval_node(n, val, g, P):
     if op == 'MULFPC': return R.f2scal(a, g.constsp[n.imm])
     if op == 'MULFP0': return R.f2scal(a, b[0])
     if op == 'MULFP1': return R.f2scal(a, b[1])
-    if op == 'INV': return R.f2inv(a)
+    if op == 'INV': return R.f2inv(a) if a != (0, 0) else (0, 0)   # the device inverse maps 0 to 0
     if op == 'COPY': return a
+    if op == 'CHK': return (0, 0) if (a == (0, 0) and b == (0, 0) and c != (0, 0)) else (1, 0)
     raise ValueError(op)
 
 
@@ -444,8 +511,9 @@ def schedule(g, G, nslots, window=96):
     # slots: inputs pinned first
     slot_of = {}
     free = list(range(nslots - 1, -1, -1))
-    for name, n in g.inputs.items():
-        slot_of[n.id] = free.pop()
+    for name, n in g.inputs.items():   # inputs are ordinary values: a slot while live, none if nothing reads them
+        if n.id in live:
+            slot_of[n.id] = free.pop()
     done = set(n.id for n in g.inputs.values())
     pending = {n.id: n for n in ops}
     phases = []
@@ -523,7 +591,7 @@ def schedule(g, G, nslots, window=96):
             # in-place: an operand that dies here and that no other lane reads this phase lends its slot to the result
             s = None
             for x in (n.a, n.b, n.c):
-                if x is not None and x.op != 'IN' and x.id not in out_ids and remaining_users[x.id] == 1 \
+                if x is not None and x.id not in out_ids and remaining_users[x.id] == 1 \
                         and readers[x.id] == 1 and slot_of[x.id] not in [slot_of.get(m.id) for m in lanes if m is not None]:
                     s = slot_of[x.id]
                     remaining_users[x.id] = -1  # consumed, slot handed over
@@ -544,7 +612,7 @@ def schedule(g, G, nslots, window=96):
                 if remaining_users[x.id] == -1:
                     continue
                 remaining_users[x.id] -= 1
-                if remaining_users[x.id] == 0 and x.id not in out_ids and x.op != 'IN':
+                if remaining_users[x.id] == 0 and x.id not in out_ids:
                     to_free.append(slot_of[x.id])
         phases.append((phase_op, lanes))
         for n in chosen:
@@ -568,7 +636,8 @@ def fix_user_counts(g):
 def run_program(g, phases, slot_of, nslots, inputs):
     slots = [None] * nslots
     for name, n in g.inputs.items():
-        slots[slot_of[n.id]] = inputs[name]
+        if n.id in slot_of:
+            slots[slot_of[n.id]] = inputs[name]
     P = inputs['P']
     for op, lanes in phases:
         lanes = [n for n in lanes if n is not None]
@@ -616,13 +685,22 @@ def main():
     for _ in range(1 if '--quick' in sys.argv else 2):
         a, b = rng.randrange(1, R.n), rng.randrange(1, R.n)
         Pp, Q = R.g1_mul(a, R.G1_GEN), R.g2_mul(b, R.G2_GEN)
-        out = run_program(g, phases, slot_of, nslots, {'P': (Pp[0], Pp[1]), 'QX': Q[0], 'QY': Q[1], 'ONE': (1, 0), 'ZERO': (0, 0)})
+        out = run_program(g, phases, slot_of, nslots, {'P': ((-Pp[0]) % R.p, Pp[1]), 'QX': Q[0], 'QY': Q[1], 'ONE': (1, 0), 'ZERO': (0, 0)})
         e = R.pair(Pp, Q)
         got = [out['E00'], out['E10'], out['E01'], out['E11'], out['E02'], out['E12']]
         assert got == e, 'micro-program disagrees with the definition'
+        assert out['SG'] == (0, 0), 'subgroup verdict wrong for a point of G2'
     print('micro-program == bn256_ref.pair on random inputs')
+    Pp = R.g1_mul(7, R.G1_GEN)
+    T = R.g2_twist_point(1)
+    outside = [T, R.g2_mul_raw(R.n, T), R.g2_mul_raw(R.n * R.TWIST_COFACTOR // 13, T), R.g2_mul_raw(R.n * R.TWIST_COFACTOR // (13 * 7369), T)]
+    for Q in outside:
+        assert Q is not None and R.g2_on_curve(Q) and not R.g2_in_subgroup(Q)
+        out = run_program(g, phases, slot_of, nslots, {'P': ((-Pp[0]) % R.p, Pp[1]), 'QX': Q[0], 'QY': Q[1], 'ONE': (1, 0), 'ZERO': (0, 0)})
+        assert out['SG'] == (1, 0), 'subgroup verdict wrong for a twist point outside G2'
+    print('subgroup verdict: rejects twist points of composite, cofactor, 13 and 7369-multiple order')
     if '--emit' in sys.argv:
-        emit(g, phases, slot_of, used, G)
+        emit(g, phases, slot_of, used, G, nslots, window)
     return g, phases, slot_of, used, G
 
 
@@ -634,21 +712,27 @@ def mont(x):
     return (x % R.p) * (1 << 256) % R.p
 
 
-def emit(g, phases, slot_of, used, G):
+def emit(g, phases, slot_of, used, G, nslots_arg, window):
     path = os.path.join(ROOT, 'drynx_b200', 'csrc', 'pairing_ucode_g%d.inc' % G)
+    rot = (lambda s_: s_ & 3) if G <= 4 else (lambda s_: (s_ >> 1) & 3)
+    off = lambda s_: s_ * 64 + rot(s_) * 16   # byte offset of a slot inside an item, swizzle folded in
     with open(path, 'w') as f:
         f.write('// GENERATED by tools/microcode/gen.py %d %d ... --emit -- do not edit.\n' % (G, used))
-        f.write('// Lane-group micro-program of the optimal ate pairing: %d Fp2 operations in %d phases for %d lanes,\n'
+        f.write('// Lane-group micro-program of the optimal ate pairing plus the G2 membership verdict: %d Fp2 operations in\n'
+                '// %d phases for %d program lanes,\n'
                 % (sum(1 for _, l in phases for n in l if n is not None), len(phases), G))
         f.write('// %d Fp2 slots per item. Executed with Python integers against the definition of the pairing by the generator before emission.\n' % used)
-        used |= 1  # odd slot count per item: adjacent lane groups then sit in opposite bank halves
+        used |= 1  # odd slot count per item: adjacent items then sit in opposite bank halves
         f.write('#define UC_G %d\n#define UC_NSLOTS %d\n#define UC_NPHASES %d\n' % (G, used, len(phases)))
-        f.write('// physical 16-byte chunk of logical chunk c of slot s (bank swizzle, see kernels_rp_ucode.cuh)\n')
-        f.write('#define UC_ROT(s) %s\n' % ('((s) & 3u)' if G <= 4 else '(((s) >> 1) & 3u)'))
+        f.write('// generator arguments (tests/test_microcode.py regenerates the program from them)\n')
+        f.write('#define UC_GEN_SLOTS %d\n#define UC_GEN_WINDOW %d\n' % (nslots_arg, window))
+        f.write('// A slot is 64 bytes = four 16-byte chunks; logical chunk c of slot s lives at physical chunk c ^ UC_SWZ(s)\n')
+        f.write('#define UC_SWZ(s) %s\n' % ('((s) & 3u)' if G <= 4 else '(((s) >> 1) & 3u)'))
         for i, name in enumerate(OPS):
             f.write('#define UC_%s %d\n' % (name, i))
         for name, n in g.inputs.items():
-            f.write('#define UC_IN_%s %d\n' % (name, slot_of[n.id]))
+            if n.id in slot_of:
+                f.write('#define UC_IN_%s %d\n' % (name, slot_of[n.id]))
         for name, n in g.outputs.items():
             f.write('#define UC_OUT_%s %d\n' % (name, slot_of[n.id]))
         f.write('__device__ const uint32_t uc_const2[%d][16] = {\n' % max(1, len(g.consts2)))
@@ -657,23 +741,26 @@ def emit(g, phases, slot_of, used, G):
         f.write('};\n__device__ const uint32_t uc_constp[%d][8] = {\n' % max(1, len(g.constsp)))
         for c in g.constsp:
             f.write('  {%s},\n' % limbs(mont(c)))
-        f.write('};\n__device__ const uint8_t uc_ops[UC_NPHASES] = {\n')
+        f.write('};\n// one opcode per phase (warp-uniform: read through the constant cache)\n')
+        f.write('__constant__ uint8_t uc_ops[UC_NPHASES] = {\n')
         for k in range(0, len(phases), 32):
             f.write('  ' + ', '.join(str(OPC[o]) for o, _ in phases[k:k + 32]) + ',\n')
-        f.write('};\n// per lane: dst | a << 8 | b << 16 | c << 24, 0xffffffff = idle (b = constant index for MULC / CONJMULC / MULFPC)\n')
-        f.write('__device__ const uint32_t uc_lanes[UC_NPHASES * UC_G] = {\n')
+        f.write('};\n// per program lane: x = dst | a << 16, y = b | c << 16, each the BYTE offset of the slot inside the item with the\n'
+                '// swizzle folded in (slot * 64 + UC_SWZ(slot) * 16); x = 0xffffffff: idle; b = constant index for MULC / CONJMULC / MULFPC\n')
+        f.write('__device__ const uint2 uc_prog[UC_NPHASES * UC_G] = {\n')
         for op, lanes in phases:
             words = []
             for k in range(G):
                 if k < len(lanes) and lanes[k] is not None:
                     n = lanes[k]
-                    a = slot_of[n.a.id] if n.a is not None else 0
-                    b = slot_of[n.b.id] if n.b is not None else n.imm
-                    c = slot_of[n.c.id] if n.c is not None else 0
-                    assert slot_of[n.id] < 255 and a < 256 and b < 256 and c < 256
-                    words.append('0x%08xu' % (slot_of[n.id] | a << 8 | b << 16 | c << 24))
+                    a = off(slot_of[n.a.id]) if n.a is not None else 0
+                    b = off(slot_of[n.b.id]) if n.b is not None else n.imm
+                    c = off(slot_of[n.c.id]) if n.c is not None else 0
+                    d = off(slot_of[n.id])
+                    assert max(a, b, c, d) < 65535
+                    words.append('{0x%08xu, 0x%08xu}' % (d | a << 16, b | c << 16))
                 else:
-                    words.append('0xffffffffu')
+                    words.append('{0xffffffffu, 0xffffffffu}')
             f.write('  ' + ', '.join(words) + ',\n')
         f.write('};\n')
     print('wrote', path, os.path.getsize(path), 'bytes')

@@ -19,6 +19,9 @@ be.set_pubkey(be.g1_mul(b'\0' + sk, g1))
 Y, A = be.init_range_proof_signature([int.from_bytes(g.bytes(31), 'big') + 1 for _ in range(NS)], U)
 be.set_signatures(0, NS, U, Y, A)
 be.set_option('rp_verify_path', int(os.environ.get('DRX_RP_PATH', '0')))
+for _o, _e in (('rp_ucode_lanes', 'DRX_UC_LANES'), ('rp_ucode_mode', 'DRX_UC_MODE'),
+               ('rp_ucode_resident', 'DRX_UC_RESIDENT'), ('rp_ucode_nseg', 'DRX_UC_NSEG')):
+    be.set_option(_o, int(os.environ.get(_e, '0')))
 dev = torch.device('cuda', 0)
 vp = lambda t: ctypes.c_void_p(t.data_ptr())
 def scal(k):
