@@ -21,6 +21,7 @@ SIGNATURES = {
     'drx_last_error': (ctypes.c_char_p, []),
     'drx_set_stream': (ctypes.c_int, [VP, VP]),
     'drx_synchronize': (ctypes.c_int, [VP]),
+    'drx_take_bad': (ctypes.c_int, [VP, ctypes.POINTER(ctypes.c_int)]),
     'drx_launch_count': (ctypes.c_uint64, [VP]),
     'drx_set_option': (ctypes.c_int, [VP, ctypes.c_char_p, ctypes.c_int]),
     'drx_profile_enable': (ctypes.c_int, [VP, ctypes.c_int]),

@@ -53,6 +53,12 @@ class Backend:
     def set_option(self, name, value):
         _lib.check(self.lib.drx_set_option(self.h, name.encode(), int(value)))
 
+    def take_bad(self):
+        """Malformed input points met by the device-buffer (`_dev`) calls since the last take_bad (waits for the stream)."""
+        n = ctypes.c_int(0)
+        _lib.check(self.lib.drx_take_bad(self.h, ctypes.byref(n)))
+        return n.value
+
     def synchronize(self):
         _lib.check(self.lib.drx_synchronize(self.h))
 

@@ -167,6 +167,9 @@ struct Guard {
   ~Guard() { c->mu.unlock(); }
 };
 
+// Device-buffer (`_dev`) calls are asynchronous and cannot return a malformed-input count; they add to a second
+// counter (word 1 of the buffer) that drx_take_bad reads and clears. Host-buffer calls use word 0, reset per call.
+int* dev_bad(drx_ctx* c) { return (int*)c->bad.p + 1; }
 int reset_bad(drx_ctx* c) {
   CU(cudaMemsetAsync(c->bad.p, 0, sizeof(int), c->stream));
   return 0;
@@ -274,7 +277,7 @@ int drx_init(drx_ctx** out, int device, const uint8_t* g1_base, const uint8_t* g
     return cleanup(rc);
   cudaMemcpyAsync(c->baseB_wire.p, g1_base ? g1_base : kDefaultG1, 64, cudaMemcpyHostToDevice, c->stream);
   cudaMemcpyAsync(c->g2_wire.p, g2_base ? g2_base : kDefaultG2, 128, cudaMemcpyHostToDevice, c->stream);
-  cudaMemsetAsync(c->bad.p, 0, 256, c->stream);  // word 0: malformed-input counter; word 16: lane-group pairing error word
+  cudaMemsetAsync(c->bad.p, 0, 256, c->stream);  // word 0: malformed-input counter; bytes 64..95: key-switching secret; word 48: lane-group pairing error word
   c->launches += launch_g1_from_wire(c->stream, 1, (const uint8_t*)c->baseB_wire.p, c->baseB_aff.p, (int*)c->bad.p);
   c->launches += launch_g2_from_wire(c->stream, 1, (const uint8_t*)c->g2_wire.p, c->g2_aff.p, (int*)c->bad.p);
   c->launches += launch_comb_table_g1(c->stream, 1, c->baseB_aff.p, c->tabB.p);
@@ -324,7 +327,7 @@ int drx_set_stream(drx_ctx* c, void* cuda_stream) {
 // waiting for a predecessor task (ucode_common.cuh): the verification results of that call are not valid then.
 static int take_pairing_error(drx_ctx* c) {
   unsigned int err = 0;
-  unsigned int* d_err = (unsigned int*)c->bad.p + 16;
+  unsigned int* d_err = (unsigned int*)c->bad.p + 48;  // kUcErrWord (capi_rp.inc); bytes 64..95 of the buffer hold the key-switching secret
   CU(cudaMemcpyAsync(&err, d_err, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   if (!err) return 0;
@@ -336,6 +339,14 @@ int drx_synchronize(drx_ctx* c) {
   Guard g(c);
   CU(cudaStreamSynchronize(c->stream));
   return take_pairing_error(c);
+}
+int drx_take_bad(drx_ctx* c, int* n_bad) {
+  if (!c || !n_bad) return fail(-1, "null argument");
+  Guard g(c);
+  CU(cudaMemcpyAsync(n_bad, dev_bad(c), sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemsetAsync(dev_bad(c), 0, sizeof(int), c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
 }
 uint64_t drx_launch_count(const drx_ctx* c) { return c ? c->launches : 0; }
 
@@ -574,8 +585,8 @@ int drx_encrypt_scalar(drx_ctx* c, size_t n, const uint8_t* m, const uint8_t* r,
 }
 
 static int aggregate_on_device(drx_ctx* c, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
-                               uint8_t* d_out) {
-  timed(c, "k_agg_partial", [&] { return launch_agg_partial(c->stream, ndp, v, d_cts, d_scratch, slices, (int*)c->bad.p); });
+                               uint8_t* d_out, int* d_bad) {
+  timed(c, "k_agg_partial", [&] { return launch_agg_partial(c->stream, ndp, v, d_cts, d_scratch, slices, d_bad); });
   timed(c, "k_agg_final", [&] { return launch_agg_final(c->stream, v, slices, d_scratch, d_out); });
   return check_launch("aggregate");
 }
@@ -590,8 +601,7 @@ int drx_aggregate_dev(drx_ctx* c, size_t ndp, size_t v, const uint8_t* d_cts, ui
   a.plan_reset();
   size_t os = a.plan(sb);
   RET(a.commit());
-  RET(reset_bad(c));
-  return aggregate_on_device(c, ndp, v, d_cts, a.at<void>(os), slices, d_out);
+  return aggregate_on_device(c, ndp, v, d_cts, a.at<void>(os), slices, d_out, dev_bad(c));
 }
 
 int drx_aggregate(drx_ctx* c, size_t ndp, size_t v, const uint8_t* const* cts, uint8_t* out) {
@@ -610,7 +620,7 @@ int drx_aggregate(drx_ctx* c, size_t ndp, size_t v, const uint8_t* const* cts, u
     if (!cts[d]) return fail(-1, "drx_aggregate: cts[%zu] is NULL", d);
     CU(cudaMemcpyAsync(a.at<uint8_t>(oi) + d * v * 128, cts[d], v * 128, cudaMemcpyHostToDevice, c->stream));
   }
-  RET(aggregate_on_device(c, ndp, v, a.at<uint8_t>(oi), a.at<void>(os), slices, a.at<uint8_t>(oo)));
+  RET(aggregate_on_device(c, ndp, v, a.at<uint8_t>(oi), a.at<void>(os), slices, a.at<uint8_t>(oo), (int*)c->bad.p));
   CU(cudaMemcpyAsync(out, a.at<void>(oo), v * 128, cudaMemcpyDeviceToHost, c->stream));
   int bad = 0;
   RET(read_bad(c, &bad));
@@ -673,7 +683,7 @@ int drx_keyswitch_dev(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t*
   CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
   timed(c, "k_keyswitch", [&] {
     return launch_keyswitch(c->stream, n, (uint8_t*)c->bad.p + 64, d_rb, d_v, c->tabB.p, c->tabQ.p, d_cv, d_rb_neg,
-                            (int*)c->bad.p);
+                            dev_bad(c));
   });
   return check_launch("keyswitch");
 }
@@ -710,7 +720,7 @@ int drx_keyswitch(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* rb,
 int drx_ct_scalar_mul_dev(drx_ctx* c, size_t n, const uint8_t* d_s, const uint8_t* d_ct, uint8_t* d_out) {
   if (!c) return fail(-1, "null context");
   Guard g(c);
-  timed(c, "k_ct_scalar_mul", [&] { return launch_ct_scalar_mul(c->stream, n, d_s, d_ct, d_out, (int*)c->bad.p); });
+  timed(c, "k_ct_scalar_mul", [&] { return launch_ct_scalar_mul(c->stream, n, d_s, d_ct, d_out, dev_bad(c)); });
   return check_launch("ct_scalar_mul");
 }
 
@@ -776,7 +786,7 @@ int drx_shuffle_rerandomize_dev(drx_ctx* c, size_t lines, size_t nq, const int32
   Guard g(c);
   if (!c->have_pub) return fail(-1, "drx_shuffle_rerandomize: call drx_set_pubkey first");
   timed(c, "k_shuffle_rerandomize", [&] {
-    return launch_shuffle_rerandomize(c->stream, lines, nq, d_pi, d_in, d_beta, c->tabB.p, c->tabP.p, d_out, (int*)c->bad.p);
+    return launch_shuffle_rerandomize(c->stream, lines, nq, d_pi, d_in, d_beta, c->tabB.p, c->tabP.p, d_out, dev_bad(c));
   });
   return check_launch("shuffle_rerandomize");
 }
@@ -812,7 +822,7 @@ int drx_decrypt_dev(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* d
   CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
   timed(c, "k_decrypt", [&] {
     return launch_decrypt(c->stream, n, (uint8_t*)c->bad.p + 64, d_ct, c->dlog_keys.p, (uint32_t*)c->dlog_vals.p, d_out,
-                          (int*)c->bad.p);
+                          dev_bad(c));
   });
   return check_launch("decrypt");
 }

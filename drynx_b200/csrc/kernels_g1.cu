@@ -588,8 +588,11 @@ k_keyswitch(size_t n, const uint32_t* __restrict__ sk, const uint32_t* __restric
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   G1Aff R;
-  if (!g1_from_wire(R, rb + 16 * i)) {
+  if (!g1_from_wire(R, rb + 16 * i)) {  // rejected element: counted, and its output rows are zeroed (never stale)
     atomicAdd(bad, 1);
+    for (int k = 0; k < 32; k++) cv[32 * i + k] = 0;
+    if (rb_neg)
+      for (int k = 0; k < 16; k++) rb_neg[16 * i + k] = 0;
     return;
   }
   const G1Aff Rn = aff_neg(R);
@@ -620,8 +623,9 @@ k_ct_scalar_mul(size_t n, const uint32_t* __restrict__ sc, const uint32_t* __res
   G1Aff K, C;
   int nbad = !g1_from_wire(K, ct + 32 * i);
   nbad += !g1_from_wire(C, ct + 32 * i + 16);
-  if (nbad) {
+  if (nbad) {  // rejected element: counted, and its output row is zeroed (never stale)
     atomicAdd(bad, nbad);
+    for (int k = 0; k < 32; k++) out[32 * i + k] = 0;
     return;
   }
   const Scalar k = sc_from_wire(sc + 8 * i);
@@ -649,8 +653,9 @@ k_shuffle_rerandomize(size_t lines, size_t nq, const int32_t* __restrict__ pi, c
   G1Aff K, C;
   int nbad = !g1_from_wire(K, in + 32 * src);
   nbad += !g1_from_wire(C, in + 32 * src + 16);
-  if (nbad) {
+  if (nbad) {  // rejected element: counted, and its output row is zeroed (never stale)
     atomicAdd(bad, nbad);
+    for (int k = 0; k < 32; k++) out[32 * t + k] = 0;
     return;
   }
   const Scalar b = sc_from_wire(beta + 8 * src);

@@ -367,6 +367,10 @@ k_rp_verify_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __res
   if (p >= b.n) return;
   int ns, nd;
   size_t off;
+  if (!proof_set_valid(b, sets, p)) {                  // unknown signature set (device-buffer calls only): rejected
+    flags[p] = 0;
+    return;
+  }
   if (!locate_proof(b, sets, p, ns, nd, off)) return;  // u = l = 0: accepted
   if (!flags[p]) return;                               // size check failed on the host
   const uint32_t* in = proofs + off / 4;

@@ -93,6 +93,7 @@ struct RpBatch {          // one create/verify call
   const size_t* d_proof_off;   // n+1, or nullptr for a uniform batch
   const uint32_t* d_item_proof;  // items, or nullptr for a uniform batch
   const uint32_t* d_item_start;  // n (first item of each proof), or nullptr
+  int nsets;              // length of the device array of signature sets (ids at or beyond it are invalid)
   int uni_ns;             // uniform batch: servers
   int uni_nd;             // uniform batch: digits
   size_t uni_size;        // uniform batch: bytes per proof

@@ -60,9 +60,19 @@ struct ItemRef {
   int i, j, ns, nd;
   const uint32_t* proof;
 };
+// Set ids of the device-buffer entry points come from device memory the host never saw: an id outside the registered
+// array, an unregistered slot, or (uniform batch) a set whose server count is not the batch's must not be followed.
+__device__ __forceinline__ bool proof_set_valid(const RpBatch& b, const RpSetDev* sets, size_t p) {
+  const int sid = b.d_set_id[p];
+  if (sid < 0) return true;  // commit-only proof (u = l = 0)
+  if (sid >= b.nsets || sets[sid].ns <= 0) return false;
+  return b.d_proof_off != nullptr || sets[sid].ns == b.uni_ns;
+}
+// false: nothing to do for this proof (commit-only, or an invalid set id, which the verification header kernel rejects)
 __device__ __forceinline__ bool locate_proof(const RpBatch& b, const RpSetDev* sets, size_t p, int& ns, int& nd,
                                              size_t& byte_off) {
-  const int sid = b.d_set_id[p];
+  int sid = b.d_set_id[p];
+  if (!proof_set_valid(b, sets, p)) sid = -1;
   if (b.d_proof_off) {
     byte_off = b.d_proof_off[p];
     if (sid < 0) { ns = 0; nd = 0; return false; }

@@ -45,7 +45,18 @@ const char* drx_last_error(void);
 /* Use an existing cudaStream_t (e.g. torch's current stream) for every later call; NULL restores the
  * context's own non-blocking stream. To name the legacy default stream pass cudaStreamLegacy ((void*)1). */
 int drx_set_stream(drx_ctx* ctx, void* cuda_stream);
+/* Waits for everything enqueued on the context's stream. Returns -5 if a range-proof verification enqueued since the
+ * last synchronising call had to abandon its pairing kernel (a device-side wait that never completed: the results of
+ * that call are invalid, repeat it); 0 otherwise. */
 int drx_synchronize(drx_ctx* ctx);
+/* Status path of the device-buffer (`_dev`) entry points, which only enqueue work and so cannot return a count:
+ * malformed input points they meet (off the curve, coordinate >= p: what kyber's UnmarshalBinary refuses and the
+ * reference aborts on) are added to a per-context counter; the affected output rows are written as ZEROS (the point at
+ * infinity), an aggregate skips the malformed term, drx_decrypt_dev writes INT64_MIN. drx_take_bad waits for the stream,
+ * stores the count accumulated since the previous drx_take_bad in *n_bad and clears it. A caller that needs the
+ * reference's "malformed input is an error" behaviour calls it once after its batch of `_dev` calls and treats
+ * *n_bad != 0 like the -2 of the host-buffer entry points. No counterpart in the reference (its calls are synchronous). */
+int drx_take_bad(drx_ctx* ctx, int* n_bad);
 /* Number of kernel launches issued by this context so far (for the benchmark's gpu_launches field). */
 uint64_t drx_launch_count(const drx_ctx* ctx);
 
@@ -105,14 +116,18 @@ int drx_encrypt_scalar(drx_ctx* ctx, size_t n, const uint8_t* m /*n*32*/, const 
  * (protocols/data_collection_protocol.go:145-166, lib/structs.go:338-350): out[j] = sum_d cts[d][j].
  * cts holds ndp pointers to v*128 bytes each. Returns -2 if any point is malformed. */
 int drx_aggregate(drx_ctx* ctx, size_t ndp, size_t v, const uint8_t* const* cts, uint8_t* out /*v*128*/);
-/* Same with the ndp vectors contiguous in device memory (d_cts[d*v*128 ...]). */
+/* Same with the ndp vectors contiguous in device memory (d_cts[d*v*128 ...]); malformed points: see drx_take_bad. */
 int drx_aggregate_dev(drx_ctx* ctx, size_t ndp, size_t v, const uint8_t* d_cts, uint8_t* d_out);
 
 /* Aggregation for callers that must not allocate GPU memory. It has no counterpart in the reference; it computes
  * exactly what drx_aggregate_dev computes (d_cts = ndp vectors of v ciphertexts back to back in device memory,
  * d_out = v ciphertexts), but needs no context and calls no cudaMalloc/cudaFree or any other allocating routine:
- * the partial sums go into a fixed 3 MiB array that every GPU holds from the moment it loads this library until
- * the process exits. Meant for hosts that give the whole GPU to one memory pool at start-up and have nothing left
+ * the partial sums go into a fixed 3 MiB array inside this library's device code. CUDA loads a library's device code
+ * (and reserves such arrays) lazily, at the first use on each device -- for a caller without a context that is the
+ * first drx_aggregate_noalloc_dev call itself. So make ONE warm-up call per device at start-up (ndp = 0, v = 1 is
+ * enough), BEFORE the memory pool takes the rest of the GPU and before any stream capture: that call is where the
+ * 3 MiB and the code are placed, and the only one that can fail for lack of memory; from then on the GPU holds them
+ * until the process exits and no later call allocates anything. Meant for hosts that give the whole GPU to one memory pool at start-up and have nothing left
  * to allocate from later, for services whose policy is "no allocation after initialisation" because a failed
  * cudaMalloc in the middle of a survey cannot be handled, and for latency-sensitive loops where the device-wide
  * synchronisation hidden in cudaMalloc/cudaFree would stall the other streams.

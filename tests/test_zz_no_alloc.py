@@ -33,6 +33,12 @@ def test_no_alloc_aggregate_equals_existing_entry_point_on_consecutive_calls(bac
     sk = (123456789).to_bytes(32, 'big')
     g1 = bytes(31) + b'\x01' + (65000549695646603732796438742359905742825358107623003571877145026864184071783 - 2).to_bytes(32, 'big')
     backend.set_pubkey(backend.g1_mul(sk, g1))
+    # the documented warm-up call (no input, one column): it is the one that places the library's device code and its
+    # fixed array on this GPU; the result of an empty sum is the point at infinity (zeros)
+    warm = torch.full((128,), 0xAB, dtype=torch.uint8, device='cuda')
+    _lib.check(lib.drx_aggregate_noalloc_dev(0, 1, None, _vp(warm), None))
+    torch.cuda.synchronize()
+    assert int(warm.max()) == 0
     # shapes chosen so that consecutive calls use different slice counts and leave stale partial sums behind
     for call, (ndp, v) in enumerate([(37, 50), (5, 3), (130, 700), (37, 50), (1, 1)]):
         cts = _encrypt_vectors(backend, 100 + call, ndp, v)
@@ -40,8 +46,12 @@ def test_no_alloc_aggregate_equals_existing_entry_point_on_consecutive_calls(bac
         got = torch.full((v * 128,), 0xAB, dtype=torch.uint8, device='cuda')
         _lib.check(lib.drx_aggregate_dev(backend.h, ndp, v, _vp(cts), _vp(want)))
         backend.synchronize()
+        torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info()[0]
         _lib.check(lib.drx_aggregate_noalloc_dev(ndp, v, _vp(cts), _vp(got), None))
         torch.cuda.synchronize()
+        # after the warm-up no call may take device memory: the driver's free-byte count does not move
+        assert torch.cuda.mem_get_info()[0] == free_before, (call, ndp, v)
         assert torch.equal(got, want), (call, ndp, v)   # bit-exact, the tolerance every test here uses
 
 
