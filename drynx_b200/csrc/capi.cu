@@ -145,6 +145,7 @@ struct drx_ctx {
   int opt_verify_path = 0;  // drx_set_option "rp_verify_path"
   int opt_create_path = 0;  // drx_set_option "rp_create_path": 0 = by batch size, 1 = never the lane-cooperative kernel
   int opt_ucode_lanes = 0;  // drx_set_option "rp_ucode_lanes": 0 = by batch size, 4 or 8
+  int opt_agg_slices = 0;   // drx_set_option "agg_slices": 0 = sized from the SM count, else forced (experiments)
   UcTune uc_tune;           // drx_set_option "rp_ucode_mode" / "rp_ucode_resident" / "rp_ucode_nseg"
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
       sets_dev, sink, tabQ, target_aff;  // tabQ: comb table of the key-switching target key
@@ -366,6 +367,11 @@ int drx_set_option(drx_ctx* c, const char* name, int value) {
   if (!strcmp(name, "rp_ucode_lanes")) {
     if (value != 0 && value != 4 && value != 8) return fail(-1, "rp_ucode_lanes must be 0 (auto), 4 or 8");
     c->opt_ucode_lanes = value;
+    return 0;
+  }
+  if (!strcmp(name, "agg_slices")) {
+    if (value < 0 || value > kAggMaxSlices) return fail(-1, "agg_slices must be 0 (auto) .. %d", kAggMaxSlices);
+    c->opt_agg_slices = value;
     return 0;
   }
   if (!strcmp(name, "rp_ucode_mode")) {
@@ -597,6 +603,10 @@ int drx_aggregate_dev(drx_ctx* c, size_t ndp, size_t v, const uint8_t* d_cts, ui
   Guard g(c);
   int slices = 1;
   size_t sb = aggregate_scratch_bytes(ndp, v, &slices);
+  if (c->opt_agg_slices > 0 && ndp) {
+    slices = c->opt_agg_slices < (int)ndp ? c->opt_agg_slices : (int)ndp;
+    sb = (size_t)slices * 2 * v * kG1JacBytes;
+  }
   Arena& a = c->arena;
   a.plan_reset();
   size_t os = a.plan(sb);
@@ -936,7 +946,8 @@ int drx_microbench(drx_ctx* c, int kind, int iters, double* ms, double* work) {
   Guard g(c);
   // kind 0: wide multiply-accumulate chains, 1: dependent Montgomery products (both fill the GPU: the roofline peaks);
   // kinds 10 + k / 20 + k / 30 + k: probe k (1: one chain of products, 2: three chains) with one warp per SM / one
-  // warp per sub-partition / two warps per sub-partition (latency probes, profiles/r01_experiments.md)
+  // warp per sub-partition / two warps per sub-partition (latency probes, profiles/r01_experiments.md); k = 3: dependent
+  // field inversions, k = 4: dependent full point additions
   int blocks = 148 * 8, threads = 256;
   if (kind >= 10) {
     blocks = 148;
@@ -957,7 +968,8 @@ int drx_microbench(drx_ctx* c, int kind, int iters, double* ms, double* work) {
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   *ms = t;
-  const double per_thread = kind == 0 ? 16.0 * iters : kind == 2 ? 3.0 * iters : 2.0 * iters;  // wide MACs or Montgomery products
+  // wide MACs, Montgomery products, or (kinds 3 / 4) inversions / full point additions
+  const double per_thread = kind == 0 ? 16.0 * iters : kind == 2 ? 3.0 * iters : kind >= 3 ? 1.0 * iters : 2.0 * iters;
   *work = per_thread * blocks * threads;
   return check_launch("microbench");
 }

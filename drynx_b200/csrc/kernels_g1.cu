@@ -170,37 +170,55 @@ int launch_encrypt(cudaStream_t st, size_t n, const int64_t* d_m, const uint8_t*
 }
 
 // ------------------------------------------------------------------ aggregation (a-3)
-// Stage 1: thread (slice s, output j) folds data providers d = s, s+S, ... of column j with mixed additions
-// straight from wire bytes. Stage 2: thread j folds the S partial sums and serialises.
-struct AggPartial {
-  G1Jac K, C;
-};
-
-__global__ void __launch_bounds__(128)
-k_agg_partial(size_t ndp, size_t v, const uint32_t* __restrict__ cts, int slices, AggPartial* __restrict__ part,
-              int* bad) {
+// A ciphertext vector is 2v points of 64 bytes back to back (K_0 C_0 K_1 C_1 ...), and K and C sum independently, so
+// the unit of work is a POINT COLUMN jp in [0, 2v). Stage 1: thread (slice s, point column jp) folds data providers
+// d = s, s + S, ... of its column with mixed additions straight from wire bytes (one accumulator per thread keeps
+// the kernel at five blocks per SM; the next point is fetched while the current one is added). Stage 2: one warp per
+// point column folds the S partial sums and serialises.
+#ifndef DRX_AGG_MIN_BLOCKS
+#define DRX_AGG_MIN_BLOCKS 5
+#endif
+__global__ void __launch_bounds__(128, DRX_AGG_MIN_BLOCKS)
+k_agg_partial(size_t ndp, size_t v2, const uint32_t* __restrict__ cts, int slices, G1Jac* __restrict__ part, int* bad) {
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= v * (size_t)slices) return;
-  const size_t j = t % v;
-  const int s = (int)(t / v);
-  G1Jac aK = jac_inf<Fp>(), aC = jac_inf<Fp>();
+  if (t >= v2 * (size_t)slices) return;
+  const size_t jp = t % v2;
+  const size_t s = t / v2;
+  const size_t stride = (size_t)slices * v2 * 4;  // uint4 words between consecutive data providers of this thread
+  const uint4* w = reinterpret_cast<const uint4*>(cts) + (s * v2 + jp) * 4;
+  G1Jac acc = jac_inf<Fp>();
   int nbad = 0;
-  for (size_t d = s; d < ndp; d += slices) {
-    const uint32_t* w = cts + (d * v + j) * 32;
-    G1Aff K, C;
-    nbad += !g1_from_wire(K, w);
-    nbad += !g1_from_wire(C, w + 16);
-    aK = jac_add_aff(aK, K);
-    aC = jac_add_aff(aC, C);
+  uint4 cur[4];
+  if (s < ndp) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) cur[k] = __ldg(w + k);
   }
-  part[t].K = aK;
-  part[t].C = aC;
+  for (size_t d = s; d < ndp; d += slices) {
+    uint4 nxt[4];
+    w += stride;
+    if (d + slices < ndp) {
+#pragma unroll
+      for (int k = 0; k < 4; k++) nxt[k] = __ldg(w + k);
+    }
+    uint32_t words[16];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      words[4 * k] = cur[k].x; words[4 * k + 1] = cur[k].y; words[4 * k + 2] = cur[k].z; words[4 * k + 3] = cur[k].w;
+    }
+    G1Aff P;
+    nbad += !g1_from_wire(P, words);  // a malformed point enters the sum as the point at infinity and is counted
+    acc = jac_add_aff(acc, P);
+#pragma unroll
+    for (int k = 0; k < 4; k++) cur[k] = nxt[k];
+  }
+  part[t] = acc;
   if (nbad) atomicAdd(bad, nbad);
 }
 
-// Stage 2, one warp per column: lane l folds slices l, l+32, ... and a five-level butterfly of full additions
-// leaves the column sum in every lane; lane 0 converts to affine and serialises. (A single thread per column
-// would walk all slices serially: 63 dependent additions for the 64-slice case.)
+// Stage 2, L = 4 / 8 / 16 / 32 lanes per point column (the smallest that covers the slices, so that a warp serves up to
+// eight columns and the multiply pipe is not spent on lanes that hold nothing): lane l of a column's group folds
+// slices l, l + L, ...; a log2(L)-level butterfly of full additions leaves the column sum in every lane of the group;
+// lane 0 converts to affine and serialises.
 __device__ __forceinline__ G1Jac jac_shfl_xor(const G1Jac& p, int m) {
   G1Jac r;
 #pragma unroll
@@ -211,48 +229,66 @@ __device__ __forceinline__ G1Jac jac_shfl_xor(const G1Jac& p, int m) {
   }
   return r;
 }
+static inline int agg_group_lanes(int slices) { return slices > 16 ? 32 : slices > 8 ? 16 : slices > 4 ? 8 : 4; }
 __global__ void __launch_bounds__(128)
-k_agg_final(size_t v, int slices, const AggPartial* __restrict__ part, uint32_t* __restrict__ out) {
-  const size_t j = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (j >= v) return;  // whole warps leave together
-  G1Jac aK = jac_inf<Fp>(), aC = jac_inf<Fp>();
-  for (int s = lane; s < slices; s += 32) {
-    aK = jac_add(aK, part[(size_t)s * v + j].K);
-    aC = jac_add(aC, part[(size_t)s * v + j].C);
-  }
-  for (int m = 16; m >= 1; m >>= 1) {
+k_agg_final(size_t v2, int slices, int L, const G1Jac* __restrict__ part, uint32_t* __restrict__ out) {
+  const size_t gt = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t jp = gt / L;
+  const int lane = (int)(gt % L);
+  const bool live = jp < v2;  // every lane of a warp takes part in the shuffles
+  G1Jac acc = jac_inf<Fp>();
+  if (live)
+    for (int s = lane; s < slices; s += L) acc = jac_add(acc, part[(size_t)s * v2 + jp]);
+  for (int m = L >> 1; m >= 1; m >>= 1) {
     if (m < slices) {  // uniform across the warp
-      const G1Jac oK = jac_shfl_xor(aK, m), oC = jac_shfl_xor(aC, m);
+      const G1Jac o = jac_shfl_xor(acc, m);
       // same operand order on both partners keeps their copies bit-identical
-      const bool low = (lane & m) == 0;
-      aK = low ? jac_add(aK, oK) : jac_add(oK, aK);
-      aC = low ? jac_add(aC, oC) : jac_add(oC, aC);
+      acc = (lane & m) == 0 ? jac_add(acc, o) : jac_add(o, acc);
     }
   }
-  if (lane == 0) store_pair_wire(out + 32 * j, aK, aC);
+  if (live && lane == 0) g1_to_wire(out + 16 * jp, jac_to_aff(acc));
 }
 
-size_t aggregate_scratch_bytes(size_t ndp, size_t v, int* slices_out) {
-  // enough threads to fill 148 SMs x 512 resident threads, at most one slice per data provider
-  size_t want = (148 * 512 + v - 1) / (v ? v : 1);
+// SM count of the current device (cached per ordinal; the slicing below sizes stage 1 for the GPU it runs on)
+static int agg_sm_count() {
+  static std::mutex mu;
+  static int sms[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  std::lock_guard<std::mutex> lk(mu);
+  if (!sms[dev] && cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms[dev] = 148;
+  return sms[dev];
+}
+// Slices for stage 1: enough (slice, point column) threads to fill every SM with DRX_AGG_MIN_BLOCKS blocks of 128, a
+// whole number of such waves when there is more work than that, never more slices than data providers.
+static int agg_slices_for(size_t ndp, size_t v, size_t cap) {
+  if (!ndp || !v) return 1;
+  const size_t resident = (size_t)agg_sm_count() * DRX_AGG_MIN_BLOCKS * 128;
+  size_t want = (resident + 2 * v - 1) / (2 * v);
+  // ... but at least eight data providers per thread: below that the second stage (a few dependent full additions
+  // and an inversion per column whatever the slice count) costs more than the extra parallelism returns
+  if (want > (ndp + 7) / 8) want = (ndp + 7) / 8;
+  if (want > cap) want = cap;
   if (want < 1) want = 1;
-  if (want > (size_t)kAggMaxSlices) want = kAggMaxSlices;
-  if (want > ndp) want = ndp ? ndp : 1;
-  if (slices_out) *slices_out = (int)want;
-  return want * v * sizeof(AggPartial);
+  return (int)want;
+}
+size_t aggregate_scratch_bytes(size_t ndp, size_t v, int* slices_out) {
+  const int slices = agg_slices_for(ndp, v, kAggMaxSlices);
+  if (slices_out) *slices_out = slices;
+  return (size_t)slices * 2 * v * sizeof(G1Jac);
 }
 
 int launch_agg_partial(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
                        int* d_bad) {
   if (!v) return 0;
-  k_agg_partial<<<grid_for(v * (size_t)slices, 128), 128, 0, st>>>(ndp, v, (const uint32_t*)d_cts, slices,
-                                                                  (AggPartial*)d_scratch, d_bad);
+  k_agg_partial<<<grid_for(2 * v * (size_t)slices, 128), 128, 0, st>>>(ndp, 2 * v, (const uint32_t*)d_cts, slices,
+                                                                      (G1Jac*)d_scratch, d_bad);
   return 1;
 }
 int launch_agg_final(cudaStream_t st, size_t v, int slices, const void* d_scratch, uint8_t* d_out) {
   if (!v) return 0;
-  k_agg_final<<<grid_for(v * 32, 128), 128, 0, st>>>(v, slices, (const AggPartial*)d_scratch, (uint32_t*)d_out);
+  const int L = agg_group_lanes(slices);
+  k_agg_final<<<grid_for(2 * v * L, 128), 128, 0, st>>>(2 * v, slices, L, (const G1Jac*)d_scratch, (uint32_t*)d_out);
   return 1;
 }
 
@@ -261,8 +297,8 @@ int launch_agg_final(cudaStream_t st, size_t v, int slices, const void* d_scratc
 // caller that must not (or cannot) allocate device memory can still aggregate. The array is shared by every
 // call on a GPU: it holds whatever the previous call left, and two calls in flight at once would overwrite each
 // other's partial sums.
-#define DRX_NOALLOC_MAX_PARTIALS 16384  // (slice, column) pairs: 16384 x 192 B = 3 MiB per GPU
-static __device__ __align__(256) unsigned char g_noalloc_scratch[256 + DRX_NOALLOC_MAX_PARTIALS * sizeof(AggPartial)];
+#define DRX_NOALLOC_MAX_PARTIALS 16384  // (slice, column) pairs: 16384 x 2 points x 96 B = 3 MiB per GPU
+static __device__ __align__(256) unsigned char g_noalloc_scratch[256 + DRX_NOALLOC_MAX_PARTIALS * 2 * sizeof(G1Jac)];
 
 // In host code `g_noalloc_scratch` is only a handle for the symbol, not a device address; the address each GPU
 // gave the array is looked up once per device (with that device current) and remembered.
@@ -294,19 +330,17 @@ int launch_aggregate_static(cudaStream_t st, size_t ndp, size_t v, const uint8_t
   *launches = 0;
   if (!v) return 0;
   if (v > (size_t)DRX_NOALLOC_MAX_PARTIALS) return -5;
-  size_t slices = (size_t)DRX_NOALLOC_MAX_PARTIALS / v;
-  if (slices > (size_t)kAggMaxSlices) slices = kAggMaxSlices;
-  if (slices > ndp) slices = ndp;
-  if (slices < 1) slices = 1;
+  const size_t slices = (size_t)agg_slices_for(ndp, v, (size_t)DRX_NOALLOC_MAX_PARTIALS / v);
   void* base = nullptr;
   cudaError_t e = noalloc_scratch(&base);
   if (e != cudaSuccess) return (int)e;
   int* d_bad = (int*)base;                                   // first 256 bytes: the malformed-point counter
-  AggPartial* part = (AggPartial*)((unsigned char*)base + 256);
+  G1Jac* part = (G1Jac*)((unsigned char*)base + 256);
   e = cudaMemsetAsync(d_bad, 0, 256, st);                    // the counter must start at zero; the partials are
   if (e != cudaSuccess) return (int)e;                       // all rewritten by stage 1 before stage 2 reads them
-  k_agg_partial<<<grid_for(v * slices, 128), 128, 0, st>>>(ndp, v, (const uint32_t*)d_cts, (int)slices, part, d_bad);
-  k_agg_final<<<grid_for(v * 32, 128), 128, 0, st>>>(v, (int)slices, part, (uint32_t*)d_out);
+  k_agg_partial<<<grid_for(2 * v * slices, 128), 128, 0, st>>>(ndp, 2 * v, (const uint32_t*)d_cts, (int)slices, part, d_bad);
+  const int L = agg_group_lanes((int)slices);
+  k_agg_final<<<grid_for(2 * v * L, 128), 128, 0, st>>>(2 * v, (int)slices, L, part, (uint32_t*)d_out);
   *launches = 2;
   e = cudaGetLastError();
   if (e != cudaSuccess) return (int)e;
@@ -804,9 +838,38 @@ __global__ void __launch_bounds__(256) k_probe_montmul3(int iters, uint32_t* sin
   for (int k = 0; k < 8; k++) s ^= x[0].v[k] ^ x[1].v[k] ^ x[2].v[k];
   sink[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
+// dependent field inversions (kind 3) / dependent full point additions (kind 4): the latency of the building blocks
+// on the critical path of the small-batch kernels and of the aggregation's second stage
+__global__ void __launch_bounds__(256) k_probe_inv(int iters, uint32_t* sink) {
+  Fp x;
+  for (int k = 0; k < 8; k++) x.v[k] = (threadIdx.x + 1) * 2654435761u + k * 40503u + blockIdx.x;
+  x.v[7] &= 0x7fffffffu;
+  for (int it = 0; it < iters; it++) {
+    x = fp_inv(x);
+    x.v[0] ^= 1u;
+  }
+  uint32_t s = 0;
+  for (int k = 0; k < 8; k++) s ^= x.v[k];
+  sink[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+__global__ void __launch_bounds__(256) k_probe_jac_add(int iters, uint32_t* sink) {
+  G1Jac a, b;
+  for (int k = 0; k < 8; k++) {
+    a.x.v[k] = (threadIdx.x + 1) * 2654435761u + k; a.y.v[k] = a.x.v[k] * 3u + 1u; a.z.v[k] = a.x.v[k] * 5u + 2u;
+    b.x.v[k] = (blockIdx.x + 1) * 40503u + k * 77u; b.y.v[k] = b.x.v[k] * 7u + 3u; b.z.v[k] = b.x.v[k] * 11u + 4u;
+  }
+  a.x.v[7] &= 0x7fffffffu; a.y.v[7] &= 0x7fffffffu; a.z.v[7] &= 0x7fffffffu;
+  b.x.v[7] &= 0x7fffffffu; b.y.v[7] &= 0x7fffffffu; b.z.v[7] &= 0x7fffffffu;
+  for (int it = 0; it < iters; it++) a = jac_add(a, b);   // the formulas run on any field elements; no curve needed
+  uint32_t s = 0;
+  for (int k = 0; k < 8; k++) s ^= a.x.v[k] ^ a.y.v[k] ^ a.z.v[k];
+  sink[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
 int launch_microbench(cudaStream_t st, int kind, int iters, int blocks, int threads, uint32_t* d_sink) {
   if (kind == 0) k_probe_imad<<<blocks, threads, 0, st>>>(iters, d_sink);
   else if (kind == 2) k_probe_montmul3<<<blocks, threads, 0, st>>>(iters, d_sink);
+  else if (kind == 3) k_probe_inv<<<blocks, threads, 0, st>>>(iters, d_sink);
+  else if (kind == 4) k_probe_jac_add<<<blocks, threads, 0, st>>>(iters, d_sink);
   else k_probe_montmul<<<blocks, threads, 0, st>>>(iters, d_sink);
   return 1;
 }

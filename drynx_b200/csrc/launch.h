@@ -13,7 +13,7 @@ constexpr size_t kCombPoints = (size_t)kCombWindows * kCombEntries;  // 8160
 constexpr size_t kG1AffBytes = 64, kG2AffBytes = 128, kGtBytes = 384, kG1JacBytes = 96;
 constexpr int64_t kMaxHomomorphicInt = 100000;  // libunlynx.MaxHomomorphicInt
 constexpr uint32_t kDlogCap = 1u << 18;         // open-addressing slots for 100001 keys
-constexpr int kAggMaxSlices = 64;
+constexpr int kAggMaxSlices = 512;  // stage-1 slices of an aggregation (sized from the SM count, see kernels_g1.cu)
 constexpr size_t kEncryptLanesMaxItems = 16384; // encryptions up to this many use eight lanes each (latency)
 constexpr size_t kCreateLanesMaxItems = 800;   // creation items up to this many: lane-cooperative kernel (8 / 16 lanes per item)
 constexpr size_t kCreateFineMaxItems = 36000; // creation items up to this many are split twelve ways (latency)
@@ -34,7 +34,7 @@ int launch_encrypt_scalar(cudaStream_t st, size_t n, const uint8_t* d_m, const u
                           const void* d_tabP, uint8_t* d_ct);
 int launch_encrypt(cudaStream_t st, size_t n, const int64_t* d_m, const uint8_t* d_r, const void* d_tabB,
                    const void* d_tabP, uint8_t* d_ct);
-// scratch: slices * v * 2 Jacobian points
+// scratch: slices * 2v Jacobian points
 size_t aggregate_scratch_bytes(size_t ndp, size_t v, int* slices_out);
 int launch_agg_partial(cudaStream_t st, size_t ndp, size_t v, const uint8_t* d_cts, void* d_scratch, int slices,
                        int* d_bad);

@@ -43,11 +43,13 @@ def test_dev_calls_report_malformed_points_through_take_bad(backend, oracle, rng
     skb = np.frombuffer(sk.to_bytes(32, 'big'), np.uint8).copy()
     skp = ctypes.c_void_p(skb.ctypes.data)
 
-    # aggregation: the malformed terms are skipped and counted; the sum equals the oracle's sum of the well-formed rows
+    # aggregation: a malformed POINT is skipped (it enters its sum as the point at infinity) and counted; the result
+    # equals the oracle's sum over the same rows with those points replaced by infinity
     d_out = torch.full((128,), 0xAB, dtype=torch.uint8, device='cuda')
     ck(lib.drx_aggregate_dev(backend.h, n, 1, _vp(d_ct), _vp(d_out)))
     assert backend.take_bad() == len(bad_rows)
-    rc, want = oracle.aggregate([cts[128 * i:128 * i + 128].tobytes() for i in range(n) if i not in bad_rows])
+    rows = [cts[128 * i:128 * i + 128].tobytes() for i in range(n)]
+    rc, want = oracle.aggregate([bytes(64) + rows[i][64:] if i in bad_rows else rows[i] for i in range(n)])
     assert rc == 0 and d_out.cpu().numpy().tobytes() == want
     assert backend.take_bad() == 0                                  # cleared by the previous call
 

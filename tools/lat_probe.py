@@ -9,3 +9,7 @@ for kind, what in ((11, '1 chain, 1 warp/SM'), (12, '3 chains, 1 warp/SM'), (21,
     ms, work = be.microbench(kind, it)
     per_thread = work / (148 * (32 if kind < 20 else 128 if kind < 30 else 256)) if kind >= 10 else work / (148 * 8 * 256)
     print('%-24s %.3f ms, %.0f cycles per product per warp (at 1965 MHz)' % (what, ms, ms * 1.965e6 / per_thread))
+for kind, what, it2 in ((13, 'fp_inv, 1 warp/SM', 200), (33, 'fp_inv, 2 warps/SMSP', 200), (3, 'fp_inv, full GPU', 200),
+                        (14, 'jac_add, 1 warp/SM', 2000), (34, 'jac_add, 2 warps/SMSP', 2000)):
+    ms, work = be.microbench(kind, it2)
+    print('%-24s %.3f ms, %.0f cycles per operation per warp (at 1965 MHz)' % (what, ms, ms * 1.965e6 / it2))
