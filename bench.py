@@ -42,6 +42,24 @@ M_SHUFFLE = 352 + 352 + 11 + 11 + 16       # two comb walks, two mixed additions
 M_KEYSWITCH = 352 + 352 + 2816 + 16 + 16   # v*B and v*Q by comb, x*rB by 4-bit windows, one addition, two affine outputs
 
 
+NCU_SUMMARY = 'profiles/r02_ncu_pair_ucode.txt'   # ncu --set full capture of the dominant kernel at the headline size
+
+
+def ncu_traffic(rel):
+    """dram__bytes_read.sum + dram__bytes_write.sum (bytes per launch) out of a committed `ncu --page raw` summary."""
+    import re
+    scale = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+    try:
+        text = open(os.path.join(ROOT, rel)).read()
+        tot = 0.0
+        for name in ('dram__bytes_read.sum', 'dram__bytes_write.sum'):
+            m = re.search(re.escape(name) + r' \[(\w+)\] = ([0-9.]+)', text)
+            tot += float(m.group(2)) * scale[m.group(1)]
+        return int(tot)
+    except Exception:
+        return None
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -214,6 +232,7 @@ def run_gpu(args):
     import torch
     import torch.distributed as dist
     from drynx_b200 import Backend, _lib
+    from drynx_b200.sharding import gather_and_fold, gather_accept_bytes, shard_range
 
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -273,6 +292,10 @@ def run_gpu(args):
     be2.set_stream(stream2.cuda_stream)
     ev_ct = torch.cuda.Event()
 
+    def fold_dev(gathered):
+        ck(lib.drx_aggregate_dev(be2.h, world, NOUT, vp(gathered), vp(d_fold)))
+        return d_fold
+
     def step_dev():
         d_flush.zero_()
         ck(lib.drx_reduce_rows_dev(be.h, ndp, rows, vp(d_rows), 3, vp(d_m)))
@@ -283,12 +306,8 @@ def run_gpu(args):
         with torch.cuda.stream(stream2):
             stream2.wait_event(ev_ct)
             ck(lib.drx_aggregate_dev(be2.h, ndp, NOUT, vp(d_ct), vp(d_agg)))
-            final = d_agg
-            if world > 1:
-                dist.all_gather_into_tensor(d_gather, d_agg)
-                if rank == 0:
-                    ck(lib.drx_aggregate_dev(be2.h, world, NOUT, vp(d_gather), vp(d_fold)))
-                final = d_fold
+            # the one exchange of the sharded survey (drynx_b200/sharding.py; tests/test_sharding.py runs it over gloo)
+            final = gather_and_fold(d_agg, rank, world, dist, fold_dev, gathered=d_gather)
             if rank == 0:
                 ck(lib.drx_decrypt_dev(be2.h, NOUT, skp, vp(final), vp(d_dec)))
         stream.wait_stream(stream2)
@@ -348,34 +367,36 @@ def run_gpu(args):
     value = world * n * args.steps / (ms / 1e3)
 
     # ------------------------------------------------------------------ e2e: host buffers through the C ABI
+    # Two sets of host buffers: PAGEABLE numpy arrays (what a cgo caller's Go slices are; the context stages them
+    # through its pinned area) -- this is `e2e` -- and pinned ones (`e2e_pinned`, the upper bound).
+    keep = []
+
     def pinned(a):
         t = torch.from_numpy(a).pin_memory()
-        return t, t.numpy()
-    keep = []
-    h = {}
-    for k in ('rows', 'r', 'rnd', 'set_id'):
-        t, h[k] = pinned(d[k])
         keep.append(t)
-    t_ct, h_ct = pinned(np.empty(n * 128, np.uint8)); keep.append(t_ct)
-    t_pr, h_pr = pinned(np.empty(n * proof_size, np.uint8)); keep.append(t_pr)
-    t_ok, h_ok = pinned(np.empty(n, np.uint8)); keep.append(t_ok)
-    t_ag, h_ag = pinned(np.empty(NOUT * 128, np.uint8)); keep.append(t_ag)
-    t_m, h_m = pinned(np.empty(n, np.int64)); keep.append(t_m)
+        return t.numpy()
+
+    def host_set(alloc):
+        h = {k: alloc(d[k].copy()) for k in ('rows', 'r', 'rnd', 'set_id')}
+        h.update(ct=alloc(np.empty(n * 128, np.uint8)), pr=alloc(np.empty(n * proof_size, np.uint8)), ok=alloc(np.empty(n, np.uint8)),
+                 ag=alloc(np.empty(NOUT * 128, np.uint8)), m=alloc(np.empty(n, np.int64)))
+        h['ptrs'] = (ctypes.c_void_p * ndp)(*[h['ct'].ctypes.data + k * NOUT * 128 for k in range(ndp)])
+        return h
     h_dec = np.empty(NOUT, np.int64)
     h_found = np.empty(NOUT, np.uint8)
     h_l = np.full(n, L, np.int64)
     poff = (np.arange(n + 1, dtype=np.uint64) * proof_size)
     roff = (np.arange(n + 1, dtype=np.uint64) * (L * (3 + NS) * 32))
     np_p = lambda a: ctypes.c_void_p(a.ctypes.data)
-    ptrs = (ctypes.c_void_p * ndp)(*[h_ct.ctypes.data + k * NOUT * 128 for k in range(ndp)])
     be.set_stream(0)
-
     be2.set_stream(0)
+    cur = {}
 
     def agg_dec():
-        ck(lib.drx_aggregate(be2.h, ndp, NOUT, ctypes.cast(ptrs, ctypes.c_void_p), np_p(h_ag)))
+        h = cur['h']
+        ck(lib.drx_aggregate(be2.h, ndp, NOUT, ctypes.cast(h['ptrs'], ctypes.c_void_p), np_p(h['ag'])))
         if rank == 0 and world == 1:
-            ck(lib.drx_decrypt(be2.h, NOUT, skp, np_p(h_ag), 1, np_p(h_dec), np_p(h_found)))
+            ck(lib.drx_decrypt(be2.h, NOUT, skp, np_p(h['ag']), 1, np_p(h_dec), np_p(h_found)))
 
     # the second goroutine: a long-lived worker thread woken once per step (ctypes calls release the GIL)
     go, done_ev, quit_flag, side_err = threading.Event(), threading.Event(), [False], []
@@ -397,35 +418,39 @@ def run_gpu(args):
     def step_e2e():
         # what a Go data provider / root / verifying node would do with two goroutines and one context each:
         # aggregation + decryption only need the ciphertexts and run next to proof creation + verification
-        ck(lib.drx_reduce_rows(be.h, ndp, rows, np_p(h['rows']), 3, np_p(h_m)))
-        m = h_m
-        ck(lib.drx_encrypt(be.h, n, np_p(m), np_p(h['r']), np_p(h_ct)))
+        h = cur['h']
+        ck(lib.drx_reduce_rows(be.h, ndp, rows, np_p(h['rows']), 3, np_p(h['m'])))
+        ck(lib.drx_encrypt(be.h, n, np_p(h['m']), np_p(h['r']), np_p(h['ct'])))
         go.set()
-        ck(lib.drx_rp_create(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(m), np_p(h['r']), np_p(h_ct), np_p(h['rnd']), np_p(roff),
-                             np_p(h_pr), np_p(poff)))
-        ck(lib.drx_rp_verify(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h_pr), np_p(poff), np_p(h_ok)))
+        ck(lib.drx_rp_create(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h['m']), np_p(h['r']), np_p(h['ct']), np_p(h['rnd']), np_p(roff),
+                             np_p(h['pr']), np_p(poff)))
+        ck(lib.drx_rp_verify(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h['pr']), np_p(poff), np_p(h['ok'])))
         done_ev.wait()
         done_ev.clear()
         if side_err:
             raise side_err[0]
-        return m
-    h2d = h['rows'].nbytes + (n * 8 + n * 32) + (n * 4 + n * 8 * 2 + n * 32 + n * 128 + h['rnd'].nbytes) + (n * 4 + n * 8 + h_pr.nbytes + n * 4) \
-        + h_ct.nbytes + (NOUT * 128 + 32)  # encrypt + create + verify + aggregate + decrypt inputs
-    d2h = n * 8 + h_ct.nbytes + h_pr.nbytes + n + NOUT * 128 + NOUT * 8
-    for _ in range(3):
-        step_e2e()
-    assert h_ok.all() and h_pr.tobytes() == d_proofs.cpu().numpy().tobytes(), 'e2e and device-resident legs disagree'
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step_e2e()
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e_val = world * n * args.steps / e2e_s
+    pr_bytes = n * proof_size
+    h2d = d['rows'].nbytes + (n * 8 + n * 32) + (n * 4 + n * 8 * 2 + n * 32 + n * 128 + d['rnd'].nbytes) + (n * 4 + n * 8 + pr_bytes + n * 4) \
+        + n * 128 + (NOUT * 128 + 32)  # encrypt + create + verify + aggregate + decrypt inputs
+    d2h = n * 8 + n * 128 + pr_bytes + n + NOUT * 128 + NOUT * 8
+    e2e_s = {}
+    for kind, alloc in (('pageable', lambda a: a), ('pinned', pinned)):
+        cur['h'] = host_set(alloc)
+        for _ in range(3):
+            step_e2e()
+        assert cur['h']['ok'].all() and cur['h']['pr'].tobytes() == d_proofs.cpu().numpy().tobytes(), 'e2e and device-resident legs disagree'
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_e2e()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e_s[kind] = dt
+    e2e_val = world * n * args.steps / e2e_s['pageable']
     quit_flag[0] = True
     go.set()
     be.set_stream(stream.cuda_stream or 1)
@@ -441,15 +466,21 @@ def run_gpu(args):
     achieved = alg_mac / (vi['ms_per_launch'] * 1e-3) / 1e12
     roofline = {'bound': 'int32 IMAD.WIDE pipe', 'kernel': dom, 'achieved': achieved, 'peak': peak_tmac,
                 'unit': 'TMAC32/s', 'frac': achieved / peak_tmac,
-                # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this size, from the committed ncu --set full
-                # capture profiles/r01_ncu_pair_ucode.txt (algorithmic bytes: 6,000 x 208 B in, 384 B out = 3.6 MB)
-                'traffic': 1544704 if dom == 'k_pair_ucode' else None,  # profiles/r01_ncu_pair_ucode.txt: dram read + write per launch
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this size, read from the committed ncu --set full
+                # summary (algorithmic bytes: 6,000 x 208 B in, 384 B out = 3.6 MB)
+                'traffic': ncu_traffic(NCU_SUMMARY) if dom == 'k_pair_ucode' else None, 'traffic_source': NCU_SUMMARY,
                 'peak_source': 'measured live: register-resident IMAD.WIDE.U32.X chains (drx_microbench kind 0); MEASURED_PEAKS.json has no integer figure',
                 'algorithmic': '%d proofs x %d (server,digit) pairs x %d M x 128 MAC32 per launch' % (n, NS * L, per_item)}
 
     secondary = {}
     if not args.no_secondary and rank == 0:
         secondary = secondary_rates(be, lib, torch, dev, stream, ck, vp, peak_tmac, skp)
+
+    # ------------------------------------------------------------------ strong scaling of configs 5 and 4 (every rank)
+    if not args.no_secondary:
+        strong = strong_scaling(be, lib, torch, dist, dev, stream, ck, vp, rank, world, skp, peak_tmac)
+        if rank == 0:
+            secondary.update(strong)
 
     # ------------------------------------------------------------------ CPU baseline (rank 0, N = 1)
     cpu = None
@@ -468,7 +499,11 @@ def run_gpu(args):
         'config': {'workload': 'config 2: mean+variance, %d DPs x %d rows per GPU, u=16 l=4 ns=3, %d encryptions + %d proofs created + %d verified per GPU per step'
                    % (ndp, rows, n, n, n), 'l2': 'flushed between steps (256 MiB memset inside the timed region)', 'sharding': 'DPs per rank; all-gather of 5x128 B partial aggregates'},
         'clocks': clocks.summary(),
-        'e2e': {'value': e2e_val, 'unit': 'proofs/s', 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h), 'ms_per_step': e2e_s / args.steps * 1e3},
+        'e2e': {'value': e2e_val, 'unit': 'proofs/s', 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
+                'ms_per_step': e2e_s['pageable'] / args.steps * 1e3,
+                'host_buffers': 'pageable numpy arrays (as a cgo caller passes Go slices), staged through the context\'s pinned area'},
+        'e2e_pinned': {'value': world * n * args.steps / e2e_s['pinned'], 'unit': 'proofs/s', 'ms_per_step': e2e_s['pinned'] / args.steps * 1e3,
+                       'host_buffers': 'pinned (torch pin_memory): copied directly'},
         'gpu_launches': int(launches),
         'roofline': roofline,
         'kernels_ms_per_launch': {k: round(v['ms_per_launch'], 4) for k, v in prof.items()},
@@ -580,6 +615,124 @@ def secondary_rates(be, lib, torch, dev, stream, ck, vp, peak_tmac, skp):
     out['proofs_verified_per_s_20k_batch'] = npf / ms * 1e3
     out['verify_roofline_frac_20k_batch'] = npf * M_VERIFY_PROOF * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
     out.update(secondary_rates_ed(be, lib, torch, dev, timed, ck, vp, peak_tmac, g))
+    return out
+
+
+def strong_scaling(be, lib, torch, dist, dev, stream, ck, vp, rank, world, skp, peak_tmac):
+    """FIXED total work split over the ranks (the headline step is weak scaling: every rank brings its own providers).
+    config 5: 10^5 range proofs (ns=3, u=16, l=4, 1 % tampered) split by proof index, accept bytes gathered over NCCL and
+    compared with the expected vector; config 4: 1,000 providers x 1,000 bins split by provider, local fold, all-gather,
+    root fold, decryption. With N > 1 rank 0 afterwards runs the whole job alone, so each line carries its own
+    efficiency t_1 / (N t_N) measured in the same process on the same GPU."""
+    from drynx_b200.sharding import gather_and_fold, gather_accept_bytes, shard_range
+    out = {}
+
+    def timed(fn, reps, everyone=True):
+        fn()
+        torch.cuda.synchronize()
+        if everyone and world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        if everyone and world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    # ---- config 5
+    NP = 100000
+    size = be.proof_size(NS, L)
+    tampered = lambda idx: idx % 100 == 7
+
+    def make_proofs(lo, hi):
+        k = hi - lo
+        g = np.random.default_rng([5, lo])
+        rb = np.frombuffer(g.bytes(32 * k * (1 + L * (3 + NS))), np.uint8).copy()
+        rb[::32] &= 0x7f
+        sid = torch.from_numpy(((np.arange(lo, hi)) % NOUT).astype(np.int32)).to(dev)
+        sec = torch.from_numpy(g.integers(0, U ** L, size=k, dtype=np.int64)).to(dev)
+        r = torch.from_numpy(rb[:32 * k]).to(dev)
+        rnd = torch.from_numpy(rb[32 * k:]).to(dev)
+        ct = torch.empty(k * 128, dtype=torch.uint8, device=dev)
+        proofs = torch.empty(k * size, dtype=torch.uint8, device=dev)
+        ck(lib.drx_encrypt_dev(be.h, k, vp(sec), vp(r), vp(ct)))
+        ck(lib.drx_rp_create_dev(be.h, k, vp(sid), NS, L, vp(sec), vp(r), vp(ct), vp(rnd), vp(proofs)))
+        bad = torch.from_numpy(np.nonzero(tampered(np.arange(lo, hi)))[0]).to(dev)
+        proofs.view(k, size)[bad, 170] ^= 1          # a byte of Zr
+        return sid, proofs
+
+    def verify_job(lo, hi, everyone):
+        sid, proofs = make_proofs(lo, hi)
+        ok = torch.empty(hi - lo, dtype=torch.uint8, device=dev)
+        res = {}
+
+        def run():
+            ck(lib.drx_rp_verify_dev(be.h, hi - lo, vp(sid), NS, L, vp(proofs), vp(ok)))
+            res['all'] = gather_accept_bytes(ok, NP, rank, world, dist) if everyone else ok
+        ms = timed(run, 2, everyone)
+        want = torch.from_numpy((~tampered(np.arange(0, NP) if everyone else np.arange(lo, hi))).astype(np.uint8)).to(dev)
+        assert torch.equal(res['all'], want), 'config 5: accept bytes differ from the expected vector'
+        return ms
+    lo, hi = shard_range(NP, rank, world)
+    tN = verify_job(lo, hi, True)
+    out['verify_1e5_strong_ms'] = tN
+    out['verify_1e5_strong_proofs_per_s'] = NP / tN * 1e3
+    out['verify_1e5_strong_roofline_frac'] = NP * M_VERIFY_PROOF * MAC32_PER_M / (tN * 1e-3) / 1e12 / (peak_tmac * world)
+    if world > 1:
+        t1 = verify_job(0, NP, False) if rank == 0 else 0.0
+        out['verify_1e5_one_gpu_ms'] = t1
+        out['verify_1e5_strong_eff'] = t1 / (world * tN) if rank == 0 else None
+    torch.cuda.empty_cache()
+
+    # ---- config 4
+    NDP, V = 1000, 1000
+    g = np.random.default_rng(4)                       # the same stream on every rank: ranks slice their block out of it
+    counts_all = g.integers(0, 10, size=(NDP, V), dtype=np.int64)
+    want = counts_all.sum(axis=0)
+
+    def freq_job(lo, hi, everyone):
+        mine = hi - lo
+        counts = torch.from_numpy(counts_all[lo:hi].copy()).to(dev).reshape(-1)
+        rb = np.frombuffer(np.random.default_rng([44, lo]).bytes(32 * mine * V), np.uint8).copy()
+        rb[::32] &= 0x7f
+        r = torch.from_numpy(rb).to(dev)
+        ct = torch.empty(mine * V * 128, dtype=torch.uint8, device=dev)
+        partial = torch.empty(V * 128, dtype=torch.uint8, device=dev)
+        total = torch.empty(V * 128, dtype=torch.uint8, device=dev)
+        dec = torch.empty(V, dtype=torch.int64, device=dev)
+        w = world if everyone else 1
+
+        def fold(gathered):
+            ck(lib.drx_aggregate_dev(be.h, w, V, vp(gathered), vp(total)))
+            return total
+
+        def run():
+            ck(lib.drx_encrypt_dev(be.h, mine * V, vp(counts), vp(r), vp(ct)))
+            ck(lib.drx_aggregate_dev(be.h, mine, V, vp(ct), vp(partial)))
+            final = gather_and_fold(partial, rank, w, dist, fold)
+            if rank == 0:
+                ck(lib.drx_decrypt_dev(be.h, V, skp, vp(final), vp(dec)))
+        ms = timed(run, 3, everyone)
+        if rank == 0:
+            assert (dec.cpu().numpy() == want).all(), 'config 4: the decrypted aggregate is not the global histogram'
+        return ms
+    lo, hi = shard_range(NDP, rank, world)
+    tN = freq_job(lo, hi, True)
+    out['config4_strong_ms'] = tN
+    out['config4_strong_encs_per_s'] = NDP * V / tN * 1e3
+    if world > 1:
+        t1 = freq_job(0, NDP, False) if rank == 0 else 0.0
+        out['config4_one_gpu_ms'] = t1
+        out['config4_strong_eff'] = t1 / (world * tN) if rank == 0 else None
+    torch.cuda.empty_cache()
+    if world > 1:
+        dist.barrier()
     return out
 
 

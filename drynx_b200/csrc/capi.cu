@@ -127,6 +127,20 @@ struct Profiler {
   std::map<std::string, std::pair<double, uint64_t>> totals;  // name -> (ms, launches)
 };
 
+// Pinned staging for the host-buffer entry points. Their callers (Go slices, numpy arrays, std::vector) hand over
+// PAGEABLE memory, which cudaMemcpyAsync moves synchronously through the driver's own bounce buffers; here inputs are
+// packed into one pinned area owned by the context and leave with true asynchronous copies, and results land in the
+// same area and are copied out after the call's single stream synchronisation. The area is allocated at drx_init and
+// only grows (at the end of a call that did not fit; that call's overflow goes the direct way). Pinned caller memory
+// is recognised and copied directly.
+struct Staging {
+  unsigned char* p = nullptr;
+  size_t cap = 0, used = 0, want = 0;
+  struct Out { void* dst; size_t off, n; };
+  std::vector<Out> outs;
+};
+constexpr size_t kStageInitial = (size_t)32 << 20, kStageMax = (size_t)1 << 30, kStageMinBytes = 256;
+
 struct RpSetHost {
   int ns = 0;
   int64_t u = 0;
@@ -150,6 +164,7 @@ struct drx_ctx {
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
       sets_dev, sink, tabQ, target_aff;  // tabQ: comb table of the key-switching target key
   Arena arena;
+  Staging stage;
   Profiler prof;
   DlogModel dlog;
   std::map<int, RpSetHost> sets;
@@ -164,9 +179,90 @@ namespace {
 
 struct Guard {
   drx_ctx* c;
-  explicit Guard(drx_ctx* ctx) : c(ctx) { c->mu.lock(); cudaSetDevice(c->device); }
+  explicit Guard(drx_ctx* ctx) : c(ctx) {
+    c->mu.lock();
+    cudaSetDevice(c->device);
+    // a call that left through an error path may have staged transfers in flight: settle them before the area is reused
+    if (c->stage.used || !c->stage.outs.empty()) {
+      cudaStreamSynchronize(c->stream);
+      c->stage.outs.clear();
+      c->stage.used = 0;
+      c->stage.want = 0;
+    }
+  }
   ~Guard() { c->mu.unlock(); }
 };
+
+#define RET(x)            \
+  do {                    \
+    int r_ = (x);         \
+    if (r_) return r_;    \
+  } while (0)
+
+bool host_ptr_is_pinned(const void* ptr) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
+}
+unsigned char* stage_reserve(drx_ctx* c, size_t n) {
+  Staging& s = c->stage;
+  const size_t need = (n + 255) & ~(size_t)255;
+  s.want += need;
+  if (!s.p || s.used + need > s.cap) return nullptr;
+  unsigned char* r = s.p + s.used;
+  s.used += need;
+  return r;
+}
+// host -> device on the context's stream
+int h2d(drx_ctx* c, void* dst, const void* src, size_t n) {
+  if (!n) return 0;
+  // (a few bytes -- a key, a counter -- go the direct way: the device-buffer calls pass such arguments and return
+  // without a synchronisation, so nothing of theirs may sit in the staging area)
+  unsigned char* st = n <= kStageMinBytes || host_ptr_is_pinned(src) ? nullptr : stage_reserve(c, n);
+  if (st) {
+    memcpy(st, src, n);
+    src = st;
+  }
+  cudaError_t e = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, c->stream);
+  if (e != cudaSuccess) return fail((int)e, "cudaMemcpyAsync (to device): %s", cudaGetErrorString(e));
+  return 0;
+}
+// device -> host; the bytes are in `dst` once sync_out has returned
+int d2h(drx_ctx* c, void* dst, const void* src, size_t n) {
+  if (!n) return 0;
+  unsigned char* st = n <= kStageMinBytes || host_ptr_is_pinned(dst) ? nullptr : stage_reserve(c, n);
+  cudaError_t e = cudaMemcpyAsync(st ? (void*)st : dst, src, n, cudaMemcpyDeviceToHost, c->stream);
+  if (e != cudaSuccess) return fail((int)e, "cudaMemcpyAsync (to host): %s", cudaGetErrorString(e));
+  if (st) c->stage.outs.push_back({dst, (size_t)(st - c->stage.p), n});
+  return 0;
+}
+// the call's stream synchronisation: delivers staged results, recycles the staging area, grows it if the call overflowed
+int sync_out(drx_ctx* c) {
+  cudaError_t e = cudaStreamSynchronize(c->stream);
+  Staging& s = c->stage;
+  if (e == cudaSuccess)
+    for (const Staging::Out& o : s.outs) memcpy(o.dst, s.p + o.off, o.n);
+  s.outs.clear();
+  s.used = 0;
+  if (s.want > s.cap && s.want <= kStageMax) {
+    size_t cap = s.cap ? s.cap : kStageInitial;
+    while (cap < s.want) cap *= 2;
+    unsigned char* np = nullptr;
+    if (cudaHostAlloc((void**)&np, cap, cudaHostAllocDefault) == cudaSuccess) {
+      if (s.p) cudaFreeHost(s.p);
+      s.p = np;
+      s.cap = cap;
+    } else {
+      cudaGetLastError();  // keep the old area; oversized transfers keep going the direct way
+    }
+  }
+  s.want = 0;
+  if (e != cudaSuccess) return fail((int)e, "cudaStreamSynchronize: %s", cudaGetErrorString(e));
+  return 0;
+}
 
 // Device-buffer (`_dev`) calls are asynchronous and cannot return a malformed-input count; they add to a second
 // counter (word 1 of the buffer) that drx_take_bad reads and clears. Host-buffer calls use word 0, reset per call.
@@ -176,8 +272,8 @@ int reset_bad(drx_ctx* c) {
   return 0;
 }
 int read_bad(drx_ctx* c, int* out) {
-  CU(cudaMemcpyAsync(out, c->bad.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  RET(d2h(c, out, c->bad.p, sizeof(int)));
+  RET(sync_out(c));
   return 0;
 }
 int check_launch(const char* what) {
@@ -185,11 +281,6 @@ int check_launch(const char* what) {
   if (e != cudaSuccess) return fail((int)e, "%s launch: %s", what, cudaGetErrorString(e));
   return 0;
 }
-#define RET(x)            \
-  do {                    \
-    int r_ = (x);         \
-    if (r_) return r_;    \
-  } while (0)
 
 // Brackets the kernels `fn` launches with an event pair when profiling is on; always counts launches.
 template <class Fn>
@@ -272,6 +363,8 @@ int drx_init(drx_ctx** out, int device, const uint8_t* g1_base, const uint8_t* g
   int rc = 0;
   auto cleanup = [&](int code) { drx_free(c); return code; };
   if ((rc = c->bad.ensure(256))) return cleanup(rc);
+  if (cudaHostAlloc((void**)&c->stage.p, kStageInitial, cudaHostAllocDefault) == cudaSuccess) c->stage.cap = kStageInitial;
+  else cudaGetLastError();  // no pinned memory to be had: every transfer goes the direct way
   if ((rc = c->baseB_wire.ensure(64)) || (rc = c->baseB_aff.ensure(64)) || (rc = c->g2_wire.ensure(128)) ||
       (rc = c->g2_aff.ensure(128)) || (rc = c->gtB.ensure(kGtBytes)) || (rc = c->tabB.ensure(kCombPoints * 64)) ||
       (rc = c->tabGtB.ensure(kCombPoints * kGtBytes)) || (rc = c->tabG2.ensure(kCombPoints * 128)))
@@ -297,6 +390,8 @@ void drx_free(drx_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
+  if (c->stage.p) cudaFreeHost(c->stage.p);
+  c->stage.p = nullptr;
   for (DevBuf* b : {&c->baseB_aff, &c->baseB_wire, &c->g2_aff, &c->g2_wire, &c->gtB, &c->tabB, &c->tabP, &c->pub_aff,
                     &c->tabGtB, &c->tabG2, &c->dlog_keys, &c->dlog_vals, &c->bad, &c->sets_dev, &c->sink, &c->tabQ,
                     &c->target_aff, &c->ed_pt,
@@ -329,8 +424,8 @@ int drx_set_stream(drx_ctx* c, void* cuda_stream) {
 static int take_pairing_error(drx_ctx* c) {
   unsigned int err = 0;
   unsigned int* d_err = (unsigned int*)c->bad.p + 48;  // kUcErrWord (capi_rp.inc); bytes 64..95 of the buffer hold the key-switching secret
-  CU(cudaMemcpyAsync(&err, d_err, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  RET(d2h(c, &err, d_err, sizeof(err)));
+  RET(sync_out(c));
   if (!err) return 0;
   CU(cudaMemsetAsync(d_err, 0, sizeof(err), c->stream));
   return fail(-5, "range-proof verification: the pairing kernel abandoned a wait on the device (results invalid; retry the call)");
@@ -338,15 +433,15 @@ static int take_pairing_error(drx_ctx* c) {
 int drx_synchronize(drx_ctx* c) {
   if (!c) return fail(-1, "null context");
   Guard g(c);
-  CU(cudaStreamSynchronize(c->stream));
+  RET(sync_out(c));
   return take_pairing_error(c);
 }
 int drx_take_bad(drx_ctx* c, int* n_bad) {
   if (!c || !n_bad) return fail(-1, "null argument");
   Guard g(c);
-  CU(cudaMemcpyAsync(n_bad, dev_bad(c), sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  RET(d2h(c, n_bad, dev_bad(c), sizeof(int)));
   CU(cudaMemsetAsync(dev_bad(c), 0, sizeof(int), c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  RET(sync_out(c));
   return 0;
 }
 uint64_t drx_launch_count(const drx_ctx* c) { return c ? c->launches : 0; }
@@ -430,11 +525,11 @@ int drx_reduce_rows(drx_ctx* c, size_t ndp, size_t nrows, const int64_t* rows, i
   a.plan_reset();
   size_t oi = a.plan(ndp * nrows * 8), oo = a.plan(ndp * w * 8);
   RET(a.commit());
-  if (nrows) CU(cudaMemcpyAsync(a.at<void>(oi), rows, ndp * nrows * 8, cudaMemcpyHostToDevice, c->stream));
+  if (nrows) RET(h2d(c, a.at<void>(oi), rows, ndp * nrows * 8));
   timed(c, "k_reduce_rows", [&] { return launch_reduce_rows(c->stream, ndp, nrows, a.at<int64_t>(oi), mode, a.at<int64_t>(oo)); });
   RET(check_launch("reduce_rows"));
-  CU(cudaMemcpyAsync(out, a.at<void>(oo), ndp * w * 8, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  RET(d2h(c, out, a.at<void>(oo), ndp * w * 8));
+  RET(sync_out(c));
   return 0;
 }
 
@@ -451,12 +546,12 @@ int drx_freq_count(drx_ctx* c, size_t ndp, size_t nrows, const int64_t* rows, in
   size_t oi = a.plan(ndp * nrows * 8), oo = a.plan(ndp * (size_t)nbins * 8);
   RET(a.commit());
   RET(reset_bad(c));
-  if (nrows) CU(cudaMemcpyAsync(a.at<void>(oi), rows, ndp * nrows * 8, cudaMemcpyHostToDevice, c->stream));
+  if (nrows) RET(h2d(c, a.at<void>(oi), rows, ndp * nrows * 8));
   timed(c, "k_freq_count", [&] {
     return launch_freq_count(c->stream, ndp, nrows, a.at<int64_t>(oi), qmin, nbins, a.at<int64_t>(oo), (int*)c->bad.p);
   });
   RET(check_launch("freq_count"));
-  CU(cudaMemcpyAsync(out, a.at<void>(oo), ndp * (size_t)nbins * 8, cudaMemcpyDeviceToHost, c->stream));
+  RET(d2h(c, out, a.at<void>(oo), ndp * (size_t)nbins * 8));
   int bad = 0;
   RET(read_bad(c, &bad));
   if (bad) return fail(-2, "drx_freq_count: %d values outside [%lld, %lld]", bad, (long long)qmin, (long long)qmax);
@@ -483,21 +578,21 @@ int drx_logreg_coefficients(drx_ctx* c, size_t ndp, const size_t* rec_off, int d
   std::vector<size_t> off(rec_off, rec_off + ndp + 1);
   for (auto& v : off) v -= rec_off[0];
   cudaStream_t st = c->stream;
-  CU(cudaMemcpyAsync(a.at<void>(oo), off.data(), (ndp + 1) * 8, cudaMemcpyHostToDevice, st));
+  RET(h2d(c, a.at<void>(oo), off.data(), (ndp + 1) * 8));
   if (nrec) {
-    CU(cudaMemcpyAsync(a.at<void>(ox), x + rec_off[0] * d, nrec * d * 8, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(a.at<void>(oy), y + rec_off[0], nrec * 8, cudaMemcpyHostToDevice, st));
+    RET(h2d(c, a.at<void>(ox), x + rec_off[0] * d, nrec * d * 8));
+    RET(h2d(c, a.at<void>(oy), y + rec_off[0], nrec * 8));
   }
-  CU(cudaMemcpyAsync(a.at<void>(om), means, d * 8, cudaMemcpyHostToDevice, st));
-  CU(cudaMemcpyAsync(a.at<void>(os), sds, d * 8, cudaMemcpyHostToDevice, st));
-  CU(cudaStreamSynchronize(st));  // `off` is a stack-owned staging vector
+  RET(h2d(c, a.at<void>(om), means, d * 8));
+  RET(h2d(c, a.at<void>(os), sds, d * 8));
+  RET(sync_out(c));  // `off` is a stack-owned staging vector
   timed(c, "k_logreg_coeffs", [&] {
     return launch_logreg_coeffs(st, ndp, nrec, a.at<size_t>(oo), d, k, a.at<double>(ox), a.at<int64_t>(oy), a.at<double>(om),
                                 a.at<double>(os), precision, a.at<double>(oxs), a.at<int64_t>(oc));
   });
   RET(check_launch("logreg_coefficients"));
-  CU(cudaMemcpyAsync(out, a.at<void>(oc), ndp * ncoef * 8, cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
+  RET(d2h(c, out, a.at<void>(oc), ndp * ncoef * 8));
+  RET(sync_out(c));
   return 0;
 }
 
@@ -529,7 +624,7 @@ int drx_set_pubkey(drx_ctx* c, const uint8_t P[64]) {
   size_t o = a.plan(64);
   RET(a.commit());
   RET(reset_bad(c));
-  CU(cudaMemcpyAsync(a.at<uint8_t>(o), P, 64, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<uint8_t>(o), P, 64));
   c->launches += launch_g1_from_wire(c->stream, 1, a.at<uint8_t>(o), c->pub_aff.p, (int*)c->bad.p);
   c->launches += launch_comb_table_g1(c->stream, 1, c->pub_aff.p, c->tabP.p);
   RET(check_launch("set_pubkey"));
@@ -558,14 +653,14 @@ int drx_encrypt(drx_ctx* c, size_t n, const int64_t* m, const uint8_t* r, uint8_
   a.plan_reset();
   size_t om = a.plan(n * 8), orr = a.plan(n * 32), oc = a.plan(n * 128);
   RET(a.commit());
-  CU(cudaMemcpyAsync(a.at<void>(om), m, n * 8, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(a.at<void>(orr), r, n * 32, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<void>(om), m, n * 8));
+  RET(h2d(c, a.at<void>(orr), r, n * 32));
   timed(c, "k_encrypt", [&] {
     return launch_encrypt(c->stream, n, a.at<int64_t>(om), a.at<uint8_t>(orr), c->tabB.p, c->tabP.p, a.at<uint8_t>(oc));
   });
   RET(check_launch("encrypt"));
-  CU(cudaMemcpyAsync(ct, a.at<void>(oc), n * 128, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  RET(d2h(c, ct, a.at<void>(oc), n * 128));
+  RET(sync_out(c));
   return 0;
 }
 
@@ -579,14 +674,14 @@ int drx_encrypt_scalar(drx_ctx* c, size_t n, const uint8_t* m, const uint8_t* r,
   a.plan_reset();
   size_t om = a.plan(n * 32), orr = a.plan(n * 32), oc = a.plan(n * 128);
   RET(a.commit());
-  CU(cudaMemcpyAsync(a.at<void>(om), m, n * 32, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(a.at<void>(orr), r, n * 32, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<void>(om), m, n * 32));
+  RET(h2d(c, a.at<void>(orr), r, n * 32));
   timed(c, "k_encrypt", [&] {
     return launch_encrypt_scalar(c->stream, n, a.at<uint8_t>(om), a.at<uint8_t>(orr), c->tabB.p, c->tabP.p, a.at<uint8_t>(oc));
   });
   RET(check_launch("encrypt_scalar"));
-  CU(cudaMemcpyAsync(ct, a.at<void>(oc), n * 128, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  RET(d2h(c, ct, a.at<void>(oc), n * 128));
+  RET(sync_out(c));
   return 0;
 }
 
@@ -628,10 +723,10 @@ int drx_aggregate(drx_ctx* c, size_t ndp, size_t v, const uint8_t* const* cts, u
   RET(reset_bad(c));
   for (size_t d = 0; d < ndp; d++) {
     if (!cts[d]) return fail(-1, "drx_aggregate: cts[%zu] is NULL", d);
-    CU(cudaMemcpyAsync(a.at<uint8_t>(oi) + d * v * 128, cts[d], v * 128, cudaMemcpyHostToDevice, c->stream));
+    RET(h2d(c, a.at<uint8_t>(oi) + d * v * 128, cts[d], v * 128));
   }
   RET(aggregate_on_device(c, ndp, v, a.at<uint8_t>(oi), a.at<void>(os), slices, a.at<uint8_t>(oo), (int*)c->bad.p));
-  CU(cudaMemcpyAsync(out, a.at<void>(oo), v * 128, cudaMemcpyDeviceToHost, c->stream));
+  RET(d2h(c, out, a.at<void>(oo), v * 128));
   int bad = 0;
   RET(read_bad(c, &bad));
   if (bad) return fail(-2, "drx_aggregate: %d malformed points", bad);
@@ -658,7 +753,7 @@ int drx_dlog_table(drx_ctx* c, int64_t limit) {
   RET(ensure_dlog(c));
   bool found;
   c->dlog.resolve(limit < kMaxHomomorphicInt ? limit : INT64_MIN, true, &found);
-  CU(cudaStreamSynchronize(c->stream));
+  RET(sync_out(c));
   return 0;
 }
 
@@ -673,7 +768,7 @@ int drx_set_target_pubkey(drx_ctx* c, const uint8_t Q[64]) {
   size_t o = a.plan(64);
   RET(a.commit());
   RET(reset_bad(c));
-  CU(cudaMemcpyAsync(a.at<uint8_t>(o), Q, 64, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<uint8_t>(o), Q, 64));
   c->launches += launch_g1_from_wire(c->stream, 1, a.at<uint8_t>(o), c->target_aff.p, (int*)c->bad.p);
   c->launches += launch_comb_table_g1(c->stream, 1, c->target_aff.p, c->tabQ.p);
   RET(check_launch("set_target_pubkey"));
@@ -690,7 +785,7 @@ int drx_keyswitch_dev(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t*
   Guard g(c);
   if (!c->have_target) return fail(-1, "drx_keyswitch: call drx_set_target_pubkey first");
   // the key travels through the tail of the 256-byte flag buffer
-  CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, (uint8_t*)c->bad.p + 64, sk, 32));
   timed(c, "k_keyswitch", [&] {
     return launch_keyswitch(c->stream, n, (uint8_t*)c->bad.p + 64, d_rb, d_v, c->tabB.p, c->tabQ.p, d_cv, d_rb_neg,
                             dev_bad(c));
@@ -710,16 +805,16 @@ int drx_keyswitch(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* rb,
   size_t orb = a.plan(n * 64), ov = a.plan(n * 32), oc = a.plan(n * 128), on = a.plan(rb_neg ? n * 64 : 0);
   RET(a.commit());
   RET(reset_bad(c));
-  CU(cudaMemcpyAsync(a.at<void>(orb), rb, n * 64, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(a.at<void>(ov), v, n * 32, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<void>(orb), rb, n * 64));
+  RET(h2d(c, a.at<void>(ov), v, n * 32));
+  RET(h2d(c, (uint8_t*)c->bad.p + 64, sk, 32));
   timed(c, "k_keyswitch", [&] {
     return launch_keyswitch(c->stream, n, (uint8_t*)c->bad.p + 64, a.at<uint8_t>(orb), a.at<uint8_t>(ov), c->tabB.p,
                             c->tabQ.p, a.at<uint8_t>(oc), rb_neg ? a.at<uint8_t>(on) : nullptr, (int*)c->bad.p);
   });
   RET(check_launch("keyswitch"));
-  CU(cudaMemcpyAsync(cv, a.at<void>(oc), n * 128, cudaMemcpyDeviceToHost, c->stream));
-  if (rb_neg) CU(cudaMemcpyAsync(rb_neg, a.at<void>(on), n * 64, cudaMemcpyDeviceToHost, c->stream));
+  RET(d2h(c, cv, a.at<void>(oc), n * 128));
+  if (rb_neg) RET(d2h(c, rb_neg, a.at<void>(on), n * 64));
   int bad = 0;
   RET(read_bad(c, &bad));
   if (bad) return fail(-2, "drx_keyswitch: %d malformed points", bad);
@@ -744,13 +839,13 @@ int drx_ct_scalar_mul(drx_ctx* c, size_t n, const uint8_t* s, const uint8_t* ct,
   size_t os = a.plan(n * 32), oc = a.plan(n * 128), oo = a.plan(n * 128);
   RET(a.commit());
   RET(reset_bad(c));
-  CU(cudaMemcpyAsync(a.at<void>(os), s, n * 32, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(a.at<void>(oc), ct, n * 128, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<void>(os), s, n * 32));
+  RET(h2d(c, a.at<void>(oc), ct, n * 128));
   timed(c, "k_ct_scalar_mul", [&] {
     return launch_ct_scalar_mul(c->stream, n, a.at<uint8_t>(os), a.at<uint8_t>(oc), a.at<uint8_t>(oo), (int*)c->bad.p);
   });
   RET(check_launch("ct_scalar_mul"));
-  CU(cudaMemcpyAsync(out, a.at<void>(oo), n * 128, cudaMemcpyDeviceToHost, c->stream));
+  RET(d2h(c, out, a.at<void>(oo), n * 128));
   int bad = 0;
   RET(read_bad(c, &bad));
   if (bad) return fail(-2, "drx_ct_scalar_mul: %d malformed points", bad);
@@ -776,15 +871,15 @@ int drx_shuffle_rerandomize(drx_ctx* c, size_t lines, size_t nq, const int32_t* 
   size_t op = a.plan(lines * 4), oi = a.plan(n * 128), ob = a.plan(n * 32), oo = a.plan(n * 128);
   RET(a.commit());
   RET(reset_bad(c));
-  CU(cudaMemcpyAsync(a.at<void>(op), pi, lines * 4, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(a.at<void>(oi), in, n * 128, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(a.at<void>(ob), beta, n * 32, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<void>(op), pi, lines * 4));
+  RET(h2d(c, a.at<void>(oi), in, n * 128));
+  RET(h2d(c, a.at<void>(ob), beta, n * 32));
   timed(c, "k_shuffle_rerandomize", [&] {
     return launch_shuffle_rerandomize(c->stream, lines, nq, a.at<int32_t>(op), a.at<uint8_t>(oi), a.at<uint8_t>(ob),
                                       c->tabB.p, c->tabP.p, a.at<uint8_t>(oo), (int*)c->bad.p);
   });
   RET(check_launch("shuffle_rerandomize"));
-  CU(cudaMemcpyAsync(out, a.at<void>(oo), n * 128, cudaMemcpyDeviceToHost, c->stream));
+  RET(d2h(c, out, a.at<void>(oo), n * 128));
   int bad = 0;
   RET(read_bad(c, &bad));
   if (bad) return fail(-2, "drx_shuffle_rerandomize: %d malformed points", bad);
@@ -811,16 +906,16 @@ int drx_schnorr_verify(drx_ctx* c, size_t n, const uint8_t* pub, const uint8_t* 
   a.plan_reset();
   size_t op = a.plan(n * 64), os = a.plan(n * 96), od = a.plan(n * 64), oo = a.plan(n);
   RET(a.commit());
-  CU(cudaMemcpyAsync(a.at<void>(op), pub, n * 64, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(a.at<void>(os), sig, n * 96, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(a.at<void>(od), digest, n * 64, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<void>(op), pub, n * 64));
+  RET(h2d(c, a.at<void>(os), sig, n * 96));
+  RET(h2d(c, a.at<void>(od), digest, n * 64));
   timed(c, "k_schnorr_verify", [&] {
     return launch_schnorr_verify(c->stream, n, a.at<uint8_t>(op), a.at<uint8_t>(os), a.at<uint8_t>(od), c->tabB.p,
                                  a.at<uint8_t>(oo));
   });
   RET(check_launch("schnorr_verify"));
-  CU(cudaMemcpyAsync(ok, a.at<void>(oo), n, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  RET(d2h(c, ok, a.at<void>(oo), n));
+  RET(sync_out(c));
   return 0;
 }
 
@@ -829,7 +924,7 @@ int drx_decrypt_dev(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* d
   Guard g(c);
   RET(ensure_dlog(c));
   // the key travels through the tail of the 256-byte flag buffer
-  CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, (uint8_t*)c->bad.p + 64, sk, 32));
   timed(c, "k_decrypt", [&] {
     return launch_decrypt(c->stream, n, (uint8_t*)c->bad.p + 64, d_ct, c->dlog_keys.p, (uint32_t*)c->dlog_vals.p, d_out,
                           dev_bad(c));
@@ -844,15 +939,15 @@ static int decrypt_raw(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t
   size_t oc = a.plan(n * 128), oo = a.plan(n * 8);
   RET(a.commit());
   RET(reset_bad(c));
-  CU(cudaMemcpyAsync(a.at<void>(oc), ct, n * 128, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync((uint8_t*)c->bad.p + 64, sk, 32, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<void>(oc), ct, n * 128));
+  RET(h2d(c, (uint8_t*)c->bad.p + 64, sk, 32));
   timed(c, "k_decrypt", [&] {
     return launch_decrypt(c->stream, n, (uint8_t*)c->bad.p + 64, a.at<uint8_t>(oc), c->dlog_keys.p,
                           (uint32_t*)c->dlog_vals.p, a.at<int64_t>(oo), (int*)c->bad.p);
   });
   RET(check_launch("decrypt"));
   raw.resize(n);
-  CU(cudaMemcpyAsync(raw.data(), a.at<void>(oo), n * 8, cudaMemcpyDeviceToHost, c->stream));
+  RET(d2h(c, raw.data(), a.at<void>(oo), n * 8));
   int bad = 0;
   RET(read_bad(c, &bad));
   if (bad) return fail(-2, "drx_decrypt: %d malformed points", bad);
@@ -894,14 +989,14 @@ static int run_wire_op(drx_ctx* c, size_t n, const void* in1, size_t s1, const v
   size_t o1 = a.plan(n * s1), o2 = a.plan(n * s2), oo = a.plan(n * so);
   RET(a.commit());
   RET(reset_bad(c));
-  CU(cudaMemcpyAsync(a.at<void>(o1), in1, n * s1, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(a.at<void>(o2), in2, n * s2, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<void>(o1), in1, n * s1));
+  RET(h2d(c, a.at<void>(o2), in2, n * s2));
   int* bad = (int*)c->bad.p;
   if (kind == 0) c->launches += launch_pair_wire(c->stream, n, a.at<uint8_t>(o1), a.at<uint8_t>(o2), a.at<uint8_t>(oo), bad);
   if (kind == 1) c->launches += launch_g1_mul(c->stream, n, a.at<uint8_t>(o1), a.at<uint8_t>(o2), a.at<uint8_t>(oo), bad);
   if (kind == 2) c->launches += launch_g2_mul(c->stream, n, a.at<uint8_t>(o1), a.at<uint8_t>(o2), a.at<uint8_t>(oo), bad);
   RET(check_launch("wire op"));
-  CU(cudaMemcpyAsync(out, a.at<void>(oo), n * so, cudaMemcpyDeviceToHost, c->stream));
+  RET(d2h(c, out, a.at<void>(oo), n * so));
   int nb = 0;
   RET(read_bad(c, &nb));
   if (nb) return fail(-2, "%d malformed points", nb);
@@ -933,12 +1028,12 @@ int drx_mont_mul(drx_ctx* c, size_t n, int which, const uint32_t* x, const uint3
   a.plan_reset();
   size_t o1 = a.plan(n * 32), o2 = a.plan(n * 32), oo = a.plan(n * 32);
   RET(a.commit());
-  CU(cudaMemcpyAsync(a.at<void>(o1), x, n * 32, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(a.at<void>(o2), y, n * 32, cudaMemcpyHostToDevice, c->stream));
+  RET(h2d(c, a.at<void>(o1), x, n * 32));
+  RET(h2d(c, a.at<void>(o2), y, n * 32));
   c->launches += launch_mont_mul(c->stream, n, which, a.at<uint32_t>(o1), a.at<uint32_t>(o2), a.at<uint32_t>(oo));
   RET(check_launch("mont_mul"));
-  CU(cudaMemcpyAsync(r, a.at<void>(oo), n * 32, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  RET(d2h(c, r, a.at<void>(oo), n * 32));
+  RET(sync_out(c));
   return 0;
 }
 int drx_microbench(drx_ctx* c, int kind, int iters, double* ms, double* work) {

@@ -29,7 +29,8 @@ WORKER = textwrap.dedent('''
     import numpy as np, torch.distributed as dist
     import bn256_ref as R
     from conftest import Oracle, SplitMix
-    from drynx_b200.sharding import shard_range, gather_partials, fold_on_root
+    from drynx_b200.sharding import shard_range, gather_partials, fold_on_root, gather_and_fold, gather_accept_bytes
+    import torch
     dist.init_process_group('gloo')
     rank, world = dist.get_rank(), dist.get_world_size()
     orc = Oracle(); rng = SplitMix(77)
@@ -42,9 +43,19 @@ WORKER = textwrap.dedent('''
     partial = np.frombuffer(orc.aggregate(mine)[1], np.uint8)
     gathered = gather_partials(partial, world, dist)
     total = fold_on_root(gathered, rank, lambda vecs: orc.aggregate([x.tobytes() for x in vecs])[1])
+    # the call bench.py and tools/config4_multi.py make (there with CUDA tensors and drx_aggregate_dev as the fold)
+    total2 = gather_and_fold(torch.from_numpy(partial.copy()), rank, world, dist,
+                             lambda g: orc.aggregate([g[r].numpy().tobytes() for r in range(world)])[1])
+    assert (total2 is None) == (rank != 0)
+    # accept bytes of a verification split by proof index come back in proof order on every rank
+    nproofs = 11
+    plo, phi = shard_range(nproofs, rank, world)
+    mine_ok = torch.tensor([(i * 7 + 3) % 5 != 0 for i in range(plo, phi)], dtype=torch.uint8)
+    all_ok = gather_accept_bytes(mine_ok, nproofs, rank, world, dist)
+    assert all_ok.tolist() == [int((i * 7 + 3) % 5 != 0) for i in range(nproofs)]
     if rank == 0:
         whole = orc.aggregate([orc.encrypt(P, vals[d], rs[d]) for d in range(ndp)])[1]
-        assert total == whole
+        assert total == whole == total2
         orc.dlog_reset()
         out, _ = orc.decrypt(sk.to_bytes(32, 'big'), total)
         assert list(out) == [sum(vals[d][j] for d in range(ndp)) for j in range(v)]

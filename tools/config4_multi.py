@@ -19,7 +19,7 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 from drynx_b200 import Backend, _lib  # noqa: E402
-from drynx_b200.sharding import shard_range  # noqa: E402
+from drynx_b200.sharding import gather_and_fold, shard_range  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument('--out', default='')
@@ -94,13 +94,14 @@ for suite in ('bn256', 'ed25519'):
     t_enc = timed(lambda: ck(enc(be.h, mine * V, vp(counts), vp(r), vp(ct))), args.reps)
     t_agg = timed(lambda: ck(agg_dev(be.h, mine, V, vp(ct), vp(partial))), args.reps)
 
+    def fold(g_):
+        ck(agg_dev(be.h, world, V, vp(g_), vp(total)))
+        return total
+
     def gather_fold():
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, partial)
-        else:
-            gathered.copy_(partial)
-        if rank == 0:
-            ck(agg_dev(be.h, world, V, vp(gathered), vp(total)))
+        res = gather_and_fold(partial, rank, world, dist, fold, gathered=gathered)
+        if world == 1:
+            total.copy_(res)
     t_gf = timed(gather_fold, args.reps)
 
     def whole():
