@@ -367,8 +367,8 @@ def run_gpu(args):
     value = world * n * args.steps / (ms / 1e3)
 
     # ------------------------------------------------------------------ e2e: host buffers through the C ABI
-    # Two sets of host buffers: PAGEABLE numpy arrays (what a cgo caller's Go slices are; the context stages them
-    # through its pinned area) -- this is `e2e` -- and pinned ones (`e2e_pinned`, the upper bound).
+    # Two sets of host buffers: PAGEABLE numpy arrays (what a cgo caller's Go slices are; they travel through the
+    # driver's bounce buffers) -- this is `e2e` -- and pinned ones (`e2e_pinned`, the upper bound).
     keep = []
 
     def pinned(a):
@@ -501,7 +501,7 @@ def run_gpu(args):
         'clocks': clocks.summary(),
         'e2e': {'value': e2e_val, 'unit': 'proofs/s', 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
                 'ms_per_step': e2e_s['pageable'] / args.steps * 1e3,
-                'host_buffers': 'pageable numpy arrays (as a cgo caller passes Go slices), staged through the context\'s pinned area'},
+                'host_buffers': 'pageable numpy arrays (as a cgo caller passes Go slices)'},
         'e2e_pinned': {'value': world * n * args.steps / e2e_s['pinned'], 'unit': 'proofs/s', 'ms_per_step': e2e_s['pinned'] / args.steps * 1e3,
                        'host_buffers': 'pinned (torch pin_memory): copied directly'},
         'gpu_launches': int(launches),

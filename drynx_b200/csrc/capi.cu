@@ -127,20 +127,6 @@ struct Profiler {
   std::map<std::string, std::pair<double, uint64_t>> totals;  // name -> (ms, launches)
 };
 
-// Pinned staging for the host-buffer entry points. Their callers (Go slices, numpy arrays, std::vector) hand over
-// PAGEABLE memory, which cudaMemcpyAsync moves synchronously through the driver's own bounce buffers; here inputs are
-// packed into one pinned area owned by the context and leave with true asynchronous copies, and results land in the
-// same area and are copied out after the call's single stream synchronisation. The area is allocated at drx_init and
-// only grows (at the end of a call that did not fit; that call's overflow goes the direct way). Pinned caller memory
-// is recognised and copied directly.
-struct Staging {
-  unsigned char* p = nullptr;
-  size_t cap = 0, used = 0, want = 0;
-  struct Out { void* dst; size_t off, n; };
-  std::vector<Out> outs;
-};
-constexpr size_t kStageInitial = (size_t)32 << 20, kStageMax = (size_t)1 << 30, kStageMinBytes = 256;
-
 struct RpSetHost {
   int ns = 0;
   int64_t u = 0;
@@ -164,7 +150,6 @@ struct drx_ctx {
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
       sets_dev, sink, tabQ, target_aff;  // tabQ: comb table of the key-switching target key
   Arena arena;
-  Staging stage;
   Profiler prof;
   DlogModel dlog;
   std::map<int, RpSetHost> sets;
@@ -179,17 +164,7 @@ namespace {
 
 struct Guard {
   drx_ctx* c;
-  explicit Guard(drx_ctx* ctx) : c(ctx) {
-    c->mu.lock();
-    cudaSetDevice(c->device);
-    // a call that left through an error path may have staged transfers in flight: settle them before the area is reused
-    if (c->stage.used || !c->stage.outs.empty()) {
-      cudaStreamSynchronize(c->stream);
-      c->stage.outs.clear();
-      c->stage.used = 0;
-      c->stage.want = 0;
-    }
-  }
+  explicit Guard(drx_ctx* ctx) : c(ctx) { c->mu.lock(); cudaSetDevice(c->device); }
   ~Guard() { c->mu.unlock(); }
 };
 
@@ -199,67 +174,26 @@ struct Guard {
     if (r_) return r_;    \
   } while (0)
 
-bool host_ptr_is_pinned(const void* ptr) {
-  cudaPointerAttributes at;
-  if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) {
-    cudaGetLastError();
-    return false;
-  }
-  return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
-}
-unsigned char* stage_reserve(drx_ctx* c, size_t n) {
-  Staging& s = c->stage;
-  const size_t need = (n + 255) & ~(size_t)255;
-  s.want += need;
-  if (!s.p || s.used + need > s.cap) return nullptr;
-  unsigned char* r = s.p + s.used;
-  s.used += need;
-  return r;
-}
-// host -> device on the context's stream
+// Transfers of the host-buffer entry points. Callers hand over pageable memory (Go slices, numpy arrays,
+// std::vector), which cudaMemcpyAsync moves through the driver's own pinned bounce buffers, chunk by chunk with the
+// copy and the DMA overlapped. A staging area inside the context was built and measured in round 2 and lost to that
+// path (config-2 step from pageable numpy arrays: 7.21 ms with the driver's path, 7.66 ms staged with one host thread,
+// 8.26 ms staged with four; from pinned memory 6.5-6.9 ms either way), so the wrappers below copy directly; they
+// remain the one place where a different transfer policy would go.
 int h2d(drx_ctx* c, void* dst, const void* src, size_t n) {
   if (!n) return 0;
-  // (a few bytes -- a key, a counter -- go the direct way: the device-buffer calls pass such arguments and return
-  // without a synchronisation, so nothing of theirs may sit in the staging area)
-  unsigned char* st = n <= kStageMinBytes || host_ptr_is_pinned(src) ? nullptr : stage_reserve(c, n);
-  if (st) {
-    memcpy(st, src, n);
-    src = st;
-  }
   cudaError_t e = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, c->stream);
   if (e != cudaSuccess) return fail((int)e, "cudaMemcpyAsync (to device): %s", cudaGetErrorString(e));
   return 0;
 }
-// device -> host; the bytes are in `dst` once sync_out has returned
 int d2h(drx_ctx* c, void* dst, const void* src, size_t n) {
   if (!n) return 0;
-  unsigned char* st = n <= kStageMinBytes || host_ptr_is_pinned(dst) ? nullptr : stage_reserve(c, n);
-  cudaError_t e = cudaMemcpyAsync(st ? (void*)st : dst, src, n, cudaMemcpyDeviceToHost, c->stream);
+  cudaError_t e = cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, c->stream);
   if (e != cudaSuccess) return fail((int)e, "cudaMemcpyAsync (to host): %s", cudaGetErrorString(e));
-  if (st) c->stage.outs.push_back({dst, (size_t)(st - c->stage.p), n});
   return 0;
 }
-// the call's stream synchronisation: delivers staged results, recycles the staging area, grows it if the call overflowed
 int sync_out(drx_ctx* c) {
   cudaError_t e = cudaStreamSynchronize(c->stream);
-  Staging& s = c->stage;
-  if (e == cudaSuccess)
-    for (const Staging::Out& o : s.outs) memcpy(o.dst, s.p + o.off, o.n);
-  s.outs.clear();
-  s.used = 0;
-  if (s.want > s.cap && s.want <= kStageMax) {
-    size_t cap = s.cap ? s.cap : kStageInitial;
-    while (cap < s.want) cap *= 2;
-    unsigned char* np = nullptr;
-    if (cudaHostAlloc((void**)&np, cap, cudaHostAllocDefault) == cudaSuccess) {
-      if (s.p) cudaFreeHost(s.p);
-      s.p = np;
-      s.cap = cap;
-    } else {
-      cudaGetLastError();  // keep the old area; oversized transfers keep going the direct way
-    }
-  }
-  s.want = 0;
   if (e != cudaSuccess) return fail((int)e, "cudaStreamSynchronize: %s", cudaGetErrorString(e));
   return 0;
 }
@@ -363,8 +297,6 @@ int drx_init(drx_ctx** out, int device, const uint8_t* g1_base, const uint8_t* g
   int rc = 0;
   auto cleanup = [&](int code) { drx_free(c); return code; };
   if ((rc = c->bad.ensure(256))) return cleanup(rc);
-  if (cudaHostAlloc((void**)&c->stage.p, kStageInitial, cudaHostAllocDefault) == cudaSuccess) c->stage.cap = kStageInitial;
-  else cudaGetLastError();  // no pinned memory to be had: every transfer goes the direct way
   if ((rc = c->baseB_wire.ensure(64)) || (rc = c->baseB_aff.ensure(64)) || (rc = c->g2_wire.ensure(128)) ||
       (rc = c->g2_aff.ensure(128)) || (rc = c->gtB.ensure(kGtBytes)) || (rc = c->tabB.ensure(kCombPoints * 64)) ||
       (rc = c->tabGtB.ensure(kCombPoints * kGtBytes)) || (rc = c->tabG2.ensure(kCombPoints * 128)))
@@ -390,8 +322,6 @@ void drx_free(drx_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
-  if (c->stage.p) cudaFreeHost(c->stage.p);
-  c->stage.p = nullptr;
   for (DevBuf* b : {&c->baseB_aff, &c->baseB_wire, &c->g2_aff, &c->g2_wire, &c->gtB, &c->tabB, &c->tabP, &c->pub_aff,
                     &c->tabGtB, &c->tabG2, &c->dlog_keys, &c->dlog_vals, &c->bad, &c->sets_dev, &c->sink, &c->tabQ,
                     &c->target_aff, &c->ed_pt,
