@@ -11,7 +11,16 @@ namespace drx {
 
 DRX_HD uint64_t rotl64(uint64_t x, int s) { return s ? (x << s) | (x >> (64 - s)) : x; }
 
-DRX_NI void keccak_f1600(uint64_t st[25]) {
+// -DDRX_KECCAK_INLINE=1 (experiment builds only) restores the inlined, fully unrolled form; see tools/keccak_repro.sh
+#ifndef DRX_KECCAK_INLINE
+#define DRX_KECCAK_INLINE 0
+#endif
+#if DRX_KECCAK_INLINE
+#define DRX_KECCAK_ATTR DRX_HD
+#else
+#define DRX_KECCAK_ATTR DRX_NI
+#endif
+DRX_KECCAK_ATTR void keccak_f1600(uint64_t st[25]) {
   const uint64_t RC[24] = {
       0x0000000000000001ULL, 0x0000000000008082ULL, 0x800000000000808aULL, 0x8000000080008000ULL,
       0x000000000000808bULL, 0x0000000080000001ULL, 0x8000000080008081ULL, 0x8000000000008009ULL,
@@ -20,8 +29,10 @@ DRX_NI void keccak_f1600(uint64_t st[25]) {
       0x8000000000008002ULL, 0x8000000000000080ULL, 0x000000000000800aULL, 0x800000008000000aULL,
       0x8000000080008081ULL, 0x8000000000008080ULL, 0x0000000080000001ULL, 0x8000000080008008ULL};
   const int ROT[25] = {0, 1, 62, 28, 27, 36, 44, 6, 55, 20, 3, 10, 43, 25, 39, 41, 45, 15, 21, 8, 18, 2, 61, 56, 14};
-#if defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__) && !DRX_KECCAK_INLINE
 #pragma unroll 1
+#elif defined(__CUDA_ARCH__)
+#pragma unroll
 #endif
   for (int round = 0; round < 24; round++) {
     uint64_t c[5], d[5], b[25];
@@ -38,7 +49,7 @@ DRX_NI void keccak_f1600(uint64_t st[25]) {
 
 // msg: nwords 32-bit words in memory (little-endian byte order within each word, as loaded from a byte
 // buffer); nwords*4 bytes total, any length. digest: 16 words = 64 bytes in memory order.
-DRX_NI void sha3_512_words(uint32_t digest[16], const uint32_t* msg, int nwords) {
+DRX_KECCAK_ATTR void sha3_512_words(uint32_t digest[16], const uint32_t* msg, int nwords) {
   uint64_t st[25];
   for (int i = 0; i < 25; i++) st[i] = 0;
   const int rate_words = 18;  // 72-byte rate

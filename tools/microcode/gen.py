@@ -714,7 +714,12 @@ def mont(x):
 
 def emit(g, phases, slot_of, used, G, nslots_arg, window):
     path = os.path.join(ROOT, 'drynx_b200', 'csrc', 'pairing_ucode_g%d.inc' % G)
-    rot = (lambda s_: s_ & 3) if G <= 4 else (lambda s_: (s_ >> 1) & 3)
+    # Swizzle: with two threads per program lane the 8 (G = 4) or 16 (G = 8) threads of an item read, in one instruction,
+    # chunk 2h + k of their lane's slot; bank group of that access = 4 (slot & 1) + ((2h + k) ^ swz(slot)). For lanes whose
+    # slots differ mod 4 (mod 8) the choice below makes the groups of one item all distinct (each twice for G = 8): no replays.
+    # (slot & 3, the round-1 rule for one thread per lane, put slots s and s + 2 of the two halves on the same groups:
+    # ncu counted 2.4x the ideal wavefronts.)
+    rot = (lambda s_: (s_ >> 1) & 1) if G <= 4 else (lambda s_: (s_ >> 1) & 3)
     off = lambda s_: s_ * 64 + rot(s_) * 16   # byte offset of a slot inside an item, swizzle folded in
     with open(path, 'w') as f:
         f.write('// GENERATED by tools/microcode/gen.py %d %d ... --emit -- do not edit.\n' % (G, used))
@@ -727,7 +732,7 @@ def emit(g, phases, slot_of, used, G, nslots_arg, window):
         f.write('// generator arguments (tests/test_microcode.py regenerates the program from them)\n')
         f.write('#define UC_GEN_SLOTS %d\n#define UC_GEN_WINDOW %d\n' % (nslots_arg, window))
         f.write('// A slot is 64 bytes = four 16-byte chunks; logical chunk c of slot s lives at physical chunk c ^ UC_SWZ(s)\n')
-        f.write('#define UC_SWZ(s) %s\n' % ('((s) & 3u)' if G <= 4 else '(((s) >> 1) & 3u)'))
+        f.write('#define UC_SWZ(s) %s\n' % ('(((s) >> 1) & 1u)' if G <= 4 else '(((s) >> 1) & 3u)'))
         for i, name in enumerate(OPS):
             f.write('#define UC_%s %d\n' % (name, i))
         for name, n in g.inputs.items():
