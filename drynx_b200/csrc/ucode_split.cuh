@@ -22,11 +22,15 @@ namespace drx {
 #ifndef UCS_BLOCK
 #define UCS_BLOCK 64
 #endif
-#define UCS_ITEMS_PER_BLOCK (UCS_BLOCK / UCS_TPI)
+// An item never straddles a warp (its threads meet at warp barriers): a warp holds 32 / UCS_TPI whole items; a thread
+// count that does not divide 32 (three program lanes = six threads per item: built and measured in round 2, 4.7-4.9 ms
+// against 4.34 at 6,000 checks, 129 against 123 ms at 240,000, because the product phases per item do not shrink) leaves
+// the last threads of the warp unseated.
+#define UCS_WARP_ITEMS (32 / UCS_TPI)
+#define UCS_ITEMS_PER_BLOCK ((UCS_BLOCK / 32) * UCS_WARP_ITEMS)
 #ifndef UCS_MIN_BLOCKS
 #define UCS_MIN_BLOCKS 8  // 16 warps per SM: at most 128 registers per thread
 #endif
-#define UCS_WARP_ITEMS (32 / UCS_TPI)
 #define UCS_ITEM_BYTES (UC_NSLOTS * 64)
 static_assert(UC_NSLOTS <= (int)kUcMaxSlots, "slot-image area is sized for kUcMaxSlots");
 
@@ -205,14 +209,17 @@ __device__ __forceinline__ Fp12 ucs_get_output(uint32_t S) {
 __global__ void __launch_bounds__(UCS_BLOCK, UCS_MIN_BLOCKS)
 UCS_KERNEL(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ scratch) {
   extern __shared__ __align__(128) unsigned char uc_smem[];
-  const int grp = threadIdx.x / UCS_TPI, sub = threadIdx.x % UCS_TPI;
+  const int wl = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int in_warp = wl / UCS_TPI, sub = wl % UCS_TPI;
+  const bool seated = in_warp < UCS_WARP_ITEMS;            // false for the spare threads of a six-thread layout
+  const int grp = warp * UCS_WARP_ITEMS + (seated ? in_warp : 0);
   const size_t t = (size_t)blockIdx.x * UCS_ITEMS_PER_BLOCK + grp;
-  const bool alive = t < items && prep[t].state == 0;
+  const bool alive = seated && t < items && prep[t].state == 0;
   const uint32_t S = (uint32_t)__cvta_generic_to_shared(uc_smem) + grp * UCS_ITEM_BYTES;
   if (alive && sub == 0) ucs_put_inputs(S, prep[t]);
   __syncwarp();
   ucs_run(S, sub >> 1, (uint32_t)(sub & 1), alive, 0, UC_NPHASES);
-  if (t < items && sub == 0) scratch[t].a = alive ? ucs_get_output(S) : fp12_one();
+  if (seated && t < items && sub == 0) scratch[t].a = alive ? ucs_get_output(S) : fp12_one();
 }
 
 // Dynamic variant (same scheme as UC_KERNEL_DYN in ucode_body.cuh): the program is cut into nseg segments, a task is
@@ -223,7 +230,10 @@ __global__ void __launch_bounds__(UCS_BLOCK, UCS_MIN_BLOCKS)
 UCS_KERNEL_DYN(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ scratch, uint4* __restrict__ state,
                unsigned int* __restrict__ ctrl, unsigned int nseg, unsigned int* __restrict__ err) {
   extern __shared__ __align__(128) unsigned char uc_smem[];
-  const int grp = threadIdx.x / UCS_TPI, sub = threadIdx.x % UCS_TPI, wl = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wl = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int in_warp = wl / UCS_TPI, sub = wl % UCS_TPI;
+  const bool seated = in_warp < UCS_WARP_ITEMS;
+  const int grp = warp * UCS_WARP_ITEMS + (seated ? in_warp : 0);
   const uint32_t S = (uint32_t)__cvta_generic_to_shared(uc_smem) + grp * UCS_ITEM_BYTES;
   uint4* W = reinterpret_cast<uint4*>(uc_smem + warp * UCS_WARP_ITEMS * UCS_ITEM_BYTES);
   const unsigned int ngroups = (unsigned int)((items + UCS_WARP_ITEMS - 1) / UCS_WARP_ITEMS);
@@ -235,8 +245,8 @@ UCS_KERNEL_DYN(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict
     task = __shfl_sync(0xffffffffu, task, 0);
     if (task >= ntasks) break;
     const unsigned int g = task % ngroups, seg = task / ngroups;
-    const size_t t = (size_t)g * UCS_WARP_ITEMS + wl / UCS_TPI;
-    const bool alive = t < items && prep[t].state == 0;
+    const size_t t = (size_t)g * UCS_WARP_ITEMS + (seated ? in_warp : 0);
+    const bool alive = seated && t < items && prep[t].state == 0;
     if (seg == 0) {
       if (alive && sub == 0) ucs_put_inputs(S, prep[t]);
     } else {
@@ -262,7 +272,7 @@ UCS_KERNEL_DYN(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict
       __threadfence();
       __syncwarp();
       if (wl == 0) done[g] = seg + 1;
-    } else if (t < items && sub == 0) {
+    } else if (seated && t < items && sub == 0) {
       scratch[t].a = alive ? ucs_get_output(S) : fp12_one();
     }
     __syncwarp();
