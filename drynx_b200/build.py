@@ -20,7 +20,7 @@ NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC',
               '-Xptxas', '-v'] + (['-DDRX_DEBUG_RP'] if os.environ.get('DRX_DEBUG_RP') else []) + \
     [f for f in os.environ.get('DRX_NVCC_EXTRA', '').split() if f]
-GPU_SOURCES = ['kernels_g1.cu', 'kernels_rp.cu', 'kernels_rp_ucode.cu', 'kernels_rp_ucode_s4.cu', 'kernels_rp_ucode_s8.cu', 'kernels_ed.cu', 'capi.cu']
+GPU_SOURCES = ['kernels_g1.cu', 'kernels_rp.cu', 'kernels_rp_ucode.cu', 'kernels_rp_ucode_s4.cu', 'kernels_rp_gtlanes.cu', 'kernels_rp_ucode_s8.cu', 'kernels_ed.cu', 'capi.cu']
 
 
 def _newer(target, sources):

@@ -143,8 +143,9 @@ struct drx_ctx {
   uint64_t launches = 0;
   bool have_pub = false, have_dlog = false, have_target = false;
   int opt_verify_path = 0;  // drx_set_option "rp_verify_path"
-  int opt_create_path = 0;  // drx_set_option "rp_create_path": 0 = by batch size, 1 = never the lane-cooperative kernel
+  int opt_create_path = 0;  // drx_set_option "rp_create_path": 0 = by batch size, 1 / 2 / 3 force one of the small-batch kernels
   int opt_ucode_lanes = 0;  // drx_set_option "rp_ucode_lanes": 0 = by batch size, 4 or 8
+  int opt_verify_gt = 0;    // drx_set_option "rp_verify_gt": 0 = by batch size, 2 = always the lane-group GT kernel (tests)
   int opt_agg_slices = 0;   // drx_set_option "agg_slices": 0 = sized from the SM count, else forced (experiments)
   UcTune uc_tune;           // drx_set_option "rp_ucode_mode" / "rp_ucode_resident" / "rp_ucode_nseg"
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
@@ -385,13 +386,19 @@ int drx_set_option(drx_ctx* c, const char* name, int value) {
     return 0;
   }
   if (!strcmp(name, "rp_create_path")) {
-    if (value < 0 || value > 2) return fail(-1, "rp_create_path must be 0 (auto), 1 (scratch-based split) or 2 (lane-cooperative)");
+    if (value < 0 || value > 3)
+      return fail(-1, "rp_create_path must be 0 (auto), 1 (scratch-based split), 2 (shuffle-cooperative) or 3 (GT factors on lane groups)");
     c->opt_create_path = value;
     return 0;
   }
   if (!strcmp(name, "rp_ucode_lanes")) {
     if (value != 0 && value != 4 && value != 8) return fail(-1, "rp_ucode_lanes must be 0 (auto), 4 or 8");
     c->opt_ucode_lanes = value;
+    return 0;
+  }
+  if (!strcmp(name, "rp_verify_gt")) {
+    if (value != 0 && value != 2) return fail(-1, "rp_verify_gt must be 0 (auto) or 2 (lane groups)");
+    c->opt_verify_gt = value;
     return 0;
   }
   if (!strcmp(name, "agg_slices")) {

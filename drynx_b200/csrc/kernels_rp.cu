@@ -303,9 +303,11 @@ size_t rp_scratch_bytes(size_t items) {
 }
 int launch_rp_create_fine(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
-                          const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch) {
+                          const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch,
+                          bool g2_only) {
   if (!b.items) return 0;
-  dim3 grid(grid_for(b.items, 64), 12), fin(grid_for(b.items, 64), 2);
+  // roles 0-3 are the four window quarters of V_ij (role 3 also writes Zv_ij), finish role 0 folds them
+  dim3 grid(grid_for(b.items, 64), g2_only ? 4 : 12), fin(grid_for(b.items, 64), g2_only ? 1 : 2);
   k_rp_create_fine<<<grid, 64, 0, st>>>(b, d_sets, d_secret, (const uint32_t*)d_rnd, d_rnd_off, (const Fp12*)d_tabGtB,
                                         (const uint32_t*)d_baseB_wire, (const uint32_t*)d_ct, (uint32_t*)d_proofs,
                                         (CreateFine*)d_scratch);

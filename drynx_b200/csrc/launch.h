@@ -16,6 +16,8 @@ constexpr uint32_t kDlogCap = 1u << 18;         // open-addressing slots for 100
 constexpr int kAggMaxSlices = 512;  // stage-1 slices of an aggregation (sized from the SM count, see kernels_g1.cu)
 constexpr size_t kEncryptLanesMaxItems = 16384; // encryptions up to this many use eight lanes each (latency)
 constexpr size_t kCreateLanesMaxItems = 800;   // creation items up to this many: lane-cooperative kernel (8 / 16 lanes per item)
+constexpr size_t kGtLanesCreateMaxItems = 12000; // creation items up to this many: GT factors on lane groups (measured, 12 items per proof: 100 proofs 0.44 against 0.76 ms, 500 proofs 1.05 against 1.24, 2,000 proofs 3.49 against 3.05)
+constexpr size_t kGtLanesVerifyMinItems = 12000; // verification items from this many on: GT factor on lane groups (below, its shared memory and warps get in the way of the pairing kernel: 500 proofs 4.91 against 4.57 ms; 2,000 proofs 15.1 against 15.7)
 constexpr size_t kCreateFineMaxItems = 36000; // creation items up to this many are split twelve ways (latency)
 constexpr size_t kUcodeG8MaxItems = 1000;      // pairing checks up to this many use eight program lanes per check instead of four (measured, pairing kernel: 480 checks 2.00 against 2.56 ms, 1,200 checks 2.61 against 2.60)
 
@@ -111,9 +113,16 @@ size_t rp_scratch_bytes(size_t items);
 int launch_rp_create_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
                            const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
                            const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs);
+// g2_only: just the V_ij (G2) and Zv_ij parts; the GT factors then come from launch_rp_create_gt_lanes
 int launch_rp_create_fine(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
                           const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
-                          const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch);
+                          const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch,
+                          bool g2_only = false);
+// fixed-base GT exponentiations on lane groups (kernels_rp_gtlanes.cu): a_ij of creation, T_ij of verification
+int launch_rp_create_gt_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
+                              const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB, uint8_t* d_proofs);
+int launch_rp_verify_gt_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabGtB,
+                              const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 int launch_rp_create_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
                            const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
                            const uint8_t* d_baseB_wire, const uint8_t* d_ct, uint8_t* d_proofs, void* d_scratch);

@@ -227,12 +227,14 @@ def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes, 
     backend.set_option('rp_verify_path', path)
     backend.set_option('rp_ucode_lanes', lanes)
     backend.set_option('rp_ucode_mode', mode)
+    backend.set_option('rp_verify_gt', 2 if mode == 2 else 0)   # the lane-group GT factor kernel on the task-queue runs
     try:
         ok = backend.verify_range_proofs([60] * n, [l] * n, bytes(bad), off)
     finally:
         backend.set_option('rp_verify_path', 0)
         backend.set_option('rp_ucode_lanes', 0)
         backend.set_option('rp_ucode_mode', 0)
+        backend.set_option('rp_verify_gt', 0)
     assert list(ok) == list(want) == [1, 0, 0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1]
 
 
@@ -271,9 +273,11 @@ def test_creation_kernels_agree(backend, oracle, rng):
         a, off = backend.create_range_proofs([61] * n, {61: ns}, {61: u}, [l] * n, secrets, rs, cts, rnd)
         backend.set_option('rp_create_path', 1)
         b, _ = backend.create_range_proofs([61] * n, {61: ns}, {61: u}, [l] * n, secrets, rs, cts, rnd)
+        backend.set_option('rp_create_path', 3)   # GT factors on lane groups (the automatic choice up to 36,000 items)
+        c3, _ = backend.create_range_proofs([61] * n, {61: ns}, {61: u}, [l] * n, secrets, rs, cts, rnd)
     finally:
         backend.set_option('rp_create_path', 0)
-    assert a.tobytes() == b.tobytes()
+    assert a.tobytes() == b.tobytes() == c3.tobytes()
     want, _ = oracle.rp_create(ns, u, l, Y, A, P, secrets, rs, cts, rnd, threads=8)
     assert a.tobytes() == bytes(want)
 

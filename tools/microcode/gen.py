@@ -386,6 +386,29 @@ def build_pairing(g):
     g.out('SG', sg.n)
 
 
+def build_fp12_mul(g):
+    """A <- A * B in Fp12 (tower order c0.c0 c0.c1 c0.c2 c1.c0 c1.c1 c1.c2, as csrc/tower.cuh fp12_mul). The A slots are
+    pinned: main() appends copy phases that move the product back into them, so a kernel can multiply a running value
+    by one table entry after another (fixed-base GT exponentiation) without touching slot numbers."""
+    a = [S(g, g.inp('A%d' % k)) for k in range(6)]
+    b = [S(g, g.inp('B%d' % k)) for k in range(6)]
+    g.pinned = [x.n.id for x in a]
+    c = f12_mul((a[0:3], a[3:6]), (b[0:3], b[3:6]))
+    for k, v in enumerate(c[0] + c[1]):
+        g.out('C%d' % k, v.n)
+
+
+def append_copy_back(g, phases, slot_of, G):
+    """C_k -> slot of A_k, after everything else (every A_k is dead by then)."""
+    todo = []
+    for k in range(6):
+        n = Node(g, 'COPY', g.outputs['C%d' % k])
+        slot_of[n.id] = slot_of[g.inputs['A%d' % k].id]
+        todo.append(n)
+    for i in range(0, 6, G):
+        phases.append(('COPY', todo[i:i + G]))
+
+
 # ---------------------------------------------------------------------------------------------- linear-op fusion
 def fuse(g):
     """Peephole fusion of chains of cheap linear operations into single micro-ops (fewer phases, fewer slot
@@ -507,7 +530,7 @@ def schedule(g, G, nslots, window=96):
                 best = max(best, prio[u_.id])
         prio[n.id] = best + COST.get(n.op, 1)
     remaining_users = {n.id: sum(1 for u_ in n.users if u_.id in live) for n in nodes if n.id in live}
-    out_ids = set(n.id for n in g.outputs.values())
+    out_ids = set(n.id for n in g.outputs.values()) | set(getattr(g, 'pinned', ()))   # never freed, never lent in place
     # slots: inputs pinned first
     slot_of = {}
     free = list(range(nslots - 1, -1, -1))
@@ -633,12 +656,12 @@ def fix_user_counts(g):
         n.users = seen
 
 
-def run_program(g, phases, slot_of, nslots, inputs):
+def run_program(g, phases, slot_of, nslots, inputs, want_slots=False):
     slots = [None] * nslots
     for name, n in g.inputs.items():
         if n.id in slot_of:
             slots[slot_of[n.id]] = inputs[name]
-    P = inputs['P']
+    P = inputs.get('P')
     for op, lanes in phases:
         lanes = [n for n in lanes if n is not None]
         reads = []
@@ -661,10 +684,42 @@ def run_program(g, phases, slot_of, nslots, inputs):
             writes.append((slot_of[n.id], eval_node(n, val, g, P)))
         for s, v in writes:
             slots[s] = v
+    if want_slots:
+        return slots
     return {name: slots[slot_of[n.id]] for name, n in g.outputs.items()}
 
 
+def main_gtmul(G, nslots, window):
+    """python gen.py gtmul G nslots window [--emit]: the Fp12 multiplication program (csrc/gtmul_ucode_g<G>.inc)."""
+    g = Graph()
+    build_fp12_mul(g)
+    fix_user_counts(g)
+    fuse(g)
+    phases, slot_of, used = schedule(g, G, nslots, window)
+    append_copy_back(g, phases, slot_of, G)
+    nops = sum(1 for _, l in phases for n in l if n is not None)
+    print('gtmul G=%d: %d ops in %d phases, %d slots used' % (G, nops, len(phases), used))
+    import random
+    rng = random.Random(7)
+    for _ in range(3):
+        A = [(rng.randrange(R.p), rng.randrange(R.p)) for _ in range(6)]   # w^0 .. w^5
+        B = [(rng.randrange(R.p), rng.randrange(R.p)) for _ in range(6)]
+        tower = lambda w: [w[0], w[2], w[4], w[1], w[3], w[5]]
+        inputs = {}
+        for k, (x, y) in enumerate(zip(tower(A), tower(B))):
+            inputs['A%d' % k], inputs['B%d' % k] = x, y
+        slots = run_program(g, phases, slot_of, nslots, inputs, want_slots=True)
+        got = [slots[slot_of[g.inputs['A%d' % k].id]] for k in range(6)]
+        assert got == tower(R.f12mul(A, B)), 'gtmul program disagrees with the definition'
+    print('gtmul program == bn256_ref.f12mul on random inputs (result read back from the A slots)')
+    if '--emit' in sys.argv:
+        emit(g, phases, slot_of, used, G, nslots, window, name='gtmul')
+    return g, phases, slot_of, used
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == 'gtmul':
+        return main_gtmul(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]))
     G = int(sys.argv[1]) if len(sys.argv) > 1 else 4
     nslots = int(sys.argv[2]) if len(sys.argv) > 2 else 96
     window = int(sys.argv[3]) if len(sys.argv) > 3 else 96
@@ -712,8 +767,8 @@ def mont(x):
     return (x % R.p) * (1 << 256) % R.p
 
 
-def emit(g, phases, slot_of, used, G, nslots_arg, window):
-    path = os.path.join(ROOT, 'drynx_b200', 'csrc', 'pairing_ucode_g%d.inc' % G)
+def emit(g, phases, slot_of, used, G, nslots_arg, window, name='pairing'):
+    path = os.path.join(ROOT, 'drynx_b200', 'csrc', '%s_ucode_g%d.inc' % (name, G))
     # Swizzle: with two threads per program lane the 8 (G = 4) or 16 (G = 8) threads of an item read, in one instruction,
     # chunk 2h + k of their lane's slot; bank group of that access = 4 (slot & 1) + ((2h + k) ^ swz(slot)). For lanes whose
     # slots differ mod 4 (mod 8) the choice below makes the groups of one item all distinct (each twice for G = 8): no replays.
@@ -722,10 +777,11 @@ def emit(g, phases, slot_of, used, G, nslots_arg, window):
     rot = (lambda s_: (s_ >> 1) & 1) if G <= 4 else (lambda s_: (s_ >> 1) & 3)
     off = lambda s_: s_ * 64 + rot(s_) * 16   # byte offset of a slot inside an item, swizzle folded in
     with open(path, 'w') as f:
-        f.write('// GENERATED by tools/microcode/gen.py %d %d ... --emit -- do not edit.\n' % (G, used))
-        f.write('// Lane-group micro-program of the optimal ate pairing plus the G2 membership verdict: %d Fp2 operations in\n'
+        f.write('// GENERATED by tools/microcode/gen.py %s%d %d ... --emit -- do not edit.\n' % ('' if name == 'pairing' else name + ' ', G, used))
+        what = 'the optimal ate pairing plus the G2 membership verdict' if name == 'pairing' else 'one Fp12 multiplication A <- A * B'
+        f.write('// Lane-group micro-program of %s: %d Fp2 operations in\n'
                 '// %d phases for %d program lanes,\n'
-                % (sum(1 for _, l in phases for n in l if n is not None), len(phases), G))
+                % (what, sum(1 for _, l in phases for n in l if n is not None), len(phases), G))
         f.write('// %d Fp2 slots per item. Executed with Python integers against the definition of the pairing by the generator before emission.\n' % used)
         used |= 1  # odd slot count per item: adjacent items then sit in opposite bank halves
         f.write('#define UC_G %d\n#define UC_NSLOTS %d\n#define UC_NPHASES %d\n' % (G, used, len(phases)))

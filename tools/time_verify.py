@@ -42,9 +42,10 @@ for n in [int(x) for x in (sys.argv[1:] or ['500', '8192'])]:
     assert bool((ok == 1).all())
     out.append('n=%d enc %.3f ms create %.2f ms verify %.2f ms (%.1f k proofs/s)' % (n, te, tc, tv, n / tv))
     ck(lib.drx_profile_enable(be.h, 1))
+    ck(lib.drx_rp_create_dev(be.h, n, vp(sid), NS, L, vp(sec), vp(r), vp(ct), vp(rnd), vp(proofs))); be.synchronize()
     ck(lib.drx_rp_verify_dev(be.h, n, vp(sid), NS, L, vp(proofs), vp(ok))); be.synchronize()
     parts = []
-    for k in ('k_rp_verify_hdr', 'k_rp_verify_items', 'k_rp_verify_prep', 'k_pair_ucode', 'k_rp_verify_gt', 'k_rp_verify_finish'):
+    for k in ('k_rp_create_hdr', 'k_rp_create_items', 'k_rp_create_g2', 'k_rp_verify_hdr', 'k_rp_verify_items', 'k_rp_verify_prep', 'k_pair_ucode', 'k_rp_verify_gt', 'k_rp_verify_finish'):
         tms, cnt = ctypes.c_double(), ctypes.c_uint64()
         ck(lib.drx_profile_get(be.h, k.encode(), ctypes.byref(tms), ctypes.byref(cnt)))
         if cnt.value: parts.append('%s=%.2f' % (k[2:], tms.value))
