@@ -205,7 +205,7 @@ def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes, 
     (lib/range/range_proof.go:225-236 aborts there; here the proof is rejected)."""
     ns, u, l = 3, 16, 2
     sk, P, Y, A = _setup(backend, oracle, rng, ns, u, set_id=60)
-    secrets = [0, 1, 77, 255, 200, 13, 99, 254, 5, 6, 7, 8, 9]
+    secrets = [0, 1, 77, 255, 200, 13, 99, 254, 5, 6, 7, 8, 9, 10]
     rs, cts, rnd = _make(backend, oracle, rng, P, ns, u, l, secrets)
     n = len(secrets)
     proofs, off = backend.create_range_proofs([60] * n, {60: ns}, {60: u}, [l] * n, secrets, rs, cts, rnd)
@@ -223,6 +223,8 @@ def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes, 
         i, j = [(0, 0), (1, 1), (2, 0), (0, 1)][k]
         pos = (8 + k) * size + blk + i * 544 * l + 128 * j
         bad[pos:pos + 128] = Q
+    pos = 12 * size + blk + 544 * l + 128 * l + 64                # A_10: one coordinate >= p (malformed GT element)
+    bad[pos:pos + 32] = b'\xff' * 32
     want = oracle.rp_verify(ns, u, l, Y, P, bytes(bad), off, threads=8)
     backend.set_option('rp_verify_path', path)
     backend.set_option('rp_ucode_lanes', lanes)
@@ -235,7 +237,7 @@ def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes, 
         backend.set_option('rp_ucode_lanes', 0)
         backend.set_option('rp_ucode_mode', 0)
         backend.set_option('rp_verify_gt', 0)
-    assert list(ok) == list(want) == [1, 0, 0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1]
+    assert list(ok) == list(want) == [1, 0, 0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 0, 1]
 
 
 def test_g2_inputs_outside_the_subgroup_are_malformed(backend, oracle, rng):
