@@ -979,7 +979,7 @@ int drx_microbench(drx_ctx* c, int kind, int iters, double* ms, double* work) {
   // kind 0: wide multiply-accumulate chains, 1: dependent Montgomery products (both fill the GPU: the roofline peaks);
   // kinds 10 + k / 20 + k / 30 + k: probe k (1: one chain of products, 2: three chains) with one warp per SM / one
   // warp per sub-partition / two warps per sub-partition (latency probes, profiles/r01_experiments.md); k = 3: dependent
-  // field inversions, k = 4: dependent full point additions
+  // field inversions, k = 4: dependent full point additions; kind 5 (full GPU only): chains of double-precision FMAs
   int blocks = 148 * 8, threads = 256;
   if (kind >= 10) {
     blocks = 148;
@@ -1001,7 +1001,7 @@ int drx_microbench(drx_ctx* c, int kind, int iters, double* ms, double* work) {
   cudaEventDestroy(e1);
   *ms = t;
   // wide MACs, Montgomery products, or (kinds 3 / 4) inversions / full point additions
-  const double per_thread = kind == 0 ? 16.0 * iters : kind == 2 ? 3.0 * iters : kind >= 3 ? 1.0 * iters : 2.0 * iters;
+  const double per_thread = kind == 0 || kind == 5 ? 16.0 * iters : kind == 2 ? 3.0 * iters : kind >= 3 ? 1.0 * iters : 2.0 * iters;
   *work = per_thread * blocks * threads;
   return check_launch("microbench");
 }

@@ -869,11 +869,28 @@ __global__ void __launch_bounds__(256) k_probe_jac_add(int iters, uint32_t* sink
   for (int k = 0; k < 8; k++) s ^= a.x.v[k] ^ a.y.v[k] ^ a.z.v[k];
   sink[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
+// kind 5: eight independent chains of double-precision fused multiply-adds (round toward zero, the form the
+// 52-bit-limb product technique uses: high part fma_rz(a, b, 2^104), low part fma_rz(a, b, 2^104 + 2^52 - high)) with
+// no memory traffic; 16 DFMA per step. Measures what the FP64 pipe offers beside the IMAD.WIDE figure of kind 0.
+__global__ void __launch_bounds__(256) k_probe_dfma(int iters, uint32_t* sink) {
+  double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 + blockIdx.x * 1e-9;
+  double c0 = a, c1 = b, c2 = a + b, c3 = a - b, c4 = a * 3, c5 = b * 3, c6 = a * 5, c7 = b * 5;
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      c0 = __fma_rz(a, b, c0); c1 = __fma_rz(a, c0, c1); c2 = __fma_rz(b, c1, c2); c3 = __fma_rz(a, c2, c3);
+      c4 = __fma_rz(b, c3, c4); c5 = __fma_rz(a, c4, c5); c6 = __fma_rz(b, c5, c6); c7 = __fma_rz(a, c6, c7);
+    }
+  }
+  const double s = c0 + c1 + c2 + c3 + c4 + c5 + c6 + c7;
+  sink[blockIdx.x * blockDim.x + threadIdx.x] = (uint32_t)__double_as_longlong(s);
+}
 int launch_microbench(cudaStream_t st, int kind, int iters, int blocks, int threads, uint32_t* d_sink) {
   if (kind == 0) k_probe_imad<<<blocks, threads, 0, st>>>(iters, d_sink);
   else if (kind == 2) k_probe_montmul3<<<blocks, threads, 0, st>>>(iters, d_sink);
   else if (kind == 3) k_probe_inv<<<blocks, threads, 0, st>>>(iters, d_sink);
   else if (kind == 4) k_probe_jac_add<<<blocks, threads, 0, st>>>(iters, d_sink);
+  else if (kind == 5) k_probe_dfma<<<blocks, threads, 0, st>>>(iters, d_sink);
   else k_probe_montmul<<<blocks, threads, 0, st>>>(iters, d_sink);
   return 1;
 }

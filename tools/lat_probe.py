@@ -13,3 +13,6 @@ for kind, what, it2 in ((13, 'fp_inv, 1 warp/SM', 200), (33, 'fp_inv, 2 warps/SM
                         (14, 'jac_add, 1 warp/SM', 2000), (34, 'jac_add, 2 warps/SMSP', 2000)):
     ms, work = be.microbench(kind, it2)
     print('%-24s %.3f ms, %.0f cycles per operation per warp (at 1965 MHz)' % (what, ms, ms * 1.965e6 / it2))
+ms0, w0 = be.microbench(0, 20000)
+ms5, w5 = be.microbench(5, 20000)
+print('IMAD.WIDE chains: %.2f T/s; DFMA (round toward zero) chains: %.2f T/s; ratio %.2f' % (w0 / ms0 / 1e9, w5 / ms5 / 1e9, (w5 / ms5) / (w0 / ms0)))
