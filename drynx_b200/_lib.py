@@ -55,6 +55,11 @@ SIGNATURES = {
     'drx_shuffle_rerandomize': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, VP, VP, VP]),
     'drx_shuffle_rerandomize_dev': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_size_t, VP, VP, VP, VP]),
     'drx_schnorr_verify': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP, VP]),
+    'drx_rep_commit': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_int, VP, VP, VP]),
+    'drx_rep_commit_dev': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_int, VP, VP, VP]),
+    'drx_rep_respond': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_int, VP, VP, VP, VP]),
+    'drx_rep_verify': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_int, VP, VP, VP, VP, VP, VP]),
+    'drx_rep_verify_dev': (ctypes.c_int, [VP, ctypes.c_size_t, ctypes.c_int, VP, VP, VP, VP, VP, VP]),
     'drx_set_target_pubkey': (ctypes.c_int, [VP, VP]),
     'drx_keyswitch': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP, VP, VP]),
     'drx_keyswitch_dev': (ctypes.c_int, [VP, ctypes.c_size_t, VP, VP, VP, VP, VP]),

@@ -158,6 +158,35 @@ class Backend:
         _lib.check(self.lib.drx_schnorr_verify(self.h, n, _ptr(pub), _ptr(sig), _ptr(dig), _ptr(ok)))
         return ok
 
+    def rep_commit(self, nterms, scalars, points):
+        """Commitments of n proof.Rep relations with nterms terms each: V_i = sum_j scalars[i][j] * points[i][j].
+        scalars n*nterms*32 bytes, points n*nterms*64 bytes -> n*64 bytes."""
+        sc, pt = _u8(scalars), _u8(points)
+        n = pt.size // (64 * nterms)
+        assert pt.size == 64 * nterms * n and sc.size == 32 * nterms * n
+        out = np.empty(64 * n, dtype=np.uint8)
+        _lib.check(self.lib.drx_rep_commit(self.h, n, nterms, _ptr(sc), _ptr(pt), _ptr(out)))
+        return out
+
+    def rep_respond(self, per, v, chal, x):
+        """Responses r_i = v_i - chal[i // per] * x_i (all 32-byte big-endian scalars) -> n*32 bytes."""
+        v, c, x = _u8(v), _u8(chal), _u8(x)
+        n = v.size // 32
+        assert v.size == 32 * n and x.size == 32 * n and c.size == 32 * ((n + per - 1) // per)
+        out = np.empty(32 * n, dtype=np.uint8)
+        _lib.check(self.lib.drx_rep_respond(self.h, n, per, _ptr(v), _ptr(c), _ptr(x), _ptr(out)))
+        return out
+
+    def rep_verify(self, nterms, resp, chal, bases, P, V):
+        """Accept bytes of n proof.Rep relations: sum_j resp[i][j] * bases[i][j] + chal[i] * P[i] == V[i]."""
+        r, c, b, p, v = _u8(resp), _u8(chal), _u8(bases), _u8(P), _u8(V)
+        n = p.size // 64
+        assert p.size == 64 * n and v.size == 64 * n and c.size == 32 * n
+        assert r.size == 32 * nterms * n and b.size == 64 * nterms * n
+        ok = np.zeros(n, dtype=np.uint8)
+        _lib.check(self.lib.drx_rep_verify(self.h, n, nterms, _ptr(r), _ptr(c), _ptr(b), _ptr(p), _ptr(v), _ptr(ok)))
+        return ok
+
     def set_target_pubkey(self, Q):
         """The querier's public key (64 bytes) for key switching."""
         q = _u8(Q)

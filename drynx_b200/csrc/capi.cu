@@ -856,6 +856,104 @@ int drx_schnorr_verify(drx_ctx* c, size_t n, const uint8_t* pub, const uint8_t* 
   return 0;
 }
 
+// ---- proof.Rep relations (obfuscation and key-switch proofs): commit, respond, verify
+static const int kRepMaxTerms = 8;
+int drx_rep_commit_dev(drx_ctx* c, size_t n, int nterms, const uint8_t* d_scalars, const uint8_t* d_points, uint8_t* d_out) {
+  if (!c) return fail(-1, "null context");
+  if (nterms < 1 || nterms > kRepMaxTerms) return fail(-1, "drx_rep_commit: nterms %d outside 1..%d", nterms, kRepMaxTerms);
+  Guard g(c);
+  timed(c, "k_rep_commit", [&] { return launch_rep_commit(c->stream, n, nterms, d_scalars, d_points, d_out, dev_bad(c)); });
+  return check_launch("rep_commit");
+}
+
+int drx_rep_commit(drx_ctx* c, size_t n, int nterms, const uint8_t* scalars, const uint8_t* points, uint8_t* out) {
+  if (!c) return fail(-1, "null context");
+  if (nterms < 1 || nterms > kRepMaxTerms) return fail(-1, "drx_rep_commit: nterms %d outside 1..%d", nterms, kRepMaxTerms);
+  if (n == 0) return 0;
+  if (!scalars || !points || !out) return fail(-1, "drx_rep_commit: null buffer");
+  Guard g(c);
+  Arena& a = c->arena;
+  a.plan_reset();
+  const size_t nt = (size_t)nterms;
+  size_t os = a.plan(n * nt * 32), op = a.plan(n * nt * 64), oo = a.plan(n * 64);
+  RET(a.commit());
+  RET(reset_bad(c));
+  RET(h2d(c, a.at<void>(os), scalars, n * nt * 32));
+  RET(h2d(c, a.at<void>(op), points, n * nt * 64));
+  timed(c, "k_rep_commit", [&] {
+    return launch_rep_commit(c->stream, n, nterms, a.at<uint8_t>(os), a.at<uint8_t>(op), a.at<uint8_t>(oo), (int*)c->bad.p);
+  });
+  RET(check_launch("rep_commit"));
+  RET(d2h(c, out, a.at<void>(oo), n * 64));
+  int bad = 0;
+  RET(read_bad(c, &bad));
+  if (bad) return fail(-2, "drx_rep_commit: %d malformed points", bad);
+  return 0;
+}
+
+int drx_rep_respond(drx_ctx* c, size_t n, int per, const uint8_t* v, const uint8_t* chal, const uint8_t* x, uint8_t* r) {
+  if (!c) return fail(-1, "null context");
+  if (per < 1) return fail(-1, "drx_rep_respond: per must be at least 1");
+  if (n == 0) return 0;
+  if (!v || !chal || !x || !r) return fail(-1, "drx_rep_respond: null buffer");
+  Guard g(c);
+  Arena& a = c->arena;
+  a.plan_reset();
+  const size_t nc = (n + (size_t)per - 1) / (size_t)per;
+  size_t ov = a.plan(n * 32), oc = a.plan(nc * 32), ox = a.plan(n * 32), orr = a.plan(n * 32);
+  RET(a.commit());
+  RET(h2d(c, a.at<void>(ov), v, n * 32));
+  RET(h2d(c, a.at<void>(oc), chal, nc * 32));
+  RET(h2d(c, a.at<void>(ox), x, n * 32));
+  timed(c, "k_rep_respond", [&] {
+    return launch_rep_respond(c->stream, n, per, a.at<uint8_t>(ov), a.at<uint8_t>(oc), a.at<uint8_t>(ox), a.at<uint8_t>(orr));
+  });
+  RET(check_launch("rep_respond"));
+  RET(d2h(c, r, a.at<void>(orr), n * 32));
+  RET(sync_out(c));
+  // the secrets and their blinding values do not stay behind in the arena
+  cudaMemsetAsync(a.at<void>(ov), 0, n * 32, c->stream);
+  cudaMemsetAsync(a.at<void>(ox), 0, n * 32, c->stream);
+  return 0;
+}
+
+int drx_rep_verify_dev(drx_ctx* c, size_t n, int nterms, const uint8_t* d_resp, const uint8_t* d_chal, const uint8_t* d_bases,
+                       const uint8_t* d_P, const uint8_t* d_V, uint8_t* d_ok) {
+  if (!c) return fail(-1, "null context");
+  if (nterms < 1 || nterms > kRepMaxTerms) return fail(-1, "drx_rep_verify: nterms %d outside 1..%d", nterms, kRepMaxTerms);
+  Guard g(c);
+  timed(c, "k_rep_verify", [&] { return launch_rep_verify(c->stream, n, nterms, d_resp, d_chal, d_bases, d_P, d_V, d_ok); });
+  return check_launch("rep_verify");
+}
+
+int drx_rep_verify(drx_ctx* c, size_t n, int nterms, const uint8_t* resp, const uint8_t* chal, const uint8_t* bases,
+                   const uint8_t* P, const uint8_t* V, uint8_t* ok) {
+  if (!c) return fail(-1, "null context");
+  if (nterms < 1 || nterms > kRepMaxTerms) return fail(-1, "drx_rep_verify: nterms %d outside 1..%d", nterms, kRepMaxTerms);
+  if (n == 0) return 0;
+  if (!resp || !chal || !bases || !P || !V || !ok) return fail(-1, "drx_rep_verify: null buffer");
+  Guard g(c);
+  Arena& a = c->arena;
+  a.plan_reset();
+  const size_t nt = (size_t)nterms;
+  size_t orr = a.plan(n * nt * 32), oc = a.plan(n * 32), ob = a.plan(n * nt * 64), op = a.plan(n * 64), ov = a.plan(n * 64),
+         oo = a.plan(n);
+  RET(a.commit());
+  RET(h2d(c, a.at<void>(orr), resp, n * nt * 32));
+  RET(h2d(c, a.at<void>(oc), chal, n * 32));
+  RET(h2d(c, a.at<void>(ob), bases, n * nt * 64));
+  RET(h2d(c, a.at<void>(op), P, n * 64));
+  RET(h2d(c, a.at<void>(ov), V, n * 64));
+  timed(c, "k_rep_verify", [&] {
+    return launch_rep_verify(c->stream, n, nterms, a.at<uint8_t>(orr), a.at<uint8_t>(oc), a.at<uint8_t>(ob), a.at<uint8_t>(op),
+                             a.at<uint8_t>(ov), a.at<uint8_t>(oo));
+  });
+  RET(check_launch("rep_verify"));
+  RET(d2h(c, ok, a.at<void>(oo), n));
+  RET(sync_out(c));
+  return 0;
+}
+
 int drx_decrypt_dev(drx_ctx* c, size_t n, const uint8_t sk[32], const uint8_t* d_ct, int64_t* d_out) {
   if (!c || !sk) return fail(-1, "null argument");
   Guard g(c);

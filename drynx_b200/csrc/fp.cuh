@@ -297,6 +297,9 @@ DRX_HD void mont_mul2(uint32_t r[8], const uint32_t a[8], const uint32_t b[8], c
   top = addc(hi9, 0);
   DRX_UNROLL
   for (int pass = 0; pass < 2; pass++) {
+    // The second subtraction is needed only when the value was at least 2M, which takes both products and m near their
+    // maxima: look at the top limbs first and skip the pass when they already say "below M".
+    if (pass == 1 && top == 0 && t[7] < M::mod(7)) break;
     s[0] = sub_cc(t[0], M::mod(0));
     DRX_UNROLL
     for (int k = 1; k < 8; k++) s[k] = subc_cc(t[k], M::mod(k));

@@ -740,6 +740,86 @@ int launch_schnorr_verify(cudaStream_t st, size_t n, const uint8_t* d_pub, const
   return 1;
 }
 
+// ------------------------------------------------------------------ proof.Rep relations
+// The group arithmetic of kyber's proof.Rep predicates as the obfuscation proof (lib/obfuscation/obfuscation_proof.go:
+// 37-91: co1 = s*c1 and co2 = s*c2) and unlynx's key-switch proof (libunlynxkeyswitch, verified from
+// lib/proof/structs_proofs.go:443-482: viB = vi*B, K = k*B, ks2 = vi*Q + k*rBNeg) use them. A relation is
+// P = x_1*B_1 + ... + x_T*B_T. kyber (proof/rep.go: commit, respond, verify; dependency, v3.0.8) has the prover send
+// V = v_1*B_1 + ... + v_T*B_T, draw the challenge c from the hash of every V of the proof, answer r_j = v_j - c*x_j,
+// and the verifier accept when r_1*B_1 + ... + r_T*B_T + c*P == V. The transcript hash stays with the caller (kyber's
+// hashProver over the suite's XOF); these kernels are the three group / scalar steps, one thread per relation.
+__global__ void __launch_bounds__(128)
+k_rep_commit(size_t n, int nt, const uint32_t* __restrict__ sc, const uint32_t* __restrict__ pts, uint32_t* __restrict__ out,
+             int* bad) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  G1Jac acc = jac_inf<Fp>();
+  for (int j = 0; j < nt; j++) {
+    G1Aff B;
+    if (!g1_from_wire(B, pts + 16 * (i * nt + j))) {  // rejected element: counted, and its output row is zeroed
+      atomicAdd(bad, 1);
+      for (int k = 0; k < 16; k++) out[16 * i + k] = 0;
+      return;
+    }
+    acc = jac_add(acc, window_mul(jac_from_aff(B), sc_from_wire(sc + 8 * (i * nt + j))));
+  }
+  g1_to_wire(out + 16 * i, jac_to_aff(acc));
+}
+// r_i = v_i - c_(i / per) * x_i: `per` secrets of one proof share its challenge
+__global__ void __launch_bounds__(128)
+k_rep_respond(size_t n, int per, const uint32_t* __restrict__ v, const uint32_t* __restrict__ c, const uint32_t* __restrict__ x,
+              uint32_t* __restrict__ r) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const Scalar ci = sc_from_wire(c + 8 * (i / per));
+  sc_to_wire(r + 8 * i, sc_sub(sc_from_wire(v + 8 * i), sc_mul(ci, sc_from_wire(x + 8 * i))));
+}
+// A malformed point or a response >= n (mod.Int.UnmarshalBinary rejects it) fails the relation, not the call.
+__global__ void __launch_bounds__(128)
+k_rep_verify(size_t n, int nt, const uint32_t* __restrict__ resp, const uint32_t* __restrict__ chal,
+             const uint32_t* __restrict__ bases, const uint32_t* __restrict__ P, const uint32_t* __restrict__ V,
+             uint8_t* __restrict__ ok) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  G1Aff Pi, Vi;
+  if (!g1_from_wire(Pi, P + 16 * i) || !g1_from_wire(Vi, V + 16 * i)) {
+    ok[i] = 0;
+    return;
+  }
+  G1Jac acc = window_mul(jac_from_aff(Pi), sc_from_wire(chal + 8 * i));
+  for (int j = 0; j < nt; j++) {
+    G1Aff B;
+    Scalar rj;
+    limbs_from_be_words(rj.v, resp + 8 * (i * nt + j));
+    if (!g1_from_wire(B, bases + 16 * (i * nt + j)) || mod_geq<ModN>(rj.v)) {
+      ok[i] = 0;
+      return;
+    }
+    acc = jac_add(acc, window_mul(jac_from_aff(B), rj));
+  }
+  acc = jac_add_aff(acc, aff_neg(Vi));
+  ok[i] = jac_is_inf(acc) ? 1 : 0;
+}
+int launch_rep_commit(cudaStream_t st, size_t n, int nt, const uint8_t* d_sc, const uint8_t* d_pts, uint8_t* d_out, int* d_bad) {
+  if (!n) return 0;
+  k_rep_commit<<<grid_for(n, 128), 128, 0, st>>>(n, nt, (const uint32_t*)d_sc, (const uint32_t*)d_pts, (uint32_t*)d_out, d_bad);
+  return 1;
+}
+int launch_rep_respond(cudaStream_t st, size_t n, int per, const uint8_t* d_v, const uint8_t* d_c, const uint8_t* d_x,
+                       uint8_t* d_r) {
+  if (!n) return 0;
+  k_rep_respond<<<grid_for(n, 128), 128, 0, st>>>(n, per, (const uint32_t*)d_v, (const uint32_t*)d_c, (const uint32_t*)d_x,
+                                                 (uint32_t*)d_r);
+  return 1;
+}
+int launch_rep_verify(cudaStream_t st, size_t n, int nt, const uint8_t* d_resp, const uint8_t* d_chal, const uint8_t* d_bases,
+                      const uint8_t* d_P, const uint8_t* d_V, uint8_t* d_ok) {
+  if (!n) return 0;
+  k_rep_verify<<<grid_for(n, 128), 128, 0, st>>>(n, nt, (const uint32_t*)d_resp, (const uint32_t*)d_chal,
+                                                (const uint32_t*)d_bases, (const uint32_t*)d_P, (const uint32_t*)d_V, d_ok);
+  return 1;
+}
+
 // ------------------------------------------------------------------ diagnostics
 __global__ void k_g1_mul(size_t n, const uint32_t* __restrict__ k, const uint32_t* __restrict__ pt,
                          uint32_t* __restrict__ out, int* bad) {
@@ -771,6 +851,7 @@ __global__ void k_mont_mul(size_t n, int which, const uint32_t* __restrict__ a, 
   else if (which == 3) mod_sub<ModP>(z, x, y);
   else if (which == 4) mod_add<ModN>(z, x, y);
   else if (which == 5) mod_sub<ModN>(z, x, y);
+  else if (which == 10) mont_mul2<ModP>(z, x, y, x, y);  // the dual-product pass on one pair: 2xy/R (x < p)
   else {  // which 6/7: halves of SHA3-512(x || y); 8/9: of SHA3-512((x || y) * 3)
     uint32_t msg[48], dig[16];
     for (int rep = 0; rep < 3; rep++)

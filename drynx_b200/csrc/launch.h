@@ -60,6 +60,11 @@ int launch_shuffle_rerandomize(cudaStream_t st, size_t lines, size_t nq, const i
 // MulCipherTextbyScalar per element: out_i = (s_i*K_i, s_i*C_i)
 int launch_ct_scalar_mul(cudaStream_t st, size_t n, const uint8_t* d_s, const uint8_t* d_ct, uint8_t* d_out, int* d_bad);
 // Schnorr over G1: ok_i = (s_i*B == R_i + h_i*P_i), sig = R || s (96 B), digest = SHA-512(R || P || msg) (64 B)
+int launch_rep_commit(cudaStream_t st, size_t n, int nt, const uint8_t* d_sc, const uint8_t* d_pts, uint8_t* d_out, int* d_bad);
+int launch_rep_respond(cudaStream_t st, size_t n, int per, const uint8_t* d_v, const uint8_t* d_c, const uint8_t* d_x,
+                       uint8_t* d_r);
+int launch_rep_verify(cudaStream_t st, size_t n, int nt, const uint8_t* d_resp, const uint8_t* d_chal, const uint8_t* d_bases,
+                      const uint8_t* d_P, const uint8_t* d_V, uint8_t* d_ok);
 int launch_schnorr_verify(cudaStream_t st, size_t n, const uint8_t* d_pub, const uint8_t* d_sig, const uint8_t* d_digest,
                           const void* d_tabB, uint8_t* d_ok);
 int launch_g1_mul(cudaStream_t st, size_t n, const uint8_t* d_k, const uint8_t* d_pt, uint8_t* d_out, int* d_bad);

@@ -91,75 +91,109 @@ __device__ __forceinline__ Fp ucs_xi_c(const Fp& ah, const Fp& ao, uint32_t h) {
 // reused in place (a phase may overwrite one of its own operands), and the two threads of a pair read each other's
 // components, so every load of a phase is separated from every store by a warp barrier.
 __device__ __forceinline__ void ucs_run(uint32_t S, int lane, uint32_t h, bool alive, int ph0, int ph1) {
+  // the next phase's opcode and lane word are fetched one phase ahead; both tables end with one idle phase, so the
+  // read ahead needs no bound check
+  const uint2* pw = uc_prog + ph0 * UC_G + lane;
   uint32_t op = uc_ops[ph0];
-  uint2 w = uc_prog[ph0 * UC_G + lane];
+  uint2 w = *pw;
   for (int ph = ph0; ph < ph1; ph++) {
-    const int nx = ph + 1 < ph1 ? ph + 1 : ph;
-    const uint32_t op_n = uc_ops[nx];
-    const uint2 w_n = uc_prog[nx * UC_G + lane];
+    pw += UC_G;
+    const uint32_t op_n = uc_ops[ph + 1];
+    const uint2 w_n = *pw;
     const bool act = alive && w.x != 0xffffffffu;
     const uint32_t d = w.x & 0xffffu, ia = w.x >> 16, ib = w.y & 0xffffu, ic = w.y >> 16;
     Fp r;
     if (act) {
-      if (op == UC_ADD) {
-        r = fp_add(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h));
-      } else if (op == UC_MUL) {
-        const Fp2 a = ucs_load(S, ia);
-        const Fp x = ucs_load_c(S, ib, h), yr = ucs_load_c(S, ib, h ^ 1u);
-        r = ucs_dual(a.c0, x, a.c1, fp_sel(h != 0, yr, ucs_neg_raw(yr)));
-      } else if (op == UC_SQR) {
-        // (a0 + a1)(a0 - a1) on h = 0, (a0 + a0) a1 on h = 1: one product each
-        const Fp2 a = ucs_load(S, ia);
-        const Fp x = fp_add(a.c0, fp_sel(h != 0, a.c0, a.c1));
-        const Fp y = fp_sel(h != 0, a.c1, fp_sub(a.c0, a.c1));
-        r = fp_mul_inl(x, y);
-      } else if (op == UC_SUB2) {
-        r = fp_sub(fp_sub(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h)), ucs_load_c(S, ic, h));
-      } else if (op == UC_AXI) {
-        r = fp_add(ucs_load_c(S, ia, h), ucs_xi_c(ucs_load_c(S, ib, h), ucs_load_c(S, ib, h ^ 1u), h));
-      } else if (op == UC_SUB) {
-        r = fp_sub(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h));
-      } else if (op == UC_CYCP || op == UC_CYCM) {
-        const Fp a = ucs_load_c(S, ia, h), b = ucs_load_c(S, ib, h);
-        const Fp s = op == UC_CYCP ? fp_add(a, b) : fp_sub(a, b);
-        r = fp_add(fp_add(s, s), a);
-      } else if (op == UC_MULXI) {
-        r = ucs_xi_c(ucs_load_c(S, ia, h), ucs_load_c(S, ia, h ^ 1u), h);
-      } else if (op == UC_MULFP0 || op == UC_MULFP1) {
-        r = fp_mul(ucs_load_c(S, ia, h), ucs_load_c(S, ib, op == UC_MULFP1 ? 1u : 0u));
-      } else if (op == UC_X4 || op == UC_X8 || op == UC_X3) {
-        const Fp a = ucs_load_c(S, ia, h);
-        const Fp d2 = fp_add(a, a);
-        if (op == UC_X3) {
-          r = fp_add(d2, a);
-        } else {
-          r = fp_add(d2, d2);
-          if (op == UC_X8) r = fp_add(r, r);
+      switch (op) {
+        case UC_ADD:
+          r = fp_add(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h));
+          break;
+        case UC_MUL: {
+          const Fp2 a = ucs_load(S, ia);
+          const Fp x = ucs_load_c(S, ib, h), yr = ucs_load_c(S, ib, h ^ 1u);
+          r = ucs_dual(a.c0, x, a.c1, fp_sel(h != 0, yr, ucs_neg_raw(yr)));
+          break;
         }
-      } else if (op == UC_NEG) {
-        r = fp_neg(ucs_load_c(S, ia, h));
-      } else if (op == UC_CONJMULC || op == UC_MULC) {
-        // (a0 +- a1 i)(k0 + k1 i): MULC c0 = a0 k0 + a1 (p - k1), c1 = a0 k1 + a1 k0;
-        // CONJMULC c0 = a0 k0 + a1 k1, c1 = a0 k1 + a1 (p - k0)
-        const Fp2 a = ucs_load(S, ia);
-        const Fp x = ucs_const2_c(ib, h), yr = ucs_const2_c(ib, h ^ 1u);
-        const bool negate = (op == UC_MULC) == (h == 0);
-        r = ucs_dual(a.c0, x, a.c1, fp_sel(negate, ucs_neg_raw(yr), yr));
-      } else if (op == UC_MULFPC) {
-        r = fp_mul(ucs_load_c(S, ia, h), uc_constp_(ib));
-      } else if (op == UC_CONJ) {
-        const Fp a = ucs_load_c(S, ia, h);
-        r = h ? fp_neg(a) : a;
-      } else if (op == UC_INV) {
-        Fp2 tmp = ucs_load(S, ia);  // both threads invert (same instructions either way) and keep their component
-        const Fp2 v = fp2_inv(tmp);
-        r = fp_sel(h != 0, v.c1, v.c0);
-      } else if (op == UC_CHK) {
-        // verdict of the G2 membership test: zero iff a == 0, b == 0 and c != 0 (see tools/microcode/gen.py)
-        const bool good = fp2_is_zero(ucs_load(S, ia)) & fp2_is_zero(ucs_load(S, ib)) & !fp2_is_zero(ucs_load(S, ic));
-        r = good ? fp_zero() : fp_one();
-      } else {
-        r = ucs_load_c(S, ia, h);  // UC_COPY
+        case UC_SQR: {
+          // (a0 + a1)(a0 - a1) on h = 0, (a0 + a0) a1 on h = 1: one product each
+          const Fp2 a = ucs_load(S, ia);
+          const Fp x = fp_add(a.c0, fp_sel(h != 0, a.c0, a.c1));
+          const Fp y = fp_sel(h != 0, a.c1, fp_sub(a.c0, a.c1));
+          r = fp_mul_inl(x, y);
+          break;
+        }
+        case UC_SUB2:
+          r = fp_sub(fp_sub(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h)), ucs_load_c(S, ic, h));
+          break;
+        case UC_AXI:
+          r = fp_add(ucs_load_c(S, ia, h), ucs_xi_c(ucs_load_c(S, ib, h), ucs_load_c(S, ib, h ^ 1u), h));
+          break;
+        case UC_SUB:
+          r = fp_sub(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h));
+          break;
+        case UC_CYCP:
+        case UC_CYCM: {
+          const Fp a = ucs_load_c(S, ia, h), b = ucs_load_c(S, ib, h);
+          const Fp s = op == UC_CYCP ? fp_add(a, b) : fp_sub(a, b);
+          r = fp_add(fp_add(s, s), a);
+          break;
+        }
+        case UC_MULXI:
+          r = ucs_xi_c(ucs_load_c(S, ia, h), ucs_load_c(S, ia, h ^ 1u), h);
+          break;
+        case UC_MULFP0:
+        case UC_MULFP1:
+          r = fp_mul(ucs_load_c(S, ia, h), ucs_load_c(S, ib, op == UC_MULFP1 ? 1u : 0u));
+          break;
+        case UC_X4:
+        case UC_X8:
+        case UC_X3: {
+          const Fp a = ucs_load_c(S, ia, h);
+          const Fp d2 = fp_add(a, a);
+          if (op == UC_X3) {
+            r = fp_add(d2, a);
+          } else {
+            r = fp_add(d2, d2);
+            if (op == UC_X8) r = fp_add(r, r);
+          }
+          break;
+        }
+        case UC_NEG:
+          r = fp_neg(ucs_load_c(S, ia, h));
+          break;
+        case UC_CONJMULC:
+        case UC_MULC: {
+          // (a0 +- a1 i)(k0 + k1 i): MULC c0 = a0 k0 + a1 (p - k1), c1 = a0 k1 + a1 k0;
+          // CONJMULC c0 = a0 k0 + a1 k1, c1 = a0 k1 + a1 (p - k0)
+          const Fp2 a = ucs_load(S, ia);
+          const Fp x = ucs_const2_c(ib, h), yr = ucs_const2_c(ib, h ^ 1u);
+          const bool negate = (op == UC_MULC) == (h == 0);
+          r = ucs_dual(a.c0, x, a.c1, fp_sel(negate, ucs_neg_raw(yr), yr));
+          break;
+        }
+        case UC_MULFPC:
+          r = fp_mul(ucs_load_c(S, ia, h), uc_constp_(ib));
+          break;
+        case UC_CONJ: {
+          const Fp a = ucs_load_c(S, ia, h);
+          r = h ? fp_neg(a) : a;
+          break;
+        }
+        case UC_INV: {
+          Fp2 tmp = ucs_load(S, ia);  // both threads invert (same instructions either way) and keep their component
+          const Fp2 v = fp2_inv(tmp);
+          r = fp_sel(h != 0, v.c1, v.c0);
+          break;
+        }
+        case UC_CHK: {
+          // verdict of the G2 membership test: zero iff a == 0, b == 0 and c != 0 (see tools/microcode/gen.py)
+          const bool good = fp2_is_zero(ucs_load(S, ia)) & fp2_is_zero(ucs_load(S, ib)) & !fp2_is_zero(ucs_load(S, ic));
+          r = good ? fp_zero() : fp_one();
+          break;
+        }
+        default:
+          r = ucs_load_c(S, ia, h);  // UC_COPY
+          break;
       }
     }
     __syncwarp();

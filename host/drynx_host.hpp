@@ -310,6 +310,26 @@ inline bool VerifyProofSignature(const Point& pubKey, const uint8_t* data, size_
   return VerifyProofSignatures({r})[0];
 }
 
+// kyber proof.HashProve / proof.HashVerify (kyber v3.0.8 proof/hash.go) draw the challenge of a Sigma protocol from the
+// suite's XOF (blake2xb) seeded with the protocol name and reseeded with every commitment Put so far. That XOF is kyber's
+// own construction and is not restated here: on the Go side the cgo shim keeps using kyber for this one step
+// (go/gpubackend/proofs.go), and the device entry points take the challenge as an input. For a C++ caller the default
+// below is a stand-in with the same shape (a hash of name || commitments): SHA-512, first 32 bytes, top bit cleared
+// (< 2^255 < n). Replace it to interoperate with another transcript.
+using ChallengeFn = std::function<drynx::Scalar(const std::string& protocol, const uint8_t* commitments, size_t len)>;
+inline drynx::Scalar default_challenge(const std::string& protocol, const uint8_t* commitments, size_t len) {
+  uint8_t d[64];
+  sha512((const uint8_t*)protocol.data(), protocol.size(), commitments, len, nullptr, 0, d);
+  drynx::Scalar c;
+  memcpy(c.b, d, 32);
+  c.b[0] &= 0x7f;
+  return c;
+}
+inline ChallengeFn& challenge_fn() {
+  static ChallengeFn f = default_challenge;
+  return f;
+}
+
 }  // namespace drynxproof
 
 namespace libunlynxaggr {
@@ -434,7 +454,192 @@ inline libunlynx::CipherVector Combine(const libunlynx::CipherVector& original, 
   return libunlynx::AddAll(all);
 }
 
+
+// PublishedKSProof / PublishedKSListProof (unlynx lib/key_switch proofs; verified by the VNs at
+// lib/proof/structs_proofs.go:469-482): the predicate is And(Rep(viB = vi*B), Rep(K = k*B), Rep(ks2 = vi*Q + k*rBNeg)),
+// the proof bytes in kyber's order V1 || V2 || V3 || r_vi || r_k (256 bytes).
+struct PublishedKSProof {
+  drynx::Bytes Proof;
+  Point K, ViB, Ks2, RbNeg, Q;
+};
+struct PublishedKSListProof {
+  std::vector<PublishedKSProof> List;
+};
+// KeySwitchListProofCreation(pubKey, targetPubKey, secretKey, ks2s, rBNegs, vis) (services/service.go:581,
+// data/data.go:81): four batched device calls for the whole list (commitments with one and two terms, viB, responses).
+inline PublishedKSListProof KeySwitchListProofCreation(const Point& pubKey, const Point& targetPubKey, const Scalar& secretKey,
+                                                       const std::vector<Point>& ks2s, const std::vector<Point>& rBNegs,
+                                                       const std::vector<Scalar>& vis) {
+  const size_t n = vis.size();
+  PublishedKSListProof l;
+  l.List.resize(n);
+  if (!n) return l;
+  const Point B = drynx::base_point();
+  std::vector<uint8_t> x(64 * n), blind(64 * n), bb(128 * n), qr(128 * n), v12(128 * n), v3(64 * n), vib(128 * n), r(64 * n),
+      chal(32 * n);
+  for (size_t i = 0; i < n; i++) {
+    memcpy(&x[64 * i], vis[i].b, 32);
+    memcpy(&x[64 * i + 32], secretKey.b, 32);
+    const Scalar a = drynx::pick(), b = drynx::pick();
+    memcpy(&blind[64 * i], a.b, 32);
+    memcpy(&blind[64 * i + 32], b.b, 32);
+    memcpy(&bb[128 * i], B.b, 64);
+    memcpy(&bb[128 * i + 64], B.b, 64);
+    memcpy(&qr[128 * i], targetPubKey.b, 64);
+    memcpy(&qr[128 * i + 64], rBNegs[i].b, 64);
+  }
+  drx_ctx* g = Gpu::get().ctx();
+  drynx::check(drx_rep_commit(g, 2 * n, 1, x.data(), bb.data(), vib.data()));       // viB (and K again)
+  drynx::check(drx_rep_commit(g, 2 * n, 1, blind.data(), bb.data(), v12.data()));
+  drynx::check(drx_rep_commit(g, n, 2, blind.data(), qr.data(), v3.data()));
+  for (size_t i = 0; i < n; i++) {
+    uint8_t V[192];
+    memcpy(V, &v12[128 * i], 128);
+    memcpy(V + 128, &v3[64 * i], 64);
+    const Scalar c = drynxproof::challenge_fn()("proofTest", V, 192);
+    memcpy(&chal[32 * i], c.b, 32);
+  }
+  drynx::check(drx_rep_respond(g, 2 * n, 2, blind.data(), chal.data(), x.data(), r.data()));
+  for (size_t i = 0; i < n; i++) {
+    auto& p = l.List[i];
+    p.Proof.resize(256);
+    memcpy(p.Proof.data(), &v12[128 * i], 128);
+    memcpy(p.Proof.data() + 128, &v3[64 * i], 64);
+    memcpy(p.Proof.data() + 192, &r[64 * i], 64);
+    p.K = pubKey;
+    memcpy(p.ViB.b, &vib[128 * i], 64);
+    p.Ks2 = ks2s[i];
+    p.RbNeg = rBNegs[i];
+    p.Q = targetPubKey;
+  }
+  return l;
+}
+// Accept bit of each of the first `count` proofs: two batched device calls.
+inline std::vector<uint8_t> KeySwitchVerifyEach(const PublishedKSListProof& l, size_t count) {
+  const size_t n = std::min(count, l.List.size());
+  std::vector<uint8_t> out(n, 1);
+  if (!n) return out;
+  const Point B = drynx::base_point();
+  std::vector<uint8_t> r1(64 * n), c1(64 * n), b1(128 * n), p1(128 * n), v1(128 * n), c2(32 * n), b2(128 * n), p2(64 * n),
+      v2(64 * n), ok1(2 * n), ok2(n);
+  for (size_t i = 0; i < n; i++) {
+    const auto& p = l.List[i];
+    if (p.Proof.size() != 256) {
+      out[i] = 0;
+      continue;
+    }
+    const Scalar c = drynxproof::challenge_fn()("proofTest", p.Proof.data(), 192);
+    memcpy(&r1[64 * i], p.Proof.data() + 192, 64);
+    memcpy(&c1[64 * i], c.b, 32);
+    memcpy(&c1[64 * i + 32], c.b, 32);
+    memcpy(&c2[32 * i], c.b, 32);
+    memcpy(&b1[128 * i], B.b, 64);
+    memcpy(&b1[128 * i + 64], B.b, 64);
+    memcpy(&p1[128 * i], p.ViB.b, 64);
+    memcpy(&p1[128 * i + 64], p.K.b, 64);
+    memcpy(&v1[128 * i], p.Proof.data(), 128);
+    memcpy(&b2[128 * i], p.Q.b, 64);
+    memcpy(&b2[128 * i + 64], p.RbNeg.b, 64);
+    memcpy(&p2[64 * i], p.Ks2.b, 64);
+    memcpy(&v2[64 * i], p.Proof.data() + 128, 64);
+  }
+  drx_ctx* g = Gpu::get().ctx();
+  drynx::check(drx_rep_verify(g, 2 * n, 1, r1.data(), c1.data(), b1.data(), p1.data(), v1.data(), ok1.data()));
+  drynx::check(drx_rep_verify(g, n, 2, r1.data(), c2.data(), b2.data(), p2.data(), v2.data(), ok2.data()));
+  for (size_t i = 0; i < n; i++) out[i] = out[i] && ok1[2 * i] && ok1[2 * i + 1] && ok2[i];
+  return out;
+}
+// KeySwitchListProofVerification(pkslp, percent): the first ceil(percent * len) proofs must all hold.
+inline bool KeySwitchListProofVerification(const PublishedKSListProof& l, double percent) {
+  const size_t nb = (size_t)std::ceil(percent * (double)l.List.size());
+  for (uint8_t b : KeySwitchVerifyEach(l, nb))
+    if (!b) return false;
+  return true;
+}
+
 }  // namespace libunlynxkeyswitch
+
+// =====================================================================================================================
+// lib/obfuscation/obfuscation_proof.go: the proof that co = s*c componentwise for a secret s, the predicate
+// And(Rep(co1 = s*c1), Rep(co2 = s*c2)); proof bytes in kyber's order V1 || V2 || r_s (160 bytes).
+namespace libdrynxobfuscation {
+using drynx::Gpu;
+using drynx::Scalar;
+using libunlynx::CipherText;
+
+struct PublishedObfuscationProof {  // obfuscation_proof.go:12-16
+  CipherText C, Co;
+  drynx::Bytes Proof;
+};
+struct PublishedListObfuscationProof {  // obfuscation_proof.go:26-28
+  std::vector<PublishedObfuscationProof> Prs;
+};
+// ObfuscationListProofCreation(c, co, s) (obfuscation_proof.go:62-77; protocols/obfuscation_protocol.go:259,
+// data/data.go:57): where the Go code starts one goroutine per proof, one commitment call and one response call
+// cover the list. A ciphertext is c1 || c2, so the commitments V1 || V2 = v*c1 || v*c2 are drx_ct_scalar_mul of c by v.
+inline PublishedListObfuscationProof ObfuscationListProofCreation(const libunlynx::CipherVector& c, const libunlynx::CipherVector& co,
+                                                                  const std::vector<Scalar>& s) {
+  const size_t n = s.size();
+  PublishedListObfuscationProof l;
+  l.Prs.resize(n);
+  if (!n) return l;
+  std::vector<Scalar> v(n), chal(n), r(n);
+  for (auto& x : v) x = drynx::pick();
+  libunlynx::CipherVector V(n);
+  drx_ctx* g = Gpu::get().ctx();
+  drynx::check(drx_ct_scalar_mul(g, n, v[0].b, c[0].b, V[0].b));
+  for (size_t i = 0; i < n; i++) chal[i] = drynxproof::challenge_fn()("proofTest", V[i].b, 128);
+  drynx::check(drx_rep_respond(g, n, 1, v[0].b, chal[0].b, s[0].b, r[0].b));
+  for (size_t i = 0; i < n; i++) {
+    l.Prs[i].C = c[i];
+    l.Prs[i].Co = co[i];
+    l.Prs[i].Proof.resize(160);
+    memcpy(l.Prs[i].Proof.data(), V[i].b, 128);
+    memcpy(l.Prs[i].Proof.data() + 128, r[i].b, 32);
+  }
+  return l;
+}
+inline PublishedObfuscationProof ObfuscationProofCreation(const CipherText& c, const CipherText& co, const Scalar& s) {
+  return ObfuscationListProofCreation({c}, {co}, {s}).Prs[0];
+}
+// Accept bit of each of the first `count` proofs: one device call over 2 * count relations.
+inline std::vector<uint8_t> VerifyEach(const PublishedListObfuscationProof& l, size_t count) {
+  const size_t n = std::min(count, l.Prs.size());
+  std::vector<uint8_t> out(n, 1);
+  if (!n) return out;
+  std::vector<uint8_t> resp(64 * n), chal(64 * n), bases(128 * n), P(128 * n), V(128 * n), ok(2 * n);
+  for (size_t i = 0; i < n; i++) {
+    const auto& p = l.Prs[i];
+    if (p.Proof.size() != 160) {
+      out[i] = 0;
+      continue;
+    }
+    const Scalar c = drynxproof::challenge_fn()("proofTest", p.Proof.data(), 128);
+    for (int h = 0; h < 2; h++) {
+      memcpy(&resp[64 * i + 32 * h], p.Proof.data() + 128, 32);
+      memcpy(&chal[64 * i + 32 * h], c.b, 32);
+    }
+    memcpy(&bases[128 * i], p.C.b, 128);
+    memcpy(&P[128 * i], p.Co.b, 128);
+    memcpy(&V[128 * i], p.Proof.data(), 128);
+  }
+  drynx::check(drx_rep_verify(Gpu::get().ctx(), 2 * n, 1, resp.data(), chal.data(), bases.data(), P.data(), V.data(), ok.data()));
+  for (size_t i = 0; i < n; i++) out[i] = out[i] && ok[2 * i] && ok[2 * i + 1];
+  return out;
+}
+inline bool ObfuscationProofVerification(const PublishedObfuscationProof& pop) {  // obfuscation_proof.go:80-91
+  PublishedListObfuscationProof l;
+  l.Prs.push_back(pop);
+  return VerifyEach(l, 1)[0] != 0;
+}
+// ObfuscationListProofVerification(plop, percent) (obfuscation_proof.go:94-111)
+inline bool ObfuscationListProofVerification(const PublishedListObfuscationProof& plop, double percent) {
+  const size_t nb = (size_t)std::ceil(percent * (double)plop.Prs.size());
+  for (uint8_t b : VerifyEach(plop, nb))
+    if (!b) return false;
+  return true;
+}
+}  // namespace libdrynxobfuscation
 
 // =====================================================================================================================
 namespace libdrynx {

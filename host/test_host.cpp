@@ -347,6 +347,65 @@ static void TestKeySwitching() {
   EXPECT(libunlynx::DecryptIntVectorWithNeg(querier.Private, cv) != values);
 }
 
+static void TestObfuscationProofVerification() {  // lib/obfuscation/obfuscation_proof_test.go:11-34
+  auto keys = drynx::NewKeyPair();
+  auto ev = libunlynx::EncryptInt(keys.Public, 2);
+  const drynx::Scalar obfuscationFactor = keys.Private;
+  auto evo = libunlynx::MulCipherTextbyScalar(ev, obfuscationFactor);
+  auto op = libdrynxobfuscation::ObfuscationProofCreation(ev, evo, obfuscationFactor);
+  EXPECT(op.Proof.size() == 160);
+  EXPECT(libdrynxobfuscation::ObfuscationProofVerification(op));
+  auto nop = op;  // the ToBytes / FromBytes round trip of the Go test: the C++ structs already hold the byte forms
+  libdrynxobfuscation::PublishedListObfuscationProof lop;
+  lop.Prs = {op, nop};
+  EXPECT(libdrynxobfuscation::ObfuscationListProofVerification(lop, 1));
+  auto wrong = libdrynxobfuscation::ObfuscationProofCreation(ev, evo, drynx::scalar_from_u64(1));
+  EXPECT(!libdrynxobfuscation::ObfuscationProofVerification(wrong));
+  // a longer list, as protocols/obfuscation_protocol.go:231-259 builds it; the threshold reads only a prefix
+  std::vector<int64_t> vals = {0, 1, 0, 7, 0, 3};
+  auto cv = libunlynx::EncryptIntVector(keys.Public, vals);
+  std::vector<drynx::Scalar> ss(cv.size());
+  for (auto& x : ss) x = drynx::pick();
+  auto co = libunlynx::MulCipherVectorByScalars(cv, ss);
+  auto list = libdrynxobfuscation::ObfuscationListProofCreation(cv, co, ss);
+  EXPECT(libdrynxobfuscation::ObfuscationListProofVerification(list, 1.0));
+  list.Prs[4].Proof[150] ^= 1;
+  EXPECT(!libdrynxobfuscation::ObfuscationListProofVerification(list, 1.0));
+  EXPECT(libdrynxobfuscation::ObfuscationListProofVerification(list, 0.5));
+  auto bits = libdrynxobfuscation::VerifyEach(list, list.Prs.size());
+  EXPECT(bits == std::vector<uint8_t>({1, 1, 1, 1, 0, 1}));
+  std::swap(list.Prs[0].Co, list.Prs[1].Co);
+  EXPECT(!libdrynxobfuscation::ObfuscationListProofVerification(list, 0.2));
+}
+
+static void TestKeySwitchListProof() {  // the proof services/service.go:581 and data/data.go:81 create
+  auto server = drynx::NewKeyPair();
+  auto querier = drynx::NewKeyPair();
+  auto coll = drynx::NewKeyPair();
+  auto cv = libunlynx::EncryptIntVector(coll.Public, {5, 0, -2, 77});
+  std::vector<drynx::Point> rBs(cv.size());
+  for (size_t i = 0; i < cv.size(); i++) memcpy(rBs[i].b, cv[i].b, 64);
+  auto seq = libunlynxkeyswitch::KeySwitchSequence(querier.Public, rBs, server.Private);
+  auto proof = libunlynxkeyswitch::KeySwitchListProofCreation(server.Public, querier.Public, server.Private, seq.ks2s, seq.rBNegs, seq.vis);
+  EXPECT(proof.List.size() == cv.size() && proof.List[0].Proof.size() == 256);
+  for (size_t i = 0; i < cv.size(); i++) EXPECT(!memcmp(proof.List[i].ViB.b, seq.cv[i].b, 64));  // viB is the K component sent on
+  EXPECT(libunlynxkeyswitch::KeySwitchListProofVerification(proof, 1.0));
+  auto t = proof;
+  t.List[2].Ks2 = t.List[1].Ks2;
+  EXPECT(!libunlynxkeyswitch::KeySwitchListProofVerification(t, 1.0));
+  EXPECT(libunlynxkeyswitch::KeySwitchListProofVerification(t, 0.5));
+  t = proof;
+  t.List[0].K = querier.Public;  // somebody else's key
+  EXPECT(!libunlynxkeyswitch::KeySwitchListProofVerification(t, 0.1));
+  t = proof;
+  t.List[3].Proof[200] ^= 1;
+  EXPECT(libunlynxkeyswitch::KeySwitchVerifyEach(t, 4) == std::vector<uint8_t>({1, 1, 1, 0}));
+  // a proof made with the wrong secret key does not verify
+  auto other = drynx::NewKeyPair();
+  auto forged = libunlynxkeyswitch::KeySwitchListProofCreation(server.Public, querier.Public, other.Private, seq.ks2s, seq.rBNegs, seq.vis);
+  EXPECT(!libunlynxkeyswitch::KeySwitchListProofVerification(forged, 1.0));
+}
+
 static void TestShuffleSequence() {  // data/data.go:60-70: two lines shuffled under the collective key
   auto keys = drynx::NewKeyPair();
   libunlynx::CreateDecryptionTable(10000, keys.Public, keys.Private);
@@ -441,6 +500,8 @@ int main(int argc, char** argv) {
       TestKeySwitching();
       TestProofSignatureAndAggregationProof();
       TestShuffleSequence();
+      TestObfuscationProofVerification();
+      TestKeySwitchListProof();
     } catch (const drynx::Error& e) {
       printf("FAIL: exception %d: %s\n", e.code, e.what());
       failures++;

@@ -195,6 +195,32 @@ int drx_shuffle_rerandomize_dev(drx_ctx* ctx, size_t lines, size_t nq, const int
  * signature), never an error of the call. */
 int drx_schnorr_verify(drx_ctx* ctx, size_t n, const uint8_t* pub, const uint8_t* sig, const uint8_t* digest, uint8_t* ok /*n*/);
 
+/* proof.Rep relations, batched: the group and scalar steps of the two kyber proof.Rep
+ * proofs on the path -- the obfuscation proof (lib/obfuscation/obfuscation_proof.go:37-91, created at
+ * protocols/obfuscation_protocol.go:259 and data/data.go:57, verified at lib/proof/structs_proofs.go:318-338:
+ * co1 = s*c1, co2 = s*c2) and unlynx's key-switch proof (libunlynxkeyswitch.KeySwitchListProofCreation /
+ * KeySwitchListProofVerification, unlynx v1.4.0; call sites services/service.go:581, data/data.go:81,
+ * lib/proof/structs_proofs.go:469-482: viB = vi*B, K = k*B, ks2 = vi*Q + k*rBNeg). A relation is
+ * P = x_1*B_1 + ... + x_T*B_T (T = nterms >= 1). As kyber v3.0.8 proof/rep.go does it: the prover sends
+ * V = sum_j v_j*B_j (drx_rep_commit; with nterms = 1 on both halves of a ciphertext it equals drx_ct_scalar_mul),
+ * the challenge c comes out of the transcript hash of every V of the proof, the answers are r_j = v_j - c*x_j
+ * (drx_rep_respond: `per` consecutive secrets share challenge i / per), and the verifier accepts when
+ * sum_j r_j*B_j + c*P == V (drx_rep_verify). The transcript (kyber proof.HashProve / HashVerify over the suite's XOF)
+ * stays on the caller's side: the challenge is an input here, the proof bytes are V's then r's in kyber's order.
+ * scalars, resp, chal: 32 bytes big-endian; points 64 bytes. drx_rep_commit returns -2 on a malformed point;
+ * drx_rep_verify gives ok[i] = 0 for a malformed point or a response >= n (kyber fails that proof), never an error
+ * of the call. */
+int drx_rep_commit(drx_ctx* ctx, size_t n, int nterms, const uint8_t* scalars /*n*nterms*32*/,
+                   const uint8_t* points /*n*nterms*64*/, uint8_t* out /*n*64*/);
+int drx_rep_commit_dev(drx_ctx* ctx, size_t n, int nterms, const uint8_t* d_scalars, const uint8_t* d_points, uint8_t* d_out);
+int drx_rep_respond(drx_ctx* ctx, size_t n, int per, const uint8_t* v /*n*32*/, const uint8_t* chal /*ceil(n/per)*32*/,
+                    const uint8_t* x /*n*32*/, uint8_t* r /*n*32*/);
+int drx_rep_verify(drx_ctx* ctx, size_t n, int nterms, const uint8_t* resp /*n*nterms*32*/, const uint8_t* chal /*n*32*/,
+                   const uint8_t* bases /*n*nterms*64*/, const uint8_t* P /*n*64*/, const uint8_t* V /*n*64*/,
+                   uint8_t* ok /*n*/);
+int drx_rep_verify_dev(drx_ctx* ctx, size_t n, int nterms, const uint8_t* d_resp, const uint8_t* d_chal, const uint8_t* d_bases,
+                       const uint8_t* d_P, const uint8_t* d_V, uint8_t* d_ok);
+
 /* Server signatures for one output column: Y_i and A_{i,k} = (x_i + k)^-1 * g2, k < u
  * (lib/range/range_proof.go:249-302 InitRangeProofSignature, PublishSignatureBytesToPublishSignatures;
  * libdrynx.PublishSignatureBytes lib/structs.go:131-141). Builds the per-set tables; set_id is the caller's

@@ -1252,6 +1252,49 @@ static bool schnorr_verify_one(const uint8_t pub[64], const uint8_t sig[96], con
   g1_marshal(b, RAs);
   return memcmp(a, b, 64) == 0;
 }
+// kyber v3.0.8 proof/rep.go (dependency, recalled): a proof.Rep("P", "x1", "B1", ..., "xT", "BT") predicate.
+//   commit:  V = v_1*B_1 + ... + v_T*B_T, v_j = the blinding scalar of secret x_j (shared by every Rep that names x_j)
+//   respond: r_j = v_j - c*x_j ("ri.Mul(c, x); ri.Sub(v, ri)")
+//   verify:  V' = c*P + r_1*B_1 + ... + r_T*B_T; V'.Equal(V)
+// The challenge c is the caller's (kyber draws it from the hashProver's XOF after every V of the proof was Put). Used by
+// lib/obfuscation/obfuscation_proof.go:37-91 and by unlynx's key-switch proof (lib/proof/structs_proofs.go:469-482).
+static bool rep_commit_one(uint8_t out[64], int nt, const uint8_t* sc, const uint8_t* pts) {
+  curvePoint V, t;
+  V.SetInfinity();
+  for (int j = 0; j < nt; j++) {
+    curvePoint B;
+    if (!g1_unmarshal(B, pts + 64 * j)) return false;
+    Sc v;
+    sc_from_bytes(v, sc + 32 * j);
+    t.Mul(B, v.v);
+    V.Add(V, t);
+  }
+  g1_marshal(out, V);
+  return true;
+}
+static bool rep_verify_one(int nt, const uint8_t* resp, const uint8_t chal[32], const uint8_t* bases, const uint8_t P[64],
+                           const uint8_t V[64]) {
+  curvePoint Pp, Vv, acc, t;
+  if (!g1_unmarshal(Pp, P) || !g1_unmarshal(Vv, V)) return false;
+  Sc c;
+  sc_from_bytes(c, chal);
+  acc.Mul(Pp, c.v);
+  for (int j = 0; j < nt; j++) {
+    curvePoint B;
+    if (!g1_unmarshal(B, bases + 64 * j)) return false;
+    gfP raw;
+    gfpUnmarshal(raw, resp + 32 * j);
+    if (geq(raw.v, MN.m)) return false;  // mod.Int.UnmarshalBinary: value out of range
+    Sc r;
+    memcpy(r.v, raw.v, 32);
+    t.Mul(B, r.v);
+    acc.Add(acc, t);
+  }
+  uint8_t a[64], b[64];
+  g1_marshal(a, acc);
+  g1_marshal(b, Vv);
+  return memcmp(a, b, 64) == 0;
+}
 struct DlogTable {  // PointToInt map keyed by the marshalled point, grown lazily like discreteLog
   std::unordered_map<std::string, int64_t> map;
   curvePoint currentGreatestM;
@@ -1544,6 +1587,33 @@ int orc_shuffle_rerandomize(size_t lines, size_t nq, const int32_t* pi, const ui
 int orc_schnorr_verify(size_t n, const uint8_t* pub, const uint8_t* sig, const uint8_t* digest, uint8_t* ok, int threads) {
   ensure_init();
   parallel_for(n, threads, [&](size_t i) { ok[i] = schnorr_verify_one(pub + 64 * i, sig + 96 * i, digest + 64 * i) ? 1 : 0; });
+  return 0;
+}
+int orc_rep_commit(size_t n, int nt, const uint8_t* sc, const uint8_t* pts, uint8_t* out, int threads) {
+  ensure_init();
+  std::atomic<int> bad(0);
+  parallel_for(n, threads, [&](size_t i) {
+    if (!rep_commit_one(out + 64 * i, nt, sc + 32 * nt * i, pts + 64 * nt * i)) bad++;
+  });
+  return bad ? -2 : 0;
+}
+int orc_rep_respond(size_t n, int per, const uint8_t* v, const uint8_t* chal, const uint8_t* x, uint8_t* r) {
+  ensure_init();
+  for (size_t i = 0; i < n; i++) {
+    Sc vi, ci, xi;
+    sc_from_bytes(vi, v + 32 * i);
+    sc_from_bytes(ci, chal + 32 * (i / per));
+    sc_from_bytes(xi, x + 32 * i);
+    sc_to_bytes(r + 32 * i, sc_sub(vi, sc_mul(ci, xi)));
+  }
+  return 0;
+}
+int orc_rep_verify(size_t n, int nt, const uint8_t* resp, const uint8_t* chal, const uint8_t* bases, const uint8_t* P,
+                   const uint8_t* V, uint8_t* ok, int threads) {
+  ensure_init();
+  parallel_for(n, threads, [&](size_t i) {
+    ok[i] = rep_verify_one(nt, resp + 32 * nt * i, chal + 32 * i, bases + 64 * nt * i, P + 64 * i, V + 64 * i) ? 1 : 0;
+  });
   return 0;
 }
 // first half of Sign: R = k*B (the caller hashes R || X || msg and calls orc_schnorr_finish)

@@ -121,6 +121,30 @@ class Oracle:
         assert self.lib.orc_schnorr_verify(ctypes.c_size_t(n), self._p(pub), self._p(sig), self._p(dig), self._p(ok), threads) == 0
         return ok
 
+    def rep_commit(self, nterms, scalars, points, threads=1):
+        sc = np.frombuffer(bytes(scalars), np.uint8).copy()
+        pt = np.frombuffer(bytes(points), np.uint8).copy()
+        n = pt.size // (64 * nterms)
+        out = np.zeros(64 * n, np.uint8)
+        rc = self.lib.orc_rep_commit(ctypes.c_size_t(n), nterms, self._p(sc), self._p(pt), self._p(out), threads)
+        return rc, out.tobytes()
+
+    def rep_respond(self, per, v, chal, x):
+        v = np.frombuffer(bytes(v), np.uint8).copy()
+        c = np.frombuffer(bytes(chal), np.uint8).copy()
+        x = np.frombuffer(bytes(x), np.uint8).copy()
+        n = v.size // 32
+        out = np.zeros(32 * n, np.uint8)
+        assert self.lib.orc_rep_respond(ctypes.c_size_t(n), per, self._p(v), self._p(c), self._p(x), self._p(out)) == 0
+        return out.tobytes()
+
+    def rep_verify(self, nterms, resp, chal, bases, P, V, threads=1):
+        arrs = [np.frombuffer(bytes(a), np.uint8).copy() for a in (resp, chal, bases, P, V)]
+        n = arrs[3].size // 64
+        ok = np.zeros(n, np.uint8)
+        assert self.lib.orc_rep_verify(ctypes.c_size_t(n), nterms, *[self._p(a) for a in arrs], self._p(ok), threads) == 0
+        return ok
+
     def key_switch(self, Q, sk, rbs, vs, threads=1):
         rb = np.frombuffer(bytes(rbs), np.uint8).copy()
         v = np.frombuffer(bytes(vs), np.uint8).copy()

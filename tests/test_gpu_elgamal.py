@@ -37,6 +37,14 @@ def test_field_ops_bit_exact(backend, rng):
         assert un(backend.mont_mul(which, a, b)) == [x * y * rinv % mod for x, y in zip(xs, ys)]
         assert un(backend.mont_mul(2 + 2 * which, a, b)) == [(x + y) % mod for x, y in zip(xs, ys)]
         assert un(backend.mont_mul(3 + 2 * which, a, b)) == [(x - y) % mod for x, y in zip(xs, ys)]
+    # the dual-product pass (fp.cuh mont_mul2) with multipliers up to 2^256 - 1: the second conditional subtraction
+    # is a rarely taken branch, (p - 1)(2^256 - 1) twice over takes it
+    xs = [R.p - 1, R.p - 1, 0, 1, R.p - 1] + [rng.scalar() % R.p for _ in range(N - 5)]
+    ys = [2 ** 256 - 1, R.p, 2 ** 256 - 1, 2 ** 256 - 1, 2 ** 255] + [(rng.scalar() * 3) % 2 ** 256 for _ in range(N - 5)]
+    a = np.array([_limbs(x) for x in xs], np.uint32).ravel()
+    b = np.array([_limbs(y) for y in ys], np.uint32).ravel()
+    rinv = pow(1 << 256, -1, R.p)
+    assert un(backend.mont_mul(10, a, b)) == [2 * x * y * rinv % R.p for x, y in zip(xs, ys)]
 
 
 def test_generators_match_oracle(backend, oracle):

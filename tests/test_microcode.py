@@ -51,5 +51,5 @@ def test_scheduled_program_computes_the_pairing_and_matches_committed_tables(rng
         assert R.g2_on_curve(Qo) and not R.g2_in_subgroup(Qo)
         assert run(P, Qo)['SG'] != (0, 0)
     # the committed opcode stream is the one just generated
-    committed = [int(x) for x in re.findall(r'\d+', re.search(r'uc_ops\[UC_NPHASES\] = \{(.*?)\};', inc, re.S).group(1))]
-    assert committed == [gen.OPC[o] for o, _ in phases]
+    committed = [int(x) for x in re.findall(r'\d+', re.search(r'uc_ops\[UC_NPHASES \+ 1\] = \{(.*?)\};', inc, re.S).group(1))]
+    assert committed == [gen.OPC[o] for o, _ in phases] + [gen.OPC['NOP']]   # one idle phase closes the table

@@ -23,6 +23,16 @@ import bn256_ref as R  # noqa: E402
 OPS = ['NOP', 'MUL', 'ADD', 'SUB', 'DBL', 'NEG', 'MULXI', 'CONJ', 'MULC', 'MULFP0', 'MULFP1', 'INV', 'COPY', 'CONJMULC', 'MULFPC',
        'SUB2', 'AXI', 'X3', 'X4', 'X8', 'CYCM', 'CYCP', 'SQR', 'CHK']
 OPC = {n: i for i, n in enumerate(OPS)}
+
+
+def uniq(*xs):
+    """The distinct non-None operands in argument order (a set of nodes would iterate in address order and make the
+    slot assignment differ from run to run)."""
+    out = []
+    for x in xs:
+        if x is not None and all(x is not y for y in out):
+            out.append(x)
+    return out
 COST = {'MUL': 10, 'SQR': 7, 'INV': 120, 'MULC': 10, 'CONJMULC': 10, 'MULFP0': 7, 'MULFP1': 7, 'MULFPC': 7}
 
 
@@ -421,7 +431,7 @@ def fuse(g):
             if x is not None and n in x.users:
                 x.users.remove(n)
         n.op, n.a, n.b, n.c = op, a, b, c
-        for x in set(y for y in (a, b, c) if y is not None):
+        for x in uniq(a, b, c):
             if n not in x.users:
                 x.users.append(n)
 
@@ -605,7 +615,7 @@ def schedule(g, G, nslots, window=96):
         for n in padded:
             if n is None:
                 continue
-            for x in set(y for y in (n.a, n.b, n.c) if y is not None):
+            for x in uniq(n.a, n.b, n.c):
                 readers[x.id] = readers.get(x.id, 0) + 1
         for lane_id, n in enumerate(padded):
             if n is None:
@@ -631,7 +641,7 @@ def schedule(g, G, nslots, window=96):
             slot_of[n.id] = s
             max_used = max(max_used, max(slot_of.values()) + 1)
             lanes.append(n)
-            for x in set(y for y in (n.a, n.b, n.c) if y is not None):
+            for x in uniq(n.a, n.b, n.c):
                 if remaining_users[x.id] == -1:
                     continue
                 remaining_users[x.id] -= 1
@@ -802,14 +812,16 @@ def emit(g, phases, slot_of, used, G, nslots_arg, window, name='pairing'):
         f.write('};\n__device__ const uint32_t uc_constp[%d][8] = {\n' % max(1, len(g.constsp)))
         for c in g.constsp:
             f.write('  {%s},\n' % limbs(mont(c)))
-        f.write('};\n// one opcode per phase (warp-uniform: read through the constant cache)\n')
-        f.write('__constant__ uint8_t uc_ops[UC_NPHASES] = {\n')
+        f.write('};\n// one opcode per phase (warp-uniform: read through the constant cache); both tables end with one idle phase so\n'
+                '// that the interpreter can read one phase ahead without a bound check\n')
+        f.write('__constant__ uint8_t uc_ops[UC_NPHASES + 1] = {\n')
         for k in range(0, len(phases), 32):
             f.write('  ' + ', '.join(str(OPC[o]) for o, _ in phases[k:k + 32]) + ',\n')
+        f.write('  %d,\n' % OPC['NOP'])
         f.write('};\n// per program lane: x = dst | a << 16, y = b | c << 16, each the BYTE offset of the slot inside the item with the\n'
                 '// swizzle folded in (slot * 64 + UC_SWZ(slot) * 16); x = 0xffffffff: idle; b = constant index for MULC / CONJMULC / MULFPC\n')
-        f.write('__device__ const uint2 uc_prog[UC_NPHASES * UC_G] = {\n')
-        for op, lanes in phases:
+        f.write('__device__ const uint2 uc_prog[(UC_NPHASES + 1) * UC_G] = {\n')
+        for op, lanes in list(phases) + [('NOP', [])]:
             words = []
             for k in range(G):
                 if k < len(lanes) and lanes[k] is not None:
