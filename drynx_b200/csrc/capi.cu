@@ -857,7 +857,7 @@ int drx_schnorr_verify(drx_ctx* c, size_t n, const uint8_t* pub, const uint8_t* 
 }
 
 // ---- proof.Rep relations (obfuscation and key-switch proofs): commit, respond, verify
-static const int kRepMaxTerms = 8;
+static const int kRepMaxTerms = 4096;  // the widest use is the list compression of the shuffle proof: one term per ciphertext of a line
 int drx_rep_commit_dev(drx_ctx* c, size_t n, int nterms, const uint8_t* d_scalars, const uint8_t* d_points, uint8_t* d_out) {
   if (!c) return fail(-1, "null context");
   if (nterms < 1 || nterms > kRepMaxTerms) return fail(-1, "drx_rep_commit: nterms %d outside 1..%d", nterms, kRepMaxTerms);

@@ -201,7 +201,7 @@ int drx_schnorr_verify(drx_ctx* ctx, size_t n, const uint8_t* pub, const uint8_t
  * co1 = s*c1, co2 = s*c2) and unlynx's key-switch proof (libunlynxkeyswitch.KeySwitchListProofCreation /
  * KeySwitchListProofVerification, unlynx v1.4.0; call sites services/service.go:581, data/data.go:81,
  * lib/proof/structs_proofs.go:469-482: viB = vi*B, K = k*B, ks2 = vi*Q + k*rBNeg). A relation is
- * P = x_1*B_1 + ... + x_T*B_T (T = nterms >= 1). As kyber v3.0.8 proof/rep.go does it: the prover sends
+ * P = x_1*B_1 + ... + x_T*B_T (T = nterms, 1..4096). As kyber v3.0.8 proof/rep.go does it: the prover sends
  * V = sum_j v_j*B_j (drx_rep_commit; with nterms = 1 on both halves of a ciphertext it equals drx_ct_scalar_mul),
  * the challenge c comes out of the transcript hash of every V of the proof, the answers are r_j = v_j - c*x_j
  * (drx_rep_respond: `per` consecutive secrets share challenge i / per), and the verifier accepts when
@@ -209,7 +209,10 @@ int drx_schnorr_verify(drx_ctx* ctx, size_t n, const uint8_t* pub, const uint8_t
  * stays on the caller's side: the challenge is an input here, the proof bytes are V's then r's in kyber's order.
  * scalars, resp, chal: 32 bytes big-endian; points 64 bytes. drx_rep_commit returns -2 on a malformed point;
  * drx_rep_verify gives ok[i] = 0 for a malformed point or a response >= n (kyber fails that proof), never an error
- * of the call. */
+ * of the call. drx_rep_commit with nterms = the length of a line also is the list compression that opens unlynx's shuffle
+ * proof (libunlynxshuffle.ShuffleProofCreation / ShuffleProofVerification, call sites services/service.go:634,
+ * data/data.go:69, lib/proof/structs_proofs.go:392-403: sum_j e_j*K_ij and sum_j e_j*C_ij per line i); the Neff
+ * pair-shuffle argument that follows it (kyber shuffle.PairShuffle) is not offered here. */
 int drx_rep_commit(drx_ctx* ctx, size_t n, int nterms, const uint8_t* scalars /*n*nterms*32*/,
                    const uint8_t* points /*n*nterms*64*/, uint8_t* out /*n*64*/);
 int drx_rep_commit_dev(drx_ctx* ctx, size_t n, int nterms, const uint8_t* d_scalars, const uint8_t* d_points, uint8_t* d_out);

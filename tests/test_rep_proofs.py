@@ -150,6 +150,32 @@ def test_gpu_rep_steps_match_oracle(backend, oracle, rng):
 
 
 @pytest.mark.gpu
+def test_gpu_line_compression_of_the_shuffle_proof(backend, oracle, rng):
+    """The list compression that opens unlynx's shuffle proof (sum_j e_j * ct_ij per line, K and C apart) is
+    rep_commit with one term per ciphertext of the line: 12 lines of 40 ciphertexts, bytes against the oracle, and
+    the plaintext of the compressed ciphertext is the same combination of the plaintexts."""
+    lines, nq = 12, 40
+    sk = rng.scalar()
+    P = _pt(sk)
+    backend.set_pubkey(P)
+    g = np.random.default_rng(5)
+    ms = [[int(v) for v in g.integers(0, 50, size=nq)] for _ in range(lines)]
+    cts = [backend.encrypt_int_vector(m, rng.scalars_bytes(nq)).tobytes() for m in ms]
+    e = [int(v) for v in g.integers(0, 40, size=nq)]                      # small, so that the result decrypts
+    eb = b''.join(v.to_bytes(32, 'big') for v in e)
+    Ks = b''.join(ct[128 * j:128 * j + 64] for ct in cts for j in range(nq))
+    Cs = b''.join(ct[128 * j + 64:128 * j + 128] for ct in cts for j in range(nq))
+    K = backend.rep_commit(nq, eb * lines, Ks).tobytes()
+    C = backend.rep_commit(nq, eb * lines, Cs).tobytes()
+    assert (0, K) == oracle.rep_commit(nq, eb * lines, Ks, threads=8) and (0, C) == oracle.rep_commit(nq, eb * lines, Cs, threads=8)
+    comp = b''.join(K[64 * i:64 * i + 64] + C[64 * i:64 * i + 64] for i in range(lines))
+    out = backend.decrypt_int_vector(sk.to_bytes(32, 'big'), comp)
+    assert list(out) == [sum(a * b for a, b in zip(e, m)) for m in ms]
+    with pytest.raises(RuntimeError):
+        backend.rep_commit(5000, bytes(32 * 5000), bytes(64 * 5000))
+
+
+@pytest.mark.gpu
 def test_gpu_obfuscation_list_proof(backend, oracle, rng):
     """ObfuscationListProofCreation / Verification on 300 ciphertexts: proofs byte-identical to the oracle's, accepted by
     both, and each kind of tampering rejected by both alike."""
