@@ -3,6 +3,9 @@
 // UC_PROGRAM_INC (the generated tables it runs): ucode_split.cuh for the pairing, kernels_rp_gtlanes.cu for the Fp12
 // multiplication behind fixed-base GT exponentiations.
 #include UC_PROGRAM_INC
+#ifdef UCS_PROFILE
+static __device__ unsigned long long uc_prof[64];  // [op]: cycles, [32 + op]: phases
+#endif
 
 #define UCS_TPI (2 * UC_G)  // threads per item
 #ifndef UCS_BLOCK
@@ -18,6 +21,7 @@
 #define UCS_MIN_BLOCKS 8  // 16 warps per SM: at most 128 registers per thread
 #endif
 #define UCS_ITEM_BYTES (UC_NSLOTS * 64)
+static_assert(UC_PAD_PHASES >= 1, "the interpreter reads one phase ahead");
 static_assert(UC_NSLOTS <= (int)kUcMaxSlots, "slot-image area is sized for kUcMaxSlots");
 
 // Shared-memory slot access by 32-bit shared-window address. A slot is 64 bytes = four 16-byte chunks; logical chunk c
@@ -87,118 +91,117 @@ __device__ __forceinline__ Fp ucs_xi_c(const Fp& ah, const Fp& ao, uint32_t h) {
   return h ? fp_add(t, ao) : fp_sub(t, ao);
 }
 
+// One phase of one thread: component h of the lane's result. All loads of the phase happen in here, before the caller's
+// barrier. `op` is the uc_ops byte: the class bits are walked first (7, 6, 5 -- ADD is two tests away, SUB2 / AXI / MUL /
+// SQR three), the opcode proper only for the rest; a balanced search over all opcodes, which is what a plain switch
+// compiles to, costs five dependent compare-and-branch pairs per phase, ~175 cycles of a lone warp's ~400-cycle phase.
+__device__ __forceinline__ Fp ucs_phase(uint32_t S, uint32_t op, uint2 w, uint32_t h) {
+  const uint32_t ia = w.x >> 16, ib = w.y & 0xffffu, ic = w.y >> 16;
+  if (op & 0x80u) {
+    if (op & 0x40u) return fp_add(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h));                                      // ADD
+    if (op & 0x20u) return fp_sub(fp_sub(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h)), ucs_load_c(S, ic, h));      // SUB2
+    return fp_add(ucs_load_c(S, ia, h), ucs_xi_c(ucs_load_c(S, ib, h), ucs_load_c(S, ib, h ^ 1u), h));             // AXI
+  }
+  if (op & 0x40u) {
+    const Fp2 a = ucs_load(S, ia);
+    if (op & 0x20u) {  // MUL: c0 = a0 b0 + a1 (p - b1) on h = 0, c1 = a0 b1 + a1 b0 on h = 1
+      const Fp x = ucs_load_c(S, ib, h), yr = ucs_load_c(S, ib, h ^ 1u);
+      return ucs_dual(a.c0, x, a.c1, fp_sel(h != 0, yr, ucs_neg_raw(yr)));
+    }
+    // SQR: (a0 + a1)(a0 - a1) on h = 0, (a0 + a0) a1 on h = 1: one product each
+    const Fp x = fp_add(a.c0, fp_sel(h != 0, a.c0, a.c1));
+    const Fp y = fp_sel(h != 0, a.c1, fp_sub(a.c0, a.c1));
+    return fp_mul_inl(x, y);
+  }
+  const uint32_t code = op & 31u;
+  if (op & 0x20u) {
+    if (code == UC_MULXI) return ucs_xi_c(ucs_load_c(S, ia, h), ucs_load_c(S, ia, h ^ 1u), h);
+    const Fp a = ucs_load_c(S, ia, h), b = ucs_load_c(S, ib, h);
+    if (code == UC_SUB) return fp_sub(a, b);
+    const Fp s = code == UC_CYCP ? fp_add(a, b) : fp_sub(a, b);  // CYCP / CYCM: 3a +- 2b
+    return fp_add(fp_add(s, s), a);
+  }
+  switch (code) {
+    case UC_MULFP0:
+    case UC_MULFP1:
+      return fp_mul(ucs_load_c(S, ia, h), ucs_load_c(S, ib, code == UC_MULFP1 ? 1u : 0u));
+    case UC_X4:
+    case UC_X8:
+    case UC_X3: {
+      const Fp a = ucs_load_c(S, ia, h);
+      const Fp d2 = fp_add(a, a);
+      if (code == UC_X3) return fp_add(d2, a);
+      const Fp d4 = fp_add(d2, d2);
+      return code == UC_X8 ? fp_add(d4, d4) : d4;
+    }
+    case UC_NEG:
+      return fp_neg(ucs_load_c(S, ia, h));
+    case UC_CONJMULC:
+    case UC_MULC: {
+      // (a0 +- a1 i)(k0 + k1 i): MULC c0 = a0 k0 + a1 (p - k1), c1 = a0 k1 + a1 k0;
+      // CONJMULC c0 = a0 k0 + a1 k1, c1 = a0 k1 + a1 (p - k0)
+      const Fp2 a = ucs_load(S, ia);
+      const Fp x = ucs_const2_c(ib, h), yr = ucs_const2_c(ib, h ^ 1u);
+      const bool negate = (code == UC_MULC) == (h == 0);
+      return ucs_dual(a.c0, x, a.c1, fp_sel(negate, ucs_neg_raw(yr), yr));
+    }
+    case UC_MULFPC:
+      return fp_mul(ucs_load_c(S, ia, h), uc_constp_(ib));
+    case UC_CONJ: {
+      const Fp a = ucs_load_c(S, ia, h);
+      return h ? fp_neg(a) : a;
+    }
+    case UC_INV: {
+      Fp2 tmp = ucs_load(S, ia);  // both threads invert (same instructions either way) and keep their component
+      const Fp2 v = fp2_inv(tmp);
+      return fp_sel(h != 0, v.c1, v.c0);
+    }
+    case UC_CHK: {
+      // verdict of the G2 membership test: zero iff a == 0, b == 0 and c != 0 (see tools/microcode/gen.py)
+      const bool good = fp2_is_zero(ucs_load(S, ia)) & fp2_is_zero(ucs_load(S, ib)) & !fp2_is_zero(ucs_load(S, ic));
+      return good ? fp_zero() : fp_one();
+    }
+    default:
+      return ucs_load_c(S, ia, h);  // UC_COPY
+  }
+}
+
 // Phases [ph0, ph1) of the program on the item at shared address S; all lanes of the warp call it together. Slots are
 // reused in place (a phase may overwrite one of its own operands), and the two threads of a pair read each other's
-// components, so every load of a phase is separated from every store by a warp barrier.
+// components, so every load of a phase is separated from every store by a warp barrier. Lanes a phase leaves idle and
+// threads with `alive` false skip it. (Letting them run the phase on a spare slot instead, to drop the divergent region
+// around the dispatch, was measured: 480 checks 2.45 -> 3.14 ms, 6,000 checks 4.07 -> 4.78 ms. Dropped.)
 __device__ __forceinline__ void ucs_run(uint32_t S, int lane, uint32_t h, bool alive, int ph0, int ph1) {
-  // the next phase's opcode and lane word are fetched one phase ahead; both tables end with one idle phase, so the
-  // read ahead needs no bound check
+  // the next phase's opcode and lane word are fetched one phase ahead; both tables end with idle phases, so the read
+  // ahead needs no bound check. (An L1 prefetch of the lane words four phases ahead saves a lone warp 25 cycles per
+  // phase and costs a full machine 1-2 %: not kept.)
   const uint2* pw = uc_prog + ph0 * UC_G + lane;
   uint32_t op = uc_ops[ph0];
   uint2 w = *pw;
+#ifdef UCS_PROFILE  // tools/phase_profile.py: cycles per opcode as the first warp of the grid sees them
+  const bool prof = blockIdx.x == 0 && threadIdx.x == 0;
+  long long prof_t0 = clock64();
+#endif
   for (int ph = ph0; ph < ph1; ph++) {
     pw += UC_G;
     const uint32_t op_n = uc_ops[ph + 1];
     const uint2 w_n = *pw;
     const bool act = alive && w.x != 0xffffffffu;
-    const uint32_t d = w.x & 0xffffu, ia = w.x >> 16, ib = w.y & 0xffffu, ic = w.y >> 16;
     Fp r;
-    if (act) {
-      switch (op) {
-        case UC_ADD:
-          r = fp_add(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h));
-          break;
-        case UC_MUL: {
-          const Fp2 a = ucs_load(S, ia);
-          const Fp x = ucs_load_c(S, ib, h), yr = ucs_load_c(S, ib, h ^ 1u);
-          r = ucs_dual(a.c0, x, a.c1, fp_sel(h != 0, yr, ucs_neg_raw(yr)));
-          break;
-        }
-        case UC_SQR: {
-          // (a0 + a1)(a0 - a1) on h = 0, (a0 + a0) a1 on h = 1: one product each
-          const Fp2 a = ucs_load(S, ia);
-          const Fp x = fp_add(a.c0, fp_sel(h != 0, a.c0, a.c1));
-          const Fp y = fp_sel(h != 0, a.c1, fp_sub(a.c0, a.c1));
-          r = fp_mul_inl(x, y);
-          break;
-        }
-        case UC_SUB2:
-          r = fp_sub(fp_sub(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h)), ucs_load_c(S, ic, h));
-          break;
-        case UC_AXI:
-          r = fp_add(ucs_load_c(S, ia, h), ucs_xi_c(ucs_load_c(S, ib, h), ucs_load_c(S, ib, h ^ 1u), h));
-          break;
-        case UC_SUB:
-          r = fp_sub(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h));
-          break;
-        case UC_CYCP:
-        case UC_CYCM: {
-          const Fp a = ucs_load_c(S, ia, h), b = ucs_load_c(S, ib, h);
-          const Fp s = op == UC_CYCP ? fp_add(a, b) : fp_sub(a, b);
-          r = fp_add(fp_add(s, s), a);
-          break;
-        }
-        case UC_MULXI:
-          r = ucs_xi_c(ucs_load_c(S, ia, h), ucs_load_c(S, ia, h ^ 1u), h);
-          break;
-        case UC_MULFP0:
-        case UC_MULFP1:
-          r = fp_mul(ucs_load_c(S, ia, h), ucs_load_c(S, ib, op == UC_MULFP1 ? 1u : 0u));
-          break;
-        case UC_X4:
-        case UC_X8:
-        case UC_X3: {
-          const Fp a = ucs_load_c(S, ia, h);
-          const Fp d2 = fp_add(a, a);
-          if (op == UC_X3) {
-            r = fp_add(d2, a);
-          } else {
-            r = fp_add(d2, d2);
-            if (op == UC_X8) r = fp_add(r, r);
-          }
-          break;
-        }
-        case UC_NEG:
-          r = fp_neg(ucs_load_c(S, ia, h));
-          break;
-        case UC_CONJMULC:
-        case UC_MULC: {
-          // (a0 +- a1 i)(k0 + k1 i): MULC c0 = a0 k0 + a1 (p - k1), c1 = a0 k1 + a1 k0;
-          // CONJMULC c0 = a0 k0 + a1 k1, c1 = a0 k1 + a1 (p - k0)
-          const Fp2 a = ucs_load(S, ia);
-          const Fp x = ucs_const2_c(ib, h), yr = ucs_const2_c(ib, h ^ 1u);
-          const bool negate = (op == UC_MULC) == (h == 0);
-          r = ucs_dual(a.c0, x, a.c1, fp_sel(negate, ucs_neg_raw(yr), yr));
-          break;
-        }
-        case UC_MULFPC:
-          r = fp_mul(ucs_load_c(S, ia, h), uc_constp_(ib));
-          break;
-        case UC_CONJ: {
-          const Fp a = ucs_load_c(S, ia, h);
-          r = h ? fp_neg(a) : a;
-          break;
-        }
-        case UC_INV: {
-          Fp2 tmp = ucs_load(S, ia);  // both threads invert (same instructions either way) and keep their component
-          const Fp2 v = fp2_inv(tmp);
-          r = fp_sel(h != 0, v.c1, v.c0);
-          break;
-        }
-        case UC_CHK: {
-          // verdict of the G2 membership test: zero iff a == 0, b == 0 and c != 0 (see tools/microcode/gen.py)
-          const bool good = fp2_is_zero(ucs_load(S, ia)) & fp2_is_zero(ucs_load(S, ib)) & !fp2_is_zero(ucs_load(S, ic));
-          r = good ? fp_zero() : fp_one();
-          break;
-        }
-        default:
-          r = ucs_load_c(S, ia, h);  // UC_COPY
-          break;
+    if (act) r = ucs_phase(S, op, w, h);
+    __syncwarp();
+    if (act) ucs_store_c(S, w.x & 0xffffu, h, r);
+    __syncwarp();
+#ifdef UCS_PROFILE
+    {
+      const long long t1 = clock64();
+      if (prof) {
+        uc_prof[op & 31u] += (unsigned long long)(t1 - prof_t0);
+        uc_prof[32u + (op & 31u)] += 1ull;
       }
+      prof_t0 = t1;
     }
-    __syncwarp();
-    if (act) ucs_store_c(S, d, h, r);
-    __syncwarp();
+#endif
     op = op_n;
     w = w_n;
   }

@@ -171,4 +171,14 @@ int UCS_LAUNCH(cudaStream_t st, size_t items, const void* d_prep, void* d_scratc
   return launches;
 }
 
+#ifdef UCS_PROFILE
+// Experiment builds only (tools/phase_profile.py): reads and clears the per-opcode cycle counters.
+extern "C" int drx_debug_phase_profile(unsigned long long* out64) {
+  static const unsigned long long zero[64] = {0};
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  if (cudaMemcpyFromSymbol(out64, uc_prof, sizeof(zero)) != cudaSuccess) return -1;
+  return cudaMemcpyToSymbol(uc_prof, zero, sizeof(zero)) == cudaSuccess ? 0 : -1;
+}
+#endif
+
 }  // namespace drx

@@ -51,5 +51,8 @@ def test_scheduled_program_computes_the_pairing_and_matches_committed_tables(rng
         assert R.g2_on_curve(Qo) and not R.g2_in_subgroup(Qo)
         assert run(P, Qo)['SG'] != (0, 0)
     # the committed opcode stream is the one just generated
-    committed = [int(x) for x in re.findall(r'\d+', re.search(r'uc_ops\[UC_NPHASES \+ 1\] = \{(.*?)\};', inc, re.S).group(1))]
-    assert committed == [gen.OPC[o] for o, _ in phases] + [gen.OPC['NOP']]   # one idle phase closes the table
+    committed = [int(x) for x in re.findall(r'\d+', re.search(r'uc_ops\[UC_NPHASES \+ UC_PAD_PHASES\] = \{(.*?)\};', inc, re.S).group(1))]
+    pad = int(re.search(r'#define UC_PAD_PHASES (\d+)', inc).group(1))
+    assert pad >= 8 and committed == [gen.op_byte(o) for o, _ in phases] + [gen.op_byte('NOP')] * pad   # idle phases close the table
+    # opcode in the low five bits, dispatch class above
+    assert all(gen.op_byte(o) & 31 == gen.OPC[o] and gen.op_byte(o) >> 5 == gen.OP_CLASS.get(o, 0) for o in gen.OPS)
