@@ -74,17 +74,40 @@ def parse():
 
 
 class Clocks(threading.Thread):
-    """Samples nvidia-smi clocks and throttle reasons during the timed region."""
+    """Samples SM clocks and throttle reasons during the timed region: through NVML every 2 ms when nvidia-ml-py is
+    there (the timed region of a default run is ~30 ms), else through nvidia-smi (one sample per ~0.25 s)."""
     Q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,' \
         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+    NAMES = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+    NVML_BITS = [0x8, 0x40, 0x20, 0x4]   # nvmlClocksThrottleReason{HwSlowdown, HwThermalSlowdown, SwThermalSlowdown, SwPowerCap}
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.stop_flag, self.rows = index, False, []
+        self.index, self.stop_flag, self.rows, self.source = index, False, [], 'nvidia-smi'
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:   # CUDA and NVML may number the devices differently: go by UUID when torch exposes it
+                import torch
+                uuid = 'GPU-' + str(torch.cuda.get_device_properties(index).uuid)
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+            self.nvml, self.source = pynvml, 'nvml'
+        except Exception:
+            self.nvml = None
 
     def run(self):
         while not self.stop_flag:
             try:
+                if self.nvml is not None:
+                    mhz = self.nvml.nvmlDeviceGetClockInfo(self.handle, self.nvml.NVML_CLOCK_SM)
+                    bits = self.nvml.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                    self.rows.append([str(mhz), str(self.max_mhz)] + ['Active' if bits & b else 'Not Active' for b in self.NVML_BITS])
+                    time.sleep(0.002)
+                    continue
                 out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits'],
                                      capture_output=True, text=True, timeout=5).stdout.strip()
                 if out:
@@ -97,11 +120,10 @@ class Clocks(threading.Thread):
         if not self.rows:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
         sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
-        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith('active') for r in self.rows if len(r) > 2 + k)]
+        reasons = [n for k, n in enumerate(self.NAMES) if any(r[2 + k].lower().startswith('active') for r in self.rows if len(r) > 2 + k)]
         mx = [int(r[1]) for r in self.rows if r[1].isdigit()]
         return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None, 'reasons': reasons,
-                'samples': len(self.rows)}
+                'samples': len(self.rows), 'source': self.source}
 
 
 def synth(seed, ndp, rows):

@@ -83,6 +83,32 @@ def test_dev_calls_report_malformed_points_through_take_bad(backend, oracle, rng
     cv, neg = d_cv.cpu().numpy().reshape(n, 128), d_neg.cpu().numpy().reshape(n, 64)
     assert all(not cv[i].any() and not neg[i].any() for i in bad_rows)
 
+    # proof.Rep commitments over device buffers: V_i = s_i*K_i + s_i*C_i per ciphertext (two terms); the rejected rows are
+    # zeroed and counted, the others equal the oracle's; verification over device buffers accepts exactly the rows that hold
+    s2 = torch.from_numpy(np.repeat(s.cpu().numpy().reshape(n, 32), 2, axis=0).ravel()).cuda()
+    d_V = torch.full((n * 64,), 0xCD, dtype=torch.uint8, device='cuda')
+    ck(lib.drx_rep_commit_dev(backend.h, n, 2, _vp(s2), _vp(d_ct), _vp(d_V)))
+    assert backend.take_bad() == len(bad_rows)
+    V = d_V.cpu().numpy().reshape(n, 64)
+    good = [i for i in range(n) if i not in bad_rows]
+    rcV, wantV = oracle.rep_commit(2, b''.join(s2.cpu().numpy().reshape(n, 64)[i].tobytes() for i in good),
+                                   b''.join(rows[i] for i in good), threads=8)
+    assert rcV == 0 and all(not V[i].any() for i in bad_rows)
+    assert b''.join(V[i].tobytes() for i in good) == wantV
+    # relations P = x*K + x*C with x = 1: P is V for s = 1; check r*K + r*C + c*P == V' for a made-up transcript
+    ones = torch.from_numpy(np.tile(np.frombuffer((1).to_bytes(32, 'big'), np.uint8), 2 * n)).cuda()
+    d_P = torch.empty(n * 64, dtype=torch.uint8, device='cuda')
+    ck(lib.drx_rep_commit_dev(backend.h, n, 2, _vp(ones), _vp(d_ct), _vp(d_P)))
+    assert backend.take_bad() == len(bad_rows)
+    chal = torch.from_numpy(_scalars(g, n)).cuda()
+    resp = backend.rep_respond(1, s.cpu().numpy(), chal.cpu().numpy(), np.tile(np.frombuffer((1).to_bytes(32, 'big'), np.uint8), n))
+    d_resp = torch.from_numpy(np.repeat(resp.reshape(n, 32), 2, axis=0).ravel()).cuda()
+    d_ok = torch.full((n,), 7, dtype=torch.uint8, device='cuda')
+    ck(lib.drx_rep_verify_dev(backend.h, n, 2, _vp(d_resp), _vp(chal), _vp(d_ct), _vp(d_P), _vp(d_V), _vp(d_ok)))
+    backend.synchronize()                                           # a _dev call returns once its work is queued
+    ok = d_ok.cpu().numpy()
+    assert [i for i in range(n) if ok[i] == 0] == bad_rows and all(ok[i] == 1 for i in good)
+
 
 def test_rp_dev_calls_validate_shape_and_set_ids(backend, oracle, rng):
     import torch
