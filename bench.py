@@ -21,6 +21,17 @@ import time
 
 import numpy as np
 
+# stdout carries the one JSON line and nothing else: file descriptor 1 is pointed at stderr for the run (NCCL prints its
+# "NCCL version ..." banner, and more with NCCL_DEBUG=INFO, straight to fd 1) and the line goes to the saved descriptor
+_RESULT_OUT = os.fdopen(os.dup(1), 'w')
+os.dup2(2, 1)
+
+
+def emit(line):
+    _RESULT_OUT.write(line + '\n')
+    _RESULT_OUT.flush()
+
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -235,7 +246,7 @@ def run_reference(args):
     sg_rate = 1024 / (time.perf_counter() - t1)
     assert bool(sg_ok.all())
     sample = '%d of %d DPs x %d rows (%d proofs/step), oracle/oracle.cpp C++ restatement of the Go path' % (ndp, args.ndp, args.rows, n)
-    print(json.dumps({
+    emit(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'proofs/s', 'n_gpus': args.gpus, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': dt / args.steps * 1e3, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'u64 (4x64-bit Montgomery limbs)', 'data': 'synthetic',
@@ -534,7 +545,7 @@ def run_gpu(args):
     }
     if cpu is not None:
         out['cpu_baseline'] = cpu
-    print(json.dumps(out))
+    emit(json.dumps(out))
 
 
 def secondary_rates(be, lib, torch, dev, stream, ck, vp, peak_tmac, skp):
