@@ -54,5 +54,9 @@ def test_scheduled_program_computes_the_pairing_and_matches_committed_tables(rng
     committed = [int(x) for x in re.findall(r'\d+', re.search(r'uc_ops\[UC_NPHASES \+ UC_PAD_PHASES\] = \{(.*?)\};', inc, re.S).group(1))]
     pad = int(re.search(r'#define UC_PAD_PHASES (\d+)', inc).group(1))
     assert pad >= 8 and committed == [gen.op_byte(o) for o, _ in phases] + [gen.op_byte('NOP')] * pad   # idle phases close the table
+    # ... and so is every lane word (the generator is deterministic)
+    words = re.search(r'uc_prog\[[^\]]*\] = \{(.*?)\n\};', inc, re.S).group(1)
+    committed_words = [(int(x, 16), int(y, 16)) for x, y in re.findall(r'\{0x([0-9a-f]{8})u, 0x([0-9a-f]{8})u\}', words)]
+    assert committed_words == [w for ph in gen.prog_words(phases, slot_of, G) for w in ph]
     # opcode in the low five bits, dispatch class above
     assert all(gen.op_byte(o) & 31 == gen.OPC[o] and gen.op_byte(o) >> 5 == gen.OP_CLASS.get(o, 0) for o in gen.OPS)

@@ -787,15 +787,38 @@ def mont(x):
     return (x % R.p) * (1 << 256) % R.p
 
 
+def slot_offset(s_, G):
+    """Byte offset of a slot inside an item with the swizzle folded in. With two threads per program lane the 8 (G = 4) or
+    16 (G = 8) threads of an item read, in one instruction, chunk 2h + k of their lane's slot; bank group of that access =
+    4 (slot & 1) + ((2h + k) ^ swz(slot)). For lanes whose slots differ mod 4 (mod 8) the rotation below makes the groups
+    of one item all distinct (each twice for G = 8): no replays. (slot & 3, the round-1 rule for one thread per lane, put
+    slots s and s + 2 of the two halves on the same groups: ncu counted 2.4x the ideal wavefronts.)"""
+    rot = (s_ >> 1) & 1 if G <= 4 else (s_ >> 1) & 3
+    return s_ * 64 + rot * 16
+
+
+def prog_words(phases, slot_of, G):
+    """The emitted lane words, one list of G (x, y) pairs per phase, closing idle phases included."""
+    out = []
+    for op, lanes in list(phases) + [('NOP', [])] * PAD_PHASES:
+        words = []
+        for k in range(G):
+            if k < len(lanes) and lanes[k] is not None:
+                n = lanes[k]
+                a = slot_offset(slot_of[n.a.id], G) if n.a is not None else 0
+                b = slot_offset(slot_of[n.b.id], G) if n.b is not None else n.imm
+                c = slot_offset(slot_of[n.c.id], G) if n.c is not None else 0
+                d = slot_offset(slot_of[n.id], G)
+                assert max(a, b, c, d) < 65535
+                words.append((d | a << 16, b | c << 16))
+            else:
+                words.append((0xffffffff, 0xffffffff))
+        out.append(words)
+    return out
+
+
 def emit(g, phases, slot_of, used, G, nslots_arg, window, name='pairing'):
     path = os.path.join(ROOT, 'drynx_b200', 'csrc', '%s_ucode_g%d.inc' % (name, G))
-    # Swizzle: with two threads per program lane the 8 (G = 4) or 16 (G = 8) threads of an item read, in one instruction,
-    # chunk 2h + k of their lane's slot; bank group of that access = 4 (slot & 1) + ((2h + k) ^ swz(slot)). For lanes whose
-    # slots differ mod 4 (mod 8) the choice below makes the groups of one item all distinct (each twice for G = 8): no replays.
-    # (slot & 3, the round-1 rule for one thread per lane, put slots s and s + 2 of the two halves on the same groups:
-    # ncu counted 2.4x the ideal wavefronts.)
-    rot = (lambda s_: (s_ >> 1) & 1) if G <= 4 else (lambda s_: (s_ >> 1) & 3)
-    off = lambda s_: s_ * 64 + rot(s_) * 16   # byte offset of a slot inside an item, swizzle folded in
     with open(path, 'w') as f:
         f.write('// GENERATED by tools/microcode/gen.py %s%d %d ... --emit -- do not edit.\n' % ('' if name == 'pairing' else name + ' ', G, used))
         what = 'the optimal ate pairing plus the G2 membership verdict' if name == 'pairing' else 'one Fp12 multiplication A <- A * B'
@@ -836,20 +859,8 @@ def emit(g, phases, slot_of, used, G, nslots_arg, window, name='pairing'):
         f.write('};\n// per program lane: x = dst | a << 16, y = b | c << 16, each the BYTE offset of the slot inside the item with the\n'
                 '// swizzle folded in (slot * 64 + UC_SWZ(slot) * 16); x = 0xffffffff: idle; b = constant index for MULC / CONJMULC / MULFPC\n')
         f.write('__device__ const uint2 uc_prog[(UC_NPHASES + UC_PAD_PHASES) * UC_G] = {\n')
-        for op, lanes in list(phases) + [('NOP', [])] * PAD_PHASES:
-            words = []
-            for k in range(G):
-                if k < len(lanes) and lanes[k] is not None:
-                    n = lanes[k]
-                    a = off(slot_of[n.a.id]) if n.a is not None else 0
-                    b = off(slot_of[n.b.id]) if n.b is not None else n.imm
-                    c = off(slot_of[n.c.id]) if n.c is not None else 0
-                    d = off(slot_of[n.id])
-                    assert max(a, b, c, d) < 65535
-                    words.append('{0x%08xu, 0x%08xu}' % (d | a << 16, b | c << 16))
-                else:
-                    words.append('{0xffffffffu, 0xffffffffu}')
-            f.write('  ' + ', '.join(words) + ',\n')
+        for words in prog_words(phases, slot_of, G):
+            f.write('  ' + ', '.join('{0x%08xu, 0x%08xu}' % w for w in words) + ',\n')
         f.write('};\n')
     print('wrote', path, os.path.getsize(path), 'bytes')
 
