@@ -50,6 +50,7 @@ M_DECRYPT = 2840
 G1_BYTES = bytes(31) + b'\x01' + (65000549695646603732796438742359905742825358107623003571877145026864184071783 - 2).to_bytes(32, 'big')
 M_OBFUSCATE = 2 * 2816 + 16               # two 4-bit-window products, two affine outputs sharing one inversion
 M_SHUFFLE = 352 + 352 + 11 + 11 + 16       # two comb walks, two mixed additions, two affine outputs
+M_REP1 = 2 * 2816 + 16 + 11             # one proof.Rep relation with one term: r*B and c*P by 4-bit windows, one addition, one mixed addition
 M_KEYSWITCH = 352 + 352 + 2816 + 16 + 16   # v*B and v*Q by comb, x*rB by 4-bit windows, one addition, two affine outputs
 
 
@@ -598,6 +599,20 @@ def secondary_rates(be, lib, torch, dev, stream, ck, vp, peak_tmac, skp):
     ms = timed(lambda: ck(lib.drx_ct_scalar_mul_dev(be.h, nd, vp(r), vp(ct), vp(obf))))
     out['obfuscations_per_s'] = nd / ms * 1e3
     out['obfuscation_roofline_frac'] = nd * M_OBFUSCATE * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
+    # obfuscation list proof over the same ciphertexts (lib/obfuscation/obfuscation_proof.go): commitments V = v*c, responses
+    # r = v - ch*s, and the verifier's 2^18 relations r*c_k + ch*co_k == V_k; the transcript hash is the caller's, a stand-in here
+    v_bl, ch = r.view(-1, 32).roll(1, 0).contiguous().view(-1), r.view(-1, 32).roll(2, 0).contiguous().view(-1)
+    V = torch.empty(nd * 128, dtype=torch.uint8, device=dev)
+    ck(lib.drx_ct_scalar_mul_dev(be.h, nd, vp(v_bl), vp(ct), vp(V)))
+    resp_h = be.rep_respond(1, v_bl[:nd * 32].cpu().numpy(), ch[:nd * 32].cpu().numpy(), r[:nd * 32].cpu().numpy())
+    resp2 = torch.from_numpy(resp_h).to(dev).view(nd, 32).repeat_interleave(2, dim=0).contiguous()
+    ch2 = ch[:nd * 32].view(nd, 32).repeat_interleave(2, dim=0).contiguous()
+    okr = torch.zeros(2 * nd, dtype=torch.uint8, device=dev)
+    ms = timed(lambda: ck(lib.drx_rep_verify_dev(be.h, 2 * nd, 1, vp(resp2), vp(ch2), vp(ct), vp(obf), vp(V), vp(okr))))
+    be.synchronize()
+    assert bool((okr == 1).all()), 'an obfuscation proof relation failed'
+    out['obfuscation_proofs_verified_per_s'] = nd / ms * 1e3
+    out['obfuscation_proof_roofline_frac'] = 2 * nd * M_REP1 * MAC32_PER_M / (ms * 1e-3) / 1e12 / peak_tmac
     # shuffling (ShuffleSequence re-randomisation) of the same ciphertexts as 2^10 lines of 2^7
     perm = torch.from_numpy(np.random.default_rng(6).permutation(1 << 10).astype(np.int32)).to(dev)
     ms = timed(lambda: ck(lib.drx_shuffle_rerandomize_dev(be.h, 1 << 10, 1 << 7, vp(perm), vp(ct), vp(r), vp(obf))))
