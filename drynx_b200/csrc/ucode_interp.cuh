@@ -102,18 +102,36 @@ __device__ __forceinline__ Fp ucs_phase(uint32_t S, uint32_t op, uint2 w, uint32
     if (op & 0x20u) return fp_sub(fp_sub(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h)), ucs_load_c(S, ic, h));      // SUB2
     return fp_add(ucs_load_c(S, ia, h), ucs_xi_c(ucs_load_c(S, ib, h), ucs_load_c(S, ib, h ^ 1u), h));             // AXI
   }
+  const uint32_t code = op & 31u;
   if (op & 0x40u) {
-    const Fp2 a = ucs_load(S, ia);
-    if (op & 0x20u) {  // MUL: c0 = a0 b0 + a1 (p - b1) on h = 0, c1 = a0 b1 + a1 b0 on h = 1
-      const Fp x = ucs_load_c(S, ib, h), yr = ucs_load_c(S, ib, h ^ 1u);
-      return ucs_dual(a.c0, x, a.c1, fp_sel(h != 0, yr, ucs_neg_raw(yr)));
+    if (op & 0x20u) {
+      // the dual-product pass. MUL: c0 = a0 b0 + a1 (p - b1) on h = 0, c1 = a0 b1 + a1 b0 on h = 1; MULC the same with
+      // b a constant; CONJMULC (a0 - a1 i)(k0 + k1 i): c0 = a0 k0 + a1 k1, c1 = a0 k1 + a1 (p - k0)
+      const Fp2 a = ucs_load(S, ia);
+      Fp x, yr;
+      if (code == UC_MUL) {
+        x = ucs_load_c(S, ib, h);
+        yr = ucs_load_c(S, ib, h ^ 1u);
+      } else {
+        x = ucs_const2_c(ib, h);
+        yr = ucs_const2_c(ib, h ^ 1u);
+      }
+      const bool negate = (code == UC_CONJMULC) != (h == 0);
+      return ucs_dual(a.c0, x, a.c1, fp_sel(negate, ucs_neg_raw(yr), yr));
     }
-    // SQR: (a0 + a1)(a0 - a1) on h = 0, (a0 + a0) a1 on h = 1: one product each
-    const Fp x = fp_add(a.c0, fp_sel(h != 0, a.c0, a.c1));
-    const Fp y = fp_sel(h != 0, a.c1, fp_sub(a.c0, a.c1));
+    // one product per thread. SQR: (a0 + a1)(a0 - a1) on h = 0, (a0 + a0) a1 on h = 1; MULFP0 / MULFP1 / MULFPC: the
+    // thread's component of a times component 0 / 1 of b / times a constant of Fp
+    Fp x, y;
+    if (code == UC_SQR) {
+      const Fp2 a = ucs_load(S, ia);
+      x = fp_add(a.c0, fp_sel(h != 0, a.c0, a.c1));
+      y = fp_sel(h != 0, a.c1, fp_sub(a.c0, a.c1));
+    } else {
+      x = ucs_load_c(S, ia, h);
+      y = code == UC_MULFPC ? uc_constp_(ib) : ucs_load_c(S, ib, code == UC_MULFP1 ? 1u : 0u);
+    }
     return fp_mul_inl(x, y);
   }
-  const uint32_t code = op & 31u;
   if (op & 0x20u) {
     if (code == UC_MULXI) return ucs_xi_c(ucs_load_c(S, ia, h), ucs_load_c(S, ia, h ^ 1u), h);
     const Fp a = ucs_load_c(S, ia, h), b = ucs_load_c(S, ib, h);
@@ -122,9 +140,6 @@ __device__ __forceinline__ Fp ucs_phase(uint32_t S, uint32_t op, uint2 w, uint32
     return fp_add(fp_add(s, s), a);
   }
   switch (code) {
-    case UC_MULFP0:
-    case UC_MULFP1:
-      return fp_mul(ucs_load_c(S, ia, h), ucs_load_c(S, ib, code == UC_MULFP1 ? 1u : 0u));
     case UC_X4:
     case UC_X8:
     case UC_X3: {
@@ -136,17 +151,6 @@ __device__ __forceinline__ Fp ucs_phase(uint32_t S, uint32_t op, uint2 w, uint32
     }
     case UC_NEG:
       return fp_neg(ucs_load_c(S, ia, h));
-    case UC_CONJMULC:
-    case UC_MULC: {
-      // (a0 +- a1 i)(k0 + k1 i): MULC c0 = a0 k0 + a1 (p - k1), c1 = a0 k1 + a1 k0;
-      // CONJMULC c0 = a0 k0 + a1 k1, c1 = a0 k1 + a1 (p - k0)
-      const Fp2 a = ucs_load(S, ia);
-      const Fp x = ucs_const2_c(ib, h), yr = ucs_const2_c(ib, h ^ 1u);
-      const bool negate = (code == UC_MULC) == (h == 0);
-      return ucs_dual(a.c0, x, a.c1, fp_sel(negate, ucs_neg_raw(yr), yr));
-    }
-    case UC_MULFPC:
-      return fp_mul(ucs_load_c(S, ia, h), uc_constp_(ib));
     case UC_CONJ: {
       const Fp a = ucs_load_c(S, ia, h);
       return h ? fp_neg(a) : a;

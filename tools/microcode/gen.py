@@ -35,7 +35,9 @@ def uniq(*xs):
     return out
 # dispatch classes of the interpreter (three bits above the opcode in uc_ops), by how often a phase of the pairing has the
 # opcode: ADD 1,888 of 6,815, SUB2 1,159, MUL 1,131, AXI 692, SQR 419, CYCP / CYCM / SUB / MULXI 1,106 together
-OP_CLASS = {'ADD': 6, 'SUB2': 5, 'AXI': 4, 'MUL': 3, 'SQR': 2, 'CYCP': 1, 'CYCM': 1, 'SUB': 1, 'MULXI': 1}
+# (class 3: the dual-product pass, class 2: one Montgomery product per thread -- each body exists once in the kernel)
+OP_CLASS = {'ADD': 6, 'SUB2': 5, 'AXI': 4, 'MUL': 3, 'MULC': 3, 'CONJMULC': 3, 'SQR': 2, 'MULFP0': 2, 'MULFP1': 2, 'MULFPC': 2,
+            'CYCP': 1, 'CYCM': 1, 'SUB': 1, 'MULXI': 1}
 
 
 def op_byte(op):
