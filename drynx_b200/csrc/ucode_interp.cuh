@@ -2,6 +2,13 @@
 // with two threads per program lane. Included inside namespace drx by a translation unit that has defined
 // UC_PROGRAM_INC (the generated tables it runs): ucode_split.cuh for the pairing, kernels_rp_gtlanes.cu for the Fp12
 // multiplication behind fixed-base GT exponentiations.
+// The slot access and ucs_phase also compile for the host (the DRX_HOST_EMU test build runs the emitted program through
+// the very code the kernels execute, shared memory replaced by a byte array); the phase loop itself is device code.
+#if defined(__CUDACC__)
+#define UCS_FN __device__ __forceinline__
+#else
+#define UCS_FN inline
+#endif
 #include UC_PROGRAM_INC
 #ifdef UCS_PROFILE
 static __device__ unsigned long long uc_prof[64];  // [op]: cycles, [32 + op]: phases
@@ -22,13 +29,16 @@ static __device__ unsigned long long uc_prof[64];  // [op]: cycles, [32 + op]: p
 #endif
 #define UCS_ITEM_BYTES (UC_NSLOTS * 64)
 static_assert(UC_PAD_PHASES >= 1, "the interpreter reads one phase ahead");
+#if defined(__CUDACC__)
 static_assert(UC_NSLOTS <= (int)kUcMaxSlots, "slot-image area is sized for kUcMaxSlots");
+#endif
 
 // Shared-memory slot access by 32-bit shared-window address. A slot is 64 bytes = four 16-byte chunks; logical chunk c
 // lives at physical chunk c ^ UC_SWZ(slot). The program (uc_prog) carries each operand as the byte offset of its slot
 // inside the item with the swizzle already folded in (slot * 64 + UC_SWZ(slot) * 16), items are 64-byte aligned, so the
 // address of chunk c is (item + offset) ^ (c << 4): one XOR per chunk. The four program lanes of an item touch slots
 // that differ mod 4 (the generator sees to it), so their 16-byte accesses fall into different bank groups.
+#if defined(__CUDACC__)
 __device__ __forceinline__ uint4 ucs_lds(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
@@ -37,9 +47,18 @@ __device__ __forceinline__ uint4 ucs_lds(uint32_t addr) {
 __device__ __forceinline__ void ucs_sts(uint32_t addr, const uint32_t* w) {
   asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
 }
-__device__ __forceinline__ uint32_t ucs_slot_off(uint32_t slot) { return slot * 64u + UC_SWZ(slot) * 16u; }
+#else   // host emulation: `addr` is an offset into ucs_host_smem
+static thread_local unsigned char* ucs_host_smem = nullptr;
+inline uint4 ucs_lds(uint32_t addr) {
+  uint4 v;
+  memcpy(&v, ucs_host_smem + addr, 16);
+  return v;
+}
+inline void ucs_sts(uint32_t addr, const uint32_t* w) { memcpy(ucs_host_smem + addr, w, 16); }
+#endif
+UCS_FN uint32_t ucs_slot_off(uint32_t slot) { return slot * 64u + UC_SWZ(slot) * 16u; }
 // component `comp` (chunks 2 comp, 2 comp + 1) of the slot at item address S + off
-__device__ __forceinline__ Fp ucs_load_c(uint32_t S, uint32_t off, uint32_t comp) {
+UCS_FN Fp ucs_load_c(uint32_t S, uint32_t off, uint32_t comp) {
   const uint32_t a0 = (S + off) ^ (comp << 5);
   const uint4 lo = ucs_lds(a0), hi = ucs_lds(a0 ^ 16u);
   Fp r;
@@ -47,26 +66,26 @@ __device__ __forceinline__ Fp ucs_load_c(uint32_t S, uint32_t off, uint32_t comp
   r.v[4] = hi.x; r.v[5] = hi.y; r.v[6] = hi.z; r.v[7] = hi.w;
   return r;
 }
-__device__ __forceinline__ void ucs_store_c(uint32_t S, uint32_t off, uint32_t comp, const Fp& r) {
+UCS_FN void ucs_store_c(uint32_t S, uint32_t off, uint32_t comp, const Fp& r) {
   const uint32_t a0 = (S + off) ^ (comp << 5);
   ucs_sts(a0, &r.v[0]);
   ucs_sts(a0 ^ 16u, &r.v[4]);
 }
-__device__ __forceinline__ Fp2 ucs_load(uint32_t S, uint32_t off) {
+UCS_FN Fp2 ucs_load(uint32_t S, uint32_t off) {
   return Fp2{ucs_load_c(S, off, 0u), ucs_load_c(S, off, 1u)};
 }
-__device__ __forceinline__ void ucs_store(uint32_t S, uint32_t off, const Fp2& r) {
+UCS_FN void ucs_store(uint32_t S, uint32_t off, const Fp2& r) {
   ucs_store_c(S, off, 0u, r.c0);
   ucs_store_c(S, off, 1u, r.c1);
 }
-__device__ __forceinline__ Fp uc_constp_(uint32_t k) {
+UCS_FN Fp uc_constp_(uint32_t k) {
   Fp r;
 #pragma unroll
   for (int q = 0; q < 8; q++) r.v[q] = uc_constp[k][q];
   return r;
 }
 // p - b, left unreduced (p for b = 0): only ever a multiplier of mont_mul2, which accepts any 256-bit value there
-__device__ __forceinline__ Fp ucs_neg_raw(const Fp& b) {
+UCS_FN Fp ucs_neg_raw(const Fp& b) {
   Fp r;
   r.v[0] = sub_cc(ModP::mod(0), b.v[0]);
 #pragma unroll
@@ -74,19 +93,19 @@ __device__ __forceinline__ Fp ucs_neg_raw(const Fp& b) {
   r.v[7] = subc(ModP::mod(7), b.v[7]);
   return r;
 }
-__device__ __forceinline__ Fp ucs_dual(const Fp& a0, const Fp& x, const Fp& a1, const Fp& y) {
+UCS_FN Fp ucs_dual(const Fp& a0, const Fp& x, const Fp& a1, const Fp& y) {
   Fp r;
   mont_mul2<ModP>(r.v, a0.v, x.v, a1.v, y.v);
   return r;
 }
-__device__ __forceinline__ Fp ucs_const2_c(uint32_t k, uint32_t comp) {
+UCS_FN Fp ucs_const2_c(uint32_t k, uint32_t comp) {
   Fp r;
 #pragma unroll
   for (int q = 0; q < 8; q++) r.v[q] = uc_const2[k][8 * comp + q];
   return r;
 }
 // component h of xi * a = (3 a0 - a1) + (3 a1 + a0) i, from a's own component ah and the other one ao
-__device__ __forceinline__ Fp ucs_xi_c(const Fp& ah, const Fp& ao, uint32_t h) {
+UCS_FN Fp ucs_xi_c(const Fp& ah, const Fp& ao, uint32_t h) {
   const Fp t = fp_add(fp_add(ah, ah), ah);
   return h ? fp_add(t, ao) : fp_sub(t, ao);
 }
@@ -95,7 +114,7 @@ __device__ __forceinline__ Fp ucs_xi_c(const Fp& ah, const Fp& ao, uint32_t h) {
 // barrier. `op` is the uc_ops byte: the class bits are walked first (7, 6, 5 -- ADD is two tests away, SUB2 / AXI / MUL /
 // SQR three), the opcode proper only for the rest; a balanced search over all opcodes, which is what a plain switch
 // compiles to, costs five dependent compare-and-branch pairs per phase, ~175 cycles of a lone warp's ~400-cycle phase.
-__device__ __forceinline__ Fp ucs_phase(uint32_t S, uint32_t op, uint2 w, uint32_t h) {
+UCS_FN Fp ucs_phase(uint32_t S, uint32_t op, uint2 w, uint32_t h) {
   const uint32_t ia = w.x >> 16, ib = w.y & 0xffffu, ic = w.y >> 16;
   if (op & 0x80u) {
     if (op & 0x40u) return fp_add(ucs_load_c(S, ia, h), ucs_load_c(S, ib, h));                                      // ADD
@@ -170,6 +189,32 @@ __device__ __forceinline__ Fp ucs_phase(uint32_t S, uint32_t op, uint2 w, uint32
   }
 }
 
+#ifdef UC_IN_QX   // the pairing programs
+// the line functions only ever use -x_P: the P slot holds (-x_P, y_P)
+UCS_FN void ucs_put_inputs(uint32_t S, const G1Aff& P, const G2Aff& V) {
+  ucs_store(S, ucs_slot_off(UC_IN_P), Fp2{fp_neg(P.x), P.y});
+  ucs_store(S, ucs_slot_off(UC_IN_QX), V.x);
+  ucs_store(S, ucs_slot_off(UC_IN_QY), V.y);
+}
+// e(P, V), or the all-zero element (no member of GT, so the comparison that follows fails) when V is outside G2
+UCS_FN Fp12 ucs_get_output(uint32_t S) {
+  Fp12 e;
+  e.c0.c0 = ucs_load(S, ucs_slot_off(UC_OUT_E00));
+  e.c0.c1 = ucs_load(S, ucs_slot_off(UC_OUT_E01));
+  e.c0.c2 = ucs_load(S, ucs_slot_off(UC_OUT_E02));
+  e.c1.c0 = ucs_load(S, ucs_slot_off(UC_OUT_E10));
+  e.c1.c1 = ucs_load(S, ucs_slot_off(UC_OUT_E11));
+  e.c1.c2 = ucs_load(S, ucs_slot_off(UC_OUT_E12));
+  if (!fp2_is_zero(ucs_load(S, ucs_slot_off(UC_OUT_SG)))) {
+    const Fp6 z = fp6_zero();
+    e.c0 = z;
+    e.c1 = z;
+  }
+  return e;
+}
+#endif
+
+#if defined(__CUDACC__)
 // Phases [ph0, ph1) of the program on the item at shared address S; all lanes of the warp call it together. Slots are
 // reused in place (a phase may overwrite one of its own operands), and the two threads of a pair read each other's
 // components, so every load of a phase is separated from every store by a warp barrier. Lanes a phase leaves idle and
@@ -210,3 +255,4 @@ __device__ __forceinline__ void ucs_run(uint32_t S, int lane, uint32_t h, bool a
     w = w_n;
   }
 }
+#endif  // __CUDACC__

@@ -18,29 +18,6 @@ namespace drx {
 
 #include "ucode_interp.cuh"
 
-// the line functions only ever use -x_P: the P slot holds (-x_P, y_P)
-__device__ __forceinline__ void ucs_put_inputs(uint32_t S, const UcPrep& in) {
-  ucs_store(S, ucs_slot_off(UC_IN_P), Fp2{fp_neg(in.P.x), in.P.y});
-  ucs_store(S, ucs_slot_off(UC_IN_QX), in.V.x);
-  ucs_store(S, ucs_slot_off(UC_IN_QY), in.V.y);
-}
-// e(P, V), or the all-zero element (no member of GT, so the comparison that follows fails) when V is outside G2
-__device__ __forceinline__ Fp12 ucs_get_output(uint32_t S) {
-  Fp12 e;
-  e.c0.c0 = ucs_load(S, ucs_slot_off(UC_OUT_E00));
-  e.c0.c1 = ucs_load(S, ucs_slot_off(UC_OUT_E01));
-  e.c0.c2 = ucs_load(S, ucs_slot_off(UC_OUT_E02));
-  e.c1.c0 = ucs_load(S, ucs_slot_off(UC_OUT_E10));
-  e.c1.c1 = ucs_load(S, ucs_slot_off(UC_OUT_E11));
-  e.c1.c2 = ucs_load(S, ucs_slot_off(UC_OUT_E12));
-  if (!fp2_is_zero(ucs_load(S, ucs_slot_off(UC_OUT_SG)))) {
-    const Fp6 z = fp6_zero();
-    e.c0 = z;
-    e.c1 = z;
-  }
-  return e;
-}
-
 __global__ void __launch_bounds__(UCS_BLOCK, UCS_MIN_BLOCKS)
 UCS_KERNEL(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ scratch) {
   extern __shared__ __align__(128) unsigned char uc_smem[];
@@ -51,7 +28,7 @@ UCS_KERNEL(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ s
   const size_t t = (size_t)blockIdx.x * UCS_ITEMS_PER_BLOCK + grp;
   const bool alive = seated && t < items && prep[t].state == 0;
   const uint32_t S = (uint32_t)__cvta_generic_to_shared(uc_smem) + grp * UCS_ITEM_BYTES;
-  if (alive && sub == 0) ucs_put_inputs(S, prep[t]);
+  if (alive && sub == 0) ucs_put_inputs(S, prep[t].P, prep[t].V);
   __syncwarp();
   ucs_run(S, sub >> 1, (uint32_t)(sub & 1), alive, 0, UC_NPHASES);
   if (seated && t < items && sub == 0) scratch[t].a = alive ? ucs_get_output(S) : fp12_one();
@@ -83,7 +60,7 @@ UCS_KERNEL_DYN(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict
     const size_t t = (size_t)g * UCS_WARP_ITEMS + (seated ? in_warp : 0);
     const bool alive = seated && t < items && prep[t].state == 0;
     if (seg == 0) {
-      if (alive && sub == 0) ucs_put_inputs(S, prep[t]);
+      if (alive && sub == 0) ucs_put_inputs(S, prep[t].P, prep[t].V);
     } else {
       unsigned int polls = 0;
       if (wl == 0) {

@@ -7,6 +7,18 @@
 #include "wire.cuh"
 #include "ed25519.cuh"
 #include <cstring>
+// The lane-group pairing program (csrc/pairing_ucode_g4.inc) through the interpreter's own slot access and phase body
+// (csrc/ucode_interp.cuh); the tables' CUDA storage qualifiers mean nothing to g++.
+struct uint2 { uint32_t x, y; };
+struct uint4 { uint32_t x, y, z, w; };
+#define __device__
+#define __constant__
+#define UC_PROGRAM_INC "pairing_ucode_g4.inc"
+namespace drx {
+#include "ucode_interp.cuh"
+}
+#undef __device__
+#undef __constant__
 using namespace drx;
 
 static void load_words(uint32_t* w, const uint8_t* b, int nbytes) { memcpy(w, b, nbytes); }
@@ -164,6 +176,34 @@ int emu_g2_membership(const uint8_t* g1, const uint8_t* g2) {
   if (!g1_from_wire(p, aw) || !g2_from_wire(q, bw)) return -1;
   Fp12 f;
   return (g2_in_subgroup(q) ? 1 : 0) | (miller_loop(f, p, q) ? 2 : 0);
+}
+
+// The emitted micro-program executed the way a warp does it: per phase every thread (program lane x component) of the
+// item computes its result from the slots, then all of them store. Returns 0 / 1 = the G2 verdict slot is zero / not.
+int emu_ucode_pair(const uint8_t* g1, const uint8_t* g2, uint8_t* gt384) {
+  uint32_t aw[16], bw[32], ow[96];
+  load_words(aw, g1, 64); load_words(bw, g2, 128);
+  G1Aff p; G2Aff q;
+  if (!g1_from_wire(p, aw) || !g2_from_wire(q, bw)) return -1;
+  static thread_local unsigned char smem[UC_NSLOTS * 64];
+  memset(smem, 0xA5, sizeof(smem));
+  ucs_host_smem = smem;
+  ucs_put_inputs(0, p, q);
+  for (int ph = 0; ph < UC_NPHASES; ph++) {
+    Fp r[UC_G][2];
+    bool act[UC_G];
+    for (int lane = 0; lane < UC_G; lane++) {
+      const uint2 w = uc_prog[ph * UC_G + lane];
+      act[lane] = w.x != 0xffffffffu;
+      for (uint32_t h = 0; h < 2 && act[lane]; h++) r[lane][h] = ucs_phase(0, uc_ops[ph], w, h);
+    }
+    for (int lane = 0; lane < UC_G; lane++)
+      for (uint32_t h = 0; h < 2 && act[lane]; h++) ucs_store_c(0, uc_prog[ph * UC_G + lane].x & 0xffffu, h, r[lane][h]);
+  }
+  const bool in_g2 = fp2_is_zero(ucs_load(0, ucs_slot_off(UC_OUT_SG)));
+  const Fp12 e = ucs_get_output(0);
+  gt_to_wire(ow, e); memcpy(gt384, ow, 384);
+  return in_g2 ? 0 : 1;
 }
 
 // checks internal identities that have no wire-level witness: cyclotomic squaring == generic squaring on a

@@ -132,3 +132,22 @@ def test_g2_membership_verdicts(emu, rng):
     for Q in (T, R.g2_mul_raw(R.n, T), R.g2_mul_raw(R.n * R.TWIST_COFACTOR // 13, T), R.g2_mul_raw(13, T)):
         assert Q is not None and R.g2_on_curve(Q) and not R.g2_in_subgroup(Q)
         assert emu.emu_g2_membership(P, R.g2_to_bytes(Q)) == 0
+
+
+def test_interpreter_runs_the_emitted_pairing_program(emu, oracle, rng):
+    """csrc/pairing_ucode_g4.inc executed on the CPU by the interpreter's own slot access and phase body
+    (csrc/ucode_interp.cuh ucs_phase: class-bit dispatch, two threads per program lane, dual-product passes): the
+    result is the oracle's pairing, byte for byte, and the verdict slot is zero exactly for points of G2 (for the
+    others the output is the all-zero element, which no comparison with a GT value can pass)."""
+    g1, g2 = oracle.generators()
+    for _ in range(2):
+        P = oracle.g1_mul(rng.scalar().to_bytes(32, 'big'), g1)
+        Q = oracle.g2_mul(rng.scalar().to_bytes(32, 'big'), g2)
+        out = ctypes.create_string_buffer(384)
+        assert emu.emu_ucode_pair(P, Q, out) == 0
+        assert out.raw == oracle.pair(P, Q)
+    T = R.g2_twist_point(11)
+    for Qo in (T, R.g2_mul_raw(R.n * R.TWIST_COFACTOR // 13, T)):
+        assert R.g2_on_curve(Qo) and not R.g2_in_subgroup(Qo)
+        assert emu.emu_ucode_pair(P, R.g2_to_bytes(Qo), out) == 1
+        assert out.raw == bytes(384)
