@@ -449,17 +449,26 @@ def run_gpu(args):
     side_thread = threading.Thread(target=side_worker, daemon=True)
     side_thread.start()
 
+    breakdown = {} if os.environ.get('DRX_E2E_BREAKDOWN') else None   # per-call wall time of the e2e leg, to stderr
+
+    def call(name, fn):
+        if breakdown is None:
+            return fn()
+        t = time.perf_counter()
+        fn()
+        breakdown[name] = breakdown.get(name, 0.0) + time.perf_counter() - t
+
     def step_e2e():
         # what a Go data provider / root / verifying node would do with two goroutines and one context each:
         # aggregation + decryption only need the ciphertexts and run next to proof creation + verification
         h = cur['h']
-        ck(lib.drx_reduce_rows(be.h, ndp, rows, np_p(h['rows']), 3, np_p(h['m'])))
-        ck(lib.drx_encrypt(be.h, n, np_p(h['m']), np_p(h['r']), np_p(h['ct'])))
+        call('reduce_rows', lambda: ck(lib.drx_reduce_rows(be.h, ndp, rows, np_p(h['rows']), 3, np_p(h['m']))))
+        call('encrypt', lambda: ck(lib.drx_encrypt(be.h, n, np_p(h['m']), np_p(h['r']), np_p(h['ct']))))
         go.set()
-        ck(lib.drx_rp_create(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h['m']), np_p(h['r']), np_p(h['ct']), np_p(h['rnd']), np_p(roff),
-                             np_p(h['pr']), np_p(poff)))
-        ck(lib.drx_rp_verify(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h['pr']), np_p(poff), np_p(h['ok'])))
-        done_ev.wait()
+        call('rp_create', lambda: ck(lib.drx_rp_create(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h['m']), np_p(h['r']), np_p(h['ct']),
+                                                       np_p(h['rnd']), np_p(roff), np_p(h['pr']), np_p(poff))))
+        call('rp_verify', lambda: ck(lib.drx_rp_verify(be.h, n, np_p(h['set_id']), np_p(h_l), np_p(h['pr']), np_p(poff), np_p(h['ok']))))
+        call('join', done_ev.wait)
         done_ev.clear()
         if side_err:
             raise side_err[0]
@@ -484,6 +493,9 @@ def run_gpu(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
         e2e_s[kind] = dt
+        if breakdown is not None and rank == 0:
+            sys.stderr.write('e2e %s, ms per step: %s\n' % (kind, ', '.join('%s %.3f' % (k, v / (args.steps + 3) * 1e3) for k, v in breakdown.items())))
+            breakdown.clear()
     e2e_val = world * n * args.steps / e2e_s['pinned']
     quit_flag[0] = True
     go.set()
