@@ -1,6 +1,6 @@
-// Shared between the lane-group pairing kernels (ucode_body.cuh: one thread per program lane; ucode_split.cuh: two
-// threads per program lane): the prepared-argument record, per-device launch state, and the layout of the dynamic
-// kernels' control words.
+// Shared between the lane-group pairing kernels (ucode_split.cuh, instantiated for four and for eight program lanes)
+// and the kernel that prepares their arguments: the prepared-argument record, per-device launch state, and the layout
+// of the dynamic kernels' control words.
 #pragma once
 #include <mutex>
 

@@ -1,12 +1,13 @@
-// Lane-group pairing, two threads per program lane. The micro-program (pairing_ucode_g*.inc) and the slot image in
-// shared memory are those of ucode_body.cuh; here each Fp2 operation of a program lane is carried out by a PAIR of
-// threads, thread h of the pair producing component h of the result: an Fp2 product is one dual-product Montgomery
-// pass per thread (c0 = a0 b0 + a1 (p - b1) on h = 0, c1 = a0 b1 + a1 b0 on h = 1), a squaring one product per thread,
-// a sum one Fp addition per thread. Both threads read whatever operand components they need straight from the item's
-// slots, so there are no shuffles and no cross-thread carries. Compared with one thread per lane this halves the
-// dependent instruction chain of every phase (the lane-group kernels are latency-bound: a lone warp issues one
-// instruction per ~4.5 cycles) and doubles the resident warps per item for the same shared-memory footprint.
-// Replaces kyber pairing/bn256 optate.go for lib/range/range_proof.go:540-544, like ucode_body.cuh.
+// Lane-group pairing, two threads per program lane. One copy of a pairing check's state lives in shared memory as
+// UC_NSLOTS Fp2 slots, and a generated micro-program (pairing_ucode_g*.inc, tools/microcode/gen.py) runs over it: every
+// phase the program lanes execute one Fp2 operation each on their own slots. Each operation of a program lane is carried
+// out by a PAIR of threads, thread h of the pair producing component h of the result: an Fp2 product is one
+// dual-product Montgomery pass per thread (c0 = a0 b0 + a1 (p - b1) on h = 0, c1 = a0 b1 + a1 b0 on h = 1), a squaring
+// one product per thread, a sum one Fp addition per thread. Both threads read whatever operand components they need
+// straight from the item's slots, so there are no shuffles and no cross-thread carries. (Round 1 gave a program lane
+// one thread; two halve the dependent instruction chain of every phase and double the resident warps per item for the
+// same shared-memory footprint.) The interpreter itself is ucode_interp.cuh; this file holds the two kernels and their
+// launcher. Replaces kyber pairing/bn256 optate.go for lib/range/range_proof.go:540-544.
 #pragma once
 #include <cstdio>
 #include <cstdlib>
@@ -34,7 +35,7 @@ UCS_KERNEL(size_t items, const UcPrep* __restrict__ prep, GtPair* __restrict__ s
   if (seated && t < items && sub == 0) scratch[t].a = alive ? ucs_get_output(S) : fp12_one();
 }
 
-// Dynamic variant (same scheme as UC_KERNEL_DYN in ucode_body.cuh): the program is cut into nseg segments, a task is
+// Dynamic variant: the program is cut into nseg segments, a task is
 // (warp-sized group of items, segment), persistent warps take tasks from an atomic counter segment-major, and a
 // group's slot image travels through global memory between segments.
 #define UCS_GROUP_U4 (UCS_WARP_ITEMS * UC_NSLOTS * 4)  // uint4 words of one group's slots
@@ -102,7 +103,7 @@ int UCS_LAUNCH(cudaStream_t st, size_t items, const void* d_prep, void* d_scratc
   const int natural = UCS_ITEMS_PER_BLOCK * UC_NSLOTS * (int)sizeof(Fp2);
   const int nblocks = uc_grid_for(items, UCS_ITEMS_PER_BLOCK);
   const int max_resident = di.smem_sm / (natural + 1024);
-  // placement by shared-memory request, as in ucode_body.cuh: c = ceil(blocks / usable SMs) blocks per SM at most
+  // placement by shared-memory request: c = ceil(blocks / usable SMs) blocks per SM at most
   const int usable = di.nsm - (di.nsm + 9) / 10;
   const int cap = (nblocks + usable - 1) / usable;
   // Static launch while everything is resident with room to spare, and again for very large batches (thousands of
