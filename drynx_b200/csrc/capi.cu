@@ -138,7 +138,7 @@ struct RpSetHost {
 struct drx_ctx {
   int device = 0;
   cudaStream_t own_stream = nullptr, stream = nullptr, side_stream = nullptr, side_stream2 = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr;  // fork/join of the side streams (independent small kernels)
+  cudaEvent_t ev_fork = nullptr, ev_fork0 = nullptr, ev_join = nullptr, ev_join2 = nullptr;  // fork/join of the side streams (independent small kernels)
   std::mutex mu;
   uint64_t launches = 0;
   bool have_pub = false, have_dlog = false, have_target = false;
@@ -146,10 +146,12 @@ struct drx_ctx {
   int opt_create_path = 0;  // drx_set_option "rp_create_path": 0 = by batch size, 1 / 2 / 3 force one of the small-batch kernels
   int opt_ucode_lanes = 0;  // drx_set_option "rp_ucode_lanes": 0 = by batch size, 4 or 8
   int opt_verify_gt = 0;    // drx_set_option "rp_verify_gt": 0 = by batch size, 2 = always the lane-group GT kernel (tests)
+  int opt_hdr_early = 0;    // drx_set_option "rp_verify_hdr_early" (experiments): 1 = the header check starts beside the preparation, 0 = with the pairing kernel
   int opt_agg_slices = 0;   // drx_set_option "agg_slices": 0 = sized from the SM count, else forced (experiments)
   UcTune uc_tune;           // drx_set_option "rp_ucode_mode" / "rp_ucode_resident" / "rp_ucode_nseg"
   DevBuf baseB_aff, baseB_wire, g2_aff, g2_wire, gtB, tabB, tabP, pub_aff, tabGtB, tabG2, dlog_keys, dlog_vals, bad,
       sets_dev, sink, tabQ, target_aff;  // tabQ: comb table of the key-switching target key
+  DevBuf tabGtB16;  // 16-bit windows of e(B, g2) for the lane-group GT kernels, built at their first use (403 MB)
   Arena arena;
   Profiler prof;
   DlogModel dlog;
@@ -291,6 +293,7 @@ int drx_init(drx_ctx** out, int device, const uint8_t* g1_base, const uint8_t* g
       cudaStreamCreateWithFlags(&c->side_stream2, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_join2, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_fork0, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
     drx_free(c);
     return fail(-3, "drx_init: cannot create side stream");
@@ -325,7 +328,7 @@ void drx_free(drx_ctx* c) {
   cudaDeviceSynchronize();
   for (DevBuf* b : {&c->baseB_aff, &c->baseB_wire, &c->g2_aff, &c->g2_wire, &c->gtB, &c->tabB, &c->tabP, &c->pub_aff,
                     &c->tabGtB, &c->tabG2, &c->dlog_keys, &c->dlog_vals, &c->bad, &c->sets_dev, &c->sink, &c->tabQ,
-                    &c->target_aff, &c->ed_pt,
+                    &c->target_aff, &c->tabGtB16, &c->ed_pt,
                     &c->ed_tabB, &c->ed_tabP, &c->ed_dlog_keys, &c->ed_dlog_vals})
     b->release();
   c->arena.buf.release();
@@ -340,6 +343,7 @@ void drx_free(drx_ctx* c) {
   if (c->side_stream2) cudaStreamDestroy(c->side_stream2);
   if (c->ev_join2) cudaEventDestroy(c->ev_join2);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_fork0) cudaEventDestroy(c->ev_fork0);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
   delete c;
 }
@@ -414,6 +418,11 @@ int drx_set_option(drx_ctx* c, const char* name, int value) {
   if (!strcmp(name, "rp_ucode_resident")) {
     if (value < 0 || value > 32) return fail(-1, "rp_ucode_resident must be 0 (auto) .. 32 blocks per SM");
     c->uc_tune.resident = value;
+    return 0;
+  }
+  if (!strcmp(name, "rp_verify_hdr_early")) {
+    if (value != 0 && value != 1) return fail(-1, "rp_verify_hdr_early must be 0 or 1");
+    c->opt_hdr_early = value;
     return 0;
   }
   if (!strcmp(name, "rp_ucode_nseg")) {

@@ -103,6 +103,30 @@ int launch_comb_table_gt(cudaStream_t st, int nbases, const void* d_bases_gt, vo
   return 1;
 }
 
+// 16-bit windows for the one base every proof shares, e(B, g2): table16[w][d-1] = base ^ (d * 2^(16w)), w < 16,
+// d = 1 .. 65535 (403 MB), each entry the product of the two 8-bit entries it consists of. Halves the Fp12 products of
+// the fixed-base exponentiations e(B, g2)^t (creation) and e(B, g2)^(-Zv) (verification) in the lane-group GT kernels.
+__global__ void __launch_bounds__(64)
+k_comb_table_gt16(const Fp12* __restrict__ tab8, Fp12* __restrict__ tab16) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= kGt16Entries) return;
+  const int w = (int)(idx / kGt16PerWindow);
+  const uint32_t d = (uint32_t)(idx - (size_t)w * kGt16PerWindow) + 1u, lo = d & 0xffu, hi = d >> 8;
+  const Fp12* elo = tab8 + (size_t)(2 * w) * DRX_COMB_ENTRIES + lo - 1;
+  const Fp12* ehi = tab8 + (size_t)(2 * w + 1) * DRX_COMB_ENTRIES + hi - 1;
+  Fp12 r;
+  if (lo && hi) {
+    fp12_mul(r, *elo, *ehi);
+  } else {
+    r = lo ? *elo : *ehi;
+  }
+  tab16[idx] = r;
+}
+int launch_comb_table_gt16(cudaStream_t st, const void* d_tab8, void* d_tab16) {
+  k_comb_table_gt16<<<grid_for(kGt16Entries, 64), 64, 0, st>>>((const Fp12*)d_tab8, (Fp12*)d_tab16);
+  return 1;
+}
+
 // ------------------------------------------------------------------ diagnostics on wire bytes
 __global__ void __launch_bounds__(64)
 k_pair_wire(size_t n, const uint32_t* __restrict__ g1, const uint32_t* __restrict__ g2, uint32_t* __restrict__ gt,

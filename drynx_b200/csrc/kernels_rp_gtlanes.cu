@@ -59,56 +59,67 @@ __device__ __forceinline__ void gtl_store_acc(uint32_t S, int sub, Fp12* __restr
 __device__ __forceinline__ void gtl_set_one(uint32_t S, int sub) {
   if (sub < 6) ucs_store(S, ucs_slot_off(gtl_slot_a(sub)), sub == 0 ? fp2_one() : fp2_zero());
 }
-// acc (the group's A slots) <- acc * table[w][digit_w(k)] over all 32 windows; `have` says whether acc already holds a
-// value (otherwise the first non-zero window loads it). The whole warp calls this together; groups that are not
-// `live` only keep the others company at the barriers. Returns `have`.
-__device__ __forceinline__ bool gtl_comb(uint32_t S, int sub, bool live, const Fp12* __restrict__ table, const Scalar& k,
-                                         bool have) {
-  for (int w = 0; w < DRX_COMB_WINDOWS; w++) {
-    const uint32_t d = live ? (k.v[w >> 2] >> ((w & 3) * 8)) & 0xffu : 0u;
-    const bool mul = d != 0 && have;
-    if (d) {
-      gtl_load_entry(S, sub, table + (size_t)w * DRX_COMB_ENTRIES + d - 1, have);
-      have = true;
-    }
-    __syncwarp();
-    if (__any_sync(0xffffffffu, mul)) ucs_run(S, sub >> 1, (uint32_t)(sub & 1), mul, 0, UC_NPHASES);
+// One comb step of a group: acc (the group's A slots) <- acc * *entry, or acc <- *entry while the group holds no value
+// yet (`have` false); a null entry (zero digit, or a group that is not live) skips the step. The whole warp calls this
+// together: groups without work keep the others company at the barriers. Returns the new `have`.
+__device__ __forceinline__ bool gtl_step(uint32_t S, int sub, const Fp12* __restrict__ entry, bool have) {
+  const bool mul = entry != nullptr && have;
+  if (entry) {
+    gtl_load_entry(S, sub, entry, have);
+    have = true;
   }
+  __syncwarp();
+  if (__any_sync(0xffffffffu, mul)) ucs_run(S, sub >> 1, (uint32_t)(sub & 1), mul, 0, UC_NPHASES);
   return have;
+}
+// entry of an 8-bit-window table (32 windows x 255 entries) / of the 16-bit-window table of e(B, g2) (16 x 65,535) for
+// window w of scalar k; null for a zero digit
+__device__ __forceinline__ const Fp12* gtl_entry8(const Fp12* __restrict__ table, const Scalar& k, int w) {
+  const uint32_t d = (k.v[w >> 2] >> ((w & 3) * 8)) & 0xffu;
+  return d ? table + (size_t)w * DRX_COMB_ENTRIES + d - 1 : nullptr;
+}
+__device__ __forceinline__ const Fp12* gtl_entry16(const Fp12* __restrict__ table16, const Scalar& k, int w) {
+  const uint32_t d = (k.v[w >> 1] >> ((w & 1) * 16)) & 0xffffu;
+  return d ? table16 + (size_t)w * kGt16PerWindow + d - 1 : nullptr;
 }
 
 // ------------------------------------------------------------------ creation: a_ij, sixteen threads per item
+// Two groups of eight threads share the 32 + 16 products of an item evenly: the even group walks windows 0..23 of
+// e(B, A_{i,phi})^(-s v) (8-bit windows, per-set table), the odd group the 16 windows of e(B, g2)^t (16-bit windows) and
+// then windows 24..31 of the first factor; one more product joins the halves.
 __global__ void __launch_bounds__(GTL_BLOCK, 8)
 k_rp_create_gt_lanes(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t* __restrict__ secret,
-                     const uint32_t* __restrict__ rnd, const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB,
+                     const uint32_t* __restrict__ rnd, const size_t* __restrict__ rnd_off, const Fp12* __restrict__ tabGtB16,
                      uint32_t* __restrict__ proofs) {
   extern __shared__ __align__(128) unsigned char uc_smem[];
   const int wl = threadIdx.x & 31, warp = threadIdx.x >> 5, grp = wl >> 3, sub = wl & 7;
   const uint32_t S = (uint32_t)__cvta_generic_to_shared(uc_smem) + (warp * kGtGroupsPerWarp + grp) * UCS_ITEM_BYTES;
-  // groups 0, 1 of a warp serve one item, groups 2, 3 the next: even group = first factor, odd group = second
+  // groups 0, 1 of a warp serve one item, groups 2, 3 the next
   const size_t t = ((size_t)blockIdx.x * (GTL_BLOCK / 32) + warp) * 2 + (grp >> 1);
+  const bool even = (grp & 1) == 0;
   size_t p = 0, off = 0;
   int i = 0, j = 0, ns = 0, nd = 0;
   const bool live = t < b.items && locate_item(b, sets, t, p, i, j, ns, nd, off);
-  Scalar k = sc_zero();
-  const Fp12* table = tabGtB;
+  Scalar ka = sc_zero(), kt = sc_zero();
+  const Fp12* tableA = nullptr;
   if (live) {
     const RpSetDev set = sets[b.d_set_id[p]];
     const uint32_t* rp = rnd + (b.d_proof_off ? rnd_off[p] / 4 : p * (size_t)nd * (3 + ns) * 8);
     const uint32_t* row = rp + (size_t)j * (3 + ns) * 8;
-    if ((grp & 1) == 0) {
-      const uint32_t phi = rp_digit(secret[p], set.u, j);
-      table = (const Fp12*)set.tabGtA + ((size_t)i * set.u + phi) * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES);
-      k = sc_neg(sc_mul(sc_from_wire(row), sc_from_wire(row + 8 * (3 + i))));  // -s_j v_ij
-    } else {
-      k = sc_from_wire(row + 8);                                              // t_j
-    }
+    const uint32_t phi = rp_digit(secret[p], set.u, j);
+    tableA = (const Fp12*)set.tabGtA + ((size_t)i * set.u + phi) * (DRX_COMB_WINDOWS * DRX_COMB_ENTRIES);
+    ka = sc_neg(sc_mul(sc_from_wire(row), sc_from_wire(row + 8 * (3 + i))));  // -s_j v_ij
+    kt = sc_from_wire(row + 8);                                              // t_j
   }
-  bool have = gtl_comb(S, sub, live, table, k, false);
+  bool have = false;
+  for (int s = 0; s < 24; s++) {
+    const Fp12* e = nullptr;
+    if (live) e = even ? gtl_entry8(tableA, ka, s) : s < 16 ? gtl_entry16(tabGtB16, kt, s) : gtl_entry8(tableA, ka, s + 8);
+    have = gtl_step(S, sub, e, have);
+  }
   if (live && !have) gtl_set_one(S, sub);  // exponent 0
   __syncwarp();
-  // a_ij = first factor * second factor: the even group takes the odd group's value as its B operand
-  const bool even = (grp & 1) == 0;
+  // a_ij = the even group's partial product * the odd group's: the even group takes the odd group's value as its B operand
   if (live && even) gtl_copy_a_to_b(S, S + UCS_ITEM_BYTES, sub);
   __syncwarp();
   ucs_run(S, sub >> 1, (uint32_t)(sub & 1), live && even, 0, UC_NPHASES);
@@ -128,7 +139,7 @@ k_rp_create_gt_lanes(RpBatch b, const RpSetDev* __restrict__ sets, const int64_t
 
 // ------------------------------------------------------------------ verification: T_ij, eight threads per item
 __global__ void __launch_bounds__(GTL_BLOCK, 8)
-k_rp_verify_gt_lanes(RpBatch b, const RpSetDev* __restrict__ sets, const Fp12* __restrict__ tabGtB,
+k_rp_verify_gt_lanes(RpBatch b, const RpSetDev* __restrict__ sets, const Fp12* __restrict__ tabGtB16,
                      const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags, GtPair* __restrict__ scratch) {
   extern __shared__ __align__(128) unsigned char uc_smem[];
   const int wl = threadIdx.x & 31, warp = threadIdx.x >> 5, grp = wl >> 3, sub = wl & 7;
@@ -158,7 +169,7 @@ k_rp_verify_gt_lanes(RpBatch b, const RpSetDev* __restrict__ sets, const Fp12* _
     live = false;
   }
   __syncwarp();
-  gtl_comb(S, sub, live, tabGtB, k, true);
+  for (int w = 0; w < 16; w++) gtl_step(S, sub, live ? gtl_entry16(tabGtB16, k, w) : nullptr, true);  // A_ij * e(B, g2)^(-Zv)
   __syncwarp();
   if (present) {
     if (live) {
@@ -181,22 +192,22 @@ static bool gtl_configure(bool (&done)[kUcMaxDevices], const void* kernel, int s
 constexpr int kGtlSmem = GTL_GROUPS_PER_BLOCK * UC_NSLOTS * 64;
 
 int launch_rp_create_gt_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                              const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB, uint8_t* d_proofs) {
+                              const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB16, uint8_t* d_proofs) {
   if (!b.items) return 0;
   static bool done[kUcMaxDevices] = {false};
   if (!gtl_configure(done, (const void*)k_rp_create_gt_lanes, kGtlSmem)) return 0;
   const size_t items_per_block = (GTL_BLOCK / 32) * 2;
   k_rp_create_gt_lanes<<<uc_grid_for(b.items, (int)items_per_block), GTL_BLOCK, kGtlSmem, st>>>(
-      b, d_sets, d_secret, (const uint32_t*)d_rnd, d_rnd_off, (const Fp12*)d_tabGtB, (uint32_t*)d_proofs);
+      b, d_sets, d_secret, (const uint32_t*)d_rnd, d_rnd_off, (const Fp12*)d_tabGtB16, (uint32_t*)d_proofs);
   return 1;
 }
-int launch_rp_verify_gt_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabGtB,
+int launch_rp_verify_gt_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabGtB16,
                               const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch) {
   if (!b.items) return 0;
   static bool done[kUcMaxDevices] = {false};
   if (!gtl_configure(done, (const void*)k_rp_verify_gt_lanes, kGtlSmem)) return 0;
   k_rp_verify_gt_lanes<<<uc_grid_for(b.items, GTL_GROUPS_PER_BLOCK), GTL_BLOCK, kGtlSmem, st>>>(
-      b, d_sets, (const Fp12*)d_tabGtB, (const uint32_t*)d_proofs, d_flags, (GtPair*)d_scratch);
+      b, d_sets, (const Fp12*)d_tabGtB16, (const uint32_t*)d_proofs, d_flags, (GtPair*)d_scratch);
   return 1;
 }
 

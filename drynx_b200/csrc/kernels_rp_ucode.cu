@@ -82,6 +82,22 @@ size_t rp_ucode_prep_bytes(size_t items) {
 int launch_rp_verify_prep(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
                           const uint8_t* d_proofs, uint32_t* d_flags, void* d_prep) {
   if (!b.items) return 0;
+  // The header check may still be running on some SMs when the pairing kernel arrives; an SM keeps the L1 / shared split
+  // of the first block that reached it while it was empty, so this kernel too asks for the shared-heavy split (it uses no
+  // shared memory itself). Per device, once; a hint, errors ignored.
+  {
+    static bool done[kUcMaxDevices] = {false};
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < kUcMaxDevices) {
+      std::lock_guard<std::mutex> lk(uc_dev_mutex());
+      if (!done[dev]) {
+        if (cudaFuncSetAttribute(k_rp_verify_prep, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                 (int)cudaSharedmemCarveoutMaxShared) != cudaSuccess)
+          cudaGetLastError();
+        done[dev] = true;
+      }
+    }
+  }
   k_rp_verify_prep<<<grid_for(b.items * 4, 64), 64, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const uint32_t*)d_proofs,
                                                         d_flags, (UcPrep*)d_prep);
   return 1;

@@ -78,6 +78,8 @@ int launch_comb_table_g2(cudaStream_t st, int nbases, const void* d_bases_aff, v
 int launch_pair_aff(cudaStream_t st, size_t n, const void* d_g1_aff, size_t g1_stride_items, const void* d_g2_aff,
                     void* d_gt);  // g1_stride_items = 0 broadcasts one G1 point
 int launch_comb_table_gt(cudaStream_t st, int nbases, const void* d_bases_gt, void* d_tables);
+constexpr size_t kGt16PerWindow = 65535, kGt16Entries = 16 * kGt16PerWindow;  // 16-bit windows of e(B, g2): 403 MB of Fp12
+int launch_comb_table_gt16(cudaStream_t st, const void* d_tab8, void* d_tab16);
 int launch_pair_wire(cudaStream_t st, size_t n, const uint8_t* d_g1, const uint8_t* d_g2, uint8_t* d_gt, int* d_bad);
 int launch_g2_mul(cudaStream_t st, size_t n, const uint8_t* d_k, const uint8_t* d_pt, uint8_t* d_out, int* d_bad);
 int launch_make_sigs(cudaStream_t st, int ns, int64_t u, const uint8_t* d_x, const void* d_tabB, const void* d_tabG2,
@@ -125,8 +127,8 @@ int launch_rp_create_fine(cudaStream_t st, const RpBatch& b, const RpSetDev* d_s
                           bool g2_only = false);
 // fixed-base GT exponentiations on lane groups (kernels_rp_gtlanes.cu): a_ij of creation, T_ij of verification
 int launch_rp_create_gt_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
-                              const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB, uint8_t* d_proofs);
-int launch_rp_verify_gt_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabGtB,
+                              const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB16, uint8_t* d_proofs);
+int launch_rp_verify_gt_lanes(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabGtB16,
                               const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
 int launch_rp_create_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const int64_t* d_secret,
                            const uint8_t* d_rnd, const size_t* d_rnd_off, const void* d_tabGtB,
