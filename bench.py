@@ -75,8 +75,8 @@ def ncu_traffic(rel):
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=5)
-    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='gpu', choices=['gpu', 'reference'])
     ap.add_argument('--ndp', type=int, default=100)
     ap.add_argument('--rows', type=int, default=10000)

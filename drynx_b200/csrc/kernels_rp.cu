@@ -384,21 +384,29 @@ int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_se
 }
 
 // ------------------------------------------------------------------ verification (a-8)
-// Header thread per proof: parse, D check (lib/range/range_proof.go:520-529, :561). flags[p] starts at the
-// host's size-check verdict and is cleared on any failure.
+// Header check per proof: parse, D check (lib/range/range_proof.go:520-529, :561). flags[p] starts at the host's
+// size-check verdict and is cleared on any failure. Two threads per proof: the even one computes c*C (a variable-base
+// product, 2,816 M), the odd one the two comb walks Zr*P + (sum_j Zphi_j u^j)*B (704 M); a shuffle brings the halves
+// together. The kernel runs beside the pairing kernel and, as one thread per proof (3,550 M in a row), outlasted it at
+// the headline size once that kernel got below 4 ms.
 __global__ void __launch_bounds__(128)
 k_rp_verify_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __restrict__ tabB,
                 const G1Aff* __restrict__ tabP, const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags) {
-  const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= b.n) return;
+  const size_t p = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 1;
+  const int half = threadIdx.x & 1;
+  const uint32_t pair_mask = 3u << (threadIdx.x & 30u);
+  if (p >= b.n) return;                                // both threads of a pair leave together, here and below
   int ns, nd;
   size_t off;
   if (!proof_set_valid(b, sets, p)) {                  // unknown signature set (device-buffer calls only): rejected
-    flags[p] = 0;
+    if (half == 0) flags[p] = 0;
     return;
   }
   if (!locate_proof(b, sets, p, ns, nd, off)) return;  // u = l = 0: accepted
-  if (!flags[p]) return;                               // size check failed on the host
+  // size check failed on the host? One thread reads the flag for both: the kernels running beside this one may clear
+  // it at any moment, and the two threads must take the same way.
+  const uint32_t seen = __shfl_sync(pair_mask, half == 0 ? flags[p] : 0u, (int)(threadIdx.x & 30u));
+  if (!seen) return;
   const uint32_t* in = proofs + off / 4;
   const int64_t u = sets[b.d_set_id[p]].u;
   ProofView pv{ns, nd};
@@ -407,21 +415,30 @@ k_rp_verify_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __res
   ok &= g1_from_wire(C, in + 16);
   ok &= g1_from_wire(D, in + ProofView::d_off());
   if (!ok) {
-    flags[p] = 0;
+    if (half == 0) flags[p] = 0;
     return;
   }
-  const Scalar c = sc_from_wire(in + ProofView::c_off());
-  const Scalar zr = sc_from_wire(in + ProofView::zr_off());
-  Scalar e = sc_zero();
-  uint64_t upow = 1;
-  for (int j = 0; j < nd; j++) {
-    e = sc_add(e, sc_mul(sc_from_wire(in + pv.zphi_off(j)), sc_from_u64(upow)));
-    upow *= (uint64_t)u;
+  G1Jac part;
+  if (half == 0) {
+    part = window_mul(jac_from_aff(C), sc_from_wire(in + ProofView::c_off()));
+  } else {
+    const Scalar zr = sc_from_wire(in + ProofView::zr_off());
+    Scalar e = sc_zero();
+    uint64_t upow = 1;
+    for (int j = 0; j < nd; j++) {
+      e = sc_add(e, sc_mul(sc_from_wire(in + pv.zphi_off(j)), sc_from_u64(upow)));
+      upow *= (uint64_t)u;
+    }
+    part = jac_add(comb_mul(tabP, zr), comb_mul(tabB, e));
   }
-  G1Jac Dp = window_mul(jac_from_aff(C), c);
-  Dp = jac_add(Dp, comb_mul(tabP, zr));
-  Dp = jac_add(Dp, comb_mul(tabB, e));
-  if (!jac_eq_aff(Dp, D)) flags[p] = 0;
+  G1Jac other;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    other.x.v[k] = __shfl_xor_sync(pair_mask, part.x.v[k], 1);
+    other.y.v[k] = __shfl_xor_sync(pair_mask, part.y.v[k], 1);
+    other.z.v[k] = __shfl_xor_sync(pair_mask, part.z.v[k], 1);
+  }
+  if (half == 0 && !jac_eq_aff(jac_add(part, other), D)) flags[p] = 0;
 }
 
 #ifndef DRX_VERIFY_MINBLOCKS
@@ -439,7 +456,7 @@ int launch_rp_verify_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_se
   // small blocks spread the extra warps over many SMs instead of stacking four on a few
   static bool carveout_set[64] = {false};
   prefer_shared_carveout(k_rp_verify_hdr, carveout_set);
-  k_rp_verify_hdr<<<grid_for(b.n, 32), 32, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const G1Aff*)d_tabP,
+  k_rp_verify_hdr<<<grid_for(b.n * 2, 32), 32, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const G1Aff*)d_tabP,
                                                      (const uint32_t*)d_proofs, d_flags);
   return 1;
 }
