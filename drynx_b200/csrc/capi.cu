@@ -292,7 +292,7 @@ int drx_init(drx_ctx** out, int device, const uint8_t* g1_base, const uint8_t* g
   if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&c->side_stream2, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_join2, cudaEventDisableTiming) != cudaSuccess ||
-      cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreate(&c->ev_fork) != cudaSuccess ||  // a TIMING event on purpose, see run_verify (capi_rp.inc)
       cudaEventCreateWithFlags(&c->ev_fork0, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
     drx_free(c);
