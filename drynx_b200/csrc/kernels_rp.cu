@@ -489,19 +489,38 @@ int launch_rp_verify_roles(cudaStream_t st, const RpBatch& b, const RpSetDev* d_
 // The GT factor alone (role 1) and the final comparison, used when the pairing runs in the cooperative kernel.
 __global__ void __launch_bounds__(64)
 k_rp_verify_gt(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __restrict__ tabB,
-               const Fp12* __restrict__ tabGtB, const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags,
-               GtPair* __restrict__ scratch) {
+               const Fp12* __restrict__ tabGtB, const Fp12* __restrict__ tabGtB16, const uint32_t* __restrict__ proofs,
+               uint32_t* __restrict__ flags, GtPair* __restrict__ scratch) {
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= b.items) return;
-  rp_verify_role(b, sets, tabB, tabGtB, proofs, flags, scratch, t, 1);
+  if (!tabGtB16) {
+    rp_verify_role(b, sets, tabB, tabGtB, proofs, flags, scratch, t, 1);
+    return;
+  }
+  // role 1 of rp_verify_role with the shared base walked in 16-bit windows: T = A_ij * e(B, g2)^(-Zv_ij)
+  size_t p, off;
+  int i, j, ns, nd;
+  if (!locate_item(b, sets, t, p, i, j, ns, nd, off)) return;
+  const uint32_t* in = proofs + off / 4;
+  ProofView pv{ns, nd};
+  Fp12 A, g;
+  if (!gt_from_wire(A, in + pv.a_off(i, j))) {
+    atomicAnd(&flags[p], 0u);
+    scratch[t].b = fp12_one();
+    return;
+  }
+  gt_comb_pow16(g, tabGtB16, sc_neg(sc_from_wire(in + pv.zv_off(i, j))));
+  fp12_mul(scratch[t].b, A, g);
 }
 int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
-                        const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch) {
+                        const void* d_tabGtB, const void* d_tabGtB16, const uint8_t* d_proofs, uint32_t* d_flags,
+                        void* d_scratch) {
   if (!b.items) return 0;
   static bool carveout_set[64] = {false};
   prefer_shared_carveout(k_rp_verify_gt, carveout_set);
   k_rp_verify_gt<<<grid_for(b.items, 32), 32, 0, st>>>(b, d_sets, (const G1Aff*)d_tabB, (const Fp12*)d_tabGtB,
-                                                      (const uint32_t*)d_proofs, d_flags, (GtPair*)d_scratch);
+                                                      (const Fp12*)d_tabGtB16, (const uint32_t*)d_proofs, d_flags,
+                                                      (GtPair*)d_scratch);
   return 1;
 }
 int launch_rp_verify_finish(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_scratch,

@@ -78,7 +78,7 @@ int launch_comb_table_g2(cudaStream_t st, int nbases, const void* d_bases_aff, v
 int launch_pair_aff(cudaStream_t st, size_t n, const void* d_g1_aff, size_t g1_stride_items, const void* d_g2_aff,
                     void* d_gt);  // g1_stride_items = 0 broadcasts one G1 point
 int launch_comb_table_gt(cudaStream_t st, int nbases, const void* d_bases_gt, void* d_tables);
-constexpr size_t kGt16PerWindow = 65535, kGt16Entries = 16 * kGt16PerWindow;  // 16-bit windows of e(B, g2): 403 MB of Fp12
+constexpr size_t kGt16PerWindow = 65535 /* = DRX_GT16_PER_WINDOW */, kGt16Entries = 16 * kGt16PerWindow;  // 16-bit windows of e(B, g2): 403 MB of Fp12
 int launch_comb_table_gt16(cudaStream_t st, const void* d_tab8, void* d_tab16);
 int launch_pair_wire(cudaStream_t st, size_t n, const uint8_t* d_g1, const uint8_t* d_g2, uint8_t* d_gt, int* d_bad);
 int launch_g2_mul(cudaStream_t st, size_t n, const uint8_t* d_k, const uint8_t* d_pt, uint8_t* d_out, int* d_bad);
@@ -151,7 +151,8 @@ int launch_pair_ucode_s4(cudaStream_t st, size_t items, const void* d_prep, void
 int launch_pair_ucode_s8(cudaStream_t st, size_t items, const void* d_prep, void* d_scratch, unsigned int* d_err,
                          const UcTune& tune);
 int launch_rp_verify_gt(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_tabB,
-                        const void* d_tabGtB, const uint8_t* d_proofs, uint32_t* d_flags, void* d_scratch);
+                        const void* d_tabGtB, const void* d_tabGtB16 /* may be null */, const uint8_t* d_proofs,
+                        uint32_t* d_flags, void* d_scratch);
 int launch_rp_verify_finish(cudaStream_t st, const RpBatch& b, const RpSetDev* d_sets, const void* d_scratch,
                             uint32_t* d_flags);
 // edwards25519 ElGamal (kernels_ed.cu); points travel as 32-byte compressed encodings, ciphertexts as K || C (64 B)

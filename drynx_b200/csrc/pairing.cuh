@@ -240,6 +240,27 @@ DRX_NI void gt_comb_pow(Fp12& out, const Fp12* __restrict__ table, const Scalar&
   out = acc;
 }
 
+// The same over 16-bit windows: table16[w * 65535 + d - 1] = g^(d * 2^(16w)), w < 16 (the one base every proof shares,
+// e(B, g2): kernels_rp.cu k_comb_table_gt16)
+#define DRX_GT16_PER_WINDOW 65535
+DRX_NI void gt_comb_pow16(Fp12& out, const Fp12* __restrict__ table16, const Scalar& k) {
+  Fp12 acc = fp12_one();
+  bool any = false;
+  for (int w = 0; w < 16; w++) {
+    const uint32_t d = (k.v[w >> 1] >> ((w & 1) * 16)) & 0xffffu;
+    if (d) {
+      const Fp12* e = &table16[(size_t)w * DRX_GT16_PER_WINDOW + d - 1];
+      if (any) {
+        fp12_mul(acc, acc, *e);
+      } else {
+        acc = *e;
+        any = true;
+      }
+    }
+  }
+  out = acc;
+}
+
 // ------------------------------------------------------------------ wire helpers for G2 / GT
 // kyber GT MarshalBinary order x.x x.y x.z y.x y.y y.z = w^5 w^3 w^1 w^4 w^2 w^0, each Fp2 as (c1, c0).
 DRX_HD const Fp2& fp12_wire_slot(const Fp12& a, int s) {
