@@ -275,16 +275,16 @@ DRX_HD Jac<F> comb_mul(const Aff<F>* __restrict__ table, const Scalar& k, int wi
   return acc;
 }
 
-// Variable base, 4-bit fixed window, most significant window first.
+// Variable base, 4-bit fixed window, most significant window first; `nibbles` = how many windows the scalar can occupy.
 template <class F>
-DRX_HD Jac<F> window_mul(const Jac<F>& base, const Scalar& k) {
+DRX_HD Jac<F> window_mul(const Jac<F>& base, const Scalar& k, int nibbles = 64) {
   Jac<F> tab[16];
   tab[0] = jac_inf<F>();
   tab[1] = base;
   for (int i = 2; i < 16; i++) tab[i] = (i & 1) ? jac_add(tab[i - 1], base) : jac_dbl(tab[i >> 1]);
   Jac<F> acc = jac_inf<F>();
-  for (int w = 63; w >= 0; w--) {
-    if (w != 63) {
+  for (int w = nibbles - 1; w >= 0; w--) {
+    if (w != nibbles - 1) {
       acc = jac_dbl(acc);
       acc = jac_dbl(acc);
       acc = jac_dbl(acc);
@@ -294,6 +294,123 @@ DRX_HD Jac<F> window_mul(const Jac<F>& base, const Scalar& k) {
     if (d) acc = jac_add(acc, tab[d]);
   }
   return acc;
+}
+
+
+// ------------------------------------------------------------------ GLV on G1 (verification header check)
+// y^2 = x^3 + 3 over Fp with p = 1 mod 3 has the endomorphism phi(x, y) = (beta x, y), beta^3 = 1, and on the group of
+// order n phi(P) = lambda P with lambda = 36u^4 - 1 (lambda^2 + lambda + 1 = 0 mod n). A scalar splits as
+// k = k1 + k2 lambda (mod n) with |k1|, |k2| < 2^128: from the lattice basis (a1, -a2), (a2, b2) of {(x, y): x + y lambda = 0},
+// a1 = 6u^2 + 2u, a2 = 2u + 1, b2 = a1 + a2, take c1 = round(b2 k / n), c2 = round(a2 k / n) and
+// k1 = k - c1 a1 - c2 a2, k2 = c1 a2 - c2 b2. k P = k1 P + k2 phi(P): two products of half length that two threads can do
+// side by side. The roundings use g1 = floor(2^256 b2 / n), g2 = floor(2^256 a2 / n); being off by one only makes k1, k2
+// a little longer, the identity k = k1 + k2 lambda holds for any c1, c2 (the CPU tests recompute the constants from u
+// and check the split and the product through the DRX_HOST_EMU build).
+struct GlvSplit {
+  Scalar k1, k2;     // magnitudes, below 2^132
+  bool neg1, neg2;   // signs
+};
+#define DRX_GLV_NIBBLES 33
+namespace glv_detail {
+DRX_HD uint32_t c_a1(int i) { const uint32_t v[4] = {0xdf0d2a08u, 0xb31b1546u, 0x288a7c7au, 0xbfcdfabeu}; return v[i]; }
+DRX_HD uint32_t c_a2(int i) { const uint32_t v[2] = {0xd8b10603u, 0xb4ed5d35u}; return v[i]; }
+DRX_HD uint32_t c_b2(int i) { const uint32_t v[4] = {0xb7be300bu, 0x6808727cu, 0x288a7c7bu, 0xbfcdfabeu}; return v[i]; }
+DRX_HD uint32_t c_g1(int i) { const uint32_t v[5] = {0xf0575aa6u, 0xf06129ebu, 0xffd56e3eu, 0x55ae596cu, 0x00000001u}; return v[i]; }
+DRX_HD uint32_t c_g2(int i) { const uint32_t v[3] = {0x740d1660u, 0x424dd4afu, 0x00000001u}; return v[i]; }
+// out[0..nout) = limbs 8.. of (k * g + 2^255), g given by the accessor G over ng limbs
+template <uint32_t (*G)(int), int NG>
+DRX_HD void mul_round_hi(uint32_t* out, const uint32_t k[8]) {
+  uint32_t prod[8 + NG + 1];
+  for (int i = 0; i < 8 + NG + 1; i++) prod[i] = 0;
+  for (int j = 0; j < NG; j++) {
+    uint64_t carry = 0;
+    for (int i = 0; i < 8; i++) {
+      const uint64_t t = (uint64_t)k[i] * G(j) + prod[i + j] + carry;
+      prod[i + j] = (uint32_t)t;
+      carry = t >> 32;
+    }
+    prod[8 + j] = (uint32_t)carry;
+  }
+  uint64_t c = (uint64_t)prod[7] + 0x80000000u;  // + 2^255
+  c >>= 32;
+  for (int i = 8; i < 8 + NG + 1; i++) {
+    c += prod[i];
+    prod[i] = (uint32_t)c;
+    c >>= 32;
+  }
+  for (int i = 0; i < NG + 1; i++) out[i] = prod[8 + i];
+}
+// acc (8 limbs, mod 2^256) -= x * y, x over nx limbs, y by accessor over NY limbs
+template <uint32_t (*Y)(int), int NY>
+DRX_HD void sub_mul(uint32_t acc[8], const uint32_t* x, int nx) {
+  uint32_t prod[8];
+  for (int i = 0; i < 8; i++) prod[i] = 0;
+  for (int j = 0; j < NY; j++) {
+    uint64_t carry = 0;
+    for (int i = 0; i < nx && i + j < 8; i++) {
+      const uint64_t t = (uint64_t)x[i] * Y(j) + prod[i + j] + carry;
+      prod[i + j] = (uint32_t)t;
+      carry = t >> 32;
+    }
+    if (nx + j < 8) prod[nx + j] = (uint32_t)carry;
+  }
+  uint64_t borrow = 0;
+  for (int i = 0; i < 8; i++) {
+    const uint64_t t = (uint64_t)acc[i] - prod[i] - borrow;
+    acc[i] = (uint32_t)t;
+    borrow = (t >> 32) & 1u;
+  }
+}
+DRX_HD bool take_sign(uint32_t v[8]) {  // two's complement -> magnitude; returns "was negative"
+  if (!(v[7] >> 31)) return false;
+  uint64_t c = 1;
+  for (int i = 0; i < 8; i++) {
+    c += (uint32_t)~v[i];
+    v[i] = (uint32_t)c;
+    c >>= 32;
+  }
+  return true;
+}
+}  // namespace glv_detail
+DRX_HD GlvSplit glv_split(const Scalar& k) {
+  using namespace glv_detail;
+  uint32_t c1[6], c2[4];
+  mul_round_hi<c_g1, 5>(c1, k.v);
+  mul_round_hi<c_g2, 3>(c2, k.v);
+  GlvSplit r;
+  for (int i = 0; i < 8; i++) {
+    r.k1.v[i] = k.v[i];
+    r.k2.v[i] = 0;
+  }
+  sub_mul<c_a1, 4>(r.k1.v, c1, 6);   // k1 = k - c1 a1 - c2 a2
+  sub_mul<c_a2, 2>(r.k1.v, c2, 4);
+  sub_mul<c_b2, 4>(r.k2.v, c2, 4);   // k2 = -c2 b2 + c1 a2: subtract, then negate the part with the other sign
+  uint32_t t[8];
+  for (int i = 0; i < 8; i++) t[i] = 0;
+  sub_mul<c_a2, 2>(t, c1, 6);        // t = -c1 a2
+  uint64_t borrow = 0;
+  for (int i = 0; i < 8; i++) {      // k2 = k2 - t
+    const uint64_t d = (uint64_t)r.k2.v[i] - t[i] - borrow;
+    r.k2.v[i] = (uint32_t)d;
+    borrow = (d >> 32) & 1u;
+  }
+  r.neg1 = take_sign(r.k1.v);
+  r.neg2 = take_sign(r.k2.v);
+  return r;
+}
+// beta in Montgomery form: phi(x, y) = (beta x, y) = lambda (x, y)
+DRX_HD Fp glv_beta() {
+  const uint32_t v[8] = {0xe1ada57du, 0x12d3cef5u, 0x3753babbu, 0xe2eca146u, 0xddccf750u, 0x0ca41e40u, 0x0397e04cu, 0x55133706u};
+  Fp r;
+  for (int i = 0; i < 8; i++) r.v[i] = v[i];
+  return r;
+}
+// half h (0 or 1) of k * P: k1 * P or k2 * phi(P), the sign folded into the point; the two halves add up to k * P
+DRX_HD Jac<Fp> glv_half_mul(const Aff<Fp>& P, const GlvSplit& s, int h) {
+  Aff<Fp> Q = P;
+  if (h) Q.x = fp_mul(Q.x, glv_beta());
+  if (h ? s.neg2 : s.neg1) Q = aff_neg(Q);
+  return window_mul(jac_from_aff(Q), h ? s.k2 : s.k1, DRX_GLV_NIBBLES);
 }
 
 }  // namespace drx

@@ -385,10 +385,12 @@ int launch_rp_create_hdr(cudaStream_t st, const RpBatch& b, const RpSetDev* d_se
 
 // ------------------------------------------------------------------ verification (a-8)
 // Header check per proof: parse, D check (lib/range/range_proof.go:520-529, :561). flags[p] starts at the host's
-// size-check verdict and is cleared on any failure. Two threads per proof: the even one computes c*C (a variable-base
-// product, 2,816 M), the odd one the two comb walks Zr*P + (sum_j Zphi_j u^j)*B (704 M); a shuffle brings the halves
-// together. The kernel runs beside the pairing kernel and, as one thread per proof (3,550 M in a row), outlasted it at
-// the headline size once that kernel got below 4 ms.
+// size-check verdict and is cleared on any failure. Two threads per proof: c*C is split by the curve's endomorphism into
+// two products of half length (curve.cuh glv_split), one per thread, and each thread adds one of the comb walks Zr*P and
+// (sum_j Zphi_j u^j)*B; a shuffle brings the halves together. The kernel runs beside the pairing kernel; as one thread
+// per proof (3,550 M in a row) it outlasted that kernel at the headline size once it got below 4 ms; now its chain is
+// 2,000 M. (Four threads per proof, 1,650 M, finish sooner but put twice the warps beside the pairing kernel, which
+// then takes 4.19 instead of 3.94 ms: measured, not kept.)
 __global__ void __launch_bounds__(128)
 k_rp_verify_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __restrict__ tabB,
                 const G1Aff* __restrict__ tabP, const uint32_t* __restrict__ proofs, uint32_t* __restrict__ flags) {
@@ -418,18 +420,17 @@ k_rp_verify_hdr(RpBatch b, const RpSetDev* __restrict__ sets, const G1Aff* __res
     if (half == 0) flags[p] = 0;
     return;
   }
-  G1Jac part;
+  G1Jac part = glv_half_mul(C, glv_split(sc_from_wire(in + ProofView::c_off())), half);
   if (half == 0) {
-    part = window_mul(jac_from_aff(C), sc_from_wire(in + ProofView::c_off()));
+    part = jac_add(part, comb_mul(tabP, sc_from_wire(in + ProofView::zr_off())));
   } else {
-    const Scalar zr = sc_from_wire(in + ProofView::zr_off());
     Scalar e = sc_zero();
     uint64_t upow = 1;
     for (int j = 0; j < nd; j++) {
       e = sc_add(e, sc_mul(sc_from_wire(in + pv.zphi_off(j)), sc_from_u64(upow)));
       upow *= (uint64_t)u;
     }
-    part = jac_add(comb_mul(tabP, zr), comb_mul(tabB, e));
+    part = jac_add(part, comb_mul(tabB, e));
   }
   G1Jac other;
 #pragma unroll

@@ -249,7 +249,7 @@ DRX_NI void gt_comb_pow16(Fp12& out, const Fp12* __restrict__ table16, const Sca
   for (int w = 0; w < 16; w++) {
     const uint32_t d = (k.v[w >> 1] >> ((w & 1) * 16)) & 0xffffu;
     if (d) {
-      const Fp12* e = &table16[(size_t)w * DRX_GT16_PER_WINDOW + d - 1];
+      const Fp12* e = &table16[(unsigned long long)w * DRX_GT16_PER_WINDOW + d - 1];
       if (any) {
         fp12_mul(acc, acc, *e);
       } else {

@@ -148,6 +148,24 @@ int emu_g1_add(const uint8_t* a64, const uint8_t* b64, uint8_t* out64) {
   return 0;
 }
 
+// GLV on G1 (curve.cuh glv_split / glv_half_mul): the split (magnitudes as 8 limbs each, signs in bits 0 and 1 of the
+// return value) and k * P as the sum of its two half products
+int emu_glv_split(const uint8_t* k32, uint32_t* k1, uint32_t* k2) {
+  uint32_t kw[8]; load_words(kw, k32, 32);
+  const GlvSplit s = glv_split(sc_from_wire(kw));
+  memcpy(k1, s.k1.v, 32); memcpy(k2, s.k2.v, 32);
+  return (s.neg1 ? 1 : 0) | (s.neg2 ? 2 : 0);
+}
+int emu_g1_mul_glv(const uint8_t* k32, const uint8_t* pt64, uint8_t* out64) {
+  uint32_t kw[8], pw[16], ow[16];
+  load_words(kw, k32, 32); load_words(pw, pt64, 64);
+  G1Aff p; if (!g1_from_wire(p, pw)) return -1;
+  const GlvSplit s = glv_split(sc_from_wire(kw));
+  const G1Jac r = jac_add(glv_half_mul(p, s, 0), glv_half_mul(p, s, 1));
+  g1_to_wire(ow, jac_to_aff(r)); memcpy(out64, ow, 64);
+  return 0;
+}
+
 int emu_g2_mul(const uint8_t* k32, const uint8_t* pt128, uint8_t* out128) {
   uint32_t kw[8], pw[32], ow[32];
   load_words(kw, k32, 32); load_words(pw, pt128, 128);

@@ -2,6 +2,7 @@
 modelled in C, against the oracle. This checks the GPU algorithms (Montgomery rows, tower, curve, Miller loop,
 final exponentiation, comb tables) on the CPU; the real kernels are checked by the -m gpu tests."""
 import ctypes
+import os
 
 import numpy as np
 import pytest
@@ -151,3 +152,41 @@ def test_interpreter_runs_the_emitted_pairing_program(emu, oracle, rng):
         assert R.g2_on_curve(Qo) and not R.g2_in_subgroup(Qo)
         assert emu.emu_ucode_pair(P, R.g2_to_bytes(Qo), out) == 1
         assert out.raw == bytes(384)
+
+
+def test_glv_split_and_product(emu, oracle, rng):
+    """curve.cuh glv_split / glv_half_mul on the CPU: the constants follow from u, every scalar splits as
+    k = +-k1 +- k2 lambda (mod n) with both parts below 2^128 (the kernel walks 33 nibbles), and the two half products
+    add up to the oracle's k * P, infinity and the edge scalars included."""
+    u = 6518589491078791937
+    lam = (36 * u ** 4 - 1) % R.n
+    assert (lam * lam + lam + 1) % R.n == 0
+    a1, a2 = 6 * u * u + 2 * u, 2 * u + 1
+    b2 = a1 + a2
+    assert (a1 - a2 * lam) % R.n == 0 and (a2 + b2 * lam) % R.n == 0
+    src = open(os.path.join(os.path.dirname(__file__), '..', 'drynx_b200', 'csrc', 'curve.cuh')).read()
+    def const(name):
+        body = src.split('c_%s(int i) { const uint32_t v[' % name)[1].split('{')[1].split('}')[0]
+        return sum(int(x.strip().rstrip('u'), 16) << (32 * i) for i, x in enumerate(body.split(',')))
+    assert (const('a1'), const('a2'), const('b2')) == (a1, a2, b2)
+    assert const('g1') == (b2 << 256) // R.n and const('g2') == (a2 << 256) // R.n
+    g1, _ = oracle.generators()
+    scalars = [0, 1, 2, R.n - 1, R.n - 2, lam, lam + 1, lam - 1, R.n // 2, 1 << 255, a1, b2, (1 << 256) - 1]
+    scalars += [rng.scalar() for _ in range(300)]
+    k1 = (ctypes.c_uint32 * 8)()
+    k2 = (ctypes.c_uint32 * 8)()
+    P = oracle.g1_mul(rng.scalar().to_bytes(32, 'big'), g1)
+    out = ctypes.create_string_buffer(64)
+    for n_, k in enumerate(scalars):
+        kb = k.to_bytes(32, 'big')
+        signs = emu.emu_glv_split(kb, k1, k2)
+        v1 = sum(int(v) << (32 * i) for i, v in enumerate(k1))
+        v2 = sum(int(v) << (32 * i) for i, v in enumerate(k2))
+        assert v1 < 1 << 128 and v2 < 1 << 128, k
+        s1 = -v1 if signs & 1 else v1
+        s2 = -v2 if signs & 2 else v2
+        assert (s1 + s2 * lam - k) % R.n == 0, k
+        if n_ < 40:
+            assert emu.emu_g1_mul_glv(kb, P, out) == 0
+            assert out.raw == oracle.g1_mul((k % R.n).to_bytes(32, 'big'), P), k
+    assert emu.emu_g1_mul_glv((12345).to_bytes(32, 'big'), bytes(64), out) == 0 and out.raw == bytes(64)
