@@ -405,6 +405,37 @@ DRX_HD Fp glv_beta() {
   for (int i = 0; i < 8; i++) r.v[i] = v[i];
   return r;
 }
+// k * P in one thread: the two half-length products walked together (Straus), 33 windows of four doublings with up to
+// two additions each; the second table is the first under phi (one field product per entry). 2,220 M against 3,040 M
+// for the plain 64-window walk.
+DRX_HD Jac<Fp> window_mul_glv(const Aff<Fp>& P, const Scalar& k) {
+  const GlvSplit s = glv_split(k);
+  const Jac<Fp> base = jac_from_aff(s.neg1 ? aff_neg(P) : P);
+  Jac<Fp> tab1[16], tab2[16];
+  tab1[0] = jac_inf<Fp>();
+  tab1[1] = base;
+  for (int i = 2; i < 16; i++) tab1[i] = (i & 1) ? jac_add(tab1[i - 1], base) : jac_dbl(tab1[i >> 1]);
+  const Fp beta = glv_beta();
+  const bool flip = s.neg1 != s.neg2;
+  for (int i = 0; i < 16; i++) {
+    tab2[i].x = fp_mul(tab1[i].x, beta);
+    tab2[i].y = flip ? fp_neg(tab1[i].y) : tab1[i].y;
+    tab2[i].z = tab1[i].z;
+  }
+  Jac<Fp> acc = jac_inf<Fp>();
+  for (int w = DRX_GLV_NIBBLES - 1; w >= 0; w--) {
+    if (w != DRX_GLV_NIBBLES - 1) {
+      acc = jac_dbl(acc);
+      acc = jac_dbl(acc);
+      acc = jac_dbl(acc);
+      acc = jac_dbl(acc);
+    }
+    const uint32_t d1 = (s.k1.v[w >> 3] >> ((w & 7) * 4)) & 15u, d2 = (s.k2.v[w >> 3] >> ((w & 7) * 4)) & 15u;
+    if (d1) acc = jac_add(acc, tab1[d1]);
+    if (d2) acc = jac_add(acc, tab2[d2]);
+  }
+  return acc;
+}
 // half h (0 or 1) of k * P: k1 * P or k2 * phi(P), the sign folded into the point; the two halves add up to k * P
 DRX_HD Jac<Fp> glv_half_mul(const Aff<Fp>& P, const GlvSplit& s, int h) {
   Aff<Fp> Q = P;

@@ -593,7 +593,7 @@ k_decrypt(size_t n, const uint32_t* __restrict__ sk, const uint32_t* __restrict_
     out[i] = INT64_MIN;
     return;
   }
-  const G1Jac S = window_mul(jac_from_aff(K), k);
+  const G1Jac S = window_mul_glv(K, k);
   const G1Jac M = jac_add_aff(jac_neg(S), C);
   out[i] = dlog_lookup(jac_to_aff(M), keys, vals);
 }
@@ -638,7 +638,7 @@ k_keyswitch(size_t n, const uint32_t* __restrict__ sk, const uint32_t* __restric
   const Scalar vi = sc_from_wire(v + 8 * i);
   const G1Jac K = comb_mul(tabB, vi);
   const G1Jac S = comb_mul(tabQ, vi);
-  const G1Jac X = window_mul(jac_from_aff(Rn), sc_from_wire(sk));
+  const G1Jac X = window_mul_glv(Rn, sc_from_wire(sk));
   store_pair_wire(cv + 32 * i, K, jac_add(X, S));
 }
 int launch_keyswitch(cudaStream_t st, size_t n, const uint8_t* d_sk, const uint8_t* d_rb, const uint8_t* d_v,
@@ -667,7 +667,7 @@ k_ct_scalar_mul(size_t n, const uint32_t* __restrict__ sc, const uint32_t* __res
     return;
   }
   const Scalar k = sc_from_wire(sc + 8 * i);
-  store_pair_wire(out + 32 * i, window_mul(jac_from_aff(K), k), window_mul(jac_from_aff(C), k));
+  store_pair_wire(out + 32 * i, window_mul_glv(K, k), window_mul_glv(C, k));
 }
 int launch_ct_scalar_mul(cudaStream_t st, size_t n, const uint8_t* d_s, const uint8_t* d_ct, uint8_t* d_out, int* d_bad) {
   if (!n) return 0;
@@ -728,7 +728,7 @@ k_schnorr_verify(size_t n, const uint32_t* __restrict__ pub, const uint32_t* __r
   }
   const Scalar h = sc_from_digest(digest + 16 * i);
   // s*B - h*P - R must be the identity
-  G1Jac T = jac_add(comb_mul(tabB, s), jac_neg(window_mul(jac_from_aff(P), h)));
+  G1Jac T = jac_add(comb_mul(tabB, s), jac_neg(window_mul_glv(P, h)));
   T = jac_add_aff(T, aff_neg(R));
   ok[i] = jac_is_inf(T) ? 1 : 0;
 }
@@ -761,7 +761,7 @@ k_rep_commit(size_t n, int nt, const uint32_t* __restrict__ sc, const uint32_t* 
       for (int k = 0; k < 16; k++) out[16 * i + k] = 0;
       return;
     }
-    acc = jac_add(acc, window_mul(jac_from_aff(B), sc_from_wire(sc + 8 * (i * nt + j))));
+    acc = jac_add(acc, window_mul_glv(B, sc_from_wire(sc + 8 * (i * nt + j))));
   }
   g1_to_wire(out + 16 * i, jac_to_aff(acc));
 }
@@ -786,7 +786,7 @@ k_rep_verify(size_t n, int nt, const uint32_t* __restrict__ resp, const uint32_t
     ok[i] = 0;
     return;
   }
-  G1Jac acc = window_mul(jac_from_aff(Pi), sc_from_wire(chal + 8 * i));
+  G1Jac acc = window_mul_glv(Pi, sc_from_wire(chal + 8 * i));
   for (int j = 0; j < nt; j++) {
     G1Aff B;
     Scalar rj;
@@ -795,7 +795,7 @@ k_rep_verify(size_t n, int nt, const uint32_t* __restrict__ resp, const uint32_t
       ok[i] = 0;
       return;
     }
-    acc = jac_add(acc, window_mul(jac_from_aff(B), rj));
+    acc = jac_add(acc, window_mul_glv(B, rj));
   }
   acc = jac_add_aff(acc, aff_neg(Vi));
   ok[i] = jac_is_inf(acc) ? 1 : 0;
@@ -827,7 +827,7 @@ __global__ void k_g1_mul(size_t n, const uint32_t* __restrict__ k, const uint32_
   if (i >= n) return;
   G1Aff p;
   if (!g1_from_wire(p, pt + 16 * i)) atomicAdd(bad, 1);
-  const G1Jac r = window_mul(jac_from_aff(p), sc_from_wire(k + 8 * i));
+  const G1Jac r = window_mul_glv(p, sc_from_wire(k + 8 * i));
   g1_to_wire(out + 16 * i, jac_to_aff(r));
 }
 int launch_g1_mul(cudaStream_t st, size_t n, const uint8_t* d_k, const uint8_t* d_pt, uint8_t* d_out, int* d_bad) {

@@ -163,7 +163,9 @@ int emu_g1_mul_glv(const uint8_t* k32, const uint8_t* pt64, uint8_t* out64) {
   const GlvSplit s = glv_split(sc_from_wire(kw));
   const G1Jac r = jac_add(glv_half_mul(p, s, 0), glv_half_mul(p, s, 1));
   g1_to_wire(ow, jac_to_aff(r)); memcpy(out64, ow, 64);
-  return 0;
+  uint32_t ow2[16];
+  g1_to_wire(ow2, jac_to_aff(window_mul_glv(p, sc_from_wire(kw))));  // the one-thread form must agree
+  return memcmp(ow, ow2, 64) ? -2 : 0;
 }
 
 int emu_g2_mul(const uint8_t* k32, const uint8_t* pt128, uint8_t* out128) {
