@@ -14,6 +14,7 @@ import (
 
 	libdrynxobfuscation "github.com/ldsec/drynx/lib/obfuscation"
 	libunlynx "github.com/ldsec/unlynx/lib"
+	libunlynxkeyswitch "github.com/ldsec/unlynx/lib/key_switch"
 	"go.dedis.ch/kyber/v3"
 	"go.dedis.ch/kyber/v3/util/random"
 )
@@ -143,6 +144,75 @@ func (x *Ctx) ObfuscationListProofVerification(plop libdrynxobfuscation.Publishe
 		return false, lastErr()
 	}
 	if bytes.IndexByte(ok, 0) >= 0 {
+		return false, nil
+	}
+	return true, nil
+}
+
+const ksProofLen = 3*G1Len + 2*ScalarLen
+
+func marshalPoints(dst []byte, pts ...kyber.Point) error {
+	for i, p := range pts {
+		b, err := p.MarshalBinary()
+		if err != nil {
+			return err
+		}
+		copy(dst[G1Len*i:], b)
+	}
+	return nil
+}
+
+// KeySwitchListProofVerification replaces libunlynxkeyswitch.KeySwitchListProofVerification (unlynx v1.4.0
+// lib/key_switch; the verifying node calls it at lib/proof/structs_proofs.go:476): predicate
+// And(Rep(viB = vi*B), Rep(K = k*B), Rep(ks2 = vi*Q + k*rBNeg)), proof bytes V1 || V2 || V3 || r_vi || r_k. Two device
+// calls for the first ceil(percent*len) proofs: 2n relations with one term, n relations with two.
+func (x *Ctx) KeySwitchListProofVerification(pkslp libunlynxkeyswitch.PublishedKSListProof, percent float64) (bool, error) {
+	n := int(math.Ceil(percent * float64(len(pkslp.List))))
+	if n == 0 {
+		return true, nil
+	}
+	B := libunlynx.SuiTe.Point().Base()
+	r1, c1 := make([]byte, 2*ScalarLen*n), make([]byte, 2*ScalarLen*n)
+	b1, p1, v1 := make([]byte, 2*G1Len*n), make([]byte, 2*G1Len*n), make([]byte, 2*G1Len*n)
+	c2, b2, p2, v2 := make([]byte, ScalarLen*n), make([]byte, 2*G1Len*n), make([]byte, G1Len*n), make([]byte, G1Len*n)
+	for i := 0; i < n; i++ {
+		pr := pkslp.List[i]
+		if len(pr.Proof) != ksProofLen {
+			return false, nil
+		}
+		ch, err := newTranscript("proofTest").challenge(pr.Proof[:3*G1Len])
+		if err != nil {
+			return false, err
+		}
+		cbin, _ := ch.MarshalBinary()
+		copy(r1[2*ScalarLen*i:], pr.Proof[3*G1Len:]) // r_vi, r_k: relation 1 uses r_vi, relation 2 uses r_k
+		copy(c1[2*ScalarLen*i:], cbin)
+		copy(c1[2*ScalarLen*i+ScalarLen:], cbin)
+		copy(c2[ScalarLen*i:], cbin)
+		if err := marshalPoints(b1[2*G1Len*i:], B, B); err != nil {
+			return false, err
+		}
+		if err := marshalPoints(p1[2*G1Len*i:], pr.ViB, pr.K); err != nil {
+			return false, err
+		}
+		copy(v1[2*G1Len*i:], pr.Proof[:2*G1Len])
+		if err := marshalPoints(b2[2*G1Len*i:], pr.Q, pr.RbNeg); err != nil {
+			return false, err
+		}
+		if err := marshalPoints(p2[G1Len*i:], pr.Ks2); err != nil {
+			return false, err
+		}
+		copy(v2[G1Len*i:], pr.Proof[2*G1Len:3*G1Len])
+	}
+	ok1, ok2 := make([]byte, 2*n), make([]byte, n)
+	if C.drx_rep_verify(x.c, C.size_t(2*n), 1, u8(r1), u8(c1), u8(b1), u8(p1), u8(v1), u8(ok1)) != 0 {
+		return false, lastErr()
+	}
+	// the two-term relation reads (r_vi, r_k) in the order they stand in the proof
+	if C.drx_rep_verify(x.c, C.size_t(n), 2, u8(r1), u8(c2), u8(b2), u8(p2), u8(v2), u8(ok2)) != 0 {
+		return false, lastErr()
+	}
+	if bytes.IndexByte(ok1, 0) >= 0 || bytes.IndexByte(ok2, 0) >= 0 {
 		return false, nil
 	}
 	return true, nil
