@@ -230,6 +230,7 @@ def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes, 
     backend.set_option('rp_ucode_lanes', lanes)
     backend.set_option('rp_ucode_mode', mode)
     backend.set_option('rp_verify_gt', 2 if mode == 2 else 0)   # the lane-group GT factor kernel on the task-queue runs
+    backend.set_option('rp_verify_hdr_early', 1 if lanes == 8 else 0)   # the header check's other place in the stream order
     try:
         ok = backend.verify_range_proofs([60] * n, [l] * n, bytes(bad), off)
     finally:
@@ -237,6 +238,7 @@ def test_all_verification_paths_match_oracle(backend, oracle, rng, path, lanes, 
         backend.set_option('rp_ucode_lanes', 0)
         backend.set_option('rp_ucode_mode', 0)
         backend.set_option('rp_verify_gt', 0)
+        backend.set_option('rp_verify_hdr_early', 0)
     assert list(ok) == list(want) == [1, 0, 0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 0, 1]
 
 
