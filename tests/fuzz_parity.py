@@ -1,0 +1,236 @@
+"""Differential fuzzing of the CUDA path against the oracle through the C ABI (test infrastructure, like the oracle).
+
+Every case draws a range-proof shape (ns, u, l), keys, secrets (in range, at the edges, out of range, negative), and the
+prover's randomness; compares the created proof bytes with the oracle's; mutates about half of the proofs (bit flips
+anywhere, 32-byte words zeroed / set to 0xff.. / replaced / swapped / copied from another proof) and compares the
+accept bits of a randomly chosen verification path with the oracle's (lib/range/range_proof.go:504-565 as restated in
+oracle/oracle.cpp). A second family does the same for ElGamal vectors: encryption, aggregation with damaged points,
+decryption with negatives and out-of-table plaintexts.
+
+    python tests/fuzz_parity.py --seconds 240 --seed 1 [--log gpurun_out/fuzz.log]
+
+tests/test_gpu_fuzz.py runs a few seeded seconds of both families with `-m gpu`.
+"""
+import argparse
+import os
+import sys
+import time
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+sys.path.insert(0, os.path.join(HERE, '..', 'oracle'))
+sys.path.insert(0, os.path.join(HERE, '..'))
+
+import bn256_ref as R  # noqa: E402
+from conftest import SplitMix  # noqa: E402
+
+SHAPES_U = [2, 3, 4, 5, 8, 10, 16]
+VERIFY_OPTIONS = ('rp_verify_path', 'rp_ucode_lanes', 'rp_ucode_mode', 'rp_verify_gt', 'rp_verify_hdr_early', 'rp_create_path')
+
+
+def _scalar_bytes(g, k):
+    """k scalars below n as big-endian bytes (top bit cleared, then reduced by rejection like kyber's Pick)."""
+    out = []
+    while len(out) < k:
+        v = int.from_bytes(g.bytes(32), 'big') >> 2
+        if v < R.n:
+            out.append(v.to_bytes(32, 'big'))
+    return b''.join(out)
+
+
+def _mutate(g, buf, lo, hi, other):
+    """One random mutation of proof bytes buf[lo:hi]; `other` = (lo, hi) of another proof of the same shape or None."""
+    kind = int(g.integers(0, 7))
+    size = hi - lo
+    words = size // 32
+    if kind == 0:
+        pos = lo + int(g.integers(0, size))
+        buf[pos] ^= 1 << int(g.integers(0, 8))
+        return 'bit'
+    w = lo + 32 * int(g.integers(0, words))
+    if kind == 1:
+        buf[w:w + 32] = bytes(32)
+        return 'zero word'
+    if kind == 2:
+        buf[w:w + 32] = b'\xff' * 32
+        return 'ff word'
+    if kind == 3:
+        buf[w:w + 32] = g.bytes(32)
+        return 'random word'
+    if kind == 4:
+        w2 = lo + 32 * int(g.integers(0, words))
+        a, b = bytes(buf[w:w + 32]), bytes(buf[w2:w2 + 32])
+        buf[w:w + 32], buf[w2:w2 + 32] = b, a
+        return 'swap words'
+    if kind == 5 and other is not None and other[1] - other[0] == size:
+        buf[w:w + 32] = buf[other[0] + (w - lo):other[0] + (w - lo) + 32]
+        return 'word of another proof'
+    # a whole 128-byte block (a G2 point or a third of a GT element) cleared
+    blocks = size // 128
+    b0 = lo + 128 * int(g.integers(0, blocks))
+    buf[b0:b0 + 128] = bytes(128)
+    return 'zero block'
+
+
+def fuzz_rangeproofs(backend, oracle, seed, seconds, log=None, max_cases=None, threads=None):
+    g = np.random.default_rng(seed)
+    threads = threads or min(16, os.cpu_count() or 1)
+    deadline = time.time() + seconds
+    stats = {'cases': 0, 'proofs_created': 0, 'proofs_verified': 0, 'accepted': 0, 'rejected': 0, 'mutations': {}}
+    while time.time() < deadline and (max_cases is None or stats['cases'] < max_cases):
+        ns = int(g.integers(1, 6))
+        u = int(g.choice(SHAPES_U))
+        lmax = 1
+        while lmax < 8 and u ** (lmax + 1) < (1 << 40):
+            lmax += 1
+        l = int(g.integers(1, lmax + 1))
+        n = int(g.integers(1, 25))
+        sid = int(g.integers(0, 64))
+        sk = int.from_bytes(_scalar_bytes(g, 1), 'big') or 1
+        P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+        backend.set_pubkey(P)
+        xs = [int.from_bytes(_scalar_bytes(g, 1), 'big') or 1 for _ in range(ns)]
+        Y, A = oracle.make_sigs(xs, u)
+        backend.set_signatures(sid, ns, u, Y, A)
+        top = u ** l
+        secrets = []
+        for _ in range(n):
+            c = int(g.integers(0, 10))
+            if c == 0:
+                secrets.append(int(g.choice([0, 1, top - 1, top // 2])))
+            elif c == 1:
+                secrets.append(int(top + g.integers(0, top)))        # needs more digits: the size check fails
+            elif c == 2:
+                secrets.append(-int(g.integers(1, 1000)))            # all-zero digits, inconsistent D
+            else:
+                secrets.append(int(g.integers(0, top)))
+        rs = _scalar_bytes(g, n)
+        cts = backend.encrypt_int_vector(secrets, rs).tobytes()
+        assert cts == oracle.encrypt(P, secrets, rs, threads=threads), ('encrypt', seed, stats['cases'])
+        rnd = [_scalar_bytes(g, len(R.to_base(s, u, l)) * (3 + ns)) for s in secrets]
+        opts = {'rp_create_path': int(g.integers(0, 4)),
+                'rp_verify_path': int(g.choice([0, 1, 2])),
+                'rp_ucode_lanes': int(g.choice([0, 4, 8])),
+                'rp_ucode_mode': int(g.choice([0, 1, 2])),
+                'rp_verify_gt': int(g.choice([0, 2])),
+                'rp_verify_hdr_early': int(g.integers(0, 2))}
+        for k, v in opts.items():
+            backend.set_option(k, v)
+        try:
+            proofs, off = backend.create_range_proofs([sid] * n, {sid: ns}, {sid: u}, [l] * n, secrets, rs, cts, rnd)
+            want, woff = oracle.rp_create(ns, u, l, Y, A, P, secrets, rs, cts, rnd, threads=threads)
+            assert list(off) == list(woff), ('offsets', seed, stats['cases'], ns, u, l, opts)
+            assert proofs.tobytes() == want, ('created bytes', seed, stats['cases'], ns, u, l, secrets, opts)
+            stats['proofs_created'] += n
+            bad = bytearray(want)
+            for p in range(n):
+                if g.integers(0, 2):
+                    continue
+                q = int(g.integers(0, n))
+                other = (int(off[q]), int(off[q + 1])) if q != p else None
+                for _ in range(int(g.integers(1, 3))):
+                    m = _mutate(g, bad, int(off[p]), int(off[p + 1]), other)
+                    stats['mutations'][m] = stats['mutations'].get(m, 0) + 1
+            ok = backend.verify_range_proofs([sid] * n, [l] * n, bytes(bad), off)
+            ref = oracle.rp_verify(ns, u, l, Y, P, bytes(bad), off, threads=threads)
+            assert list(ok) == list(ref), ('accept bits', seed, stats['cases'], ns, u, l, secrets, opts, list(ok), list(ref))
+        finally:
+            for k in opts:
+                backend.set_option(k, 0)
+        stats['cases'] += 1
+        stats['proofs_verified'] += n
+        stats['accepted'] += int(np.sum(ref))
+        stats['rejected'] += n - int(np.sum(ref))
+        if log:
+            log.write('rp case %d: ns=%d u=%d l=%d n=%d %s accepted %d/%d\n' % (stats['cases'], ns, u, l, n, opts, int(np.sum(ref)), n))
+    return stats
+
+
+def fuzz_elgamal(backend, oracle, seed, seconds, log=None, max_cases=None, threads=None, make_backend=None):
+    g = np.random.default_rng(seed ^ 0x5eed)
+    threads = threads or min(16, os.cpu_count() or 1)
+    deadline = time.time() + seconds
+    stats = {'cases': 0, 'ciphertexts': 0, 'damaged_points': 0}
+    # the reference's discrete-log map grows lazily and remembers what earlier calls made it store
+    # (tests/test_gpu_elgamal.py::test_decrypt_matches_oracle_including_table_state): fresh state on both sides,
+    # then the same sequence of calls
+    backend = make_backend() if make_backend else backend
+    oracle.dlog_reset()
+    while time.time() < deadline and (max_cases is None or stats['cases'] < max_cases):
+        sk = int.from_bytes(_scalar_bytes(g, 1), 'big') or 1
+        P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+        backend.set_pubkey(P)
+        ndp = int(g.integers(1, 40))
+        v = int(g.integers(1, 20))
+        msgs = g.integers(-3000, 3000, size=ndp * v)
+        big = g.integers(0, ndp * v, size=max(1, ndp * v // 16))
+        msgs[big] = g.integers(-(1 << 40), 1 << 40, size=big.size)        # outside every table: reported as not found
+        msgs = [int(m) for m in msgs]
+        rs = _scalar_bytes(g, ndp * v)
+        cts = backend.encrypt_int_vector(msgs, rs).tobytes()
+        assert cts == oracle.encrypt(P, msgs, rs, threads=threads), ('encrypt', seed, stats['cases'])
+        vectors = [bytearray(cts[k * v * 128:(k + 1) * v * 128]) for k in range(ndp)]
+        damaged = 0
+        with_damage = g.integers(0, 3) == 0
+        for k in range(ndp):
+            if with_damage and g.integers(0, 8) == 0:                                     # a point that leaves the curve / a coordinate >= p
+                pos = 64 * int(g.integers(0, 2 * v))
+                if g.integers(0, 2):
+                    vectors[k][pos + int(g.integers(0, 64))] ^= 1 << int(g.integers(0, 8))
+                else:
+                    vectors[k][pos:pos + 32] = b'\xff' * 32
+                damaged += 1
+        vectors = [bytes(x) for x in vectors]
+        rc, want = oracle.aggregate(vectors, threads=threads)
+        try:
+            got = backend.aggregate(vectors).tobytes()
+            refused = False
+        except Exception:
+            refused = True
+        # a flipped bit can land on another curve point only with negligible probability: damaged input is refused
+        # by both (a failed UnmarshalBinary in CipherVector.FromBytes), clean input by neither
+        assert refused == (rc != 0), ('aggregate refusal', seed, stats['cases'], ndp, v, damaged, rc)
+        assert refused == (damaged > 0), ('aggregate refusal vs damage', seed, stats['cases'], damaged)
+        if not refused:
+            assert got == want, ('aggregate', seed, stats['cases'], ndp, v)
+            skb = sk.to_bytes(32, 'big')
+            with_neg = bool(g.integers(0, 4))
+            dec, found = backend.decrypt_int_vector(skb, got, with_neg=with_neg, return_found=True)
+            ref, rfound = oracle.decrypt(skb, got, with_neg=with_neg, threads=1)
+            assert list(found) == list(rfound), ('decrypt found flags', seed, stats['cases'])
+            assert [int(x) for x, f in zip(dec, found) if f] == [int(x) for x, f in zip(ref, rfound) if f], ('decrypt', seed, stats['cases'])
+        stats['cases'] += 1
+        stats['ciphertexts'] += ndp * v
+        stats['damaged_points'] += damaged
+        if log:
+            log.write('eg case %d: ndp=%d v=%d damaged=%d\n' % (stats['cases'], ndp, v, damaged))
+    if make_backend:
+        backend.close()
+    return stats
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--seconds', type=float, default=120)
+    ap.add_argument('--seed', type=int, default=1)
+    ap.add_argument('--log', default=None)
+    args = ap.parse_args()
+    from conftest import Oracle
+    from drynx_b200 import Backend
+    backend, oracle = Backend(0), Oracle()
+    log = open(args.log, 'w') if args.log else None
+    t = time.time()
+    eg = fuzz_elgamal(None, oracle, args.seed, args.seconds * 0.15, log, make_backend=lambda: Backend(0))
+    rp = fuzz_rangeproofs(backend, oracle, args.seed, args.seconds * 0.85, log)
+    line = 'fuzz seed %d, %.0f s: ElGamal %s; range proofs %s; 0 mismatches' % (args.seed, time.time() - t, eg, rp)
+    print(line)
+    if log:
+        log.write(line + '\n')
+        log.close()
+    backend.close()
+
+
+if __name__ == '__main__':
+    main()
