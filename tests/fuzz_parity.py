@@ -148,6 +148,101 @@ def fuzz_rangeproofs(backend, oracle, seed, seconds, log=None, max_cases=None, t
     return stats
 
 
+def fuzz_mixed_batches(backend, oracle, seed, seconds, log=None, max_cases=None, threads=None):
+    """One call over several signature sets: per-proof (set, l), commit-only proofs (u = l = 0,
+    lib/range/range_proof.go:322-324, :508-510) in between, some proofs verified with another l than they were made
+    with. The oracle judges each (set, l) group on its own."""
+    g = np.random.default_rng(seed ^ 0xba7c4)
+    threads = threads or min(16, os.cpu_count() or 1)
+    deadline = time.time() + seconds
+    stats = {'cases': 0, 'proofs_verified': 0, 'accepted': 0, 'rejected': 0, 'commit_only': 0, 'wrong_l': 0}
+    while time.time() < deadline and (max_cases is None or stats['cases'] < max_cases):
+        sk = int.from_bytes(_scalar_bytes(g, 1), 'big') or 1
+        P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+        backend.set_pubkey(P)
+        sets = {}
+        for sid in g.choice(np.arange(64, 128), size=int(g.integers(1, 4)), replace=False):
+            ns, u = int(g.integers(1, 5)), int(g.choice(SHAPES_U))
+            xs = [int.from_bytes(_scalar_bytes(g, 1), 'big') or 1 for _ in range(ns)]
+            Y, A = oracle.make_sigs(xs, u)
+            backend.set_signatures(int(sid), ns, u, Y, A)
+            sets[int(sid)] = (ns, u, Y, A)
+        n = int(g.integers(1, 49))
+        plan = []
+        for _ in range(n):
+            if g.integers(0, 6) == 0:
+                plan.append((-1, 0, int(g.integers(0, 1000))))
+                continue
+            sid = int(g.choice(list(sets)))
+            u = sets[sid][1]
+            lmax = 1
+            while lmax < 6 and u ** (lmax + 1) < (1 << 32):
+                lmax += 1
+            l = int(g.integers(1, lmax + 1))
+            top = u ** l
+            s_ = int(g.integers(0, top)) if g.integers(0, 8) else int(top + g.integers(0, top))
+            plan.append((sid, l, s_))
+        sids = [p[0] for p in plan]; ls = [p[1] for p in plan]; secrets = [p[2] for p in plan]
+        rs = _scalar_bytes(g, n)
+        cts = backend.encrypt_int_vector(secrets, rs).tobytes()
+        rnd = [b'' if sid < 0 else _scalar_bytes(g, len(R.to_base(s_, sets[sid][1], l)) * (3 + sets[sid][0])) for sid, l, s_ in plan]
+        opts = {'rp_create_path': int(g.integers(0, 4)), 'rp_verify_path': int(g.choice([0, 1, 2])),
+                'rp_ucode_lanes': int(g.choice([0, 4, 8])), 'rp_ucode_mode': int(g.choice([0, 1, 2])),
+                'rp_verify_gt': int(g.choice([0, 2]))}
+        for k, v in opts.items():
+            backend.set_option(k, v)
+        try:
+            proofs, off = backend.create_range_proofs(sids, {k: v[0] for k, v in sets.items()}, {k: v[1] for k, v in sets.items()},
+                                                      ls, secrets, rs, cts, rnd)
+            pb = bytearray(proofs.tobytes())
+            for i, (sid, l, s_) in enumerate(plan):
+                mine = bytes(pb[int(off[i]):int(off[i + 1])])
+                if sid < 0:
+                    assert mine == cts[128 * i:128 * i + 128], ('commit-only bytes', seed, stats['cases'], i)
+                    continue
+                ns, u, Y, A = sets[sid]
+                want, _ = oracle.rp_create(ns, u, l, Y, A, P, [s_], rs[32 * i:32 * i + 32], cts[128 * i:128 * i + 128], [rnd[i]])
+                assert mine == want, ('created bytes', seed, stats['cases'], i, sid, ns, u, l, s_, opts)
+            ls_v = list(ls)
+            for i, (sid, l, s_) in enumerate(plan):
+                if sid < 0:
+                    continue
+                if g.integers(0, 20) == 0:
+                    ls_v[i] = l + 1 if l == 1 or g.integers(0, 2) else l - 1
+                    stats['wrong_l'] += 1
+                elif g.integers(0, 3) == 0:
+                    _mutate(g, pb, int(off[i]), int(off[i + 1]), None)
+            ok = list(backend.verify_range_proofs(sids, ls_v, bytes(pb), off))
+            ref = [None] * n
+            groups = {}
+            for i, (sid, l, s_) in enumerate(plan):
+                if sid < 0:
+                    ref[i] = 1
+                    stats['commit_only'] += 1
+                else:
+                    groups.setdefault((sid, ls_v[i]), []).append(i)
+            for (sid, l), idx in groups.items():
+                ns, u, Y, A = sets[sid]
+                blob = b''.join(bytes(pb[int(off[i]):int(off[i + 1])]) for i in idx)
+                goff = np.zeros(len(idx) + 1, np.uint64)
+                for k, i in enumerate(idx):
+                    goff[k + 1] = goff[k] + off[i + 1] - off[i]
+                r = oracle.rp_verify(ns, u, l, Y, P, blob, goff, threads=threads)
+                for k, i in enumerate(idx):
+                    ref[i] = int(r[k])
+            assert ok == ref, ('accept bits', seed, stats['cases'], plan, ls_v, opts, ok, ref)
+        finally:
+            for k in opts:
+                backend.set_option(k, 0)
+        stats['cases'] += 1
+        stats['proofs_verified'] += n
+        stats['accepted'] += sum(ref)
+        stats['rejected'] += n - sum(ref)
+        if log:
+            log.write('mixed case %d: %d sets, n=%d %s accepted %d/%d\n' % (stats['cases'], len(sets), n, opts, sum(ref), n))
+    return stats
+
+
 def fuzz_elgamal(backend, oracle, seed, seconds, log=None, max_cases=None, threads=None, make_backend=None):
     g = np.random.default_rng(seed ^ 0x5eed)
     threads = threads or min(16, os.cpu_count() or 1)
@@ -223,8 +318,9 @@ def main():
     log = open(args.log, 'w') if args.log else None
     t = time.time()
     eg = fuzz_elgamal(None, oracle, args.seed, args.seconds * 0.15, log, make_backend=lambda: Backend(0))
-    rp = fuzz_rangeproofs(backend, oracle, args.seed, args.seconds * 0.85, log)
-    line = 'fuzz seed %d, %.0f s: ElGamal %s; range proofs %s; 0 mismatches' % (args.seed, time.time() - t, eg, rp)
+    rp = fuzz_rangeproofs(backend, oracle, args.seed, args.seconds * 0.45, log)
+    mx = fuzz_mixed_batches(backend, oracle, args.seed, args.seconds * 0.40, log)
+    line = 'fuzz seed %d, %.0f s: ElGamal %s; range proofs %s; mixed batches %s; 0 mismatches' % (args.seed, time.time() - t, eg, rp, mx)
     print(line)
     if log:
         log.write(line + '\n')

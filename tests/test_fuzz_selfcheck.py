@@ -26,13 +26,28 @@ class OracleAsBackend:
         return np.frombuffer(self.o.encrypt(self.P, m, r), np.uint8)
 
     def create_range_proofs(self, sids, ns_of, u_of, ls, secrets, rs, cts, rnd):
-        ns, u, Y, A = self.sets[sids[0]]
-        proofs, off = self.o.rp_create(ns, u, ls[0], Y, A, self.P, secrets, rs, cts, rnd)
-        return np.frombuffer(proofs, np.uint8), off
+        parts = []
+        for i, sid in enumerate(sids):
+            if sid < 0:
+                parts.append(bytes(cts[128 * i:128 * i + 128]))
+                continue
+            ns, u, Y, A = self.sets[sid]
+            one, _ = self.o.rp_create(ns, u, ls[i], Y, A, self.P, [secrets[i]], rs[32 * i:32 * i + 32], cts[128 * i:128 * i + 128], [rnd[i]])
+            parts.append(one)
+        off = np.zeros(len(sids) + 1, np.uint64)
+        off[1:] = np.cumsum([len(x) for x in parts])
+        return np.frombuffer(b''.join(parts), np.uint8), off
 
     def verify_range_proofs(self, sids, ls, proofs, off):
-        ns, u, Y, A = self.sets[sids[0]]
-        return self.o.rp_verify(ns, u, ls[0], Y, self.P, proofs, off, threads=4)
+        ok = []
+        for i, sid in enumerate(sids):
+            if sid < 0:
+                ok.append(1)
+                continue
+            ns, u, Y, A = self.sets[sid]
+            one = bytes(proofs[int(off[i]):int(off[i + 1])])
+            ok.append(int(self.o.rp_verify(ns, u, ls[i], Y, self.P, one, np.array([0, len(one)], np.uint64))[0]))
+        return np.array(ok, np.uint8)
 
     def aggregate(self, vectors):
         rc, out = self.o.aggregate(vectors)
@@ -57,3 +72,8 @@ def test_fuzzer_plumbing_rangeproofs(oracle):
 def test_fuzzer_plumbing_elgamal(oracle):
     stats = fuzz_parity.fuzz_elgamal(None, oracle, 5, seconds=60, max_cases=6, threads=4, make_backend=lambda: OracleAsBackend(oracle))
     assert stats['cases'] == 6 and stats['ciphertexts'] > 0
+
+
+def test_fuzzer_plumbing_mixed_batches(oracle):
+    stats = fuzz_parity.fuzz_mixed_batches(OracleAsBackend(oracle), oracle, 5, seconds=120, max_cases=2, threads=4)
+    assert stats['cases'] == 2 and stats['proofs_verified'] == stats['accepted'] + stats['rejected']

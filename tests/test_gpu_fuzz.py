@@ -17,3 +17,8 @@ def test_fuzz_elgamal(oracle):
     from drynx_b200 import Backend
     stats = fuzz_parity.fuzz_elgamal(None, oracle, 21, seconds=60, max_cases=10, make_backend=lambda: Backend(0))
     assert stats['cases'] == 10
+
+
+def test_fuzz_mixed_batches(backend, oracle):
+    stats = fuzz_parity.fuzz_mixed_batches(backend, oracle, 31, seconds=60, max_cases=5)
+    assert stats['cases'] == 5 and stats['rejected'] > 0 and stats['accepted'] > 0
