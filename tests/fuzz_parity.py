@@ -243,6 +243,122 @@ def fuzz_mixed_batches(backend, oracle, seed, seconds, log=None, max_cases=None,
     return stats
 
 
+def _special_scalars():
+    """Scalars around the places where the device code branches: zero, the group order's neighbourhood, the
+    endomorphism's eigenvalue lambda = 36u^4 - 1 and the lattice basis of its split, window and limb boundaries."""
+    u = R.u
+    lam = 36 * u ** 4 - 1
+    a1, a2 = 6 * u * u + 2 * u, 2 * u + 1
+    out = [0, 1, 2, 3, R.n - 1, R.n - 2, lam, lam + 1, lam - 1, R.n - lam, (lam * lam) % R.n, a1, a2, a1 + a2,
+           (a1 * lam) % R.n, (a2 * lam) % R.n, 1 << 127, (1 << 127) - 1, 1 << 128, (1 << 128) + 1, (1 << 128) - 1,
+           (1 << 192) - 1, 1 << 253, R.n >> 1, (R.n >> 1) + 1]
+    out += [(1 << (32 * k)) - 1 for k in range(1, 8)] + [1 << (32 * k) for k in range(1, 8)]
+    out += [int('f' * k, 16) << (4 * j) for k in (1, 2, 8) for j in (0, 4, 60)]
+    return [v % R.n for v in out]
+
+
+def fuzz_group_ops(backend, oracle, seed, seconds, log=None, max_cases=None, threads=None):
+    """Variable-base G1 products (endomorphism split), the ciphertext-by-scalar product, key switching, Schnorr
+    verification and the proof.Rep relations against the oracle, with the special scalars above mixed in and some
+    points damaged."""
+    g = np.random.default_rng(seed ^ 0x9047)
+    threads = threads or min(16, os.cpu_count() or 1)
+    deadline = time.time() + seconds
+    special = _special_scalars()
+    stats = {'cases': 0, 'g1_mul': 0, 'ct_scalar_mul': 0, 'key_switch': 0, 'schnorr': 0, 'rep': 0}
+
+    def scalars(k):
+        vals = [int.from_bytes(_scalar_bytes(g, 1), 'big') if g.integers(0, 3) else int(g.choice(len(special))) for _ in range(k)]
+        vals = [special[v] if v < len(special) else v for v in vals]
+        return vals, b''.join(v.to_bytes(32, 'big') for v in vals)
+
+    def points(k):
+        ks = _scalar_bytes(g, k)
+        gen = R.g1_to_bytes(R.G1_GEN)
+        return backend.g1_mul(ks, gen * k).tobytes()
+
+    while time.time() < deadline and (max_cases is None or stats['cases'] < max_cases):
+        k = int(g.integers(1, 40))
+        # a) k * P
+        vals, sc = scalars(k)
+        pts = points(k)
+        got = backend.g1_mul(sc, pts).tobytes()
+        for i in range(k):
+            want = oracle.g1_mul(sc[32 * i:32 * i + 32], pts[64 * i:64 * i + 64])
+            assert got[64 * i:64 * i + 64] == want, ('g1_mul', seed, stats['cases'], hex(vals[i]))
+        stats['g1_mul'] += k
+        # b) MulCipherTextbyScalar
+        sk = int.from_bytes(_scalar_bytes(g, 1), 'big') or 1
+        P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+        backend.set_pubkey(P)
+        cts = bytearray(backend.encrypt_int_vector([int(x) for x in g.integers(-1000, 1000, size=k)], _scalar_bytes(g, k)).tobytes())
+        damaged = g.integers(0, 5) == 0
+        if damaged:
+            cts[int(g.integers(0, len(cts)))] ^= 1 << int(g.integers(0, 8))
+        vals, sc = scalars(k)
+        rc, want = oracle.ct_scalar_mul(sc, bytes(cts), threads=threads)
+        try:
+            got = backend.ct_scalar_mul(sc, bytes(cts)).tobytes()
+            refused = False
+        except Exception:
+            refused = True
+        assert refused == (rc != 0) == bool(damaged), ('ct_scalar_mul refusal', seed, stats['cases'], rc, damaged)
+        if not refused:
+            assert got == want, ('ct_scalar_mul', seed, stats['cases'])
+        stats['ct_scalar_mul'] += k
+        # c) key switching contributions
+        Q = points(1)
+        backend.set_target_pubkey(Q)
+        skv, skb = scalars(1)
+        rbs = points(k)
+        vs_v, vs = scalars(k)
+        rc, wcv, wneg = oracle.key_switch(Q, skb, rbs, vs, threads=threads)
+        cv, neg = backend.key_switch(skb, rbs, vs, want_rb_neg=True)
+        assert rc == 0 and cv.tobytes() == wcv and neg.tobytes() == wneg, ('key_switch', seed, stats['cases'], hex(skv[0]))
+        stats['key_switch'] += k
+        # d) Schnorr signatures, some of them damaged
+        pubs, sigs, msgs = [], [], []
+        for i in range(k):
+            x = int.from_bytes(_scalar_bytes(g, 1), 'big') or 1
+            xb = x.to_bytes(32, 'big')
+            pub = oracle.g1_mul(xb, R.g1_to_bytes(R.G1_GEN))
+            msg = g.bytes(int(g.integers(0, 80)))
+            sig = bytearray(oracle.schnorr_sign(xb, _scalar_bytes(g, 1), pub, msg))
+            c = int(g.integers(0, 6))
+            if c == 0:
+                sig[int(g.integers(0, 96))] ^= 1 << int(g.integers(0, 8))
+            elif c == 1:
+                sig[64:96] = b'\xff' * 32
+            elif c == 2:
+                msg = msg + b'x'
+            pubs.append(pub); sigs.append(bytes(sig)); msgs.append(msg)
+        assert list(backend.schnorr_verify(pubs, sigs, msgs)) == list(oracle.schnorr_verify(pubs, sigs, msgs, threads=threads)), \
+            ('schnorr', seed, stats['cases'])
+        stats['schnorr'] += k
+        # e) proof.Rep relations: commit, respond, verify; a third of the responses damaged
+        nterms = int(g.integers(1, 5))
+        xv, xs = scalars(k * nterms)
+        vv, vs = scalars(k * nterms)
+        bases = points(k * nterms)
+        rc, V = oracle.rep_commit(nterms, vs, bases, threads=threads)
+        assert rc == 0 and backend.rep_commit(nterms, vs, bases).tobytes() == V, ('rep_commit', seed, stats['cases'])
+        rc, Pp = oracle.rep_commit(nterms, xs, bases, threads=threads)
+        cv_, chal = scalars(k)
+        resp = oracle.rep_respond(nterms, vs, chal, xs)
+        assert backend.rep_respond(nterms, vs, chal, xs).tobytes() == resp, ('rep_respond', seed, stats['cases'])
+        resp = bytearray(resp)
+        for i in range(k):
+            if g.integers(0, 3) == 0:
+                resp[32 * nterms * i + 31] ^= 1
+        want = oracle.rep_verify(nterms, bytes(resp), chal, bases, Pp, V, threads=threads)
+        assert list(backend.rep_verify(nterms, bytes(resp), chal, bases, Pp, V)) == list(want), ('rep_verify', seed, stats['cases'])
+        stats['rep'] += k
+        stats['cases'] += 1
+        if log:
+            log.write('group case %d: k=%d nterms=%d\n' % (stats['cases'], k, nterms))
+    return stats
+
+
 def fuzz_elgamal(backend, oracle, seed, seconds, log=None, max_cases=None, threads=None, make_backend=None):
     g = np.random.default_rng(seed ^ 0x5eed)
     threads = threads or min(16, os.cpu_count() or 1)
@@ -319,8 +435,10 @@ def main():
     t = time.time()
     eg = fuzz_elgamal(None, oracle, args.seed, args.seconds * 0.15, log, make_backend=lambda: Backend(0))
     rp = fuzz_rangeproofs(backend, oracle, args.seed, args.seconds * 0.45, log)
-    mx = fuzz_mixed_batches(backend, oracle, args.seed, args.seconds * 0.40, log)
-    line = 'fuzz seed %d, %.0f s: ElGamal %s; range proofs %s; mixed batches %s; 0 mismatches' % (args.seed, time.time() - t, eg, rp, mx)
+    mx = fuzz_mixed_batches(backend, oracle, args.seed, args.seconds * 0.25, log)
+    gr = fuzz_group_ops(backend, oracle, args.seed, args.seconds * 0.15, log)
+    line = 'fuzz seed %d, %.0f s: ElGamal %s; range proofs %s; mixed batches %s; group operations %s; 0 mismatches' % (
+        args.seed, time.time() - t, eg, rp, mx, gr)
     print(line)
     if log:
         log.write(line + '\n')

@@ -59,6 +59,35 @@ class OracleAsBackend:
         # the oracle has one table: ask once and hand the fuzzer's second (oracle) call the same state by not growing it twice
         return self.o.decrypt(sk, ct, with_neg=with_neg)
 
+    def g1_mul(self, k, pt):
+        k, pt = bytes(k), bytes(pt)
+        return np.frombuffer(b''.join(self.o.g1_mul(k[32 * i:32 * i + 32], pt[64 * i:64 * i + 64]) for i in range(len(k) // 32)), np.uint8)
+
+    def ct_scalar_mul(self, sc, cts):
+        rc, out = self.o.ct_scalar_mul(sc, cts)
+        if rc:
+            raise ValueError('malformed point')
+        return np.frombuffer(out, np.uint8)
+
+    def set_target_pubkey(self, Q):
+        self.Q = bytes(Q)
+
+    def key_switch(self, sk, rbs, vs, want_rb_neg=False):
+        rc, cv, neg = self.o.key_switch(self.Q, sk, rbs, vs)
+        return np.frombuffer(cv, np.uint8), np.frombuffer(neg, np.uint8)
+
+    def schnorr_verify(self, pubs, sigs, msgs):
+        return self.o.schnorr_verify(pubs, sigs, msgs)
+
+    def rep_commit(self, nterms, sc, pts):
+        return np.frombuffer(self.o.rep_commit(nterms, sc, pts)[1], np.uint8)
+
+    def rep_respond(self, per, v, chal, x):
+        return np.frombuffer(self.o.rep_respond(per, v, chal, x), np.uint8)
+
+    def rep_verify(self, nterms, resp, chal, bases, P, V):
+        return self.o.rep_verify(nterms, resp, chal, bases, P, V)
+
     def close(self):
         pass
 
@@ -77,3 +106,8 @@ def test_fuzzer_plumbing_elgamal(oracle):
 def test_fuzzer_plumbing_mixed_batches(oracle):
     stats = fuzz_parity.fuzz_mixed_batches(OracleAsBackend(oracle), oracle, 5, seconds=120, max_cases=2, threads=4)
     assert stats['cases'] == 2 and stats['proofs_verified'] == stats['accepted'] + stats['rejected']
+
+
+def test_fuzzer_plumbing_group_operations(oracle):
+    stats = fuzz_parity.fuzz_group_ops(OracleAsBackend(oracle), oracle, 5, seconds=120, max_cases=2, threads=4)
+    assert stats['cases'] == 2 and stats['rep'] > 0

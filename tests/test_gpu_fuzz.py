@@ -22,3 +22,8 @@ def test_fuzz_elgamal(oracle):
 def test_fuzz_mixed_batches(backend, oracle):
     stats = fuzz_parity.fuzz_mixed_batches(backend, oracle, 31, seconds=60, max_cases=5)
     assert stats['cases'] == 5 and stats['rejected'] > 0 and stats['accepted'] > 0
+
+
+def test_fuzz_group_operations(backend, oracle):
+    stats = fuzz_parity.fuzz_group_ops(backend, oracle, 41, seconds=60, max_cases=8)
+    assert stats['cases'] == 8
