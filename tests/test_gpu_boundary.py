@@ -197,3 +197,37 @@ def test_two_devices_in_one_process(oracle, rng):
     for dev in (0, 1):
         ok, want = results[dev]
         assert [i for i in range(n) if not ok[i]] == [17] and want == [1, 0, 1]
+
+
+def test_empty_inputs_on_every_entry_point(backend, oracle, rng):
+    """n = 0 (an empty CipherVector, no proofs, no signatures ...) is a successful call that launches nothing and
+    touches no buffer; the reference's loops over empty slices do the same (e.g. lib/range/range_proof.go:171-205
+    ranges over the proof list, unlynx CipherVector.Add over the vector)."""
+    P = R.g1_to_bytes(R.g1_mul(rng.scalar(), R.G1_GEN))
+    backend.set_pubkey(P)
+    backend.set_target_pubkey(P)
+    launches = backend.launches
+    skb = (5).to_bytes(32, 'big')
+    assert backend.encrypt_int_vector([], b'').size == 0
+    assert backend.encrypt_scalar_vector(b'', b'').size == 0
+    assert backend.aggregate([b'', b'', b'']).size == 0                 # three providers, empty vectors
+    zero_dps = backend.aggregate([])                                      # no provider at all
+    assert zero_dps.size == 0
+    assert backend.decrypt_int_vector(skb, b'').size == 0
+    assert backend.decrypt_check_zero(skb, b'').size == 0
+    assert backend.ct_scalar_mul(b'', b'').size == 0
+    assert backend.key_switch(skb, b'', b'').size == 0
+    assert backend.shuffle_rerandomize([], [], []) == []
+    assert backend.schnorr_verify([], [], []).size == 0
+    assert backend.rep_commit(2, b'', b'').size == 0
+    assert backend.rep_respond(2, b'', b'', b'').size == 0
+    assert backend.rep_verify(2, b'', b'', b'', b'', b'').size == 0
+    assert backend.g1_mul(b'', b'').size == 0 and backend.g2_mul(b'', b'').size == 0
+    proofs, off = backend.create_range_proofs([], {}, {}, [], [], b'', b'', [])
+    assert proofs.size == 0 and list(off) == [0]
+    assert backend.verify_range_proofs([], [], b'', off).size == 0
+    assert backend.reduce_rows(np.empty((0, 4), np.int64), 3).shape == (0, 5)
+    assert backend.launches == launches
+    # a provider vector of zero ciphertexts next to the aggregate of one provider: the identity of the fold
+    ct = backend.encrypt_int_vector([7, -7], rng.scalars_bytes(2)).tobytes()
+    assert backend.aggregate([ct]).tobytes() == ct
