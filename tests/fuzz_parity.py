@@ -359,6 +359,88 @@ def fuzz_group_ops(backend, oracle, seed, seconds, log=None, max_cases=None, thr
     return stats
 
 
+def fuzz_misc(backend, oracle, seed, seconds, log=None, max_cases=None, threads=None, make_backend=None):
+    """What the other families leave out: EncryptScalar, DecryptCheckZero, the shuffle's re-randomisation, the
+    edwards25519 suite (full 256-bit little-endian scalars, reduced mod l like SetBytes) and the plaintext reductions
+    against numpy's wrapping int64 arithmetic (lib/encoding/sum.go:19-23, mean.go:19-24, variance.go:19-27)."""
+    g = np.random.default_rng(seed ^ 0x315c)
+    threads = threads or min(16, os.cpu_count() or 1)
+    deadline = time.time() + seconds
+    special = _special_scalars()
+    stats = {'cases': 0, 'encrypt_scalar': 0, 'shuffle_lines': 0, 'ed_ciphertexts': 0, 'reduced_rows': 0}
+    backend = make_backend() if make_backend else backend
+    oracle.ed_dlog_reset()
+    ed_base = None
+    while time.time() < deadline and (max_cases is None or stats['cases'] < max_cases):
+        k = int(g.integers(1, 30))
+        sk = int.from_bytes(_scalar_bytes(g, 1), 'big') or 1
+        skb = sk.to_bytes(32, 'big')
+        P = R.g1_to_bytes(R.g1_mul(sk, R.G1_GEN))
+        backend.set_pubkey(P)
+        # a) EncryptScalar with special scalars as messages and as randomness
+        ms = b''.join((special[int(g.integers(0, len(special)))] if g.integers(0, 3) == 0 else int.from_bytes(_scalar_bytes(g, 1), 'big')).to_bytes(32, 'big')
+                      for _ in range(k))
+        rs = b''.join((special[int(g.integers(0, len(special)))] if g.integers(0, 3) == 0 else int.from_bytes(_scalar_bytes(g, 1), 'big')).to_bytes(32, 'big')
+                      for _ in range(k))
+        assert backend.encrypt_scalar_vector(ms, rs).tobytes() == oracle.encrypt_scalar(P, ms, rs, threads=threads), ('encrypt_scalar', seed, stats['cases'])
+        stats['encrypt_scalar'] += k
+        # b) DecryptCheckZero on a vector with zeros in it
+        vals = [0 if g.integers(0, 3) == 0 else int(g.integers(-50, 50)) for _ in range(k)]
+        cts = backend.encrypt_int_vector(vals, _scalar_bytes(g, k)).tobytes()
+        assert list(backend.decrypt_check_zero(skb, cts)) == list(oracle.decrypt_check_zero(skb, cts)), ('check_zero', seed, stats['cases'])
+        # c) shuffle + re-randomisation of k lines of nq ciphertexts
+        nq = int(g.integers(1, 6))
+        lines = [backend.encrypt_int_vector([int(x) for x in g.integers(-9, 9, size=nq)], _scalar_bytes(g, nq)).tobytes() for _ in range(k)]
+        betas = [_scalar_bytes(g, nq) for _ in range(k)]
+        pi = [int(x) for x in g.permutation(k)]
+        rc, want = oracle.shuffle_rerandomize(P, lines, betas, pi, threads=threads)
+        got = backend.shuffle_rerandomize(lines, betas, pi)
+        assert rc == 0 and [bytes(x.tobytes()) for x in got] == want, ('shuffle', seed, stats['cases'])
+        stats['shuffle_lines'] += k
+        # d) edwards25519: encryption with unreduced scalars, aggregation, decryption (table state follows the calls)
+        esk = g.bytes(32)
+        if ed_base is None:
+            ed_base = oracle.ed_mul((1).to_bytes(32, 'little'))
+        eP = oracle.ed_mul(esk)
+        backend.ed_set_pubkey(eP)
+        ndp, v = int(g.integers(1, 12)), int(g.integers(1, 8))
+        msgs = [int(x) for x in g.integers(-2000, 2000, size=ndp * v)]
+        ers = g.bytes(32 * ndp * v)
+        ect = backend.ed_encrypt_int_vector(msgs, ers).tobytes()
+        assert ect == oracle.ed_encrypt(eP, msgs, ers, threads=threads), ('ed encrypt', seed, stats['cases'])
+        vecs = [ect[d * v * 64:(d + 1) * v * 64] for d in range(ndp)]
+        rc, eagg = oracle.ed_aggregate(vecs, threads=threads)
+        assert rc == 0 and backend.ed_aggregate(vecs).tobytes() == eagg, ('ed aggregate', seed, stats['cases'])
+        with_neg = bool(g.integers(0, 4))
+        dec, found = backend.ed_decrypt_int_vector(esk, eagg, with_neg=with_neg, return_found=True)
+        rc, ref, rfound = oracle.ed_decrypt(esk, eagg, with_neg=with_neg)
+        assert rc == 0 and list(found) == list(rfound), ('ed decrypt flags', seed, stats['cases'])
+        assert [int(x) for x, f in zip(dec, found) if f] == [int(x) for x, f in zip(ref, rfound) if f], ('ed decrypt', seed, stats['cases'])
+        stats['ed_ciphertexts'] += ndp * v
+        # e) plaintext reductions, wrap-around of int64 included
+        ndp, nrows = int(g.integers(1, 20)), int(g.integers(0, 600))
+        span = int(g.choice([3, 1 << 20, 1 << 40, (1 << 62) - 1]))
+        rows = g.integers(-span, span, size=(ndp, nrows), dtype=np.int64)
+        with np.errstate(over='ignore'):
+            ssum = rows.sum(axis=1)
+            q = (rows * rows).sum(axis=1)
+        cnt = np.full(ndp, nrows, np.int64)
+        assert (backend.reduce_rows(rows, 2) == np.stack([ssum, cnt, q], 1)).all(), ('reduce_rows', seed, stats['cases'])
+        assert (backend.reduce_rows(rows, 3) == np.stack([ssum, cnt, ssum, cnt, q], 1)).all(), ('reduce_rows 3', seed, stats['cases'])
+        qmin = int(g.integers(-5, 5))
+        qmax = qmin + int(g.integers(0, 40))
+        frows = g.integers(qmin, qmax + 1, size=(ndp, nrows), dtype=np.int64)
+        want = np.stack([np.bincount(frows[d] - qmin, minlength=qmax - qmin + 1) for d in range(ndp)]).astype(np.int64)
+        assert (backend.freq_count(frows, qmin, qmax) == want).all(), ('freq_count', seed, stats['cases'])
+        stats['reduced_rows'] += ndp * nrows
+        stats['cases'] += 1
+        if log:
+            log.write('misc case %d: k=%d nq=%d\n' % (stats['cases'], k, nq))
+    if make_backend:
+        backend.close()
+    return stats
+
+
 def fuzz_elgamal(backend, oracle, seed, seconds, log=None, max_cases=None, threads=None, make_backend=None):
     g = np.random.default_rng(seed ^ 0x5eed)
     threads = threads or min(16, os.cpu_count() or 1)
@@ -437,8 +519,9 @@ def main():
     rp = fuzz_rangeproofs(backend, oracle, args.seed, args.seconds * 0.45, log)
     mx = fuzz_mixed_batches(backend, oracle, args.seed, args.seconds * 0.25, log)
     gr = fuzz_group_ops(backend, oracle, args.seed, args.seconds * 0.15, log)
-    line = 'fuzz seed %d, %.0f s: ElGamal %s; range proofs %s; mixed batches %s; group operations %s; 0 mismatches' % (
-        args.seed, time.time() - t, eg, rp, mx, gr)
+    mi = fuzz_misc(None, oracle, args.seed, args.seconds * 0.15, log, make_backend=lambda: Backend(0))
+    line = 'fuzz seed %d, %.0f s: ElGamal %s; range proofs %s; mixed batches %s; group operations %s; other entry points %s; 0 mismatches' % (
+        args.seed, time.time() - t, eg, rp, mx, gr, mi)
     print(line)
     if log:
         log.write(line + '\n')

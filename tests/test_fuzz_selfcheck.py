@@ -88,6 +88,36 @@ class OracleAsBackend:
     def rep_verify(self, nterms, resp, chal, bases, P, V):
         return self.o.rep_verify(nterms, resp, chal, bases, P, V)
 
+    def encrypt_scalar_vector(self, m, r):
+        return np.frombuffer(self.o.encrypt_scalar(self.P, m, r), np.uint8)
+
+    def decrypt_check_zero(self, sk, ct):
+        return self.o.decrypt_check_zero(sk, ct)
+
+    def shuffle_rerandomize(self, lines, betas, pi):
+        return [np.frombuffer(x, np.uint8) for x in self.o.shuffle_rerandomize(self.P, lines, betas, pi)[1]]
+
+    def ed_set_pubkey(self, P):
+        self.eP = bytes(P)
+
+    def ed_encrypt_int_vector(self, m, r):
+        return np.frombuffer(self.o.ed_encrypt(self.eP, m, r), np.uint8)
+
+    def ed_aggregate(self, vectors):
+        return np.frombuffer(self.o.ed_aggregate(vectors)[1], np.uint8)
+
+    def ed_decrypt_int_vector(self, sk, ct, with_neg=True, return_found=False):
+        rc, out, found = self.o.ed_decrypt(sk, ct, with_neg=with_neg)
+        return out, found
+
+    def reduce_rows(self, rows, mode):
+        with np.errstate(over='ignore'):
+            s_, q, cnt = rows.sum(axis=1), (rows * rows).sum(axis=1), np.full(rows.shape[0], rows.shape[1], np.int64)
+        return np.stack([s_, cnt, q] if mode == 2 else [s_, cnt, s_, cnt, q], 1)
+
+    def freq_count(self, rows, qmin, qmax):
+        return np.stack([np.bincount(r - qmin, minlength=qmax - qmin + 1) for r in rows]).astype(np.int64)
+
     def close(self):
         pass
 
@@ -111,3 +141,8 @@ def test_fuzzer_plumbing_mixed_batches(oracle):
 def test_fuzzer_plumbing_group_operations(oracle):
     stats = fuzz_parity.fuzz_group_ops(OracleAsBackend(oracle), oracle, 5, seconds=120, max_cases=2, threads=4)
     assert stats['cases'] == 2 and stats['rep'] > 0
+
+
+def test_fuzzer_plumbing_other_entry_points(oracle):
+    stats = fuzz_parity.fuzz_misc(None, oracle, 5, seconds=120, max_cases=2, threads=4, make_backend=lambda: OracleAsBackend(oracle))
+    assert stats['cases'] == 2 and stats['ed_ciphertexts'] > 0

@@ -27,3 +27,9 @@ def test_fuzz_mixed_batches(backend, oracle):
 def test_fuzz_group_operations(backend, oracle):
     stats = fuzz_parity.fuzz_group_ops(backend, oracle, 41, seconds=60, max_cases=8)
     assert stats['cases'] == 8
+
+
+def test_fuzz_other_entry_points(oracle):
+    from drynx_b200 import Backend
+    stats = fuzz_parity.fuzz_misc(None, oracle, 51, seconds=60, max_cases=8, make_backend=lambda: Backend(0))
+    assert stats['cases'] == 8
