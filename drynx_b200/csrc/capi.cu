@@ -122,7 +122,7 @@ struct ProfSpan {
   cudaEvent_t a, b;
 };
 struct Profiler {
-  bool on = false;
+  int on = 0;  // 0 off, 1 every kernel, 2 only the pairing kernel of verification (k_pair_ucode / k_rp_verify_items)
   std::vector<ProfSpan> spans;
   std::map<std::string, std::pair<double, uint64_t>> totals;  // name -> (ms, launches)
 };
@@ -222,7 +222,7 @@ int check_launch(const char* what) {
 // Brackets the kernels `fn` launches with an event pair when profiling is on; always counts launches.
 template <class Fn>
 void timed_on(drx_ctx* c, cudaStream_t st, const char* name, Fn fn) {
-  if (!c->prof.on) {
+  if (!c->prof.on || (c->prof.on == 2 && strcmp(name, "k_pair_ucode") != 0 && strcmp(name, "k_rp_verify_items") != 0)) {
     c->launches += fn();
     return;
   }
@@ -438,7 +438,7 @@ int drx_profile_enable(drx_ctx* c, int on) {
   Guard g(c);
   prof_collect(c);
   c->prof.totals.clear();
-  c->prof.on = on != 0;
+  c->prof.on = on == 2 ? 2 : on != 0;
   return 0;
 }
 int drx_profile_get(drx_ctx* c, const char* kernel, double* total_ms, uint64_t* launches) {

@@ -67,7 +67,9 @@ int drx_set_option(drx_ctx* ctx, const char* name, int value);
 /* Per-kernel timing with CUDA events on the launching stream (bench.py's roofline leg): enable (which clears
  * the totals), run, then read the summed duration and launch count of a kernel by name (k_encrypt,
  * k_agg_partial, k_agg_final, k_decrypt, k_reduce_rows, k_rp_create_hdr, k_rp_create_items, k_rp_verify_hdr,
- * k_rp_verify_items or k_rp_verify_prep + k_pair_ucode + k_rp_verify_gt + k_rp_verify_finish, k_rp_flags). No counterpart in the reference (it times with onet monitor.TimeMeasure). */
+ * k_rp_verify_items or k_rp_verify_prep + k_pair_ucode + k_rp_verify_gt + k_rp_verify_finish, k_rp_flags). on = 1 brackets every kernel,
+ * on = 2 only the pairing kernel of verification (what bench.py's timed region uses: one event pair per step), 0 none.
+ * No counterpart in the reference (it times with onet monitor.TimeMeasure). */
 int drx_profile_enable(drx_ctx* ctx, int on);
 int drx_profile_get(drx_ctx* ctx, const char* kernel, double* total_ms, uint64_t* launches);
 
