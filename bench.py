@@ -383,7 +383,7 @@ def run_gpu(args):
     ms = e0.elapsed_time(e1)
     launches = be.launches + be2.launches - launches0
     clocks.stop_flag = True
-    KERNELS = ('k_reduce_rows', 'k_encrypt', 'k_rp_create_hdr', 'k_rp_create_items', 'k_rp_verify_hdr', 'k_rp_verify_items',
+    KERNELS = ('k_reduce_rows', 'k_encrypt', 'k_rp_create_hdr', 'k_rp_create_g2', 'k_rp_create_items', 'k_rp_verify_hdr', 'k_rp_verify_items',
                'k_rp_verify_prep', 'k_pair_ucode', 'k_rp_verify_gt', 'k_rp_verify_finish', 'k_rp_flags', 'k_agg_partial',
                'k_agg_final', 'k_decrypt')
 

@@ -138,6 +138,8 @@ struct RpSetHost {
 struct drx_ctx {
   int device = 0;
   cudaStream_t own_stream = nullptr, stream = nullptr, side_stream = nullptr, side_stream2 = nullptr;
+  // creation's two short kernels (header, G2 part) run on high-priority streams beside the GT kernel on `stream`, see run_create
+  cudaStream_t hi_stream = nullptr, hi_stream2 = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_fork0 = nullptr, ev_join = nullptr, ev_join2 = nullptr;  // fork/join of the side streams (independent small kernels)
   std::mutex mu;
   uint64_t launches = 0;
@@ -240,6 +242,16 @@ void timed(drx_ctx* c, const char* name, Fn fn) {
   timed_on(c, c->stream, name, fn);
 }
 void prof_collect(drx_ctx* c) {
+  // DRX_PROFILE_TIMELINE=1: every span's start (relative to the first span collected with it) and duration to stderr
+  static const bool timeline = getenv("DRX_PROFILE_TIMELINE") != nullptr;
+  if (timeline)
+    for (auto& sp : c->prof.spans) {
+      cudaEventSynchronize(sp.b);
+      float at = 0, ms = 0;
+      cudaEventElapsedTime(&at, c->prof.spans.front().a, sp.a);
+      cudaEventElapsedTime(&ms, sp.a, sp.b);
+      fprintf(stderr, "[drx timeline %p] %-22s start %9.3f ms  duration %8.3f ms\n", (void*)c, sp.name.c_str(), at, ms);
+    }
   for (auto& sp : c->prof.spans) {
     cudaEventSynchronize(sp.b);
     float ms = 0;
@@ -289,8 +301,12 @@ int drx_init(drx_ctx** out, int device, const uint8_t* g1_base, const uint8_t* g
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { delete c; return fail((int)e, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
   c->stream = c->own_stream;
+  int prio_least = 0, prio_greatest = 0;
+  cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
   if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&c->side_stream2, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithPriority(&c->hi_stream, cudaStreamNonBlocking, prio_greatest) != cudaSuccess ||
+      cudaStreamCreateWithPriority(&c->hi_stream2, cudaStreamNonBlocking, prio_greatest) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_join2, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreate(&c->ev_fork) != cudaSuccess ||  // a TIMING event on purpose, see run_verify (capi_rp.inc)
       cudaEventCreateWithFlags(&c->ev_fork0, cudaEventDisableTiming) != cudaSuccess ||
@@ -341,6 +357,8 @@ void drx_free(drx_ctx* c) {
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   if (c->side_stream) cudaStreamDestroy(c->side_stream);
   if (c->side_stream2) cudaStreamDestroy(c->side_stream2);
+  if (c->hi_stream) cudaStreamDestroy(c->hi_stream);
+  if (c->hi_stream2) cudaStreamDestroy(c->hi_stream2);
   if (c->ev_join2) cudaEventDestroy(c->ev_join2);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_fork0) cudaEventDestroy(c->ev_fork0);
