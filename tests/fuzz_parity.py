@@ -24,10 +24,8 @@ sys.path.insert(0, os.path.join(HERE, '..', 'oracle'))
 sys.path.insert(0, os.path.join(HERE, '..'))
 
 import bn256_ref as R  # noqa: E402
-from conftest import SplitMix  # noqa: E402
 
 SHAPES_U = [2, 3, 4, 5, 8, 10, 16]
-VERIFY_OPTIONS = ('rp_verify_path', 'rp_ucode_lanes', 'rp_ucode_mode', 'rp_verify_gt', 'rp_verify_hdr_early', 'rp_create_path')
 
 
 def _scalar_bytes(g, k):
