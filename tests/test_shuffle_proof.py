@@ -4,7 +4,6 @@ over rep_commit / rep_verify. CPU: the oracle engine accepts an honest proof and
 permutation, a wrong re-randomisation. GPU: the same proof through drx_rep_commit / drx_rep_verify is byte-identical
 and gets the same verdicts. kyber's own test (shuffle/shuffle_test.go as recalled: shuffle k pairs, prove, verify) is the
 first case."""
-import numpy as np
 import pytest
 
 import bn256_ref as R
