@@ -47,6 +47,36 @@ func (x *Ctx) SetSignatures(setID int, u int64, sigs []libdrynx.PublishSignature
 	return nil
 }
 
+// InitRangeProofSignature replaces libdrynxrange.InitRangeProofSignature (lib/range/range_proof.go:270-288; called per
+// server and range at simul/drynx_simul.go:293-295 and by the range-proof tests): the key pair is still drawn in Go (key.NewKeyPair),
+// Y = x B and the u signatures A_k = (x + k)^-1 g2 come from one device call. InitRangeProofSignatureDeterministic
+// (:249-267) is the same with x = 12.
+func (x *Ctx) InitRangeProofSignature(u int64) (libdrynx.PublishSignatureBytes, error) {
+	priv := libunlynx.SuiTe.Scalar().Pick(libunlynx.SuiTe.RandomStream())
+	return x.initRangeProofSignature(u, priv)
+}
+
+func (x *Ctx) InitRangeProofSignatureDeterministic(u int64) (libdrynx.PublishSignatureBytes, error) {
+	return x.initRangeProofSignature(u, libunlynx.SuiTe.Scalar().SetInt64(12))
+}
+
+func (x *Ctx) initRangeProofSignature(u int64, priv kyber.Scalar) (libdrynx.PublishSignatureBytes, error) {
+	var out libdrynx.PublishSignatureBytes
+	xb, err := priv.MarshalBinary()
+	if err != nil {
+		return out, err
+	}
+	Y, A := make([]byte, G1Len), make([]byte, G2Len*int(u))
+	if C.drx_rp_make_sigs(x.c, 1, C.int64_t(u), u8(xb), u8(Y), u8(A)) != 0 {
+		return out, lastErr()
+	}
+	pub := libunlynx.SuiTe.Point()
+	if err := pub.UnmarshalBinary(Y); err != nil {
+		return out, err
+	}
+	return libdrynx.PublishSignatureBytes{Signature: A, Public: pub}, nil
+}
+
 // drawProofRandomness draws, for one proof with nd digits and ns servers, the scalars
 // s_j, t_j, m_j, v_0j .. v_(ns-1)j for j = 0 .. nd-1 in the order CreatePredicateRangeProofForAllServ draws them
 // (lib/range/range_proof.go:377-390) from the suite's random stream.
