@@ -38,7 +38,7 @@ def _header_arity():
 
 def _go_calls():
     calls = []
-    for path in sorted(glob.glob(os.path.join(ROOT, 'go', 'gpubackend', '*.go'))):
+    for path in sorted(glob.glob(os.path.join(ROOT, 'go', 'gpubackend', '*.go'))) + [os.path.join(ROOT, 'INTEGRATION.md')]:
         src = open(path).read()
         src = re.sub(r'//.*', '', src)
         for m in re.finditer(r'\bC\.(drx_\w+)\s*\(', src):
