@@ -67,3 +67,15 @@ def test_go_shim_covers_the_hot_path_entry_points():
                  'drx_ct_scalar_mul', 'drx_shuffle_rerandomize', 'drx_schnorr_verify', 'drx_rep_commit',
                  'drx_rep_respond', 'drx_rep_verify'):
         assert name in used, name
+
+
+def test_ctypes_binding_has_the_header_arity():
+    """drynx_b200/_lib.py binds every declared function with as many argtypes as the declaration has parameters."""
+    import sys
+    sys.path.insert(0, ROOT)
+    from drynx_b200 import _lib
+    decl = _header_arity()
+    for name, (_, argtypes) in _lib.SIGNATURES.items():
+        assert name in decl, name
+        assert len(argtypes) == decl[name], '%s: %d argtypes, %d parameters' % (name, len(argtypes), decl[name])
+    assert set(decl) == set(_lib.SIGNATURES)
