@@ -11,7 +11,8 @@ scalars in Go), and EVERY group operation goes through the engine's rep_commit /
 drx_rep_commit / drx_rep_verify on the GPU: what a Go shim over the C ABI would call, with no new entry point.
 
 Group work per proof of k pairs: prover 7k + 3 fixed-base products and two sums of k + 1 terms; verifier 2k two-term
-sums, 3k one-term relations and two relations of 2k + 1 terms (k <= 2047 with the ABI's 4096-term limit)."""
+sums, 3k one-term relations and two sums of 2k + 1 terms. One thread walks a relation's terms, so the wide sums are
+taken up a tree of 16-term relations (`_sum`)."""
 import hashlib
 
 import numpy as np
@@ -53,9 +54,23 @@ def _mul_base(engine, scalars, base):
     return [out[64 * i:64 * i + 64] for i in range(len(scalars))]
 
 
-def _sum(engine, scalars, points):
-    """sum_j scalars[j] * points[j] as one relation."""
-    return engine.rep_commit(len(scalars), b''.join(sb(s) for s in scalars), b''.join(points))
+CHUNK = 16
+
+
+def _sum(engine, scalars, points, pad_point):
+    """sum_j scalars[j] * points[j]. A relation's terms are walked by one thread, so a wide sum goes up a tree: CHUNK
+    terms per relation (all relations of a level in one call), then the partial sums with scalar 1, until one is left.
+    `pad_point` (any valid point) fills the last chunk with zero terms."""
+    scalars, points = [sb(s) for s in scalars], list(points)
+    one, zero = sb(1), sb(0)
+    while len(scalars) > CHUNK:
+        pad = (-len(scalars)) % CHUNK
+        scalars += [zero] * pad
+        points += [pad_point] * pad
+        part = engine.rep_commit(CHUNK, b''.join(scalars), b''.join(points))
+        points = [part[64 * i:64 * i + 64] for i in range(len(scalars) // CHUNK)]
+        scalars = [one] * len(points)
+    return engine.rep_commit(len(scalars), b''.join(scalars), b''.join(points))
 
 
 def shuffle_pairs(engine, pi, g, h, beta, X, Y):
@@ -152,8 +167,8 @@ def pair_shuffle_prove(engine, pi, g, h, beta, X, Y, secrets, name=b'PairShuffle
     Gamma, A, C, U, W = base[0], base[1:1 + k], base[1 + k:1 + 2 * k], base[1 + 2 * k:1 + 3 * k], base[1 + 3 * k:1 + 4 * k]
     wbetasum = (tau0 + sum(w[i] * beta[pi[i]] for i in range(k))) % N
     coef = [(w[piinv[i]] - u[i]) % N for i in range(k)]
-    Lambda1 = _sum(engine, coef + [wbetasum], list(X) + [g])
-    Lambda2 = _sum(engine, coef + [wbetasum], list(Y) + [h])
+    Lambda1 = _sum(engine, coef + [wbetasum], list(X) + [g], g)
+    Lambda2 = _sum(engine, coef + [wbetasum], list(Y) + [h], g)
     p1 = Gamma + b''.join(A) + b''.join(C) + b''.join(U) + b''.join(W) + Lambda1 + Lambda2
     tr.put(p1)
     rho = tr.pub_rand(k)                                              # V step 2
@@ -208,11 +223,11 @@ def pair_shuffle_verify(engine, g, h, X, Y, Xbar, Ybar, proof, name=b'PairShuffl
             return False
         # (33): sigma_i Gamma == W_i + D_i
         ok33 = engine.rep_verify(1, b''.join(sb(v) for v in sigma), sb(-1) * k, Gamma * k, b''.join(D), b''.join(W))
-        # (31)-(35): Lambda + tau base == sum sigma_i bar_i - sum rho_i orig_i, as one relation of 2k + 1 terms each
-        resp = b''.join(sb(v) for v in sigma) + b''.join(sb(-v) for v in rho) + sb(-tau)
-        bases = b''.join(Xbar) + b''.join(X) + g + b''.join(Ybar) + b''.join(Y) + h
-        ok34 = engine.rep_verify(2 * k + 1, resp * 2, sb(0) * 2, bases, Lambda1 + Lambda2, Lambda1 + Lambda2)
-        ok = bool(np.all(np.asarray(ok33) == 1)) and bool(np.all(np.asarray(ok34) == 1))
+        # (31)-(35): Lambda == sum sigma_i bar_i - sum rho_i orig_i - tau base, the sums of 2k + 1 terms up a tree
+        coef = list(sigma) + [-v for v in rho] + [-tau]
+        Phi1 = _sum(engine, coef, list(Xbar) + list(X) + [g], g)
+        Phi2 = _sum(engine, coef, list(Ybar) + list(Y) + [h], g)
+        ok = bool(np.all(np.asarray(ok33) == 1)) and Phi1 == Lambda1 and Phi2 == Lambda2
         if ok and link_simple_shuffle:
             # R_i = A_i + lambda B_i with B_i = rho_i g - U_i; S_i = C_i + lambda D_i
             sc = b''.join(sb(1) + sb(lam * rho[i]) + sb(-lam) for i in range(k))
