@@ -884,6 +884,7 @@ int drx_schnorr_verify(drx_ctx* c, size_t n, const uint8_t* pub, const uint8_t* 
 }
 
 // ---- proof.Rep relations (obfuscation and key-switch proofs): commit, respond, verify
+static const int kRepTreeMinTerms = 33;  // drx_rep_commit sums relations at least this wide in two levels
 static const int kRepMaxTerms = 4096;  // the widest use is the list compression of the shuffle proof: one term per ciphertext of a line
 int drx_rep_commit_dev(drx_ctx* c, size_t n, int nterms, const uint8_t* d_scalars, const uint8_t* d_points, uint8_t* d_out) {
   if (!c) return fail(-1, "null context");
@@ -902,6 +903,38 @@ int drx_rep_commit(drx_ctx* c, size_t n, int nterms, const uint8_t* scalars, con
   Arena& a = c->arena;
   a.plan_reset();
   const size_t nt = (size_t)nterms;
+  if (nterms >= kRepTreeMinTerms) {
+    // One thread walks the terms of a relation (~1.2 ms each), so a wide relation is summed in two levels: `chunk`
+    // terms per thread (chunk = the power of two at or above sqrt(nterms)), then the m partial sums with scalar 1.
+    // Rows are padded to m * chunk terms with zero scalars on the row's own first point.
+    size_t chunk = 8;
+    while (chunk * chunk < nt) chunk *= 2;
+    const size_t m = (nt + chunk - 1) / chunk, T = m * chunk;
+    std::vector<uint8_t> hs(n * T * 32, 0), hp(n * T * 64), ones(n * m * 32, 0);
+    for (size_t i = 0; i < n; i++) {
+      memcpy(&hs[i * T * 32], scalars + i * nt * 32, nt * 32);
+      memcpy(&hp[i * T * 64], points + i * nt * 64, nt * 64);
+      for (size_t j = nt; j < T; j++) memcpy(&hp[(i * T + j) * 64], points + i * nt * 64, 64);
+    }
+    for (size_t k = 0; k < n * m; k++) ones[k * 32 + 31] = 1;
+    size_t os = a.plan(n * T * 32), op = a.plan(n * T * 64), o1 = a.plan(n * m * 32), opart = a.plan(n * m * 64), oo = a.plan(n * 64);
+    RET(a.commit());
+    RET(reset_bad(c));
+    RET(h2d(c, a.at<void>(os), hs.data(), n * T * 32));
+    RET(h2d(c, a.at<void>(op), hp.data(), n * T * 64));
+    RET(h2d(c, a.at<void>(o1), ones.data(), n * m * 32));
+    timed(c, "k_rep_commit", [&] {
+      return launch_rep_commit(c->stream, n * m, (int)chunk, a.at<uint8_t>(os), a.at<uint8_t>(op), a.at<uint8_t>(opart), (int*)c->bad.p) +
+             launch_rep_commit(c->stream, n, (int)m, a.at<uint8_t>(o1), a.at<uint8_t>(opart), a.at<uint8_t>(oo), (int*)c->bad.p);
+    });
+    RET(check_launch("rep_commit"));
+    RET(d2h(c, out, a.at<void>(oo), n * 64));
+    RET(sync_out(c));  // the staging vectors above are read by the copies until here
+    int bad = 0;
+    RET(read_bad(c, &bad));
+    if (bad) return fail(-2, "drx_rep_commit: %d malformed points", bad);
+    return 0;
+  }
   size_t os = a.plan(n * nt * 32), op = a.plan(n * nt * 64), oo = a.plan(n * 64);
   RET(a.commit());
   RET(reset_bad(c));

@@ -216,8 +216,10 @@ int drx_schnorr_verify(drx_ctx* ctx, size_t n, const uint8_t* pub, const uint8_t
  * data/data.go:69, lib/proof/structs_proofs.go:392-403: sum_j e_j*K_ij and sum_j e_j*C_ij per line i); the Neff
  * pair-shuffle argument that follows it (kyber shuffle.PairShuffle) consists of sums and checks of these two shapes
  * and runs over these calls as well (go/gpubackend/shuffle.go, tests/shuffle_proof.py). One device thread walks the terms
- * of a relation (~1.2 ms per term when n is small): callers with few, wide relations split them into a tree of 16-term
- * relations, as wideSum in go/gpubackend/shuffle.go does. The `_dev` forms only enqueue work:
+ * of a relation (~1.2 ms per term when n is small), so drx_rep_commit sums relations of 33 terms and more in two levels
+ * (chunks of about sqrt(nterms) terms, then the partial sums; same bytes). drx_rep_commit_dev and drx_rep_verify do not:
+ * callers with few, wide relations there split them themselves, as wideSum in go/gpubackend/shuffle.go does. The `_dev`
+ * forms only enqueue work:
  * drx_rep_commit_dev zeroes the row of a relation with a malformed point and counts it for drx_take_bad. */
 int drx_rep_commit(drx_ctx* ctx, size_t n, int nterms, const uint8_t* scalars /*n*nterms*32*/,
                    const uint8_t* points /*n*nterms*64*/, uint8_t* out /*n*64*/);

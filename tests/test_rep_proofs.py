@@ -230,3 +230,28 @@ def test_gpu_keyswitch_list_proof(backend, oracle, rng):
     bits = RP.keyswitch_verify(gpu, B, Q, publics, neg, t)
     assert list(bits) == list(RP.keyswitch_verify(cpu, B, Q, publics, neg, t))
     assert list(bits) == [i % 5 != 0 for i in range(n)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('nt,n', [(32, 3), (33, 3), (64, 2), (65, 5), (300, 2), (4096, 1)])
+def test_gpu_wide_relations_match_oracle(backend, oracle, rng, nt, n):
+    """drx_rep_commit sums relations of 33 terms and more in two levels (chunks, then the partial sums): the bytes are
+    those of the oracle's single loop on both sides of the threshold, at the chunk boundaries and at the widest
+    relation the ABI takes; zero scalars, the identity among the points and a whole chunk of zero terms included; a
+    malformed point anywhere is still an error of the call."""
+    sc = bytearray(rng.scalars_bytes(n * nt))
+    base = [_pt(rng.scalar()) for _ in range(min(nt, 24))]
+    pts = bytearray(b''.join(base[(i * 7 + i // 5) % len(base)] for i in range(n * nt)))
+    sc[0:32] = bytes(32)
+    pts[64:128] = bytes(64)
+    if nt >= 65:
+        sc[32 * 16:32 * 32] = bytes(32 * 16)                       # the second 16 terms of relation 0: all zero
+    got = backend.rep_commit(nt, bytes(sc), bytes(pts)).tobytes()
+    rc, want = oracle.rep_commit(nt, bytes(sc), bytes(pts), threads=8)
+    assert rc == 0 and got == want
+    bad = bytearray(pts)
+    bad[64 * (n * nt - 1) + 3] ^= 1                                 # the last point of the last relation
+    with pytest.raises(RuntimeError):
+        backend.rep_commit(nt, bytes(sc), bytes(bad))
+    with pytest.raises(RuntimeError):
+        backend.rep_commit(4097, bytes(32 * 4097), bytes(64 * 4097))
